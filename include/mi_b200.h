@@ -1,0 +1,257 @@
+/*
+ * mi_b200.h -- C ABI of libmi_b200.so: the B200-native volumetric path tracing
+ * hot path (volpath / volpathaos forward, prbvolpath / prb_volpathaos adjoint)
+ * of the mitsuba3-nasa fork.
+ *
+ * Every entry point below replaces one reference interface; the citation says
+ * which (paths relative to the reference checkout):
+ *
+ *   mib_scene_create / mib_scene_destroy
+ *       the flattened result of mi.load_dict(): PluginManager::create_object
+ *       (src/core/plugin.cpp:174-211) + Scene ctor (src/render/scene.cpp).
+ *   mib_scene_set_buffer / mib_scene_commit
+ *       params[key] = ...; params.update() -> parameters_changed()
+ *       (src/python/python/util.py:185-232, src/media/heterogeneous.cpp:176-178,
+ *        src/volumes/grid.cpp:306-319).
+ *   mib_render
+ *       SamplingIntegrator::render (src/render/integrator.cpp:150-397) and
+ *       ADIntegrator.render (src/python/python/ad/integrators/common.py:47-111).
+ *   mib_render_1
+ *       SamplingIntegrator::render_1 (src/render/integrator.cpp:399-743) and
+ *       ADIntegrator.render_1 (common.py:113-196).
+ *   mib_render_backward / mib_render_1_backward
+ *       RBIntegrator.render_backward / render_1_backward (common.py:828-1102).
+ *   mib_grad_get / mib_grad_zero
+ *       dr.grad(params[key]) after dr.backward().
+ *   mib_counters_get
+ *       no reference counterpart: exact event counters used for the roofline.
+ *
+ * Plain pointers and sizes only; no torch / pybind types.  All functions return
+ * 0 on success, non-zero on failure with a message in mib_last_error().
+ * "_dev" variants take / return device pointers (used by bench.py to time the
+ * kernels with inputs already resident in HBM).
+ */
+#ifndef MI_B200_H
+#define MI_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MIB_ABI_VERSION 3
+
+#define MIB_MAX_SHAPES   8
+#define MIB_MAX_MEDIA    4
+#define MIB_MAX_PHASES   4
+#define MIB_MAX_BSDFS    8
+#define MIB_MAX_EMITTERS 4
+#define MIB_MAX_BUFFERS  16
+
+/* ---- enums (plugin types become tags) ---- */
+enum { MIB_SPEC_MONO = 0, MIB_SPEC_RGB = 1, MIB_SPEC_MONO_POLARIZED = 2 };
+enum { MIB_INTEG_VOLPATH = 0, MIB_INTEG_VOLPATHAOS = 1,
+       MIB_INTEG_PRBVOLPATH = 2, MIB_INTEG_PRBVOLPATHAOS = 3 };
+enum { MIB_SHAPE_CUBE = 0, MIB_SHAPE_RECTANGLE = 1, MIB_SHAPE_SPHERE = 2 };
+enum { MIB_BSDF_NULL = 0, MIB_BSDF_DIFFUSE = 1 };
+enum { MIB_MEDIUM_HOMOGENEOUS = 0, MIB_MEDIUM_HETEROGENEOUS = 1 };
+enum { MIB_VOLUME_CONST = 0, MIB_VOLUME_GRID = 1 };
+enum { MIB_FILTER_NEAREST = 0, MIB_FILTER_TRILINEAR = 1 };
+enum { MIB_WRAP_REPEAT = 0, MIB_WRAP_MIRROR = 1, MIB_WRAP_CLAMP = 2 };
+enum { MIB_PHASE_ISOTROPIC = 0, MIB_PHASE_HG = 1, MIB_PHASE_RAYLEIGH = 2,
+       MIB_PHASE_TABPHASE = 3, MIB_PHASE_TABPHASE_POLARIZED = 4 };
+enum { MIB_EMITTER_CONSTANT = 0, MIB_EMITTER_DIRECTIONAL = 1, MIB_EMITTER_AREA = 2 };
+enum { MIB_SENSOR_PERSPECTIVE = 0, MIB_SENSOR_DISTANT = 1, MIB_SENSOR_RADIANCEMETER = 2 };
+enum { MIB_RFILTER_BOX = 0, MIB_RFILTER_GAUSSIAN = 1, MIB_RFILTER_TENT = 2 };
+enum { MIB_RNG_ARGS_LEFT_TO_RIGHT = 0, MIB_RNG_ARGS_RIGHT_TO_LEFT = 1 };
+
+/* ---- POD scene description.  Matrices are 4x4 row-major float. ---- */
+typedef struct mib_volume {
+    int32_t type;            /* MIB_VOLUME_* */
+    int32_t channels;        /* 1 or 3 */
+    float   value[3];        /* constvolume value (src/volumes/const.cpp:61-84) */
+    int32_t res[3];          /* grid resolution x,y,z (src/volumes/grid.cpp:156-299) */
+    int32_t filter;          /* MIB_FILTER_* */
+    int32_t wrap;            /* MIB_WRAP_* */
+    int32_t buffer;          /* index of the data buffer [z][y][x][c], -1 if none */
+    float   to_local[16];    /* world -> [0,1]^3 (src/render/volume.cpp:13-17) */
+    float   bbox_min[3];
+    float   bbox_max[3];
+    float   max_value;       /* filled by mib_scene_commit (grid.cpp:306-319) */
+} mib_volume;
+
+typedef struct mib_phase {
+    int32_t type;            /* MIB_PHASE_* */
+    float   g;               /* hg (src/phase/hg.cpp:50-62) */
+    float   depolarization;  /* rayleigh (src/phase/rayleigh.cpp:41-48) */
+    int32_t n_nodes;         /* tabulated: number of cos(theta) nodes */
+    int32_t buf_nodes;       /* buffer indices: cos(theta) nodes, m11, m12, m33, m34 */
+    int32_t buf_m11;
+    int32_t buf_m12;
+    int32_t buf_m33;
+    int32_t buf_m34;
+} mib_phase;
+
+typedef struct mib_medium {
+    int32_t type;            /* MIB_MEDIUM_* */
+    int32_t phase;           /* index into phases */
+    int32_t sample_emitters;
+    int32_t has_spectral_extinction;
+    float   scale;
+    mib_volume sigma_t;
+    mib_volume albedo;
+    float   max_density;     /* filled by mib_scene_commit (heterogeneous.cpp:163) */
+} mib_medium;
+
+typedef struct mib_bsdf {
+    int32_t type;            /* MIB_BSDF_* */
+    float   reflectance[3];  /* diffuse (src/bsdfs/diffuse.cpp) */
+} mib_bsdf;
+
+typedef struct mib_shape {
+    int32_t type;            /* MIB_SHAPE_* */
+    int32_t bsdf;            /* index into bsdfs */
+    int32_t interior_medium; /* -1: none */
+    int32_t exterior_medium; /* -1: none */
+    int32_t emitter;         /* area emitter index or -1 */
+    float   to_world[16];
+    float   to_object[16];
+    /* rectangle frame (src/shapes/rectangle.cpp:115-125): dp_du, dp_dv, n */
+    float   frame_s[3];
+    float   frame_t[3];
+    float   frame_n[3];
+    float   inv_surface_area;
+    /* sphere (src/shapes/sphere.cpp): world-space center / radius */
+    float   center[3];
+    float   radius;
+} mib_shape;
+
+typedef struct mib_emitter {
+    int32_t type;            /* MIB_EMITTER_* */
+    float   radiance[3];     /* constant radiance / directional irradiance / area radiance */
+    float   direction[3];    /* directional: to_world * (0,0,1) */
+    float   bsphere_center[3];
+    float   bsphere_radius;  /* after set_scene (constant.cpp:70-85, directional.cpp:98-108) */
+    int32_t shape;           /* area emitter: owning shape */
+} mib_emitter;
+
+typedef struct mib_sensor {
+    int32_t type;            /* MIB_SENSOR_* */
+    int32_t medium;          /* medium the sensor sits in, -1 none */
+    float   to_world[16];
+    float   sample_to_camera[16]; /* perspective (src/sensors/perspective.cpp:173-199) */
+    float   near_clip, far_clip;
+    float   principal_point_offset[2];
+    float   target[3];       /* distant: point target (src/sensors/distant.cpp:165-167) */
+    int32_t target_type;     /* 0 none, 1 point */
+    float   bsphere_center[3];
+    float   bsphere_radius;
+    int32_t needs_aperture_sample;
+    /* film (src/films/hdrfilm.cpp:245-273, src/render/film.cpp:10-51) */
+    int32_t film_width, film_height;
+    int32_t crop_offset_x, crop_offset_y, crop_width, crop_height;
+    int32_t rfilter;         /* MIB_RFILTER_* */
+    float   rfilter_radius;
+    float   rfilter_stddev;
+    int32_t sample_border;
+} mib_sensor;
+
+typedef struct mib_integrator {
+    int32_t type;            /* MIB_INTEG_* */
+    int32_t max_depth;       /* -1 = unbounded (integrator.cpp:1286-1293) */
+    int32_t rr_depth;
+    int32_t hide_emitters;
+    int32_t rng_arg_order;   /* MIB_RNG_ARGS_*  */
+    int32_t double_phase_quirk; /* volpath multiplies phase_weight twice (volpath.cpp:244,251) */
+} mib_integrator;
+
+typedef struct mib_scene_desc {
+    int32_t abi_version;     /* MIB_ABI_VERSION */
+    int32_t spectrum;        /* MIB_SPEC_* */
+    int32_t n_shapes, n_media, n_phases, n_bsdfs, n_emitters;
+    int32_t environment;     /* index of the constant environment emitter or -1 */
+    mib_shape      shapes[MIB_MAX_SHAPES];
+    mib_medium     media[MIB_MAX_MEDIA];
+    mib_phase      phases[MIB_MAX_PHASES];
+    mib_bsdf       bsdfs[MIB_MAX_BSDFS];
+    mib_emitter    emitters[MIB_MAX_EMITTERS];
+    mib_sensor     sensor;
+    mib_integrator integrator;
+    uint32_t sampler_base_seed; /* independent sampler 'seed' (sampler.cpp:12-20) */
+} mib_scene_desc;
+
+/* Event counters accumulated by the kernels (exact, per render call). */
+typedef struct mib_counters {
+    uint64_t n_samples;      /* camera paths */
+    uint64_t n_lookups;      /* gridvolume lookups (main walk + shadow walks) */
+    uint64_t n_real;         /* real medium scatter events */
+    uint64_t n_null;         /* null collisions in the main walk */
+    uint64_t n_nee_steps;    /* tentative collisions inside shadow walks */
+    uint64_t n_surface;      /* surface interactions handled */
+    double   kernel_ms;      /* CUDA-event time of the last render kernel(s) */
+    uint64_t n_launches;     /* kernels launched by the last call */
+} mib_counters;
+
+typedef struct mib_scene mib_scene;
+
+const char *mib_last_error(void);
+int  mib_abi_version(void);
+size_t mib_sizeof_scene_desc(void);
+
+/* device = CUDA ordinal the scene lives on (one process per GPU). */
+int  mib_scene_create(const mib_scene_desc *desc, int device, mib_scene **out);
+int  mib_scene_destroy(mib_scene *scene);
+/* Upload (copy) a float buffer (grid data, phase tables) into slot idx. */
+int  mib_scene_set_buffer(mib_scene *scene, int idx, const float *host, size_t count);
+int  mib_scene_get_buffer(mib_scene *scene, int idx, float *host, size_t count);
+/* Device pointer of a buffer (for torch-side updates without a host round trip). */
+int  mib_scene_buffer_dev(mib_scene *scene, int idx, float **dev, size_t *count);
+/* Replace the POD description (scalar parameter updates such as albedo, g, scale). */
+int  mib_scene_set_desc(mib_scene *scene, const mib_scene_desc *desc);
+/* Recompute derived data: grid maxima, majorants, table CDFs. Must be called
+   after set_buffer / set_desc and before rendering. */
+int  mib_scene_commit(mib_scene *scene);
+int  mib_scene_get_desc(mib_scene *scene, mib_scene_desc *out);
+
+/* Restrict rendering to the global lane range [lane_begin, lane_end) of the
+   wavefront (multi-GPU sharding by sample range). (0,0) = all. */
+int  mib_scene_set_lane_range(mib_scene *scene, uint64_t lane_begin, uint64_t lane_end);
+
+/* Forward render into the raw accumulation film [H][W][C] (C = 4: R,G,B,W for
+   rgb; I,Q,U,V for mono_polarized; C = 2: I,W for mono) and, if develop != 0,
+   the developed image [H][W][Cout] (Cout = 3 rgb, 1 mono, 4 mono_polarized).
+   out_host may be NULL (result stays on the device, see mib_film_dev). */
+int  mib_render(mib_scene *scene, uint32_t seed, uint32_t spp, int develop, float *out_host);
+int  mib_film_dev(mib_scene *scene, float **raw_dev, size_t *raw_count,
+                  float **developed_dev, size_t *developed_count);
+int  mib_film_develop(mib_scene *scene);      /* (re)develop after an external reduce */
+
+/* render_1: sums all samples, returns n_channels doubles normalised by
+   W*H*spp (mono: I; mono_polarized: I,Q,U,V). */
+int  mib_render_1(mib_scene *scene, uint32_t seed, uint32_t spp, double *out4);
+/* Un-normalised sums (for multi-GPU reduction before normalising). */
+int  mib_render_1_raw(mib_scene *scene, uint32_t seed, uint32_t spp, double *out4);
+
+/* Adjoint.  grad_in_host: [H][W][Cout] image gradient (render_backward) or 4
+   floats (render_1_backward: d loss / d (I,Q,U,V)).  Gradients accumulate
+   into per-parameter device buffers until mib_grad_zero. */
+int  mib_render_backward(mib_scene *scene, uint32_t seed, uint32_t spp, const float *grad_in_host);
+int  mib_render_1_backward(mib_scene *scene, uint32_t seed, uint32_t spp, const float *grad_in4);
+/* Gradient of buffer slot idx (same shape as the buffer). */
+int  mib_grad_get(mib_scene *scene, int idx, float *host, size_t count);
+int  mib_grad_dev(mib_scene *scene, int idx, float **dev, size_t *count);
+/* Gradients of scalar medium parameters: out[0..2] = d/d albedo (per channel),
+   out[3] = d/d sigma_t (const volume), for medium m. */
+int  mib_grad_get_scalar(mib_scene *scene, int medium, double *out4);
+int  mib_grad_zero(mib_scene *scene);
+
+int  mib_counters_get(mib_scene *scene, mib_counters *out);
+/* The CUDA stream the scene launches on (cudaStream_t as void*). */
+int  mib_scene_stream(mib_scene *scene, void **stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MI_B200_H */

@@ -1,0 +1,669 @@
+"""Host-side mirror of the reference's plugin tree for the volumetric hot path.
+
+`load_dict` builds a tree of `Plugin` nodes from nested dicts exactly as
+`mi.load_dict` does (src/core/python/xml_v.cpp:112-146): `'type'` keys select
+plugins, `{'type': 'ref', 'id': ...}` reuses an object, floats / rgb dicts are
+auto-wrapped into `uniform` / `srgb` textures and `constvolume`s
+(include/mitsuba/core/properties.h:341-386).  Plugin names, parameter names and
+defaults are those of the reference (citations next to each plugin below).
+`Scene.flatten()` turns the tree into the POD `mib_scene_desc` + float buffers
+consumed by the C ABI (include/mi_b200.h).
+"""
+import numpy as np
+
+from . import _abi as A
+from .transforms import ScalarTransform4f, coordinate_system
+
+RAY_EPSILON = 1500.0 * 2.0 ** -24   # include/mitsuba/core/math.h:17-23
+
+
+class PluginError(RuntimeError):
+    pass
+
+
+def _luminance(rgb):
+    # include/mitsuba/core/spectrum.h:431-434
+    return float(rgb[0] * 0.212671 + rgb[1] * 0.715160 + rgb[2] * 0.072169)
+
+
+class Plugin:
+    """One instantiated plugin.  `props` holds the parameters (defaults applied)."""
+    CATEGORY = {
+        'volpath': 'integrator', 'volpathaos': 'integrator', 'prbvolpath': 'integrator', 'prb_volpathaos': 'integrator',
+        'homogeneous': 'medium', 'heterogeneous': 'medium',
+        'gridvolume': 'volume', 'constvolume': 'volume',
+        'hg': 'phase', 'rayleigh': 'phase', 'isotropic': 'phase', 'tabphase': 'phase', 'tabphase_polarized': 'phase',
+        'mie': 'phase',
+        'lognormal': 'sizedistr', 'gamma': 'sizedistr', 'powerlaw': 'sizedistr', 'monodisperse': 'sizedistr',
+        'independent': 'sampler', 'hdrfilm': 'film',
+        'box': 'rfilter', 'gaussian': 'rfilter', 'tent': 'rfilter',
+        'perspective': 'sensor', 'distant': 'sensor', 'radiancemeter': 'sensor',
+        'constant': 'emitter', 'directional': 'emitter', 'area': 'emitter',
+        'cube': 'shape', 'rectangle': 'shape', 'sphere': 'shape',
+        'null': 'bsdf', 'diffuse': 'bsdf',
+        'uniform': 'texture', 'srgb': 'texture', 'rgb': 'texture', 'd65': 'texture',
+        'scene': 'scene',
+    }
+
+    def __init__(self, type_, props, children, id_=None):
+        self.type = type_
+        self.category = Plugin.CATEGORY[type_]
+        self.props = props          # plain values
+        self.children = children    # name -> Plugin
+        self.id = id_
+
+    def __repr__(self):
+        return "%s[%s]" % (self.type, ", ".join("%s=%r" % kv for kv in self.props.items()))
+
+
+class _Loader:
+    def __init__(self, variant):
+        self.variant = variant
+        self.by_id = {}
+        self.root_dict = None
+
+    def is_rgb(self):
+        return 'rgb' in self.variant
+
+    # -- generic dict -> Plugin --
+    def load(self, d, name=None):
+        if not isinstance(d, dict) or 'type' not in d:
+            raise PluginError("load_dict(): expected a dict with a 'type' key for %r" % (name,))
+        t = d['type']
+        if t == 'ref':
+            if d['id'] not in self.by_id:
+                # forward reference to a top-level object declared later in the dict
+                if self.root_dict is not None and isinstance(self.root_dict.get(d['id']), dict):
+                    self.by_id[d['id']] = self.load(self.root_dict[d['id']], d['id'])
+                else:
+                    raise PluginError("load_dict(): reference to unknown id '%s'" % d['id'])
+            return self.by_id[d['id']]
+        if t not in Plugin.CATEGORY:
+            raise PluginError("Plugin \"%s\" not found! (only the plugins of the volumetric hot path exist "
+                              "in this build, see DESIGN.md)" % t)
+        props, children = {}, {}
+        if t == 'scene' and self.root_dict is None:
+            self.root_dict = d
+        for k, v in d.items():
+            if k in ('type', 'id'):
+                continue
+            if isinstance(v, dict):
+                if t == 'scene' and k in self.by_id:
+                    children[k] = self.by_id[k]     # already instantiated through a forward reference
+                else:
+                    children[k] = self.load(v, k)
+            else:
+                props[k] = v
+        p = Plugin(t, props, children, d.get('id', name))
+        if p.id is not None and p.id not in self.by_id:
+            self.by_id[p.id] = p
+        return p
+
+
+# --------------------------------------------------------------------------
+# Property access with reference semantics: defaults + "unqueried property" errors
+# --------------------------------------------------------------------------
+class _Props:
+    def __init__(self, plugin):
+        self.p = plugin
+        self.queried = set()
+
+    def get(self, name, default=None, required=False):
+        self.queried.add(name)
+        if name in self.p.props:
+            return self.p.props[name]
+        if required:
+            raise PluginError("Property \"%s\" has not been specified! (plugin %s)" % (name, self.p.type))
+        return default
+
+    def has(self, name):
+        return name in self.p.props or name in self.p.children
+
+    def child(self, name):
+        self.queried.add(name)
+        return self.p.children.get(name)
+
+    def children_of(self, category):
+        out = []
+        for k, c in self.p.children.items():
+            if c.category == category:
+                self.queried.add(k)
+                out.append((k, c))
+        return out
+
+    def finish(self):
+        extra = (set(self.p.props) | set(self.p.children)) - self.queried
+        if extra:
+            raise PluginError("Error while loading \"%s\": unreferenced propert%s %s" %
+                              (self.p.type, "y" if len(extra) == 1 else "ies", sorted(extra)))
+
+
+def _to_transform(v):
+    if v is None:
+        return ScalarTransform4f()
+    return v if isinstance(v, ScalarTransform4f) else ScalarTransform4f(v)
+
+
+class Scene:
+    """Flattened scene + parameter map.  Mirrors the parts of mi.Scene the hot path needs."""
+
+    def __init__(self, root, variant):
+        self.root = root
+        self.variant = variant
+        self.spectrum = A.SPEC_MONO_POLARIZED if 'polarized' in variant else (A.SPEC_RGB if 'rgb' in variant else A.SPEC_MONO)
+        self.desc = A.SceneDesc()
+        self.buffers = {}      # slot -> np.float32 array (flat)
+        self.buffer_shapes = {}
+        self.params = {}       # dotted key -> accessor dict
+        self._n_buffers = 0
+        self._media_index = {}
+        self._phase_index = {}
+        self._bsdf_index = {}
+        self._flatten()
+
+    # ------------------------------------------------------------------
+    def _color(self, v, what):
+        """float | [r,g,b] | texture Plugin -> 3 floats for the current variant."""
+        if isinstance(v, Plugin):
+            pr = _Props(v)
+            if v.type in ('rgb', 'srgb'):
+                val = pr.get('value', required=True)
+                pr.finish()
+                val = np.broadcast_to(np.asarray(val, dtype=np.float64), (3,))
+                if self.spectrum == A.SPEC_RGB:
+                    return [float(x) for x in val]
+                lum = _luminance(val)
+                return [lum] * 3
+            if v.type == 'uniform':
+                val = float(pr.get('value', 1.0))
+                pr.finish()
+                return [val] * 3
+            if v.type == 'd65':
+                # mono / rgb variants: D65 collapses to its scale factor (texture_d65, properties.h)
+                val = float(pr.get('scale', 1.0))
+                pr.finish()
+                return [val] * 3
+            raise PluginError("%s: unsupported texture plugin '%s'" % (what, v.type))
+        if isinstance(v, (int, float)):
+            return [float(v)] * 3
+        val = np.asarray(v, dtype=np.float64)
+        if self.spectrum == A.SPEC_RGB:
+            return [float(x) for x in np.broadcast_to(val, (3,))]
+        return [_luminance(np.broadcast_to(val, (3,)))] * 3
+
+    def _new_buffer(self, arr, shape=None):
+        slot = self._n_buffers
+        if slot >= A.MIB_MAX_BUFFERS:
+            raise PluginError("too many data buffers (max %d)" % A.MIB_MAX_BUFFERS)
+        self._n_buffers += 1
+        a = np.ascontiguousarray(arr, dtype=np.float32)
+        self.buffers[slot] = a.reshape(-1).copy()
+        self.buffer_shapes[slot] = tuple(a.shape if shape is None else shape)
+        return slot
+
+    # -- volumes: src/volumes/const.cpp:61-84, src/volumes/grid.cpp:156-299 --
+    def _volume(self, out, v, default, key):
+        out.buffer = -1
+        out.max_value = 0.0
+        ident = np.eye(4, dtype=np.float32)
+        out.to_local[:] = ident.reshape(-1).tolist()
+        if v is None:
+            v = default
+        if isinstance(v, Plugin) and v.type == 'gridvolume':
+            pr = _Props(v)
+            data = pr.get('data')
+            grid = pr.get('grid')
+            fname = pr.get('filename')
+            if data is None and grid is not None:
+                data = grid
+            if data is None and fname is not None:
+                from .volumegrid import read_vol
+                data, _bbox = read_vol(fname)
+            if data is None:
+                raise PluginError("gridvolume: one of 'filename', 'grid' or 'data' must be specified")
+            data = np.asarray(data, dtype=np.float32)
+            if data.ndim == 3:
+                data = data[..., None]
+            if data.ndim != 4 or data.shape[3] not in (1, 3):
+                raise PluginError("gridvolume: data must be [z, y, x, c] with c in {1, 3}")
+            ftype = pr.get('filter_type', 'trilinear')
+            wmode = pr.get('wrap_mode', 'clamp')
+            pr.get('raw', False); pr.get('accel', True); pr.get('use_grid_bbox', False)
+            fixed_max = pr.get('max_value')
+            to_world = _to_transform(pr.get('to_world'))
+            pr.finish()
+            if ftype not in ('nearest', 'trilinear'):
+                raise PluginError("Invalid filter type \"%s\", must be one of: \"nearest\" or \"trilinear\"!" % ftype)
+            if wmode not in ('repeat', 'mirror', 'clamp'):
+                raise PluginError("Invalid wrap mode \"%s\", must be one of: \"repeat\", \"mirror\", or \"clamp\"!" % wmode)
+            out.type = A.VOLUME_GRID
+            out.channels = data.shape[3]
+            out.res[:] = [data.shape[2], data.shape[1], data.shape[0]]
+            out.filter = A.FILTER_NEAREST if ftype == 'nearest' else A.FILTER_TRILINEAR
+            out.wrap = {'repeat': A.WRAP_REPEAT, 'mirror': A.WRAP_MIRROR, 'clamp': A.WRAP_CLAMP}[wmode]
+            out.buffer = self._new_buffer(data)
+            to_local = to_world.inverse()
+            out.to_local[:] = to_local.f32().reshape(-1).tolist()
+            # update_bbox (include/mitsuba/render/volume.h:99-110)
+            corners = np.array([to_world @ [x, y, z] for x in (0, 1) for y in (0, 1) for z in (0, 1)])
+            out.bbox_min[:] = corners.min(0).astype(np.float32).tolist()
+            out.bbox_max[:] = corners.max(0).astype(np.float32).tolist()
+            if fixed_max is not None:
+                out.max_value = float(fixed_max)   # NOTE: commit() recomputes unless fixed; kept host-side
+            self.params[key + '.data'] = {'kind': 'buffer', 'slot': out.buffer}
+            return
+        # constvolume (explicit plugin, bare float or texture)
+        if isinstance(v, Plugin) and v.type == 'constvolume':
+            pr = _Props(v)
+            val = pr.child('value') or pr.get('value', 1.0)
+            pr.finish()
+            v = val
+        col = self._color(v, key)
+        out.type = A.VOLUME_CONST
+        out.channels = 3 if (self.spectrum == A.SPEC_RGB and len(set(col)) > 1) else 1
+        out.value[:] = col
+        out.res[:] = [1, 1, 1]
+        self.params[key + '.value.value'] = {'kind': 'volume_const', 'vol': out}
+
+    # -- phase functions --
+    def _phase(self, p, key):
+        if id(p) in self._phase_index:
+            return self._phase_index[id(p)]
+        i = self.desc.n_phases
+        if i >= A.MIB_MAX_PHASES:
+            raise PluginError("too many phase functions")
+        self.desc.n_phases += 1
+        self._phase_index[id(p)] = i
+        out = self.desc.phases[i]
+        out.buf_nodes = out.buf_m11 = out.buf_m12 = out.buf_m33 = out.buf_m34 = -1
+        pr = _Props(p)
+        if p.type == 'isotropic':                      # src/phase/isotropic.cpp
+            out.type = A.PHASE_ISOTROPIC
+        elif p.type == 'hg':                           # src/phase/hg.cpp:50-62
+            g = float(pr.get('g', 0.8))
+            if g >= 1.0 or g <= -1.0:
+                raise PluginError("The asymmetry parameter must lie in the interval (-1, 1)!")
+            out.type = A.PHASE_HG
+            out.g = g
+            self.params[key + '.g'] = {'kind': 'phase_g', 'phase': out}
+        elif p.type == 'rayleigh':                     # src/phase/rayleigh.cpp:41-48
+            rho = float(pr.get('depolarization', 0.0))
+            if rho < 0.0 or rho >= 1.0:
+                raise PluginError("Depolarization factor must be between 0 and 1!")
+            out.type = A.PHASE_RAYLEIGH
+            out.depolarization = rho
+        elif p.type in ('tabphase', 'tabphase_polarized'):   # src/phase/tabphase.cpp:44-79, tabphase_polarized.cpp:48-112
+            def parse(name):
+                s = pr.get(name, required=True)
+                if isinstance(s, str):
+                    return np.array([float(t) for t in s.replace(',', ' ').split()], dtype=np.float32)
+                return np.asarray(s, dtype=np.float32)
+            cost = parse('cost')
+            names = ['values'] if p.type == 'tabphase' else ['m11', 'm12', 'm33', 'm34']
+            tabs = [parse(n) for n in names]
+            for n, t in zip(names, tabs):
+                if t.size != cost.size:
+                    raise PluginError("%s: 'cost' and '%s' parameters must have the same size!" % (p.type, n))
+            out.type = A.PHASE_TABPHASE if p.type == 'tabphase' else A.PHASE_TABPHASE_POLARIZED
+            out.n_nodes = cost.size
+            out.buf_nodes = self._new_buffer(cost)
+            out.buf_m11 = self._new_buffer(tabs[0])
+            self.params[key + ('.values' if p.type == 'tabphase' else '.m11')] = {'kind': 'buffer', 'slot': out.buf_m11}
+            if p.type == 'tabphase_polarized':
+                out.buf_m12 = self._new_buffer(tabs[1])
+                out.buf_m33 = self._new_buffer(tabs[2])
+                out.buf_m34 = self._new_buffer(tabs[3])
+                for n, s in zip(names[1:], (out.buf_m12, out.buf_m33, out.buf_m34)):
+                    self.params[key + '.' + n] = {'kind': 'buffer', 'slot': s}
+        elif p.type == 'mie':
+            # src/phase/mie.cpp:251-257: mie is tabulated before rendering
+            from .mie import tabulate_mie_plugin
+            cost, m11, m12, m33, m34 = tabulate_mie_plugin(p, pr)
+            out.type = A.PHASE_TABPHASE_POLARIZED
+            out.n_nodes = cost.size
+            out.buf_nodes = self._new_buffer(cost)
+            out.buf_m11 = self._new_buffer(m11)
+            out.buf_m12 = self._new_buffer(m12)
+            out.buf_m33 = self._new_buffer(m33)
+            out.buf_m34 = self._new_buffer(m34)
+        else:
+            raise PluginError("unsupported phase function '%s'" % p.type)
+        pr.finish()
+        return i
+
+    # -- media: src/media/homogeneous.cpp:137-147, heterogeneous.cpp:155-167, src/render/medium.cpp:12-32 --
+    def _medium(self, m, key):
+        if id(m) in self._media_index:
+            return self._media_index[id(m)]
+        i = self.desc.n_media
+        if i >= A.MIB_MAX_MEDIA:
+            raise PluginError("too many media")
+        self.desc.n_media += 1
+        self._media_index[id(m)] = i
+        if m.id is not None and m.id in self.root.children and self.root.children[m.id] is m:
+            key = m.id
+        out = self.desc.media[i]
+        pr = _Props(m)
+        out.type = A.MEDIUM_HOMOGENEOUS if m.type == 'homogeneous' else A.MEDIUM_HETEROGENEOUS
+        phases = pr.children_of('phase')
+        if len(phases) > 1:
+            raise PluginError("Only a single phase function can be specified per medium")
+        if phases:
+            out.phase = self._phase(phases[0][1], key + '.phase_function')
+        else:
+            out.phase = self._phase(Plugin('isotropic', {}, {}), key + '.phase_function')
+        out.sample_emitters = int(bool(pr.get('sample_emitters', True)))
+        out.has_spectral_extinction = int(bool(pr.get('has_spectral_extinction', True)))
+        out.scale = float(pr.get('scale', 1.0))
+        self._volume(out.albedo, pr.child('albedo') or pr.get('albedo'), 0.75, key + '.albedo')
+        self._volume(out.sigma_t, pr.child('sigma_t') or pr.get('sigma_t'), 1.0, key + '.sigma_t')
+        if out.type == A.MEDIUM_HOMOGENEOUS and out.sigma_t.type != A.VOLUME_CONST:
+            raise PluginError("homogeneous medium: sigma_t must be constant in this build")
+        self.params[key + '.scale'] = {'kind': 'medium_scale', 'medium': out}
+        pr.finish()
+        return i
+
+    # -- bsdfs: src/bsdfs/null.cpp, diffuse.cpp --
+    def _bsdf(self, b, key):
+        if b is not None and id(b) in self._bsdf_index:
+            return self._bsdf_index[id(b)]
+        i = self.desc.n_bsdfs
+        if i >= A.MIB_MAX_BSDFS:
+            raise PluginError("too many BSDFs")
+        self.desc.n_bsdfs += 1
+        out = self.desc.bsdfs[i]
+        if b is None:                     # default BSDF of a shape: diffuse (shape.cpp)
+            out.type = A.BSDF_DIFFUSE
+            out.reflectance[:] = [0.5] * 3
+            return i
+        self._bsdf_index[id(b)] = i
+        pr = _Props(b)
+        if b.type == 'null':
+            out.type = A.BSDF_NULL
+        elif b.type == 'diffuse':
+            out.type = A.BSDF_DIFFUSE
+            out.reflectance[:] = self._color(pr.child('reflectance') or pr.get('reflectance', 0.5), key)
+            self.params[key + '.reflectance.value'] = {'kind': 'bsdf_reflectance', 'bsdf': out}
+        else:
+            raise PluginError("unsupported BSDF '%s'" % b.type)
+        pr.finish()
+        return i
+
+    # -- shapes: src/shapes/cube.cpp, rectangle.cpp:86-125, sphere.cpp --
+    def _shape(self, s, key):
+        i = self.desc.n_shapes
+        if i >= A.MIB_MAX_SHAPES:
+            raise PluginError("too many shapes (max %d)" % A.MIB_MAX_SHAPES)
+        self.desc.n_shapes += 1
+        out = self.desc.shapes[i]
+        pr = _Props(s)
+        to_world = _to_transform(pr.get('to_world'))
+        if pr.get('flip_normals', False):
+            to_world = to_world @ ScalarTransform4f.scale([1, 1, -1])
+        out.type = {'cube': A.SHAPE_CUBE, 'rectangle': A.SHAPE_RECTANGLE, 'sphere': A.SHAPE_SPHERE}[s.type]
+        if s.type == 'sphere':
+            c = np.asarray(pr.get('center', [0, 0, 0]), dtype=np.float64)
+            r = float(pr.get('radius', 1.0))
+            to_world = to_world @ ScalarTransform4f.translate(c) @ ScalarTransform4f.scale(r)
+            out.center[:] = (to_world @ [0, 0, 0]).astype(np.float32).tolist()
+            out.radius = float(np.linalg.norm(to_world.transform_vector([1, 0, 0])))
+        out.to_world[:] = to_world.f32().reshape(-1).tolist()
+        out.to_object[:] = to_world.inverse().f32().reshape(-1).tolist()
+        if s.type == 'rectangle':
+            dp_du = to_world.transform_vector([2, 0, 0])
+            dp_dv = to_world.transform_vector([0, 2, 0])
+            n = np.linalg.inv(to_world.matrix[:3, :3]).T @ np.array([0, 0, 1.0])
+            n = n / np.linalg.norm(n)
+            out.frame_s[:] = dp_du.astype(np.float32).tolist()
+            out.frame_t[:] = dp_dv.astype(np.float32).tolist()
+            out.frame_n[:] = n.astype(np.float32).tolist()
+            out.inv_surface_area = float(1.0 / np.linalg.norm(np.cross(dp_du, dp_dv)))
+        bsdfs = pr.children_of('bsdf')
+        out.bsdf = self._bsdf(bsdfs[0][1] if bsdfs else None, key + '.bsdf')
+        interior, exterior = pr.child('interior'), pr.child('exterior')
+        out.interior_medium = self._medium(interior, key + '.interior_medium') if interior else -1
+        out.exterior_medium = self._medium(exterior, key + '.exterior_medium') if exterior else -1
+        out.emitter = -1
+        ems = pr.children_of('emitter')
+        if ems:
+            out.emitter = self._emitter(ems[0][1], key + '.emitter', shape=i)
+        pr.finish()
+        # world-space bbox corners for the scene bounding sphere
+        if s.type == 'rectangle':
+            pts = [to_world @ [x, y, 0] for x in (-1, 1) for y in (-1, 1)]
+        elif s.type == 'cube':
+            pts = [to_world @ [x, y, z] for x in (-1, 1) for y in (-1, 1) for z in (-1, 1)]
+        else:
+            c, r = np.array(out.center[:]), out.radius
+            pts = [c - r, c + r]
+        self._bbox_pts.extend(pts)
+        return i
+
+    # -- emitters: src/emitters/constant.cpp:55-92, directional.cpp:60-108, area.cpp --
+    def _emitter(self, e, key, shape=-1):
+        i = self.desc.n_emitters
+        if i >= A.MIB_MAX_EMITTERS:
+            raise PluginError("too many emitters")
+        self.desc.n_emitters += 1
+        out = self.desc.emitters[i]
+        out.shape = shape
+        pr = _Props(e)
+        if e.type == 'constant':
+            out.type = A.EMITTER_CONSTANT
+            out.radiance[:] = self._color(pr.child('radiance') or pr.get('radiance', 1.0), key)
+            if self.desc.environment >= 0:
+                raise PluginError("Only one environment emitter can be specified per scene.")
+            self.desc.environment = i
+            self.params[key + '.radiance.value'] = {'kind': 'emitter_radiance', 'emitter': out}
+        elif e.type == 'directional':
+            out.type = A.EMITTER_DIRECTIONAL
+            out.radiance[:] = self._color(pr.child('irradiance') or pr.get('irradiance', 1.0), key)
+            if pr.has('direction'):
+                if pr.has('to_world'):
+                    raise PluginError("Only one of the parameters 'direction' and 'to_world' can be specified at the same time!'")
+                d = np.asarray(pr.get('direction'), dtype=np.float64)
+                d = d / np.linalg.norm(d)
+                up, _ = coordinate_system(d)
+                tw = ScalarTransform4f.look_at([0, 0, 0], d, up)
+            else:
+                tw = _to_transform(pr.get('to_world'))
+            out.direction[:] = tw.transform_vector([0, 0, 1]).astype(np.float32).tolist()
+            self.params[key + '.irradiance.value'] = {'kind': 'emitter_radiance', 'emitter': out}
+        elif e.type == 'area':
+            out.type = A.EMITTER_AREA
+            out.radiance[:] = self._color(pr.child('radiance') or pr.get('radiance', 1.0), key)
+            if shape < 0:
+                raise PluginError("area emitter must be attached to a shape")
+        else:
+            raise PluginError("unsupported emitter '%s'" % e.type)
+        pr.finish()
+        return i
+
+    # -- sensor + film + sampler --
+    def _sensor(self, s):
+        out = self.desc.sensor
+        pr = _Props(s)
+        out.medium = -1
+        med = pr.children_of('medium')
+        if med:
+            out.medium = self._medium(med[0][1], 'sensor.medium')
+        # film: src/films/hdrfilm.cpp:122-243, src/render/film.cpp:10-51
+        film = None
+        for k, c in pr.children_of('film'):
+            film = c
+        fw, fh, rf, rad, std = 768, 576, A.RFILTER_GAUSSIAN, 2.0, 0.5
+        crop = None
+        sample_border = False
+        if film is not None:
+            fp = _Props(film)
+            fw, fh = int(fp.get('width', 768)), int(fp.get('height', 576))
+            crop = (int(fp.get('crop_offset_x', 0)), int(fp.get('crop_offset_y', 0)),
+                    int(fp.get('crop_width', fw)), int(fp.get('crop_height', fh)))
+            sample_border = bool(fp.get('sample_border', False))
+            for n in ('pixel_format', 'component_format', 'file_format', 'compensate'):
+                fp.get(n)
+            for k, c in fp.children_of('rfilter'):
+                rp = _Props(c)
+                if c.type == 'box':
+                    rf, rad = A.RFILTER_BOX, 0.5
+                elif c.type == 'gaussian':          # src/rfilters/gaussian.cpp:50-53
+                    std = float(rp.get('stddev', 0.5))
+                    rf, rad = A.RFILTER_GAUSSIAN, 4.0 * std
+                elif c.type == 'tent':
+                    rad = float(rp.get('radius', 1.0))
+                    rf = A.RFILTER_TENT
+                rp.finish()
+            fp.finish()
+        if crop is None:
+            crop = (0, 0, fw, fh)
+        out.film_width, out.film_height = fw, fh
+        out.crop_offset_x, out.crop_offset_y, out.crop_width, out.crop_height = crop
+        out.rfilter, out.rfilter_radius, out.rfilter_stddev = rf, rad, std
+        out.sample_border = int(sample_border)
+        # sampler: src/render/sampler.cpp:12-20
+        self.sample_count = 4
+        self.desc.sampler_base_seed = 0
+        for k, c in pr.children_of('sampler'):
+            sp = _Props(c)
+            if c.type != 'independent':
+                raise PluginError("only the 'independent' sampler exists in this build")
+            self.sample_count = int(sp.get('sample_count', 4))
+            self.desc.sampler_base_seed = int(sp.get('seed', 0))
+            sp.finish()
+        ident = np.eye(4, dtype=np.float32).reshape(-1).tolist()
+        out.sample_to_camera[:] = ident
+        if s.type == 'perspective':               # src/sensors/perspective.cpp:120-199
+            out.type = A.SENSOR_PERSPECTIVE
+            tw = _to_transform(pr.get('to_world'))
+            fov = float(pr.get('fov', 39.3077))   # default focal length 50mm equivalent
+            pr.get('fov_axis', 'x')
+            near, far = float(pr.get('near_clip', 1e-2)), float(pr.get('far_clip', 1e4))
+            ppx = float(pr.get('principal_point_offset_x', 0.0))
+            ppy = float(pr.get('principal_point_offset_y', 0.0))
+            out.near_clip, out.far_clip = near, far
+            out.principal_point_offset[:] = [ppx, ppy]
+            # perspective_projection (include/mitsuba/render/sensor.h:228-263)
+            aspect = fw / fh
+            rel_size = (crop[2] / fw, crop[3] / fh)
+            rel_off = (crop[0] / fw, crop[1] / fh)
+            T = ScalarTransform4f
+            c2s = (T.scale([1.0 / rel_size[0], 1.0 / rel_size[1], 1.0]) @
+                   T.translate([-rel_off[0], -rel_off[1], 0.0]) @
+                   T.scale([-0.5, -0.5 * aspect, 1.0]) @
+                   T.translate([-1.0, -1.0 / aspect, 0.0]) @
+                   T.perspective(fov, near, far))
+            out.sample_to_camera[:] = c2s.inverse().f32().reshape(-1).tolist()
+            out.to_world[:] = tw.f32().reshape(-1).tolist()
+            out.needs_aperture_sample = 0
+        elif s.type == 'distant':                 # src/sensors/distant.cpp:140-178
+            out.type = A.SENSOR_DISTANT
+            if (fw, fh) != (1, 1):
+                raise PluginError("This sensor only supports films of size 1x1 Pixels!")
+            if pr.has('direction'):
+                if pr.has('to_world'):
+                    raise PluginError("Only one of the parameters 'direction' and 'to_world'can be specified at the same time!'")
+                d = np.asarray(pr.get('direction'), dtype=np.float64)
+                d = d / np.linalg.norm(d)
+                _, up = coordinate_system(d)
+                tw = ScalarTransform4f.look_at([0, 0, 0], d, up)
+            else:
+                tw = _to_transform(pr.get('to_world'))
+            out.to_world[:] = tw.f32().reshape(-1).tolist()
+            tgt = pr.get('target')
+            if tgt is not None:
+                out.target_type = 1
+                out.target[:] = [float(x) for x in tgt]
+            else:
+                out.target_type = 0
+            out.needs_aperture_sample = 1          # include/mitsuba/render/endpoint.h:401 default
+        elif s.type == 'radiancemeter':           # src/sensors/radiancemeter.cpp:55-95
+            out.type = A.SENSOR_RADIANCEMETER
+            if pr.has('origin') or pr.has('direction'):
+                o = np.asarray(pr.get('origin', required=True), dtype=np.float64)
+                d = np.asarray(pr.get('direction', required=True), dtype=np.float64)
+                d = d / np.linalg.norm(d)
+                _, up = coordinate_system(d)
+                tw = ScalarTransform4f.look_at(o, o + d, up)
+            else:
+                tw = _to_transform(pr.get('to_world'))
+            pr.get('wavelength', -1.0)
+            out.to_world[:] = tw.f32().reshape(-1).tolist()
+            out.needs_aperture_sample = 0
+        pr.finish()
+
+    # -- integrators: src/render/integrator.cpp:24-27,1281-1298; common.py:32-41 --
+    def _integrator(self, it):
+        out = self.desc.integrator
+        out.type = {'volpath': A.INTEG_VOLPATH, 'volpathaos': A.INTEG_VOLPATHAOS,
+                    'prbvolpath': A.INTEG_PRBVOLPATH, 'prb_volpathaos': A.INTEG_PRBVOLPATHAOS}[it.type]
+        pr = _Props(it)
+        is_prb = it.type.startswith('prb')
+        max_depth = int(pr.get('max_depth', 6 if is_prb else -1))
+        if max_depth < 0 and max_depth != -1:
+            raise PluginError("\"max_depth\" must be set to -1 (infinite) or a value >= 0")
+        rr_depth = int(pr.get('rr_depth', 5))
+        if rr_depth <= 0:
+            raise PluginError("\"rr_depth\" must be set to a value greater than zero!")
+        out.max_depth, out.rr_depth = max_depth, rr_depth
+        out.hide_emitters = int(bool(pr.get('hide_emitters', False)))
+        for n in ('timeout', 'block_size', 'samples_per_pass'):
+            pr.get(n)
+        out.rng_arg_order = A.RNG_ARGS_LEFT_TO_RIGHT
+        out.double_phase_quirk = 1 if it.type == 'volpath' else 0
+        if it.type == 'prb_volpathaos' and self.spectrum != A.SPEC_MONO_POLARIZED:
+            # prb_volpathaos.py:72-78
+            raise PluginError("prb_volpathaos requires a monochromatic polarized variant")
+        pr.finish()
+
+    def _flatten(self):
+        d = self.desc
+        d.abi_version = A.MIB_ABI_VERSION
+        d.spectrum = self.spectrum
+        d.environment = -1
+        self._bbox_pts = []
+        root = self.root
+        integrator = sensor = None
+        pending_emitters = []
+        for name, c in root.children.items():
+            if c.category == 'integrator':
+                integrator = c
+            elif c.category == 'sensor':
+                sensor = c
+            elif c.category == 'shape':
+                self._shape(c, name)
+            elif c.category == 'emitter':
+                pending_emitters.append((name, c))
+            elif c.category in ('medium', 'bsdf', 'phase', 'texture', 'volume'):
+                pass  # only instantiated when referenced
+            else:
+                raise PluginError("unexpected top-level object '%s' of type '%s'" % (name, c.type))
+        for name, c in pending_emitters:
+            self._emitter(c, name)
+        if integrator is None:
+            integrator = Plugin('volpath', {}, {})
+        if sensor is None:
+            raise PluginError("the scene needs a sensor")
+        self._sensor(sensor)
+        self._integrator(integrator)
+        # scene bounding sphere (include/mitsuba/core/bbox.h:330-333) -> emitters / distant sensor set_scene
+        if self._bbox_pts:
+            pts = np.array(self._bbox_pts, dtype=np.float32)
+            bmin, bmax = pts.min(0), pts.max(0)
+            center = ((bmin + bmax) * np.float32(0.5)).astype(np.float32)
+            radius = np.float32(np.linalg.norm((center - bmax).astype(np.float32)))
+            radius = max(np.float32(RAY_EPSILON), np.float32(radius * np.float32(1.0 + RAY_EPSILON)))
+        else:
+            center, radius = np.zeros(3, np.float32), np.float32(RAY_EPSILON)
+        for i in range(d.n_emitters):
+            d.emitters[i].bsphere_center[:] = center.tolist()
+            d.emitters[i].bsphere_radius = float(radius)
+        d.sensor.bsphere_center[:] = center.tolist()
+        d.sensor.bsphere_radius = float(radius)
+
+
+def load_dict(d, variant):
+    loader = _Loader(variant)
+    root = loader.load(d, None)
+    if root.type != 'scene':
+        raise PluginError("load_dict(): the top-level object must be of type 'scene' in this build")
+    return Scene(root, variant)

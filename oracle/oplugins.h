@@ -1,0 +1,310 @@
+// oplugins.h -- TEST INFRASTRUCTURE (parity oracle). Not part of the product.
+// Phase functions, emitters, BSDFs and sensors restated from the reference.
+#pragma once
+#include "oscene.h"
+
+namespace orc {
+
+// ------------------------------------------------------------------
+// warp (include/mitsuba/core/warp.h)
+// ------------------------------------------------------------------
+static inline float circ(float x) { return safe_sqrt(fnmadd(x, x, 1.f)); }               // warp.h:23
+static inline Vec3 square_to_uniform_sphere(float sx, float sy) {                           // warp.h:250-255
+    float z = fnmadd(2.f, sy, 1.f), r = circ(z), s, c;
+    sincos(2.f * Pi * sx, &s, &c);
+    return { r * c, r * s, z };
+}
+static inline void square_to_uniform_disk_concentric(float sx, float sy, float *ox, float *oy) { // warp.h:54-90
+    float x = fmsub(2.f, sx, 1.f), y = fmsub(2.f, sy, 1.f);
+    bool is_zero = x == 0.f && y == 0.f, quadrant_1_or_3 = std::fabs(x) < std::fabs(y);
+    float r = quadrant_1_or_3 ? y : x, rp = quadrant_1_or_3 ? x : y;
+    float phi = 0.25f * Pi * rp / r;
+    if (quadrant_1_or_3) phi = 0.5f * Pi - phi;
+    if (is_zero) phi = 0.f;
+    float s, c; sincos(phi, &s, &c);
+    *ox = r * c; *oy = r * s;
+}
+static inline Vec3 square_to_cosine_hemisphere(float sx, float sy) {                        // warp.h:412-420
+    float px, py; square_to_uniform_disk_concentric(sx, sy, &px, &py);
+    // squared_norm of a Point2f
+    float z = safe_sqrt(1.f - fmadd(py, py, sqr(px)));
+    return { px, py, z };
+}
+
+// ------------------------------------------------------------------
+// Phase functions.  wo is LOCAL (+z = ray.d), mei.wi = (0,0,-1) (medium.cpp:48-54)
+// ------------------------------------------------------------------
+template <typename Spec> struct PhaseSample { Vec3 wo; Spec weight; float pdf; };
+template <typename Spec> struct PhaseEval { Spec val; float pdf; };
+
+template <typename Spec> static inline Spec phase_scalar(float v) { return Spec(v); }
+
+// rayleigh.cpp:50-95 / tabphase_polarized.cpp:169-197: rotate from the scattering plane to the implicit bases
+static inline Mueller phase_rotate(const Mueller &M, Vec3 wo, Vec3 wi) {
+    Vec3 wo_hat = wo, wi_hat = wi;
+    Vec3 x_hat = cross(-wo_hat, wi_hat),
+         p_axis_in = normalize(cross(x_hat, -wo_hat)),
+         p_axis_out = normalize(cross(x_hat, wi_hat));
+    Mueller R = rotate_mueller_basis(M, -wo_hat, p_axis_in, stokes_basis(-wo_hat),
+                                     wi_hat, p_axis_out, stokes_basis(wi_hat));
+    zero_nans(R);
+    return R;
+}
+
+template <int SPEC> struct Phase {
+    using Tr = SpecTraits<SPEC>;
+    using Spec = typename Tr::Spec;
+
+    // hg.cpp:66-71
+    static float eval_hg(float g, float cos_theta) {
+        float temp = 1.f + sqr(g) + 2.f * g * cos_theta;
+        return InvFourPi * (1.f - sqr(g)) / (temp * std::sqrt(temp));
+    }
+    static float rayleigh_pdf(float c) { return (3.f / 16.f) * InvPi * (1.f + sqr(c)); }   // rayleigh.cpp:50-52
+    static Spec eval_rayleigh(float rho, Vec3 wo, Vec3 wi, float cos_theta) {                // rayleigh.cpp:54-98
+        if constexpr (Tr::POL) {
+            float sin_theta = safe_sqrt(1.0f - sqr(cos_theta));
+            return phase_rotate(rayleigh_scatter(cos_theta, sin_theta, rho), wo, wi);
+        } else {
+            float r1 = (1.f - rho) / (1.f + rho / 2.f), r2 = (1.f + rho) / (1.f - rho);
+            return Spec((3.f / 16.f) * InvPi * r1 * (r2 + sqr(cos_theta)));
+        }
+    }
+
+    static PhaseEval<Spec> eval_pdf(const Scene &sc, int idx, Vec3 wo, Vec3 wi) {
+        const mib_phase &p = sc.d.phases[idx];
+        switch (p.type) {
+            case MIB_PHASE_ISOTROPIC: return { Spec(InvFourPi), InvFourPi };                 // isotropic.cpp:51-58
+            case MIB_PHASE_HG: { float pdf = eval_hg(p.g, dot(wo, wi)); return { Spec(pdf), pdf }; } // hg.cpp:96-104
+            case MIB_PHASE_RAYLEIGH: {                                                        // rayleigh.cpp:118-128
+                float cos_theta = dot(wo, -wi);
+                return { eval_rayleigh(p.depolarization, wo, wi, cos_theta), rayleigh_pdf(cos_theta) };
+            }
+            case MIB_PHASE_TABPHASE: {                                                        // tabphase.cpp:121-133
+                float cos_theta = -dot(wo, wi);
+                float pdf = sc.tables[idx].m11.eval_pdf_normalized(cos_theta) * InvTwoPi;
+                return { Spec(pdf), pdf };
+            }
+            default: {                                                                        // tabphase_polarized.cpp:146-205
+                const PhaseTables &t = sc.tables[idx];
+                float cos_theta = -dot(wo, wi);
+                float m11 = t.m11.eval_pdf(cos_theta);
+                Spec val;
+                if constexpr (Tr::POL) {
+                    float m12 = t.m12.eval_pdf(cos_theta), m33 = t.m33.eval_pdf(cos_theta), m34 = t.m34.eval_pdf(cos_theta);
+                    Mueller M;
+                    M.m[0][0] = m11; M.m[0][1] = m12; M.m[1][0] = m12; M.m[1][1] = m11;
+                    M.m[2][2] = m33; M.m[2][3] = m34; M.m[3][2] = -m34; M.m[3][3] = m33;
+                    val = phase_rotate(M, wo, wi);
+                } else {
+                    val = Spec(m11);
+                }
+                float pdf = t.m11.eval_pdf_normalized(cos_theta) * InvTwoPi;
+                return { val, pdf };
+            }
+        }
+    }
+
+    static PhaseSample<Spec> sample(const Scene &sc, int idx, Vec3 wi, float /*sample1*/, float s2x, float s2y) {
+        const mib_phase &p = sc.d.phases[idx];
+        switch (p.type) {
+            case MIB_PHASE_ISOTROPIC: {                                                       // isotropic.cpp:40-49
+                Vec3 wo = square_to_uniform_sphere(s2x, s2y);
+                return { wo, Spec(1.f), InvFourPi };
+            }
+            case MIB_PHASE_HG: {                                                              // hg.cpp:73-94
+                float g = p.g;
+                float sqr_term = (1.f - sqr(g)) / (1.f - g + 2.f * g * s2x),
+                      cos_theta = (1.f + sqr(g) - sqr(sqr_term)) / (2.f * g);
+                if (std::fabs(g) < EpsilonF) cos_theta = 1.f - 2.f * s2x;
+                float sin_theta = safe_sqrt(1.f - sqr(cos_theta)), sp, cp;
+                sincos(2.f * Pi * s2y, &sp, &cp);
+                Vec3 wo(sin_theta * cp, sin_theta * sp, cos_theta);
+                return { wo, Spec(1.f), eval_hg(g, -cos_theta) };
+            }
+            case MIB_PHASE_RAYLEIGH: {                                                        // rayleigh.cpp:100-116
+                float z = 2.f * (2.f * s2x - 1.f), tmp = std::sqrt(sqr(z) + 1.f);
+                float A = cbrt_(z + tmp), B = cbrt_(z - tmp), cos_theta = A + B;
+                float sin_theta = safe_sqrt(1.0f - sqr(cos_theta)), sp, cp;
+                sincos(TwoPi * s2y, &sp, &cp);
+                Vec3 wo(sin_theta * cp, sin_theta * sp, cos_theta);
+                float pdf = rayleigh_pdf(cos_theta);
+                Spec w = eval_rayleigh(p.depolarization, wo, wi, cos_theta) * rcp(pdf);
+                return { wo, w, pdf };
+            }
+            case MIB_PHASE_TABPHASE: {                                                        // tabphase.cpp:91-119
+                float ctp = sc.tables[idx].m11.sample(s2x);
+                float stp = safe_sqrt(1.f - ctp * ctp), sp, cp;
+                sincos(2.f * Pi * s2y, &sp, &cp);
+                Vec3 wo(stp * cp, stp * sp, ctp);
+                float pdf = sc.tables[idx].m11.eval_pdf_normalized(ctp) * InvTwoPi;
+                return { wo, Spec(1.f), pdf };
+            }
+            default: {                                                                        // tabphase_polarized.cpp:119-144
+                float ctp = sc.tables[idx].m11.sample(s2x);
+                float stp = safe_sqrt(1.f - ctp * ctp), sp, cp;
+                sincos(2.f * Pi * s2y, &sp, &cp);
+                Vec3 wo(stp * cp, stp * sp, ctp);
+                PhaseEval<Spec> e = eval_pdf(sc, idx, wo, wi);
+                return { wo, e.val * rcp(e.pdf), e.pdf };
+            }
+        }
+    }
+};
+
+// ------------------------------------------------------------------
+// Emitters (constant.cpp:116-146, directional.cpp:150-177), scene.cpp:299-366
+// ------------------------------------------------------------------
+template <int NC> struct DirectionSample {
+    Vec3 p, n, d; float dist = 0.f, pdf = 0.f; bool delta = false; int emitter = -1;
+};
+
+template <int NC> static inline Color<NC> emitter_radiance(const mib_emitter &e) {
+    Color<NC> r; for (int c = 0; c < NC; ++c) r.v[c] = e.radiance[NC == 3 ? c : 0]; return r;
+}
+
+// Returns the UNPOLARIZED spectrum; callers wrap with depolarizer<Spectrum>()
+template <int NC>
+static inline Color<NC> sample_emitter_direction(const Scene &sc, Vec3 ref_p, float sx, float sy, DirectionSample<NC> *ds_out) {
+    DirectionSample<NC> ds;
+    Color<NC> spec(0.f);
+    int n = sc.d.n_emitters;
+    if (n == 0) { *ds_out = ds; return spec; }
+    int index = 0; float emitter_weight = 1.f, pmf = 1.f;
+    if (n > 1) {
+        // scene.cpp:227-262 sample_emitter (uniform selection, sample reuse)
+        float ec = (float) n;
+        float index_sample_scaled = sx * ec;
+        index = (int) std::min((uint32_t) index_sample_scaled, (uint32_t) n - 1u);
+        sx = index_sample_scaled - (float) index;
+        emitter_weight = ec;
+        pmf = rcp(ec);
+    }
+    const mib_emitter &e = sc.d.emitters[index];
+    Vec3 c(e.bsphere_center[0], e.bsphere_center[1], e.bsphere_center[2]);
+    if (e.type == MIB_EMITTER_CONSTANT) {
+        Vec3 d = square_to_uniform_sphere(sx, sy);
+        float radius = maximum(e.bsphere_radius, norm(ref_p - c)), dist = 2.f * radius;
+        ds.p = fmadd(d, dist, ref_p); ds.n = -d; ds.pdf = InvFourPi; ds.delta = false; ds.d = d; ds.dist = dist;
+        spec = div_scalar(emitter_radiance<NC>(e), ds.pdf);
+    } else if (e.type == MIB_EMITTER_DIRECTIONAL) {
+        Vec3 d(e.direction[0], e.direction[1], e.direction[2]);
+        float dist = Inf;
+        ds.p = ref_p - d * dist; ds.n = d; ds.pdf = 1.f; ds.delta = true; ds.d = -d; ds.dist = dist;
+        spec = emitter_radiance<NC>(e);
+    } else {
+        throw std::runtime_error("oracle: area emitters not supported yet");
+    }
+    ds.emitter = index;
+    if (n > 1) { ds.pdf *= pmf; spec = spec * emitter_weight; }
+    *ds_out = ds;
+    return spec;
+}
+
+// scene.cpp:355-366 + constant.cpp:139-144 / directional.cpp pdf_direction (= 0)
+template <int NC> static inline float pdf_emitter_direction(const Scene &sc, int emitter) {
+    const mib_emitter &e = sc.d.emitters[emitter];
+    float pmf = sc.d.n_emitters > 1 ? rcp((float) sc.d.n_emitters) : 1.f;
+    float pdf = e.type == MIB_EMITTER_CONSTANT ? InvFourPi : 0.f;
+    return pdf * pmf;
+}
+
+// si.emitter(scene): shape emitter if valid, else the environment (interaction.h)
+static inline int si_emitter(const Scene &sc, const SurfaceInteraction &si) {
+    if (si.is_valid()) return sc.d.shapes[si.shape].emitter;
+    return sc.d.environment;
+}
+
+// ------------------------------------------------------------------
+// BSDFs: null (null.cpp:36-86), diffuse (diffuse.cpp:101-160)
+// ------------------------------------------------------------------
+enum : uint32_t { BSDF_Null = 0x1, BSDF_DiffuseReflection = 0x2, BSDF_Smooth = 0x2 | 0x4 | 0x8 | 0x10,
+                  BSDF_Delta = 0x1 | 0x20 | 0x40 };
+static inline uint32_t bsdf_flags(const mib_bsdf &b) { return b.type == MIB_BSDF_NULL ? (uint32_t) BSDF_Null : (uint32_t) BSDF_DiffuseReflection; }
+
+template <typename Spec> struct BSDFSample { Vec3 wo; float pdf = 0.f, eta = 1.f; uint32_t sampled_type = 0; Spec value; };
+
+template <int SPEC> struct BSDF {
+    using Tr = SpecTraits<SPEC>;
+    using Spec = typename Tr::Spec;
+    using USpec = typename Tr::USpec;
+    static USpec reflectance(const mib_bsdf &b) { USpec r; for (int c = 0; c < Tr::NC; ++c) r.v[c] = b.reflectance[Tr::NC == 3 ? c : 0]; return r; }
+
+    static BSDFSample<Spec> sample(const mib_bsdf &b, const SurfaceInteraction &si, float /*s1*/, float s2x, float s2y) {
+        BSDFSample<Spec> bs;
+        bs.value = Spec(0.f);
+        if constexpr (Tr::POL) bs.value = Mueller();
+        if (b.type == MIB_BSDF_NULL) {
+            bs.wo = -si.wi; bs.sampled_type = BSDF_Null; bs.eta = 1.f; bs.pdf = 1.f;
+            bs.value = Spec(1.f); // identity in polarized modes (null.cpp:57-63)
+            return bs;
+        }
+        // JIT variants have no early exit: all fields are written for every lane and
+        // only the value is masked by (cos_theta_i > 0 && pdf > 0) (diffuse.cpp:101-126)
+        float cos_theta_i = si.wi.z;
+        bs.wo = square_to_cosine_hemisphere(s2x, s2y);
+        bs.pdf = InvPi * bs.wo.z;
+        bs.eta = 1.f;
+        bs.sampled_type = BSDF_DiffuseReflection;
+        bs.value = Depol<Spec, Tr::NC>::make((cos_theta_i > 0.f && bs.pdf > 0.f) ? reflectance(b) : USpec(0.f));
+        return bs;
+    }
+    static Spec eval(const mib_bsdf &b, const SurfaceInteraction &si, Vec3 wo) {
+        Spec zero = Depol<Spec, Tr::NC>::make(USpec(0.f));
+        if (b.type == MIB_BSDF_NULL) return zero;
+        float cos_theta_i = si.wi.z, cos_theta_o = wo.z;
+        if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) return zero;
+        USpec value = reflectance(b) * InvPi * cos_theta_o;
+        return Depol<Spec, Tr::NC>::make(value);
+    }
+    static float pdf(const mib_bsdf &b, const SurfaceInteraction &si, Vec3 wo) {
+        if (b.type == MIB_BSDF_NULL) return 0.f;
+        float cos_theta_i = si.wi.z, cos_theta_o = wo.z;
+        return (cos_theta_i > 0.f && cos_theta_o > 0.f) ? InvPi * wo.z : 0.f;
+    }
+    static Spec eval_null_transmission(const mib_bsdf &b) {
+        if (b.type == MIB_BSDF_NULL) return Spec(1.f);
+        return Depol<Spec, Tr::NC>::make(USpec(0.f)); // bsdf.h default: 0
+    }
+};
+
+// ------------------------------------------------------------------
+// Sensors (perspective.cpp:201-235, distant.cpp:193-235)
+// ------------------------------------------------------------------
+static inline Ray sensor_sample_ray(const Scene &sc, float px, float py, float ax, float ay) {
+    const mib_sensor &s = sc.d.sensor;
+    Mat4 to_world = mat4_from(s.to_world);
+    Ray ray;
+    if (s.type == MIB_SENSOR_PERSPECTIVE) {
+        Mat4 s2c = mat4_from(s.sample_to_camera);
+        // film size * offset / crop size (principal point, 0 by default)
+        float ox = (float) s.film_width * s.principal_point_offset[0] / (float) s.crop_width,
+              oy = (float) s.film_height * s.principal_point_offset[1] / (float) s.crop_height;
+        Vec3 near_p = transform_point(s2c, Vec3(px + ox, py + oy, 0.f));
+        Vec3 d = normalize(near_p);
+        ray.o = Vec3(to_world.m[0][3], to_world.m[1][3], to_world.m[2][3]);
+        ray.d = transform_vector(to_world, d);
+        float inv_z = rcp(d.z), near_t = s.near_clip * inv_z, far_t = s.far_clip * inv_z;
+        ray.o = ray.o + ray.d * near_t;
+        ray.maxt = far_t - near_t;
+    } else if (s.type == MIB_SENSOR_DISTANT) {
+        ray.d = transform_vector(to_world, Vec3(0.f, 0.f, 1.f));
+        Vec3 c(s.bsphere_center[0], s.bsphere_center[1], s.bsphere_center[2]);
+        if (s.target_type == 1) {
+            ray.o = Vec3(s.target[0], s.target[1], s.target[2]) - 2.f * ray.d * s.bsphere_radius;
+        } else {
+            float ox, oy; square_to_uniform_disk_concentric(ax, ay, &ox, &oy);
+            Vec3 perp = transform_vector(to_world, Vec3(ox, oy, 0.f));
+            ray.o = c + perp * s.bsphere_radius - ray.d * s.bsphere_radius;
+        }
+        ray.maxt = Largest;
+    } else { // radiancemeter (radiancemeter.cpp:97-126)
+        ray.o = transform_point_affine(to_world, Vec3(0.f));
+        ray.d = transform_vector(to_world, Vec3(0.f, 0.f, 1.f));
+        ray.o = ray.o + ray.d * RayEpsilon;
+        ray.maxt = Largest;
+    }
+    return ray;
+}
+
+} // namespace orc

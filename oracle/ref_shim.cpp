@@ -1,0 +1,136 @@
+// ref_shim.cpp -- TEST INFRASTRUCTURE.  Thin extern "C" wrappers around the
+// REFERENCE'S OWN HEADERS (compiled where they lie under /root/reference; no
+// reference source is copied into this repository).  Built by oracle/Makefile
+// into oracle/_ref/libmiref.so and used by tests to pin the building blocks of
+// the oracle restatement (scalar float instantiation of the same templates the
+// llvm_ad variants trace).
+#include <mitsuba/core/fwd.h>
+#include <mitsuba/core/vector.h>
+#include <mitsuba/core/frame.h>
+#include <mitsuba/core/random.h>
+#include <mitsuba/core/warp.h>
+#include <mitsuba/core/spectrum.h>
+#include <mitsuba/core/transform.h>
+#include <mitsuba/core/distr_1d.h>
+#include <mitsuba/render/mueller.h>
+#include <mitsuba/render/interaction.h>
+#include <drjit/math.h>
+#include <drjit/random.h>
+#include <drjit/sphere.h>
+#include <drjit/texture.h>
+#include <cstring>
+
+
+// Link stubs for the two non-template symbols the headers reference (libmitsuba is not built here).
+#include <stdexcept>
+namespace mitsuba {
+    const Class *m_class = nullptr;
+    namespace detail {
+        void (Throw)(LogLevel, const Class *, const char *, int, const std::string &msg) { throw std::runtime_error(msg); }
+    }
+}
+
+using namespace mitsuba;
+using Float = float;
+using V3 = Vector<float, 3>;
+using P3 = Point<float, 3>;
+using P2 = Point<float, 2>;
+using MM = MuellerMatrix<float>;
+using SpecPol = MuellerMatrix<Color<float, 1>>;
+
+static void store(const MM &M, float *o) { for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) o[4 * r + c] = M(r, c); }
+static MM load(const float *i) { MM M; for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) M(r, c) = i[4 * r + c]; return M; }
+
+extern "C" {
+
+void ref_sincos(const float *x, float *s, float *c, size_t n) { for (size_t i = 0; i < n; ++i) { auto [a, b] = dr::sincos(x[i]); s[i] = a; c[i] = b; } }
+void ref_exp(const float *x, float *y, size_t n) { for (size_t i = 0; i < n; ++i) y[i] = dr::exp(x[i]); }
+void ref_log(const float *x, float *y, size_t n) { for (size_t i = 0; i < n; ++i) y[i] = dr::log(x[i]); }
+void ref_cbrt(const float *x, float *y, size_t n) { for (size_t i = 0; i < n; ++i) y[i] = dr::cbrt(x[i]); }
+void ref_asin(const float *x, float *y, size_t n) { for (size_t i = 0; i < n; ++i) y[i] = dr::asin(x[i]); }
+void ref_tea(const uint32_t *v0, const uint32_t *v1, uint32_t *o0, uint32_t *o1, size_t n) {
+    for (size_t i = 0; i < n; ++i) { auto [a, b] = sample_tea_32<uint32_t>(v0[i], v1[i]); o0[i] = a; o1[i] = b; }
+}
+void ref_pcg32_floats(uint64_t initstate, uint64_t initseq, float *out, size_t n) {
+    dr::PCG32<uint32_t> r; r.seed(1, initstate, initseq);
+    for (size_t i = 0; i < n; ++i) out[i] = r.next_float32();
+}
+void ref_pcg32_uints(uint64_t initstate, uint64_t initseq, uint32_t *out, size_t n) {
+    dr::PCG32<uint32_t> r; r.seed(1, initstate, initseq);
+    for (size_t i = 0; i < n; ++i) out[i] = r.next_uint32();
+}
+void ref_coordinate_system(const float *n3, float *s3, float *t3, size_t n) {
+    for (size_t i = 0; i < n; ++i) {
+        auto [s, t] = coordinate_system(V3(n3[3*i], n3[3*i+1], n3[3*i+2]));
+        for (int k = 0; k < 3; ++k) { s3[3*i+k] = s[k]; t3[3*i+k] = t[k]; }
+    }
+}
+void ref_unit_angle(const float *a3, const float *b3, float *out, size_t n) {
+    for (size_t i = 0; i < n; ++i)
+        out[i] = dr::unit_angle(V3(a3[3*i], a3[3*i+1], a3[3*i+2]), V3(b3[3*i], b3[3*i+1], b3[3*i+2]));
+}
+void ref_rotator(const float *theta, float *m16, size_t n) { for (size_t i = 0; i < n; ++i) store(mueller::rotator<float>(theta[i]), m16 + 16*i); }
+void ref_rayleigh_scatter(const float *ct, const float *st, float rho, float *m16, size_t n) {
+    for (size_t i = 0; i < n; ++i) store(mueller::rayleigh_scatter<float>(ct[i], st[i], rho), m16 + 16*i);
+}
+void ref_rotate_mueller_basis(const float *m16_in, const float *v18, float *m16_out, size_t n) {
+    for (size_t i = 0; i < n; ++i) {
+        const float *v = v18 + 18*i;
+        MM R = mueller::rotate_mueller_basis(load(m16_in + 16*i), V3(v[0],v[1],v[2]), V3(v[3],v[4],v[5]), V3(v[6],v[7],v[8]),
+                                             V3(v[9],v[10],v[11]), V3(v[12],v[13],v[14]), V3(v[15],v[16],v[17]));
+        store(R, m16_out + 16*i);
+    }
+}
+void ref_mei_to_world_mueller(const float *m16_in, const float *d3, const float *in3, const float *out3, float *m16_out, size_t n) {
+    for (size_t i = 0; i < n; ++i) {
+        MediumInteraction<float, SpecPol> mei = dr::zeros<MediumInteraction<float, SpecPol>>();
+        mei.sh_frame = Frame<float>(V3(d3[3*i], d3[3*i+1], d3[3*i+2]));
+        MM Min = load(m16_in + 16*i);
+        SpecPol S;
+        for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) S(r, c) = Color<float, 1>(Min(r, c));
+        SpecPol R = mei.to_world_mueller(S, V3(in3[3*i], in3[3*i+1], in3[3*i+2]), V3(out3[3*i], out3[3*i+1], out3[3*i+2]));
+        for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) m16_out[16*i + 4*r + c] = R(r, c)[0];
+    }
+}
+void ref_square_to_uniform_sphere(const float *s2, float *o3, size_t n) {
+    for (size_t i = 0; i < n; ++i) { V3 v = warp::square_to_uniform_sphere(P2(s2[2*i], s2[2*i+1])); for (int k = 0; k < 3; ++k) o3[3*i+k] = v[k]; }
+}
+void ref_square_to_cosine_hemisphere(const float *s2, float *o3, size_t n) {
+    for (size_t i = 0; i < n; ++i) { V3 v = warp::square_to_cosine_hemisphere(P2(s2[2*i], s2[2*i+1])); for (int k = 0; k < 3; ++k) o3[3*i+k] = v[k]; }
+}
+void ref_texture3_eval(const float *data, int rx, int ry, int rz, int ch, int filter, int wrap, const float *p3, float *out, size_t n) {
+    using Tex = dr::Texture<float, 3>;
+    size_t shape[3] = { (size_t) rz, (size_t) ry, (size_t) rx };
+    dr::FilterMode fm = filter == 0 ? dr::FilterMode::Nearest : dr::FilterMode::Linear;
+    dr::WrapMode wm = wrap == 0 ? dr::WrapMode::Repeat : (wrap == 1 ? dr::WrapMode::Mirror : dr::WrapMode::Clamp);
+    Tex tex(shape, (size_t) ch, false, fm, wm);
+    size_t total = (size_t) rx * ry * rz * ch;
+    dr::DynamicArray<float> arr = dr::load<dr::DynamicArray<float>>(data, total);
+    tex.set_value(arr);
+    for (size_t i = 0; i < n; ++i) {
+        dr::Array<float, 3> p(p3[3*i], p3[3*i+1], p3[3*i+2]);
+        float o[3] = { 0, 0, 0 };
+        tex.eval_nonaccel(p, o);
+        for (int k = 0; k < ch; ++k) out[ch*i + k] = o[k];
+    }
+}
+void ref_irregular(const float *nodes, const float *pdf, uint32_t size, const float *x, float *eval_out, float *evaln_out,
+                   const float *u, float *sample_out, size_t n, float *integral) {
+    IrregularContinuousDistribution<float> d(nodes, pdf, size);
+    *integral = d.integral();
+    for (size_t i = 0; i < n; ++i) { eval_out[i] = d.eval_pdf(x[i]); evaln_out[i] = d.eval_pdf_normalized(x[i], true); sample_out[i] = d.sample(u[i]); }
+}
+void ref_transform_point(const float *m16, const float *p3, float *o3, size_t n) {
+    Transform<Point<float, 4>> T; dr::Matrix<float, 4> M;
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) M(r, c) = m16[4*r + c];
+    T = Transform<Point<float, 4>>(M);
+    for (size_t i = 0; i < n; ++i) { P3 v = T * P3(p3[3*i], p3[3*i+1], p3[3*i+2]); for (int k = 0; k < 3; ++k) o3[3*i+k] = v[k]; }
+}
+void ref_transform_vector(const float *m16, const float *p3, float *o3, size_t n) {
+    dr::Matrix<float, 4> M;
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) M(r, c) = m16[4*r + c];
+    Transform<Point<float, 4>> T(M);
+    for (size_t i = 0; i < n; ++i) { V3 v = T * V3(p3[3*i], p3[3*i+1], p3[3*i+2]); for (int k = 0; k < 3; ++k) o3[3*i+k] = v[k]; }
+}
+
+} // extern "C"
