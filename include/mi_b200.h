@@ -251,6 +251,11 @@ int  mib_counters_get(mib_scene *scene, mib_counters *out);
 /* The CUDA stream the scene launches on (cudaStream_t as void*). */
 int  mib_scene_stream(mib_scene *scene, void **stream);
 
+/* Test hooks (no reference counterpart): per-lane sample values and device math. */
+int  mib_debug_sample_lanes(mib_scene *scene, uint32_t seed, uint32_t spp, uint64_t lane_begin,
+                            uint64_t count, float *out_host /* [count][C] */);
+int  mib_debug_math(int op /*0 sincos,1 exp,2 log,3 cbrt,4 asin*/, const float *in_host, float *out_host, size_t n);
+
 #ifdef __cplusplus
 }
 #endif

@@ -101,6 +101,7 @@ EXPORTS = [
     "mib_render_1", "mib_render_1_raw", "mib_render_backward", "mib_render_1_backward",
     "mib_grad_get", "mib_grad_dev", "mib_grad_get_scalar", "mib_grad_zero",
     "mib_counters_get", "mib_scene_stream",
+    "mib_debug_sample_lanes", "mib_debug_math",
 ]
 
 

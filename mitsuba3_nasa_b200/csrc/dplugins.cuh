@@ -1,0 +1,257 @@
+// dplugins.cuh -- phase functions, emitters, BSDFs, sensors as inlined device code.
+// Reference: src/phase/{hg,rayleigh,isotropic,tabphase,tabphase_polarized}.cpp,
+// src/emitters/{constant,directional}.cpp, src/bsdfs/{null,diffuse}.cpp,
+// src/sensors/{perspective,distant,radiancemeter}.cpp, include/mitsuba/core/warp.h.
+#pragma once
+#include "dspec.cuh"
+
+namespace mib {
+
+// ---- warp.h ----
+MIB_D V3 square_to_uniform_sphere(float sx, float sy) {                    // warp.h:250-255
+    float z = fnma_(2.f, sy, 1.f), r = safe_sqrt_(fnma_(z, z, 1.f)), s, c;
+    sincos_(2.f * kPi * sx, s, c);
+    return v3(r * c, r * s, z);
+}
+MIB_D void square_to_uniform_disk_concentric(float sx, float sy, float &ox, float &oy) { // warp.h:54-90
+    float x = fms_(2.f, sx, 1.f), y = fms_(2.f, sy, 1.f);
+    bool is_zero = x == 0.f && y == 0.f, q13 = fabsf(x) < fabsf(y);
+    float r = q13 ? y : x, rp = q13 ? x : y;
+    float phi = __fdiv_rn(0.25f * kPi * rp, r);
+    if (q13) phi = 0.5f * kPi - phi;
+    if (is_zero) phi = 0.f;
+    float s, c;
+    sincos_(phi, s, c);
+    ox = r * c; oy = r * s;
+}
+MIB_D V3 square_to_cosine_hemisphere(float sx, float sy) {                 // warp.h:412-420
+    float px, py;
+    square_to_uniform_disk_concentric(sx, sy, px, py);
+    return v3(px, py, safe_sqrt_(1.f - fma_(py, py, px * px)));
+}
+
+// ---- phase functions: wo local (+z = ray.d), wi = (0,0,-1) ----
+MIB_D float eval_hg(float g, float cos_theta) {                             // hg.cpp:66-71
+    float temp = 1.f + sqr_(g) + 2.f * g * cos_theta;
+    return __fdiv_rn(kInvFourPi * (1.f - sqr_(g)), temp * sqrt_(temp));
+}
+MIB_D float rayleigh_pdf(float c) { return (3.f / 16.f) * kInvPi * (1.f + sqr_(c)); }
+// mueller.h:311-328, scaled matrix
+MIB_D void rayleigh_matrix(float cos_theta, float sin_theta, float rho, float *M) {
+    float r1 = __fdiv_rn(1.f - rho, 1.f + __fdiv_rn(rho, 2.f)), r2 = __fdiv_rn(1.f + rho, 1.f - rho),
+          r3 = __fdiv_rn(1.f - 2.f * rho, 1.f - rho);
+    float a = r2 + sqr_(cos_theta), b = 1.f + sqr_(cos_theta), c = -sqr_(sin_theta), d = 2.f * cos_theta;
+    float k = (3.f / 16.f) * kInvPi * r1;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) M[i] = k * 0.f;
+    M[0] = k * a; M[1] = k * c; M[4] = k * c; M[5] = k * b; M[10] = k * d; M[15] = k * (d * r3);
+}
+
+// eval_pdf: W = phase value (Mueller in local Stokes frames, or one float replicated), returns pdf
+template <int SPEC>
+MIB_D float phase_eval(const DScene &sc, int idx, V3 wo, float *W) {
+    constexpr bool POL = ST<SPEC>::POL;
+    constexpr int NC = ST<SPEC>::NC;
+    const mib_phase &p = sc.d.phases[idx];
+    const V3 wi = v3(0.f, 0.f, -1.f);
+    float val, pdf;
+    switch (p.type) {
+        case MIB_PHASE_ISOTROPIC: val = pdf = kInvFourPi; break;                        // isotropic.cpp:51-58
+        case MIB_PHASE_HG: val = pdf = eval_hg(p.g, dot(wo, wi)); break;                 // hg.cpp:96-104
+        case MIB_PHASE_TABPHASE: {                                                       // tabphase.cpp:121-133
+            float ct = -dot(wo, wi);
+            val = pdf = tab_eval(sc.tables[idx][0], ct) * sc.tables[idx][0].normalization * kInvTwoPi;
+            break;
+        }
+        case MIB_PHASE_RAYLEIGH: {                                                       // rayleigh.cpp:118-128
+            float ct = dot(wo, -wi);
+            pdf = rayleigh_pdf(ct);
+            if constexpr (POL) {
+                rayleigh_matrix(ct, safe_sqrt_(1.0f - sqr_(ct)), p.depolarization, W);
+                m4_phase_rotate(W, wo, wi);
+                return pdf;
+            } else {
+                float rho = p.depolarization, r1 = __fdiv_rn(1.f - rho, 1.f + __fdiv_rn(rho, 2.f)), r2 = __fdiv_rn(1.f + rho, 1.f - rho);
+                val = (3.f / 16.f) * kInvPi * r1 * (r2 + sqr_(ct));
+            }
+            break;
+        }
+        default: {                                                                       // tabphase_polarized.cpp:146-205
+            float ct = -dot(wo, wi);
+            float m11 = tab_eval(sc.tables[idx][0], ct);
+            pdf = m11 * sc.tables[idx][0].normalization * kInvTwoPi;
+            if constexpr (POL) {
+                float m12 = tab_eval(sc.tables[idx][1], ct), m33 = tab_eval(sc.tables[idx][2], ct), m34 = tab_eval(sc.tables[idx][3], ct);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) W[i] = 0.f;
+                W[0] = m11; W[1] = m12; W[4] = m12; W[5] = m11; W[10] = m33; W[11] = m34; W[14] = -m34; W[15] = m33;
+                m4_phase_rotate(W, wo, wi);
+                return pdf;
+            } else val = m11;
+            break;
+        }
+    }
+    if constexpr (POL) m4_identity(W, val);
+    else { for (int c = 0; c < NC; ++c) W[c] = val; }
+    return pdf;
+}
+
+// sample: returns pdf, writes local wo and the weight W
+template <int SPEC>
+MIB_D float phase_sample(const DScene &sc, int idx, float s2x, float s2y, V3 &wo, float *W) {
+    constexpr bool POL = ST<SPEC>::POL;
+    constexpr int NC = ST<SPEC>::NC;
+    const mib_phase &p = sc.d.phases[idx];
+    float pdf, ct, sp, cp;
+    switch (p.type) {
+        case MIB_PHASE_ISOTROPIC:                                                        // isotropic.cpp:40-49
+            wo = square_to_uniform_sphere(s2x, s2y);
+            pdf = kInvFourPi;
+            break;
+        case MIB_PHASE_HG: {                                                             // hg.cpp:73-94
+            float g = p.g;
+            float sqr_term = __fdiv_rn(1.f - sqr_(g), 1.f - g + 2.f * g * s2x);
+            ct = __fdiv_rn(1.f + sqr_(g) - sqr_(sqr_term), 2.f * g);
+            if (fabsf(g) < kEps) ct = 1.f - 2.f * s2x;
+            float st = safe_sqrt_(1.f - sqr_(ct));
+            sincos_(2.f * kPi * s2y, sp, cp);
+            wo = v3(st * cp, st * sp, ct);
+            pdf = eval_hg(g, -ct);
+            break;
+        }
+        case MIB_PHASE_RAYLEIGH: {                                                       // rayleigh.cpp:100-116
+            float z = 2.f * (2.f * s2x - 1.f), tmp = sqrt_(sqr_(z) + 1.f);
+            float A = cbrt_(z + tmp), B = cbrt_(z - tmp);
+            ct = A + B;
+            float st = safe_sqrt_(1.0f - sqr_(ct));
+            sincos_(kTwoPi * s2y, sp, cp);
+            wo = v3(st * cp, st * sp, ct);
+            pdf = rayleigh_pdf(ct);
+            float ipdf = rcp_(pdf);
+            if constexpr (POL) {
+                rayleigh_matrix(ct, st, p.depolarization, W);
+                m4_phase_rotate(W, wo, v3(0.f, 0.f, -1.f));
+#pragma unroll
+                for (int i = 0; i < 16; ++i) W[i] *= ipdf;
+            } else {
+                float rho = p.depolarization, r1 = __fdiv_rn(1.f - rho, 1.f + __fdiv_rn(rho, 2.f)), r2 = __fdiv_rn(1.f + rho, 1.f - rho);
+                float val = (3.f / 16.f) * kInvPi * r1 * (r2 + sqr_(ct));
+                for (int c = 0; c < NC; ++c) W[c] = val * ipdf;
+            }
+            return pdf;
+        }
+        case MIB_PHASE_TABPHASE: {                                                       // tabphase.cpp:91-119
+            ct = tab_sample(sc.tables[idx][0], s2x);
+            float st = safe_sqrt_(1.f - ct * ct);
+            sincos_(2.f * kPi * s2y, sp, cp);
+            wo = v3(st * cp, st * sp, ct);
+            pdf = tab_eval(sc.tables[idx][0], ct) * sc.tables[idx][0].normalization * kInvTwoPi;
+            break;
+        }
+        default: {                                                                       // tabphase_polarized.cpp:119-144
+            ct = tab_sample(sc.tables[idx][0], s2x);
+            float st = safe_sqrt_(1.f - ct * ct);
+            sincos_(2.f * kPi * s2y, sp, cp);
+            wo = v3(st * cp, st * sp, ct);
+            pdf = phase_eval<SPEC>(sc, idx, wo, W);
+            float ipdf = rcp_(pdf);
+#pragma unroll
+            for (int i = 0; i < ST<SPEC>::NT; ++i) W[i] *= ipdf;
+            return pdf;
+        }
+    }
+    if constexpr (POL) m4_identity(W, 1.f);
+    else { for (int c = 0; c < NC; ++c) W[c] = 1.f; }
+    return pdf;
+}
+
+// ---- emitters (constant.cpp:116-146, directional.cpp:150-177, scene.cpp:227-353) ----
+template <int NC> struct DirSample { V3 p, d; float dist, pdf; bool delta; int emitter; };
+
+template <int NC>
+MIB_D void sample_emitter_direction(const DScene &sc, V3 ref_p, float sx, float sy, DirSample<NC> &ds, float *spec) {
+    int n = sc.d.n_emitters;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) spec[c] = 0.f;
+    ds.pdf = 0.f; ds.dist = 0.f; ds.delta = false; ds.emitter = -1; ds.p = v3(0.f); ds.d = v3(0.f);
+    if (n == 0) return;
+    int index = 0;
+    float weight = 1.f, pmf = 1.f;
+    if (n > 1) {
+        float ec = (float) n, scaled = sx * ec;
+        index = (int) min((uint32_t) scaled, (uint32_t) n - 1u);
+        sx = scaled - (float) index;
+        weight = ec;
+        pmf = rcp_(ec);
+    }
+    const mib_emitter &e = sc.d.emitters[index];
+    if (e.type == MIB_EMITTER_CONSTANT) {
+        V3 d = square_to_uniform_sphere(sx, sy);
+        V3 c = v3(e.bsphere_center[0], e.bsphere_center[1], e.bsphere_center[2]);
+        float radius = fmaxf(e.bsphere_radius, norm(ref_p - c)), dist = 2.f * radius;
+        ds.p = vfma(d, dist, ref_p); ds.pdf = kInvFourPi; ds.delta = false; ds.d = d; ds.dist = dist;
+        float ip = rcp_(ds.pdf);
+#pragma unroll
+        for (int c2 = 0; c2 < NC; ++c2) spec[c2] = e.radiance[NC == 3 ? c2 : 0] * ip;
+    } else if (e.type == MIB_EMITTER_DIRECTIONAL) {
+        V3 d = v3(e.direction[0], e.direction[1], e.direction[2]);
+        float dist = inf_f();
+        ds.p = ref_p - d * dist; ds.pdf = 1.f; ds.delta = true; ds.d = -d; ds.dist = dist;
+#pragma unroll
+        for (int c2 = 0; c2 < NC; ++c2) spec[c2] = e.radiance[NC == 3 ? c2 : 0];
+    }
+    ds.emitter = index;
+    if (n > 1) {
+        ds.pdf *= pmf;
+#pragma unroll
+        for (int c2 = 0; c2 < NC; ++c2) spec[c2] *= weight;
+    }
+}
+MIB_D float pdf_emitter_direction(const DScene &sc, int emitter) {          // scene.cpp:355-366
+    const mib_emitter &e = sc.d.emitters[emitter];
+    float pmf = sc.d.n_emitters > 1 ? rcp_((float) sc.d.n_emitters) : 1.f;
+    return (e.type == MIB_EMITTER_CONSTANT ? kInvFourPi : 0.f) * pmf;
+}
+MIB_D int si_emitter(const DScene &sc, const SurfIt &si) {
+    return valid(si) ? sc.d.shapes[si.shape].emitter : sc.d.environment;
+}
+
+// ---- BSDF flags (include/mitsuba/render/bsdf.h:37-64) ----
+constexpr uint32_t kBsdfNull = 0x1, kBsdfDiffuseRefl = 0x2, kBsdfSmooth = 0x2 | 0x4 | 0x8 | 0x10, kBsdfDelta = 0x1 | 0x20 | 0x40;
+
+// ---- sensors ----
+MIB_D Ray sensor_ray(const DScene &sc, float px, float py, float ax, float ay) {
+    const mib_sensor &s = sc.d.sensor;
+    Ray ray;
+    if (s.type == MIB_SENSOR_PERSPECTIVE) {                                  // perspective.cpp:201-235
+        float ox = __fdiv_rn((float) s.film_width * s.principal_point_offset[0], (float) s.crop_width),
+              oy = __fdiv_rn((float) s.film_height * s.principal_point_offset[1], (float) s.crop_height);
+        V3 near_p = xform_point(s.sample_to_camera, v3(px + ox, py + oy, 0.f));
+        V3 d = normalize(near_p);
+        ray.o = v3(s.to_world[3], s.to_world[7], s.to_world[11]);
+        ray.d = xform_vector(s.to_world, d);
+        float inv_z = rcp_(d.z), near_t = s.near_clip * inv_z, far_t = s.far_clip * inv_z;
+        ray.o = ray.o + ray.d * near_t;
+        ray.maxt = far_t - near_t;
+    } else if (s.type == MIB_SENSOR_DISTANT) {                               // distant.cpp:193-235
+        ray.d = xform_vector(s.to_world, v3(0.f, 0.f, 1.f));
+        if (s.target_type == 1) {
+            ray.o = v3(s.target[0], s.target[1], s.target[2]) - 2.f * ray.d * s.bsphere_radius;
+        } else {
+            float ox, oy;
+            square_to_uniform_disk_concentric(ax, ay, ox, oy);
+            V3 perp = xform_vector(s.to_world, v3(ox, oy, 0.f));
+            V3 c = v3(s.bsphere_center[0], s.bsphere_center[1], s.bsphere_center[2]);
+            ray.o = c + perp * s.bsphere_radius - ray.d * s.bsphere_radius;
+        }
+        ray.maxt = largest_f();
+    } else {                                                                 // radiancemeter.cpp:97-126
+        ray.o = xform_point_affine(s.to_world, v3(0.f));
+        ray.d = xform_vector(s.to_world, v3(0.f, 0.f, 1.f));
+        ray.o = ray.o + ray.d * kRayEps;
+        ray.maxt = largest_f();
+    }
+    return ray;
+}
+
+} // namespace mib

@@ -1,0 +1,345 @@
+// dscene.cuh -- device-side scene: analytic shapes, media, grid lookups, tables.
+//
+// The whole scene description travels as ONE __grid_constant__ kernel parameter
+// (a few KiB, served by the constant cache): plugin types are enum tags, there
+// is no virtual dispatch on the device.
+#pragma once
+#include "dmath.cuh"
+#include "../../include/mi_b200.h"
+
+namespace mib {
+
+// include/mitsuba/core/distr_1d.h:618-989, prepared on the host (mib_scene_commit)
+struct DTable {
+    const float *nodes, *pdf, *cdf;
+    uint32_t n, valid_x, valid_y;
+    float integral, normalization, range_x, range_y;
+};
+
+struct DScene {
+    mib_scene_desc d;
+    const float *buffers[MIB_MAX_BUFFERS];
+    float *grad[MIB_MAX_BUFFERS];                 // gradient accumulators (adjoint), same shape as buffers
+    DTable tables[MIB_MAX_PHASES][4];             // m11, m12, m33, m34
+    float cube_normals[MIB_MAX_SHAPES][6][3];     // world-space outward face normals (-x,+x,-y,+y,-z,+z)
+};
+
+struct Ray { V3 o, d; float maxt; };
+MIB_D V3 ray_at(const Ray &r, float t) { return vfma(r.d, t, r.o); }
+
+struct Counters { unsigned long long n_lookups, n_real, n_null, n_nee_steps, n_surface; };
+
+// ------------------------------------------------------------------
+// Surface interaction (include/mitsuba/render/interaction.h)
+// ------------------------------------------------------------------
+struct SurfIt {
+    float t;
+    V3 p, n, wi;
+    Frame3 sh;
+    int shape;
+};
+MIB_D bool valid(const SurfIt &si) { return si.t != inf_f(); }
+
+// interaction.h:133-162
+MIB_D V3 offset_p(V3 p, V3 n, V3 d) {
+    float mag = (1.f + fmaxf(fmaxf(fabsf(p.x), fabsf(p.y)), fabsf(p.z))) * kRayEps;
+    mag = mulsign_ad(mag, dot(n, d));
+    return v3(fma_(mag, n.x, p.x), fma_(mag, n.y, p.y), fma_(mag, n.z, p.z));
+}
+MIB_D Ray spawn_ray(V3 p, V3 n, V3 d) { Ray r; r.o = offset_p(p, n, d); r.d = d; r.maxt = largest_f(); return r; }
+MIB_D Ray spawn_ray_to(V3 p, V3 n, V3 target) {
+    Ray r;
+    r.o = offset_p(p, n, target - p);
+    V3 d = target - r.o;
+    float dist = norm(d);
+    float inv = rcp_(dist);
+    r.d = v3(d.x * inv, d.y * inv, d.z * inv);
+    r.maxt = dist * (1.f - kShadowEps);
+    return r;
+}
+
+// Analytic intersection.  rectangle: src/shapes/rectangle.cpp:449-470 (+ :497-568, AD branch p = ray(t));
+// cube: slab test in object space; sphere: quadratic in object space.
+MIB_D float intersect_shape(const DScene &sc, int idx, const Ray &ray, int &face) {
+    const mib_shape &s = sc.d.shapes[idx];
+    V3 o = xform_point_affine(s.to_object, ray.o), d = xform_vector(s.to_object, ray.d);
+    face = 0;
+    if (s.type == MIB_SHAPE_RECTANGLE) {
+        float t = __fdiv_rn(-o.z, d.z);
+        float lx = fma_(d.x, t, o.x), ly = fma_(d.y, t, o.y);
+        bool hit = t >= 0.f && t <= ray.maxt && fabsf(lx) <= 1.f && fabsf(ly) <= 1.f;
+        return hit ? t : inf_f();
+    } else if (s.type == MIB_SHAPE_CUBE) {
+        float tn = -inf_f(), tf = inf_f();
+        int fn = 0, ff = 0;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            float oa = comp(o, a), inv = rcp_(comp(d, a));
+            float t1 = (-1.f - oa) * inv, t2 = (1.f - oa) * inv;
+            int f1 = 2 * a, f2 = 2 * a + 1;
+            if (t1 > t2) { float tt = t1; t1 = t2; t2 = tt; int ft = f1; f1 = f2; f2 = ft; }
+            if (t1 > tn) { tn = t1; fn = f1; }
+            if (t2 < tf) { tf = t2; ff = f2; }
+        }
+        if (!(tn <= tf)) return inf_f();
+        float t;
+        if (tn >= 0.f) { t = tn; face = fn; } else { t = tf; face = ff; }
+        if (!(t >= 0.f && t <= ray.maxt)) return inf_f();
+        return t;
+    } else {
+        float A = sqnorm(d), B = 2.f * dot(o, d), C = sqnorm(o) - 1.f;
+        float disc = fms_(B, B, 4.f * A * C);
+        if (!(disc >= 0.f)) return inf_f();
+        float sq = sqrt_(disc);
+        float q = -0.5f * (B + (B >= 0.f ? sq : -sq));
+        float t0 = __fdiv_rn(q, A), t1 = __fdiv_rn(C, q);
+        if (t0 > t1) { float tt = t0; t0 = t1; t1 = tt; }
+        float t = t0 >= 0.f ? t0 : t1;
+        if (!(t >= 0.f && t <= ray.maxt)) return inf_f();
+        return t;
+    }
+}
+
+// Scene::ray_intersect + finalize_surface_interaction (interaction.h:245-255, :464-484)
+MIB_D void ray_intersect(const DScene &sc, const Ray &ray, SurfIt &si) {
+    float best = inf_f();
+    int bs = -1, bf = 0;
+    for (int i = 0; i < sc.d.n_shapes; ++i) {
+        int face;
+        float t = intersect_shape(sc, i, ray, face);
+        if (t < best) { best = t; bs = i; bf = face; }
+    }
+    si.t = best;
+    si.shape = bs;
+    if (bs < 0) { si.wi = -ray.d; return; }
+    const mib_shape &s = sc.d.shapes[bs];
+    si.p = ray_at(ray, best);
+    V3 dp_du = v3(0.f);
+    if (s.type == MIB_SHAPE_RECTANGLE) {
+        si.n = v3(s.frame_n[0], s.frame_n[1], s.frame_n[2]);
+        dp_du = v3(s.frame_s[0], s.frame_s[1], s.frame_s[2]);
+    } else if (s.type == MIB_SHAPE_CUBE) {
+        const float *nn = sc.cube_normals[bs][bf];
+        si.n = v3(nn[0], nn[1], nn[2]);
+    } else {
+        si.n = normalize(si.p - v3(s.center[0], s.center[1], s.center[2]));
+    }
+    V3 n = si.n;
+    si.sh.n = n;
+    si.sh.s = normalize(vfma(n, -dot(n, dp_du), dp_du));
+    if (dp_du.x == 0.f && dp_du.y == 0.f && dp_du.z == 0.f) { V3 s2, t2; coordinate_system(n, s2, t2); si.sh.s = s2; }
+    si.sh.t = cross(n, si.sh.s);
+    si.wi = to_local(si.sh, -ray.d);
+}
+
+MIB_D int target_medium(const DScene &sc, const SurfIt &si, V3 d) {              // interaction.h:285-299
+    const mib_shape &s = sc.d.shapes[si.shape];
+    return dot(d, si.n) > 0.f ? s.exterior_medium : s.interior_medium;
+}
+MIB_D bool is_medium_transition(const DScene &sc, const SurfIt &si) {
+    const mib_shape &s = sc.d.shapes[si.shape];
+    return s.interior_medium >= 0 || s.exterior_medium >= 0;
+}
+
+// ------------------------------------------------------------------
+// Grid lookups (drjit/texture.h:346-412, :1143-1172, :1270-1294; grid.cpp:545-575)
+// The 8 taps are plain read-only loads served from the 126 MB L2 (a 256^3 fp32
+// grid is 64 MiB and stays resident); accumulation order 000,100,010,...,111.
+// ------------------------------------------------------------------
+MIB_D int wrap_coord(int pos, int shape, int mode) {
+    if (mode == MIB_WRAP_CLAMP) return max(min(pos, shape - 1), 0);
+    int sn = pos < 0 ? pos + 1 : pos;
+    int dv = sn / shape;
+    int md = pos - dv * shape;
+    if (md < 0) md += shape;
+    if (mode == MIB_WRAP_MIRROR) md = (((dv & 1) == 0) != (pos < 0)) ? md : shape - 1 - md;
+    return md;
+}
+
+struct GridTaps { uint32_t idx[8]; float w[8]; };   // used by the adjoint to scatter through the same taps
+
+template <int NC>
+MIB_D void eval_grid(const DScene &sc, const mib_volume &v, V3 p, float *out, GridTaps *taps) {
+    V3 pl = xform_point(v.to_local, p);
+    const float *__restrict__ data = sc.buffers[v.buffer];
+    const int ch = v.channels, rx = v.res[0], ry = v.res[1], rz = v.res[2];
+    float tmp[3] = { 0.f, 0.f, 0.f };
+    if (v.filter == MIB_FILTER_NEAREST) {
+        int ix = wrap_coord((int) floorf(pl.x * (float) rx), rx, v.wrap), iy = wrap_coord((int) floorf(pl.y * (float) ry), ry, v.wrap),
+            iz = wrap_coord((int) floorf(pl.z * (float) rz), rz, v.wrap);
+        uint32_t idx = (((uint32_t) iz * ry + iy) * rx + ix) * ch;
+        for (int c = 0; c < ch; ++c) tmp[c] = __ldg(data + idx + c);
+        if (taps) { for (int k = 0; k < 8; ++k) { taps->idx[k] = idx; taps->w[k] = k == 0 ? 1.f : 0.f; } }
+    } else {
+        float fx = fma_(pl.x, (float) rx, -.5f), fy = fma_(pl.y, (float) ry, -.5f), fz = fma_(pl.z, (float) rz, -.5f);
+        float flx = floorf(fx), fly = floorf(fy), flz = floorf(fz);
+        int ix = (int) flx, iy = (int) fly, iz = (int) flz;
+        float w1x = fx - flx, w1y = fy - fly, w1z = fz - flz;
+        float w0x = 1.f - w1x, w0y = 1.f - w1y, w0z = 1.f - w1z;
+        int x0 = wrap_coord(ix, rx, v.wrap), x1 = wrap_coord(ix + 1, rx, v.wrap);
+        int y0 = wrap_coord(iy, ry, v.wrap), y1 = wrap_coord(iy + 1, ry, v.wrap);
+        int z0 = wrap_coord(iz, rz, v.wrap), z1 = wrap_coord(iz + 1, rz, v.wrap);
+        uint32_t r00 = ((uint32_t) z0 * ry + y0) * rx, r10 = ((uint32_t) z0 * ry + y1) * rx,
+                 r01 = ((uint32_t) z1 * ry + y0) * rx, r11 = ((uint32_t) z1 * ry + y1) * rx;
+        uint32_t id[8] = { (r00 + x0) * ch, (r00 + x1) * ch, (r10 + x0) * ch, (r10 + x1) * ch,
+                           (r01 + x0) * ch, (r01 + x1) * ch, (r11 + x0) * ch, (r11 + x1) * ch };
+        float w[8] = { w0x * w0y * w0z, w1x * w0y * w0z, w0x * w1y * w0z, w1x * w1y * w0z,
+                       w0x * w0y * w1z, w1x * w0y * w1z, w0x * w1y * w1z, w1x * w1y * w1z };
+        if (ch == 1) {
+            // issue the 8 independent loads first so they overlap in the memory pipeline
+            float val[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) val[k] = __ldg(data + id[k]);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) tmp[0] = fma_(val[k], w[k], tmp[0]);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+                for (int c = 0; c < 3; ++c) tmp[c] = fma_(__ldg(data + id[k] + c), w[k], tmp[c]);
+        }
+        if (taps) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { taps->idx[k] = id[k]; taps->w[k] = w[k]; }
+        }
+    }
+    if (ch == 1) { for (int c = 0; c < NC; ++c) out[c] = tmp[0]; }
+    else if (NC == 3) { out[0] = tmp[0]; out[1] = tmp[1]; out[2] = tmp[2]; }
+    else out[0] = tmp[0] * 0.212671f + tmp[1] * 0.715160f + tmp[2] * 0.072169f;
+}
+
+template <int NC>
+MIB_D void eval_volume(const DScene &sc, const mib_volume &v, V3 p, float *out, Counters &cnt, GridTaps *taps = nullptr) {
+    if (v.type == MIB_VOLUME_CONST) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) out[c] = v.value[v.channels == 1 ? 0 : c];
+        return;
+    }
+    cnt.n_lookups++;
+    eval_grid<NC>(sc, v, p, out, taps);
+}
+
+// include/mitsuba/core/bbox.h:303-326
+MIB_D bool bbox_intersect(const float *bmin, const float *bmax, const Ray &ray, float &mint, float &maxt) {
+    bool active = true;
+    float lo = -inf_f(), hi = inf_f();
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        float o = comp(ray.o, a), d = comp(ray.d, a);
+        active = active && ((d != 0.f) || (o > bmin[a]) || (o < bmax[a]));
+        float dr = rcp_(d);
+        float t1 = (bmin[a] - o) * dr, t2 = (bmax[a] - o) * dr;
+        float t1p = fminf(t1, t2), t2p = fmaxf(t1, t2);
+        lo = a == 0 ? t1p : fmaxf(lo, t1p);
+        hi = a == 0 ? t2p : fminf(hi, t2p);
+    }
+    mint = lo; maxt = hi;
+    return active && maxt >= mint;
+}
+
+// ------------------------------------------------------------------
+// Medium interaction (src/render/medium.cpp:40-86)
+// ------------------------------------------------------------------
+template <int NC> struct MedIt {
+    float t, mint;
+    V3 p;
+    Frame3 sh;                    // Frame(ray.d); wi = (0,0,-1)
+    float sigma_s[NC], sigma_n[NC], sigma_t[NC], maj[NC];
+    int medium;
+};
+template <int NC> MIB_D bool valid(const MedIt<NC> &m) { return m.t != inf_f(); }
+template <int NC> MIB_D float ch(const float *s, uint32_t c) { return NC == 3 ? s[c] : s[0]; }
+
+template <int NC>
+MIB_D void sample_interaction(const DScene &sc, int mi, const Ray &ray, float sample, uint32_t channel,
+                              MedIt<NC> &mei, Counters &cnt, GridTaps *taps = nullptr) {
+    const mib_medium &m = sc.d.media[mi];
+    mei.sh = make_frame(ray.d);
+    bool active = true;
+    float mint = 0.f, maxt = inf_f();
+    if (m.type != MIB_MEDIUM_HOMOGENEOUS)
+        active = bbox_intersect(m.sigma_t.bbox_min, m.sigma_t.bbox_max, ray, mint, maxt);
+    active = active && (isfinite(mint) || isfinite(maxt));
+    if (!active) { mint = 0.f; maxt = inf_f(); }
+    mint = fmaxf(0.f, mint);
+    maxt = fminf(ray.maxt, maxt);
+    if (m.type == MIB_MEDIUM_HOMOGENEOUS) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) mei.maj[c] = active ? m.sigma_t.value[m.sigma_t.channels == 1 ? 0 : c] * m.scale : 0.f;
+    } else {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) mei.maj[c] = m.max_density;
+    }
+    float mj = ch<NC>(mei.maj, channel);
+    float sampled_t = mint + __fdiv_rn(-log_(1.f - sample), mj);
+    bool valid_mi = active && (sampled_t <= maxt);
+    mei.t = valid_mi ? sampled_t : inf_f();
+    mei.p = ray_at(ray, sampled_t);
+    mei.medium = mi;
+    mei.mint = mint;
+    if (m.type == MIB_MEDIUM_HOMOGENEOUS) {
+        float alb[NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) alb[c] = 0.f;
+        if (valid_mi || m.albedo.type == MIB_VOLUME_CONST) eval_volume<NC>(sc, m.albedo, mei.p, alb, cnt);
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            float st = m.sigma_t.value[m.sigma_t.channels == 1 ? 0 : c] * m.scale;
+            mei.sigma_s[c] = valid_mi ? st * alb[c] : 0.f;
+            mei.sigma_n[c] = 0.f;
+            mei.sigma_t[c] = valid_mi ? st : 0.f;
+        }
+    } else {
+        float sv[NC], av[NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) { sv[c] = 0.f; av[c] = 0.f; }
+        if (valid_mi) eval_volume<NC>(sc, m.sigma_t, mei.p, sv, cnt, taps);
+        if (valid_mi || m.albedo.type == MIB_VOLUME_CONST) eval_volume<NC>(sc, m.albedo, mei.p, av, cnt);
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            float st = m.scale * sv[c];
+            mei.sigma_s[c] = st * av[c];
+            mei.sigma_n[c] = m.max_density - st;
+            mei.sigma_t[c] = st;
+        }
+    }
+}
+
+// ------------------------------------------------------------------
+// Irregular 1D distribution (distr_1d.h:707-729, :781-814; drjit/util.h:172-220)
+// Tables are a few KiB and stay in L1/L2; binary search = log2(N) dependent loads.
+// ------------------------------------------------------------------
+MIB_D float tab_eval(const DTable &t, float x) {
+    bool active = x >= t.range_x && x <= t.range_y;
+    uint32_t start = 0, end = t.n;
+    uint32_t iters = (start < end) ? (31 - __clz(end - start)) + 1 : 0;
+    for (uint32_t i = 0; i < iters; ++i) {
+        uint32_t mid = (start + end) >> 1;
+        float nv = (active && mid < t.n) ? __ldg(t.nodes + mid) : 0.f;
+        if (nv < x) start = min(mid + 1, end); else end = mid;
+    }
+    uint32_t index = max(min(start, t.n - 1u), 1u) - 1u;
+    float x0 = __ldg(t.nodes + index), x1 = __ldg(t.nodes + index + 1), y0 = __ldg(t.pdf + index), y1 = __ldg(t.pdf + index + 1);
+    x = __fdiv_rn(x - x0, x1 - x0);
+    return active ? fma_(x, y1 - y0, y0) : 0.f;
+}
+MIB_D float tab_sample(const DTable &t, float sample) {
+    sample *= t.integral;
+    uint32_t start = t.valid_x, end = t.valid_y;
+    uint32_t iters = (start < end) ? (31 - __clz(end - start)) + 1 : 0;
+    for (uint32_t i = 0; i < iters; ++i) {
+        uint32_t mid = (start + end) >> 1;
+        float value = __ldg(t.cdf + mid);
+        bool pred = ((value < sample) || (value == 0.f)) && (value != t.integral);
+        if (pred) start = min(mid + 1, end); else end = mid;
+    }
+    uint32_t index = start;
+    float x0 = __ldg(t.nodes + index), x1 = __ldg(t.nodes + index + 1), y0 = __ldg(t.pdf + index), y1 = __ldg(t.pdf + index + 1);
+    float c0 = index > 0 ? __ldg(t.cdf + index - 1) : 0.f, w = x1 - x0;
+    sample = __fdiv_rn(sample - c0, w);
+    float t_linear = __fdiv_rn(y0 - safe_sqrt_(sqr_(y0) + 2.f * sample * (y1 - y0)), y0 - y1);
+    float t_const = __fdiv_rn(sample, y0);
+    float tt = (y0 == y1) ? t_const : t_linear;
+    return fma_(tt, w, x0);
+}
+
+} // namespace mib

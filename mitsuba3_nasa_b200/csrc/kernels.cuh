@@ -1,0 +1,160 @@
+// kernels.cuh -- sm_100a kernels of the forward pass.
+//
+// Mapping: global lane l = (y*W + x)*spp + s, seeded TEA(base_seed+seed, l).
+// Each thread owns `spt` CONSECUTIVE lanes, i.e. (part of) the samples of one pixel:
+// the film contribution is accumulated in registers and leaves the thread with one
+// red.global.add per channel when the pixel changes -- no per-sample atomics, no
+// inter-thread exchange.  Grid = ceil(lanes / spt / 128) CTAs of 128 threads; with
+// spt chosen by the host the grid is many multiples of 148 SMs x resident CTAs.
+#pragma once
+#include "dwalk.cuh"
+
+namespace mib {
+
+struct LaunchParams {
+    uint32_t seed_value;       // sampler base seed + render seed
+    uint32_t spp;
+    uint64_t lane_begin, lane_end;
+    uint32_t spt;              // lanes per thread
+    int mode;                  // 0 = film accumulate, 1 = render_1 sums (double), 2 = per-sample dump
+    float *film;               // [H*W*C]
+    double *sums;              // [4]
+    float *per_sample;         // [lanes*C] (mode 2)
+    unsigned long long *counters; // [6]: lookups, real, null, nee_steps, surface, samples
+};
+
+template <int SPEC> struct RawChannels { static constexpr int C = SPEC == MIB_SPEC_MONO ? 2 : 4; };
+
+// integrator.cpp:1245-1267 applied to a Stokes vector (first column of spec2sensor * spec)
+MIB_D void to_sensor_stokes(const Ray &ray, float *S) {
+    V3 md = -ray.d;
+    V3 cur = stokes_basis(md);
+    V3 tmp = cross(md, v3(0.f, 0.f, 1.f));
+    bool vertical = norm(tmp) < kRayEps;
+    V3 tgt = vertical ? v3(1.f, 0.f, 0.f) : cross(md, normalize(tmp));
+    float c, s;
+    stokes_rotation(md, cur, tgt, c, s);
+    float s1 = S[1], s2 = S[2];
+    S[1] = fma_(s, s2, c * s1);
+    S[2] = fma_(c, s2, (-s) * s1);
+}
+
+template <int SPEC, bool AOS>
+__global__ void __launch_bounds__(128) k_forward(const __grid_constant__ DScene sc, const __grid_constant__ LaunchParams lp) {
+    constexpr int C = RawChannels<SPEC>::C, NR = ST<SPEC>::NR;
+    const mib_sensor &sn = sc.d.sensor;
+    uint64_t tid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t l0 = lp.lane_begin + tid * lp.spt;
+    uint64_t l1 = min(l0 + (uint64_t) lp.spt, lp.lane_end);
+    Counters cnt = { 0, 0, 0, 0, 0 };
+    unsigned long long n_samples = 0;
+    float acc[C];
+    double dacc[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) { acc[c] = 0.f; dacc[c] = 0.0; }
+    long long cur_pixel = -1;
+    const float scale_x = 1.f / (float) sn.crop_width, scale_y = 1.f / (float) sn.crop_height;
+    const float offset_x = -(float) sn.crop_offset_x * scale_x, offset_y = -(float) sn.crop_offset_y * scale_y;
+
+    for (uint64_t lane = l0; lane < l1; ++lane) {
+        Pcg32 rng;
+        rng.seed_lane(lp.seed_value, (uint32_t) lane);
+        // integrator.cpp:323-340: lane -> pixel
+        uint32_t idx = (uint32_t) (lane / lp.spp);
+        uint32_t py = idx / (uint32_t) sn.crop_width, px = idx - (uint32_t) sn.crop_width * py;
+        float posx = (float) ((int) px + sn.crop_offset_x), posy = (float) ((int) py + sn.crop_offset_y);
+        // render_sample (integrator.cpp:1139-1170)
+        float jx = rng.next(), jy = rng.next();
+        float sx = posx + jx, sy = posy + jy;
+        float ax = fma_(sx, scale_x, offset_x), ay = fma_(sy, scale_y, offset_y);
+        float apx = .5f, apy = .5f;
+        if (sn.needs_aperture_sample) { apx = rng.next(); apy = rng.next(); }
+        Ray ray = sensor_ray(sc, ax, ay, apx, apy);
+        float R[NR];
+        trace_path<SPEC, AOS>(sc, rng, cnt, ray, R);
+        n_samples++;
+        float aov[C];
+        if constexpr (SPEC == MIB_SPEC_RGB) { aov[0] = R[0]; aov[1] = R[1]; aov[2] = R[2]; aov[3] = 1.f; }
+        else if constexpr (SPEC == MIB_SPEC_MONO) { aov[0] = R[0]; aov[1] = 1.f; }
+        else { to_sensor_stokes(ray, R); aov[0] = R[0]; aov[1] = R[1]; aov[2] = R[2]; aov[3] = R[3]; }
+
+        if (lp.mode == 2) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) lp.per_sample[(lane - lp.lane_begin) * C + c] = aov[c];
+            continue;
+        }
+        // box-filter put (imageblock.cpp:206-232)
+        int ix = (int) floorf(sx) - sn.crop_offset_x, iy = (int) floorf(sy) - sn.crop_offset_y;
+        if ((uint32_t) ix >= (uint32_t) sn.crop_width || (uint32_t) iy >= (uint32_t) sn.crop_height) continue;
+        if (lp.mode == 1) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) dacc[c] += (double) aov[c];
+        } else {
+            long long pixel = (long long) iy * sn.crop_width + ix;
+            if (pixel != cur_pixel) {
+                if (cur_pixel >= 0) {
+#pragma unroll
+                    for (int c = 0; c < C; ++c) atomicAdd(lp.film + cur_pixel * C + c, acc[c]);
+                }
+#pragma unroll
+                for (int c = 0; c < C; ++c) acc[c] = 0.f;
+                cur_pixel = pixel;
+            }
+#pragma unroll
+            for (int c = 0; c < C; ++c) acc[c] += aov[c];
+        }
+    }
+    if (lp.mode == 0 && cur_pixel >= 0) {
+#pragma unroll
+        for (int c = 0; c < C; ++c) atomicAdd(lp.film + cur_pixel * C + c, acc[c]);
+    }
+    if (lp.mode == 1) {
+        // warp-level pre-aggregation, then one atomic per warp and channel
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            double v = dacc[c];
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if ((threadIdx.x & 31) == 0) atomicAdd(lp.sums + c, v);
+        }
+    }
+    unsigned long long cv[6] = { cnt.n_lookups, cnt.n_real, cnt.n_null, cnt.n_nee_steps, cnt.n_surface, n_samples };
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        unsigned long long v = cv[k];
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0 && v) atomicAdd(lp.counters + k, v);
+    }
+}
+
+// HDRFilm::develop (hdrfilm.cpp:304-418): value / (weight == 0 ? 1 : weight)
+template <int SPEC>
+__global__ void k_develop(const float *raw, float *out, size_t npix, uint32_t spp) {
+    size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npix) return;
+    if constexpr (SPEC == MIB_SPEC_RGB) {
+        float w = raw[4 * p + 3], dv = (w == 0.f) ? 1.f : w;
+        for (int c = 0; c < 3; ++c) out[3 * p + c] = __fdiv_rn(raw[4 * p + c], dv);
+    } else if constexpr (SPEC == MIB_SPEC_MONO) {
+        float I = raw[2 * p], w = raw[2 * p + 1], dv = (w == 0.f) ? 1.f : w;
+        float lum = I * 0.212671f + I * 0.715160f + I * 0.072169f;
+        out[p] = __fdiv_rn(lum, dv);
+    } else {
+        for (int c = 0; c < 4; ++c) out[4 * p + c] = (float) ((double) raw[4 * p + c] / (double) spp);
+    }
+}
+
+// grid maximum (gridvolume m_max, grid.cpp:306-319): grid-stride max + one atomic per block
+__global__ void k_max(const float *data, size_t n, unsigned int *out_bits) {
+    float m = -inf_f();
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x)
+        m = fmaxf(m, data[i]);
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) {
+        // order-preserving float -> uint key
+        unsigned int b = (unsigned int) __float_as_int(m);
+        b = (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+        atomicMax(out_bits, b);
+    }
+}
+
+} // namespace mib

@@ -1,0 +1,459 @@
+// mib_api.cu -- C ABI of libmi_b200.so (include/mi_b200.h) and the host-side
+// render drivers: passes, seeding, lane ranges, film develop (the C++ side of
+// SamplingIntegrator::render / render_1, src/render/integrator.cpp:150-743).
+// There is NO CPU fallback: every entry point needs a CUDA device and fails
+// with an error message otherwise.
+#include "kernels.cuh"
+#include "adjoint.cuh"
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <cmath>
+#include <stdexcept>
+
+using namespace mib;
+
+static_assert(sizeof(DScene) < 32000, "DScene must fit the kernel parameter space");
+
+static thread_local std::string g_err;
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            throw std::runtime_error(std::string(#call) + ": " + cudaGetErrorString(e_));         \
+    } while (0)
+
+struct mib_scene {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    DScene ds;                                   // host copy handed to kernels by value
+    float *buf[MIB_MAX_BUFFERS] = {};
+    size_t buf_n[MIB_MAX_BUFFERS] = {};
+    float *grad[MIB_MAX_BUFFERS] = {};
+    float *cdf[MIB_MAX_PHASES] = {};             // cdf of the m11 table per phase
+    float *film_raw = nullptr, *film_dev = nullptr;
+    size_t film_raw_n = 0, film_dev_n = 0;
+    double *sums = nullptr;                      // [8] device
+    unsigned long long *counters = nullptr;      // [8] device
+    unsigned int *maxbits = nullptr;
+    double *grad_scalar = nullptr;               // [MIB_MAX_MEDIA*4] device
+    float *lane_L = nullptr;                     // adjoint: per-lane primal radiance
+    size_t lane_L_n = 0;
+    uint64_t lane_begin = 0, lane_end = 0;
+    mib_counters last = {};
+    bool committed = false;
+    uint32_t last_spp = 1;
+};
+
+static int raw_channels(int spec) { return spec == MIB_SPEC_MONO ? 2 : 4; }
+static int dev_channels(int spec) { return spec == MIB_SPEC_MONO ? 1 : (spec == MIB_SPEC_RGB ? 3 : 4); }
+
+static void ensure_film(mib_scene *s) {
+    const mib_sensor &sn = s->ds.d.sensor;
+    size_t npix = (size_t) sn.crop_width * sn.crop_height;
+    size_t nr = npix * raw_channels(s->ds.d.spectrum), nd = npix * dev_channels(s->ds.d.spectrum);
+    if (nr != s->film_raw_n) {
+        if (s->film_raw) CK(cudaFree(s->film_raw));
+        CK(cudaMalloc(&s->film_raw, nr * sizeof(float)));
+        s->film_raw_n = nr;
+    }
+    if (nd != s->film_dev_n) {
+        if (s->film_dev) CK(cudaFree(s->film_dev));
+        CK(cudaMalloc(&s->film_dev, nd * sizeof(float)));
+        s->film_dev_n = nd;
+    }
+}
+
+static float device_max(mib_scene *s, const float *data, size_t n) {
+    CK(cudaMemsetAsync(s->maxbits, 0, sizeof(unsigned int), s->stream));
+    int blocks = (int) std::min<size_t>((n + 255) / 256, 148 * 8);
+    k_max<<<blocks, 256, 0, s->stream>>>(data, n, s->maxbits);
+    CK(cudaGetLastError());
+    unsigned int b = 0;
+    CK(cudaMemcpyAsync(&b, s->maxbits, sizeof(b), cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    b = (b & 0x80000000u) ? (b & 0x7fffffffu) : ~b;
+    float f;
+    memcpy(&f, &b, 4);
+    return f;
+}
+
+// IrregularContinuousDistribution::compute_cdf_scalar (include/mitsuba/core/distr_1d.h:916-975)
+static void build_table(mib_scene *s, int phase, int which, int buf_nodes, int buf_pdf, uint32_t n, bool sampling) {
+    DTable &t = s->ds.tables[phase][which];
+    memset(&t, 0, sizeof(t));
+    if (buf_nodes < 0 || buf_pdf < 0 || !s->buf[buf_nodes] || !s->buf[buf_pdf])
+        throw std::runtime_error("tabulated phase function: table buffer missing");
+    if (n < 2) throw std::runtime_error("IrregularContinuousDistribution: needs at least two entries!");
+    if (s->buf_n[buf_nodes] < n || s->buf_n[buf_pdf] < n) throw std::runtime_error("tabulated phase function: table buffer too small");
+    std::vector<float> nodes(n), pdf(n), cdf(n, 0.f);
+    CK(cudaMemcpy(nodes.data(), s->buf[buf_nodes], n * sizeof(float), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(pdf.data(), s->buf[buf_pdf], n * sizeof(float), cudaMemcpyDeviceToHost));
+    uint32_t vx = (uint32_t) -1, vy = (uint32_t) -1;
+    float rx = INFINITY, ry = -INFINITY;
+    double integral = 0.;
+    for (uint32_t i = 0; i + 1 < n; ++i) {
+        double x0 = nodes[i], x1 = nodes[i + 1], y0 = pdf[i], y1 = pdf[i + 1];
+        double value = 0.5 * (x1 - x0) * (y0 + y1);
+        rx = fminf(rx, (float) x0);
+        ry = fmaxf(ry, (float) x1);
+        integral += value;
+        cdf[i] = (float) integral;
+        if (!(x1 > x0)) throw std::runtime_error("IrregularContinuousDistribution: node positions must be strictly increasing!");
+        if (sampling) {
+            if (y0 < 0. || y1 < 0.) throw std::runtime_error("IrregularContinuousDistribution: entries must be non-negative!");
+            else if (value > 0.) { if (vx == (uint32_t) -1) vx = i; vy = i; }
+        }
+    }
+    t.nodes = s->buf[buf_nodes];
+    t.pdf = s->buf[buf_pdf];
+    t.n = n;
+    t.range_x = rx; t.range_y = ry;
+    if (sampling) {
+        if (vx == (uint32_t) -1) throw std::runtime_error("IrregularContinuousDistribution: no probability mass found!");
+        t.valid_x = vx; t.valid_y = vy;
+        t.integral = cdf[vy];
+        t.normalization = 1.f / t.integral;
+        if (s->cdf[phase]) CK(cudaFree(s->cdf[phase]));
+        CK(cudaMalloc(&s->cdf[phase], n * sizeof(float)));
+        CK(cudaMemcpy(s->cdf[phase], cdf.data(), n * sizeof(float), cudaMemcpyHostToDevice));
+        t.cdf = s->cdf[phase];
+    }
+}
+
+static void commit(mib_scene *s) {
+    mib_scene_desc &d = s->ds.d;
+    for (int i = 0; i < MIB_MAX_BUFFERS; ++i) { s->ds.buffers[i] = s->buf[i]; s->ds.grad[i] = s->grad[i]; }
+    for (int i = 0; i < d.n_media; ++i) {
+        mib_medium &m = d.media[i];
+        mib_volume *vols[2] = { &m.sigma_t, &m.albedo };
+        for (mib_volume *v : vols) {
+            if (v->type == MIB_VOLUME_GRID) {
+                size_t n = (size_t) v->res[0] * v->res[1] * v->res[2] * v->channels;
+                if (v->buffer < 0 || v->buffer >= MIB_MAX_BUFFERS || !s->buf[v->buffer] || s->buf_n[v->buffer] < n)
+                    throw std::runtime_error("gridvolume: data buffer missing or too small");
+                v->max_value = device_max(s, s->buf[v->buffer], n);
+            } else {
+                v->max_value = v->value[0];
+                for (int c = 1; c < v->channels; ++c) v->max_value = fmaxf(v->max_value, v->value[c]);
+            }
+        }
+        m.max_density = m.scale * m.sigma_t.max_value;           // heterogeneous.cpp:163,176-178
+    }
+    for (int i = 0; i < d.n_phases; ++i) {
+        const mib_phase &p = d.phases[i];
+        if (p.type == MIB_PHASE_TABPHASE || p.type == MIB_PHASE_TABPHASE_POLARIZED) {
+            build_table(s, i, 0, p.buf_nodes, p.buf_m11, p.n_nodes, true);
+            if (p.type == MIB_PHASE_TABPHASE_POLARIZED) {
+                build_table(s, i, 1, p.buf_nodes, p.buf_m12, p.n_nodes, false);
+                build_table(s, i, 2, p.buf_nodes, p.buf_m33, p.n_nodes, false);
+                build_table(s, i, 3, p.buf_nodes, p.buf_m34, p.n_nodes, false);
+            }
+        }
+    }
+    for (int i = 0; i < d.n_shapes; ++i) {
+        if (d.shapes[i].type != MIB_SHAPE_CUBE) continue;
+        const float *T = d.shapes[i].to_object;                   // normals: transpose(to_object) (transform.h:146-155)
+        for (int f = 0; f < 6; ++f) {
+            float nl[3] = { 0, 0, 0 };
+            nl[f / 2] = (f & 1) ? 1.f : -1.f;
+            float nw[3];
+            for (int r = 0; r < 3; ++r)
+                nw[r] = fmaf(T[8 + r], nl[2], fmaf(T[4 + r], nl[1], T[r] * nl[0]));
+            float sq = fmaf(nw[2], nw[2], fmaf(nw[1], nw[1], nw[0] * nw[0]));
+            float inv = sqrtf(1.f / sq);
+            for (int r = 0; r < 3; ++r) s->ds.cube_normals[i][f][r] = nw[r] * inv;
+        }
+    }
+    ensure_film(s);
+    s->committed = true;
+}
+
+// ---------------------------------------------------------------------------
+// Launch helpers
+// ---------------------------------------------------------------------------
+static uint32_t pick_spt(uint64_t lanes, uint32_t spp) {
+    // Aim for >= 8 waves of 148 SMs x 16 resident CTAs x 128 threads while keeping all
+    // lanes of a thread inside one pixel whenever spp allows (one film flush per thread).
+    const uint64_t target_threads = 148ull * 16 * 128 * 8;
+    uint64_t spt = lanes / target_threads;
+    if (spt < 1) spt = 1;
+    if (spt > 256) spt = 256;
+    if (spp >= spt) { while (spp % spt) --spt; }   // largest divisor of spp not above the target
+    return (uint32_t) spt;
+}
+
+template <int SPEC, bool AOS>
+static void launch_forward(mib_scene *s, const LaunchParams &lp) {
+    uint64_t lanes = lp.lane_end - lp.lane_begin;
+    uint64_t threads = (lanes + lp.spt - 1) / lp.spt;
+    uint64_t blocks = (threads + 127) / 128;
+    if (blocks == 0) return;
+    if (blocks > 0x7fffffffull) throw std::runtime_error("render: too many blocks");
+    k_forward<SPEC, AOS><<<(unsigned) blocks, 128, 0, s->stream>>>(s->ds, lp);
+    CK(cudaGetLastError());
+}
+
+static void dispatch_forward(mib_scene *s, const LaunchParams &lp) {
+    int spec = s->ds.d.spectrum, integ = s->ds.d.integrator.type;
+    if (integ != MIB_INTEG_VOLPATH && integ != MIB_INTEG_VOLPATHAOS)
+        throw std::runtime_error("forward kernel: integrator type not handled here");
+    bool aos = integ == MIB_INTEG_VOLPATHAOS;
+    switch (spec * 2 + (aos ? 1 : 0)) {
+        case 0: launch_forward<0, false>(s, lp); break;
+        case 1: launch_forward<0, true>(s, lp); break;
+        case 2: launch_forward<1, false>(s, lp); break;
+        case 3: launch_forward<1, true>(s, lp); break;
+        case 4: launch_forward<2, false>(s, lp); break;
+        case 5: launch_forward<2, true>(s, lp); break;
+        default: throw std::runtime_error("unknown spectrum kind");
+    }
+}
+
+static void lane_range(mib_scene *s, uint32_t spp, uint64_t &b, uint64_t &e) {
+    const mib_sensor &sn = s->ds.d.sensor;
+    uint64_t total = (uint64_t) sn.crop_width * sn.crop_height * spp;
+    // integrator.cpp:566-578: the reference's wavefront is limited to 2^32 lanes (32-bit lane index in the seed)
+    if (total > 0xffffffffull)
+        throw std::runtime_error("Tried to perform a rendering with a total sample count that exceeds 2^32 "
+                                 "(the upper limit for one pass). Please use fewer samples per pixel or render using multiple passes.");
+    if (s->lane_begin == 0 && s->lane_end == 0) { b = 0; e = total; }
+    else { b = std::min(s->lane_begin, total); e = std::min(s->lane_end, total); }
+}
+
+static void fetch_counters(mib_scene *s, float ms, uint64_t launches) {
+    unsigned long long c[8];
+    CK(cudaMemcpy(c, s->counters, sizeof(c), cudaMemcpyDeviceToHost));
+    s->last.n_lookups = c[0]; s->last.n_real = c[1]; s->last.n_null = c[2];
+    s->last.n_nee_steps = c[3]; s->last.n_surface = c[4]; s->last.n_samples = c[5];
+    s->last.kernel_ms = ms; s->last.n_launches = launches;
+}
+
+// mode 0: film, mode 1: sums, mode 2: per-sample dump into per_sample_dev
+static void run_forward(mib_scene *s, uint32_t seed, uint32_t spp, int mode, float *per_sample_dev) {
+    if (!s->committed) throw std::runtime_error("mib_scene_commit() must be called before rendering");
+    if (spp == 0) throw std::runtime_error("spp must be > 0");
+    if (s->ds.d.sensor.rfilter != MIB_RFILTER_BOX)
+        throw std::runtime_error("only the box reconstruction filter is implemented on the device in this build");
+    CK(cudaSetDevice(s->device));
+    LaunchParams lp;
+    lp.seed_value = s->ds.d.sampler_base_seed + seed;
+    lp.spp = spp;
+    lane_range(s, spp, lp.lane_begin, lp.lane_end);
+    lp.spt = pick_spt(lp.lane_end - lp.lane_begin, spp);
+    lp.mode = mode;
+    lp.film = s->film_raw;
+    lp.sums = s->sums;
+    lp.per_sample = per_sample_dev;
+    lp.counters = s->counters;
+    CK(cudaMemsetAsync(s->counters, 0, 8 * sizeof(unsigned long long), s->stream));
+    if (mode == 0) CK(cudaMemsetAsync(s->film_raw, 0, s->film_raw_n * sizeof(float), s->stream));
+    if (mode == 1) CK(cudaMemsetAsync(s->sums, 0, 8 * sizeof(double), s->stream));
+    CK(cudaEventRecord(s->ev0, s->stream));
+    dispatch_forward(s, lp);
+    CK(cudaEventRecord(s->ev1, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+    fetch_counters(s, ms, 1);
+    s->last_spp = spp;
+}
+
+static void develop(mib_scene *s) {
+    const mib_sensor &sn = s->ds.d.sensor;
+    size_t npix = (size_t) sn.crop_width * sn.crop_height;
+    unsigned blocks = (unsigned) ((npix + 255) / 256);
+    switch (s->ds.d.spectrum) {
+        case MIB_SPEC_MONO: k_develop<0><<<blocks, 256, 0, s->stream>>>(s->film_raw, s->film_dev, npix, s->last_spp); break;
+        case MIB_SPEC_RGB: k_develop<1><<<blocks, 256, 0, s->stream>>>(s->film_raw, s->film_dev, npix, s->last_spp); break;
+        default: k_develop<2><<<blocks, 256, 0, s->stream>>>(s->film_raw, s->film_dev, npix, s->last_spp); break;
+    }
+    CK(cudaGetLastError());
+    s->last.n_launches += 1;
+}
+
+// ---------------------------------------------------------------------------
+// extern "C" entry points (include/mi_b200.h)
+// ---------------------------------------------------------------------------
+#define MIB_TRY try {
+#define MIB_CATCH                                                       \
+    } catch (const std::exception &e) { g_err = e.what(); return 1; }   \
+    return 0;
+
+extern "C" {
+
+const char *mib_last_error(void) { return g_err.c_str(); }
+int mib_abi_version(void) { return MIB_ABI_VERSION; }
+size_t mib_sizeof_scene_desc(void) { return sizeof(mib_scene_desc); }
+
+int mib_scene_create(const mib_scene_desc *desc, int device, mib_scene **out) {
+    MIB_TRY
+    if (!desc || !out) throw std::runtime_error("mib_scene_create: null argument");
+    if (desc->abi_version != MIB_ABI_VERSION) throw std::runtime_error("mib_scene_create: ABI version mismatch");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        throw std::runtime_error("mib_scene_create: no CUDA device available (this library has no CPU fallback)");
+    if (device < 0 || device >= ndev) throw std::runtime_error("mib_scene_create: invalid device ordinal");
+    CK(cudaSetDevice(device));
+    mib_scene *s = new mib_scene();
+    s->device = device;
+    memset(&s->ds, 0, sizeof(s->ds));
+    s->ds.d = *desc;
+    CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&s->ev0));
+    CK(cudaEventCreate(&s->ev1));
+    CK(cudaMalloc(&s->sums, 8 * sizeof(double)));
+    CK(cudaMalloc(&s->counters, 8 * sizeof(unsigned long long)));
+    CK(cudaMalloc(&s->maxbits, sizeof(unsigned int)));
+    CK(cudaMalloc(&s->grad_scalar, MIB_MAX_MEDIA * 4 * sizeof(double)));
+    CK(cudaMemset(s->grad_scalar, 0, MIB_MAX_MEDIA * 4 * sizeof(double)));
+    *out = s;
+    MIB_CATCH
+}
+
+int mib_scene_destroy(mib_scene *s) {
+    MIB_TRY
+    if (!s) return 0;
+    cudaSetDevice(s->device);
+    for (int i = 0; i < MIB_MAX_BUFFERS; ++i) { if (s->buf[i]) cudaFree(s->buf[i]); if (s->grad[i]) cudaFree(s->grad[i]); }
+    for (int i = 0; i < MIB_MAX_PHASES; ++i) if (s->cdf[i]) cudaFree(s->cdf[i]);
+    if (s->film_raw) cudaFree(s->film_raw);
+    if (s->film_dev) cudaFree(s->film_dev);
+    if (s->lane_L) cudaFree(s->lane_L);
+    cudaFree(s->sums); cudaFree(s->counters); cudaFree(s->maxbits); cudaFree(s->grad_scalar);
+    cudaEventDestroy(s->ev0); cudaEventDestroy(s->ev1);
+    cudaStreamDestroy(s->stream);
+    delete s;
+    MIB_CATCH
+}
+
+int mib_scene_set_buffer(mib_scene *s, int idx, const float *host, size_t count) {
+    MIB_TRY
+    if (idx < 0 || idx >= MIB_MAX_BUFFERS) throw std::runtime_error("mib_scene_set_buffer: slot out of range");
+    if (!host || count == 0) throw std::runtime_error("mib_scene_set_buffer: empty buffer");
+    CK(cudaSetDevice(s->device));
+    if (s->buf_n[idx] != count) {
+        if (s->buf[idx]) CK(cudaFree(s->buf[idx]));
+        if (s->grad[idx]) { CK(cudaFree(s->grad[idx])); s->grad[idx] = nullptr; }
+        CK(cudaMalloc(&s->buf[idx], count * sizeof(float)));
+        s->buf_n[idx] = count;
+    }
+    CK(cudaMemcpyAsync(s->buf[idx], host, count * sizeof(float), cudaMemcpyHostToDevice, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    s->committed = false;
+    MIB_CATCH
+}
+
+int mib_scene_get_buffer(mib_scene *s, int idx, float *host, size_t count) {
+    MIB_TRY
+    if (idx < 0 || idx >= MIB_MAX_BUFFERS || !s->buf[idx] || count > s->buf_n[idx]) throw std::runtime_error("mib_scene_get_buffer: bad slot/size");
+    CK(cudaMemcpy(host, s->buf[idx], count * sizeof(float), cudaMemcpyDeviceToHost));
+    MIB_CATCH
+}
+
+int mib_scene_buffer_dev(mib_scene *s, int idx, float **dev, size_t *count) {
+    MIB_TRY
+    if (idx < 0 || idx >= MIB_MAX_BUFFERS || !s->buf[idx]) throw std::runtime_error("mib_scene_buffer_dev: bad slot");
+    *dev = s->buf[idx]; *count = s->buf_n[idx];
+    s->committed = false;   // the caller may write through the pointer: derived data must be recomputed
+    MIB_CATCH
+}
+
+int mib_scene_set_desc(mib_scene *s, const mib_scene_desc *desc) {
+    MIB_TRY
+    if (desc->abi_version != MIB_ABI_VERSION) throw std::runtime_error("mib_scene_set_desc: ABI version mismatch");
+    s->ds.d = *desc;
+    s->committed = false;
+    MIB_CATCH
+}
+
+int mib_scene_commit(mib_scene *s) {
+    MIB_TRY
+    CK(cudaSetDevice(s->device));
+    commit(s);
+    MIB_CATCH
+}
+
+int mib_scene_get_desc(mib_scene *s, mib_scene_desc *out) { *out = s->ds.d; return 0; }
+
+int mib_scene_set_lane_range(mib_scene *s, uint64_t b, uint64_t e) {
+    MIB_TRY
+    if (e < b) throw std::runtime_error("mib_scene_set_lane_range: end < begin");
+    s->lane_begin = b; s->lane_end = e;
+    MIB_CATCH
+}
+
+int mib_render(mib_scene *s, uint32_t seed, uint32_t spp, int do_develop, float *out_host) {
+    MIB_TRY
+    run_forward(s, seed, spp, 0, nullptr);
+    if (do_develop) develop(s);
+    if (out_host) {
+        if (do_develop) CK(cudaMemcpyAsync(out_host, s->film_dev, s->film_dev_n * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+        else CK(cudaMemcpyAsync(out_host, s->film_raw, s->film_raw_n * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+    }
+    CK(cudaStreamSynchronize(s->stream));
+    MIB_CATCH
+}
+
+int mib_film_dev(mib_scene *s, float **raw_dev, size_t *raw_count, float **developed_dev, size_t *developed_count) {
+    MIB_TRY
+    if (!s->committed) throw std::runtime_error("mib_film_dev: scene not committed");
+    if (raw_dev) *raw_dev = s->film_raw;
+    if (raw_count) *raw_count = s->film_raw_n;
+    if (developed_dev) *developed_dev = s->film_dev;
+    if (developed_count) *developed_count = s->film_dev_n;
+    MIB_CATCH
+}
+
+int mib_film_develop(mib_scene *s) {
+    MIB_TRY
+    CK(cudaSetDevice(s->device));
+    develop(s);
+    CK(cudaStreamSynchronize(s->stream));
+    MIB_CATCH
+}
+
+static int render_1_impl(mib_scene *s, uint32_t seed, uint32_t spp, double *out4, bool normalize) {
+    MIB_TRY
+    if (s->ds.d.spectrum == MIB_SPEC_RGB)
+        throw std::runtime_error("This render loop only supports monochromatic and spectral modes!");   // integrator.cpp:409-410
+    run_forward(s, seed, spp, 1, nullptr);
+    double h[8];
+    CK(cudaMemcpy(h, s->sums, sizeof(h), cudaMemcpyDeviceToHost));
+    int nch = s->ds.d.spectrum == MIB_SPEC_MONO_POLARIZED ? 4 : 1;
+    const mib_sensor &sn = s->ds.d.sensor;
+    // integrator.cpp:702-705: nf = rcp((float) n_pixels * total_samples_done)
+    float nf = 1.f / ((float) ((size_t) sn.crop_width * sn.crop_height) * (float) spp);
+    for (int c = 0; c < 4; ++c) out4[c] = c < nch ? (normalize ? h[c] * (double) nf : h[c]) : 0.0;
+    MIB_CATCH
+}
+int mib_render_1(mib_scene *s, uint32_t seed, uint32_t spp, double *out4) { return render_1_impl(s, seed, spp, out4, true); }
+int mib_render_1_raw(mib_scene *s, uint32_t seed, uint32_t spp, double *out4) { return render_1_impl(s, seed, spp, out4, false); }
+
+int mib_counters_get(mib_scene *s, mib_counters *out) { *out = s->last; return 0; }
+int mib_scene_stream(mib_scene *s, void **stream) { *stream = (void *) s->stream; return 0; }
+
+// Debug / test hook: per-lane aovs (C floats per lane) for lanes [lane_begin, lane_begin+count)
+int mib_debug_sample_lanes(mib_scene *s, uint32_t seed, uint32_t spp, uint64_t lane_begin, uint64_t count, float *out_host) {
+    MIB_TRY
+    CK(cudaSetDevice(s->device));
+    int C = raw_channels(s->ds.d.spectrum);
+    float *dev = nullptr;
+    CK(cudaMalloc(&dev, count * C * sizeof(float)));
+    uint64_t sb = s->lane_begin, se = s->lane_end;
+    s->lane_begin = lane_begin; s->lane_end = lane_begin + count;
+    try { run_forward(s, seed, spp, 2, dev); } catch (...) { s->lane_begin = sb; s->lane_end = se; cudaFree(dev); throw; }
+    s->lane_begin = sb; s->lane_end = se;
+    CK(cudaMemcpy(out_host, dev, count * C * sizeof(float), cudaMemcpyDeviceToHost));
+    CK(cudaFree(dev));
+    MIB_CATCH
+}
+
+} // extern "C"
+
+#include "mib_api_adjoint.inc"
+#include "mib_api_debug.inc"
