@@ -1,0 +1,216 @@
+"""The reference-facing Python surface for the volumetric hot path.
+
+Mirrors src/python/python/util.py (traverse :292-350, SceneParameters :20-290,
+render :512-625, render_1 :627-670) and the integrator methods of
+src/python/python/ad/integrators/common.py (render, render_1, render_backward,
+render_1_backward).  Computation happens only in libmi_b200.so (CUDA).
+"""
+import numpy as np
+
+from . import _abi as A
+from . import scene as _scene
+from ._lib import DeviceScene
+
+_VARIANTS = ['scalar_rgb', 'llvm_ad_rgb', 'llvm_ad_mono', 'llvm_ad_mono_polarized',
+             'b200_ad_rgb', 'b200_ad_mono', 'b200_ad_mono_polarized']
+_variant = None
+
+
+def variants():
+    return list(_VARIANTS)
+
+
+def set_variant(*names):
+    """mi.set_variant: accepts the reference's variant names; results are defined to equal llvm_ad_*."""
+    global _variant
+    for n in names:
+        if n in _VARIANTS:
+            _variant = n
+            return
+    raise ImportError("Requested an unsupported variant \"%s\". The following variants are available: %s."
+                      % (", ".join(names), ", ".join(_VARIANTS)))
+
+
+def variant():
+    return _variant
+
+
+def sample_tea_32(v0, v1, rounds=4):
+    """include/mitsuba/core/random.h:76-91 (host copy, used for seed_grad: util.py:617-619)."""
+    v0, v1, s = int(v0) & 0xffffffff, int(v1) & 0xffffffff, 0
+    for _ in range(rounds):
+        s = (s + 0x9e3779b9) & 0xffffffff
+        v0 = (v0 + ((((v1 << 4) & 0xffffffff) + 0xa341316c) ^ ((v1 + s) & 0xffffffff) ^ ((v1 >> 5) + 0xc8013ea4))) & 0xffffffff
+        v1 = (v1 + ((((v0 << 4) & 0xffffffff) + 0xad90777d) ^ ((v0 + s) & 0xffffffff) ^ ((v0 >> 5) + 0x7e95761e))) & 0xffffffff
+    return v0, v1
+
+
+class Integrator:
+    """Integrator object bound to a scene (volpath, volpathaos, prbvolpath, prb_volpathaos)."""
+
+    def __init__(self, scene):
+        self._scene = scene
+
+    def render(self, scene=None, sensor=0, seed=0, spp=0, develop=True, evaluate=True):
+        return (scene or self._scene)._render(seed, spp, develop)
+
+    def render_1(self, scene=None, sensor=0, seed=0, spp=0, develop=True, evaluate=True, thread_count=0):
+        return (scene or self._scene)._render_1(seed, spp)
+
+    def render_backward(self, scene, params, grad_in, sensor=0, seed=0, spp=0):
+        (scene or self._scene)._render_backward(seed, spp, grad_in)
+
+    def render_1_backward(self, scene, params, grad_in, sensor=0, seed=0, spp=0):
+        (scene or self._scene)._render_1_backward(seed, spp, grad_in)
+
+
+class Scene:
+    """mi.Scene stand-in: the flattened description + its device replica."""
+
+    def __init__(self, flat, device=0):
+        self.flat = flat
+        self.device = DeviceScene(flat, device)
+        self._integrator = Integrator(self)
+
+    def integrator(self):
+        return self._integrator
+
+    def sensors(self):
+        return [self.flat.desc.sensor]
+
+    def _spp(self, spp):
+        return int(spp) if spp else int(self.flat.sample_count)
+
+    def _render(self, seed, spp, develop=True):
+        return self.device.render(int(seed), self._spp(spp), develop=develop)
+
+    def _render_1(self, seed, spp):
+        out = self.device.render_1(int(seed), self._spp(spp))
+        if self.flat.desc.spectrum == A.SPEC_MONO_POLARIZED:
+            m = np.zeros((4, 4), np.float64)     # integrator.cpp:707-713: Stokes vector in column 0
+            m[:, 0] = out
+            return m
+        return float(out[0])
+
+    def _render_backward(self, seed, spp, grad_in):
+        self.device.render_backward(int(seed), self._spp(spp), grad_in)
+
+    def _render_1_backward(self, seed, spp, grad_in):
+        g = np.asarray(grad_in, dtype=np.float64)
+        if g.ndim == 2:
+            g = g[:, 0]
+        self.device.render_1_backward(int(seed), self._spp(spp), g)
+
+    def counters(self):
+        return self.device.counters()
+
+
+def load_dict(d, parallel=True, device=0):
+    """mi.load_dict (src/core/python/xml_v.cpp:112-146)."""
+    if _variant is None:
+        raise ImportError("set_variant() must be called before load_dict()")
+    return Scene(_scene.load_dict(d, _variant), device)
+
+
+class SceneParameters:
+    """Dictionary-like parameter map (util.py:20-290): params[key] = value; params.update()."""
+
+    def __init__(self, scene):
+        self.scene = scene
+        self._dirty = set()
+        self._grad_enabled = set()
+
+    def keys(self):
+        return sorted(self.scene.flat.params.keys())
+
+    def __contains__(self, k):
+        return k in self.scene.flat.params
+
+    def __iter__(self):
+        return iter(self.keys())
+
+    def __len__(self):
+        return len(self.scene.flat.params)
+
+    def items(self):
+        return [(k, self[k]) for k in self.keys()]
+
+    def __getitem__(self, key):
+        if key not in self.scene.flat.params:
+            raise KeyError(key)
+        acc = self.scene.flat.params[key]
+        f = self.scene.flat
+        kind = acc['kind']
+        if kind == 'buffer':
+            return f.buffers[acc['slot']].reshape(f.buffer_shapes[acc['slot']])
+        if kind == 'volume_const':
+            v = acc['vol']
+            return np.array(v.value[:]) if f.spectrum == A.SPEC_RGB else float(v.value[0])
+        if kind == 'phase_g':
+            return float(acc['phase'].g)
+        if kind == 'medium_scale':
+            return float(acc['medium'].scale)
+        if kind == 'bsdf_reflectance':
+            b = acc['bsdf']
+            return np.array(b.reflectance[:]) if f.spectrum == A.SPEC_RGB else float(b.reflectance[0])
+        if kind == 'emitter_radiance':
+            e = acc['emitter']
+            return np.array(e.radiance[:]) if f.spectrum == A.SPEC_RGB else float(e.radiance[0])
+        raise KeyError(key)
+
+    def __setitem__(self, key, value):
+        if key not in self.scene.flat.params:
+            raise KeyError(key)
+        acc = self.scene.flat.params[key]
+        f = self.scene.flat
+        kind = acc['kind']
+        if kind == 'buffer':
+            arr = np.ascontiguousarray(np.asarray(value, dtype=np.float32))
+            slot = acc['slot']
+            if arr.size != f.buffers[slot].size:
+                raise ValueError("set: size mismatch for '%s' (%d vs %d); resizing grids is not supported" %
+                                 (key, arr.size, f.buffers[slot].size))
+            f.buffers[slot] = arr.reshape(-1).copy()
+        elif kind in ('volume_const', 'bsdf_reflectance', 'emitter_radiance'):
+            tgt = {'volume_const': 'vol', 'bsdf_reflectance': 'bsdf', 'emitter_radiance': 'emitter'}[kind]
+            field = {'volume_const': 'value', 'bsdf_reflectance': 'reflectance', 'emitter_radiance': 'radiance'}[kind]
+            col = np.broadcast_to(np.asarray(value, dtype=np.float64), (3,))
+            getattr(acc[tgt], field)[:] = [float(x) for x in col]
+            if kind == 'volume_const':
+                acc['vol'].channels = 3 if (f.spectrum == A.SPEC_RGB and len(set(col.tolist())) > 1) else 1
+        elif kind == 'phase_g':
+            acc['phase'].g = float(value)
+        elif kind == 'medium_scale':
+            acc['medium'].scale = float(value)
+        self._dirty.add(key)
+
+    def update(self, values=None):
+        """Push modified parameters to the device and recompute derived data (parameters_changed)."""
+        if values:
+            for k, v in values.items():
+                self[k] = v
+        f, dev = self.scene.flat, self.scene.device
+        for key in self._dirty:
+            acc = f.params[key]
+            if acc['kind'] == 'buffer':
+                dev.set_buffer(acc['slot'], f.buffers[acc['slot']])
+        dev.set_desc(f.desc)
+        dev.commit()
+        done = sorted(self._dirty)
+        self._dirty.clear()
+        return done
+
+
+def traverse(scene):
+    """mi.traverse (util.py:292-350)."""
+    return SceneParameters(scene)
+
+
+def render(scene, params=None, sensor=0, integrator=None, seed=0, seed_grad=0, spp=0, spp_grad=0):
+    """mi.render (util.py:512-625), primal part; the differentiable wrapper lives in .ad"""
+    return scene.integrator().render(scene, sensor, seed, spp, develop=True, evaluate=False)
+
+
+def render_1(scene, params=None, sensor=0, integrator=None, seed=0, seed_grad=0, spp=0, spp_grad=0):
+    """mi.render_1 (util.py:627-670): one Spectrum / Mueller matrix (Stokes vector in column 0)."""
+    return scene.integrator().render_1(scene, sensor, seed, spp)
