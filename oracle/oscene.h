@@ -317,6 +317,34 @@ static inline Color<NC> eval_volume(const Scene &sc, const mib_volume &v, Vec3 p
     return out;
 }
 
+// Trilinear taps (indices into the data buffer for channel 0, weights) of a grid lookup: the adjoint
+// scatters d(value)/d(voxel_k) = w_k through the same 8 taps (drjit/texture.h:366-408).
+static inline int grid_taps(const mib_volume &v, Vec3 p, uint32_t *idx, float *w) {
+    Mat4 T = mat4_from(v.to_local);
+    Vec3 pl = transform_point(T, p);
+    const int ch = v.channels, rx = v.res[0], ry = v.res[1], rz = v.res[2];
+    if (v.filter == MIB_FILTER_NEAREST) {
+        int ix = wrap_coord((int) std::floor(pl.x * (float) rx), rx, v.wrap), iy = wrap_coord((int) std::floor(pl.y * (float) ry), ry, v.wrap),
+            iz = wrap_coord((int) std::floor(pl.z * (float) rz), rz, v.wrap);
+        idx[0] = (((uint32_t) iz * ry + iy) * rx + ix) * ch; w[0] = 1.f;
+        return 1;
+    }
+    float fx = fmadd(pl.x, (float) rx, -.5f), fy = fmadd(pl.y, (float) ry, -.5f), fz = fmadd(pl.z, (float) rz, -.5f);
+    int ix = (int) std::floor(fx), iy = (int) std::floor(fy), iz = (int) std::floor(fz);
+    float w1x = fx - (float) ix, w1y = fy - (float) iy, w1z = fz - (float) iz;
+    float w0x = 1.f - w1x, w0y = 1.f - w1y, w0z = 1.f - w1z;
+    const int xs[2] = { wrap_coord(ix, rx, v.wrap), wrap_coord(ix + 1, rx, v.wrap) },
+              ys[2] = { wrap_coord(iy, ry, v.wrap), wrap_coord(iy + 1, ry, v.wrap) },
+              zs[2] = { wrap_coord(iz, rz, v.wrap), wrap_coord(iz + 1, rz, v.wrap) };
+    const float wx[2] = { w0x, w1x }, wy[2] = { w0y, w1y }, wz[2] = { w0z, w1z };
+    for (int k = 0; k < 8; ++k) {
+        int a = k & 1, b = (k >> 1) & 1, c3 = (k >> 2) & 1;
+        idx[k] = (((uint32_t) zs[c3] * ry + ys[b]) * rx + xs[a]) * ch;
+        w[k] = wx[a] * wy[b] * wz[c3];
+    }
+    return 8;
+}
+
 // bbox.h:303-326
 static inline bool bbox_ray_intersect(const float *bmin, const float *bmax, const Ray &ray, float *mint, float *maxt) {
     bool active = true;

@@ -96,6 +96,32 @@ class OracleScene:
                                           C.c_int(nthreads), C.c_int(int(normalize)), fp(out)))
         return out
 
+    # ---- adjoint (oracle/oracle_adjoint_api.inc) ----
+    def render_backward(self, seed, spp, grad_in, lanes=(0, 0), nthreads=8):
+        g = np.ascontiguousarray(np.asarray(grad_in, np.float32).reshape(self.H, self.W, self.dev_channels))
+        self._check(self.lib.orc_render_backward(self.h, C.c_uint32(seed), C.c_uint32(spp), fp(g), C.c_uint64(lanes[0]),
+                                                 C.c_uint64(lanes[1]), C.c_int(nthreads)))
+
+    def render_1_backward(self, seed, spp, grad4, lanes=(0, 0), nthreads=8):
+        g = np.zeros(4, np.float64)
+        gi = np.asarray(grad4, np.float64).reshape(-1)
+        g[:gi.size] = gi
+        self._check(self.lib.orc_render_1_backward(self.h, C.c_uint32(seed), C.c_uint32(spp), fp(g), C.c_uint64(lanes[0]),
+                                                   C.c_uint64(lanes[1]), C.c_int(nthreads)))
+
+    def grad_get(self, slot, count):
+        out = np.zeros(count, np.float64)
+        self._check(self.lib.orc_grad_get(self.h, C.c_int(slot), fp(out), C.c_size_t(count)))
+        return out
+
+    def grad_get_scalar(self, medium=0):
+        out = np.zeros(4, np.float64)
+        self._check(self.lib.orc_grad_get_scalar(self.h, C.c_int(medium), fp(out)))
+        return out
+
+    def grad_zero(self):
+        self._check(self.lib.orc_grad_zero(self.h))
+
     def counters(self):
         c = A.Counters()
         self.lib.orc_counters_get(self.h, C.byref(c))
