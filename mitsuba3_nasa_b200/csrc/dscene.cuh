@@ -22,6 +22,8 @@ struct DScene {
     float *grad[MIB_MAX_BUFFERS];                 // gradient accumulators (adjoint), same shape as buffers
     DTable tables[MIB_MAX_PHASES][4];             // m11, m12, m33, m34
     float cube_normals[MIB_MAX_SHAPES][6][3];     // world-space outward face normals (-x,+x,-y,+y,-z,+z)
+    double *grad_scalar;                          // [MIB_MAX_MEDIA*4] constant-volume gradients (adjoint)
+    int prb_null, prb_homog;                      // prepare_scene flags (prbvolpath.py:76-89)
 };
 
 struct Ray { V3 o, d; float maxt; };

@@ -7,7 +7,7 @@
 // inter-thread exchange.  Grid = ceil(lanes / spt / 128) CTAs of 128 threads; with
 // spt chosen by the host the grid is many multiples of 148 SMs x resident CTAs.
 #pragma once
-#include "dwalk.cuh"
+#include "adjoint.cuh"
 
 namespace mib {
 
@@ -39,7 +39,8 @@ MIB_D void to_sensor_stokes(const Ray &ray, float *S) {
     S[2] = fma_(c, s2, (-s) * s1);
 }
 
-template <int SPEC, bool AOS>
+// MODE: 0 volpath, 1 volpathaos, 2 prbvolpath (primal), 3 prb_volpathaos (primal)
+template <int SPEC, int MODE>
 __global__ void __launch_bounds__(128) k_forward(const __grid_constant__ DScene sc, const __grid_constant__ LaunchParams lp) {
     constexpr int C = RawChannels<SPEC>::C, NR = ST<SPEC>::NR;
     const mib_sensor &sn = sc.d.sensor;
@@ -71,7 +72,12 @@ __global__ void __launch_bounds__(128) k_forward(const __grid_constant__ DScene 
         if (sn.needs_aperture_sample) { apx = rng.next(); apy = rng.next(); }
         Ray ray = sensor_ray(sc, ax, ay, apx, apy);
         float R[NR];
-        trace_path<SPEC, AOS>(sc, rng, cnt, ray, R);
+        if constexpr (MODE <= 1) trace_path<SPEC, MODE == 1>(sc, rng, cnt, ray, R);
+        else {
+            Sink sink;
+            sink.init();
+            prb_walk<SPEC, MODE == 3>(sc, rng, cnt, ray, false, nullptr, nullptr, sink, R);
+        }
         n_samples++;
         float aov[C];
         if constexpr (SPEC == MIB_SPEC_RGB) { aov[0] = R[0]; aov[1] = R[1]; aov[2] = R[2]; aov[3] = 1.f; }
@@ -117,6 +123,69 @@ __global__ void __launch_bounds__(128) k_forward(const __grid_constant__ DScene 
             if ((threadIdx.x & 31) == 0) atomicAdd(lp.sums + c, v);
         }
     }
+    unsigned long long cv[6] = { cnt.n_lookups, cnt.n_real, cnt.n_null, cnt.n_nee_steps, cnt.n_surface, n_samples };
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        unsigned long long v = cv[k];
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0 && v) atomicAdd(lp.counters + k, v);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Adjoint kernel (common.py:828-1102): per lane, primal walk -> L, then the replay with
+// the same PCG32 state that scatters parameter gradients.  Same lane -> thread mapping as
+// k_forward so that neighbouring threads walk neighbouring samples of one pixel.
+// ---------------------------------------------------------------------------
+template <int SPEC>
+__global__ void __launch_bounds__(128) k_adjoint(const __grid_constant__ DScene sc, const __grid_constant__ LaunchParams lp,
+                                                 const __grid_constant__ AdjParams ap) {
+    constexpr int NR = ST<SPEC>::NR, Cd = SPEC == MIB_SPEC_MONO ? 1 : (SPEC == MIB_SPEC_RGB ? 3 : 4);
+    constexpr bool AOS = ST<SPEC>::POL;
+    const mib_sensor &sn = sc.d.sensor;
+    uint64_t tid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t l0 = lp.lane_begin + tid * lp.spt;
+    uint64_t l1 = min(l0 + (uint64_t) lp.spt, lp.lane_end);
+    Counters cnt = { 0, 0, 0, 0, 0 };
+    unsigned long long n_samples = 0;
+    Sink sink;
+    sink.init();
+    const float scale_x = 1.f / (float) sn.crop_width, scale_y = 1.f / (float) sn.crop_height;
+    const float offset_x = -(float) sn.crop_offset_x * scale_x, offset_y = -(float) sn.crop_offset_y * scale_y;
+    const float nf = rcp_((float) ((uint32_t) sn.crop_width * (uint32_t) sn.crop_height * lp.spp));   // common.py:1046
+
+    for (uint64_t lane = l0; lane < l1; ++lane) {
+        Pcg32 rng;
+        rng.seed_lane(lp.seed_value, (uint32_t) lane);
+        uint32_t idx = (uint32_t) (lane / lp.spp);
+        uint32_t py = idx / (uint32_t) sn.crop_width, px = idx - (uint32_t) sn.crop_width * py;
+        float posx = (float) ((int) px + sn.crop_offset_x), posy = (float) ((int) py + sn.crop_offset_y);
+        float jx = rng.next(), jy = rng.next();
+        float sx = posx + jx, sy = posy + jy;
+        float ax = fma_(sx, scale_x, offset_x), ay = fma_(sy, scale_y, offset_y);
+        float apx = .5f, apy = .5f;
+        if (sn.needs_aperture_sample) { apx = rng.next(); apy = rng.next(); }
+        Ray ray = sensor_ray(sc, ax, ay, apx, apy);
+        n_samples++;
+        float dl[4] = { 0.f, 0.f, 0.f, 0.f };
+        if (ap.render_1) {
+#pragma unroll
+            for (int c = 0; c < Cd; ++c) dl[c] = ap.grad1[c] * nf;
+        } else {
+            int ix = (int) floorf(sx) - sn.crop_offset_x, iy = (int) floorf(sy) - sn.crop_offset_y;
+            if ((uint32_t) ix < (uint32_t) sn.crop_width && (uint32_t) iy < (uint32_t) sn.crop_height) {
+                size_t pixel = (size_t) iy * sn.crop_width + ix;
+#pragma unroll
+                for (int c = 0; c < Cd; ++c) dl[c] = __fdiv_rn(__ldg(ap.grad_image + pixel * Cd + c), (float) lp.spp);
+            }
+        }
+        const Pcg32 start = rng;
+        float Lp[NR], Lres[NR];
+        prb_walk<SPEC, AOS>(sc, rng, cnt, ray, false, nullptr, nullptr, sink, Lp);
+        rng = start;
+        prb_walk<SPEC, AOS>(sc, rng, cnt, ray, true, Lp, dl, sink, Lres);
+    }
+    sink.flush(sc);
     unsigned long long cv[6] = { cnt.n_lookups, cnt.n_real, cnt.n_null, cnt.n_nee_steps, cnt.n_surface, n_samples };
 #pragma unroll
     for (int k = 0; k < 6; ++k) {

@@ -168,6 +168,16 @@ static void commit(mib_scene *s) {
             for (int r = 0; r < 3; ++r) s->ds.cube_normals[i][f][r] = nw[r] * inv;
         }
     }
+    // prepare_scene (prbvolpath.py:76-89): which special cases the prb walks need
+    s->ds.prb_null = 0; s->ds.prb_homog = 0;
+    for (int i = 0; i < d.n_shapes; ++i)
+        for (int m : { d.shapes[i].interior_medium, d.shapes[i].exterior_medium })
+            if (m >= 0) {
+                bool hom = d.media[m].type == MIB_MEDIUM_HOMOGENEOUS;
+                s->ds.prb_homog |= hom ? 1 : 0;
+                s->ds.prb_null |= hom ? 0 : 1;
+            }
+    s->ds.grad_scalar = s->grad_scalar;
     ensure_film(s);
     s->committed = true;
 }
@@ -186,30 +196,36 @@ static uint32_t pick_spt(uint64_t lanes, uint32_t spp) {
     return (uint32_t) spt;
 }
 
-template <int SPEC, bool AOS>
+template <int SPEC, int MODE>
 static void launch_forward(mib_scene *s, const LaunchParams &lp) {
     uint64_t lanes = lp.lane_end - lp.lane_begin;
     uint64_t threads = (lanes + lp.spt - 1) / lp.spt;
     uint64_t blocks = (threads + 127) / 128;
     if (blocks == 0) return;
     if (blocks > 0x7fffffffull) throw std::runtime_error("render: too many blocks");
-    k_forward<SPEC, AOS><<<(unsigned) blocks, 128, 0, s->stream>>>(s->ds, lp);
+    k_forward<SPEC, MODE><<<(unsigned) blocks, 128, 0, s->stream>>>(s->ds, lp);
     CK(cudaGetLastError());
 }
 
 static void dispatch_forward(mib_scene *s, const LaunchParams &lp) {
     int spec = s->ds.d.spectrum, integ = s->ds.d.integrator.type;
-    if (integ != MIB_INTEG_VOLPATH && integ != MIB_INTEG_VOLPATHAOS)
-        throw std::runtime_error("forward kernel: integrator type not handled here");
-    bool aos = integ == MIB_INTEG_VOLPATHAOS;
-    switch (spec * 2 + (aos ? 1 : 0)) {
-        case 0: launch_forward<0, false>(s, lp); break;
-        case 1: launch_forward<0, true>(s, lp); break;
-        case 2: launch_forward<1, false>(s, lp); break;
-        case 3: launch_forward<1, true>(s, lp); break;
-        case 4: launch_forward<2, false>(s, lp); break;
-        case 5: launch_forward<2, true>(s, lp); break;
-        default: throw std::runtime_error("unknown spectrum kind");
+    if (spec < 0 || spec > 2) throw std::runtime_error("unknown spectrum kind");
+    switch (integ) {
+        case MIB_INTEG_VOLPATH:
+            if (spec == 0) launch_forward<0, 0>(s, lp); else if (spec == 1) launch_forward<1, 0>(s, lp); else launch_forward<2, 0>(s, lp);
+            break;
+        case MIB_INTEG_VOLPATHAOS:
+            if (spec == 0) launch_forward<0, 1>(s, lp); else if (spec == 1) launch_forward<1, 1>(s, lp); else launch_forward<2, 1>(s, lp);
+            break;
+        case MIB_INTEG_PRBVOLPATH:
+            if (spec == 2) throw std::runtime_error("prbvolpath does not support polarized variants; use prb_volpathaos");
+            if (spec == 0) launch_forward<0, 2>(s, lp); else launch_forward<1, 2>(s, lp);
+            break;
+        case MIB_INTEG_PRBVOLPATHAOS:
+            if (spec != 2) throw std::runtime_error("prb_volpathaos requires a monochromatic polarized variant");
+            launch_forward<2, 3>(s, lp);
+            break;
+        default: throw std::runtime_error("unknown integrator type");
     }
 }
 
