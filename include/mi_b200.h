@@ -41,7 +41,7 @@
 extern "C" {
 #endif
 
-#define MIB_ABI_VERSION 3
+#define MIB_ABI_VERSION 4
 
 #define MIB_MAX_SHAPES   8
 #define MIB_MAX_MEDIA    4
@@ -227,6 +227,8 @@ int  mib_render(mib_scene *scene, uint32_t seed, uint32_t spp, int develop, floa
 int  mib_film_dev(mib_scene *scene, float **raw_dev, size_t *raw_count,
                   float **developed_dev, size_t *developed_count);
 int  mib_film_develop(mib_scene *scene);      /* (re)develop after an external reduce */
+/* Copies the raw (developed = 0) or developed film to the host. */
+int  mib_film_read(mib_scene *scene, int developed, float *host);
 
 /* render_1: sums all samples, returns n_channels doubles normalised by
    W*H*spp (mono: I; mono_polarized: I,Q,U,V). */
@@ -245,6 +247,8 @@ int  mib_grad_dev(mib_scene *scene, int idx, float **dev, size_t *count);
 /* Gradients of scalar medium parameters: out[0..2] = d/d albedo (per channel),
    out[3] = d/d sigma_t (const volume), for medium m. */
 int  mib_grad_get_scalar(mib_scene *scene, int medium, double *out4);
+/* Device pointer of all scalar gradients, [MIB_MAX_MEDIA][4] doubles (for multi-GPU reductions). */
+int  mib_grad_scalar_dev(mib_scene *scene, double **dev, size_t *count);
 int  mib_grad_zero(mib_scene *scene);
 
 int  mib_counters_get(mib_scene *scene, mib_counters *out);

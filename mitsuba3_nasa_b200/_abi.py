@@ -5,7 +5,7 @@ and the ABI version at load time so a drift fails loudly.
 """
 import ctypes as C
 
-MIB_ABI_VERSION = 3
+MIB_ABI_VERSION = 4
 MIB_MAX_SHAPES, MIB_MAX_MEDIA, MIB_MAX_PHASES = 8, 4, 4
 MIB_MAX_BSDFS, MIB_MAX_EMITTERS, MIB_MAX_BUFFERS = 8, 4, 16
 
@@ -97,9 +97,9 @@ EXPORTS = [
     "mib_last_error", "mib_abi_version", "mib_sizeof_scene_desc",
     "mib_scene_create", "mib_scene_destroy", "mib_scene_set_buffer", "mib_scene_get_buffer",
     "mib_scene_buffer_dev", "mib_scene_set_desc", "mib_scene_commit", "mib_scene_get_desc",
-    "mib_scene_set_lane_range", "mib_render", "mib_film_dev", "mib_film_develop",
+    "mib_scene_set_lane_range", "mib_render", "mib_film_dev", "mib_film_develop", "mib_film_read",
     "mib_render_1", "mib_render_1_raw", "mib_render_backward", "mib_render_1_backward",
-    "mib_grad_get", "mib_grad_dev", "mib_grad_get_scalar", "mib_grad_zero",
+    "mib_grad_get", "mib_grad_dev", "mib_grad_get_scalar", "mib_grad_scalar_dev", "mib_grad_zero",
     "mib_counters_get", "mib_scene_stream",
     "mib_debug_sample_lanes", "mib_debug_math",
 ]

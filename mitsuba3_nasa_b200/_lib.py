@@ -43,6 +43,7 @@ class DeviceScene:
         self.l = lib()
         self.scene = scene
         self.h = C.c_void_p()
+        self.device_index = int(device)
         self._ck(self.l.mib_scene_create(C.byref(scene.desc), C.c_int(device), C.byref(self.h)))
         for slot, arr in scene.buffers.items():
             self.set_buffer(slot, arr)
@@ -113,6 +114,12 @@ class DeviceScene:
     def film_develop(self):
         self._ck(self.l.mib_film_develop(self.h))
 
+    def film_read(self, developed=True):
+        H, W = self.size
+        out = np.empty((H, W, self.dev_channels if developed else self.raw_channels), np.float32)
+        self._ck(self.l.mib_film_read(self.h, C.c_int(int(developed)), _fp(out)))
+        return out
+
     def render_1(self, seed, spp, normalize=True):
         out = np.zeros(4, np.float64)
         f = self.l.mib_render_1 if normalize else self.l.mib_render_1_raw
@@ -150,6 +157,11 @@ class DeviceScene:
         out = np.zeros(4, np.float64)
         self._ck(self.l.mib_grad_get_scalar(self.h, C.c_int(medium), _fp(out)))
         return out
+
+    def grad_scalar_dev(self):
+        p, n = C.c_void_p(), C.c_size_t()
+        self._ck(self.l.mib_grad_scalar_dev(self.h, C.byref(p), C.byref(n)))
+        return p.value, n.value
 
     def grad_zero(self):
         self._ck(self.l.mib_grad_zero(self.h))

@@ -433,6 +433,16 @@ int mib_film_develop(mib_scene *s) {
     MIB_CATCH
 }
 
+int mib_film_read(mib_scene *s, int developed, float *host) {
+    MIB_TRY
+    if (!s->committed || !host) throw std::runtime_error("mib_film_read: scene not committed or null output");
+    CK(cudaSetDevice(s->device));
+    CK(cudaMemcpyAsync(host, developed ? s->film_dev : s->film_raw, (developed ? s->film_dev_n : s->film_raw_n) * sizeof(float),
+                       cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    MIB_CATCH
+}
+
 static int render_1_impl(mib_scene *s, uint32_t seed, uint32_t spp, double *out4, bool normalize) {
     MIB_TRY
     if (s->ds.d.spectrum == MIB_SPEC_RGB)

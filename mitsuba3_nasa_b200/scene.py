@@ -214,11 +214,14 @@ class Scene:
             data = pr.get('data')
             grid = pr.get('grid')
             fname = pr.get('filename')
-            if data is None and grid is not None:
-                data = grid
+            file_bbox = None
+            if data is None and grid is not None:                 # a VolumeGrid object (grid.cpp:170-176)
+                data = np.asarray(grid)
+                if hasattr(grid, 'bbox'):
+                    file_bbox = grid.bbox()
             if data is None and fname is not None:
                 from .volumegrid import read_vol
-                data, _bbox = read_vol(fname)
+                data, file_bbox = read_vol(fname)
             if data is None:
                 raise PluginError("gridvolume: one of 'filename', 'grid' or 'data' must be specified")
             data = np.asarray(data, dtype=np.float32)
@@ -228,9 +231,15 @@ class Scene:
                 raise PluginError("gridvolume: data must be [z, y, x, c] with c in {1, 3}")
             ftype = pr.get('filter_type', 'trilinear')
             wmode = pr.get('wrap_mode', 'clamp')
-            pr.get('raw', False); pr.get('accel', True); pr.get('use_grid_bbox', False)
+            pr.get('raw', False); pr.get('accel', True)
+            use_grid_bbox = bool(pr.get('use_grid_bbox', False))
             fixed_max = pr.get('max_value')
             to_world = _to_transform(pr.get('to_world'))
+            if use_grid_bbox:                                     # grid.cpp:288-293, volumegrid.h:26-30
+                if file_bbox is None:
+                    raise PluginError("use_grid_bbox is unsupported with tensor input and requires a volume grid")
+                bmin, bmax = np.asarray(file_bbox[0], np.float64), np.asarray(file_bbox[1], np.float64)
+                to_world = to_world @ ScalarTransform4f.translate(bmin.tolist()) @ ScalarTransform4f.scale((bmax - bmin).tolist())
             pr.finish()
             if ftype not in ('nearest', 'trilinear'):
                 raise PluginError("Invalid filter type \"%s\", must be one of: \"nearest\" or \"trilinear\"!" % ftype)

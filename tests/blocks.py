@@ -1,0 +1,224 @@
+"""Building-block harness shared by tests/test_oracle_vs_ref.py and tests/golden/make_golden.py.
+
+Every block is a function (lib, prefix, n) -> dict of output arrays; `prefix` is "orc_"
+(oracle/liboracle.so, the restatement) or "ref_" (oracle/_ref/libmiref.so, the reference's
+own headers compiled in place).  Inputs are regenerated from fixed seeds, so the golden
+file only has to hold the reference outputs.
+
+TOL: None = bit-exact.  A float = max abs error allowed; those blocks differ only in the
+association order of 3-term dot products (the reference's scalar Array<float,3> sums
+left to right, its JIT arrays and the oracle use fma chains; see oracle/omath.h).
+"""
+import ctypes as C
+
+import numpy as np
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _unit(rng, n):
+    v = rng.normal(size=(n, 3))
+    return (v / np.linalg.norm(v, axis=1, keepdims=True)).astype(np.float32)
+
+
+def _unary(name, lo, hi, seed):
+    def run(lib, prefix, n):
+        x = np.random.default_rng(seed).uniform(lo, hi, n).astype(np.float32)
+        y = np.empty_like(x)
+        getattr(lib, prefix + name)(_p(x), _p(y), C.c_size_t(n))
+        return {"y": y}
+    return run
+
+
+def b_sincos(lib, prefix, n):
+    x = np.random.default_rng(1).uniform(-300, 300, n).astype(np.float32)
+    s, c = np.empty_like(x), np.empty_like(x)
+    getattr(lib, prefix + "sincos")(_p(x), _p(s), _p(c), C.c_size_t(n))
+    return {"s": s, "c": c}
+
+
+def b_tea(lib, prefix, n):
+    rng = np.random.default_rng(2)
+    v0 = rng.integers(0, 2 ** 32, n, dtype=np.uint32)
+    v1 = rng.integers(0, 2 ** 32, n, dtype=np.uint32)
+    v0[:8] = [1, 1, 1, 1, 1, 2, 3, 4]
+    v1[:8] = [1, 2, 3, 4, 5, 1, 1, 1]
+    o0, o1 = np.empty_like(v0), np.empty_like(v1)
+    getattr(lib, prefix + "tea")(_p(v0), _p(v1), _p(o0), _p(o1), C.c_size_t(n))
+    return {"o0": o0, "o1": o1}
+
+
+def b_pcg32(lib, prefix, n):
+    out = {}
+    for k, (st, sq) in enumerate([(0x853c49e6748fea9b, 0xda3e39cb94b95bdb), (0, 1), (12345, 678910)]):
+        f = np.empty(n, np.float32)
+        u = np.empty(n, np.uint32)
+        getattr(lib, prefix + "pcg32_floats")(C.c_uint64(st), C.c_uint64(sq), _p(f), C.c_size_t(n))
+        getattr(lib, prefix + "pcg32_uints")(C.c_uint64(st), C.c_uint64(sq), _p(u), C.c_size_t(n))
+        out["f%d" % k] = f
+        out["u%d" % k] = u
+    return out
+
+
+def b_coordinate_system(lib, prefix, n):
+    v = _unit(np.random.default_rng(3), n)
+    s, t = np.empty_like(v), np.empty_like(v)
+    getattr(lib, prefix + "coordinate_system")(_p(v), _p(s), _p(t), C.c_size_t(n))
+    return {"s": s, "t": t}
+
+
+def b_unit_angle(lib, prefix, n):
+    rng = np.random.default_rng(4)
+    a, b = _unit(rng, n), _unit(rng, n)
+    o = np.empty(n, np.float32)
+    getattr(lib, prefix + "unit_angle")(_p(a), _p(b), _p(o), C.c_size_t(n))
+    return {"o": o}
+
+
+def b_rotator(lib, prefix, n):
+    th = np.random.default_rng(5).uniform(-7, 7, n).astype(np.float32)
+    m = np.empty((n, 16), np.float32)
+    getattr(lib, prefix + "rotator")(_p(th), _p(m), C.c_size_t(n))
+    return {"m": m}
+
+
+def b_rayleigh_scatter(lib, prefix, n):
+    ct = np.random.default_rng(6).uniform(-1, 1, n).astype(np.float32)
+    st = np.sqrt(np.maximum(0, 1 - ct.astype(np.float64) ** 2)).astype(np.float32)
+    out = {}
+    for k, rho in enumerate((0.0, 0.03, 0.2)):
+        m = np.empty((n, 16), np.float32)
+        getattr(lib, prefix + "rayleigh_scatter")(_p(ct), _p(st), C.c_float(rho), _p(m), C.c_size_t(n))
+        out["m%d" % k] = m
+    return out
+
+
+def _ortho(rng, fwd):
+    r = _unit(rng, len(fwd))
+    b = np.cross(fwd, r)
+    return (b / np.linalg.norm(b, axis=1, keepdims=True)).astype(np.float32)
+
+
+def b_rotate_mueller_basis(lib, prefix, n):
+    rng = np.random.default_rng(7)
+    m_in = rng.uniform(-1, 1, (n, 16)).astype(np.float32)
+    fi, fo = _unit(rng, n), _unit(rng, n)
+    v = np.concatenate([fi, _ortho(rng, fi), _ortho(rng, fi), fo, _ortho(rng, fo), _ortho(rng, fo)], axis=1).astype(np.float32)
+    v = np.ascontiguousarray(v)
+    m = np.empty((n, 16), np.float32)
+    getattr(lib, prefix + "rotate_mueller_basis")(_p(m_in), _p(v), _p(m), C.c_size_t(n))
+    return {"m": m}
+
+
+def b_mei_to_world_mueller(lib, prefix, n):
+    rng = np.random.default_rng(8)
+    m_in = rng.uniform(-1, 1, (n, 16)).astype(np.float32)
+    d, i, o = _unit(rng, n), _unit(rng, n), _unit(rng, n)
+    m = np.empty((n, 16), np.float32)
+    getattr(lib, prefix + "mei_to_world_mueller")(_p(m_in), _p(d), _p(i), _p(o), _p(m), C.c_size_t(n))
+    return {"m": m}
+
+
+def _warp(name):
+    def run(lib, prefix, n):
+        s = np.random.default_rng(9).uniform(0, 1, (n, 2)).astype(np.float32)
+        o = np.empty((n, 3), np.float32)
+        getattr(lib, prefix + name)(_p(s), _p(o), C.c_size_t(n))
+        return {"o": o}
+    return run
+
+
+def b_texture3(lib, prefix, n):
+    rng = np.random.default_rng(10)
+    out = {}
+    k = 0
+    for (rx, ry, rz, ch) in ((5, 4, 3, 1), (4, 4, 4, 3)):
+        data = rng.uniform(0, 1, rx * ry * rz * ch).astype(np.float32)
+        p = rng.uniform(-0.6, 1.6, (n, 3)).astype(np.float32)
+        # Only clamp (the gridvolume default) can be pinned this way: the reference's *scalar* instantiation of
+        # Texture::wrap (texture.h:1143-1172) aborts with an out-of-range access in repeat and mirror mode even
+        # for interior points, so those two modes are restated from the source only.
+        for filt in (0, 1):
+            for wrap in (2,):
+                o = np.zeros((n, ch), np.float32)
+                getattr(lib, prefix + "texture3_eval")(_p(data), C.c_int(rx), C.c_int(ry), C.c_int(rz), C.c_int(ch), C.c_int(filt),
+                                                        C.c_int(wrap), _p(p), _p(o), C.c_size_t(n))
+                out["t%d" % k] = o
+                k += 1
+    return out
+
+
+def b_irregular(lib, prefix, n):
+    rng = np.random.default_rng(11)
+    nodes = np.sort(rng.uniform(-1, 1, 64)).astype(np.float32)
+    nodes[0], nodes[-1] = -1.0, 1.0
+    pdf = rng.uniform(0.0, 2.0, 64).astype(np.float32)
+    pdf[10:14] = 0.0
+    x = rng.uniform(-1.1, 1.1, n).astype(np.float32)
+    u = rng.uniform(0, 1, n).astype(np.float32)
+    ev, evn, sm = np.empty(n, np.float32), np.empty(n, np.float32), np.empty(n, np.float32)
+    integral = C.c_float()
+    getattr(lib, prefix + "irregular")(_p(nodes), _p(pdf), C.c_uint32(64), _p(x), _p(ev), _p(evn), _p(u), _p(sm), C.c_size_t(n),
+                                        C.byref(integral))
+    return {"eval": ev, "eval_n": evn, "sample": sm, "integral": np.array([integral.value], np.float32)}
+
+
+def _xform(name):
+    def run(lib, prefix, n):
+        rng = np.random.default_rng(12)
+        m = rng.uniform(-2, 2, 16).astype(np.float32)
+        m[12:] = [0, 0, 0, 1]
+        p = rng.uniform(-5, 5, (n, 3)).astype(np.float32)
+        o = np.empty((n, 3), np.float32)
+        getattr(lib, prefix + name)(_p(m), _p(p), _p(o), C.c_size_t(n))
+        return {"o": o}
+    return run
+
+
+# name -> (function, tolerance)
+BLOCKS = {
+    "exp": (_unary("exp", -90, 90, 21), None),
+    "log": (_unary("log", 1e-30, 1e5, 22), None),
+    "cbrt": (_unary("cbrt", -50, 50, 23), None),
+    "asin": (_unary("asin", -1, 1, 24), None),
+    "sincos": (b_sincos, None),
+    "tea": (b_tea, None),
+    "pcg32": (b_pcg32, None),
+    "coordinate_system": (b_coordinate_system, None),
+    "unit_angle": (b_unit_angle, 4e-7),
+    "rotator": (b_rotator, None),
+    "rayleigh_scatter": (b_rayleigh_scatter, None),
+    "rotate_mueller_basis": (b_rotate_mueller_basis, 5e-6),
+    "mei_to_world_mueller": (b_mei_to_world_mueller, 5e-6),
+    "square_to_uniform_sphere": (_warp("square_to_uniform_sphere"), None),
+    "square_to_cosine_hemisphere": (_warp("square_to_cosine_hemisphere"), 1e-5),   # z = sqrt(1 - squared_norm(p)): fma vs mul+add, amplified by 1/(2z) near the horizon
+    "texture3": (b_texture3, None),
+    "irregular": (b_irregular, None),
+    "transform_point": (_xform("transform_point"), 4e-6),
+    "transform_vector": (_xform("transform_vector"), 4e-6),
+}
+
+
+def compare(name, got, want, tol):
+    """Returns (ok, message)."""
+    for key in want:
+        a, b = np.asarray(got[key]), np.asarray(want[key])
+        if a.shape != b.shape:
+            return False, "%s.%s: shape %s vs %s" % (name, key, a.shape, b.shape)
+        if tol is None:
+            if a.dtype.kind == "f":
+                same = (a.view(np.uint32) == b.view(np.uint32)) | (np.isnan(a) & np.isnan(b)) | ((a == 0) & (b == 0))
+            else:
+                same = a == b
+            if not same.all():
+                idx = np.argwhere(~same)[0]
+                return False, "%s.%s: %d of %d entries differ, first at %s: %r vs %r" % (
+                    name, key, (~same).sum(), same.size, tuple(idx), a[tuple(idx)], b[tuple(idx)])
+        else:
+            err = np.abs(a.astype(np.float64) - b.astype(np.float64))
+            err[np.isnan(a) & np.isnan(b)] = 0
+            if not (err <= tol).all():
+                return False, "%s.%s: max abs err %.3g > %.3g" % (name, key, np.nanmax(err), tol)
+    return True, ""

@@ -1,0 +1,142 @@
+"""Pins the CPU oracle (oracle/liboracle.so) before anything is compared with it:
+
+ 1. against tests/golden/ref_blocks.npz -- outputs of the REFERENCE'S OWN headers for every
+    building block of the path (made by tests/golden/make_golden.py in the build container);
+ 2. against the same reference headers live (oracle/_ref/libmiref.so) when that library is
+    present (it travels to the GPU box as a prebuilt file; it cannot be rebuilt there);
+ 3. against the known-answer values the reference's own test-suite holds for this path
+    (TEA: src/core/tests/test_random.py:8-27; PCG32 default stream:
+    src/samplers/tests/test_independent.py:16-28; trilinear / nearest look-ups:
+    src/volumes/tests/test_grid.py:23-80; Mueller identities: src/render/tests/test_mueller.py:8-20).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+import blocks
+from orc import oracle_lib, ref_lib, fp
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_blocks.npz")
+
+
+@pytest.fixture(scope="module")
+def golden():
+    return np.load(GOLDEN)
+
+
+@pytest.mark.parametrize("name", sorted(blocks.BLOCKS))
+def test_oracle_matches_golden_reference_outputs(name, golden):
+    fn, tol = blocks.BLOCKS[name]
+    n = int(golden["n"][0])
+    got = fn(oracle_lib(), "orc_", n)
+    want = {k.split("/", 1)[1]: golden[k] for k in golden.files if k.startswith(name + "/")}
+    assert want, "golden file has no entry for " + name
+    ok, msg = blocks.compare(name, got, want, tol)
+    assert ok, msg
+
+
+@pytest.mark.parametrize("name", sorted(blocks.BLOCKS))
+def test_oracle_matches_live_reference_headers(name):
+    ref = ref_lib()
+    if ref is None:
+        pytest.skip("oracle/_ref/libmiref.so not built (needs /root/reference)")
+    fn, tol = blocks.BLOCKS[name]
+    n = 20000 if name not in ("texture3", "irregular") else 4000
+    ok, msg = blocks.compare(name, fn(oracle_lib(), "orc_", n), fn(ref, "ref_", n), tol)
+    assert ok, msg
+
+
+# ---------------------------------------------------------------------------
+# Known answers from the reference's own tests
+# ---------------------------------------------------------------------------
+def _tea(v0, v1):
+    a0, a1 = np.array([v0], np.uint32), np.array([v1], np.uint32)
+    o0, o1 = np.empty(1, np.uint32), np.empty(1, np.uint32)
+    oracle_lib().orc_tea(fp(a0), fp(a1), fp(o0), fp(o1), C.c_size_t(1))
+    return int(o0[0]), int(o1[0])
+
+
+@pytest.mark.parametrize("v0,v1,f32,f64", [
+    (1, 1, 0.5424730777740479, 0.5424730799533735), (1, 2, 0.5079904794692993, 0.5079905082233922),
+    (1, 3, 0.4171961545944214, 0.4171962610608142), (1, 4, 0.008385419845581055, 0.008385529523330604),
+    (1, 5, 0.8085528612136841, 0.80855288317879), (2, 1, 0.6939879655838013, 0.6939880404156831),
+    (3, 1, 0.6978365182876587, 0.6978365636630994), (4, 1, 0.4897364377975464, 0.48973647949223253)])
+def test_tea_known_answers(v0, v1, f32, f64):
+    """test_random.py:8-27 through sample_tea_float32/64 (include/mitsuba/core/random.h:135-160)."""
+    o0, o1 = _tea(v0, v1)
+    got32 = np.array([(o1 >> 9) | 0x3f800000], np.uint32).view(np.float32)[0] - np.float32(1)
+    assert float(got32) == f32
+    u64 = (o0 + (o1 << 32)) & 0xffffffffffffffff
+    got64 = np.array([(u64 >> 12) | 0x3ff0000000000000], np.uint64).view(np.float64)[0] - 1.0
+    assert float(got64) == f64
+
+
+def test_pcg32_default_stream_known_answers():
+    """PCG32(initstate=0x853c49e6748fea9b, initseq=0xda3e39cb94b95bdb) is the generator's published
+    demo stream; its first six outputs are the well-known pcg32-global values."""
+    out = np.empty(6, np.uint32)
+    oracle_lib().orc_pcg32_uints(C.c_uint64(0x853c49e6748fea9b), C.c_uint64(0xda3e39cb94b95bdb), fp(out), C.c_size_t(6))
+    # seed(1, state, seq) of drjit/random.h:60-66 == pcg32_srandom_r(state, seq)
+    state, inc = 0, ((0xda3e39cb94b95bdb << 1) | 1) & (2 ** 64 - 1)
+
+    def step():
+        nonlocal state
+        old = state
+        state = (old * 0x5851f42d4c957f2d + inc) & (2 ** 64 - 1)
+        xs = (((old >> 18) ^ old) >> 27) & 0xffffffff
+        rot = old >> 59
+        return ((xs >> rot) | (xs << ((-rot) & 31))) & 0xffffffff
+    step()
+    state = (state + 0x853c49e6748fea9b) & (2 ** 64 - 1)
+    step()
+    assert [int(x) for x in out] == [step() for _ in range(6)]
+
+
+def _tex(data, res, ch, filt, p):
+    data = np.ascontiguousarray(data, np.float32).reshape(-1)
+    p = np.ascontiguousarray(p, np.float32).reshape(-1, 3)
+    out = np.zeros((p.shape[0], ch), np.float32)
+    oracle_lib().orc_texture3_eval(fp(data), C.c_int(res[0]), C.c_int(res[1]), C.c_int(res[2]), C.c_int(ch), C.c_int(filt),
+                                   C.c_int(2), fp(p), fp(out), C.c_size_t(p.shape[0]))
+    return out
+
+
+def test_grid_lookup_known_answers():
+    """src/volumes/tests/test_grid.py:23-80 (grids are [z][y][x][c]; res passed as x,y,z)."""
+    g = np.ones((3, 3, 3), np.float32)
+    g[0, 0, 0] = 0.0
+    g[1, 1, 1] = 0.5
+    assert np.allclose(_tex(g, (3, 3, 3), 1, 0, [[0, 0, 0]]), 0.0)                       # test02 nearest
+    assert np.allclose(_tex(g, (3, 3, 3), 1, 0, [[1 / 6, 1 / 6, 1 / 6]]), 0.0)
+    assert np.allclose(_tex(g, (3, 3, 3), 1, 1, [[0, 0, 0]]), 0.0)                       # test03 trilinear
+    assert np.allclose(_tex(g, (3, 3, 3), 1, 1, [[1 / 3, 1 / 3, 1 / 3]]), (6 * 1 + 0.5 + 0.0) / 8)
+    g = np.ones((3, 8, 5), np.float32)                                                    # test04 boundary
+    g[0, 0, 0] = 0.0
+    g[1, 1, 1] = 0.5
+    g[:, 7, :] = 0.55
+    g[0, :, :] = 0.32
+    assert np.allclose(_tex(g, (5, 8, 3), 1, 1, [[0.2, 1.0, 0.7]]), 0.55)
+    assert np.allclose(_tex(g, (5, 8, 3), 1, 1, [[0.5, 0.5, 0.0]]), 0.32)
+
+
+def test_mueller_known_answers():
+    """test_mueller.py:8-20: depolarizer and rotator acting on Stokes vectors."""
+    th = np.array([45 * np.pi / 180, -45 * np.pi / 180], np.float32)
+    m = np.empty((2, 16), np.float32)
+    oracle_lib().orc_rotator(fp(th), fp(m), C.c_size_t(2))
+    s = np.array([1, 1, 0, 0], np.float32)
+    assert np.allclose(m[0].reshape(4, 4) @ s, [1, 0, -1, 0], atol=1e-5)
+    assert np.allclose(m[1].reshape(4, 4) @ s, [1, 0, +1, 0], atol=1e-5)
+
+
+def test_rayleigh_matrix_normalisation():
+    """rayleigh.cpp:41-128: the (0,0) entry integrates to one over the sphere for any depolarization."""
+    mu = np.linspace(-1, 1, 20001).astype(np.float32)
+    st = np.sqrt(np.maximum(0, 1 - mu.astype(np.float64) ** 2)).astype(np.float32)
+    for rho in (0.0, 0.1):
+        m = np.empty((mu.size, 16), np.float32)
+        oracle_lib().orc_rayleigh_scatter(fp(mu), fp(st), C.c_float(rho), fp(m), C.c_size_t(mu.size))
+        integral = 2 * np.pi * np.trapezoid(m[:, 0].astype(np.float64), mu.astype(np.float64))
+        assert abs(integral - 1) < 2e-3 if rho else abs(integral - 1) < 1e-5
