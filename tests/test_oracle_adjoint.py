@@ -1,0 +1,120 @@
+"""Validates the adjoint ORACLE itself (oracle/oadjoint.h) before the CUDA kernels are compared with it.
+
+The reference has no fixed-seed gradient golden; its own methodology is finite differences
+(src/integrators/tests/test_ad_volpathaos.py:476-529).  Path replay with detached sampling makes the albedo
+gradient the exact derivative of the same-seed primal estimator (albedo only enters through weights) as long
+as Russian roulette is off, so that check is tight; sigma_t changes the sampling densities, so that check is
+statistical.  prb_volpathaos is biased by construction: its restatement is checked literally
+(ratio = albedo) and with the test-only unbiased switch.
+"""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from mitsuba3_nasa_b200 import scene as S, scenes
+from orc import OracleScene
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _homog(variant, integ, albedo, sigma_t, spp, phase=None):
+    d = scenes.c1_homogeneous_cube(res=4, spp=spp, max_depth=12)
+    d['integrator'] = {'type': integ, 'max_depth': 12, 'rr_depth': 1000}
+    d['medium1']['sigma_t'] = sigma_t
+    d['medium1']['albedo'] = albedo
+    if phase:
+        d['medium1']['phase'] = phase
+    d['sensor']['film']['pixel_format'] = 'luminance'
+    if integ == 'prb_volpathaos':
+        d['emitter'] = {'type': 'directional', 'direction': [0.3, -0.2, -1.0], 'irradiance': 1.0}
+    return S.load_dict(d, variant)
+
+
+def _fd(variant, integ, key, x0, h, spp, phase, seed):
+    vals = []
+    for sgn in (+1, -1):
+        kw = dict(albedo=0.8, sigma_t=0.6)
+        kw[key] = x0 + sgn * h
+        vals.append(OracleScene(_homog(variant, integ, spp=spp, phase=phase, **kw)).render_1(seed, spp, nthreads=8)[0])
+    return (vals[0] - vals[1]) / (2 * h)
+
+
+def test_prbvolpath_albedo_gradient_is_the_same_seed_derivative():
+    spp = 2048
+    o = OracleScene(_homog('llvm_ad_mono', 'prbvolpath', 0.8, 0.6, spp))
+    o.render_1_backward(7, spp, [1.0, 0, 0, 0], nthreads=8)
+    g = o.grad_get_scalar(0)
+    fd = _fd('llvm_ad_mono', 'prbvolpath', 'albedo', 0.8, 1e-2, spp, None, 7)
+    assert abs(g[0] / fd - 1) < 2e-4, (g[0], fd)
+
+
+def test_prbvolpath_sigma_t_gradient_statistical():
+    spp = 1 << 15
+    o = OracleScene(_homog('llvm_ad_mono', 'prbvolpath', 0.8, 0.6, spp))
+    o.render_1_backward(7, spp, [1.0, 0, 0, 0], nthreads=8)
+    g = o.grad_get_scalar(0)
+    fd = _fd('llvm_ad_mono', 'prbvolpath', 'sigma_t', 0.6, 3e-2, spp, None, 11)
+    assert abs(g[3] / fd - 1) < 0.05, (g[3], fd)      # the reference's own tolerance (test_ad_volpathaos.py:599-618)
+
+
+def test_prb_volpathaos_literal_bias_is_the_albedo():
+    """I = replace_grad(1, weight) without the division: each real scatter contributes albedo x the true term, and
+    d/d albedo sums one term per scatter, so the literal gradient is exactly albedo x the FD derivative."""
+    spp = 2048
+    ph = {'type': 'rayleigh'}
+    o = OracleScene(_homog('llvm_ad_mono_polarized', 'prb_volpathaos', 0.8, 0.6, spp, ph))
+    o.render_1_backward(7, spp, [1.0, 0, 0, 0], nthreads=8)
+    g = o.grad_get_scalar(0)
+    fd = _fd('llvm_ad_mono_polarized', 'prb_volpathaos', 'albedo', 0.8, 1e-2, spp, ph, 7)
+    assert abs(g[0] / fd - 0.8) < 1e-3, (g[0], fd)
+
+
+def test_prb_volpathaos_machinery_with_division_matches_fd():
+    code = r'''
+import sys
+sys.path.insert(0, %r); sys.path.insert(0, %r)
+import test_oracle_adjoint as t
+from orc import OracleScene
+spp = 2048
+ph = {'type': 'rayleigh'}
+o = OracleScene(t._homog('llvm_ad_mono_polarized', 'prb_volpathaos', 0.8, 0.6, spp, ph))
+o.render_1_backward(7, spp, [1.0, 0, 0, 0], nthreads=8)
+g = o.grad_get_scalar(0)
+fd = t._fd('llvm_ad_mono_polarized', 'prb_volpathaos', 'albedo', 0.8, 1e-2, spp, ph, 7)
+print("RATIO", g[0] / fd)
+''' % (ROOT, os.path.join(ROOT, "tests"))
+    env = dict(os.environ, ORC_PRB_AOS_UNBIASED="1")
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    ratio = float(out.stdout.split("RATIO")[1])
+    assert abs(ratio - 1) < 2e-4, ratio
+
+
+def test_grid_gradient_directional_derivative():
+    rng = np.random.default_rng(3)
+    n = 5
+    grid = rng.uniform(0.2, 0.8, size=(n, n, n, 1)).astype(np.float32)
+    grid[0, 0, 0, 0] = 1.0                                   # pins the global majorant
+    v = rng.uniform(0.0, 1.0, size=grid.shape).astype(np.float32)
+    v[0, 0, 0, 0] = 0
+
+    def mk(g, spp):
+        d = scenes.c3_cloud(res=4, spp=spp, max_depth=12, integrator='prbvolpath', grid=g, optical_depth=4.0, albedo=0.9,
+                            phase={'type': 'hg', 'g': 0.3})
+        d['integrator']['rr_depth'] = 1000
+        d['object']['interior']['scale'] = 2.0
+        d['sensor']['film']['pixel_format'] = 'luminance'
+        return S.load_dict(d, 'llvm_ad_mono')
+    spp = 1 << 15
+    f = mk(grid, spp)
+    o = OracleScene(f)
+    slot = f.desc.media[0].sigma_t.buffer
+    o.render_1_backward(5, spp, [1, 0, 0, 0], nthreads=8)
+    g = o.grad_get(slot, grid.size)
+    h = 0.05
+    vals = [OracleScene(mk(grid + s * h * v, spp)).render_1(9, spp, nthreads=8)[0] for s in (1, -1)]
+    fd = (vals[0] - vals[1]) / (2 * h)
+    assert abs(float(g @ v.reshape(-1)) / fd - 1) < 0.06
