@@ -132,37 +132,65 @@ MIB_D void sample_emitter(const DScene &sc, Pcg32 &rng, Counters &cnt, V3 ref_p,
 }
 
 // ---------------------------------------------------------------------------
-// One complete camera path.  R receives the radiance (Stokes 4-vector in polarized mode).
+// One camera path as explicit state + one-iteration step, so that the kernel can run a
+// flat loop and start the thread's next lane the moment a path ends (no lane of a warp
+// waits for the longest path of the warp).  R receives the radiance (Stokes 4-vector in
+// polarized mode).
 // ---------------------------------------------------------------------------
+template <int SPEC> struct PathState {
+    float T[ST<SPEC>::NT];
+    float R[ST<SPEC>::NR];
+    Ray ray;
+    SurfIt si;
+    float eta, last_pdf;
+    int medium;
+    uint32_t depth, channel;
+    bool active, specular_chain, needs_intersection;
+};
+
+template <int SPEC>
+MIB_D void path_init(const DScene &sc, Pcg32 &rng, const Ray &ray, PathState<SPEC> &st) {
+    constexpr int NR = ST<SPEC>::NR;
+    T_init<SPEC>(st.T);
+#pragma unroll
+    for (int i = 0; i < NR; ++i) st.R[i] = 0.f;
+    st.ray = ray;
+    st.eta = 1.f;
+    st.medium = sc.d.sensor.medium;
+    st.active = true;
+    st.specular_chain = !sc.d.integrator.hide_emitters;
+    st.needs_intersection = true;
+    st.depth = 0; st.channel = 0;
+    if (SPEC == MIB_SPEC_RGB) st.channel = (uint32_t) fminf(rng.next() * 3.f, 2.f);
+    st.si.t = inf_f(); st.si.shape = -1; st.si.wi = v3(0.f);
+    st.last_pdf = 1.f;
+}
+
+// One iteration of the reference's while loop (volpath.cpp:121-328 / volpathaos.cpp:85-294).
 template <int SPEC, bool AOS>
-MIB_D void trace_path(const DScene &sc, Pcg32 &rng, Counters &cnt, Ray ray, float *R) {
+MIB_D void path_step(const DScene &sc, Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
     constexpr int NC = ST<SPEC>::NC, NT = ST<SPEC>::NT, NR = ST<SPEC>::NR;
     constexpr bool POL = ST<SPEC>::POL;
     const mib_integrator &I = sc.d.integrator;
-    float T[NT];
-    T_init<SPEC>(T);
-#pragma unroll
-    for (int i = 0; i < NR; ++i) R[i] = 0.f;
-    float eta = 1.f;
-    int medium = sc.d.sensor.medium;
-    bool active = true, specular_chain = !I.hide_emitters, needs_intersection = true;
-    uint32_t depth = 0, channel = 0;
+    float *T = st.T, *R = st.R;
+    Ray &ray = st.ray;
+    SurfIt &si = st.si;
+    float &eta = st.eta, &last_pdf = st.last_pdf;
+    int &medium = st.medium;
+    uint32_t &depth = st.depth;
+    const uint32_t channel = st.channel;
+    bool &active = st.active, &specular_chain = st.specular_chain, &needs_intersection = st.needs_intersection;
     const uint32_t maxd = (uint32_t) I.max_depth, rrd = (uint32_t) I.rr_depth;
-    if (SPEC == MIB_SPEC_RGB) channel = (uint32_t) fminf(rng.next() * 3.f, 2.f);
-    SurfIt si;
-    si.t = inf_f(); si.shape = -1; si.wi = v3(0.f);
-    MedIt<NC> mei;
-    float last_pdf = 1.f;
     const bool ltr = I.rng_arg_order == MIB_RNG_ARGS_LEFT_TO_RIGHT;
-
-    while (active) {
+    MedIt<NC> mei;
+    {
         active = active && T_any_nonzero<SPEC>(T);
         float q = fminf(T_max<SPEC>(T) * sqr_(eta), .95f);
         bool perform_rr = depth > rrd;
         if (active) { float u = rng.next(); active = (u < q) || !perform_rr; }
         if (perform_rr) T_mul_f<SPEC>(T, rcp_(q));
         active = active && depth < maxd;
-        if (!active) break;
+        if (!active) return;
 
         bool active_medium = medium >= 0, active_surface = !active_medium;
         bool act_null = false, act_scatter = false, escaped = false, is_spectral = false, not_spectral = false;
@@ -339,6 +367,15 @@ MIB_D void trace_path(const DScene &sc, Pcg32 &rng, Counters &cnt, Ray ray, floa
         }
         active = active && (active_surface || active_medium);
     }
+}
+
+template <int SPEC, bool AOS>
+MIB_D void trace_path(const DScene &sc, Pcg32 &rng, Counters &cnt, Ray ray, float *R) {
+    PathState<SPEC> st;
+    path_init<SPEC>(sc, rng, ray, st);
+    while (st.active) path_step<SPEC, AOS>(sc, rng, cnt, st);
+#pragma unroll
+    for (int i = 0; i < ST<SPEC>::NR; ++i) R[i] = st.R[i];
 }
 
 } // namespace mib

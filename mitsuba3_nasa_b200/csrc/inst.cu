@@ -1,0 +1,15 @@
+// inst.cu -- one explicit instantiation of a walk kernel per object file.
+// Compiled as:  nvcc -DINST_FWD -DINST_SPEC=s -DINST_MODE=m   or   nvcc -DINST_ADJ -DINST_SPEC=s   (see Makefile).
+#include "kernels.cuh"
+
+namespace mib {
+#if defined(INST_FWD)
+template <> void launch_k_forward<INST_SPEC, INST_MODE>(const DScene &sc, const LaunchParams &lp, unsigned blocks, cudaStream_t st) {
+    k_forward<INST_SPEC, INST_MODE><<<blocks, 128, 0, st>>>(sc, lp);
+}
+#elif defined(INST_ADJ)
+template <> void launch_k_adjoint<INST_SPEC>(const DScene &sc, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, cudaStream_t st) {
+    k_adjoint<INST_SPEC><<<blocks, 128, 0, st>>>(sc, lp, ap);
+}
+#endif
+}

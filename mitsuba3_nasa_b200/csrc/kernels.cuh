@@ -23,6 +23,9 @@ struct LaunchParams {
     unsigned long long *counters; // [6]: lookups, real, null, nee_steps, surface, samples
 };
 
+// launchers defined in inst.cu (one per object file)
+template <int SPEC, int MODE> void launch_k_forward(const DScene &sc, const LaunchParams &lp, unsigned blocks, cudaStream_t st);
+
 template <int SPEC> struct RawChannels { static constexpr int C = SPEC == MIB_SPEC_MONO ? 2 : 4; };
 
 // integrator.cpp:1245-1267 applied to a Stokes vector (first column of spec2sensor * spec)
@@ -57,41 +60,20 @@ __global__ void __launch_bounds__(128) k_forward(const __grid_constant__ DScene 
     const float scale_x = 1.f / (float) sn.crop_width, scale_y = 1.f / (float) sn.crop_height;
     const float offset_x = -(float) sn.crop_offset_x * scale_x, offset_y = -(float) sn.crop_offset_y * scale_y;
 
-    for (uint64_t lane = l0; lane < l1; ++lane) {
-        Pcg32 rng;
-        rng.seed_lane(lp.seed_value, (uint32_t) lane);
-        // integrator.cpp:323-340: lane -> pixel
-        uint32_t idx = (uint32_t) (lane / lp.spp);
-        uint32_t py = idx / (uint32_t) sn.crop_width, px = idx - (uint32_t) sn.crop_width * py;
-        float posx = (float) ((int) px + sn.crop_offset_x), posy = (float) ((int) py + sn.crop_offset_y);
-        // render_sample (integrator.cpp:1139-1170)
-        float jx = rng.next(), jy = rng.next();
-        float sx = posx + jx, sy = posy + jy;
-        float ax = fma_(sx, scale_x, offset_x), ay = fma_(sy, scale_y, offset_y);
-        float apx = .5f, apy = .5f;
-        if (sn.needs_aperture_sample) { apx = rng.next(); apy = rng.next(); }
-        Ray ray = sensor_ray(sc, ax, ay, apx, apy);
-        float R[NR];
-        if constexpr (MODE <= 1) trace_path<SPEC, MODE == 1>(sc, rng, cnt, ray, R);
-        else {
-            Sink sink;
-            sink.init();
-            prb_walk<SPEC, MODE == 3>(sc, rng, cnt, ray, false, nullptr, nullptr, sink, R);
-        }
+    // Film / render_1 accumulation of one finished sample (imageblock.cpp:206-232 box put).
+    auto finish = [&](uint64_t lane, const Ray &ray0, float sx, float sy, float *R) {
         n_samples++;
         float aov[C];
         if constexpr (SPEC == MIB_SPEC_RGB) { aov[0] = R[0]; aov[1] = R[1]; aov[2] = R[2]; aov[3] = 1.f; }
         else if constexpr (SPEC == MIB_SPEC_MONO) { aov[0] = R[0]; aov[1] = 1.f; }
-        else { to_sensor_stokes(ray, R); aov[0] = R[0]; aov[1] = R[1]; aov[2] = R[2]; aov[3] = R[3]; }
-
+        else { to_sensor_stokes(ray0, R); aov[0] = R[0]; aov[1] = R[1]; aov[2] = R[2]; aov[3] = R[3]; }
         if (lp.mode == 2) {
 #pragma unroll
             for (int c = 0; c < C; ++c) lp.per_sample[(lane - lp.lane_begin) * C + c] = aov[c];
-            continue;
+            return;
         }
-        // box-filter put (imageblock.cpp:206-232)
         int ix = (int) floorf(sx) - sn.crop_offset_x, iy = (int) floorf(sy) - sn.crop_offset_y;
-        if ((uint32_t) ix >= (uint32_t) sn.crop_width || (uint32_t) iy >= (uint32_t) sn.crop_height) continue;
+        if ((uint32_t) ix >= (uint32_t) sn.crop_width || (uint32_t) iy >= (uint32_t) sn.crop_height) return;
         if (lp.mode == 1) {
 #pragma unroll
             for (int c = 0; c < C; ++c) dacc[c] += (double) aov[c];
@@ -108,6 +90,50 @@ __global__ void __launch_bounds__(128) k_forward(const __grid_constant__ DScene 
             }
 #pragma unroll
             for (int c = 0; c < C; ++c) acc[c] += aov[c];
+        }
+    };
+    // integrator.cpp:323-340 (lane -> pixel) + render_sample :1139-1170 (film position, sensor ray)
+    auto start = [&](uint64_t lane, Pcg32 &rng, float &sx, float &sy) -> Ray {
+        rng.seed_lane(lp.seed_value, (uint32_t) lane);
+        uint32_t idx = (uint32_t) (lane / lp.spp);
+        uint32_t py = idx / (uint32_t) sn.crop_width, px = idx - (uint32_t) sn.crop_width * py;
+        float posx = (float) ((int) px + sn.crop_offset_x), posy = (float) ((int) py + sn.crop_offset_y);
+        float jx = rng.next(), jy = rng.next();
+        sx = posx + jx; sy = posy + jy;
+        float ax = fma_(sx, scale_x, offset_x), ay = fma_(sy, scale_y, offset_y);
+        float apx = .5f, apy = .5f;
+        if (sn.needs_aperture_sample) { apx = rng.next(); apy = rng.next(); }
+        return sensor_ray(sc, ax, ay, apx, apy);
+    };
+
+    if constexpr (MODE <= 1) {
+        // Flat loop with lane regeneration: a thread starts its next lane as soon as its current
+        // path ends instead of idling until the longest path of the warp is finished.
+        PathState<SPEC> st;
+        st.active = false;
+        Pcg32 rng;
+        Ray ray0;
+        float sx = 0.f, sy = 0.f;
+        uint64_t lane = l0, cur = l0;
+        while (true) {
+            if (!st.active) {
+                if (lane >= l1) break;
+                cur = lane++;
+                ray0 = start(cur, rng, sx, sy);
+                path_init<SPEC>(sc, rng, ray0, st);
+            }
+            path_step<SPEC, MODE == 1>(sc, rng, cnt, st);
+            if (!st.active) finish(cur, ray0, sx, sy, st.R);
+        }
+    } else {
+        for (uint64_t lane = l0; lane < l1; ++lane) {
+            Pcg32 rng;
+            float sx, sy, R[NR];
+            Ray ray = start(lane, rng, sx, sy);
+            Sink sink;
+            sink.init();
+            prb_walk<SPEC, MODE == 3>(sc, rng, cnt, ray, false, nullptr, nullptr, sink, R);
+            finish(lane, ray, sx, sy, R);
         }
     }
     if (lp.mode == 0 && cur_pixel >= 0) {
@@ -195,6 +221,8 @@ __global__ void __launch_bounds__(128) k_adjoint(const __grid_constant__ DScene 
     }
 }
 
+template <int SPEC> void launch_k_adjoint(const DScene &sc, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, cudaStream_t st);
+
 // HDRFilm::develop (hdrfilm.cpp:304-418): value / (weight == 0 ? 1 : weight)
 template <int SPEC>
 __global__ void k_develop(const float *raw, float *out, size_t npix, uint32_t spp) {
@@ -213,7 +241,7 @@ __global__ void k_develop(const float *raw, float *out, size_t npix, uint32_t sp
 }
 
 // grid maximum (gridvolume m_max, grid.cpp:306-319): grid-stride max + one atomic per block
-__global__ void k_max(const float *data, size_t n, unsigned int *out_bits) {
+static __global__ void k_max(const float *data, size_t n, unsigned int *out_bits) {
     float m = -inf_f();
     for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x)
         m = fmaxf(m, data[i]);

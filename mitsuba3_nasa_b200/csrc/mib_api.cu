@@ -196,6 +196,13 @@ static uint32_t pick_spt(uint64_t lanes, uint32_t spp) {
     return (uint32_t) spt;
 }
 
+// The walk kernels are instantiated one per translation unit (inst.cu compiled with -DINST_*), so that the
+// library builds in parallel; this file only sees their launchers.
+namespace mib {
+template <int SPEC, int MODE> void launch_k_forward(const DScene &sc, const LaunchParams &lp, unsigned blocks, cudaStream_t st);
+template <int SPEC> void launch_k_adjoint(const DScene &sc, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, cudaStream_t st);
+}
+
 template <int SPEC, int MODE>
 static void launch_forward(mib_scene *s, const LaunchParams &lp) {
     uint64_t lanes = lp.lane_end - lp.lane_begin;
@@ -203,7 +210,7 @@ static void launch_forward(mib_scene *s, const LaunchParams &lp) {
     uint64_t blocks = (threads + 127) / 128;
     if (blocks == 0) return;
     if (blocks > 0x7fffffffull) throw std::runtime_error("render: too many blocks");
-    k_forward<SPEC, MODE><<<(unsigned) blocks, 128, 0, s->stream>>>(s->ds, lp);
+    launch_k_forward<SPEC, MODE>(s->ds, lp, (unsigned) blocks, s->stream);
     CK(cudaGetLastError());
 }
 
