@@ -11,7 +11,8 @@ import numpy as np
 from . import _abi as A
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmi_b200.so")
+# MIB_B200_LIB: alternative build of the same library (kernel A/B experiments)
+LIB_PATH = os.environ.get("MIB_B200_LIB") or os.path.join(_HERE, "libmi_b200.so")
 _lib = None
 
 

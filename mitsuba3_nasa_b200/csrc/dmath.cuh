@@ -13,6 +13,22 @@
 namespace mib {
 
 #define MIB_D __device__ __forceinline__
+// Heavy helpers (intersection, medium sampling, plugin dispatch, transcendental polynomials).  Inlined by default:
+// the walk kernels are 190-700 KB of SASS that way and instruction fetch is the top stall reason (ncu:
+// no_instruction), but real calls (-DMIB_HEAVY_NOINLINE: 3x less code, 96-128 registers) pass MedIt / SurfIt / 4x4
+// matrices through the local-memory stack and measured slower on the ALU-bound configs (C2 246 vs 400 Msamples/s,
+// C1 862 vs 1272) and only 6 % faster on the grid config (profiles/r01_ab_variants.md).
+#ifndef MIB_HEAVY_NOINLINE
+#define MIB_DH static __device__ __forceinline__
+#else
+#define MIB_DH static __device__ __noinline__
+#endif
+// transcendental polynomials + Stokes rotations (leaf functions, scalar arguments)
+#if !defined(MIB_HEAVY_NOINLINE) || defined(MIB_MATH_INLINE)
+#define MIB_DM static __device__ __forceinline__
+#else
+#define MIB_DM static __device__ __noinline__
+#endif
 
 constexpr float kPi        = 3.14159265358979323846f;
 constexpr float kInvPi     = 0.31830988618379067154f;
@@ -37,7 +53,7 @@ MIB_D float mulsign_ad(float v1, float v2) { return v2 >= 0.f ? v1 : -v1; }     
 MIB_D float mulsign_bits(float v1, float v2) { return __int_as_float(__float_as_int(v1) ^ (__float_as_int(v2) & 0x80000000)); }
 
 // ext/drjit/include/drjit/math.h:74-180
-MIB_D void sincos_(float x, float &s_out, float &c_out) {
+MIB_DM void sincos_(float x, float &s_out, float &c_out) {
     float xa = fabsf(x);
     int j = (int) (xa * 1.2732395447351626862f);
     j = (j + 1) & ~1;
@@ -70,7 +86,7 @@ MIB_D void frexp_(float x, float &mant, float &expo) {                          
 }
 
 // math.h:685-747.  estrin with 6 coefficients: level 1 pairs, level 2 on y^2, level 3 on y^4
-MIB_D float exp_(float x) {
+MIB_DM float exp_(float x) {
     float n = floorf(fma_(1.44269504088896340736f, x, 0.5f));
     float y = fma_(n, -0.693359375f, x);
     y = fma_(n, 2.12194440e-4f, y);
@@ -87,7 +103,7 @@ MIB_D float exp_(float x) {
 }
 
 // math.h:824-897.  estrin with 9 coefficients
-MIB_D float log_(float x) {
+MIB_DM float log_(float x) {
     float xm, e;
     frexp_(x, xm, e);
     bool ge = xm >= 0.70710678118654752440f;
@@ -114,7 +130,7 @@ MIB_D float log_(float x) {
 }
 
 // math.h:1411-1468 (one Newton step in single precision).  estrin with 5 coefficients
-MIB_D float cbrt_(float x) {
+MIB_DM float cbrt_(float x) {
     const float cbrt2 = 1.25992104989487316477f, cbrt4 = 1.58740105196819947475f, third = (float) (1.0 / 3.0);
     float xa = fabsf(x), xm, xe;
     frexp_(xa, xm, xe);
@@ -136,7 +152,7 @@ MIB_D float cbrt_(float x) {
 }
 
 // math.h:366-456.  estrin with 5 coefficients
-MIB_D float asin_(float x) {
+MIB_DM float asin_(float x) {
     float xa = fabsf(x), x2 = x * x;
     bool big = xa > 0.5f;
     float x1 = 0.5f * (1.f - xa);

@@ -49,7 +49,7 @@ MIB_D void rayleigh_matrix(float cos_theta, float sin_theta, float rho, float *M
 
 // eval_pdf: W = phase value (Mueller in local Stokes frames, or one float replicated), returns pdf
 template <int SPEC>
-MIB_D float phase_eval(const DScene &sc, int idx, V3 wo, float *W) {
+MIB_DH float phase_eval(const DScene &sc, int idx, V3 wo, float *W) {
     constexpr bool POL = ST<SPEC>::POL;
     constexpr int NC = ST<SPEC>::NC;
     const mib_phase &p = sc.d.phases[idx];
@@ -98,7 +98,7 @@ MIB_D float phase_eval(const DScene &sc, int idx, V3 wo, float *W) {
 
 // sample: returns pdf, writes local wo and the weight W
 template <int SPEC>
-MIB_D float phase_sample(const DScene &sc, int idx, float s2x, float s2y, V3 &wo, float *W) {
+MIB_DH float phase_sample(const DScene &sc, int idx, float s2x, float s2y, V3 &wo, float *W) {
     constexpr bool POL = ST<SPEC>::POL;
     constexpr int NC = ST<SPEC>::NC;
     const mib_phase &p = sc.d.phases[idx];
@@ -169,7 +169,7 @@ MIB_D float phase_sample(const DScene &sc, int idx, float s2x, float s2y, V3 &wo
 template <int NC> struct DirSample { V3 p, d; float dist, pdf; bool delta; int emitter; };
 
 template <int NC>
-MIB_D void sample_emitter_direction(const DScene &sc, V3 ref_p, float sx, float sy, DirSample<NC> &ds, float *spec) {
+MIB_DH void sample_emitter_direction(const DScene &sc, V3 ref_p, float sx, float sy, DirSample<NC> &ds, float *spec) {
     int n = sc.d.n_emitters;
 #pragma unroll
     for (int c = 0; c < NC; ++c) spec[c] = 0.f;
@@ -220,7 +220,7 @@ MIB_D int si_emitter(const DScene &sc, const SurfIt &si) {
 constexpr uint32_t kBsdfNull = 0x1, kBsdfDiffuseRefl = 0x2, kBsdfSmooth = 0x2 | 0x4 | 0x8 | 0x10, kBsdfDelta = 0x1 | 0x20 | 0x40;
 
 // ---- sensors ----
-MIB_D Ray sensor_ray(const DScene &sc, float px, float py, float ax, float ay) {
+MIB_DH Ray sensor_ray(const DScene &sc, float px, float py, float ax, float ay) {
     const mib_sensor &s = sc.d.sensor;
     Ray ray;
     if (s.type == MIB_SENSOR_PERSPECTIVE) {                                  // perspective.cpp:201-235

@@ -103,7 +103,7 @@ MIB_D float intersect_shape(const DScene &sc, int idx, const Ray &ray, int &face
 }
 
 // Scene::ray_intersect + finalize_surface_interaction (interaction.h:245-255, :464-484)
-MIB_D void ray_intersect(const DScene &sc, const Ray &ray, SurfIt &si) {
+MIB_DH void ray_intersect(const DScene &sc, const Ray &ray, SurfIt &si) {
     float best = inf_f();
     int bs = -1, bf = 0;
     for (int i = 0; i < sc.d.n_shapes; ++i) {
@@ -161,7 +161,7 @@ MIB_D int wrap_coord(int pos, int shape, int mode) {
 struct GridTaps { uint32_t idx[8]; float w[8]; };   // used by the adjoint to scatter through the same taps
 
 template <int NC>
-MIB_D void eval_grid(const DScene &sc, const mib_volume &v, V3 p, float *out, GridTaps *taps) {
+MIB_DH void eval_grid(const DScene &sc, const mib_volume &v, V3 p, float *out, GridTaps *taps) {
     V3 pl = xform_point(v.to_local, p);
     const float *__restrict__ data = sc.buffers[v.buffer];
     const int ch = v.channels, rx = v.res[0], ry = v.res[1], rz = v.res[2];
@@ -252,7 +252,7 @@ template <int NC> MIB_D bool valid(const MedIt<NC> &m) { return m.t != inf_f(); 
 template <int NC> MIB_D float ch(const float *s, uint32_t c) { return NC == 3 ? s[c] : s[0]; }
 
 template <int NC>
-MIB_D void sample_interaction(const DScene &sc, int mi, const Ray &ray, float sample, uint32_t channel,
+MIB_DH void sample_interaction(const DScene &sc, int mi, const Ray &ray, float sample, uint32_t channel,
                               MedIt<NC> &mei, Counters &cnt, GridTaps *taps = nullptr) {
     const mib_medium &m = sc.d.media[mi];
     mei.sh = make_frame(ray.d);
@@ -310,7 +310,7 @@ MIB_D void sample_interaction(const DScene &sc, int mi, const Ray &ray, float sa
 // Irregular 1D distribution (distr_1d.h:707-729, :781-814; drjit/util.h:172-220)
 // Tables are a few KiB and stay in L1/L2; binary search = log2(N) dependent loads.
 // ------------------------------------------------------------------
-MIB_D float tab_eval(const DTable &t, float x) {
+MIB_DH float tab_eval(const DTable &t, float x) {
     bool active = x >= t.range_x && x <= t.range_y;
     uint32_t start = 0, end = t.n;
     uint32_t iters = (start < end) ? (31 - __clz(end - start)) + 1 : 0;
@@ -324,7 +324,7 @@ MIB_D float tab_eval(const DTable &t, float x) {
     x = __fdiv_rn(x - x0, x1 - x0);
     return active ? fma_(x, y1 - y0, y0) : 0.f;
 }
-MIB_D float tab_sample(const DTable &t, float sample) {
+MIB_DH float tab_sample(const DTable &t, float sample) {
     sample *= t.integral;
     uint32_t start = t.valid_x, end = t.valid_y;
     uint32_t iters = (start < end) ? (31 - __clz(end - start)) + 1 : 0;

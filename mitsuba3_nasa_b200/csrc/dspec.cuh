@@ -68,14 +68,14 @@ MIB_D void m4_identity(float *M, float s) {
 }
 
 // mueller.h:375-386: angle of rotate_stokes_basis -> (cos 2theta, sin 2theta)
-MIB_D void stokes_rotation(V3 forward, V3 basis_current, V3 basis_target, float &c, float &s) {
+MIB_DM void stokes_rotation(V3 forward, V3 basis_current, V3 basis_target, float &c, float &s) {
     float theta = unit_angle(normalize(basis_current), normalize(basis_target));
     if (dot(forward, cross(basis_current, basis_target)) < 0.f) theta *= -1.f;
     sincos_(2.f * theta, s, c);
 }
 
 // to_world_mueller (interaction.h:374-395, :574-595): the two rotations for local directions in/out
-MIB_D void world_rotations(const Frame3 &fr, V3 in_l, V3 out_l, float &ci, float &si, float &co, float &so) {
+MIB_DM void world_rotations(const Frame3 &fr, V3 in_l, V3 out_l, float &ci, float &si, float &co, float &so) {
     V3 in_w = to_world(fr, in_l), out_w = to_world(fr, out_l);
     V3 in_cur = to_world(fr, stokes_basis(in_l)), in_tgt = stokes_basis(in_w);
     V3 out_cur = to_world(fr, stokes_basis(out_l)), out_tgt = stokes_basis(out_w);
