@@ -24,6 +24,9 @@ struct DScene {
     float cube_normals[MIB_MAX_SHAPES][6][3];     // world-space outward face normals (-x,+x,-y,+y,-z,+z)
     double *grad_scalar;                          // [MIB_MAX_MEDIA*4] constant-volume gradients (adjoint)
     int prb_null, prb_homog;                      // prepare_scene flags (prbvolpath.py:76-89)
+    float rf_coeff[10];                           // gaussian reconstruction filter polynomial (gaussian.cpp:50-98)
+    float rf_inv_radius;                          // tent filter
+    const float *weight_film;                     // [H*W] filter-weight film for the adjoint of non-box filters
 };
 
 struct Ray { V3 o, d; float maxt; };

@@ -53,6 +53,61 @@ MIB_D void to_sensor_stokes(const Ray &ray, float *S) {
     S[2] = fma_(c, s2, (-s) * s1);
 }
 
+// Reconstruction filters (src/rfilters/gaussian.cpp:86-98 non-CUDA branch: estrin in x^2; tent.cpp:41-43)
+MIB_D float rfilter_eval(const DScene &sc, float x) {
+    if (sc.d.sensor.rfilter == MIB_RFILTER_GAUSSIAN) {
+        // drjit estrin_impl (math.h:26-41) for 10 coefficients
+        const float *c = sc.rf_coeff;
+        float x1 = sqr_(x), x2 = sqr_(x1), x4 = sqr_(x2), x8 = sqr_(x4);
+        float a0 = fma_(x1, c[1], c[0]), a1 = fma_(x1, c[3], c[2]), a2 = fma_(x1, c[5], c[4]), a3 = fma_(x1, c[7], c[6]),
+              a4 = fma_(x1, c[9], c[8]);
+        float b0 = fma_(x2, a1, a0), b1 = fma_(x2, a3, a2), b2 = a4;
+        float d0 = fma_(x4, b1, b0), d1 = b2;
+        return fmaxf(fma_(x8, d1, d0), 0.f);
+    }
+    return fmaxf(0.f, 1.f - fabsf(x * sc.rf_inv_radius));
+}
+
+// ImageBlock::put for a reconstruction filter (imageblock.cpp:261-530, JIT recorded-loop forms, border 0): fn(pixel, weight)
+// for every pixel of the footprint.  Coalesced form when spp >= 4 (integrator.cpp:320), general form otherwise.
+template <typename Fn>
+MIB_D void filter_footprint(const DScene &sc, uint32_t spp, float pos_x, float pos_y, Fn &&fn) {
+    const mib_sensor &s = sc.d.sensor;
+    const float radius = s.rfilter_radius;
+    const uint32_t size_x = (uint32_t) s.crop_width, size_y = (uint32_t) s.crop_height;
+    if (spp >= 4) {
+        uint32_t n = (uint32_t) (int) ceilf(radius - .5f), count = 2 * n + 1;
+        int pix = (int) floorf(pos_x) - (int) n, piy = (int) floorf(pos_y) - (int) n;
+        uint32_t x = (uint32_t) (pix - s.crop_offset_x), y = (uint32_t) (piy - s.crop_offset_y);
+        float rel_x = ((float) pix + .5f) - pos_x, rel_y = ((float) piy + .5f) - pos_y;
+        for (uint32_t ys = 0; ys < count; ++ys) {
+            float weight_y = rfilter_eval(sc, rel_y + (float) ys);
+            bool active_1 = y + ys < size_y;
+            for (uint32_t xs = 0; xs < count; ++xs) {
+                float weight = rfilter_eval(sc, rel_x + (float) xs) * weight_y;
+                if (active_1 && x + xs < size_x) fn((size_t) (y + ys) * size_x + (x + xs), weight);
+            }
+        }
+    } else {
+        float off_x = (float) (-s.crop_offset_x) - .5f, off_y = (float) (-s.crop_offset_y) - .5f;
+        float pfx = pos_x + off_x, pfy = pos_y + off_y;
+        float p0x = pfx - radius, p0y = pfy - radius, p1x = pfx + radius, p1y = pfy + radius;
+        uint32_t x0 = (uint32_t) max((int) ceilf(p0x), 0), y0 = (uint32_t) max((int) ceilf(p0y), 0);
+        uint32_t x1 = (uint32_t) min((int) floorf(p1x), (int) size_x - 1), y1 = (uint32_t) min((int) floorf(p1y), (int) size_y - 1);
+        uint32_t count = (uint32_t) (int) ceilf(2.f * radius);
+        bool active = x0 <= x1 && y0 <= y1;
+        float rel_x = (float) x0 - pfx, rel_y = (float) y0 - pfy;
+        for (uint32_t ys = 0; ys < count; ++ys) {
+            float weight_y = rfilter_eval(sc, rel_y + (float) ys);
+            bool active_1 = active && (y0 + ys <= y1);
+            for (uint32_t xs = 0; xs < count; ++xs) {
+                float weight = rfilter_eval(sc, rel_x + (float) xs) * weight_y;
+                if (active_1 && (x0 + xs <= x1)) fn((size_t) (y0 + ys) * size_x + (x0 + xs), weight);
+            }
+        }
+    }
+}
+
 // MODE: 0 volpath, 1 volpathaos, 2 prbvolpath (primal), 3 prb_volpathaos (primal)
 template <int SPEC, int MODE>
 __global__ void __launch_bounds__(128, MIB_MINB) k_forward(const __grid_constant__ DScene sc, const __grid_constant__ LaunchParams lp) {
@@ -81,6 +136,13 @@ __global__ void __launch_bounds__(128, MIB_MINB) k_forward(const __grid_constant
         if (lp.mode == 2) {
 #pragma unroll
             for (int c = 0; c < C; ++c) lp.per_sample[(lane - lp.lane_begin) * C + c] = aov[c];
+            return;
+        }
+        if (lp.mode == 0 && sn.rfilter != MIB_RFILTER_BOX) {
+            filter_footprint(sc, lp.spp, sx, sy, [&](size_t pixel, float w) {
+#pragma unroll
+                for (int c = 0; c < C; ++c) atomicAdd(lp.film + pixel * C + c, aov[c] * w);
+            });
             return;
         }
         int ix = (int) floorf(sx) - sn.crop_offset_x, iy = (int) floorf(sy) - sn.crop_offset_y;
@@ -277,7 +339,14 @@ __global__ void __launch_bounds__(128) k_adjoint(const __grid_constant__ DScene 
             for (int c = 0; c < Cd; ++c) dl[c] = ap.grad1[c] * nf;
         } else {
             int ix = (int) floorf(sx) - sn.crop_offset_x, iy = (int) floorf(sy) - sn.crop_offset_y;
-            if ((uint32_t) ix < (uint32_t) sn.crop_width && (uint32_t) iy < (uint32_t) sn.crop_height) {
+            if (sn.rfilter != MIB_RFILTER_BOX) {
+                // adjoint of splat + weight division (hdrfilm.cpp:304-418): dL_c = sum_p grad[p,c] / W[p] * w_p
+                filter_footprint(sc, lp.spp, sx, sy, [&](size_t pixel, float w) {
+                    float W = __ldg(sc.weight_film + pixel), dv = W == 0.f ? 1.f : W;
+#pragma unroll
+                    for (int c = 0; c < Cd; ++c) dl[c] += __fdiv_rn(__ldg(ap.grad_image + pixel * Cd + c), dv) * w;
+                });
+            } else if ((uint32_t) ix < (uint32_t) sn.crop_width && (uint32_t) iy < (uint32_t) sn.crop_height) {
                 size_t pixel = (size_t) iy * sn.crop_width + ix;
 #pragma unroll
                 for (int c = 0; c < Cd; ++c) dl[c] = __fdiv_rn(__ldg(ap.grad_image + pixel * Cd + c), (float) lp.spp);
@@ -300,6 +369,20 @@ __global__ void __launch_bounds__(128) k_adjoint(const __grid_constant__ DScene 
 }
 
 template <int SPEC> void launch_k_adjoint(const DScene &sc, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, cudaStream_t st);
+
+// Filter-weight film of the whole wavefront (positions only): the denominator HDRFilm::develop divides by.
+static __global__ void k_weight_film(const __grid_constant__ DScene sc, uint32_t seed_value, uint32_t spp, uint64_t total, float *wfilm) {
+    const mib_sensor &sn = sc.d.sensor;
+    for (uint64_t lane = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; lane < total; lane += (uint64_t) gridDim.x * blockDim.x) {
+        Pcg32 rng;
+        rng.seed_lane(seed_value, (uint32_t) lane);
+        uint32_t idx = (uint32_t) (lane / spp);
+        uint32_t py = idx / (uint32_t) sn.crop_width, px = idx - (uint32_t) sn.crop_width * py;
+        float posx = (float) ((int) px + sn.crop_offset_x), posy = (float) ((int) py + sn.crop_offset_y);
+        float jx = rng.next(), jy = rng.next();
+        filter_footprint(sc, spp, posx + jx, posy + jy, [&](size_t pixel, float w) { atomicAdd(wfilm + pixel, w); });
+    }
+}
 
 // HDRFilm::develop (hdrfilm.cpp:304-418): value / (weight == 0 ? 1 : weight)
 template <int SPEC>

@@ -178,6 +178,25 @@ static void commit(mib_scene *s) {
                 s->ds.prb_null |= hom ? 0 : 1;
             }
     s->ds.grad_scalar = s->grad_scalar;
+    {   // reconstruction filter constants (gaussian.cpp:50-84: Remez fit to exp(-x/2), scaled, zero at the radius)
+        const mib_sensor &sn = d.sensor;
+        for (int i = 0; i < 10; ++i) s->ds.rf_coeff[i] = 0.f;
+        s->ds.rf_inv_radius = 1.f;
+        if (sn.rfilter == MIB_RFILTER_GAUSSIAN) {
+            const double coeff[10] = { 9.992604880e-1, -4.977025247e-1, 1.222248550e-1, -1.932406282e-2, 2.136713061e-3,
+                                       -1.679873860e-4, 9.202145248e-6, -3.329417433e-7, 7.128382794e-9, -6.821193280e-11 };
+            double scale = 1;
+            float *c = s->ds.rf_coeff;
+            for (int i = 0; i < 10; ++i) { c[i] = (float) (coeff[i] * scale); scale /= (double) sn.rfilter_stddev * (double) sn.rfilter_stddev; }
+            float x1 = sn.rfilter_radius * sn.rfilter_radius, x2 = x1 * x1, x4 = x2 * x2, x8 = x4 * x4;
+            float a0 = fmaf(x1, c[1], c[0]), a1 = fmaf(x1, c[3], c[2]), a2 = fmaf(x1, c[5], c[4]), a3 = fmaf(x1, c[7], c[6]), a4 = fmaf(x1, c[9], c[8]);
+            float b0 = fmaf(x2, a1, a0), b1 = fmaf(x2, a3, a2);
+            c[0] -= fmaf(x8, a4, fmaf(x4, b1, b0));
+        } else if (sn.rfilter == MIB_RFILTER_TENT) {
+            s->ds.rf_inv_radius = 1.f / sn.rfilter_radius;
+        }
+    }
+    s->ds.weight_film = nullptr;
     ensure_film(s);
     s->committed = true;
 }
@@ -259,8 +278,8 @@ static void fetch_counters(mib_scene *s, float ms, uint64_t launches) {
 static void run_forward(mib_scene *s, uint32_t seed, uint32_t spp, int mode, float *per_sample_dev) {
     if (!s->committed) throw std::runtime_error("mib_scene_commit() must be called before rendering");
     if (spp == 0) throw std::runtime_error("spp must be > 0");
-    if (s->ds.d.sensor.rfilter != MIB_RFILTER_BOX)
-        throw std::runtime_error("only the box reconstruction filter is implemented on the device in this build");
+    if (s->ds.d.sensor.rfilter != MIB_RFILTER_BOX && s->ds.d.spectrum == MIB_SPEC_MONO_POLARIZED && mode == 0)
+        throw std::runtime_error("the polarized Stokes film supports only the box filter");
     CK(cudaSetDevice(s->device));
     LaunchParams lp;
     lp.seed_value = s->ds.d.sampler_base_seed + seed;

@@ -96,6 +96,47 @@ int sample_aovs(const Scene &sc, Sampler &sampler, Counters &cnt, const Ray &ray
     }
 }
 
+// ImageBlock::put for a reconstruction filter (imageblock.cpp:261-530, the JIT recorded-loop forms, border 0):
+// calls fn(pixel, weight) for every pixel of the footprint.  Coalesced form when spp >= 4 (integrator.cpp:320,
+// common.py:93), the general form otherwise.
+template <typename Fn>
+void filter_footprint(const Scene &sc, uint32_t spp, float pos_x, float pos_y, Fn &&fn) {
+    const mib_sensor &s = sc.d.sensor;
+    const float radius = s.rfilter_radius;
+    const uint32_t size_x = (uint32_t) s.crop_width, size_y = (uint32_t) s.crop_height;
+    if (spp >= 4) {
+        uint32_t n = (uint32_t) (int) std::ceil(radius - .5f), count = 2 * n + 1;
+        int pix = (int) std::floor(pos_x) - (int) n, piy = (int) std::floor(pos_y) - (int) n;
+        uint32_t x = (uint32_t) (pix - s.crop_offset_x), y = (uint32_t) (piy - s.crop_offset_y);
+        float rel_x = ((float) pix + .5f) - pos_x, rel_y = ((float) piy + .5f) - pos_y;
+        for (uint32_t ys = 0; ys < count; ++ys) {
+            float weight_y = sc.rfilter_eval(rel_y + (float) ys);
+            bool active_1 = y + ys < size_y;
+            for (uint32_t xs = 0; xs < count; ++xs) {
+                float weight = sc.rfilter_eval(rel_x + (float) xs) * weight_y;
+                if (active_1 && x + xs < size_x) fn((size_t) (y + ys) * size_x + (x + xs), weight);
+            }
+        }
+    } else {
+        float off_x = (float) (-s.crop_offset_x) - .5f, off_y = (float) (-s.crop_offset_y) - .5f;
+        float pfx = pos_x + off_x, pfy = pos_y + off_y;
+        float p0x = pfx - radius, p0y = pfy - radius, p1x = pfx + radius, p1y = pfy + radius;
+        uint32_t x0 = (uint32_t) std::max((int) std::ceil(p0x), 0), y0 = (uint32_t) std::max((int) std::ceil(p0y), 0);
+        uint32_t x1 = (uint32_t) std::min((int) std::floor(p1x), (int) size_x - 1), y1 = (uint32_t) std::min((int) std::floor(p1y), (int) size_y - 1);
+        uint32_t count = (uint32_t) (int) std::ceil(2.f * radius);
+        bool active = x0 <= x1 && y0 <= y1;
+        float rel_x = (float) x0 - pfx, rel_y = (float) y0 - pfy;
+        for (uint32_t ys = 0; ys < count; ++ys) {
+            float weight_y = sc.rfilter_eval(rel_y + (float) ys);
+            bool active_1 = active && (y0 + ys <= y1);
+            for (uint32_t xs = 0; xs < count; ++xs) {
+                float weight = sc.rfilter_eval(rel_x + (float) xs) * weight_y;
+                if (active_1 && (x0 + xs <= x1)) fn((size_t) (y0 + ys) * size_x + (x0 + xs), weight);
+            }
+        }
+    }
+}
+
 int n_raw_channels(int spec) { return spec == MIB_SPEC_MONO ? 2 : 4; }
 int n_dev_channels(int spec) { return spec == MIB_SPEC_MONO ? 1 : (spec == MIB_SPEC_RGB ? 3 : 4); }
 
@@ -121,6 +162,13 @@ void render_range(OScene *os, uint32_t seed, uint32_t spp, uint64_t lane_begin, 
         float aovs[4];
         sample_aovs<SPEC>(sc, sampler, cnt, L.ray, aovs);
         if (per_sample) for (int c = 0; c < C; ++c) per_sample[(lane - lane_begin) * C + c] = aovs[c];
+        if (s.rfilter != MIB_RFILTER_BOX && !per_sample) {
+            std::lock_guard<std::mutex> g(*mtx);
+            filter_footprint(sc, spp, L.sample_x, L.sample_y, [&](size_t pixel, float w) {
+                for (int c = 0; c < C; ++c) film[pixel * C + c] += (double) (aovs[c] * w);
+            });
+            continue;
+        }
         // box filter put (imageblock.cpp:206-232): p = floor2int(pos) - offset; active &= all(p < size)
         int ix = (int) std::floor(L.sample_x) - s.crop_offset_x, iy = (int) std::floor(L.sample_y) - s.crop_offset_y;
         if ((uint32_t) ix >= (uint32_t) s.crop_width || (uint32_t) iy >= (uint32_t) s.crop_height) continue;
@@ -156,6 +204,8 @@ void render_all(OScene *os, uint32_t seed, uint32_t spp, uint64_t lane_begin, ui
 }
 
 void dispatch_render(OScene *os, uint32_t seed, uint32_t spp, uint64_t lb, uint64_t le, int nthreads, double *film, float *per_sample) {
+    if (os->sc.d.sensor.rfilter != MIB_RFILTER_BOX && os->sc.d.spectrum == MIB_SPEC_MONO_POLARIZED && !per_sample)
+        throw std::runtime_error("the polarized Stokes film supports only the box filter");
     switch (os->sc.d.spectrum) {
         case MIB_SPEC_MONO: render_all<0>(os, seed, spp, lb, le, nthreads, film, per_sample); break;
         case MIB_SPEC_RGB: render_all<1>(os, seed, spp, lb, le, nthreads, film, per_sample); break;

@@ -98,7 +98,28 @@ struct Scene {
     static float grid_max(const float *data, size_t n) { float m = -Inf; for (size_t i = 0; i < n; ++i) m = maximum(m, data[i]); return m; }
 
     // heterogeneous.cpp:163,176-178; grid.cpp:306-319; tabphase*.cpp ctor
+    // Reconstruction filter (src/rfilters/gaussian.cpp:50-98 non-CUDA branch, tent.cpp:33-45)
+    float rf_coeff[10] = {};
+    float rf_inv_radius = 1.f;
+    void prepare_rfilter() {
+        const mib_sensor &s = d.sensor;
+        if (s.rfilter == MIB_RFILTER_GAUSSIAN) {
+            const double coeff[10] = { 9.992604880e-1, -4.977025247e-1, 1.222248550e-1, -1.932406282e-2, 2.136713061e-3,
+                                       -1.679873860e-4, 9.202145248e-6, -3.329417433e-7, 7.128382794e-9, -6.821193280e-11 };
+            double scale = 1;
+            for (int i = 0; i < 10; ++i) { rf_coeff[i] = (float) (coeff[i] * scale); scale /= (double) s.rfilter_stddev * (double) s.rfilter_stddev; }
+            rf_coeff[0] -= estrin(sqr(s.rfilter_radius), rf_coeff, 10);
+        } else if (s.rfilter == MIB_RFILTER_TENT) {
+            rf_inv_radius = 1.f / s.rfilter_radius;
+        }
+    }
+    float rfilter_eval(float x) const {
+        if (d.sensor.rfilter == MIB_RFILTER_GAUSSIAN) return maximum(estrin(sqr(x), rf_coeff, 10), 0.f);
+        return maximum(0.f, 1.f - std::fabs(x * rf_inv_radius));
+    }
+
     void prepare() {
+        prepare_rfilter();
         for (int i = 0; i < d.n_media; ++i) {
             mib_medium &m = d.media[i];
             mib_volume *vols[2] = { &m.sigma_t, &m.albedo };

@@ -188,3 +188,19 @@ def test_backward_needs_prb_integrator():
     dev = _lib.DeviceScene(sc, 0)
     with pytest.raises(RuntimeError, match="prbvolpath"):
         dev.render_backward(0, 4, np.zeros((8, 8, 3), np.float32))
+
+
+@pytest.mark.parametrize("rfilter,spp", [("gaussian", 8), ("tent", 8), ("gaussian", 2)])
+def test_render_backward_through_reconstruction_filter(rfilter, spp):
+    """Adjoint of splat + weight division: dL = sum_p grad[p] / W[p] * w_p (common.py:899-945)."""
+    d = scenes.c1_homogeneous_cube(res=12, spp=spp, max_depth=8, rfilter=rfilter)
+    d['integrator'] = {'type': 'prbvolpath', 'max_depth': 8, 'rr_depth': 5}
+    sc = S.load_dict(d, "llvm_ad_rgb")
+    dev, orc = _lib.DeviceScene(sc, 0), OracleScene(sc)
+    gi = np.random.default_rng(5).uniform(-1, 1, size=(12, 12, 3)).astype(np.float32)
+    dev.grad_zero()
+    dev.render_backward(1, spp, gi)
+    orc.render_backward(1, spp, gi)
+    g, o = dev.grad_get_scalar(0), orc.grad_get_scalar(0)
+    print("scalar grads gpu", g, "oracle", o)
+    assert np.allclose(g, o, rtol=GRAD_TOL, atol=GRAD_TOL * np.abs(o).max())

@@ -127,8 +127,39 @@ def test_heterogeneous_polarized_tabphase_lanes():
     m34 = (0.1 * (1 - cost ** 2)).astype(np.float32)
     # tabphase_polarized returns the UNNORMALISED matrix with the NORMALISED pdf
     # (tabphase_polarized.cpp:161-164,201-202): tables must integrate to 1 over the sphere
-    k = np.float32(1.0 / (2 * np.pi * np.trapz(m11.astype(np.float64), cost.astype(np.float64))))
+    k = np.float32(1.0 / (2 * np.pi * np.trapezoid(m11.astype(np.float64), cost.astype(np.float64))))
     m11, m12, m33, m34 = m11 * k, m12 * k, m33 * k, m34 * k
     phase = {'type': 'tabphase_polarized', 'cost': cost, 'm11': m11, 'm12': m12, 'm33': m33, 'm34': m34}
     d = scenes.c3_cloud(res=12, spp=8, grid=grid, phase=phase, optical_depth=6.0)
     _lane_compare(d, "llvm_ad_mono_polarized", 8, 12 * 12 * 8, flip_frac=5e-3)
+
+
+@pytest.mark.parametrize("rfilter", ["gaussian", "tent"])
+@pytest.mark.parametrize("spp", [8, 2])          # >= 4: coalesced put, < 4: general put (integrator.cpp:320)
+@pytest.mark.parametrize("variant", ["llvm_ad_rgb", "llvm_ad_mono"])
+def test_reconstruction_filters(rfilter, spp, variant):
+    """ImageBlock::put with a reconstruction filter (imageblock.cpp:261-530) + weight division (hdrfilm.cpp:304-418).
+    Cropped film so that the crop offset arithmetic is exercised too."""
+    d = scenes.c1_homogeneous_cube(res=24, spp=spp, max_depth=8, rfilter=rfilter)
+    d['sensor']['film'].update({'crop_offset_x': 3, 'crop_offset_y': 5, 'crop_width': 17, 'crop_height': 13})
+    if 'mono' in variant:
+        d['sensor']['film']['pixel_format'] = 'luminance'
+    sc = S.load_dict(d, variant)
+    dev, orc = _lib.DeviceScene(sc, 0), OracleScene(sc)
+    g_raw = dev.render(2, spp, develop=False)
+    g_dev = dev.render(2, spp, develop=True)
+    o_raw, o_dev = orc.render(2, spp, nthreads=4)
+    assert g_dev.shape == o_dev.shape == (13, 17, 3 if 'rgb' in variant else 1)
+    # float atomics in arbitrary order vs double accumulation
+    assert np.allclose(g_raw, o_raw, rtol=2e-5, atol=1e-6)
+    assert np.allclose(g_dev, o_dev, rtol=REL_TOL, atol=1e-6)
+
+
+def test_polarized_film_rejects_filters():
+    d = scenes.c2_rayleigh_slab(spp=4)
+    d['sensor']['film']['rfilter'] = {'type': 'gaussian'}
+    sc = S.load_dict(d, "llvm_ad_mono_polarized")
+    dev = _lib.DeviceScene(sc, 0)
+    with pytest.raises(RuntimeError, match="box filter"):
+        dev.render(0, 4)
+    assert np.isfinite(dev.render_1(0, 64)).all()        # render_1 never touches the film filter
