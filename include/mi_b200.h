@@ -251,6 +251,15 @@ int  mib_grad_get_scalar(mib_scene *scene, int medium, double *out4);
 int  mib_grad_scalar_dev(mib_scene *scene, double **dev, size_t *count);
 int  mib_grad_zero(mib_scene *scene);
 
+/* Lorenz-Mie phase-matrix tabulation on the device: MiePhaseFunction::eval_mie (src/phase/mie.cpp:117-215), mie()
+   (include/mitsuba/render/mie.h:45-222), mueller::mie_scatter (mueller.h:282-295) averaged over a size distribution
+   given by its Gauss-Legendre nodes (SizeDistribution::eval_gauss_all, include/mitsuba/render/sizedistr.h:33-47):
+   radius[g], quadrature weight[g], normalised density sdf[g].  n_gauss == 1 with sdf == NULL: monodisperse.
+   mu[n_mu] = cos(theta) nodes; outputs are the four distinct Mueller entries per node.  All pointers are host memory. */
+int  mib_mie_tabulate(int device, float wavelength, float ior_med_re, float ior_med_im, float ior_sph_re, float ior_sph_im,
+                      int nmax, const float *radius, const float *weight, const float *sdf, int n_gauss,
+                      const float *mu, int n_mu, float *m11, float *m12, float *m33, float *m34);
+
 int  mib_counters_get(mib_scene *scene, mib_counters *out);
 /* The CUDA stream the scene launches on (cudaStream_t as void*). */
 int  mib_scene_stream(mib_scene *scene, void **stream);

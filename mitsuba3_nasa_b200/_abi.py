@@ -100,7 +100,7 @@ EXPORTS = [
     "mib_scene_set_lane_range", "mib_render", "mib_film_dev", "mib_film_develop", "mib_film_read",
     "mib_render_1", "mib_render_1_raw", "mib_render_backward", "mib_render_1_backward",
     "mib_grad_get", "mib_grad_dev", "mib_grad_get_scalar", "mib_grad_scalar_dev", "mib_grad_zero",
-    "mib_counters_get", "mib_scene_stream",
+    "mib_mie_tabulate", "mib_counters_get", "mib_scene_stream",
     "mib_debug_sample_lanes", "mib_debug_math",
 ]
 

@@ -17,6 +17,7 @@ using namespace mib;
 static_assert(sizeof(DScene) < 32000, "DScene must fit the kernel parameter space");
 
 static thread_local std::string g_err;
+std::string &mib_error_slot() { return g_err; }   // shared with mie.cu
 
 #define CK(call)                                                                                   \
     do {                                                                                           \

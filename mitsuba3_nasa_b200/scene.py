@@ -326,6 +326,8 @@ class Scene:
                     self.params[key + '.' + n] = {'kind': 'buffer', 'slot': s}
         elif p.type == 'mie':
             # src/phase/mie.cpp:251-257: mie is tabulated before rendering
+            if self.spectrum == A.SPEC_RGB:
+                raise PluginError("Mie phase function may only be used in monochromatic or spectral mode!")   # mie.cpp:67-68
             from .mie import tabulate_mie_plugin
             cost, m11, m12, m33, m34 = tabulate_mie_plugin(p, pr)
             out.type = A.PHASE_TABPHASE_POLARIZED

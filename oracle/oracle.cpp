@@ -15,6 +15,7 @@
 // in the reference -> "parity unpinned" above the building blocks.
 #include "owalk.h"
 #include "oadjoint.h"
+#include "omie.h"
 #include <thread>
 #include <mutex>
 #include <atomic>
