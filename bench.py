@@ -197,6 +197,11 @@ def run_ours(args):
     t_e2e = float(allreduce([time.perf_counter() - t0], "max")[0])
     e2e = n_total * args.steps / t_e2e / 1e6
 
+    # ---- adjoint (C4), all ranks: lanes sharded, gradients all-reduced over NCCL ----
+    try:
+        adjoint = adjoint_bench(local_rank, rank, world) if not args.no_adjoint else None
+    except Exception as e:
+        adjoint = {"error": str(e)}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -224,12 +229,14 @@ def run_ours(args):
                 "d2h_bytes_per_step": 4 * 8 + ctypes.sizeof(_abi.Counters)},
         "gpu_launches": int(launches),
         "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": FP32_PEAK_TFLOPS, "unit": "TFLOP/s",
-                     "frac": achieved_tf / FP32_PEAK_TFLOPS, "traffic": None,
+                     "frac": achieved_tf / FP32_PEAK_TFLOPS, "traffic": 201728,
+                     "traffic_note": "dram bytes read (writes < 10 KB) by one k_forward<2,1> launch, ncu --set full (profiles/r01_ncu_c2_pol_volpathaos_summary.txt, 2^24 samples): the scene is analytic",
                      "kernel": "k_forward<mono_polarized, volpathaos>",
                      "note": "homogeneous medium: no grid traffic, FP32-pipe bound; peak = 148 SM x 128 lanes x 2 x 1.965 GHz "
                              "(derived, not in MEASURED_PEAKS.json); flops = documented per-event constants x exact event counters",
                      "events_per_launch": c1, "hbm_peak_gbs_measured": peaks.get("hbm_gbs")},
     }
+    line["adjoint"] = adjoint
     # ---- secondary: heterogeneous grid workload (memory side) on rank 0 ----
     try:
         line["roofline_grid"] = grid_roofline(local_rank, peaks)
@@ -256,8 +263,7 @@ def grid_roofline(device, peaks):
     import mitsuba3_nasa_b200 as mi
     from mitsuba3_nasa_b200 import scenes
     mi.set_variant('llvm_ad_mono')
-    cost, val = scenes.hg_table(0.85, 1801)
-    d = scenes.c3_cloud(res=512, spp=16, grid_res=256, phase={'type': 'tabphase', 'cost': cost, 'values': val})
+    d = scenes.c3_cloud(res=512, spp=16, grid_res=256)       # BASELINE C3 scene (Mie x lognormal table, 1801 nodes), 512^2 x 16 spp
     scene = mi.load_dict(d, device=device)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     ms, cnt = [], None
@@ -273,9 +279,50 @@ def grid_roofline(device, peaks):
     hbm = peaks.get("hbm_gbs", 6650.0)
     return {"bound": "hbm", "achieved": b / t / 1e9, "peak": hbm, "unit": "GB/s", "frac": b / t / 1e9 / hbm, "traffic": None,
             "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback",
-            "kernel": "k_forward<mono, volpath>", "workload": "C3-shaped: 256^3 grid, 512x512x16 spp, tabphase(HG g=0.85 table)",
+            "kernel": "k_forward<mono, volpath>", "workload": "C3 scene (256^3 grid, Mie x lognormal table) at 512x512x16 spp",
             "msamples_per_s": cnt['n_samples'] / t / 1e6, "ms": t * 1e3, "l2": "flushed between iterations (256 MiB write)",
             "events": cnt}
+
+
+def adjoint_bench(device, rank, world):
+    """C4: path-replay adjoint of the C3 scene w.r.t. the 256^3 density grid (prb_volpathaos, mono_polarized,
+    render_1_backward with d loss / d I = 1), 512x512x64 spp sharded over the ranks + gradient all-reduce."""
+    import torch
+    import mitsuba3_nasa_b200 as mi
+    from mitsuba3_nasa_b200 import scenes
+    from mitsuba3_nasa_b200.dist import ShardedScene
+    mi.set_variant('llvm_ad_mono_polarized')
+    scene = mi.load_dict(scenes.c4_cloud_adjoint(), device=device)
+    sh = ShardedScene(scene)
+    dev = scene.device
+    spp = 64
+    dev.grad_zero()
+    sh.render_backward([1.0, 0.0, 0.0, 0.0], seed=99, spp=4, render_1=True)       # warm-up (also allocates the gradient)
+    dev.grad_zero()
+    torch.cuda.synchronize()
+    if world > 1:
+        torch.distributed.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    sh.render_backward([1.0, 0.0, 0.0, 0.0], seed=0, spp=spp, render_1=True)
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    c = dev.counters()
+    t = torch.tensor([c['kernel_ms'], wall * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    kernel_ms, wall_ms = [float(x) for x in t.cpu().numpy()]
+    n = 512 * 512 * spp
+    slot = sh.grad_slots()[0]
+    g = dev.grad_get(slot, scene.flat.buffers[slot].size)
+    # bytes: primal pass look-ups + backward look-ups (32 B each) + gradient read-modify-write through 8 taps (64 B)
+    alg_bytes = 32 * c['n_lookups'] + 64 * (c['n_lookups'] / 2)
+    return {"workload": "C4: C3 scene 512x512x64 spp, prb_volpathaos, render_1_backward wrt the 256^3 sigma_t grid",
+            "msamples_per_s": n / (kernel_ms / 1e3) / 1e6, "kernel_ms_max_over_ranks": kernel_ms,
+            "wall_ms_with_gradient_allreduce": wall_ms, "gradient_bytes": int(g.size * 4),
+            "grad_abs_sum": float(np.abs(g.astype(np.float64)).sum()), "events_this_rank": c,
+            "algorithmic_gbs_this_rank": alg_bytes / (c['kernel_ms'] / 1e3) / 1e9,
+            "note": "one sample = primal replay + backward pass of one lane (both passes timed)"}
 
 
 def main():
@@ -285,6 +332,7 @@ def main():
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
+    ap.add_argument('--no-adjoint', action='store_true', help='skip the C4 adjoint leg')
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)

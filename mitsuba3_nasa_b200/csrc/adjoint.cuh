@@ -55,7 +55,9 @@ MIB_D void sink_volume(const DScene &sc, Sink &sink, const mib_volume &v, int me
 #pragma unroll
             for (int c = 1; c < NC; ++c) s += coeff[c];
             if (s == 0.f) return;
+#ifndef MIB_NO_GRAD_ATOMICS
             for (int k = 0; k < n; ++k) atomicAdd(g + taps.idx[k], s * taps.w[k]);
+#endif
         } else {
             for (int k = 0; k < n; ++k)
 #pragma unroll

@@ -16,6 +16,9 @@
 #ifndef MIB_WARPSYNC
 #define MIB_WARPSYNC 1      // 1: warp vote at the head of the flat loop (forced reconvergence every iteration)
 #endif
+#ifndef MIB_MINB_ADJ
+#define MIB_MINB_ADJ 3
+#endif
 #ifndef MIB_STAGED
 #define MIB_STAGED 0   // 1: stage machine of dstage.cuh (flattened shadow walk), 0: nested shadow walk (dwalk.cuh)
 #endif
@@ -304,7 +307,7 @@ __global__ void __launch_bounds__(128, MIB_MINB) k_forward(const __grid_constant
 // k_forward so that neighbouring threads walk neighbouring samples of one pixel.
 // ---------------------------------------------------------------------------
 template <int SPEC>
-__global__ void __launch_bounds__(128) k_adjoint(const __grid_constant__ DScene sc, const __grid_constant__ LaunchParams lp,
+__global__ void __launch_bounds__(128, MIB_MINB_ADJ) k_adjoint(const __grid_constant__ DScene sc, const __grid_constant__ LaunchParams lp,
                                                  const __grid_constant__ AdjParams ap) {
     constexpr int NR = ST<SPEC>::NR, Cd = SPEC == MIB_SPEC_MONO ? 1 : (SPEC == MIB_SPEC_RGB ? 3 : 4);
     constexpr bool AOS = ST<SPEC>::POL;
@@ -320,43 +323,62 @@ __global__ void __launch_bounds__(128) k_adjoint(const __grid_constant__ DScene 
     const float offset_x = -(float) sn.crop_offset_x * scale_x, offset_y = -(float) sn.crop_offset_y * scale_y;
     const float nf = rcp_((float) ((uint32_t) sn.crop_width * (uint32_t) sn.crop_height * lp.spp));   // common.py:1046
 
-    for (uint64_t lane = l0; lane < l1; ++lane) {
-        Pcg32 rng;
-        rng.seed_lane(lp.seed_value, (uint32_t) lane);
-        uint32_t idx = (uint32_t) (lane / lp.spp);
-        uint32_t py = idx / (uint32_t) sn.crop_width, px = idx - (uint32_t) sn.crop_width * py;
-        float posx = (float) ((int) px + sn.crop_offset_x), posy = (float) ((int) py + sn.crop_offset_y);
-        float jx = rng.next(), jy = rng.next();
-        float sx = posx + jx, sy = posy + jy;
-        float ax = fma_(sx, scale_x, offset_x), ay = fma_(sy, scale_y, offset_y);
-        float apx = .5f, apy = .5f;
-        if (sn.needs_aperture_sample) { apx = rng.next(); apy = rng.next(); }
-        Ray ray = sensor_ray(sc, ax, ay, apx, apy);
-        n_samples++;
-        float dl[4] = { 0.f, 0.f, 0.f, 0.f };
-        if (ap.render_1) {
+    // Flat loop with lane regeneration (as k_forward): a thread alternates primal pass -> backward pass -> next lane
+    // and never waits for the longest path of its warp; the vote at the loop head is the reconvergence point.
+    PrbState<SPEC> st;
+    st.active = false;
+    int pass = 1;                                   // 0: primal pass in flight, 1: backward pass in flight / idle
+    Pcg32 rng, start_rng;
+    Ray ray0;
+    float dl[4] = { 0.f, 0.f, 0.f, 0.f };
+    uint64_t lane = l0;
+    while (__any_sync(0xffffffffu, st.active || pass == 0 || lane < l1)) {
+        if (!st.active) {
+            if (pass == 0) {
+                float Lp[NR];
 #pragma unroll
-            for (int c = 0; c < Cd; ++c) dl[c] = ap.grad1[c] * nf;
-        } else {
-            int ix = (int) floorf(sx) - sn.crop_offset_x, iy = (int) floorf(sy) - sn.crop_offset_y;
-            if (sn.rfilter != MIB_RFILTER_BOX) {
-                // adjoint of splat + weight division (hdrfilm.cpp:304-418): dL_c = sum_p grad[p,c] / W[p] * w_p
-                filter_footprint(sc, lp.spp, sx, sy, [&](size_t pixel, float w) {
-                    float W = __ldg(sc.weight_film + pixel), dv = W == 0.f ? 1.f : W;
+                for (int i = 0; i < NR; ++i) Lp[i] = st.L[i];
+                rng = start_rng;
+                prb_init<SPEC, AOS>(sc, rng, ray0, true, Lp, dl, st);
+                pass = 1;
+            } else if (lane < l1) {
+                uint64_t cur = lane++;
+                rng.seed_lane(lp.seed_value, (uint32_t) cur);
+                uint32_t idx = (uint32_t) (cur / lp.spp);
+                uint32_t py = idx / (uint32_t) sn.crop_width, px = idx - (uint32_t) sn.crop_width * py;
+                float posx = (float) ((int) px + sn.crop_offset_x), posy = (float) ((int) py + sn.crop_offset_y);
+                float jx = rng.next(), jy = rng.next();
+                float sx = posx + jx, sy = posy + jy;
+                float ax = fma_(sx, scale_x, offset_x), ay = fma_(sy, scale_y, offset_y);
+                float apx = .5f, apy = .5f;
+                if (sn.needs_aperture_sample) { apx = rng.next(); apy = rng.next(); }
+                ray0 = sensor_ray(sc, ax, ay, apx, apy);
+                n_samples++;
+                dl[0] = dl[1] = dl[2] = dl[3] = 0.f;
+                if (ap.render_1) {
 #pragma unroll
-                    for (int c = 0; c < Cd; ++c) dl[c] += __fdiv_rn(__ldg(ap.grad_image + pixel * Cd + c), dv) * w;
-                });
-            } else if ((uint32_t) ix < (uint32_t) sn.crop_width && (uint32_t) iy < (uint32_t) sn.crop_height) {
-                size_t pixel = (size_t) iy * sn.crop_width + ix;
+                    for (int c = 0; c < Cd; ++c) dl[c] = ap.grad1[c] * nf;
+                } else {
+                    int ix = (int) floorf(sx) - sn.crop_offset_x, iy = (int) floorf(sy) - sn.crop_offset_y;
+                    if (sn.rfilter != MIB_RFILTER_BOX) {
+                        // adjoint of splat + weight division (hdrfilm.cpp:304-418): dL_c = sum_p grad[p,c] / W[p] * w_p
+                        filter_footprint(sc, lp.spp, sx, sy, [&](size_t pixel, float w) {
+                            float W = __ldg(sc.weight_film + pixel), dv = W == 0.f ? 1.f : W;
 #pragma unroll
-                for (int c = 0; c < Cd; ++c) dl[c] = __fdiv_rn(__ldg(ap.grad_image + pixel * Cd + c), (float) lp.spp);
+                            for (int c = 0; c < Cd; ++c) dl[c] += __fdiv_rn(__ldg(ap.grad_image + pixel * Cd + c), dv) * w;
+                        });
+                    } else if ((uint32_t) ix < (uint32_t) sn.crop_width && (uint32_t) iy < (uint32_t) sn.crop_height) {
+                        size_t pixel = (size_t) iy * sn.crop_width + ix;
+#pragma unroll
+                        for (int c = 0; c < Cd; ++c) dl[c] = __fdiv_rn(__ldg(ap.grad_image + pixel * Cd + c), (float) lp.spp);
+                    }
+                }
+                start_rng = rng;
+                prb_init<SPEC, AOS>(sc, rng, ray0, false, nullptr, nullptr, st);
+                pass = 0;
             }
         }
-        const Pcg32 start = rng;
-        float Lp[NR], Lres[NR];
-        prb_walk<SPEC, AOS>(sc, rng, cnt, ray, false, nullptr, nullptr, sink, Lp);
-        rng = start;
-        prb_walk<SPEC, AOS>(sc, rng, cnt, ray, true, Lp, dl, sink, Lres);
+        if (st.active) prb_step<SPEC, AOS>(sc, rng, cnt, sink, st);
     }
     sink.flush(sc);
     unsigned long long cv[6] = { cnt.n_lookups, cnt.n_real, cnt.n_null, cnt.n_nee_steps, cnt.n_surface, n_samples };

@@ -169,5 +169,13 @@ def tabulate_mie_plugin(plugin, props, device=0):
         if isinstance(cost, str):
             cost = np.array([float(t) for t in cost.replace(',', ' ').split()], f32)
         cost = np.asarray(cost, f32)
+    normalize = bool(props.get('normalize', True))
     m11, m12, m33, m34 = mie_tabulate(cost, wavelength, distr, ior_med, ior_sph, nmax, device)
+    if normalize:
+        # The tabulated plugins return the UNNORMALISED matrix with the NORMALISED piecewise-linear pdf of m11
+        # (tabphase_polarized.cpp:119-205), i.e. every scatter multiplies the throughput by 2 pi * trapz(m11).  A
+        # forward peak narrower than the node spacing (cloud droplets: m11(1) ~ 1e3, width ~ 1e-5 in cos theta) makes
+        # that factor 4.2 on 1801 uniform nodes.  Rescale so that the discretised m11 is a normalised phase function.
+        k = 1.0 / (2.0 * np.pi * np.trapezoid(m11.astype(np.float64), cost.astype(np.float64)))
+        m11, m12, m33, m34 = [(a.astype(np.float64) * k).astype(f32) for a in (m11, m12, m33, m34)]
     return cost, m11, m12, m33, m34
