@@ -49,6 +49,13 @@ def _as_tensor(ptr, count, dtype, device):
     return torch.as_tensor(_DevArray(ptr, count, typestr), device=torch.device("cuda", device))
 
 
+def _sync(device):
+    """The collectives run on torch's NCCL stream, the kernels on the library's own stream: the buffers may only be
+    touched again (grad_zero, develop, the next render) once the collective has finished."""
+    import torch
+    torch.cuda.synchronize(device)
+
+
 def _world():
     import torch.distributed as dist
     if dist.is_available() and dist.is_initialized():
@@ -91,6 +98,7 @@ class ShardedScene:
         if self.world > 1:
             (raw_ptr, raw_n), _ = dev.film_dev()
             dist.all_reduce(_as_tensor(raw_ptr, raw_n, "float32", dev.device_index), op=dist.ReduceOp.SUM)
+            _sync(dev.device_index)
         dev.film_develop()
         return dev.film_read(developed=True)
 
@@ -106,7 +114,9 @@ class ShardedScene:
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
             sums = t.cpu().numpy()
         sn = self.scene.flat.desc.sensor
-        return sums / float(sn.crop_width * sn.crop_height * spp)
+        # integrator.cpp:702-705: the normalisation factor is a float32 reciprocal (same as mib_render_1)
+        nf = np.float32(1.0) / (np.float32(sn.crop_width * sn.crop_height) * np.float32(spp))
+        return sums * float(nf)
 
     def render_backward(self, grad_in, seed=0, spp=0, render_1=False):
         """Accumulates the gradients of this rank's lanes, then sums every gradient buffer over the ranks.
@@ -125,3 +135,4 @@ class ShardedScene:
                 dist.all_reduce(_as_tensor(ptr, n, "float32", dev.device_index), op=dist.ReduceOp.SUM)
             ptr, n = dev.grad_scalar_dev()
             dist.all_reduce(_as_tensor(ptr, n, "float64", dev.device_index), op=dist.ReduceOp.SUM)
+            _sync(dev.device_index)
