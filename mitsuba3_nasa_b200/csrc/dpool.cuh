@@ -1,0 +1,553 @@
+// dpool.cuh -- k_forward_pool: the forward walk as a persistent, CTA-resident path pool.
+//
+// One CTA per SM keeps P paths ("slots") in shared memory (structure of arrays, one 32-bit word
+// per field and slot).  Every slot sits in exactly one of six stage queues (rings of slot ids in
+// shared memory).  A warp repeatedly
+//     1. claims up to 32 slot ids from the fullest queue        (one CAS by lane 0),
+//     2. loads the fields that stage needs into registers,
+//     3. runs the stage (dstage.cuh) -- all 32 lanes execute the SAME stage,
+//     4. stores the changed fields and appends the slot id to the queue of its next stage.
+// There is no CTA-wide barrier in the steady state; P is 2-3x the thread count so that a full
+// batch of 32 is (almost) always available.  A finished path goes back to START, which adds its
+// radiance to the film / render_1 sums and starts the next lane of the CTA in the same slot.
+//
+// Lanes are dealt to CTAs in interleaved chunks of kPoolChunk lanes (chunk c belongs to CTA
+// c mod gridDim), so every CTA samples the whole image and the load is balanced without a global
+// work counter.  Per-lane seeds depend only on the global lane index (integrator.cpp:323-340), so
+// the result is independent of which slot / warp / CTA walked a lane.
+//
+// Why this shape: the one-thread-one-path kernel (k_forward in kernels.cuh) measured 6-10 of 32
+// lanes active per warp instruction and `no_instruction` as the top stall (profiles/r01_*): lanes of
+// a warp sit in different branches of a 200 KB loop body.  Here a warp fetches one stage's code once
+// for 32 paths.
+#pragma once
+#include "dstage.cuh"
+
+#ifndef MIB_POOL_NT
+#define MIB_POOL_NT 384        // max threads per CTA (register cap 65536 / 384 = 168)
+#endif
+
+namespace mib {
+
+constexpr int kPoolChunk = 256;            // lanes per interleaved chunk
+constexpr int kPoolMainIters = 2;          // MAIN: null collisions handled per batch before the slot is re-queued
+constexpr int kPoolNeeIters = 4;           // NEE: shadow steps per batch
+constexpr unsigned kPoolSpinLimit = 1u << 26;
+constexpr uint32_t kNoLane = 0xffffffffu;
+constexpr unsigned kRingEmpty = 0xffffu;
+
+enum { C_START = 0, C_MAIN = 1, C_SCAT = 2, C_NEE = 3, C_PHASE = 4, C_BSDF = 5, C_COUNT = 6 };
+
+// Field map of one slot (units: 32-bit words; word f of slot s lives at pw[f * P + s]).
+template <int SPEC> struct PoolL {
+    static constexpr int NC = ST<SPEC>::NC, NT = ST<SPEC>::NT, NR = ST<SPEC>::NR;
+    static constexpr int F_RNG = 0;                    // state lo, state hi, inc lo, inc hi
+    static constexpr int F_LANE = 4;                   // CTA-local lane index of the path in this slot (kNoLane: none)
+    static constexpr int F_DEPTH = 5;
+    static constexpr int F_FLAGS = 6;
+    static constexpr int F_ETA = 7, F_LASTPDF = 8;
+    static constexpr int F_RAY = 9;                    // o(3) d(3) maxt
+    static constexpr int F_SI = 16;                    // t, p(3), shape | face << 16
+    static constexpr int F_SCP = 21;                   // scatter_p(3)
+    static constexpr int F_T = 24;
+    static constexpr int F_R = F_T + NT;
+    static constexpr int F_NRAY = F_R + NR;            // shadow ray o(3) d(3)
+    static constexpr int F_NSI = F_NRAY + 6;           // t, p(3), shape | face << 16
+    static constexpr int F_NED = F_NSI + 5;            // emitter_d(3)
+    static constexpr int F_NTR = F_NED + 3;
+    static constexpr int F_NEV = F_NTR + NC;           // emitter value; between MAIN and SCATTER: the albedo factor u
+    static constexpr int F_NDIST = F_NEV + NC;         // total_dist, max_dist, ds_dist
+    static constexpr int F_NA = F_NDIST + 3;
+    static constexpr int F_NW = F_NA + NR;
+    static constexpr int F_COUNT = F_NW + 1;
+};
+
+// flags word
+constexpr uint32_t FL_CHANNEL = 0x3, FL_SPEC_CHAIN = 0x4, FL_NEEDS_INT = 0x8, FL_NEE_ACTIVE = 0x10, FL_NEE_NEEDS_INT = 0x20,
+                   FL_NEE_MULW = 0x40, FL_NEE_SURFACE = 0x80;
+MIB_D uint32_t fl_medium(uint32_t f) { return (f >> 8) & 0xff; }         // medium + 1
+MIB_D uint32_t fl_nee_medium(uint32_t f) { return (f >> 16) & 0xff; }    // nee.medium + 1
+
+struct PoolShared {
+    unsigned head[8], tail[8];
+    unsigned next_local, total_local, retired, error;
+};
+
+MIB_D size_t pool_ring_offset() { return (sizeof(PoolShared) + 15) & ~(size_t) 15; }
+MIB_D size_t pool_state_offset(int P) { return (pool_ring_offset() + (size_t) C_COUNT * P * sizeof(uint16_t) + 15) & ~(size_t) 15; }
+template <int SPEC> size_t pool_smem_bytes(int P) {
+    size_t ring = (sizeof(PoolShared) + 15) & ~(size_t) 15;
+    size_t state = (ring + (size_t) C_COUNT * P * sizeof(uint16_t) + 15) & ~(size_t) 15;
+    return state + (size_t) PoolL<SPEC>::F_COUNT * P * sizeof(uint32_t);
+}
+
+// slot accessors
+struct PoolMem {
+    uint32_t *pw;
+    int P;
+    MIB_D float f(int field, int slot) const { return __uint_as_float(pw[field * P + slot]); }
+    MIB_D uint32_t u(int field, int slot) const { return pw[field * P + slot]; }
+    MIB_D void sf(int field, int slot, float v) const { pw[field * P + slot] = __float_as_uint(v); }
+    MIB_D void su(int field, int slot, uint32_t v) const { pw[field * P + slot] = v; }
+    MIB_D V3 v3f(int field, int slot) const { return v3(f(field, slot), f(field + 1, slot), f(field + 2, slot)); }
+    MIB_D void sv3(int field, int slot, V3 v) const { sf(field, slot, v.x); sf(field + 1, slot, v.y); sf(field + 2, slot, v.z); }
+    MIB_D void load_rng(int slot, Pcg32 &r) const {
+        r.state = (uint64_t) u(0, slot) | ((uint64_t) u(1, slot) << 32);
+        r.inc = (uint64_t) u(2, slot) | ((uint64_t) u(3, slot) << 32);
+    }
+    MIB_D void store_rng_state(int slot, const Pcg32 &r) const { su(0, slot, (uint32_t) r.state); su(1, slot, (uint32_t) (r.state >> 32)); }
+    MIB_D void store_rng(int slot, const Pcg32 &r) const {
+        store_rng_state(slot, r);
+        su(2, slot, (uint32_t) r.inc); su(3, slot, (uint32_t) (r.inc >> 32));
+    }
+    MIB_D void load_si(int field, int slot, SurfIt &si) const {
+        si.t = f(field, slot);
+        si.p = v3f(field + 1, slot);
+        uint32_t sf_ = u(field + 4, slot);
+        si.shape = (int) (sf_ & 0xffffu) - 1;
+        si.face = (int) (sf_ >> 16);
+    }
+    MIB_D void store_si(int field, int slot, const SurfIt &si) const {
+        sf(field, slot, si.t);
+        sv3(field + 1, slot, si.p);
+        su(field + 4, slot, (uint32_t) (si.shape + 1) | ((uint32_t) si.face << 16));
+    }
+};
+
+// CTA-local lane index -> lane of the wavefront (interleaved chunks)
+MIB_D uint64_t pool_lane(uint32_t i, uint32_t cta, uint32_t n_cta) {
+    uint64_t chunk = (uint64_t) cta + (uint64_t) (i / kPoolChunk) * n_cta;
+    return chunk * kPoolChunk + (i % kPoolChunk);
+}
+
+template <int SPEC, int MODE>
+__global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_constant__ DScene sc, const __grid_constant__ LaunchParams lp) {
+    using L = PoolL<SPEC>;
+    constexpr int C = RawChannels<SPEC>::C, NR = ST<SPEC>::NR, NC = ST<SPEC>::NC, NT = ST<SPEC>::NT;
+    constexpr bool AOS = MODE == 1;
+    constexpr unsigned FULL = 0xffffffffu;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int P = (int) lp.pool_slots;
+    PoolShared *ps = reinterpret_cast<PoolShared *>(smem_raw);
+    volatile uint16_t *ring = reinterpret_cast<volatile uint16_t *>(smem_raw + pool_ring_offset());
+    PoolMem pm;
+    pm.pw = reinterpret_cast<uint32_t *>(smem_raw + pool_state_offset(P));
+    pm.P = P;
+    const mib_sensor &sn = sc.d.sensor;
+    const unsigned lane_id = threadIdx.x & 31;
+
+    // ---- lanes of this CTA ----
+    const uint64_t N = lp.lane_end - lp.lane_begin;
+    const uint64_t n_chunks = (N + kPoolChunk - 1) / kPoolChunk;
+    uint64_t owned = n_chunks > blockIdx.x ? (n_chunks - 1 - blockIdx.x) / gridDim.x + 1 : 0;
+    uint64_t total_local = 0;
+    if (owned) {
+        uint64_t last = blockIdx.x + (owned - 1) * gridDim.x;
+        uint64_t last_size = (last == n_chunks - 1) ? N - last * kPoolChunk : (uint64_t) kPoolChunk;
+        total_local = (owned - 1) * kPoolChunk + last_size;
+    }
+    if (threadIdx.x == 0) {
+        for (int c = 0; c < 8; ++c) { ps->head[c] = 0; ps->tail[c] = 0; }
+        ps->tail[C_START] = (unsigned) P;                 // every slot begins in START with no path to finish
+        ps->next_local = 0;
+        ps->total_local = (unsigned) total_local;
+        ps->retired = 0;
+        ps->error = 0;
+    }
+    for (int i = threadIdx.x; i < C_COUNT * P; i += blockDim.x) ring[i] = (uint16_t) (i < P ? i : kRingEmpty);
+    for (int s = threadIdx.x; s < P; s += blockDim.x) pm.su(L::F_LANE, s, kNoLane);
+    __syncthreads();
+
+    Counters cnt = { 0, 0, 0, 0, 0 };
+    unsigned long long n_samples = 0;
+    double dacc[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) dacc[c] = 0.0;
+    const float scale_x = 1.f / (float) sn.crop_width, scale_y = 1.f / (float) sn.crop_height;
+    const float offset_x = -(float) sn.crop_offset_x * scale_x, offset_y = -(float) sn.crop_offset_y * scale_y;
+
+    // integrator.cpp:323-340 (lane -> pixel) + render_sample :1139-1170 (film position, sensor ray)
+    auto start = [&](uint64_t lane, Pcg32 &rng, float &sx, float &sy) -> Ray {
+        rng.seed_lane(lp.seed_value, (uint32_t) lane);
+        uint32_t idx = (uint32_t) (lane / lp.spp);
+        uint32_t py = idx / (uint32_t) sn.crop_width, px = idx - (uint32_t) sn.crop_width * py;
+        float posx = (float) ((int) px + sn.crop_offset_x), posy = (float) ((int) py + sn.crop_offset_y);
+        float jx = rng.next(), jy = rng.next();
+        sx = posx + jx; sy = posy + jy;
+        float ax = fma_(sx, scale_x, offset_x), ay = fma_(sy, scale_y, offset_y);
+        float apx = .5f, apy = .5f;
+        if (sn.needs_aperture_sample) { apx = rng.next(); apy = rng.next(); }
+        return sensor_ray(sc, ax, ay, apx, apy);
+    };
+    // Film / render_1 accumulation of one finished sample (imageblock.cpp:206-232 box put)
+    auto finish = [&](uint64_t lane, float *R) {
+        n_samples++;
+        Pcg32 tmp;
+        float sx, sy;
+        Ray ray0 = start(lane, tmp, sx, sy);           // film position and sensor ray are functions of the lane only
+        float aov[C];
+        if constexpr (SPEC == MIB_SPEC_RGB) { aov[0] = R[0]; aov[1] = R[1]; aov[2] = R[2]; aov[3] = 1.f; }
+        else if constexpr (SPEC == MIB_SPEC_MONO) { aov[0] = R[0]; aov[1] = 1.f; }
+        else { to_sensor_stokes(ray0, R); aov[0] = R[0]; aov[1] = R[1]; aov[2] = R[2]; aov[3] = R[3]; }
+        if (lp.mode == 2) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) lp.per_sample[(lane - lp.lane_begin) * C + c] = aov[c];
+            return;
+        }
+        if (lp.mode == 0 && sn.rfilter != MIB_RFILTER_BOX) {
+            filter_footprint(sc, lp.spp, sx, sy, [&](size_t pixel, float w) {
+#pragma unroll
+                for (int c = 0; c < C; ++c) atomicAdd(lp.film + pixel * C + c, aov[c] * w);
+            });
+            return;
+        }
+        int ix = (int) floorf(sx) - sn.crop_offset_x, iy = (int) floorf(sy) - sn.crop_offset_y;
+        if ((uint32_t) ix >= (uint32_t) sn.crop_width || (uint32_t) iy >= (uint32_t) sn.crop_height) return;
+        if (lp.mode == 1) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) dacc[c] += (double) aov[c];
+        } else {
+            size_t pixel = (size_t) iy * sn.crop_width + ix;
+            if constexpr (C == 2) atomicAdd(reinterpret_cast<float2 *>(lp.film) + pixel, make_float2(aov[0], aov[1]));
+            else atomicAdd(reinterpret_cast<float4 *>(lp.film) + pixel, make_float4(aov[0], aov[1], aov[2], aov[3]));
+        }
+    };
+
+    unsigned idle_spins = 0;
+    while (true) {
+        // ---- 1. claim a batch ----
+        int cls = -1;
+        unsigned base = 0, n = 0;
+        if (lane_id == 0) {
+            while (true) {
+                unsigned best_n = 0, best_h = 0;
+                int best = -1;
+#pragma unroll
+                for (int c = 0; c < C_COUNT; ++c) {
+                    unsigned h = *(volatile unsigned *) &ps->head[c], t = *(volatile unsigned *) &ps->tail[c];
+                    unsigned a = t - h;
+                    if (a > best_n) { best_n = a; best = c; best_h = h; }
+                }
+                if (best >= 0) {
+                    unsigned take = best_n < 32u ? best_n : 32u;
+                    if (atomicCAS(&ps->head[best], best_h, best_h + take) == best_h) { cls = best; base = best_h; n = take; break; }
+                    continue;
+                }
+                if (*(volatile unsigned *) &ps->retired >= (unsigned) P || *(volatile unsigned *) &ps->error) break;
+                __nanosleep(100);
+                if (++idle_spins > kPoolSpinLimit) { ps->error = 1; break; }
+            }
+        }
+        cls = __shfl_sync(FULL, cls, 0);
+        base = __shfl_sync(FULL, base, 0);
+        n = __shfl_sync(FULL, n, 0);
+        if (cls < 0) break;
+        const bool has = lane_id < n;
+        int slot = 0;
+        if (has) {
+            unsigned pos = (base + lane_id) % (unsigned) P;
+            unsigned v, sp = 0;
+            while ((v = ring[cls * P + pos]) == kRingEmpty) {
+                if (++sp > kPoolSpinLimit) { ps->error = 2; v = 0; break; }
+            }
+            ring[cls * P + pos] = (uint16_t) kRingEmpty;
+            slot = (int) v;
+        }
+        __threadfence_block();
+
+        // ---- 2.-3. run the stage ----
+        int next = -1;
+        switch (cls) {
+        case C_START: {
+            // finish the path that ended in this slot, then start the CTA's next lane in it
+            if (has) {
+                uint32_t j = pm.u(L::F_LANE, slot);
+                if (j != kNoLane) {
+                    float R[NR];
+#pragma unroll
+                    for (int r = 0; r < NR; ++r) R[r] = pm.f(L::F_R + r, slot);
+                    finish(lp.lane_begin + pool_lane(j, blockIdx.x, gridDim.x), R);
+                }
+            }
+            unsigned b0 = 0;
+            if (lane_id == 0) b0 = atomicAdd(&ps->next_local, n);
+            b0 = __shfl_sync(FULL, b0, 0);
+            if (has) {
+                uint32_t j = b0 + lane_id;
+                if (j < ps->total_local) {
+                    Pcg32 rng;
+                    float sx, sy;
+                    Ray ray0 = start(lp.lane_begin + pool_lane(j, blockIdx.x, gridDim.x), rng, sx, sy);
+                    WalkState<SPEC> st;
+                    walk_init<SPEC>(sc, rng, ray0, st);
+                    pm.store_rng(slot, rng);
+                    pm.su(L::F_LANE, slot, j);
+                    pm.su(L::F_DEPTH, slot, 0u);
+                    pm.su(L::F_FLAGS, slot, st.channel | (st.specular_chain ? FL_SPEC_CHAIN : 0u) | FL_NEEDS_INT |
+                                                ((uint32_t) (st.medium + 1) << 8));
+                    pm.sf(L::F_ETA, slot, 1.f);
+                    pm.sf(L::F_LASTPDF, slot, 1.f);
+                    pm.sv3(L::F_RAY, slot, ray0.o); pm.sv3(L::F_RAY + 3, slot, ray0.d); pm.sf(L::F_RAY + 6, slot, ray0.maxt);
+                    pm.store_si(L::F_SI, slot, st.si);
+#pragma unroll
+                    for (int i = 0; i < NT; ++i) pm.sf(L::F_T + i, slot, st.T[i]);
+#pragma unroll
+                    for (int r = 0; r < NR; ++r) pm.sf(L::F_R + r, slot, 0.f);
+                    next = C_MAIN;
+                } else {
+                    pm.su(L::F_LANE, slot, kNoLane);
+                    atomicAdd(&ps->retired, 1u);
+                }
+            }
+            break;
+        }
+        case C_MAIN: {
+            if (has) {
+                WalkState<SPEC> st;
+                Pcg32 rng;
+                pm.load_rng(slot, rng);
+                uint32_t fl = pm.u(L::F_FLAGS, slot);
+                st.depth = pm.u(L::F_DEPTH, slot);
+                st.channel = fl & FL_CHANNEL;
+                st.specular_chain = fl & FL_SPEC_CHAIN;
+                st.needs_intersection = fl & FL_NEEDS_INT;
+                st.medium = (int) fl_medium(fl) - 1;
+                st.eta = pm.f(L::F_ETA, slot);
+                st.last_pdf = pm.f(L::F_LASTPDF, slot);
+                st.ray.o = pm.v3f(L::F_RAY, slot); st.ray.d = pm.v3f(L::F_RAY + 3, slot); st.ray.maxt = pm.f(L::F_RAY + 6, slot);
+                pm.load_si(L::F_SI, slot, st.si);
+                if (!st.needs_intersection && st.si.shape >= 0) si_finalize(sc, st.ray.d, st.si);
+#pragma unroll
+                for (int i = 0; i < NT; ++i) st.T[i] = pm.f(L::F_T + i, slot);
+#pragma unroll
+                for (int r = 0; r < NR; ++r) st.R[r] = pm.f(L::F_R + r, slot);
+                float u[NC];
+                bool T_dirty = false, R_dirty = false;
+                int ev = EV_NULL;
+                for (int it = 0; it < kPoolMainIters && ev == EV_NULL; ++it)
+                    ev = stg_main<SPEC, AOS>(sc, rng, cnt, st, u, T_dirty, R_dirty);
+                pm.store_rng_state(slot, rng);
+                if (T_dirty) {
+#pragma unroll
+                    for (int i = 0; i < NT; ++i) pm.sf(L::F_T + i, slot, st.T[i]);
+                }
+                if (R_dirty) {
+#pragma unroll
+                    for (int r = 0; r < NR; ++r) pm.sf(L::F_R + r, slot, st.R[r]);
+                }
+                if (ev == EV_DONE) next = C_START;
+                else {
+                    pm.su(L::F_DEPTH, slot, st.depth);
+                    fl = (fl & ~(FL_NEEDS_INT | FL_NEE_ACTIVE | FL_NEE_NEEDS_INT | FL_NEE_MULW | FL_NEE_SURFACE | 0xff0000u)) |
+                         (st.needs_intersection ? FL_NEEDS_INT : 0u);
+                    pm.sv3(L::F_RAY, slot, st.ray.o); pm.sf(L::F_RAY + 6, slot, st.ray.maxt);
+                    pm.store_si(L::F_SI, slot, st.si);
+                    if (ev == EV_NULL) next = C_MAIN;
+                    else if (ev == EV_SCATTER) {
+                        pm.sv3(L::F_SCP, slot, st.scatter_p);
+#pragma unroll
+                        for (int c = 0; c < NC; ++c) pm.sf(L::F_NEV + c, slot, u[c]);
+                        next = C_SCAT;
+                    } else if (ev == EV_NEE) {
+                        const NeeState<SPEC> &ns = st.nee;
+                        pm.sv3(L::F_NRAY, slot, ns.ray.o); pm.sv3(L::F_NRAY + 3, slot, ns.ray.d);
+                        pm.store_si(L::F_NSI, slot, ns.si);
+                        pm.sv3(L::F_NED, slot, ns.emitter_d);
+#pragma unroll
+                        for (int c = 0; c < NC; ++c) { pm.sf(L::F_NTR + c, slot, ns.tr[c]); pm.sf(L::F_NEV + c, slot, ns.ev[c]); }
+                        pm.sf(L::F_NDIST, slot, ns.total_dist); pm.sf(L::F_NDIST + 1, slot, ns.max_dist); pm.sf(L::F_NDIST + 2, slot, ns.ds_dist);
+#pragma unroll
+                        for (int r = 0; r < NR; ++r) pm.sf(L::F_NA + r, slot, ns.a[r]);
+                        pm.sf(L::F_NW, slot, ns.w);
+                        fl |= (ns.active ? FL_NEE_ACTIVE : 0u) | (ns.needs_intersection ? FL_NEE_NEEDS_INT : 0u) |
+                              (ns.mul_w_after ? FL_NEE_MULW : 0u) | FL_NEE_SURFACE | ((uint32_t) (ns.medium + 1) << 16);
+                        next = C_NEE;
+                    } else next = C_BSDF;
+                    pm.su(L::F_FLAGS, slot, fl);
+                }
+            }
+            break;
+        }
+        case C_SCAT: {
+            if (has) {
+                WalkState<SPEC> st;
+                Pcg32 rng;
+                pm.load_rng(slot, rng);
+                uint32_t fl = pm.u(L::F_FLAGS, slot);
+                st.medium = (int) fl_medium(fl) - 1;
+                st.channel = fl & FL_CHANNEL;
+                st.ray.d = pm.v3f(L::F_RAY + 3, slot);
+                st.scatter_p = pm.v3f(L::F_SCP, slot);
+#pragma unroll
+                for (int i = 0; i < NT; ++i) st.T[i] = pm.f(L::F_T + i, slot);
+                float u[NC];
+#pragma unroll
+                for (int c = 0; c < NC; ++c) u[c] = pm.f(L::F_NEV + c, slot);
+                bool nee = stg_scatter<SPEC, AOS>(sc, rng, st, u);
+#pragma unroll
+                for (int i = 0; i < NT; ++i) pm.sf(L::F_T + i, slot, st.T[i]);
+                fl = (fl & ~(FL_SPEC_CHAIN | FL_NEE_ACTIVE | FL_NEE_NEEDS_INT | FL_NEE_MULW | FL_NEE_SURFACE | 0xff0000u)) |
+                     (st.specular_chain ? FL_SPEC_CHAIN : 0u);
+                if (nee) {
+                    const NeeState<SPEC> &ns = st.nee;
+                    pm.store_rng_state(slot, rng);
+                    pm.sv3(L::F_NRAY, slot, ns.ray.o); pm.sv3(L::F_NRAY + 3, slot, ns.ray.d);
+                    pm.store_si(L::F_NSI, slot, ns.si);
+                    pm.sv3(L::F_NED, slot, ns.emitter_d);
+#pragma unroll
+                    for (int c = 0; c < NC; ++c) { pm.sf(L::F_NTR + c, slot, ns.tr[c]); pm.sf(L::F_NEV + c, slot, ns.ev[c]); }
+                    pm.sf(L::F_NDIST, slot, ns.total_dist); pm.sf(L::F_NDIST + 1, slot, ns.max_dist); pm.sf(L::F_NDIST + 2, slot, ns.ds_dist);
+#pragma unroll
+                    for (int r = 0; r < NR; ++r) pm.sf(L::F_NA + r, slot, ns.a[r]);
+                    pm.sf(L::F_NW, slot, ns.w);
+                    fl |= (ns.active ? FL_NEE_ACTIVE : 0u) | (ns.needs_intersection ? FL_NEE_NEEDS_INT : 0u) |
+                          (ns.mul_w_after ? FL_NEE_MULW : 0u) | ((uint32_t) (ns.medium + 1) << 16);
+                    next = C_NEE;
+                } else next = C_PHASE;
+                pm.su(L::F_FLAGS, slot, fl);
+            }
+            break;
+        }
+        case C_NEE: {
+            if (has) {
+                NeeState<SPEC> ns;
+                Pcg32 rng;
+                pm.load_rng(slot, rng);
+                uint32_t fl = pm.u(L::F_FLAGS, slot);
+                const uint32_t channel = fl & FL_CHANNEL;
+                ns.active = fl & FL_NEE_ACTIVE;
+                ns.needs_intersection = fl & FL_NEE_NEEDS_INT;
+                ns.medium = (int) fl_nee_medium(fl) - 1;
+                ns.ray.o = pm.v3f(L::F_NRAY, slot); ns.ray.d = pm.v3f(L::F_NRAY + 3, slot); ns.ray.maxt = 0.f;
+                pm.load_si(L::F_NSI, slot, ns.si);
+                if (!ns.needs_intersection && ns.si.shape >= 0) si_finalize(sc, ns.ray.d, ns.si);
+                ns.emitter_d = pm.v3f(L::F_NED, slot);
+#pragma unroll
+                for (int c = 0; c < NC; ++c) ns.tr[c] = pm.f(L::F_NTR + c, slot);
+                ns.total_dist = pm.f(L::F_NDIST, slot); ns.max_dist = pm.f(L::F_NDIST + 1, slot); ns.ds_dist = pm.f(L::F_NDIST + 2, slot);
+                for (int it = 0; it < kPoolNeeIters && ns.active; ++it) nee_step<SPEC, AOS>(sc, rng, cnt, channel, ns);
+                pm.store_rng_state(slot, rng);
+                if (ns.active) {
+                    pm.sv3(L::F_NRAY, slot, ns.ray.o); pm.sv3(L::F_NRAY + 3, slot, ns.ray.d);
+                    pm.store_si(L::F_NSI, slot, ns.si);
+#pragma unroll
+                    for (int c = 0; c < NC; ++c) pm.sf(L::F_NTR + c, slot, ns.tr[c]);
+                    pm.sf(L::F_NDIST, slot, ns.total_dist);
+                    fl = (fl & ~(FL_NEE_NEEDS_INT | 0xff0000u)) | (ns.needs_intersection ? FL_NEE_NEEDS_INT : 0u) |
+                         ((uint32_t) (ns.medium + 1) << 16);
+                    pm.su(L::F_FLAGS, slot, fl);
+                    next = C_NEE;
+                } else {
+#pragma unroll
+                    for (int c = 0; c < NC; ++c) ns.ev[c] = pm.f(L::F_NEV + c, slot);
+#pragma unroll
+                    for (int r = 0; r < NR; ++r) ns.a[r] = pm.f(L::F_NA + r, slot);
+                    ns.w = pm.f(L::F_NW, slot);
+                    ns.mul_w_after = fl & FL_NEE_MULW;
+                    float R[NR];
+#pragma unroll
+                    for (int r = 0; r < NR; ++r) R[r] = pm.f(L::F_R + r, slot);
+                    nee_finish<SPEC>(ns, R);
+#pragma unroll
+                    for (int r = 0; r < NR; ++r) pm.sf(L::F_R + r, slot, R[r]);
+                    next = (fl & FL_NEE_SURFACE) ? C_BSDF : C_PHASE;
+                }
+            }
+            break;
+        }
+        case C_PHASE: {
+            if (has) {
+                WalkState<SPEC> st;
+                Pcg32 rng;
+                pm.load_rng(slot, rng);
+                uint32_t fl = pm.u(L::F_FLAGS, slot);
+                st.medium = (int) fl_medium(fl) - 1;
+                st.channel = fl & FL_CHANNEL;
+                st.needs_intersection = fl & FL_NEEDS_INT;
+                st.ray.o = pm.v3f(L::F_RAY, slot); st.ray.d = pm.v3f(L::F_RAY + 3, slot); st.ray.maxt = pm.f(L::F_RAY + 6, slot);
+                st.scatter_p = pm.v3f(L::F_SCP, slot);
+                st.last_pdf = pm.f(L::F_LASTPDF, slot);
+#pragma unroll
+                for (int i = 0; i < NT; ++i) st.T[i] = pm.f(L::F_T + i, slot);
+                stg_phase<SPEC, AOS>(sc, rng, st);
+                pm.store_rng_state(slot, rng);
+#pragma unroll
+                for (int i = 0; i < NT; ++i) pm.sf(L::F_T + i, slot, st.T[i]);
+                pm.sv3(L::F_RAY, slot, st.ray.o); pm.sv3(L::F_RAY + 3, slot, st.ray.d); pm.sf(L::F_RAY + 6, slot, st.ray.maxt);
+                pm.sf(L::F_LASTPDF, slot, st.last_pdf);
+                pm.su(L::F_FLAGS, slot, (fl & ~FL_NEEDS_INT) | (st.needs_intersection ? FL_NEEDS_INT : 0u));
+                next = C_MAIN;
+            }
+            break;
+        }
+        default: {   // C_BSDF
+            if (has) {
+                WalkState<SPEC> st;
+                Pcg32 rng;
+                pm.load_rng(slot, rng);
+                uint32_t fl = pm.u(L::F_FLAGS, slot);
+                st.medium = (int) fl_medium(fl) - 1;
+                st.channel = fl & FL_CHANNEL;
+                st.specular_chain = fl & FL_SPEC_CHAIN;
+                st.depth = pm.u(L::F_DEPTH, slot);
+                st.last_pdf = pm.f(L::F_LASTPDF, slot);
+                st.ray.o = pm.v3f(L::F_RAY, slot); st.ray.d = pm.v3f(L::F_RAY + 3, slot); st.ray.maxt = pm.f(L::F_RAY + 6, slot);
+                pm.load_si(L::F_SI, slot, st.si);
+                si_finalize(sc, st.ray.d, st.si);
+#pragma unroll
+                for (int i = 0; i < NT; ++i) st.T[i] = pm.f(L::F_T + i, slot);
+                stg_bsdf<SPEC, AOS>(sc, rng, st);
+                pm.store_rng_state(slot, rng);
+#pragma unroll
+                for (int i = 0; i < NT; ++i) pm.sf(L::F_T + i, slot, st.T[i]);
+                pm.sv3(L::F_RAY, slot, st.ray.o); pm.sv3(L::F_RAY + 3, slot, st.ray.d); pm.sf(L::F_RAY + 6, slot, st.ray.maxt);
+                pm.sf(L::F_LASTPDF, slot, st.last_pdf);
+                pm.su(L::F_DEPTH, slot, st.depth);
+                pm.su(L::F_FLAGS, slot, (fl & ~(FL_NEEDS_INT | FL_SPEC_CHAIN | 0xff00u)) | FL_NEEDS_INT |
+                                            (st.specular_chain ? FL_SPEC_CHAIN : 0u) | ((uint32_t) (st.medium + 1) << 8));
+                next = C_MAIN;
+            }
+            break;
+        }
+        }
+        __threadfence_block();
+
+        // ---- 4. append the slots to their next queues (one atomic per class and warp) ----
+#pragma unroll
+        for (int c = 0; c < C_COUNT; ++c) {
+            unsigned m = __ballot_sync(FULL, next == c);
+            if (m) {
+                int leader = __ffs(m) - 1;
+                unsigned b0 = 0;
+                if ((int) lane_id == leader) b0 = atomicAdd(&ps->tail[c], (unsigned) __popc(m));
+                b0 = __shfl_sync(FULL, b0, leader);
+                if (next == c) {
+                    unsigned pos = (b0 + (unsigned) __popc(m & ((1u << lane_id) - 1u))) % (unsigned) P;
+                    ring[c * P + pos] = (uint16_t) slot;
+                }
+            }
+        }
+    }
+
+    if (lp.mode == 1) {
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            double v = dacc[c];
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+            if (lane_id == 0) atomicAdd(lp.sums + c, v);
+        }
+    }
+    unsigned long long cv[6] = { cnt.n_lookups, cnt.n_real, cnt.n_null, cnt.n_nee_steps, cnt.n_surface, n_samples };
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        unsigned long long v = cv[k];
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+        if (lane_id == 0 && v) atomicAdd(lp.counters + k, v);
+    }
+    if (threadIdx.x == 0 && ps->error) atomicExch((unsigned int *) (lp.counters + 7), ps->error);
+}
+
+template <int SPEC, int MODE> void launch_k_forward_pool(const DScene &sc, const LaunchParams &lp, unsigned blocks, unsigned threads, cudaStream_t st);
+template <int SPEC, int MODE> size_t pool_bytes(int slots);   // dynamic shared memory of a pool of `slots` paths
+
+} // namespace mib

@@ -41,7 +41,7 @@ struct SurfIt {
     float t;
     V3 p, n, wi;
     Frame3 sh;
-    int shape;
+    int shape, face;
 };
 MIB_D bool valid(const SurfIt &si) { return si.t != inf_f(); }
 
@@ -105,7 +105,29 @@ MIB_D float intersect_shape(const DScene &sc, int idx, const Ray &ray, int &face
     }
 }
 
-// Scene::ray_intersect + finalize_surface_interaction (interaction.h:245-255, :464-484)
+// finalize_surface_interaction (interaction.h:245-255, :464-484): n, shading frame and wi as functions of
+// (shape, face, p, ray.d) only -- the pool kernel keeps just those in shared memory and rebuilds the rest.
+MIB_DH void si_finalize(const DScene &sc, V3 ray_d, SurfIt &si) {
+    const mib_shape &s = sc.d.shapes[si.shape];
+    V3 dp_du = v3(0.f);
+    if (s.type == MIB_SHAPE_RECTANGLE) {
+        si.n = v3(s.frame_n[0], s.frame_n[1], s.frame_n[2]);
+        dp_du = v3(s.frame_s[0], s.frame_s[1], s.frame_s[2]);
+    } else if (s.type == MIB_SHAPE_CUBE) {
+        const float *nn = sc.cube_normals[si.shape][si.face];
+        si.n = v3(nn[0], nn[1], nn[2]);
+    } else {
+        si.n = normalize(si.p - v3(s.center[0], s.center[1], s.center[2]));
+    }
+    V3 n = si.n;
+    si.sh.n = n;
+    si.sh.s = normalize(vfma(n, -dot(n, dp_du), dp_du));
+    if (dp_du.x == 0.f && dp_du.y == 0.f && dp_du.z == 0.f) { V3 s2, t2; coordinate_system(n, s2, t2); si.sh.s = s2; }
+    si.sh.t = cross(n, si.sh.s);
+    si.wi = to_local(si.sh, -ray_d);
+}
+
+// Scene::ray_intersect: nearest analytic hit over the (few) shapes of the scene
 MIB_DH void ray_intersect(const DScene &sc, const Ray &ray, SurfIt &si) {
     float best = inf_f();
     int bs = -1, bf = 0;
@@ -116,25 +138,10 @@ MIB_DH void ray_intersect(const DScene &sc, const Ray &ray, SurfIt &si) {
     }
     si.t = best;
     si.shape = bs;
+    si.face = bf;
     if (bs < 0) { si.wi = -ray.d; return; }
-    const mib_shape &s = sc.d.shapes[bs];
     si.p = ray_at(ray, best);
-    V3 dp_du = v3(0.f);
-    if (s.type == MIB_SHAPE_RECTANGLE) {
-        si.n = v3(s.frame_n[0], s.frame_n[1], s.frame_n[2]);
-        dp_du = v3(s.frame_s[0], s.frame_s[1], s.frame_s[2]);
-    } else if (s.type == MIB_SHAPE_CUBE) {
-        const float *nn = sc.cube_normals[bs][bf];
-        si.n = v3(nn[0], nn[1], nn[2]);
-    } else {
-        si.n = normalize(si.p - v3(s.center[0], s.center[1], s.center[2]));
-    }
-    V3 n = si.n;
-    si.sh.n = n;
-    si.sh.s = normalize(vfma(n, -dot(n, dp_du), dp_du));
-    if (dp_du.x == 0.f && dp_du.y == 0.f && dp_du.z == 0.f) { V3 s2, t2; coordinate_system(n, s2, t2); si.sh.s = s2; }
-    si.sh.t = cross(n, si.sh.s);
-    si.wi = to_local(si.sh, -ray.d);
+    si_finalize(sc, ray.d, si);
 }
 
 MIB_D int target_medium(const DScene &sc, const SurfIt &si, V3 d) {              // interaction.h:285-299

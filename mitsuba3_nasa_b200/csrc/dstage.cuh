@@ -1,28 +1,24 @@
-// dstage.cuh -- the forward walks (volpath.cpp:95-450, volpathaos.cpp:61-455) as a per-thread
-// stage machine.
+// dstage.cuh -- the forward walks (volpath.cpp:95-450, volpathaos.cpp:61-455) cut into STAGES.
 //
-// Why: in the reference both the main walk and the shadow (NEE) walk are data-dependent loops
-// and the shadow loop is nested in the main one.  Written that way on a GPU, the 32 lanes of a
-// warp wait for the longest path AND, at every real scatter of any lane, for the longest shadow
-// walk (C3: 7 shadow steps per real scatter on average while 3 of 4 lanes only had a null
-// collision).  Here every thread carries an explicit stage and the kernel runs ONE flat loop:
+// Why: in the reference both the main walk and the shadow (NEE) walk are data-dependent loops,
+// the shadow loop is nested in the main one, and every loop iteration branches into one of
+// {null collision, real scatter, null surface, diffuse surface, path end}.  One thread per
+// path therefore leaves 6-10 of 32 lanes active per warp instruction (profiles/r01_*).
+// The pool kernel (dpool.cuh) keeps the paths of a CTA in shared memory and lets every warp
+// execute ONE stage for 32 paths that all wait for that stage:
 //
-//     IDLE --start lane--> MAIN --real scatter--> NEE_MEDIUM --done--> PHASE --> MAIN
-//                            |  --surface hit---> NEE_SURFACE -done--> BSDF  --> MAIN
-//                            '--path ended--> IDLE (film accumulate, next lane)
+//   START --> MAIN --real scatter--> SCATTER --> NEE --> PHASE --> MAIN
+//               |  --diffuse hit--------------> NEE --> BSDF  --> MAIN
+//               |  --null surface--------------------> BSDF  --> MAIN
+//               '--path ended--> START (film accumulate, next lane)
 //
-// One loop iteration executes, in this order, the blocks main-front / shadow-step / phase /
-// bsdf, each predicated on the thread's stage; a thread whose shadow walk needs one step runs
-// through all blocks in a single iteration (same instruction stream as the nested form), a
-// thread with a long shadow walk just stays in NEE for a few iterations while its neighbours
-// go on with their own paths.  Arithmetic, RNG draw order and all decisions are unchanged
-// (the GPU parity tests compare every lane bit-for-bit against the oracle).
+// The functions below are those stages on a register copy of the path state.  Arithmetic,
+// RNG draw order and every decision are exactly the reference's (dwalk.cuh is the same walk
+// as one straight-line loop; the GPU parity tests compare both against the oracle lane by lane).
 #pragma once
 #include "dwalk.cuh"
 
 namespace mib {
-
-enum { STG_MAIN = 0, STG_NEE_MEDIUM = 1, STG_NEE_SURFACE = 2, STG_PHASE = 3, STG_BSDF = 4 };
 
 // Shadow walk in flight + the contribution waiting for its result.
 template <int SPEC> struct NeeState {
@@ -47,12 +43,13 @@ template <int SPEC> struct WalkState {
     SurfIt si;
     float eta, last_pdf;
     V3 scatter_p;                 // mei.p of the real scatter being processed
-    int medium, scatter_medium;
+    int medium;
     uint32_t depth, channel;
-    int stage;
-    bool active, specular_chain, needs_intersection;
+    bool specular_chain, needs_intersection;
     NeeState<SPEC> nee;
 };
+
+enum { EV_NULL = 0, EV_SCATTER = 1, EV_NEE = 2, EV_BSDF = 3, EV_DONE = 4 };
 
 template <int SPEC>
 MIB_D void walk_init(const DScene &sc, Pcg32 &rng, const Ray &ray, WalkState<SPEC> &st) {
@@ -62,13 +59,11 @@ MIB_D void walk_init(const DScene &sc, Pcg32 &rng, const Ray &ray, WalkState<SPE
     st.ray = ray;
     st.eta = 1.f;
     st.medium = sc.d.sensor.medium;
-    st.active = true;
-    st.stage = STG_MAIN;
     st.specular_chain = !sc.d.integrator.hide_emitters;
     st.needs_intersection = true;
     st.depth = 0; st.channel = 0;
     if (SPEC == MIB_SPEC_RGB) st.channel = (uint32_t) fminf(rng.next() * 3.f, 2.f);
-    st.si.t = inf_f(); st.si.shape = -1; st.si.wi = v3(0.f);
+    st.si.t = inf_f(); st.si.shape = -1; st.si.face = 0; st.si.p = v3(0.f); st.si.wi = v3(0.f);
     st.last_pdf = 1.f;
     st.nee.active = false;
 }
@@ -84,6 +79,13 @@ MIB_D void nee_begin(const DScene &sc, Pcg32 &rng, V3 ref_p, V3 ref_n, bool surf
     sample_emitter_direction<NC>(sc, ref_p, sx, sy, ds, ns.ev);
     ns.emitter_d = AOS ? normalize(ds.d) : ds.d;
     ns.active = true;
+    ns.medium = medium;
+    ns.ds_dist = ds.dist;
+    ns.total_dist = 0.f;
+    ns.max_dist = 0.f;
+    ns.si.t = inf_f(); ns.si.shape = -1; ns.si.face = 0; ns.si.p = v3(0.f);
+    ns.needs_intersection = true;
+    ns.ray.o = ref_p; ns.ray.d = ds.d; ns.ray.maxt = 0.f;
     if (ds.pdf == 0.f) {
 #pragma unroll
         for (int c = 0; c < NC; ++c) ns.ev[c] = 0.f;
@@ -94,13 +96,8 @@ MIB_D void nee_begin(const DScene &sc, Pcg32 &rng, V3 ref_p, V3 ref_n, bool surf
     else {
         ns.ray = spawn_ray_to(ref_p, ref_n, ds.p);
         ns.max_dist = ns.ray.maxt;
-        if (surface_ref && is_medium_transition(sc, *ref_si)) medium = target_medium(sc, *ref_si, ns.ray.d);
+        if (surface_ref && is_medium_transition(sc, *ref_si)) ns.medium = target_medium(sc, *ref_si, ns.ray.d);
     }
-    ns.medium = medium;
-    ns.ds_dist = ds.dist;
-    ns.total_dist = 0.f;
-    ns.si.t = inf_f(); ns.si.shape = -1;
-    ns.needs_intersection = true;
 }
 
 // ---- shadow walk: one iteration (volpath.cpp:374-447 / volpathaos.cpp:347-452) ----
@@ -179,19 +176,273 @@ MIB_D void nee_step(const DScene &sc, Pcg32 &rng, Counters &cnt, uint32_t channe
 
 // ---- shadow walk finished: add the pending contribution ----
 template <int SPEC>
-MIB_D void nee_finish(WalkState<SPEC> &st) {
+MIB_D void nee_finish(const NeeState<SPEC> &ns, float *R) {
     constexpr int NC = ST<SPEC>::NC, NR = ST<SPEC>::NR;
-    const NeeState<SPEC> &ns = st.nee;
     float em[NC];
 #pragma unroll
     for (int c = 0; c < NC; ++c) em[c] = ns.tr[c] * ns.ev[c];
 #pragma unroll
     for (int r = 0; r < NR; ++r) {
         float v = ns.a[r] * emis<SPEC>(em, r);
-        st.R[r] += ns.mul_w_after ? v * ns.w : v;
+        R[r] += ns.mul_w_after ? v * ns.w : v;
     }
 }
 
-#include "dstage_step.inc"
+// ---------------------------------------------------------------------------------------------
+// MAIN: head of one iteration of the reference's while loop (volpath.cpp:121-232 / volpathaos.cpp:85-196)
+// up to the point where the event is known, plus the surface-event setup (emission, NEE start).
+//   EV_NULL    null collision handled, call again
+//   EV_SCATTER real scatter at st.scatter_p; u = albedo factor the SCATTER stage multiplies into T
+//   EV_NEE     diffuse surface: st.nee holds a started shadow walk, then BSDF
+//   EV_BSDF    null surface: BSDF stage next
+//   EV_DONE    path ended
+// T_dirty / R_dirty report whether T / R changed.
+// ---------------------------------------------------------------------------------------------
+template <int SPEC, bool AOS>
+MIB_D int stg_main(const DScene &sc, Pcg32 &rng, Counters &cnt, WalkState<SPEC> &st, float *u_out, bool &T_dirty, bool &R_dirty) {
+    constexpr int NC = ST<SPEC>::NC, NR = ST<SPEC>::NR;
+    const mib_integrator &I = sc.d.integrator;
+    float *T = st.T, *R = st.R;
+    Ray &ray = st.ray;
+    SurfIt &si = st.si;
+    const uint32_t channel = st.channel;
+    const uint32_t maxd = (uint32_t) I.max_depth, rrd = (uint32_t) I.rr_depth;
+
+    bool active = T_any_nonzero<SPEC>(T);
+    float q = fminf(T_max<SPEC>(T) * sqr_(st.eta), .95f);
+    bool perform_rr = st.depth > rrd;
+    if (active) { float u = rng.next(); active = (u < q) || !perform_rr; }
+    if (perform_rr) { T_mul_f<SPEC>(T, rcp_(q)); T_dirty = true; }
+    active = active && st.depth < maxd;
+    if (!active) return EV_DONE;
+
+    bool active_medium = st.medium >= 0, active_surface = !active_medium;
+    bool act_null = false, act_scatter = false, escaped = false, is_spectral = false;
+    MedIt<NC> mei;
+    if (active_medium) {
+        const mib_medium &md = sc.d.media[st.medium];
+        is_spectral = md.has_spectral_extinction != 0;
+        sample_interaction<NC>(sc, st.medium, ray, rng.next(), channel, mei, cnt);
+        if (md.type == MIB_MEDIUM_HOMOGENEOUS && valid(mei)) ray.maxt = mei.t;
+        if (st.needs_intersection) ray_intersect(sc, ray, si);
+        st.needs_intersection = st.needs_intersection && !valid(si);
+        if (si.t < mei.t) mei.t = inf_f();
+        if (is_spectral) {                                               // medium.cpp:99-111
+            float t = fminf(mei.t, si.t) - mei.mint;
+            float trv[NC], ffp[NC];
+            bool surf = si.t < mei.t;
+#pragma unroll
+            for (int c = 0; c < NC; ++c) { trv[c] = exp_(-t * mei.maj[c]); ffp[c] = surf ? trv[c] : trv[c] * mei.maj[c]; }
+            float tr_pdf = ch<NC>(ffp, channel), ip = rcp_(tr_pdf);
+            float u[NC];
+#pragma unroll
+            for (int c = 0; c < NC; ++c) u[c] = tr_pdf > 0.f ? trv[c] * ip : 0.f;
+            T_mul_u<SPEC>(T, u);
+            T_dirty = true;
+        }
+        escaped = !valid(mei);
+        active_medium = valid(mei);
+        if (active_medium) {
+            float u = rng.next();
+            bool null_scatter = u >= __fdiv_rn(ch<NC>(mei.sigma_t, channel), ch<NC>(mei.maj, channel));
+            act_null = null_scatter;
+            act_scatter = !null_scatter;
+            if (is_spectral && act_null) {
+                float mjc = ch<NC>(mei.maj, channel), isn = rcp_(ch<NC>(mei.sigma_n, channel)), u2[NC];
+#pragma unroll
+                for (int c = 0; c < NC; ++c) u2[c] = (mei.sigma_n[c] * mjc) * isn;
+                T_mul_u<SPEC>(T, u2);
+            }
+            if (act_scatter) st.depth += 1;
+        }
+    }
+    // `active` of the reference loop from here on; lanes that hit max_depth finish this iteration and stop
+    const bool still = st.depth < maxd;
+    act_scatter = act_scatter && still;
+    if (act_null) { cnt.n_null++; ray.o = mei.p; si.t = si.t - mei.t; }
+
+    if (act_scatter) {
+        cnt.n_real++;
+        if (is_spectral) {
+            float mjc = ch<NC>(mei.maj, channel), ist = rcp_(ch<NC>(mei.sigma_t, channel));
+#pragma unroll
+            for (int c = 0; c < NC; ++c) u_out[c] = (mei.sigma_s[c] * mjc) * ist;
+        } else {
+#pragma unroll
+            for (int c = 0; c < NC; ++c) u_out[c] = __fdiv_rn(mei.sigma_s[c], mei.sigma_t[c]);
+        }
+        st.scatter_p = mei.p;
+        return EV_SCATTER;
+    }
+    if (active_surface || escaped) {
+        if (st.needs_intersection) ray_intersect(sc, ray, si);
+        if (!AOS) {                                                      // volpath.cpp:258-279
+            bool count_direct = st.depth == 0u || st.specular_chain;
+            int emitter = si_emitter(sc, si);
+            if (emitter >= 0 && !(st.depth == 0u && I.hide_emitters)) {
+                float emitter_pdf = 1.0f;
+                if (!count_direct) emitter_pdf = pdf_emitter_direction(sc, emitter);
+                const mib_emitter &e = sc.d.emitters[emitter];
+                float x[NR];
+                T_col0<SPEC>(T, x);
+                float w = mis_weight<SPEC>(st.last_pdf, emitter_pdf);
+#pragma unroll
+                for (int r = 0; r < NR; ++r) {
+                    float er = e.radiance[NC == 3 ? r : 0];
+                    R[r] += count_direct ? x[r] * er : (x[r] * w) * er;
+                }
+                R_dirty = true;
+            }
+        }
+        if (!valid(si)) return EV_DONE;                                  // active &= (active_surface | active_medium)
+        cnt.n_surface++;
+        const mib_bsdf &bsdf = sc.d.bsdfs[sc.d.shapes[si.shape].bsdf];
+        const bool is_null = bsdf.type == MIB_BSDF_NULL;
+        const uint32_t flags = is_null ? kBsdfNull : kBsdfDiffuseRefl;
+        if ((flags & kBsdfSmooth) && (st.depth + 1 < maxd)) {
+            DirSample<NC> ds;
+            nee_begin<SPEC, AOS>(sc, rng, si.p, si.n, true, &si, st.medium, st.nee, ds);
+            V3 wo = to_local(si.sh, ds.d);
+            bool ok = si.wi.z > 0.f && wo.z > 0.f;
+            float x[NR];
+            T_col0<SPEC>(T, x);
+            float bsdf_pdf = ok ? kInvPi * wo.z : 0.f;
+            float w = AOS ? 1.f : mis_weight<SPEC>(ds.pdf, ds.delta ? 0.f : bsdf_pdf);
+#pragma unroll
+            for (int r = 0; r < NR; ++r) {
+                float bv = ok ? bsdf.reflectance[NC == 3 ? r : 0] * kInvPi * wo.z : 0.f;
+                st.nee.a[r] = AOS ? x[r] * bv : (x[r] * bv) * w;             // (T * depol(bv)) col 0 = T(r,0) * bv
+            }
+            st.nee.mul_w_after = false;
+            st.nee.w = 1.f;
+            return EV_NEE;
+        }
+        return EV_BSDF;
+    }
+    // null collision (or a scatter cut off by max_depth): next iteration, unless the path just ended
+    return (still && active_medium) ? EV_NULL : EV_DONE;
+}
+
+// ---------------------------------------------------------------------------------------------
+// SCATTER: albedo factor, NEE start + phase evaluation toward the emitter (volpath.cpp:206-234 /
+// volpathaos.cpp:170-200).  Returns true when st.nee holds a shadow walk (then PHASE), false -> PHASE directly.
+// ---------------------------------------------------------------------------------------------
+template <int SPEC, bool AOS>
+MIB_D bool stg_scatter(const DScene &sc, Pcg32 &rng, WalkState<SPEC> &st, const float *u) {
+    constexpr int NC = ST<SPEC>::NC, NT = ST<SPEC>::NT;
+    constexpr bool POL = ST<SPEC>::POL;
+    const mib_medium &md = sc.d.media[st.medium];
+    T_mul_u<SPEC>(st.T, u);
+    const bool sample_emitters = md.sample_emitters != 0;
+    st.specular_chain = !sample_emitters;
+    if (!sample_emitters) return false;
+    Frame3 sh = make_frame(st.ray.d);
+    DirSample<NC> ds;
+    nee_begin<SPEC, AOS>(sc, rng, st.scatter_p, v3(0.f), false, nullptr, st.medium, st.nee, ds);
+    V3 wo = to_local(sh, ds.d);
+    float W[NT];
+    float ppdf = phase_eval<SPEC>(sc, md.phase, wo, W);
+    if constexpr (POL) m4_to_world(sh, W, -wo, v3(0.f, 0.f, -1.f));
+    TW_col0<SPEC>(st.T, W, st.nee.a);
+    st.nee.mul_w_after = !AOS;
+    st.nee.w = AOS ? 1.f : mis_weight<SPEC>(ds.pdf, ds.delta ? 0.f : ppdf);
+    return true;
+}
+
+// ---- PHASE: sample the phase function, continue the walk (volpath.cpp:236-256 / volpathaos.cpp:202-218) ----
+template <int SPEC, bool AOS>
+MIB_D void stg_phase(const DScene &sc, Pcg32 &rng, WalkState<SPEC> &st) {
+    constexpr int NT = ST<SPEC>::NT;
+    constexpr bool POL = ST<SPEC>::POL;
+    const mib_integrator &I = sc.d.integrator;
+    const bool ltr = I.rng_arg_order == MIB_RNG_ARGS_LEFT_TO_RIGHT;
+    const mib_medium &md = sc.d.media[st.medium];
+    float s1, s2x, s2y;
+    if (ltr) { s1 = rng.next(); s2x = rng.next(); s2y = rng.next(); }
+    else { s2x = rng.next(); s2y = rng.next(); s1 = rng.next(); }
+    (void) s1;
+    V3 wo;
+    float W[NT];
+    Frame3 sh = make_frame(st.ray.d);
+    float ppdf = phase_sample<SPEC>(sc, md.phase, s2x, s2y, wo, W);
+    if constexpr (POL) m4_to_world(sh, W, -wo, v3(0.f, 0.f, -1.f));
+    if (!AOS) T_mul_W<SPEC>(st.T, W);                                    // volpath.cpp:244 (before the pdf test)
+    if (ppdf > 0.f) {
+        if (AOS || I.double_phase_quirk) T_mul_W<SPEC>(st.T, W);         // volpathaos.cpp:211 / volpath.cpp:251
+        st.ray = spawn_ray(st.scatter_p, v3(0.f), to_world(sh, wo));
+        st.needs_intersection = true;
+        st.last_pdf = ppdf;
+    }
+}
+
+// ---- BSDF: sample the surface, continue the walk (volpath.cpp:296-326 / volpathaos.cpp:262-292) ----
+template <int SPEC, bool AOS>
+MIB_D void stg_bsdf(const DScene &sc, Pcg32 &rng, WalkState<SPEC> &st) {
+    constexpr int NC = ST<SPEC>::NC;
+    constexpr bool POL = ST<SPEC>::POL;
+    const mib_integrator &I = sc.d.integrator;
+    const bool ltr = I.rng_arg_order == MIB_RNG_ARGS_LEFT_TO_RIGHT;
+    SurfIt &si = st.si;
+    const mib_bsdf &bsdf = sc.d.bsdfs[sc.d.shapes[si.shape].bsdf];
+    const bool is_null = bsdf.type == MIB_BSDF_NULL;
+    float s1, s2x, s2y;
+    if (ltr) { s1 = rng.next(); s2x = rng.next(); s2y = rng.next(); }
+    else { s2x = rng.next(); s2y = rng.next(); s1 = rng.next(); }
+    (void) s1;
+    V3 wo_l;
+    float bs_pdf;
+    uint32_t sampled;
+    if (is_null) {
+        wo_l = -si.wi; sampled = kBsdfNull; bs_pdf = 1.f;
+        if constexpr (POL) {
+            float b11, b12, b21, b22;
+            null_block(si, b11, b12, b21, b22);
+            m4_mul_right_block(st.T, b11, b12, b21, b22);
+        }
+    } else {
+        wo_l = square_to_cosine_hemisphere(s2x, s2y);
+        bs_pdf = kInvPi * wo_l.z;
+        sampled = kBsdfDiffuseRefl;
+        bool ok = si.wi.z > 0.f && bs_pdf > 0.f;
+        float v[NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) v[c] = ok ? bsdf.reflectance[NC == 3 ? c : 0] : 0.f;
+        T_mul_depol<SPEC>(st.T, v);
+    }
+    st.ray = spawn_ray(si.p, si.n, to_world(si.sh, wo_l));
+    st.needs_intersection = true;
+    bool non_null = !(sampled & kBsdfNull);
+    if (non_null) { st.depth += 1; st.last_pdf = bs_pdf; }
+    st.specular_chain = st.specular_chain || (non_null && (sampled & kBsdfDelta));
+    st.specular_chain = st.specular_chain && !(sampled & kBsdfSmooth);
+    if (is_medium_transition(sc, si)) st.medium = target_medium(sc, si, st.ray.d);
+}
+
+// Whole path through the stage functions in one thread (per-sample dumps of the debug ABI: checks the
+// stage decomposition itself, independent of the pool machinery).
+template <int SPEC, bool AOS>
+MIB_D void trace_path_staged(const DScene &sc, Pcg32 &rng, Counters &cnt, Ray ray, float *R) {
+    constexpr int NC = ST<SPEC>::NC;
+    WalkState<SPEC> st;
+    walk_init<SPEC>(sc, rng, ray, st);
+    while (true) {
+        float u[NC];
+        bool td = false, rd = false;
+        int ev = stg_main<SPEC, AOS>(sc, rng, cnt, st, u, td, rd);
+        if (ev == EV_DONE) break;
+        if (ev == EV_NULL) continue;
+        bool after_bsdf = ev != EV_SCATTER;
+        bool nee = ev == EV_NEE;
+        if (ev == EV_SCATTER) nee = stg_scatter<SPEC, AOS>(sc, rng, st, u);
+        if (nee) {
+            while (st.nee.active) nee_step<SPEC, AOS>(sc, rng, cnt, st.channel, st.nee);
+            nee_finish<SPEC>(st.nee, st.R);
+        }
+        if (after_bsdf) stg_bsdf<SPEC, AOS>(sc, rng, st);
+        else stg_phase<SPEC, AOS>(sc, rng, st);
+    }
+#pragma unroll
+    for (int i = 0; i < ST<SPEC>::NR; ++i) R[i] = st.R[i];
+}
 
 } // namespace mib

@@ -1,5 +1,5 @@
 // inst.cu -- one explicit instantiation of a walk kernel per object file.
-// Compiled as:  nvcc -DINST_FWD -DINST_SPEC=s -DINST_MODE=m   or   nvcc -DINST_ADJ -DINST_SPEC=s   (see Makefile).
+// Compiled as:  nvcc -DINST_FWD|-DINST_POOL -DINST_SPEC=s -DINST_MODE=m   or   nvcc -DINST_ADJ -DINST_SPEC=s   (see Makefile).
 #include "kernels.cuh"
 
 namespace mib {
@@ -7,6 +7,17 @@ namespace mib {
 template <> void launch_k_forward<INST_SPEC, INST_MODE>(const DScene &sc, const LaunchParams &lp, unsigned blocks, cudaStream_t st) {
     k_forward<INST_SPEC, INST_MODE><<<blocks, 128, 0, st>>>(sc, lp);
 }
+#elif defined(INST_POOL)
+template <> void launch_k_forward_pool<INST_SPEC, INST_MODE>(const DScene &sc, const LaunchParams &lp, unsigned blocks, unsigned threads, cudaStream_t st) {
+    static bool configured = false;
+    const size_t smem = pool_smem_bytes<INST_SPEC>((int) lp.pool_slots);
+    if (!configured) {
+        cudaFuncSetAttribute(k_forward_pool<INST_SPEC, INST_MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+        configured = true;
+    }
+    k_forward_pool<INST_SPEC, INST_MODE><<<blocks, threads, smem, st>>>(sc, lp);
+}
+template <> size_t pool_bytes<INST_SPEC, INST_MODE>(int slots) { return pool_smem_bytes<INST_SPEC>(slots); }
 #elif defined(INST_ADJ)
 template <> void launch_k_adjoint<INST_SPEC>(const DScene &sc, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, cudaStream_t st) {
     k_adjoint<INST_SPEC><<<blocks, 128, 0, st>>>(sc, lp, ap);

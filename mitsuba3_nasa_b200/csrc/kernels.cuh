@@ -8,7 +8,6 @@
 // spt chosen by the host the grid is many multiples of 148 SMs x resident CTAs.
 #pragma once
 #include "adjoint.cuh"
-#include "dstage.cuh"
 
 #ifndef MIB_MINB
 #define MIB_MINB 4          // __launch_bounds__(128, MIB_MINB): min resident CTAs per SM (register cap experiments)
@@ -18,9 +17,6 @@
 #endif
 #ifndef MIB_MINB_ADJ
 #define MIB_MINB_ADJ 3
-#endif
-#ifndef MIB_STAGED
-#define MIB_STAGED 0   // 1: stage machine of dstage.cuh (flattened shadow walk), 0: nested shadow walk (dwalk.cuh)
 #endif
 
 namespace mib {
@@ -34,7 +30,8 @@ struct LaunchParams {
     float *film;               // [H*W*C]
     double *sums;              // [4]
     float *per_sample;         // [lanes*C] (mode 2)
-    unsigned long long *counters; // [6]: lookups, real, null, nee_steps, surface, samples
+    unsigned long long *counters; // [8]: lookups, real, null, nee_steps, surface, samples, -, pool error code
+    uint32_t pool_slots;       // k_forward_pool: paths resident per CTA
 };
 
 // launchers defined in inst.cu (one per object file)
@@ -183,43 +180,9 @@ __global__ void __launch_bounds__(128, MIB_MINB) k_forward(const __grid_constant
     };
 
     if constexpr (MODE <= 1) {
-#if MIB_STAGED == 2
-        // Warp-voting stage machine: every iteration the warp executes the ONE block most of its lanes wait for.
-        WalkState<SPEC> st;
-        st.active = false;
-        Pcg32 rng;
-        Ray ray0;
-        float sx = 0.f, sy = 0.f;
-        uint64_t lane = l0, cur = l0;
-        while (true) {
-            if (!st.active && lane < l1) {
-                cur = lane++;
-                ray0 = start(cur, rng, sx, sy);
-                walk_init<SPEC>(sc, rng, ray0, st);
-            }
-            // stage classes: 0 main-front, 1 shadow step, 2 phase sampling, 3 bsdf sampling
-            int cls = !st.active ? -1 : (st.stage == STG_MAIN ? 0 : (st.stage == STG_PHASE ? 2 : (st.stage == STG_BSDF ? 3 : 1)));
-            unsigned m0 = __ballot_sync(0xffffffffu, cls == 0), m1 = __ballot_sync(0xffffffffu, cls == 1),
-                     m2 = __ballot_sync(0xffffffffu, cls == 2), m3 = __ballot_sync(0xffffffffu, cls == 3);
-            if (!(m0 | m1 | m2 | m3)) break;
-            int c0 = __popc(m0), c1 = __popc(m1), c2 = __popc(m2), c3 = __popc(m3);
-            int best = 0, bc = c0;
-            if (c1 > bc) { best = 1; bc = c1; }
-            if (c2 > bc) { best = 2; bc = c2; }
-            if (c3 > bc) { best = 3; bc = c3; }
-            if (cls == best) {
-                walk_step<SPEC, MODE == 1, true>(sc, rng, cnt, st);
-                if (!st.active) finish(cur, ray0, sx, sy, st.R);
-            }
-        }
-#else
         // Flat loop with lane regeneration: a thread starts its next lane as soon as its current
         // path ends instead of idling until the longest path of the warp is finished.
-#if MIB_STAGED
-        WalkState<SPEC> st;
-#else
         PathState<SPEC> st;
-#endif
         st.active = false;
         Pcg32 rng;
         Ray ray0;
@@ -232,18 +195,10 @@ __global__ void __launch_bounds__(128, MIB_MINB) k_forward(const __grid_constant
             if (!st.active && lane < l1) {
                 cur = lane++;
                 ray0 = start(cur, rng, sx, sy);
-#if MIB_STAGED
-                walk_init<SPEC>(sc, rng, ray0, st);
-#else
                 path_init<SPEC>(sc, rng, ray0, st);
-#endif
             }
             if (st.active) {
-#if MIB_STAGED
-                walk_step<SPEC, MODE == 1>(sc, rng, cnt, st);
-#else
                 path_step<SPEC, MODE == 1>(sc, rng, cnt, st);
-#endif
                 if (!st.active) finish(cur, ray0, sx, sy, st.R);
             }
         }
@@ -253,20 +208,11 @@ __global__ void __launch_bounds__(128, MIB_MINB) k_forward(const __grid_constant
                 if (lane >= l1) break;
                 cur = lane++;
                 ray0 = start(cur, rng, sx, sy);
-#if MIB_STAGED
-                walk_init<SPEC>(sc, rng, ray0, st);
-#else
                 path_init<SPEC>(sc, rng, ray0, st);
-#endif
             }
-#if MIB_STAGED
-            walk_step<SPEC, MODE == 1>(sc, rng, cnt, st);
-#else
             path_step<SPEC, MODE == 1>(sc, rng, cnt, st);
-#endif
             if (!st.active) finish(cur, ray0, sx, sy, st.R);
         }
-#endif
 #endif
     } else {
         for (uint64_t lane = l0; lane < l1; ++lane) {
@@ -438,3 +384,5 @@ static __global__ void k_max(const float *data, size_t n, unsigned int *out_bits
 }
 
 } // namespace mib
+
+#include "dpool.cuh"
