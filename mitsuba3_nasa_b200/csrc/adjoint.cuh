@@ -30,22 +30,22 @@ struct Sink {
     double acc[4];             // [0..2] albedo (per channel), [3] sigma_t
     int medium;
     MIB_D void init() { acc[0] = acc[1] = acc[2] = acc[3] = 0.0; medium = -1; }
-    MIB_D void flush(const DScene &sc) {
+    MIB_D void flush() {
         if (medium >= 0) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) if (acc[k] != 0.0) atomicAdd(sc.grad_scalar + medium * 4 + k, acc[k]);
         }
         acc[0] = acc[1] = acc[2] = acc[3] = 0.0;
     }
-    MIB_D void scalar(const DScene &sc, int m, int k, float v) {
-        if (m != medium) { flush(sc); medium = m; }
+    MIB_D void scalar(int m, int k, float v) {
+        if (m != medium) { flush(); medium = m; }
         acc[k] += (double) v;
     }
 };
 
 // d(loss) += coeff[c] * d(volume value at the taps, channel c)
 template <int NC>
-MIB_D void sink_volume(const DScene &sc, Sink &sink, const mib_volume &v, int medium, bool is_albedo, const GridTaps &taps, const float *coeff) {
+MIB_D void sink_volume(Sink &sink, const mib_volume &v, int medium, bool is_albedo, const GridTaps &taps, const float *coeff) {
     if (v.type == MIB_VOLUME_GRID) {
         float *g = sc.grad[v.buffer];
         if (!g) return;
@@ -65,7 +65,7 @@ MIB_D void sink_volume(const DScene &sc, Sink &sink, const mib_volume &v, int me
         }
     } else {
 #pragma unroll
-        for (int c = 0; c < NC; ++c) sink.scalar(sc, medium, is_albedo ? (v.channels == 1 ? 0 : c) : 3, coeff[c]);
+        for (int c = 0; c < NC; ++c) sink.scalar(medium, is_albedo ? (v.channels == 1 ? 0 : c) : 3, coeff[c]);
     }
 }
 
@@ -75,7 +75,7 @@ MIB_D void sink_volume(const DScene &sc, Sink &sink, const mib_volume &v, int me
 // entry in polarized mode), dl = adjoint radiance (per channel / Stokes column).
 // ---------------------------------------------------------------------------
 template <int SPEC, bool AOS>
-MIB_D void prb_sample_emitter(const DScene &sc, Pcg32 &rng, Counters &cnt, V3 ref_p, V3 ref_n, const SurfIt *ref_si,
+MIB_D void prb_sample_emitter(Pcg32 &rng, Counters &cnt, V3 ref_p, V3 ref_n, const SurfIt *ref_si,
                               int medium, uint32_t channel, DirSample<ST<SPEC>::NC> &ds, float *emitted,
                               bool backward, Sink &sink, const float *adj, const float *dl) {
     constexpr int NC = ST<SPEC>::NC;
@@ -83,10 +83,10 @@ MIB_D void prb_sample_emitter(const DScene &sc, Pcg32 &rng, Counters &cnt, V3 re
 #pragma unroll
     for (int c = 0; c < NC; ++c) tr[c] = 1.f;
     float sx = rng.next(), sy = rng.next();
-    sample_emitter_direction<NC>(sc, ref_p, sx, sy, ds, ev);
+    sample_emitter_direction<NC>(ref_p, sx, sy, ds, ev);
     bool active = true;
     if (ds.pdf == 0.f) { for (int c = 0; c < NC; ++c) ev[c] = 0.f; active = false; }
-    if (!AOS && ref_si && is_medium_transition(sc, *ref_si)) medium = target_medium(sc, *ref_si, ds.d);
+    if (!AOS && ref_si && is_medium_transition(*ref_si)) medium = target_medium(*ref_si, ds.d);
     V3 emitter_d = normalize(ds.d);
     Ray ray = spawn_ray(ref_p, ref_n, ds.d);
     float total_dist = 0.f;
@@ -99,7 +99,7 @@ MIB_D void prb_sample_emitter(const DScene &sc, Pcg32 &rng, Counters &cnt, V3 re
         ray.maxt = remaining;
         active = remaining > 0.f;
         if (!active) break;
-        if (needs_intersection) ray_intersect(sc, ray, si);
+        if (needs_intersection) ray_intersect(ray, si);
         needs_intersection = false;
         bool active_medium = medium >= 0, active_surface = !active_medium;
         float trm[NC];
@@ -117,9 +117,9 @@ MIB_D void prb_sample_emitter(const DScene &sc, Pcg32 &rng, Counters &cnt, V3 re
             cnt.n_nee_steps++;
             bool analytic = sc.prb_homog && is_h;
             if (AOS && sc.prb_homog) {
-                sample_interaction<NC>(sc, medium, ray, .5f, channel, mei, cnt, &taps);     // no sampler draw (prb_volpathaos.py:422)
+                sample_interaction<NC>(medium, ray, .5f, channel, mei, cnt, &taps);     // no sampler draw (prb_volpathaos.py:422)
             } else {
-                sample_interaction<NC>(sc, medium, ray, rng.next(), channel, mei, cnt, &taps);
+                sample_interaction<NC>(medium, ray, rng.next(), channel, mei, cnt, &taps);
                 if (si.t < mei.t) mei.t = inf_f();
             }
             if (analytic) {
@@ -139,7 +139,7 @@ MIB_D void prb_sample_emitter(const DScene &sc, Pcg32 &rng, Counters &cnt, V3 re
             ray.o = mei.p;
             si.t = si.t - mei.t;
 #pragma unroll
-            for (int c = 0; c < NC; ++c) trm[c] *= __fdiv_rn(mei.sigma_n[c], mei.maj[c]);
+            for (int c = 0; c < NC; ++c) trm[c] *= div_(mei.sigma_n[c], mei.maj[c]);
         }
         active_surface = (active_surface || escaped) && valid(si) && !active_medium;
         float cs1 = 1.f, cs2 = 1.f, cs0 = 1.f, cs3 = 1.f;      // column sums of the surface Mueller matrix (AOS backward)
@@ -175,21 +175,21 @@ MIB_D void prb_sample_emitter(const DScene &sc, Pcg32 &rng, Counters &cnt, V3 re
                         any = true;
                     } else if (active_medium && het_step) {
                         float s = ((dl[0] + dl[1]) + dl[2]) + dl[3];
-                        cf[0] = __fdiv_rn((s * adj[0]) * (-md_scale), mei.maj[0]);
+                        cf[0] = div_((s * adj[0]) * (-md_scale), mei.maj[0]);
                         any = true;
                     }
                 }
             } else {
 #pragma unroll
                 for (int c = 0; c < NC; ++c) {
-                    float g = trm[c] > 0.f ? __fdiv_rn(dl[c] * adj[c], trm[c]) : 0.f;
+                    float g = trm[c] > 0.f ? div_(dl[c] * adj[c], trm[c]) : 0.f;
                     if (homog) cf[c] = (g * (-t_h * md_scale)) * trm[c];
-                    else if (active_medium) cf[c] = __fdiv_rn(g * (-md_scale), mei.maj[c]);
+                    else if (active_medium) cf[c] = div_(g * (-md_scale), mei.maj[c]);
                     else cf[c] = 0.f;
                     any = any || cf[c] != 0.f;
                 }
             }
-            if (any) sink_volume<NC>(sc, sink, sc.d.media[medium].sigma_t, medium, false, taps, cf);
+            if (any) sink_volume<NC>(sink, sc.d.media[medium].sigma_t, medium, false, taps, cf);
         }
 #pragma unroll
         for (int c = 0; c < NC; ++c) tr[c] *= trm[c];
@@ -201,7 +201,7 @@ MIB_D void prb_sample_emitter(const DScene &sc, Pcg32 &rng, Counters &cnt, V3 re
         for (int c = 0; c < NC; ++c) any_tr = any_tr || tr[c] != 0.f;
         active = (active_medium || active_surface) && any_tr;
         if (active) total_dist += active_medium ? mei.t : si.t;
-        if (active_surface && is_medium_transition(sc, si)) medium = target_medium(sc, si, ray.d);
+        if (active_surface && is_medium_transition(si)) medium = target_medium(si, ray.d);
     }
 #pragma unroll
     for (int c = 0; c < NC; ++c) emitted[c] = ev[c] * tr[c];

@@ -13,22 +13,42 @@
 namespace mib {
 
 #define MIB_D __device__ __forceinline__
-// Heavy helpers (intersection, medium sampling, plugin dispatch, transcendental polynomials).  Inlined by default:
-// the walk kernels are 190-700 KB of SASS that way and instruction fetch is the top stall reason (ncu:
-// no_instruction), but real calls (-DMIB_HEAVY_NOINLINE: 3x less code, 96-128 registers) pass MedIt / SurfIt / 4x4
-// matrices through the local-memory stack and measured slower on the ALU-bound configs (C2 246 vs 400 Msamples/s,
-// C1 862 vs 1272) and only 6 % faster on the grid config (profiles/r01_ab_variants.md).
-#ifndef MIB_HEAVY_NOINLINE
+// Real subroutines.  The walk kernels are instruction-fetch bound when everything is inlined (190-440 KB of SASS
+// per kernel against a 32 KB L1.5 instruction cache; ncu: stall_no_instruction 5-30x the issue rate,
+// profiles/r01_*).  Helpers that are used from many places are therefore compiled ONCE per kernel as
+// __noinline__ functions with by-value arguments and by-value results: within one translation unit ptxas
+// allocates registers across the call (no ABI spills, no stack traffic), so a call costs CALL + RET + a few moves.
+// Never pass references / pointers to locals into a MIB_SUB function: that would force the local into memory.
+// Four groups, each switchable for A/B runs (-DMIB_SUBS=mask; profiles/r01_ab_variants.md):
+//   1 ARITH  div_ rcp_ sqrt_ rsqrt_ normalize coordinate_system2      2 TRANS  sincos2_ exp_ log_ cbrt_ asin_
+//   4 ROT    stokes_rotation2 world_rotation1 phase_rotation_angles   8 GEOM   ray_intersect2 si_finalize2 sample_interaction2
+#ifndef MIB_SUBS
+#define MIB_SUBS 15
+#endif
+#define MIB_INL static __device__ __forceinline__
+#define MIB_NOI static __device__ __noinline__
+#if MIB_SUBS & 1
+#define MIB_SUB_ARITH MIB_NOI
+#else
+#define MIB_SUB_ARITH MIB_INL
+#endif
+#if MIB_SUBS & 2
+#define MIB_SUB_TRANS MIB_NOI
+#else
+#define MIB_SUB_TRANS MIB_INL
+#endif
+#if MIB_SUBS & 4
+#define MIB_SUB_ROT MIB_NOI
+#else
+#define MIB_SUB_ROT MIB_INL
+#endif
+#if MIB_SUBS & 8
+#define MIB_SUB_GEOM MIB_NOI
+#else
+#define MIB_SUB_GEOM MIB_INL
+#endif
 #define MIB_DH static __device__ __forceinline__
-#else
-#define MIB_DH static __device__ __noinline__
-#endif
-// transcendental polynomials + Stokes rotations (leaf functions, scalar arguments)
-#if !defined(MIB_HEAVY_NOINLINE) || defined(MIB_MATH_INLINE)
 #define MIB_DM static __device__ __forceinline__
-#else
-#define MIB_DM static __device__ __noinline__
-#endif
 
 constexpr float kPi        = 3.14159265358979323846f;
 constexpr float kInvPi     = 0.31830988618379067154f;
@@ -45,15 +65,19 @@ MIB_D float fma_(float a, float b, float c) { return __fmaf_rn(a, b, c); }
 MIB_D float fms_(float a, float b, float c) { return __fmaf_rn(a, b, -c); }
 MIB_D float fnma_(float a, float b, float c) { return __fmaf_rn(-a, b, c); }
 MIB_D float sqr_(float a) { return a * a; }
-MIB_D float rcp_(float a) { return __fdiv_rn(1.f, a); }            // drjit-core op.cpp:1195 (LLVM: 1/x)
-MIB_D float sqrt_(float a) { return __fsqrt_rn(a); }
-MIB_D float rsqrt_(float a) { return __fsqrt_rn(__fdiv_rn(1.f, a)); } // op.cpp:1226 (LLVM: sqrt(1/x))
-MIB_D float safe_sqrt_(float a) { return __fsqrt_rn(fmaxf(a, 0.f)); }
+// IEEE division / square root: ~10 SASS instructions + a slow-path call each when inlined, and the walks contain
+// well over a hundred of them -> one real subroutine each.
+MIB_SUB_ARITH float div_(float a, float b) { return __fdiv_rn(a, b); }
+MIB_SUB_ARITH float rcp_(float a) { return __fdiv_rn(1.f, a); }            // drjit-core op.cpp:1195 (LLVM: 1/x)
+MIB_SUB_ARITH float sqrt_(float a) { return __fsqrt_rn(a); }
+MIB_SUB_ARITH float rsqrt_(float a) { return __fsqrt_rn(__fdiv_rn(1.f, a)); } // op.cpp:1226 (LLVM: sqrt(1/x))
+MIB_D float safe_sqrt_(float a) { return sqrt_(fmaxf(a, 0.f)); }
 MIB_D float mulsign_ad(float v1, float v2) { return v2 >= 0.f ? v1 : -v1; }      // array_router.h:381-387 (diff arrays)
 MIB_D float mulsign_bits(float v1, float v2) { return __int_as_float(__float_as_int(v1) ^ (__float_as_int(v2) & 0x80000000)); }
 
 // ext/drjit/include/drjit/math.h:74-180
-MIB_DM void sincos_(float x, float &s_out, float &c_out) {
+MIB_SUB_TRANS float2 sincos2_(float x) {          // (sin, cos)
+    float s_out, c_out;
     float xa = fabsf(x);
     int j = (int) (xa * 1.2732395447351626862f);
     j = (j + 1) & ~1;
@@ -72,7 +96,9 @@ MIB_DM void sincos_(float x, float &s_out, float &c_out) {
     bool polymask = (j & 2) == 0;
     s_out = mulsign_bits(polymask ? s : c, __int_as_float((int) sign_sin));
     c_out = mulsign_bits(polymask ? c : s, __int_as_float((int) sign_cos));
+    return make_float2(s_out, c_out);
 }
+MIB_D void sincos_(float x, float &s_out, float &c_out) { float2 r = sincos2_(x); s_out = r.x; c_out = r.y; }
 
 MIB_D float ldexp_(float x, float n) { return x * __int_as_float(((int) n + 0x7f) << 23); }  // math.h:610-627
 MIB_D void frexp_(float x, float &mant, float &expo) {                                        // math.h:634-678
@@ -86,7 +112,7 @@ MIB_D void frexp_(float x, float &mant, float &expo) {                          
 }
 
 // math.h:685-747.  estrin with 6 coefficients: level 1 pairs, level 2 on y^2, level 3 on y^4
-MIB_DM float exp_(float x) {
+MIB_SUB_TRANS float exp_(float x) {
     float n = floorf(fma_(1.44269504088896340736f, x, 0.5f));
     float y = fma_(n, -0.693359375f, x);
     y = fma_(n, 2.12194440e-4f, y);
@@ -103,7 +129,7 @@ MIB_DM float exp_(float x) {
 }
 
 // math.h:824-897.  estrin with 9 coefficients
-MIB_DM float log_(float x) {
+MIB_SUB_TRANS float log_(float x) {
     float xm, e;
     frexp_(x, xm, e);
     bool ge = xm >= 0.70710678118654752440f;
@@ -130,7 +156,7 @@ MIB_DM float log_(float x) {
 }
 
 // math.h:1411-1468 (one Newton step in single precision).  estrin with 5 coefficients
-MIB_DM float cbrt_(float x) {
+MIB_SUB_TRANS float cbrt_(float x) {
     const float cbrt2 = 1.25992104989487316477f, cbrt4 = 1.58740105196819947475f, third = (float) (1.0 / 3.0);
     float xa = fabsf(x), xm, xe;
     frexp_(xa, xm, xe);
@@ -147,12 +173,12 @@ MIB_DM float cbrt_(float x) {
     if (rem != 0.f) xm *= f;
     float r = ldexp_(xm, mulsign_bits(xea1, xe));
     r = mulsign_bits(r, x);
-    r -= (r - __fdiv_rn(x, sqr_(r))) * third;
+    r -= (r - div_(x, sqr_(r))) * third;
     return (isfinite(x) && x != 0.f) ? r : x;
 }
 
 // math.h:366-456.  estrin with 5 coefficients
-MIB_DM float asin_(float x) {
+MIB_SUB_TRANS float asin_(float x) {
     float xa = fabsf(x), x2 = x * x;
     bool big = xa > 0.5f;
     float x1 = 0.5f * (1.f - xa);
@@ -183,18 +209,22 @@ MIB_D V3 vfma(V3 a, float b, V3 c) { return v3(fma_(a.x, b, c.x), fma_(a.y, b, c
 MIB_D float dot(V3 a, V3 b) { return fma_(a.z, b.z, fma_(a.y, b.y, a.x * b.x)); }              // array_base.h:603-630
 MIB_D float sqnorm(V3 v) { return fma_(v.z, v.z, fma_(v.y, v.y, v.x * v.x)); }                  // array_router.h:635-644
 MIB_D float norm(V3 v) { return sqrt_(sqnorm(v)); }
-MIB_D V3 normalize(V3 v) { return v * rsqrt_(sqnorm(v)); }
+MIB_SUB_ARITH V3 normalize(V3 v) { return v * rsqrt_(sqnorm(v)); }
 MIB_D V3 cross(V3 a, V3 b) {                                                                     // array_router.h:654-666
     return v3(fms_(a.y, b.z, a.z * b.y), fms_(a.z, b.x, a.x * b.z), fms_(a.x, b.y, a.y * b.x));
 }
 MIB_D float comp(V3 v, int i) { return i == 0 ? v.x : (i == 1 ? v.y : v.z); }
 
 // include/mitsuba/core/vector.h:116-136
-MIB_D void coordinate_system(V3 n, V3 &s, V3 &t) {
+struct V3x2 { V3 a, b; };
+MIB_SUB_ARITH V3x2 coordinate_system2(V3 n) {
     float sign = n.z >= 0.f ? 1.f : -1.f, a = -rcp_(sign + n.z), b = n.x * n.y * a;
-    s = v3(mulsign_ad(sqr_(n.x) * a, n.z) + 1.f, mulsign_ad(b, n.z), n.z >= 0.f ? -n.x : n.x);
-    t = v3(b, fma_(n.y, n.y * a, sign), -n.y);
+    V3x2 r;
+    r.a = v3(mulsign_ad(sqr_(n.x) * a, n.z) + 1.f, mulsign_ad(b, n.z), n.z >= 0.f ? -n.x : n.x);
+    r.b = v3(b, fma_(n.y, n.y * a, sign), -n.y);
+    return r;
 }
+MIB_D void coordinate_system(V3 n, V3 &s, V3 &t) { V3x2 r = coordinate_system2(n); s = r.a; t = r.b; }
 MIB_D V3 stokes_basis(V3 fwd) { V3 s, t; coordinate_system(fwd, s, t); return s; }               // mueller.h:347-350
 
 // include/mitsuba/core/frame.h:17-41

@@ -17,7 +17,7 @@ MIB_D void square_to_uniform_disk_concentric(float sx, float sy, float &ox, floa
     float x = fms_(2.f, sx, 1.f), y = fms_(2.f, sy, 1.f);
     bool is_zero = x == 0.f && y == 0.f, q13 = fabsf(x) < fabsf(y);
     float r = q13 ? y : x, rp = q13 ? x : y;
-    float phi = __fdiv_rn(0.25f * kPi * rp, r);
+    float phi = div_(0.25f * kPi * rp, r);
     if (q13) phi = 0.5f * kPi - phi;
     if (is_zero) phi = 0.f;
     float s, c;
@@ -33,13 +33,13 @@ MIB_D V3 square_to_cosine_hemisphere(float sx, float sy) {                 // wa
 // ---- phase functions: wo local (+z = ray.d), wi = (0,0,-1) ----
 MIB_D float eval_hg(float g, float cos_theta) {                             // hg.cpp:66-71
     float temp = 1.f + sqr_(g) + 2.f * g * cos_theta;
-    return __fdiv_rn(kInvFourPi * (1.f - sqr_(g)), temp * sqrt_(temp));
+    return div_(kInvFourPi * (1.f - sqr_(g)), temp * sqrt_(temp));
 }
 MIB_D float rayleigh_pdf(float c) { return (3.f / 16.f) * kInvPi * (1.f + sqr_(c)); }
 // mueller.h:311-328, scaled matrix
 MIB_D void rayleigh_matrix(float cos_theta, float sin_theta, float rho, float *M) {
-    float r1 = __fdiv_rn(1.f - rho, 1.f + __fdiv_rn(rho, 2.f)), r2 = __fdiv_rn(1.f + rho, 1.f - rho),
-          r3 = __fdiv_rn(1.f - 2.f * rho, 1.f - rho);
+    float r1 = div_(1.f - rho, 1.f + div_(rho, 2.f)), r2 = div_(1.f + rho, 1.f - rho),
+          r3 = div_(1.f - 2.f * rho, 1.f - rho);
     float a = r2 + sqr_(cos_theta), b = 1.f + sqr_(cos_theta), c = -sqr_(sin_theta), d = 2.f * cos_theta;
     float k = (3.f / 16.f) * kInvPi * r1;
 #pragma unroll
@@ -49,7 +49,7 @@ MIB_D void rayleigh_matrix(float cos_theta, float sin_theta, float rho, float *M
 
 // eval_pdf: W = phase value (Mueller in local Stokes frames, or one float replicated), returns pdf
 template <int SPEC>
-MIB_DH float phase_eval(const DScene &sc, int idx, V3 wo, float *W) {
+MIB_DH float phase_eval(int idx, V3 wo, float *W) {
     constexpr bool POL = ST<SPEC>::POL;
     constexpr int NC = ST<SPEC>::NC;
     const mib_phase &p = sc.d.phases[idx];
@@ -71,7 +71,7 @@ MIB_DH float phase_eval(const DScene &sc, int idx, V3 wo, float *W) {
                 m4_phase_rotate(W, wo, wi);
                 return pdf;
             } else {
-                float rho = p.depolarization, r1 = __fdiv_rn(1.f - rho, 1.f + __fdiv_rn(rho, 2.f)), r2 = __fdiv_rn(1.f + rho, 1.f - rho);
+                float rho = p.depolarization, r1 = div_(1.f - rho, 1.f + div_(rho, 2.f)), r2 = div_(1.f + rho, 1.f - rho);
                 val = (3.f / 16.f) * kInvPi * r1 * (r2 + sqr_(ct));
             }
             break;
@@ -98,7 +98,7 @@ MIB_DH float phase_eval(const DScene &sc, int idx, V3 wo, float *W) {
 
 // sample: returns pdf, writes local wo and the weight W
 template <int SPEC>
-MIB_DH float phase_sample(const DScene &sc, int idx, float s2x, float s2y, V3 &wo, float *W) {
+MIB_DH float phase_sample(int idx, float s2x, float s2y, V3 &wo, float *W) {
     constexpr bool POL = ST<SPEC>::POL;
     constexpr int NC = ST<SPEC>::NC;
     const mib_phase &p = sc.d.phases[idx];
@@ -110,8 +110,8 @@ MIB_DH float phase_sample(const DScene &sc, int idx, float s2x, float s2y, V3 &w
             break;
         case MIB_PHASE_HG: {                                                             // hg.cpp:73-94
             float g = p.g;
-            float sqr_term = __fdiv_rn(1.f - sqr_(g), 1.f - g + 2.f * g * s2x);
-            ct = __fdiv_rn(1.f + sqr_(g) - sqr_(sqr_term), 2.f * g);
+            float sqr_term = div_(1.f - sqr_(g), 1.f - g + 2.f * g * s2x);
+            ct = div_(1.f + sqr_(g) - sqr_(sqr_term), 2.f * g);
             if (fabsf(g) < kEps) ct = 1.f - 2.f * s2x;
             float st = safe_sqrt_(1.f - sqr_(ct));
             sincos_(2.f * kPi * s2y, sp, cp);
@@ -134,7 +134,7 @@ MIB_DH float phase_sample(const DScene &sc, int idx, float s2x, float s2y, V3 &w
 #pragma unroll
                 for (int i = 0; i < 16; ++i) W[i] *= ipdf;
             } else {
-                float rho = p.depolarization, r1 = __fdiv_rn(1.f - rho, 1.f + __fdiv_rn(rho, 2.f)), r2 = __fdiv_rn(1.f + rho, 1.f - rho);
+                float rho = p.depolarization, r1 = div_(1.f - rho, 1.f + div_(rho, 2.f)), r2 = div_(1.f + rho, 1.f - rho);
                 float val = (3.f / 16.f) * kInvPi * r1 * (r2 + sqr_(ct));
                 for (int c = 0; c < NC; ++c) W[c] = val * ipdf;
             }
@@ -153,7 +153,7 @@ MIB_DH float phase_sample(const DScene &sc, int idx, float s2x, float s2y, V3 &w
             float st = safe_sqrt_(1.f - ct * ct);
             sincos_(2.f * kPi * s2y, sp, cp);
             wo = v3(st * cp, st * sp, ct);
-            pdf = phase_eval<SPEC>(sc, idx, wo, W);
+            pdf = phase_eval<SPEC>(idx, wo, W);
             float ipdf = rcp_(pdf);
 #pragma unroll
             for (int i = 0; i < ST<SPEC>::NT; ++i) W[i] *= ipdf;
@@ -169,7 +169,7 @@ MIB_DH float phase_sample(const DScene &sc, int idx, float s2x, float s2y, V3 &w
 template <int NC> struct DirSample { V3 p, d; float dist, pdf; bool delta; int emitter; };
 
 template <int NC>
-MIB_DH void sample_emitter_direction(const DScene &sc, V3 ref_p, float sx, float sy, DirSample<NC> &ds, float *spec) {
+MIB_DH void sample_emitter_direction(V3 ref_p, float sx, float sy, DirSample<NC> &ds, float *spec) {
     int n = sc.d.n_emitters;
 #pragma unroll
     for (int c = 0; c < NC; ++c) spec[c] = 0.f;
@@ -207,12 +207,12 @@ MIB_DH void sample_emitter_direction(const DScene &sc, V3 ref_p, float sx, float
         for (int c2 = 0; c2 < NC; ++c2) spec[c2] *= weight;
     }
 }
-MIB_D float pdf_emitter_direction(const DScene &sc, int emitter) {          // scene.cpp:355-366
+MIB_D float pdf_emitter_direction(int emitter) {          // scene.cpp:355-366
     const mib_emitter &e = sc.d.emitters[emitter];
     float pmf = sc.d.n_emitters > 1 ? rcp_((float) sc.d.n_emitters) : 1.f;
     return (e.type == MIB_EMITTER_CONSTANT ? kInvFourPi : 0.f) * pmf;
 }
-MIB_D int si_emitter(const DScene &sc, const SurfIt &si) {
+MIB_D int si_emitter(const SurfIt &si) {
     return valid(si) ? sc.d.shapes[si.shape].emitter : sc.d.environment;
 }
 
@@ -220,12 +220,12 @@ MIB_D int si_emitter(const DScene &sc, const SurfIt &si) {
 constexpr uint32_t kBsdfNull = 0x1, kBsdfDiffuseRefl = 0x2, kBsdfSmooth = 0x2 | 0x4 | 0x8 | 0x10, kBsdfDelta = 0x1 | 0x20 | 0x40;
 
 // ---- sensors ----
-MIB_DH Ray sensor_ray(const DScene &sc, float px, float py, float ax, float ay) {
+MIB_DH Ray sensor_ray(float px, float py, float ax, float ay) {
     const mib_sensor &s = sc.d.sensor;
     Ray ray;
     if (s.type == MIB_SENSOR_PERSPECTIVE) {                                  // perspective.cpp:201-235
-        float ox = __fdiv_rn((float) s.film_width * s.principal_point_offset[0], (float) s.crop_width),
-              oy = __fdiv_rn((float) s.film_height * s.principal_point_offset[1], (float) s.crop_height);
+        float ox = div_((float) s.film_width * s.principal_point_offset[0], (float) s.crop_width),
+              oy = div_((float) s.film_height * s.principal_point_offset[1], (float) s.crop_height);
         V3 near_p = xform_point(s.sample_to_camera, v3(px + ox, py + oy, 0.f));
         V3 d = normalize(near_p);
         ray.o = v3(s.to_world[3], s.to_world[7], s.to_world[11]);

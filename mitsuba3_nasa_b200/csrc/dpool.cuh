@@ -121,7 +121,7 @@ MIB_D uint64_t pool_lane(uint32_t i, uint32_t cta, uint32_t n_cta) {
 }
 
 template <int SPEC, int MODE>
-__global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_constant__ DScene sc, const __grid_constant__ LaunchParams lp) {
+__global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_constant__ LaunchParams lp) {
     using L = PoolL<SPEC>;
     constexpr int C = RawChannels<SPEC>::C, NR = ST<SPEC>::NR, NC = ST<SPEC>::NC, NT = ST<SPEC>::NT;
     constexpr bool AOS = MODE == 1;
@@ -177,7 +177,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
         float ax = fma_(sx, scale_x, offset_x), ay = fma_(sy, scale_y, offset_y);
         float apx = .5f, apy = .5f;
         if (sn.needs_aperture_sample) { apx = rng.next(); apy = rng.next(); }
-        return sensor_ray(sc, ax, ay, apx, apy);
+        return sensor_ray(ax, ay, apx, apy);
     };
     // Film / render_1 accumulation of one finished sample (imageblock.cpp:206-232 box put)
     auto finish = [&](uint64_t lane, float *R) {
@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
             return;
         }
         if (lp.mode == 0 && sn.rfilter != MIB_RFILTER_BOX) {
-            filter_footprint(sc, lp.spp, sx, sy, [&](size_t pixel, float w) {
+            filter_footprint(lp.spp, sx, sy, [&](size_t pixel, float w) {
 #pragma unroll
                 for (int c = 0; c < C; ++c) atomicAdd(lp.film + pixel * C + c, aov[c] * w);
             });
@@ -279,7 +279,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                     float sx, sy;
                     Ray ray0 = start(lp.lane_begin + pool_lane(j, blockIdx.x, gridDim.x), rng, sx, sy);
                     WalkState<SPEC> st;
-                    walk_init<SPEC>(sc, rng, ray0, st);
+                    walk_init<SPEC>(rng, ray0, st);
                     pm.store_rng(slot, rng);
                     pm.su(L::F_LANE, slot, j);
                     pm.su(L::F_DEPTH, slot, 0u);
@@ -316,7 +316,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                 st.last_pdf = pm.f(L::F_LASTPDF, slot);
                 st.ray.o = pm.v3f(L::F_RAY, slot); st.ray.d = pm.v3f(L::F_RAY + 3, slot); st.ray.maxt = pm.f(L::F_RAY + 6, slot);
                 pm.load_si(L::F_SI, slot, st.si);
-                if (!st.needs_intersection && st.si.shape >= 0) si_finalize(sc, st.ray.d, st.si);
+                if (!st.needs_intersection && st.si.shape >= 0) si_finalize(st.ray.d, st.si);
 #pragma unroll
                 for (int i = 0; i < NT; ++i) st.T[i] = pm.f(L::F_T + i, slot);
 #pragma unroll
@@ -325,7 +325,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                 bool T_dirty = false, R_dirty = false;
                 int ev = EV_NULL;
                 for (int it = 0; it < kPoolMainIters && ev == EV_NULL; ++it)
-                    ev = stg_main<SPEC, AOS>(sc, rng, cnt, st, u, T_dirty, R_dirty);
+                    ev = stg_main<SPEC, AOS>(rng, cnt, st, u, T_dirty, R_dirty);
                 pm.store_rng_state(slot, rng);
                 if (T_dirty) {
 #pragma unroll
@@ -383,7 +383,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                 float u[NC];
 #pragma unroll
                 for (int c = 0; c < NC; ++c) u[c] = pm.f(L::F_NEV + c, slot);
-                bool nee = stg_scatter<SPEC, AOS>(sc, rng, st, u);
+                bool nee = stg_scatter<SPEC, AOS>(rng, st, u);
 #pragma unroll
                 for (int i = 0; i < NT; ++i) pm.sf(L::F_T + i, slot, st.T[i]);
                 fl = (fl & ~(FL_SPEC_CHAIN | FL_NEE_ACTIVE | FL_NEE_NEEDS_INT | FL_NEE_MULW | FL_NEE_SURFACE | 0xff0000u)) |
@@ -420,12 +420,12 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                 ns.medium = (int) fl_nee_medium(fl) - 1;
                 ns.ray.o = pm.v3f(L::F_NRAY, slot); ns.ray.d = pm.v3f(L::F_NRAY + 3, slot); ns.ray.maxt = 0.f;
                 pm.load_si(L::F_NSI, slot, ns.si);
-                if (!ns.needs_intersection && ns.si.shape >= 0) si_finalize(sc, ns.ray.d, ns.si);
+                if (!ns.needs_intersection && ns.si.shape >= 0) si_finalize(ns.ray.d, ns.si);
                 ns.emitter_d = pm.v3f(L::F_NED, slot);
 #pragma unroll
                 for (int c = 0; c < NC; ++c) ns.tr[c] = pm.f(L::F_NTR + c, slot);
                 ns.total_dist = pm.f(L::F_NDIST, slot); ns.max_dist = pm.f(L::F_NDIST + 1, slot); ns.ds_dist = pm.f(L::F_NDIST + 2, slot);
-                for (int it = 0; it < kPoolNeeIters && ns.active; ++it) nee_step<SPEC, AOS>(sc, rng, cnt, channel, ns);
+                for (int it = 0; it < kPoolNeeIters && ns.active; ++it) nee_step<SPEC, AOS>(rng, cnt, channel, ns);
                 pm.store_rng_state(slot, rng);
                 if (ns.active) {
                     pm.sv3(L::F_NRAY, slot, ns.ray.o); pm.sv3(L::F_NRAY + 3, slot, ns.ray.d);
@@ -469,7 +469,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                 st.last_pdf = pm.f(L::F_LASTPDF, slot);
 #pragma unroll
                 for (int i = 0; i < NT; ++i) st.T[i] = pm.f(L::F_T + i, slot);
-                stg_phase<SPEC, AOS>(sc, rng, st);
+                stg_phase<SPEC, AOS>(rng, st);
                 pm.store_rng_state(slot, rng);
 #pragma unroll
                 for (int i = 0; i < NT; ++i) pm.sf(L::F_T + i, slot, st.T[i]);
@@ -493,10 +493,10 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                 st.last_pdf = pm.f(L::F_LASTPDF, slot);
                 st.ray.o = pm.v3f(L::F_RAY, slot); st.ray.d = pm.v3f(L::F_RAY + 3, slot); st.ray.maxt = pm.f(L::F_RAY + 6, slot);
                 pm.load_si(L::F_SI, slot, st.si);
-                si_finalize(sc, st.ray.d, st.si);
+                si_finalize(st.ray.d, st.si);
 #pragma unroll
                 for (int i = 0; i < NT; ++i) st.T[i] = pm.f(L::F_T + i, slot);
-                stg_bsdf<SPEC, AOS>(sc, rng, st);
+                stg_bsdf<SPEC, AOS>(rng, st);
                 pm.store_rng_state(slot, rng);
 #pragma unroll
                 for (int i = 0; i < NT; ++i) pm.sf(L::F_T + i, slot, st.T[i]);
@@ -547,7 +547,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
     if (threadIdx.x == 0 && ps->error) atomicExch((unsigned int *) (lp.counters + 7), ps->error);
 }
 
-template <int SPEC, int MODE> void launch_k_forward_pool(const DScene &sc, const LaunchParams &lp, unsigned blocks, unsigned threads, cudaStream_t st);
+template <int SPEC, int MODE> void launch_k_forward_pool(const DScene &scene, const LaunchParams &lp, unsigned blocks, unsigned threads, cudaStream_t st);
 template <int SPEC, int MODE> size_t pool_bytes(int slots);   // dynamic shared memory of a pool of `slots` paths
 
 } // namespace mib

@@ -29,6 +29,11 @@ struct DScene {
     const float *weight_film;                     // [H*W] filter-weight film for the adjoint of non-box filters
 };
 
+// The scene of the running launch.  One copy per translation unit (each kernel instantiation is its own object
+// file); the launchers in inst.cu / mib_api.cu upload it on the launch stream right before the kernel.  Device
+// code anywhere -- inlined or a real subroutine -- reads it through the constant bank (operands like c[0x3][..]).
+static __constant__ DScene sc;
+
 struct Ray { V3 o, d; float maxt; };
 MIB_D V3 ray_at(const Ray &r, float t) { return vfma(r.d, t, r.o); }
 
@@ -65,12 +70,12 @@ MIB_D Ray spawn_ray_to(V3 p, V3 n, V3 target) {
 
 // Analytic intersection.  rectangle: src/shapes/rectangle.cpp:449-470 (+ :497-568, AD branch p = ray(t));
 // cube: slab test in object space; sphere: quadratic in object space.
-MIB_D float intersect_shape(const DScene &sc, int idx, const Ray &ray, int &face) {
+MIB_D float intersect_shape(int idx, const Ray &ray, int &face) {
     const mib_shape &s = sc.d.shapes[idx];
     V3 o = xform_point_affine(s.to_object, ray.o), d = xform_vector(s.to_object, ray.d);
     face = 0;
     if (s.type == MIB_SHAPE_RECTANGLE) {
-        float t = __fdiv_rn(-o.z, d.z);
+        float t = div_(-o.z, d.z);
         float lx = fma_(d.x, t, o.x), ly = fma_(d.y, t, o.y);
         bool hit = t >= 0.f && t <= ray.maxt && fabsf(lx) <= 1.f && fabsf(ly) <= 1.f;
         return hit ? t : inf_f();
@@ -97,7 +102,7 @@ MIB_D float intersect_shape(const DScene &sc, int idx, const Ray &ray, int &face
         if (!(disc >= 0.f)) return inf_f();
         float sq = sqrt_(disc);
         float q = -0.5f * (B + (B >= 0.f ? sq : -sq));
-        float t0 = __fdiv_rn(q, A), t1 = __fdiv_rn(C, q);
+        float t0 = div_(q, A), t1 = div_(C, q);
         if (t0 > t1) { float tt = t0; t0 = t1; t1 = tt; }
         float t = t0 >= 0.f ? t0 : t1;
         if (!(t >= 0.f && t <= ray.maxt)) return inf_f();
@@ -107,14 +112,16 @@ MIB_D float intersect_shape(const DScene &sc, int idx, const Ray &ray, int &face
 
 // finalize_surface_interaction (interaction.h:245-255, :464-484): n, shading frame and wi as functions of
 // (shape, face, p, ray.d) only -- the pool kernel keeps just those in shared memory and rebuilds the rest.
-MIB_DH void si_finalize(const DScene &sc, V3 ray_d, SurfIt &si) {
-    const mib_shape &s = sc.d.shapes[si.shape];
+MIB_SUB_GEOM SurfIt si_finalize2(int shape, int face, float t, V3 p, V3 ray_d) {
+    SurfIt si;
+    si.t = t; si.shape = shape; si.face = face; si.p = p;
+    const mib_shape &s = sc.d.shapes[shape];
     V3 dp_du = v3(0.f);
     if (s.type == MIB_SHAPE_RECTANGLE) {
         si.n = v3(s.frame_n[0], s.frame_n[1], s.frame_n[2]);
         dp_du = v3(s.frame_s[0], s.frame_s[1], s.frame_s[2]);
     } else if (s.type == MIB_SHAPE_CUBE) {
-        const float *nn = sc.cube_normals[si.shape][si.face];
+        const float *nn = sc.cube_normals[shape][face];
         si.n = v3(nn[0], nn[1], nn[2]);
     } else {
         si.n = normalize(si.p - v3(s.center[0], s.center[1], s.center[2]));
@@ -125,30 +132,35 @@ MIB_DH void si_finalize(const DScene &sc, V3 ray_d, SurfIt &si) {
     if (dp_du.x == 0.f && dp_du.y == 0.f && dp_du.z == 0.f) { V3 s2, t2; coordinate_system(n, s2, t2); si.sh.s = s2; }
     si.sh.t = cross(n, si.sh.s);
     si.wi = to_local(si.sh, -ray_d);
+    return si;
 }
+MIB_D void si_finalize(V3 ray_d, SurfIt &si) { si = si_finalize2(si.shape, si.face, si.t, si.p, ray_d); }
 
 // Scene::ray_intersect: nearest analytic hit over the (few) shapes of the scene
-MIB_DH void ray_intersect(const DScene &sc, const Ray &ray, SurfIt &si) {
+MIB_SUB_GEOM SurfIt ray_intersect2(Ray ray) {
     float best = inf_f();
     int bs = -1, bf = 0;
     for (int i = 0; i < sc.d.n_shapes; ++i) {
         int face;
-        float t = intersect_shape(sc, i, ray, face);
+        float t = intersect_shape(i, ray, face);
         if (t < best) { best = t; bs = i; bf = face; }
     }
-    si.t = best;
-    si.shape = bs;
-    si.face = bf;
-    if (bs < 0) { si.wi = -ray.d; return; }
-    si.p = ray_at(ray, best);
-    si_finalize(sc, ray.d, si);
+    if (bs < 0) {
+        SurfIt si;
+        si.t = best; si.shape = -1; si.face = 0;
+        si.p = v3(0.f); si.n = v3(0.f); si.sh.s = v3(0.f); si.sh.t = v3(0.f); si.sh.n = v3(0.f);
+        si.wi = -ray.d;
+        return si;
+    }
+    return si_finalize2(bs, bf, best, ray_at(ray, best), ray.d);
 }
+MIB_D void ray_intersect(const Ray &ray, SurfIt &si) { si = ray_intersect2(ray); }
 
-MIB_D int target_medium(const DScene &sc, const SurfIt &si, V3 d) {              // interaction.h:285-299
+MIB_D int target_medium(const SurfIt &si, V3 d) {              // interaction.h:285-299
     const mib_shape &s = sc.d.shapes[si.shape];
     return dot(d, si.n) > 0.f ? s.exterior_medium : s.interior_medium;
 }
-MIB_D bool is_medium_transition(const DScene &sc, const SurfIt &si) {
+MIB_D bool is_medium_transition(const SurfIt &si) {
     const mib_shape &s = sc.d.shapes[si.shape];
     return s.interior_medium >= 0 || s.exterior_medium >= 0;
 }
@@ -171,7 +183,7 @@ MIB_D int wrap_coord(int pos, int shape, int mode) {
 struct GridTaps { uint32_t idx[8]; float w[8]; };   // used by the adjoint to scatter through the same taps
 
 template <int NC>
-MIB_DH void eval_grid(const DScene &sc, const mib_volume &v, V3 p, float *out, GridTaps *taps) {
+MIB_DH void eval_grid(const mib_volume &v, V3 p, float *out, GridTaps *taps) {
     V3 pl = xform_point(v.to_local, p);
     const float *__restrict__ data = sc.buffers[v.buffer];
     const int ch = v.channels, rx = v.res[0], ry = v.res[1], rz = v.res[2];
@@ -220,14 +232,14 @@ MIB_DH void eval_grid(const DScene &sc, const mib_volume &v, V3 p, float *out, G
 }
 
 template <int NC>
-MIB_D void eval_volume(const DScene &sc, const mib_volume &v, V3 p, float *out, Counters &cnt, GridTaps *taps = nullptr) {
+MIB_D void eval_volume(const mib_volume &v, V3 p, float *out, Counters &cnt, GridTaps *taps = nullptr) {
     if (v.type == MIB_VOLUME_CONST) {
 #pragma unroll
         for (int c = 0; c < NC; ++c) out[c] = v.value[v.channels == 1 ? 0 : c];
         return;
     }
     cnt.n_lookups++;
-    eval_grid<NC>(sc, v, p, out, taps);
+    eval_grid<NC>(v, p, out, taps);
 }
 
 // include/mitsuba/core/bbox.h:303-326
@@ -261,9 +273,23 @@ template <int NC> struct MedIt {
 template <int NC> MIB_D bool valid(const MedIt<NC> &m) { return m.t != inf_f(); }
 template <int NC> MIB_D float ch(const float *s, uint32_t c) { return NC == 3 ? s[c] : s[0]; }
 
-template <int NC>
-MIB_DH void sample_interaction(const DScene &sc, int mi, const Ray &ray, float sample, uint32_t channel,
-                              MedIt<NC> &mei, Counters &cnt, GridTaps *taps = nullptr) {
+template <bool TAPS> struct TapsOpt { GridTaps t; };       // the 8 taps travel with the result only for the adjoint
+template <> struct TapsOpt<false> {};
+template <int NC, bool TAPS> struct MedRes : TapsOpt<TAPS> {
+    MedIt<NC> mei;
+    int lookups;
+};
+template <int NC, bool TAPS>
+MIB_SUB_GEOM MedRes<NC, TAPS> sample_interaction2(int mi, Ray ray, float sample, uint32_t channel) {
+    MedRes<NC, TAPS> res;
+    MedIt<NC> &mei = res.mei;
+    Counters cnt = { 0, 0, 0, 0, 0 };
+    GridTaps *taps = nullptr;
+    if constexpr (TAPS) {
+        taps = &res.t;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { res.t.idx[k] = 0; res.t.w[k] = 0.f; }
+    }
     const mib_medium &m = sc.d.media[mi];
     mei.sh = make_frame(ray.d);
     bool active = true;
@@ -282,7 +308,7 @@ MIB_DH void sample_interaction(const DScene &sc, int mi, const Ray &ray, float s
         for (int c = 0; c < NC; ++c) mei.maj[c] = m.max_density;
     }
     float mj = ch<NC>(mei.maj, channel);
-    float sampled_t = mint + __fdiv_rn(-log_(1.f - sample), mj);
+    float sampled_t = mint + div_(-log_(1.f - sample), mj);
     bool valid_mi = active && (sampled_t <= maxt);
     mei.t = valid_mi ? sampled_t : inf_f();
     mei.p = ray_at(ray, sampled_t);
@@ -292,7 +318,7 @@ MIB_DH void sample_interaction(const DScene &sc, int mi, const Ray &ray, float s
         float alb[NC];
 #pragma unroll
         for (int c = 0; c < NC; ++c) alb[c] = 0.f;
-        if (valid_mi || m.albedo.type == MIB_VOLUME_CONST) eval_volume<NC>(sc, m.albedo, mei.p, alb, cnt);
+        if (valid_mi || m.albedo.type == MIB_VOLUME_CONST) eval_volume<NC>(m.albedo, mei.p, alb, cnt);
 #pragma unroll
         for (int c = 0; c < NC; ++c) {
             float st = m.sigma_t.value[m.sigma_t.channels == 1 ? 0 : c] * m.scale;
@@ -304,8 +330,8 @@ MIB_DH void sample_interaction(const DScene &sc, int mi, const Ray &ray, float s
         float sv[NC], av[NC];
 #pragma unroll
         for (int c = 0; c < NC; ++c) { sv[c] = 0.f; av[c] = 0.f; }
-        if (valid_mi) eval_volume<NC>(sc, m.sigma_t, mei.p, sv, cnt, taps);
-        if (valid_mi || m.albedo.type == MIB_VOLUME_CONST) eval_volume<NC>(sc, m.albedo, mei.p, av, cnt);
+        if (valid_mi) eval_volume<NC>(m.sigma_t, mei.p, sv, cnt, taps);
+        if (valid_mi || m.albedo.type == MIB_VOLUME_CONST) eval_volume<NC>(m.albedo, mei.p, av, cnt);
 #pragma unroll
         for (int c = 0; c < NC; ++c) {
             float st = m.scale * sv[c];
@@ -313,6 +339,19 @@ MIB_DH void sample_interaction(const DScene &sc, int mi, const Ray &ray, float s
             mei.sigma_n[c] = m.max_density - st;
             mei.sigma_t[c] = st;
         }
+    }
+    res.lookups = (int) cnt.n_lookups;
+    return res;
+}
+template <int NC>
+MIB_D void sample_interaction(int mi, const Ray &ray, float sample, uint32_t channel,
+                              MedIt<NC> &mei, Counters &cnt, GridTaps *taps = nullptr) {
+    if (taps) {
+        MedRes<NC, true> r = sample_interaction2<NC, true>(mi, ray, sample, channel);
+        mei = r.mei; cnt.n_lookups += r.lookups; *taps = r.t;
+    } else {
+        MedRes<NC, false> r = sample_interaction2<NC, false>(mi, ray, sample, channel);
+        mei = r.mei; cnt.n_lookups += r.lookups;
     }
 }
 
@@ -331,7 +370,7 @@ MIB_DH float tab_eval(const DTable &t, float x) {
     }
     uint32_t index = max(min(start, t.n - 1u), 1u) - 1u;
     float x0 = __ldg(t.nodes + index), x1 = __ldg(t.nodes + index + 1), y0 = __ldg(t.pdf + index), y1 = __ldg(t.pdf + index + 1);
-    x = __fdiv_rn(x - x0, x1 - x0);
+    x = div_(x - x0, x1 - x0);
     return active ? fma_(x, y1 - y0, y0) : 0.f;
 }
 MIB_DH float tab_sample(const DTable &t, float sample) {
@@ -347,9 +386,9 @@ MIB_DH float tab_sample(const DTable &t, float sample) {
     uint32_t index = start;
     float x0 = __ldg(t.nodes + index), x1 = __ldg(t.nodes + index + 1), y0 = __ldg(t.pdf + index), y1 = __ldg(t.pdf + index + 1);
     float c0 = index > 0 ? __ldg(t.cdf + index - 1) : 0.f, w = x1 - x0;
-    sample = __fdiv_rn(sample - c0, w);
-    float t_linear = __fdiv_rn(y0 - safe_sqrt_(sqr_(y0) + 2.f * sample * (y1 - y0)), y0 - y1);
-    float t_const = __fdiv_rn(sample, y0);
+    sample = div_(sample - c0, w);
+    float t_linear = div_(y0 - safe_sqrt_(sqr_(y0) + 2.f * sample * (y1 - y0)), y0 - y1);
+    float t_const = div_(sample, y0);
     float tt = (y0 == y1) ? t_const : t_linear;
     return fma_(tt, w, x0);
 }

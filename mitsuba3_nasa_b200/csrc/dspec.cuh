@@ -68,19 +68,27 @@ MIB_D void m4_identity(float *M, float s) {
 }
 
 // mueller.h:375-386: angle of rotate_stokes_basis -> (cos 2theta, sin 2theta)
-MIB_DM void stokes_rotation(V3 forward, V3 basis_current, V3 basis_target, float &c, float &s) {
+MIB_SUB_ROT float2 stokes_rotation2(V3 forward, V3 basis_current, V3 basis_target) {       // (cos, sin)
     float theta = unit_angle(normalize(basis_current), normalize(basis_target));
     if (dot(forward, cross(basis_current, basis_target)) < 0.f) theta *= -1.f;
+    float s, c;
     sincos_(2.f * theta, s, c);
+    return make_float2(c, s);
+}
+MIB_D void stokes_rotation(V3 forward, V3 basis_current, V3 basis_target, float &c, float &s) {
+    float2 r = stokes_rotation2(forward, basis_current, basis_target);
+    c = r.x; s = r.y;
 }
 
 // to_world_mueller (interaction.h:374-395, :574-595): the two rotations for local directions in/out
-MIB_DM void world_rotations(const Frame3 &fr, V3 in_l, V3 out_l, float &ci, float &si, float &co, float &so) {
-    V3 in_w = to_world(fr, in_l), out_w = to_world(fr, out_l);
-    V3 in_cur = to_world(fr, stokes_basis(in_l)), in_tgt = stokes_basis(in_w);
-    V3 out_cur = to_world(fr, stokes_basis(out_l)), out_tgt = stokes_basis(out_w);
-    stokes_rotation(in_w, in_cur, in_tgt, ci, si);
-    stokes_rotation(out_w, out_cur, out_tgt, co, so);
+MIB_SUB_ROT float2 world_rotation1(Frame3 fr, V3 l) {
+    V3 w = to_world(fr, l);
+    V3 cur = to_world(fr, stokes_basis(l)), tgt = stokes_basis(w);
+    return stokes_rotation2(w, cur, tgt);
+}
+MIB_D void world_rotations(const Frame3 &fr, V3 in_l, V3 out_l, float &ci, float &si, float &co, float &so) {
+    float2 ri = world_rotation1(fr, in_l), ro = world_rotation1(fr, out_l);
+    ci = ri.x; si = ri.y; co = ro.x; so = ro.y;
 }
 MIB_D void m4_to_world(const Frame3 &fr, float *M, V3 in_l, V3 out_l) {
     float ci, si, co, so;
@@ -90,15 +98,17 @@ MIB_D void m4_to_world(const Frame3 &fr, float *M, V3 in_l, V3 out_l) {
 }
 
 // Phase-matrix rotation from the scattering plane (rayleigh.cpp:68-88, tabphase_polarized.cpp:169-197)
-MIB_D void m4_phase_rotate(float *M, V3 wo, V3 wi) {
+MIB_SUB_ROT float4 phase_rotation_angles(V3 wo, V3 wi) {           // (ci, si, co, so)
     V3 mwo = -wo;
     V3 x_hat = cross(mwo, wi);
     V3 p_in = normalize(cross(x_hat, mwo)), p_out = normalize(cross(x_hat, wi));
-    float ci, si, co, so;
-    stokes_rotation(mwo, p_in, stokes_basis(mwo), ci, si);
-    stokes_rotation(wi, p_out, stokes_basis(wi), co, so);
-    m4_rot_left(M, co, so);
-    m4_rot_right_t(M, ci, si);
+    float2 a = stokes_rotation2(mwo, p_in, stokes_basis(mwo)), b = stokes_rotation2(wi, p_out, stokes_basis(wi));
+    return make_float4(a.x, a.y, b.x, b.y);
+}
+MIB_D void m4_phase_rotate(float *M, V3 wo, V3 wi) {
+    float4 r = phase_rotation_angles(wo, wi);
+    m4_rot_left(M, r.z, r.w);
+    m4_rot_right_t(M, r.x, r.y);
 #pragma unroll
     for (int i = 0; i < 16; ++i) if (M[i] != M[i]) M[i] = 0.f;
 }

@@ -52,7 +52,7 @@ template <int SPEC> struct WalkState {
 enum { EV_NULL = 0, EV_SCATTER = 1, EV_NEE = 2, EV_BSDF = 3, EV_DONE = 4 };
 
 template <int SPEC>
-MIB_D void walk_init(const DScene &sc, Pcg32 &rng, const Ray &ray, WalkState<SPEC> &st) {
+MIB_D void walk_init(Pcg32 &rng, const Ray &ray, WalkState<SPEC> &st) {
     T_init<SPEC>(st.T);
 #pragma unroll
     for (int i = 0; i < ST<SPEC>::NR; ++i) st.R[i] = 0.f;
@@ -70,13 +70,13 @@ MIB_D void walk_init(const DScene &sc, Pcg32 &rng, const Ray &ray, WalkState<SPE
 
 // ---- shadow walk: setup (volpath.cpp:334-372 / volpathaos.cpp:299-345) ----
 template <int SPEC, bool AOS>
-MIB_D void nee_begin(const DScene &sc, Pcg32 &rng, V3 ref_p, V3 ref_n, bool surface_ref, const SurfIt *ref_si, int medium,
+MIB_D void nee_begin(Pcg32 &rng, V3 ref_p, V3 ref_n, bool surface_ref, const SurfIt *ref_si, int medium,
                      NeeState<SPEC> &ns, DirSample<ST<SPEC>::NC> &ds) {
     constexpr int NC = ST<SPEC>::NC;
 #pragma unroll
     for (int c = 0; c < NC; ++c) ns.tr[c] = 1.f;
     float sx = rng.next(), sy = rng.next();
-    sample_emitter_direction<NC>(sc, ref_p, sx, sy, ds, ns.ev);
+    sample_emitter_direction<NC>(ref_p, sx, sy, ds, ns.ev);
     ns.emitter_d = AOS ? normalize(ds.d) : ds.d;
     ns.active = true;
     ns.medium = medium;
@@ -96,13 +96,13 @@ MIB_D void nee_begin(const DScene &sc, Pcg32 &rng, V3 ref_p, V3 ref_n, bool surf
     else {
         ns.ray = spawn_ray_to(ref_p, ref_n, ds.p);
         ns.max_dist = ns.ray.maxt;
-        if (surface_ref && is_medium_transition(sc, *ref_si)) ns.medium = target_medium(sc, *ref_si, ns.ray.d);
+        if (surface_ref && is_medium_transition(*ref_si)) ns.medium = target_medium(*ref_si, ns.ray.d);
     }
 }
 
 // ---- shadow walk: one iteration (volpath.cpp:374-447 / volpathaos.cpp:347-452) ----
 template <int SPEC, bool AOS>
-MIB_D void nee_step(const DScene &sc, Pcg32 &rng, Counters &cnt, uint32_t channel, NeeState<SPEC> &ns) {
+MIB_D void nee_step(Pcg32 &rng, Counters &cnt, uint32_t channel, NeeState<SPEC> &ns) {
     constexpr int NC = ST<SPEC>::NC;
     Ray &ray = ns.ray;
     SurfIt &si = ns.si;
@@ -115,9 +115,9 @@ MIB_D void nee_step(const DScene &sc, Pcg32 &rng, Counters &cnt, uint32_t channe
         const mib_medium &md = sc.d.media[ns.medium];
         cnt.n_nee_steps++;
         MedIt<NC> mei;
-        sample_interaction<NC>(sc, ns.medium, ray, rng.next(), channel, mei, cnt);
+        sample_interaction<NC>(ns.medium, ray, rng.next(), channel, mei, cnt);
         if (md.type == MIB_MEDIUM_HOMOGENEOUS && valid(mei)) ray.maxt = fminf(mei.t, remaining);
-        if (ns.needs_intersection) ray_intersect(sc, ray, si);
+        if (ns.needs_intersection) ray_intersect(ray, si);
         if (si.t < mei.t) mei.t = inf_f();
         ns.needs_intersection = ns.needs_intersection && !valid(si);
         const bool is_spectral = md.has_spectral_extinction != 0;
@@ -140,11 +140,11 @@ MIB_D void nee_step(const DScene &sc, Pcg32 &rng, Counters &cnt, uint32_t channe
             ray.o = mei.p;
             si.t = si.t - mei.t;
 #pragma unroll
-            for (int c = 0; c < NC; ++c) tr[c] *= is_spectral ? mei.sigma_n[c] : __fdiv_rn(mei.sigma_n[c], mei.maj[c]);
+            for (int c = 0; c < NC; ++c) tr[c] *= is_spectral ? mei.sigma_n[c] : div_(mei.sigma_n[c], mei.maj[c]);
         }
     }
     bool intersect = active_surface && ns.needs_intersection;
-    if (intersect) ray_intersect(sc, ray, si);
+    if (intersect) ray_intersect(ray, si);
     ns.needs_intersection = ns.needs_intersection && !intersect;
     active_surface = active_surface || escaped_medium;
     if (active_surface) ns.total_dist += si.t;
@@ -171,7 +171,7 @@ MIB_D void nee_step(const DScene &sc, Pcg32 &rng, Counters &cnt, uint32_t channe
 #pragma unroll
     for (int c = 0; c < NC; ++c) any_tr = any_tr || tr[c] != 0.f;
     ns.active = (active_medium || active_surface) && any_tr;
-    if (active_surface && is_medium_transition(sc, si)) ns.medium = target_medium(sc, si, ray.d);
+    if (active_surface && is_medium_transition(si)) ns.medium = target_medium(si, ray.d);
 }
 
 // ---- shadow walk finished: add the pending contribution ----
@@ -199,7 +199,7 @@ MIB_D void nee_finish(const NeeState<SPEC> &ns, float *R) {
 // T_dirty / R_dirty report whether T / R changed.
 // ---------------------------------------------------------------------------------------------
 template <int SPEC, bool AOS>
-MIB_D int stg_main(const DScene &sc, Pcg32 &rng, Counters &cnt, WalkState<SPEC> &st, float *u_out, bool &T_dirty, bool &R_dirty) {
+MIB_D int stg_main(Pcg32 &rng, Counters &cnt, WalkState<SPEC> &st, float *u_out, bool &T_dirty, bool &R_dirty) {
     constexpr int NC = ST<SPEC>::NC, NR = ST<SPEC>::NR;
     const mib_integrator &I = sc.d.integrator;
     float *T = st.T, *R = st.R;
@@ -222,9 +222,9 @@ MIB_D int stg_main(const DScene &sc, Pcg32 &rng, Counters &cnt, WalkState<SPEC> 
     if (active_medium) {
         const mib_medium &md = sc.d.media[st.medium];
         is_spectral = md.has_spectral_extinction != 0;
-        sample_interaction<NC>(sc, st.medium, ray, rng.next(), channel, mei, cnt);
+        sample_interaction<NC>(st.medium, ray, rng.next(), channel, mei, cnt);
         if (md.type == MIB_MEDIUM_HOMOGENEOUS && valid(mei)) ray.maxt = mei.t;
-        if (st.needs_intersection) ray_intersect(sc, ray, si);
+        if (st.needs_intersection) ray_intersect(ray, si);
         st.needs_intersection = st.needs_intersection && !valid(si);
         if (si.t < mei.t) mei.t = inf_f();
         if (is_spectral) {                                               // medium.cpp:99-111
@@ -244,7 +244,7 @@ MIB_D int stg_main(const DScene &sc, Pcg32 &rng, Counters &cnt, WalkState<SPEC> 
         active_medium = valid(mei);
         if (active_medium) {
             float u = rng.next();
-            bool null_scatter = u >= __fdiv_rn(ch<NC>(mei.sigma_t, channel), ch<NC>(mei.maj, channel));
+            bool null_scatter = u >= div_(ch<NC>(mei.sigma_t, channel), ch<NC>(mei.maj, channel));
             act_null = null_scatter;
             act_scatter = !null_scatter;
             if (is_spectral && act_null) {
@@ -269,19 +269,19 @@ MIB_D int stg_main(const DScene &sc, Pcg32 &rng, Counters &cnt, WalkState<SPEC> 
             for (int c = 0; c < NC; ++c) u_out[c] = (mei.sigma_s[c] * mjc) * ist;
         } else {
 #pragma unroll
-            for (int c = 0; c < NC; ++c) u_out[c] = __fdiv_rn(mei.sigma_s[c], mei.sigma_t[c]);
+            for (int c = 0; c < NC; ++c) u_out[c] = div_(mei.sigma_s[c], mei.sigma_t[c]);
         }
         st.scatter_p = mei.p;
         return EV_SCATTER;
     }
     if (active_surface || escaped) {
-        if (st.needs_intersection) ray_intersect(sc, ray, si);
+        if (st.needs_intersection) ray_intersect(ray, si);
         if (!AOS) {                                                      // volpath.cpp:258-279
             bool count_direct = st.depth == 0u || st.specular_chain;
-            int emitter = si_emitter(sc, si);
+            int emitter = si_emitter(si);
             if (emitter >= 0 && !(st.depth == 0u && I.hide_emitters)) {
                 float emitter_pdf = 1.0f;
-                if (!count_direct) emitter_pdf = pdf_emitter_direction(sc, emitter);
+                if (!count_direct) emitter_pdf = pdf_emitter_direction(emitter);
                 const mib_emitter &e = sc.d.emitters[emitter];
                 float x[NR];
                 T_col0<SPEC>(T, x);
@@ -301,7 +301,7 @@ MIB_D int stg_main(const DScene &sc, Pcg32 &rng, Counters &cnt, WalkState<SPEC> 
         const uint32_t flags = is_null ? kBsdfNull : kBsdfDiffuseRefl;
         if ((flags & kBsdfSmooth) && (st.depth + 1 < maxd)) {
             DirSample<NC> ds;
-            nee_begin<SPEC, AOS>(sc, rng, si.p, si.n, true, &si, st.medium, st.nee, ds);
+            nee_begin<SPEC, AOS>(rng, si.p, si.n, true, &si, st.medium, st.nee, ds);
             V3 wo = to_local(si.sh, ds.d);
             bool ok = si.wi.z > 0.f && wo.z > 0.f;
             float x[NR];
@@ -328,7 +328,7 @@ MIB_D int stg_main(const DScene &sc, Pcg32 &rng, Counters &cnt, WalkState<SPEC> 
 // volpathaos.cpp:170-200).  Returns true when st.nee holds a shadow walk (then PHASE), false -> PHASE directly.
 // ---------------------------------------------------------------------------------------------
 template <int SPEC, bool AOS>
-MIB_D bool stg_scatter(const DScene &sc, Pcg32 &rng, WalkState<SPEC> &st, const float *u) {
+MIB_D bool stg_scatter(Pcg32 &rng, WalkState<SPEC> &st, const float *u) {
     constexpr int NC = ST<SPEC>::NC, NT = ST<SPEC>::NT;
     constexpr bool POL = ST<SPEC>::POL;
     const mib_medium &md = sc.d.media[st.medium];
@@ -338,10 +338,10 @@ MIB_D bool stg_scatter(const DScene &sc, Pcg32 &rng, WalkState<SPEC> &st, const 
     if (!sample_emitters) return false;
     Frame3 sh = make_frame(st.ray.d);
     DirSample<NC> ds;
-    nee_begin<SPEC, AOS>(sc, rng, st.scatter_p, v3(0.f), false, nullptr, st.medium, st.nee, ds);
+    nee_begin<SPEC, AOS>(rng, st.scatter_p, v3(0.f), false, nullptr, st.medium, st.nee, ds);
     V3 wo = to_local(sh, ds.d);
     float W[NT];
-    float ppdf = phase_eval<SPEC>(sc, md.phase, wo, W);
+    float ppdf = phase_eval<SPEC>(md.phase, wo, W);
     if constexpr (POL) m4_to_world(sh, W, -wo, v3(0.f, 0.f, -1.f));
     TW_col0<SPEC>(st.T, W, st.nee.a);
     st.nee.mul_w_after = !AOS;
@@ -351,7 +351,7 @@ MIB_D bool stg_scatter(const DScene &sc, Pcg32 &rng, WalkState<SPEC> &st, const 
 
 // ---- PHASE: sample the phase function, continue the walk (volpath.cpp:236-256 / volpathaos.cpp:202-218) ----
 template <int SPEC, bool AOS>
-MIB_D void stg_phase(const DScene &sc, Pcg32 &rng, WalkState<SPEC> &st) {
+MIB_D void stg_phase(Pcg32 &rng, WalkState<SPEC> &st) {
     constexpr int NT = ST<SPEC>::NT;
     constexpr bool POL = ST<SPEC>::POL;
     const mib_integrator &I = sc.d.integrator;
@@ -364,7 +364,7 @@ MIB_D void stg_phase(const DScene &sc, Pcg32 &rng, WalkState<SPEC> &st) {
     V3 wo;
     float W[NT];
     Frame3 sh = make_frame(st.ray.d);
-    float ppdf = phase_sample<SPEC>(sc, md.phase, s2x, s2y, wo, W);
+    float ppdf = phase_sample<SPEC>(md.phase, s2x, s2y, wo, W);
     if constexpr (POL) m4_to_world(sh, W, -wo, v3(0.f, 0.f, -1.f));
     if (!AOS) T_mul_W<SPEC>(st.T, W);                                    // volpath.cpp:244 (before the pdf test)
     if (ppdf > 0.f) {
@@ -377,7 +377,7 @@ MIB_D void stg_phase(const DScene &sc, Pcg32 &rng, WalkState<SPEC> &st) {
 
 // ---- BSDF: sample the surface, continue the walk (volpath.cpp:296-326 / volpathaos.cpp:262-292) ----
 template <int SPEC, bool AOS>
-MIB_D void stg_bsdf(const DScene &sc, Pcg32 &rng, WalkState<SPEC> &st) {
+MIB_D void stg_bsdf(Pcg32 &rng, WalkState<SPEC> &st) {
     constexpr int NC = ST<SPEC>::NC;
     constexpr bool POL = ST<SPEC>::POL;
     const mib_integrator &I = sc.d.integrator;
@@ -415,31 +415,31 @@ MIB_D void stg_bsdf(const DScene &sc, Pcg32 &rng, WalkState<SPEC> &st) {
     if (non_null) { st.depth += 1; st.last_pdf = bs_pdf; }
     st.specular_chain = st.specular_chain || (non_null && (sampled & kBsdfDelta));
     st.specular_chain = st.specular_chain && !(sampled & kBsdfSmooth);
-    if (is_medium_transition(sc, si)) st.medium = target_medium(sc, si, st.ray.d);
+    if (is_medium_transition(si)) st.medium = target_medium(si, st.ray.d);
 }
 
 // Whole path through the stage functions in one thread (per-sample dumps of the debug ABI: checks the
 // stage decomposition itself, independent of the pool machinery).
 template <int SPEC, bool AOS>
-MIB_D void trace_path_staged(const DScene &sc, Pcg32 &rng, Counters &cnt, Ray ray, float *R) {
+MIB_D void trace_path_staged(Pcg32 &rng, Counters &cnt, Ray ray, float *R) {
     constexpr int NC = ST<SPEC>::NC;
     WalkState<SPEC> st;
-    walk_init<SPEC>(sc, rng, ray, st);
+    walk_init<SPEC>(rng, ray, st);
     while (true) {
         float u[NC];
         bool td = false, rd = false;
-        int ev = stg_main<SPEC, AOS>(sc, rng, cnt, st, u, td, rd);
+        int ev = stg_main<SPEC, AOS>(rng, cnt, st, u, td, rd);
         if (ev == EV_DONE) break;
         if (ev == EV_NULL) continue;
         bool after_bsdf = ev != EV_SCATTER;
         bool nee = ev == EV_NEE;
-        if (ev == EV_SCATTER) nee = stg_scatter<SPEC, AOS>(sc, rng, st, u);
+        if (ev == EV_SCATTER) nee = stg_scatter<SPEC, AOS>(rng, st, u);
         if (nee) {
-            while (st.nee.active) nee_step<SPEC, AOS>(sc, rng, cnt, st.channel, st.nee);
+            while (st.nee.active) nee_step<SPEC, AOS>(rng, cnt, st.channel, st.nee);
             nee_finish<SPEC>(st.nee, st.R);
         }
-        if (after_bsdf) stg_bsdf<SPEC, AOS>(sc, rng, st);
-        else stg_phase<SPEC, AOS>(sc, rng, st);
+        if (after_bsdf) stg_bsdf<SPEC, AOS>(rng, st);
+        else stg_phase<SPEC, AOS>(rng, st);
     }
 #pragma unroll
     for (int i = 0; i < ST<SPEC>::NR; ++i) R[i] = st.R[i];

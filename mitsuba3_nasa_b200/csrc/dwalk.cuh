@@ -12,7 +12,7 @@ namespace mib {
 
 template <int SPEC> MIB_D float mis_weight(float a, float b) {               // volpath.cpp:463-468
     a *= a; b *= b;
-    float w = __fdiv_rn(a, a + b);
+    float w = div_(a, a + b);
     return isfinite(w) ? w : 0.f;
 }
 
@@ -32,14 +32,14 @@ MIB_D void null_block(const SurfIt &si, float &b11, float &b12, float &b21, floa
 // The transmittance only needs its (0,0) entry in polarized mode (dspec.cuh notes).
 // ---------------------------------------------------------------------------
 template <int SPEC, bool AOS>
-MIB_D void sample_emitter(const DScene &sc, Pcg32 &rng, Counters &cnt, V3 ref_p, V3 ref_n, bool surface_ref,
+MIB_D void sample_emitter(Pcg32 &rng, Counters &cnt, V3 ref_p, V3 ref_n, bool surface_ref,
                           const SurfIt *ref_si, int medium, uint32_t channel, DirSample<ST<SPEC>::NC> &ds, float *emitted) {
     constexpr int NC = ST<SPEC>::NC;
     float tr[NC], ev[NC];
 #pragma unroll
     for (int c = 0; c < NC; ++c) tr[c] = 1.f;
     float sx = rng.next(), sy = rng.next();
-    sample_emitter_direction<NC>(sc, ref_p, sx, sy, ds, ev);
+    sample_emitter_direction<NC>(ref_p, sx, sy, ds, ev);
     V3 emitter_d = AOS ? normalize(ds.d) : ds.d;
     bool active = true;
     if (ds.pdf == 0.f) { for (int c = 0; c < NC; ++c) ev[c] = 0.f; active = false; }
@@ -51,7 +51,7 @@ MIB_D void sample_emitter(const DScene &sc, Pcg32 &rng, Counters &cnt, V3 ref_p,
     else {
         ray = spawn_ray_to(ref_p, ref_n, ds.p);
         max_dist = ray.maxt;
-        if (surface_ref && is_medium_transition(sc, *ref_si)) medium = target_medium(sc, *ref_si, ray.d);
+        if (surface_ref && is_medium_transition(*ref_si)) medium = target_medium(*ref_si, ray.d);
     }
     float total_dist = 0.f;
     SurfIt si;
@@ -67,9 +67,9 @@ MIB_D void sample_emitter(const DScene &sc, Pcg32 &rng, Counters &cnt, V3 ref_p,
             const mib_medium &md = sc.d.media[medium];
             cnt.n_nee_steps++;
             MedIt<NC> mei;
-            sample_interaction<NC>(sc, medium, ray, rng.next(), channel, mei, cnt);
+            sample_interaction<NC>(medium, ray, rng.next(), channel, mei, cnt);
             if (md.type == MIB_MEDIUM_HOMOGENEOUS && valid(mei)) ray.maxt = fminf(mei.t, remaining);
-            if (needs_intersection) ray_intersect(sc, ray, si);
+            if (needs_intersection) ray_intersect(ray, si);
             if (si.t < mei.t) mei.t = inf_f();
             needs_intersection = needs_intersection && !valid(si);
             bool is_spectral = md.has_spectral_extinction != 0, not_spectral = !is_spectral;
@@ -92,12 +92,12 @@ MIB_D void sample_emitter(const DScene &sc, Pcg32 &rng, Counters &cnt, V3 ref_p,
                 ray.o = mei.p;
                 si.t = si.t - mei.t;
 #pragma unroll
-                for (int c = 0; c < NC; ++c) tr[c] *= is_spectral ? mei.sigma_n[c] : __fdiv_rn(mei.sigma_n[c], mei.maj[c]);
+                for (int c = 0; c < NC; ++c) tr[c] *= is_spectral ? mei.sigma_n[c] : div_(mei.sigma_n[c], mei.maj[c]);
             }
             (void) not_spectral;
         }
         bool intersect = active_surface && needs_intersection;
-        if (intersect) ray_intersect(sc, ray, si);
+        if (intersect) ray_intersect(ray, si);
         needs_intersection = needs_intersection && !intersect;
         active_surface = active_surface || escaped_medium;
         if (active_surface) total_dist += si.t;
@@ -125,7 +125,7 @@ MIB_D void sample_emitter(const DScene &sc, Pcg32 &rng, Counters &cnt, V3 ref_p,
 #pragma unroll
         for (int c = 0; c < NC; ++c) any_tr = any_tr || tr[c] != 0.f;
         active = active && (active_medium || active_surface) && any_tr;
-        if (active_surface && is_medium_transition(sc, si)) medium = target_medium(sc, si, ray.d);
+        if (active_surface && is_medium_transition(si)) medium = target_medium(si, ray.d);
     }
 #pragma unroll
     for (int c = 0; c < NC; ++c) emitted[c] = tr[c] * ev[c];
@@ -149,7 +149,7 @@ template <int SPEC> struct PathState {
 };
 
 template <int SPEC>
-MIB_D void path_init(const DScene &sc, Pcg32 &rng, const Ray &ray, PathState<SPEC> &st) {
+MIB_D void path_init(Pcg32 &rng, const Ray &ray, PathState<SPEC> &st) {
     constexpr int NR = ST<SPEC>::NR;
     T_init<SPEC>(st.T);
 #pragma unroll
@@ -168,7 +168,7 @@ MIB_D void path_init(const DScene &sc, Pcg32 &rng, const Ray &ray, PathState<SPE
 
 // One iteration of the reference's while loop (volpath.cpp:121-328 / volpathaos.cpp:85-294).
 template <int SPEC, bool AOS>
-MIB_D void path_step(const DScene &sc, Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
+MIB_D void path_step(Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
     constexpr int NC = ST<SPEC>::NC, NT = ST<SPEC>::NT, NR = ST<SPEC>::NR;
     constexpr bool POL = ST<SPEC>::POL;
     const mib_integrator &I = sc.d.integrator;
@@ -198,9 +198,9 @@ MIB_D void path_step(const DScene &sc, Pcg32 &rng, Counters &cnt, PathState<SPEC
             const mib_medium &md = sc.d.media[medium];
             is_spectral = md.has_spectral_extinction != 0;
             not_spectral = !is_spectral;
-            sample_interaction<NC>(sc, medium, ray, rng.next(), channel, mei, cnt);
+            sample_interaction<NC>(medium, ray, rng.next(), channel, mei, cnt);
             if (md.type == MIB_MEDIUM_HOMOGENEOUS && valid(mei)) ray.maxt = mei.t;
-            if (needs_intersection) ray_intersect(sc, ray, si);
+            if (needs_intersection) ray_intersect(ray, si);
             needs_intersection = needs_intersection && !valid(si);
             if (si.t < mei.t) mei.t = inf_f();
             if (is_spectral) {                                               // medium.cpp:99-111
@@ -219,7 +219,7 @@ MIB_D void path_step(const DScene &sc, Pcg32 &rng, Counters &cnt, PathState<SPEC
             active_medium = valid(mei);
             if (active_medium) {
                 float u = rng.next();
-                bool null_scatter = u >= __fdiv_rn(ch<NC>(mei.sigma_t, channel), ch<NC>(mei.maj, channel));
+                bool null_scatter = u >= div_(ch<NC>(mei.sigma_t, channel), ch<NC>(mei.maj, channel));
                 act_null = null_scatter;
                 act_scatter = !null_scatter;
                 if (is_spectral && act_null) {
@@ -245,7 +245,7 @@ MIB_D void path_step(const DScene &sc, Pcg32 &rng, Counters &cnt, PathState<SPEC
                 for (int c = 0; c < NC; ++c) u[c] = (mei.sigma_s[c] * mjc) * ist;
             } else {
 #pragma unroll
-                for (int c = 0; c < NC; ++c) u[c] = __fdiv_rn(mei.sigma_s[c], mei.sigma_t[c]);
+                for (int c = 0; c < NC; ++c) u[c] = div_(mei.sigma_s[c], mei.sigma_t[c]);
             }
             (void) not_spectral;
             T_mul_u<SPEC>(T, u);
@@ -256,9 +256,9 @@ MIB_D void path_step(const DScene &sc, Pcg32 &rng, Counters &cnt, PathState<SPEC
             if (sample_emitters) {
                 DirSample<NC> ds;
                 float em[NC];
-                sample_emitter<SPEC, AOS>(sc, rng, cnt, mei.p, v3(0.f), false, nullptr, medium, channel, ds, em);
+                sample_emitter<SPEC, AOS>(rng, cnt, mei.p, v3(0.f), false, nullptr, medium, channel, ds, em);
                 V3 wo = to_local(mei.sh, ds.d);
-                float ppdf = phase_eval<SPEC>(sc, phase, wo, W);
+                float ppdf = phase_eval<SPEC>(phase, wo, W);
                 if constexpr (POL) m4_to_world(mei.sh, W, -wo, v3(0.f, 0.f, -1.f));
                 float x[NR];
                 TW_col0<SPEC>(T, W, x);
@@ -276,7 +276,7 @@ MIB_D void path_step(const DScene &sc, Pcg32 &rng, Counters &cnt, PathState<SPEC
             else { s2x = rng.next(); s2y = rng.next(); s1 = rng.next(); }
             (void) s1;
             V3 wo;
-            float ppdf = phase_sample<SPEC>(sc, phase, s2x, s2y, wo, W);
+            float ppdf = phase_sample<SPEC>(phase, s2x, s2y, wo, W);
             if constexpr (POL) m4_to_world(mei.sh, W, -wo, v3(0.f, 0.f, -1.f));
             if (!AOS) T_mul_W<SPEC>(T, W);                                   // volpath.cpp:244 (before the pdf test)
             act_scatter = act_scatter && ppdf > 0.f;
@@ -289,13 +289,13 @@ MIB_D void path_step(const DScene &sc, Pcg32 &rng, Counters &cnt, PathState<SPEC
         }
 
         active_surface = active_surface || escaped;
-        if (active_surface && needs_intersection) ray_intersect(sc, ray, si);
+        if (active_surface && needs_intersection) ray_intersect(ray, si);
         if (!AOS && active_surface) {                                        // volpath.cpp:258-279
             bool count_direct = depth == 0u || specular_chain;
-            int emitter = si_emitter(sc, si);
+            int emitter = si_emitter(si);
             if (emitter >= 0 && !(depth == 0u && I.hide_emitters)) {
                 float emitter_pdf = 1.0f;
-                if (!count_direct) emitter_pdf = pdf_emitter_direction(sc, emitter);
+                if (!count_direct) emitter_pdf = pdf_emitter_direction(emitter);
                 const mib_emitter &e = sc.d.emitters[emitter];
                 float x[NR];
                 T_col0<SPEC>(T, x);
@@ -317,7 +317,7 @@ MIB_D void path_step(const DScene &sc, Pcg32 &rng, Counters &cnt, PathState<SPEC
             if (active_e) {
                 DirSample<NC> ds;
                 float em[NC];
-                sample_emitter<SPEC, AOS>(sc, rng, cnt, si.p, si.n, true, &si, medium, channel, ds, em);
+                sample_emitter<SPEC, AOS>(rng, cnt, si.p, si.n, true, &si, medium, channel, ds, em);
                 V3 wo = to_local(si.sh, ds.d);
                 bool ok = si.wi.z > 0.f && wo.z > 0.f;
                 float x[NR];
@@ -363,17 +363,17 @@ MIB_D void path_step(const DScene &sc, Pcg32 &rng, Counters &cnt, PathState<SPEC
             if (non_null) { depth += 1; last_pdf = bs_pdf; }
             specular_chain = specular_chain || (non_null && (sampled & kBsdfDelta));
             specular_chain = specular_chain && !(sampled & kBsdfSmooth);
-            if (is_medium_transition(sc, si)) medium = target_medium(sc, si, ray.d);
+            if (is_medium_transition(si)) medium = target_medium(si, ray.d);
         }
         active = active && (active_surface || active_medium);
     }
 }
 
 template <int SPEC, bool AOS>
-MIB_D void trace_path(const DScene &sc, Pcg32 &rng, Counters &cnt, Ray ray, float *R) {
+MIB_D void trace_path(Pcg32 &rng, Counters &cnt, Ray ray, float *R) {
     PathState<SPEC> st;
-    path_init<SPEC>(sc, rng, ray, st);
-    while (st.active) path_step<SPEC, AOS>(sc, rng, cnt, st);
+    path_init<SPEC>(rng, ray, st);
+    while (st.active) path_step<SPEC, AOS>(rng, cnt, st);
 #pragma unroll
     for (int i = 0; i < ST<SPEC>::NR; ++i) R[i] = st.R[i];
 }

@@ -4,23 +4,26 @@
 
 namespace mib {
 #if defined(INST_FWD)
-template <> void launch_k_forward<INST_SPEC, INST_MODE>(const DScene &sc, const LaunchParams &lp, unsigned blocks, cudaStream_t st) {
-    k_forward<INST_SPEC, INST_MODE><<<blocks, 128, 0, st>>>(sc, lp);
+template <> void launch_k_forward<INST_SPEC, INST_MODE>(const DScene &scene, const LaunchParams &lp, unsigned blocks, cudaStream_t st) {
+    cudaMemcpyToSymbolAsync(sc, &scene, sizeof(DScene), 0, cudaMemcpyHostToDevice, st);
+    k_forward<INST_SPEC, INST_MODE><<<blocks, 128, 0, st>>>(lp);
 }
 #elif defined(INST_POOL)
-template <> void launch_k_forward_pool<INST_SPEC, INST_MODE>(const DScene &sc, const LaunchParams &lp, unsigned blocks, unsigned threads, cudaStream_t st) {
+template <> void launch_k_forward_pool<INST_SPEC, INST_MODE>(const DScene &scene, const LaunchParams &lp, unsigned blocks, unsigned threads, cudaStream_t st) {
     static bool configured = false;
     const size_t smem = pool_smem_bytes<INST_SPEC>((int) lp.pool_slots);
     if (!configured) {
         cudaFuncSetAttribute(k_forward_pool<INST_SPEC, INST_MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
         configured = true;
     }
-    k_forward_pool<INST_SPEC, INST_MODE><<<blocks, threads, smem, st>>>(sc, lp);
+    cudaMemcpyToSymbolAsync(sc, &scene, sizeof(DScene), 0, cudaMemcpyHostToDevice, st);
+    k_forward_pool<INST_SPEC, INST_MODE><<<blocks, threads, smem, st>>>(lp);
 }
 template <> size_t pool_bytes<INST_SPEC, INST_MODE>(int slots) { return pool_smem_bytes<INST_SPEC>(slots); }
 #elif defined(INST_ADJ)
-template <> void launch_k_adjoint<INST_SPEC>(const DScene &sc, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, cudaStream_t st) {
-    k_adjoint<INST_SPEC><<<blocks, 128, 0, st>>>(sc, lp, ap);
+template <> void launch_k_adjoint<INST_SPEC>(const DScene &scene, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, cudaStream_t st) {
+    cudaMemcpyToSymbolAsync(sc, &scene, sizeof(DScene), 0, cudaMemcpyHostToDevice, st);
+    k_adjoint<INST_SPEC><<<blocks, 128, 0, st>>>(lp, ap);
 }
 #endif
 }

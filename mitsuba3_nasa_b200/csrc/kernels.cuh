@@ -35,7 +35,7 @@ struct LaunchParams {
 };
 
 // launchers defined in inst.cu (one per object file)
-template <int SPEC, int MODE> void launch_k_forward(const DScene &sc, const LaunchParams &lp, unsigned blocks, cudaStream_t st);
+template <int SPEC, int MODE> void launch_k_forward(const DScene &scene, const LaunchParams &lp, unsigned blocks, cudaStream_t st);
 
 template <int SPEC> struct RawChannels { static constexpr int C = SPEC == MIB_SPEC_MONO ? 2 : 4; };
 
@@ -54,7 +54,7 @@ MIB_D void to_sensor_stokes(const Ray &ray, float *S) {
 }
 
 // Reconstruction filters (src/rfilters/gaussian.cpp:86-98 non-CUDA branch: estrin in x^2; tent.cpp:41-43)
-MIB_D float rfilter_eval(const DScene &sc, float x) {
+MIB_D float rfilter_eval(float x) {
     if (sc.d.sensor.rfilter == MIB_RFILTER_GAUSSIAN) {
         // drjit estrin_impl (math.h:26-41) for 10 coefficients
         const float *c = sc.rf_coeff;
@@ -71,7 +71,7 @@ MIB_D float rfilter_eval(const DScene &sc, float x) {
 // ImageBlock::put for a reconstruction filter (imageblock.cpp:261-530, JIT recorded-loop forms, border 0): fn(pixel, weight)
 // for every pixel of the footprint.  Coalesced form when spp >= 4 (integrator.cpp:320), general form otherwise.
 template <typename Fn>
-MIB_D void filter_footprint(const DScene &sc, uint32_t spp, float pos_x, float pos_y, Fn &&fn) {
+MIB_D void filter_footprint(uint32_t spp, float pos_x, float pos_y, Fn &&fn) {
     const mib_sensor &s = sc.d.sensor;
     const float radius = s.rfilter_radius;
     const uint32_t size_x = (uint32_t) s.crop_width, size_y = (uint32_t) s.crop_height;
@@ -81,10 +81,10 @@ MIB_D void filter_footprint(const DScene &sc, uint32_t spp, float pos_x, float p
         uint32_t x = (uint32_t) (pix - s.crop_offset_x), y = (uint32_t) (piy - s.crop_offset_y);
         float rel_x = ((float) pix + .5f) - pos_x, rel_y = ((float) piy + .5f) - pos_y;
         for (uint32_t ys = 0; ys < count; ++ys) {
-            float weight_y = rfilter_eval(sc, rel_y + (float) ys);
+            float weight_y = rfilter_eval(rel_y + (float) ys);
             bool active_1 = y + ys < size_y;
             for (uint32_t xs = 0; xs < count; ++xs) {
-                float weight = rfilter_eval(sc, rel_x + (float) xs) * weight_y;
+                float weight = rfilter_eval(rel_x + (float) xs) * weight_y;
                 if (active_1 && x + xs < size_x) fn((size_t) (y + ys) * size_x + (x + xs), weight);
             }
         }
@@ -98,10 +98,10 @@ MIB_D void filter_footprint(const DScene &sc, uint32_t spp, float pos_x, float p
         bool active = x0 <= x1 && y0 <= y1;
         float rel_x = (float) x0 - pfx, rel_y = (float) y0 - pfy;
         for (uint32_t ys = 0; ys < count; ++ys) {
-            float weight_y = rfilter_eval(sc, rel_y + (float) ys);
+            float weight_y = rfilter_eval(rel_y + (float) ys);
             bool active_1 = active && (y0 + ys <= y1);
             for (uint32_t xs = 0; xs < count; ++xs) {
-                float weight = rfilter_eval(sc, rel_x + (float) xs) * weight_y;
+                float weight = rfilter_eval(rel_x + (float) xs) * weight_y;
                 if (active_1 && (x0 + xs <= x1)) fn((size_t) (y0 + ys) * size_x + (x0 + xs), weight);
             }
         }
@@ -110,7 +110,7 @@ MIB_D void filter_footprint(const DScene &sc, uint32_t spp, float pos_x, float p
 
 // MODE: 0 volpath, 1 volpathaos, 2 prbvolpath (primal), 3 prb_volpathaos (primal)
 template <int SPEC, int MODE>
-__global__ void __launch_bounds__(128, MIB_MINB) k_forward(const __grid_constant__ DScene sc, const __grid_constant__ LaunchParams lp) {
+__global__ void __launch_bounds__(128, MIB_MINB) k_forward(const __grid_constant__ LaunchParams lp) {
     constexpr int C = RawChannels<SPEC>::C, NR = ST<SPEC>::NR;
     const mib_sensor &sn = sc.d.sensor;
     uint64_t tid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(128, MIB_MINB) k_forward(const __grid_constant
             return;
         }
         if (lp.mode == 0 && sn.rfilter != MIB_RFILTER_BOX) {
-            filter_footprint(sc, lp.spp, sx, sy, [&](size_t pixel, float w) {
+            filter_footprint(lp.spp, sx, sy, [&](size_t pixel, float w) {
 #pragma unroll
                 for (int c = 0; c < C; ++c) atomicAdd(lp.film + pixel * C + c, aov[c] * w);
             });
@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(128, MIB_MINB) k_forward(const __grid_constant
         float ax = fma_(sx, scale_x, offset_x), ay = fma_(sy, scale_y, offset_y);
         float apx = .5f, apy = .5f;
         if (sn.needs_aperture_sample) { apx = rng.next(); apy = rng.next(); }
-        return sensor_ray(sc, ax, ay, apx, apy);
+        return sensor_ray(ax, ay, apx, apy);
     };
 
     if constexpr (MODE <= 1) {
@@ -195,10 +195,10 @@ __global__ void __launch_bounds__(128, MIB_MINB) k_forward(const __grid_constant
             if (!st.active && lane < l1) {
                 cur = lane++;
                 ray0 = start(cur, rng, sx, sy);
-                path_init<SPEC>(sc, rng, ray0, st);
+                path_init<SPEC>(rng, ray0, st);
             }
             if (st.active) {
-                path_step<SPEC, MODE == 1>(sc, rng, cnt, st);
+                path_step<SPEC, MODE == 1>(rng, cnt, st);
                 if (!st.active) finish(cur, ray0, sx, sy, st.R);
             }
         }
@@ -208,9 +208,9 @@ __global__ void __launch_bounds__(128, MIB_MINB) k_forward(const __grid_constant
                 if (lane >= l1) break;
                 cur = lane++;
                 ray0 = start(cur, rng, sx, sy);
-                path_init<SPEC>(sc, rng, ray0, st);
+                path_init<SPEC>(rng, ray0, st);
             }
-            path_step<SPEC, MODE == 1>(sc, rng, cnt, st);
+            path_step<SPEC, MODE == 1>(rng, cnt, st);
             if (!st.active) finish(cur, ray0, sx, sy, st.R);
         }
 #endif
@@ -221,7 +221,7 @@ __global__ void __launch_bounds__(128, MIB_MINB) k_forward(const __grid_constant
             Ray ray = start(lane, rng, sx, sy);
             Sink sink;
             sink.init();
-            prb_walk<SPEC, MODE == 3>(sc, rng, cnt, ray, false, nullptr, nullptr, sink, R);
+            prb_walk<SPEC, MODE == 3>(rng, cnt, ray, false, nullptr, nullptr, sink, R);
             finish(lane, ray, sx, sy, R);
         }
     }
@@ -253,7 +253,7 @@ __global__ void __launch_bounds__(128, MIB_MINB) k_forward(const __grid_constant
 // k_forward so that neighbouring threads walk neighbouring samples of one pixel.
 // ---------------------------------------------------------------------------
 template <int SPEC>
-__global__ void __launch_bounds__(128, MIB_MINB_ADJ) k_adjoint(const __grid_constant__ DScene sc, const __grid_constant__ LaunchParams lp,
+__global__ void __launch_bounds__(128, MIB_MINB_ADJ) k_adjoint(const __grid_constant__ LaunchParams lp,
                                                  const __grid_constant__ AdjParams ap) {
     constexpr int NR = ST<SPEC>::NR, Cd = SPEC == MIB_SPEC_MONO ? 1 : (SPEC == MIB_SPEC_RGB ? 3 : 4);
     constexpr bool AOS = ST<SPEC>::POL;
@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(128, MIB_MINB_ADJ) k_adjoint(const __grid_cons
 #pragma unroll
                 for (int i = 0; i < NR; ++i) Lp[i] = st.L[i];
                 rng = start_rng;
-                prb_init<SPEC, AOS>(sc, rng, ray0, true, Lp, dl, st);
+                prb_init<SPEC, AOS>(rng, ray0, true, Lp, dl, st);
                 pass = 1;
             } else if (lane < l1) {
                 uint64_t cur = lane++;
@@ -298,7 +298,7 @@ __global__ void __launch_bounds__(128, MIB_MINB_ADJ) k_adjoint(const __grid_cons
                 float ax = fma_(sx, scale_x, offset_x), ay = fma_(sy, scale_y, offset_y);
                 float apx = .5f, apy = .5f;
                 if (sn.needs_aperture_sample) { apx = rng.next(); apy = rng.next(); }
-                ray0 = sensor_ray(sc, ax, ay, apx, apy);
+                ray0 = sensor_ray(ax, ay, apx, apy);
                 n_samples++;
                 dl[0] = dl[1] = dl[2] = dl[3] = 0.f;
                 if (ap.render_1) {
@@ -308,25 +308,25 @@ __global__ void __launch_bounds__(128, MIB_MINB_ADJ) k_adjoint(const __grid_cons
                     int ix = (int) floorf(sx) - sn.crop_offset_x, iy = (int) floorf(sy) - sn.crop_offset_y;
                     if (sn.rfilter != MIB_RFILTER_BOX) {
                         // adjoint of splat + weight division (hdrfilm.cpp:304-418): dL_c = sum_p grad[p,c] / W[p] * w_p
-                        filter_footprint(sc, lp.spp, sx, sy, [&](size_t pixel, float w) {
+                        filter_footprint(lp.spp, sx, sy, [&](size_t pixel, float w) {
                             float W = __ldg(sc.weight_film + pixel), dv = W == 0.f ? 1.f : W;
 #pragma unroll
-                            for (int c = 0; c < Cd; ++c) dl[c] += __fdiv_rn(__ldg(ap.grad_image + pixel * Cd + c), dv) * w;
+                            for (int c = 0; c < Cd; ++c) dl[c] += div_(__ldg(ap.grad_image + pixel * Cd + c), dv) * w;
                         });
                     } else if ((uint32_t) ix < (uint32_t) sn.crop_width && (uint32_t) iy < (uint32_t) sn.crop_height) {
                         size_t pixel = (size_t) iy * sn.crop_width + ix;
 #pragma unroll
-                        for (int c = 0; c < Cd; ++c) dl[c] = __fdiv_rn(__ldg(ap.grad_image + pixel * Cd + c), (float) lp.spp);
+                        for (int c = 0; c < Cd; ++c) dl[c] = div_(__ldg(ap.grad_image + pixel * Cd + c), (float) lp.spp);
                     }
                 }
                 start_rng = rng;
-                prb_init<SPEC, AOS>(sc, rng, ray0, false, nullptr, nullptr, st);
+                prb_init<SPEC, AOS>(rng, ray0, false, nullptr, nullptr, st);
                 pass = 0;
             }
         }
-        if (st.active) prb_step<SPEC, AOS>(sc, rng, cnt, sink, st);
+        if (st.active) prb_step<SPEC, AOS>(rng, cnt, sink, st);
     }
-    sink.flush(sc);
+    sink.flush();
     unsigned long long cv[6] = { cnt.n_lookups, cnt.n_real, cnt.n_null, cnt.n_nee_steps, cnt.n_surface, n_samples };
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
@@ -336,10 +336,10 @@ __global__ void __launch_bounds__(128, MIB_MINB_ADJ) k_adjoint(const __grid_cons
     }
 }
 
-template <int SPEC> void launch_k_adjoint(const DScene &sc, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, cudaStream_t st);
+template <int SPEC> void launch_k_adjoint(const DScene &scene, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, cudaStream_t st);
 
 // Filter-weight film of the whole wavefront (positions only): the denominator HDRFilm::develop divides by.
-static __global__ void k_weight_film(const __grid_constant__ DScene sc, uint32_t seed_value, uint32_t spp, uint64_t total, float *wfilm) {
+static __global__ void k_weight_film(uint32_t seed_value, uint32_t spp, uint64_t total, float *wfilm) {
     const mib_sensor &sn = sc.d.sensor;
     for (uint64_t lane = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; lane < total; lane += (uint64_t) gridDim.x * blockDim.x) {
         Pcg32 rng;
@@ -348,7 +348,7 @@ static __global__ void k_weight_film(const __grid_constant__ DScene sc, uint32_t
         uint32_t py = idx / (uint32_t) sn.crop_width, px = idx - (uint32_t) sn.crop_width * py;
         float posx = (float) ((int) px + sn.crop_offset_x), posy = (float) ((int) py + sn.crop_offset_y);
         float jx = rng.next(), jy = rng.next();
-        filter_footprint(sc, spp, posx + jx, posy + jy, [&](size_t pixel, float w) { atomicAdd(wfilm + pixel, w); });
+        filter_footprint(spp, posx + jx, posy + jy, [&](size_t pixel, float w) { atomicAdd(wfilm + pixel, w); });
     }
 }
 
@@ -359,11 +359,11 @@ __global__ void k_develop(const float *raw, float *out, size_t npix, uint32_t sp
     if (p >= npix) return;
     if constexpr (SPEC == MIB_SPEC_RGB) {
         float w = raw[4 * p + 3], dv = (w == 0.f) ? 1.f : w;
-        for (int c = 0; c < 3; ++c) out[3 * p + c] = __fdiv_rn(raw[4 * p + c], dv);
+        for (int c = 0; c < 3; ++c) out[3 * p + c] = div_(raw[4 * p + c], dv);
     } else if constexpr (SPEC == MIB_SPEC_MONO) {
         float I = raw[2 * p], w = raw[2 * p + 1], dv = (w == 0.f) ? 1.f : w;
         float lum = I * 0.212671f + I * 0.715160f + I * 0.072169f;
-        out[p] = __fdiv_rn(lum, dv);
+        out[p] = div_(lum, dv);
     } else {
         for (int c = 0; c < 4; ++c) out[4 * p + c] = (float) ((double) raw[4 * p + c] / (double) spp);
     }

@@ -13,10 +13,15 @@
 #include <vector>
 #include <cmath>
 #include <stdexcept>
+#include <mutex>
 
 using namespace mib;
 
-static_assert(sizeof(DScene) < 32000, "DScene must fit the kernel parameter space");
+static_assert(sizeof(DScene) < 32000, "DScene must fit the constant bank next to the other module constants");
+
+// The device scene is a __constant__ symbol per kernel module: launches of different scenes from concurrent host threads
+// are serialised from the upload to the end of the kernel (every render entry point synchronises its stream anyway).
+static std::mutex g_launch_mutex;
 
 static thread_local std::string g_err;
 std::string &mib_error_slot() { return g_err; }   // shared with mie.cu
@@ -255,8 +260,14 @@ static void launch_forward_pool(mib_scene *s, LaunchParams lp) {
 template <int SPEC, int MODE>
 static void launch_forward(mib_scene *s, const LaunchParams &lp) {
     if constexpr (MODE <= 1) {
+        // auto: the pool kernel when the scene has a heterogeneous medium (long walks of null collisions and shadow steps:
+        // C3 211 vs 126 Msamples/s), the one-thread-one-path kernel for homogeneous scenes (few, heavy events: C2 433 vs 178).
         const char *k = getenv("MIB_FORWARD_KERNEL");
-        if (!(k && strcmp(k, "thread") == 0)) { launch_forward_pool<SPEC, MODE>(s, lp); return; }
+        bool pool = false;
+        for (int m = 0; m < s->ds.d.n_media; ++m) pool = pool || s->ds.d.media[m].type != MIB_MEDIUM_HOMOGENEOUS;
+        if (k && strcmp(k, "thread") == 0) pool = false;
+        if (k && strcmp(k, "pool") == 0) pool = true;
+        if (pool) { launch_forward_pool<SPEC, MODE>(s, lp); return; }
     }
     uint64_t lanes = lp.lane_end - lp.lane_begin;
     uint64_t threads = (lanes + lp.spt - 1) / lp.spt;
@@ -313,6 +324,7 @@ static void fetch_counters(mib_scene *s, float ms, uint64_t launches) {
 static void run_forward(mib_scene *s, uint32_t seed, uint32_t spp, int mode, float *per_sample_dev) {
     if (!s->committed) throw std::runtime_error("mib_scene_commit() must be called before rendering");
     if (spp == 0) throw std::runtime_error("spp must be > 0");
+    std::lock_guard<std::mutex> launch_lock(g_launch_mutex);
     if (s->ds.d.sensor.rfilter != MIB_RFILTER_BOX && s->ds.d.spectrum == MIB_SPEC_MONO_POLARIZED && mode == 0)
         throw std::runtime_error("the polarized Stokes film supports only the box filter");
     CK(cudaSetDevice(s->device));
