@@ -29,10 +29,24 @@
 
 namespace mib {
 
+#ifndef MIB_POOL_GROUPS
+#define MIB_POOL_GROUPS 1
+#endif
+#ifndef MIB_POOL_CLAIM
+#define MIB_POOL_CLAIM 32
+#endif
+constexpr int kPoolClaim = MIB_POOL_CLAIM; // slots a warp claims at once (processed as sub-batches of 32: one queue transaction and one
+                                           // pass over the stage's code for up to kPoolClaim paths)
 constexpr int kPoolChunk = 256;            // lanes per interleaved chunk
-constexpr int kPoolMainIters = 2;          // MAIN: null collisions handled per batch before the slot is re-queued
-constexpr int kPoolNeeIters = 4;           // NEE: shadow steps per batch
-constexpr unsigned kPoolSpinLimit = 1u << 26;
+#ifndef MIB_POOL_MAIN_ITERS
+#define MIB_POOL_MAIN_ITERS 2
+#endif
+#ifndef MIB_POOL_NEE_ITERS
+#define MIB_POOL_NEE_ITERS 4
+#endif
+constexpr int kPoolMainIters = MIB_POOL_MAIN_ITERS;   // MAIN: null collisions handled per batch before the slot is re-queued
+constexpr int kPoolNeeIters = MIB_POOL_NEE_ITERS;     // NEE: shadow steps per batch
+constexpr unsigned kPoolSpinLimit = 1u << 22;   // watchdog of the two wait loops (idle poll: x 100 ns; ring entry: x ~50 ns)
 constexpr uint32_t kNoLane = 0xffffffffu;
 constexpr unsigned kRingEmpty = 0xffffu;
 
@@ -60,6 +74,9 @@ template <int SPEC> struct PoolL {
     static constexpr int F_NA = F_NDIST + 3;
     static constexpr int F_NW = F_NA + NR;
     static constexpr int F_COUNT = F_NW + 1;
+    // slots per CTA: as many as fit into the 227 KB of opt-in shared memory (state words + one 16-bit entry per stage ring),
+    // a compile-time constant so that every field access is one LDS / STS with an immediate offset
+    static constexpr int P = ((232448 - 256) / (F_COUNT * 4 + 2 * 6)) / 32 * 32;
 };
 
 // flags word
@@ -71,20 +88,18 @@ MIB_D uint32_t fl_nee_medium(uint32_t f) { return (f >> 16) & 0xff; }    // nee.
 struct PoolShared {
     unsigned head[8], tail[8];
     unsigned next_local, total_local, retired, error;
+    unsigned group, pad[3];
 };
 
-MIB_D size_t pool_ring_offset() { return (sizeof(PoolShared) + 15) & ~(size_t) 15; }
-MIB_D size_t pool_state_offset(int P) { return (pool_ring_offset() + (size_t) C_COUNT * P * sizeof(uint16_t) + 15) & ~(size_t) 15; }
-template <int SPEC> size_t pool_smem_bytes(int P) {
-    size_t ring = (sizeof(PoolShared) + 15) & ~(size_t) 15;
-    size_t state = (ring + (size_t) C_COUNT * P * sizeof(uint16_t) + 15) & ~(size_t) 15;
-    return state + (size_t) PoolL<SPEC>::F_COUNT * P * sizeof(uint32_t);
+__host__ __device__ constexpr size_t pool_ring_offset() { return (sizeof(PoolShared) + 15) & ~(size_t) 15; }
+__host__ __device__ constexpr size_t pool_state_offset(int P) { return (pool_ring_offset() + (size_t) C_COUNT * P * sizeof(uint16_t) + 15) & ~(size_t) 15; }
+template <int SPEC> __host__ __device__ constexpr size_t pool_smem_bytes() {
+    return pool_state_offset(PoolL<SPEC>::P) + (size_t) PoolL<SPEC>::F_COUNT * PoolL<SPEC>::P * sizeof(uint32_t);
 }
 
 // slot accessors
-struct PoolMem {
+template <int P> struct PoolMem {
     uint32_t *pw;
-    int P;
     MIB_D float f(int field, int slot) const { return __uint_as_float(pw[field * P + slot]); }
     MIB_D uint32_t u(int field, int slot) const { return pw[field * P + slot]; }
     MIB_D void sf(int field, int slot, float v) const { pw[field * P + slot] = __float_as_uint(v); }
@@ -127,12 +142,12 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
     constexpr bool AOS = MODE == 1;
     constexpr unsigned FULL = 0xffffffffu;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int P = (int) lp.pool_slots;
+    constexpr int P = L::P;
+    static_assert(pool_smem_bytes<SPEC>() <= 232448, "pool does not fit the shared memory of sm_100");
     PoolShared *ps = reinterpret_cast<PoolShared *>(smem_raw);
     volatile uint16_t *ring = reinterpret_cast<volatile uint16_t *>(smem_raw + pool_ring_offset());
-    PoolMem pm;
+    PoolMem<P> pm;
     pm.pw = reinterpret_cast<uint32_t *>(smem_raw + pool_state_offset(P));
-    pm.P = P;
     const mib_sensor &sn = sc.d.sensor;
     const unsigned lane_id = threadIdx.x & 31;
 
@@ -153,6 +168,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
         ps->total_local = (unsigned) total_local;
         ps->retired = 0;
         ps->error = 0;
+        ps->group = 1;                                    // START is in group 1
     }
     for (int i = threadIdx.x; i < C_COUNT * P; i += blockDim.x) ring[i] = (uint16_t) (i < P ? i : kRingEmpty);
     for (int s = threadIdx.x; s < P; s += blockDim.x) pm.su(L::F_LANE, s, kNoLane);
@@ -215,22 +231,45 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
 
     unsigned idle_spins = 0;
     while (true) {
-        // ---- 1. claim a batch ----
+        // ---- 1. claim a batch: up to kPoolClaim slots of ONE class (lane 0 scans the six queues, one CAS) ----
+        // Policy (MIB_POOL_GROUPS): the classes form two groups, {MAIN, NEE} -- the loops of the walk, where a slot
+        // is executed several times in a row -- and {START, SCATTER, PHASE, BSDF}.  All warps of the CTA serve the
+        // current group until it has no full batch left and then switch together, so that the code live in the
+        // instruction cache at any time is one group's, not the whole kernel's.
         int cls = -1;
-        unsigned base = 0, n = 0;
+        unsigned base = 0, n_total = 0;
         if (lane_id == 0) {
             while (true) {
-                unsigned best_n = 0, best_h = 0;
-                int best = -1;
+                unsigned a[C_COUNT], h[C_COUNT];
 #pragma unroll
                 for (int c = 0; c < C_COUNT; ++c) {
-                    unsigned h = *(volatile unsigned *) &ps->head[c], t = *(volatile unsigned *) &ps->tail[c];
-                    unsigned a = t - h;
-                    if (a > best_n) { best_n = a; best = c; best_h = h; }
+                    h[c] = *(volatile unsigned *) &ps->head[c];
+                    a[c] = *(volatile unsigned *) &ps->tail[c] - h[c];
                 }
+                int best = -1;
+#if MIB_POOL_GROUPS
+                const unsigned g = *(volatile unsigned *) &ps->group;
+                int best_in = -1, best_out = -1;
+                unsigned n_in = 0, n_out = 0;
+#pragma unroll
+                for (int c = 0; c < C_COUNT; ++c) {
+                    const bool in = ((c == C_MAIN || c == C_NEE) ? 0u : 1u) == g;
+                    if (in) { if (a[c] > n_in) { n_in = a[c]; best_in = c; } }
+                    else { if (a[c] > n_out) { n_out = a[c]; best_out = c; } }
+                }
+                if (n_in >= 32u || (n_in > 0u && n_out < 32u)) best = best_in;
+                else if (n_out > 0u) { ps->group = g ^ 1u; best = best_out; }
+#else
+                unsigned best_n = 0;
+#pragma unroll
+                for (int c = 0; c < C_COUNT; ++c) if (a[c] > best_n) { best_n = a[c]; best = c; }
+#endif
                 if (best >= 0) {
-                    unsigned take = best_n < 32u ? best_n : 32u;
-                    if (atomicCAS(&ps->head[best], best_h, best_h + take) == best_h) { cls = best; base = best_h; n = take; break; }
+                    unsigned av = 0, hh = 0;
+#pragma unroll
+                    for (int c = 0; c < C_COUNT; ++c) if (c == best) { av = a[c]; hh = h[c]; }
+                    unsigned take = av < (unsigned) kPoolClaim ? av : (unsigned) kPoolClaim;
+                    if (atomicCAS(&ps->head[best], hh, hh + take) == hh) { cls = best; base = hh; n_total = take; break; }
                     continue;
                 }
                 if (*(volatile unsigned *) &ps->retired >= (unsigned) P || *(volatile unsigned *) &ps->error) break;
@@ -240,19 +279,31 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
         }
         cls = __shfl_sync(FULL, cls, 0);
         base = __shfl_sync(FULL, base, 0);
-        n = __shfl_sync(FULL, n, 0);
+        n_total = __shfl_sync(FULL, n_total, 0);
         if (cls < 0) break;
+        // Take the claimed ids out of the ring right away (a ring position may be reused as soon as it is emptied;
+        // a producer that has reserved a position but not yet written it is waited for).
+        int claimed[kPoolClaim / 32];
+#pragma unroll
+        for (int k = 0; k < kPoolClaim / 32; ++k) {
+            claimed[k] = 0;
+            if (k * 32u + lane_id < n_total) {
+                unsigned pos = (base + k * 32u + lane_id) % (unsigned) P;
+                unsigned v, sp = 0;
+                while ((v = ring[cls * P + pos]) == kRingEmpty) {
+                    if (++sp > kPoolSpinLimit) { ps->error = 2; v = 0; break; }
+                }
+                ring[cls * P + pos] = (uint16_t) kRingEmpty;
+                claimed[k] = (int) v;
+            }
+        }
+#pragma unroll 1
+        for (unsigned sub = 0; sub < n_total; sub += 32u) {
+        const unsigned n = n_total - sub < 32u ? n_total - sub : 32u;
         const bool has = lane_id < n;
         int slot = 0;
-        if (has) {
-            unsigned pos = (base + lane_id) % (unsigned) P;
-            unsigned v, sp = 0;
-            while ((v = ring[cls * P + pos]) == kRingEmpty) {
-                if (++sp > kPoolSpinLimit) { ps->error = 2; v = 0; break; }
-            }
-            ring[cls * P + pos] = (uint16_t) kRingEmpty;
-            slot = (int) v;
-        }
+#pragma unroll
+        for (int k = 0; k < kPoolClaim / 32; ++k) if (sub == k * 32u) slot = claimed[k];
         __threadfence_block();
 
         // ---- 2.-3. run the stage ----
@@ -527,6 +578,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                 }
             }
         }
+        }   // sub-batches of the claim
     }
 
     if (lp.mode == 1) {
@@ -548,6 +600,6 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
 }
 
 template <int SPEC, int MODE> void launch_k_forward_pool(const DScene &scene, const LaunchParams &lp, unsigned blocks, unsigned threads, cudaStream_t st);
-template <int SPEC, int MODE> size_t pool_bytes(int slots);   // dynamic shared memory of a pool of `slots` paths
+template <int SPEC, int MODE> int pool_slots();   // paths resident per CTA (PoolL<SPEC>::P)
 
 } // namespace mib

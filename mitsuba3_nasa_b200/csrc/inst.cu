@@ -11,7 +11,7 @@ template <> void launch_k_forward<INST_SPEC, INST_MODE>(const DScene &scene, con
 #elif defined(INST_POOL)
 template <> void launch_k_forward_pool<INST_SPEC, INST_MODE>(const DScene &scene, const LaunchParams &lp, unsigned blocks, unsigned threads, cudaStream_t st) {
     static bool configured = false;
-    const size_t smem = pool_smem_bytes<INST_SPEC>((int) lp.pool_slots);
+    const size_t smem = pool_smem_bytes<INST_SPEC>();
     if (!configured) {
         cudaFuncSetAttribute(k_forward_pool<INST_SPEC, INST_MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
         configured = true;
@@ -19,7 +19,7 @@ template <> void launch_k_forward_pool<INST_SPEC, INST_MODE>(const DScene &scene
     cudaMemcpyToSymbolAsync(sc, &scene, sizeof(DScene), 0, cudaMemcpyHostToDevice, st);
     k_forward_pool<INST_SPEC, INST_MODE><<<blocks, threads, smem, st>>>(lp);
 }
-template <> size_t pool_bytes<INST_SPEC, INST_MODE>(int slots) { return pool_smem_bytes<INST_SPEC>(slots); }
+template <> int pool_slots<INST_SPEC, INST_MODE>() { return PoolL<INST_SPEC>::P; }
 #elif defined(INST_ADJ)
 template <> void launch_k_adjoint<INST_SPEC>(const DScene &scene, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, cudaStream_t st) {
     cudaMemcpyToSymbolAsync(sc, &scene, sizeof(DScene), 0, cudaMemcpyHostToDevice, st);

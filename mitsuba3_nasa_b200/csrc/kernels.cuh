@@ -31,7 +31,6 @@ struct LaunchParams {
     double *sums;              // [4]
     float *per_sample;         // [lanes*C] (mode 2)
     unsigned long long *counters; // [8]: lookups, real, null, nee_steps, surface, samples, -, pool error code
-    uint32_t pool_slots;       // k_forward_pool: paths resident per CTA
 };
 
 // launchers defined in inst.cu (one per object file)

@@ -228,7 +228,7 @@ static uint32_t pick_spt(uint64_t lanes, uint32_t spp) {
 namespace mib {
 template <int SPEC, int MODE> void launch_k_forward(const DScene &sc, const LaunchParams &lp, unsigned blocks, cudaStream_t st);
 template <int SPEC, int MODE> void launch_k_forward_pool(const DScene &sc, const LaunchParams &lp, unsigned blocks, unsigned threads, cudaStream_t st);
-template <int SPEC, int MODE> size_t pool_bytes(int slots);
+template <int SPEC, int MODE> int pool_slots();
 template <int SPEC> void launch_k_adjoint(const DScene &sc, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, cudaStream_t st);
 }
 
@@ -239,7 +239,7 @@ static int env_int(const char *name, int dflt) {
 
 // Forward kernel choice: the persistent path-pool kernel (dpool.cuh) for volpath / volpathaos; MIB_FORWARD_KERNEL=thread
 // selects the one-thread-one-path kernel (A/B runs, profiles/).  Pool geometry: one CTA per SM, MIB_POOL_NT threads,
-// as many slots as fit in the 227 KB of shared memory (MIB_POOL_SLOTS overrides), fewer CTAs for tiny wavefronts.
+// as many slots as fit in the 227 KB of shared memory (compile-time, PoolL<SPEC>::P), fewer CTAs for tiny wavefronts.
 template <int SPEC, int MODE>
 static void launch_forward_pool(mib_scene *s, LaunchParams lp) {
     uint64_t lanes = lp.lane_end - lp.lane_begin;
@@ -248,11 +248,9 @@ static void launch_forward_pool(mib_scene *s, LaunchParams lp) {
     CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, s->device));
     int threads = env_int("MIB_POOL_NT", 384);
     threads = std::max(32, std::min(threads, MIB_POOL_NT)) & ~31;
-    int slots = std::max(64, std::min(env_int("MIB_POOL_SLOTS", 8192), 8192)) & ~31;
-    while (slots > 64 && pool_bytes<SPEC, MODE>(slots) > 232448) slots -= 32;     // 227 KB opt-in limit of sm_100
+    const int slots = pool_slots<SPEC, MODE>();
     uint64_t blocks = (lanes + 2ull * slots - 1) / (2ull * slots);
     blocks = std::max<uint64_t>(1, std::min<uint64_t>(blocks, (uint64_t) n_sm * env_int("MIB_POOL_CTAS_PER_SM", 1)));
-    lp.pool_slots = (uint32_t) slots;
     launch_k_forward_pool<SPEC, MODE>(s->ds, lp, (unsigned) blocks, (unsigned) threads, s->stream);
     CK(cudaGetLastError());
 }
@@ -338,7 +336,6 @@ static void run_forward(mib_scene *s, uint32_t seed, uint32_t spp, int mode, flo
     lp.sums = s->sums;
     lp.per_sample = per_sample_dev;
     lp.counters = s->counters;
-    lp.pool_slots = 0;
     CK(cudaMemsetAsync(s->counters, 0, 8 * sizeof(unsigned long long), s->stream));
     if (mode == 0) CK(cudaMemsetAsync(s->film_raw, 0, s->film_raw_n * sizeof(float), s->stream));
     if (mode == 1) CK(cudaMemsetAsync(s->sums, 0, 8 * sizeof(double), s->stream));

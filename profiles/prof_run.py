@@ -23,6 +23,15 @@ elif which == 'c3':
         scene.device.render(k, 0 or d['sensor']['sampler']['sample_count'], develop=False, to_host=False)
         c = scene.device.counters()
         print('c3', c['kernel_ms'], 'ms', c['n_samples'] / c['kernel_ms'] / 1e3, 'Msamples/s', c)
+elif which == 'c3pol':
+    # BASELINE C3 as specified: polarized, Mie x lognormal tabulated phase
+    mi.set_variant('llvm_ad_mono_polarized')
+    d = scenes.c3_cloud(res=512, spp=max(1, (1 << lg) // (512 * 512)), grid_res=256)
+    scene = mi.load_dict(d)
+    for k in range(3):
+        scene.device.render(k, d['sensor']['sampler']['sample_count'], develop=False, to_host=False)
+        c = scene.device.counters()
+        print('c3pol', c['kernel_ms'], 'ms', c['n_samples'] / c['kernel_ms'] / 1e3, 'Msamples/s', c)
 else:
     mi.set_variant('llvm_ad_rgb')
     scene = mi.load_dict(scenes.c1_homogeneous_cube())
