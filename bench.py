@@ -258,30 +258,39 @@ def run_ours(args):
 
 
 def grid_roofline(device, peaks):
-    """C3-shaped workload (256^3 grid, global majorant, tabulated phase) for the memory-side roofline."""
+    """C3-shaped workload (256^3 grid, global majorant, Mie x lognormal tabulated phase) for the memory-side roofline:
+    the path-pool kernel (k_forward_pool), mono volpath and -- as BASELINE configs[2] reads -- mono_polarized volpath."""
     import torch
     import mitsuba3_nasa_b200 as mi
     from mitsuba3_nasa_b200 import scenes
-    mi.set_variant('llvm_ad_mono')
-    d = scenes.c3_cloud(res=512, spp=16, grid_res=256)       # BASELINE C3 scene (Mie x lognormal table, 1801 nodes), 512^2 x 16 spp
-    scene = mi.load_dict(d, device=device)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-    ms, cnt = [], None
-    for k in range(4):
-        flush.zero_()                                      # evict the 64 MiB grid from the 126 MB L2
-        torch.cuda.synchronize()
-        scene.device.render(k, 16, develop=False, to_host=False)
-        cnt = scene.device.counters()
-        if k > 0:
-            ms.append(cnt['kernel_ms'])
-    t = float(np.mean(ms)) / 1e3
-    b = algorithmic_bytes(cnt, 2)
     hbm = peaks.get("hbm_gbs", 6650.0)
-    return {"bound": "hbm", "achieved": b / t / 1e9, "peak": hbm, "unit": "GB/s", "frac": b / t / 1e9 / hbm, "traffic": None,
-            "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback",
-            "kernel": "k_forward<mono, volpath>", "workload": "C3 scene (256^3 grid, Mie x lognormal table) at 512x512x16 spp",
-            "msamples_per_s": cnt['n_samples'] / t / 1e6, "ms": t * 1e3, "l2": "flushed between iterations (256 MiB write)",
-            "events": cnt}
+    out = {}
+    for variant, channels in (('llvm_ad_mono', 2), ('llvm_ad_mono_polarized', 4)):
+        mi.set_variant(variant)
+        d = scenes.c3_cloud(res=512, spp=16, grid_res=256)   # BASELINE C3 scene (Mie x lognormal table, 1801 nodes), 512^2 x 16 spp
+        scene = mi.load_dict(d, device=device)
+        ms, cnt = [], None
+        for k in range(4):
+            flush.zero_()                                      # evict the 64 MiB grid from the 126 MB L2
+            torch.cuda.synchronize()
+            scene.device.render(k, 16, develop=False, to_host=False)
+            cnt = scene.device.counters()
+            if k > 0:
+                ms.append(cnt['kernel_ms'])
+        t = float(np.mean(ms)) / 1e3
+        b = algorithmic_bytes(cnt, channels)
+        leg = {"bound": "hbm", "achieved": b / t / 1e9, "peak": hbm, "unit": "GB/s", "frac": b / t / 1e9 / hbm, "traffic": None,
+               "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback",
+               "kernel": "k_forward_pool<%s, volpath>" % variant.replace('llvm_ad_', ''),
+               "workload": "C3 scene (256^3 grid, Mie x lognormal table) at 512x512x16 spp, %s" % variant,
+               "msamples_per_s": cnt['n_samples'] / t / 1e6, "ms": t * 1e3, "l2": "flushed between iterations (256 MiB write)",
+               "events": cnt}
+        if variant == 'llvm_ad_mono':
+            out = leg
+        else:
+            out["polarized"] = leg
+    return out
 
 
 def adjoint_bench(device, rank, world):

@@ -32,11 +32,17 @@ namespace mib {
 #ifndef MIB_POOL_GROUPS
 #define MIB_POOL_GROUPS 1
 #endif
-#ifndef MIB_POOL_CLAIM
-#define MIB_POOL_CLAIM 32
+#ifndef MIB_POOL_RINGS
+#define MIB_POOL_RINGS 8
 #endif
-constexpr int kPoolClaim = MIB_POOL_CLAIM; // slots a warp claims at once (processed as sub-batches of 32: one queue transaction and one
-                                           // pass over the stage's code for up to kPoolClaim paths)
+constexpr int kPoolRings = MIB_POOL_RINGS;   // stage rings laid out in shared memory (forward: 6 classes, adjoint: 7)
+// Ring capacity = P + kPoolRingSlack cells.  A cell is reused kPoolRingCap positions later; a queue never holds more than P
+// entries, so the cell being written was claimed at least kPoolRingSlack positions ago -- 16 batches, while a consumer takes
+// its entry out of the ring within a few hundred cycles of claiming it.  (With capacity P exactly, the push of the last
+// batch of a group could land on the cells a warp had just claimed when all other slots were queued in one class: lost
+// entries.)  pool_push checks that the cell it writes is empty and raises error 3 otherwise.
+constexpr int kPoolRingSlack = 512;
+template <int P> __host__ __device__ constexpr int pool_ring_cap() { return P + kPoolRingSlack; }
 constexpr int kPoolChunk = 256;            // lanes per interleaved chunk
 #ifndef MIB_POOL_MAIN_ITERS
 #define MIB_POOL_MAIN_ITERS 2
@@ -50,7 +56,8 @@ constexpr unsigned kPoolSpinLimit = 1u << 22;   // watchdog of the two wait loop
 constexpr uint32_t kNoLane = 0xffffffffu;
 constexpr unsigned kRingEmpty = 0xffffu;
 
-enum { C_START = 0, C_MAIN = 1, C_SCAT = 2, C_NEE = 3, C_PHASE = 4, C_BSDF = 5, C_COUNT = 6 };
+enum { C_START = 0, C_MAIN = 1, C_SCAT = 2, C_NEE = 3, C_PHASE = 4, C_BSDF = 5, C_NEEG = 6, C_COUNT = 6 };   // C_NEEG: adjoint only (apool.cuh)
+constexpr unsigned kFwdGroup0 = (1u << C_MAIN) | (1u << C_NEE);
 
 // Field map of one slot (units: 32-bit words; word f of slot s lives at pw[f * P + s]).
 template <int SPEC> struct PoolL {
@@ -76,7 +83,7 @@ template <int SPEC> struct PoolL {
     static constexpr int F_COUNT = F_NW + 1;
     // slots per CTA: as many as fit into the 227 KB of opt-in shared memory (state words + one 16-bit entry per stage ring),
     // a compile-time constant so that every field access is one LDS / STS with an immediate offset
-    static constexpr int P = ((232448 - 256) / (F_COUNT * 4 + 2 * 6)) / 32 * 32;
+    static constexpr int P = ((232448 - 256 - 2 * kPoolRings * kPoolRingSlack) / (F_COUNT * 4 + 2 * kPoolRings)) / 32 * 32;
 };
 
 // flags word
@@ -92,7 +99,7 @@ struct PoolShared {
 };
 
 __host__ __device__ constexpr size_t pool_ring_offset() { return (sizeof(PoolShared) + 15) & ~(size_t) 15; }
-__host__ __device__ constexpr size_t pool_state_offset(int P) { return (pool_ring_offset() + (size_t) C_COUNT * P * sizeof(uint16_t) + 15) & ~(size_t) 15; }
+__host__ __device__ constexpr size_t pool_state_offset(int P) { return (pool_ring_offset() + (size_t) kPoolRings * (P + kPoolRingSlack) * sizeof(uint16_t) + 15) & ~(size_t) 15; }
 template <int SPEC> __host__ __device__ constexpr size_t pool_smem_bytes() {
     return pool_state_offset(PoolL<SPEC>::P) + (size_t) PoolL<SPEC>::F_COUNT * PoolL<SPEC>::P * sizeof(uint32_t);
 }
@@ -129,6 +136,133 @@ template <int P> struct PoolMem {
     }
 };
 
+// ---------------------------------------------------------------------------------------------
+// Queue machinery shared by the forward and the adjoint pool kernels.
+// ---------------------------------------------------------------------------------------------
+// All slots start in class `start_class` (ring position i holds slot i).
+template <int P>
+MIB_D void pool_init(PoolShared *ps, volatile uint16_t *ring, unsigned total_local, int start_class) {
+    if (threadIdx.x == 0) {
+        for (int c = 0; c < 8; ++c) { ps->head[c] = 0; ps->tail[c] = 0; }
+        ps->tail[start_class] = (unsigned) P;
+        ps->next_local = 0;
+        ps->total_local = total_local;
+        ps->retired = 0;
+        ps->error = 0;
+        ps->group = 1;                                    // the start class is in group 1
+    }
+    constexpr int R = pool_ring_cap<P>();
+    for (int i = threadIdx.x; i < kPoolRings * R; i += blockDim.x) {
+        int c = i / R, k = i - c * R;
+        ring[i] = (uint16_t) ((c == start_class && k < P) ? k : kRingEmpty);
+    }
+}
+
+// Claim up to 32 slots of ONE class: lane 0 scans the queues and moves one head with a CAS; every lane then takes
+// its slot id out of the ring (a producer that has reserved the position but not yet written it is waited for).
+// Policy (MIB_POOL_GROUPS): the classes form two groups, GROUP0 = the loops of the walk (MAIN, NEE: a slot is
+// executed several times in a row) and the rest.  All warps of the CTA serve the current group until it has no
+// full batch left and then switch together, so that the code live in the instruction cache at any time is one
+// group's, not the whole kernel's (+8 ... +29 % measured, profiles/r01_ab_variants.md).
+// Returns false when every slot of the CTA has retired (or the watchdog fired).
+template <int P, unsigned GROUP0>
+MIB_D bool pool_claim(PoolShared *ps, volatile uint16_t *ring, unsigned lane_id, unsigned &idle_spins, int &cls, unsigned &n, int &slot) {
+    constexpr unsigned FULL = 0xffffffffu;
+    int c_sel = -1;
+    unsigned base = 0, take = 0;
+    if (lane_id == 0) {
+        while (true) {
+            unsigned a[8], h[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                h[c] = *(volatile unsigned *) &ps->head[c];
+                a[c] = *(volatile unsigned *) &ps->tail[c] - h[c];
+            }
+            int best = -1;
+#if MIB_POOL_GROUPS
+            const unsigned g = *(volatile unsigned *) &ps->group;
+            int best_in = -1, best_out = -1;
+            unsigned n_in = 0, n_out = 0;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const bool in = (((GROUP0 >> c) & 1u) ? 0u : 1u) == g;
+                if (in) { if (a[c] > n_in) { n_in = a[c]; best_in = c; } }
+                else { if (a[c] > n_out) { n_out = a[c]; best_out = c; } }
+            }
+            if (n_in >= 32u || (n_in > 0u && n_out < 32u)) best = best_in;
+            else if (n_out > 0u) { ps->group = g ^ 1u; best = best_out; }
+#else
+            unsigned best_n = 0;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) if (a[c] > best_n) { best_n = a[c]; best = c; }
+#endif
+            if (best >= 0) {
+                unsigned av = 0, hh = 0;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) if (c == best) { av = a[c]; hh = h[c]; }
+                unsigned t = av < 32u ? av : 32u;
+                if (atomicCAS(&ps->head[best], hh, hh + t) == hh) { c_sel = best; base = hh; take = t; break; }
+                continue;
+            }
+            if (*(volatile unsigned *) &ps->retired >= (unsigned) P || *(volatile unsigned *) &ps->error) break;
+            __nanosleep(100);
+            if (++idle_spins > kPoolSpinLimit) { ps->error = 1; break; }
+        }
+    }
+    c_sel = __shfl_sync(FULL, c_sel, 0);
+    base = __shfl_sync(FULL, base, 0);
+    take = __shfl_sync(FULL, take, 0);
+    cls = c_sel; n = take; slot = 0;
+    if (c_sel < 0) return false;
+    if (lane_id < take) {
+        constexpr unsigned R = (unsigned) pool_ring_cap<P>();
+        unsigned pos = (base + lane_id) % R;
+        unsigned v, sp = 0;
+        while ((v = ring[c_sel * R + pos]) == kRingEmpty) {
+            if (++sp > kPoolSpinLimit) {
+                ps->error = 2;
+                v = 0; break;
+            }
+        }
+        ring[c_sel * R + pos] = (uint16_t) kRingEmpty;
+        slot = (int) v;
+    }
+    return true;
+}
+
+// Append each lane's slot to the queue of class `next` (< 0: nothing to append): one atomic per class and warp.
+template <int P>
+MIB_D void pool_push(PoolShared *ps, volatile uint16_t *ring, unsigned lane_id, int next, int slot) {
+    constexpr unsigned FULL = 0xffffffffu;
+    __threadfence_block();
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        unsigned m = __ballot_sync(FULL, next == c);
+        if (m) {
+            int leader = __ffs(m) - 1;
+            unsigned b0 = 0;
+            if ((int) lane_id == leader) b0 = atomicAdd(&ps->tail[c], (unsigned) __popc(m));
+            b0 = __shfl_sync(FULL, b0, leader);
+            if (next == c) {
+                constexpr unsigned R = (unsigned) pool_ring_cap<P>();
+                unsigned pos = (b0 + (unsigned) __popc(m & ((1u << lane_id) - 1u))) % R;
+                if (ring[c * R + pos] != kRingEmpty) ps->error = 3;
+                ring[c * R + pos] = (uint16_t) slot;
+            }
+        }
+    }
+}
+
+// Lanes of CTA `cta`: interleaved chunks of kPoolChunk lanes (chunk c belongs to CTA c mod n_cta)
+MIB_D uint64_t pool_local_total(uint64_t N, uint32_t cta, uint32_t n_cta) {
+    const uint64_t n_chunks = (N + kPoolChunk - 1) / kPoolChunk;
+    uint64_t owned = n_chunks > cta ? (n_chunks - 1 - cta) / n_cta + 1 : 0;
+    if (!owned) return 0;
+    uint64_t last = cta + (owned - 1) * n_cta;
+    uint64_t last_size = (last == n_chunks - 1) ? N - last * kPoolChunk : (uint64_t) kPoolChunk;
+    return (owned - 1) * kPoolChunk + last_size;
+}
+
 // CTA-local lane index -> lane of the wavefront (interleaved chunks)
 MIB_D uint64_t pool_lane(uint32_t i, uint32_t cta, uint32_t n_cta) {
     uint64_t chunk = (uint64_t) cta + (uint64_t) (i / kPoolChunk) * n_cta;
@@ -152,25 +286,8 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
     const unsigned lane_id = threadIdx.x & 31;
 
     // ---- lanes of this CTA ----
-    const uint64_t N = lp.lane_end - lp.lane_begin;
-    const uint64_t n_chunks = (N + kPoolChunk - 1) / kPoolChunk;
-    uint64_t owned = n_chunks > blockIdx.x ? (n_chunks - 1 - blockIdx.x) / gridDim.x + 1 : 0;
-    uint64_t total_local = 0;
-    if (owned) {
-        uint64_t last = blockIdx.x + (owned - 1) * gridDim.x;
-        uint64_t last_size = (last == n_chunks - 1) ? N - last * kPoolChunk : (uint64_t) kPoolChunk;
-        total_local = (owned - 1) * kPoolChunk + last_size;
-    }
-    if (threadIdx.x == 0) {
-        for (int c = 0; c < 8; ++c) { ps->head[c] = 0; ps->tail[c] = 0; }
-        ps->tail[C_START] = (unsigned) P;                 // every slot begins in START with no path to finish
-        ps->next_local = 0;
-        ps->total_local = (unsigned) total_local;
-        ps->retired = 0;
-        ps->error = 0;
-        ps->group = 1;                                    // START is in group 1
-    }
-    for (int i = threadIdx.x; i < C_COUNT * P; i += blockDim.x) ring[i] = (uint16_t) (i < P ? i : kRingEmpty);
+    const uint64_t total_local = pool_local_total(lp.lane_end - lp.lane_begin, blockIdx.x, gridDim.x);
+    pool_init<P>(ps, ring, (unsigned) total_local, C_START);
     for (int s = threadIdx.x; s < P; s += blockDim.x) pm.su(L::F_LANE, s, kNoLane);
     __syncthreads();
 
@@ -231,79 +348,11 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
 
     unsigned idle_spins = 0;
     while (true) {
-        // ---- 1. claim a batch: up to kPoolClaim slots of ONE class (lane 0 scans the six queues, one CAS) ----
-        // Policy (MIB_POOL_GROUPS): the classes form two groups, {MAIN, NEE} -- the loops of the walk, where a slot
-        // is executed several times in a row -- and {START, SCATTER, PHASE, BSDF}.  All warps of the CTA serve the
-        // current group until it has no full batch left and then switch together, so that the code live in the
-        // instruction cache at any time is one group's, not the whole kernel's.
-        int cls = -1;
-        unsigned base = 0, n_total = 0;
-        if (lane_id == 0) {
-            while (true) {
-                unsigned a[C_COUNT], h[C_COUNT];
-#pragma unroll
-                for (int c = 0; c < C_COUNT; ++c) {
-                    h[c] = *(volatile unsigned *) &ps->head[c];
-                    a[c] = *(volatile unsigned *) &ps->tail[c] - h[c];
-                }
-                int best = -1;
-#if MIB_POOL_GROUPS
-                const unsigned g = *(volatile unsigned *) &ps->group;
-                int best_in = -1, best_out = -1;
-                unsigned n_in = 0, n_out = 0;
-#pragma unroll
-                for (int c = 0; c < C_COUNT; ++c) {
-                    const bool in = ((c == C_MAIN || c == C_NEE) ? 0u : 1u) == g;
-                    if (in) { if (a[c] > n_in) { n_in = a[c]; best_in = c; } }
-                    else { if (a[c] > n_out) { n_out = a[c]; best_out = c; } }
-                }
-                if (n_in >= 32u || (n_in > 0u && n_out < 32u)) best = best_in;
-                else if (n_out > 0u) { ps->group = g ^ 1u; best = best_out; }
-#else
-                unsigned best_n = 0;
-#pragma unroll
-                for (int c = 0; c < C_COUNT; ++c) if (a[c] > best_n) { best_n = a[c]; best = c; }
-#endif
-                if (best >= 0) {
-                    unsigned av = 0, hh = 0;
-#pragma unroll
-                    for (int c = 0; c < C_COUNT; ++c) if (c == best) { av = a[c]; hh = h[c]; }
-                    unsigned take = av < (unsigned) kPoolClaim ? av : (unsigned) kPoolClaim;
-                    if (atomicCAS(&ps->head[best], hh, hh + take) == hh) { cls = best; base = hh; n_total = take; break; }
-                    continue;
-                }
-                if (*(volatile unsigned *) &ps->retired >= (unsigned) P || *(volatile unsigned *) &ps->error) break;
-                __nanosleep(100);
-                if (++idle_spins > kPoolSpinLimit) { ps->error = 1; break; }
-            }
-        }
-        cls = __shfl_sync(FULL, cls, 0);
-        base = __shfl_sync(FULL, base, 0);
-        n_total = __shfl_sync(FULL, n_total, 0);
-        if (cls < 0) break;
-        // Take the claimed ids out of the ring right away (a ring position may be reused as soon as it is emptied;
-        // a producer that has reserved a position but not yet written it is waited for).
-        int claimed[kPoolClaim / 32];
-#pragma unroll
-        for (int k = 0; k < kPoolClaim / 32; ++k) {
-            claimed[k] = 0;
-            if (k * 32u + lane_id < n_total) {
-                unsigned pos = (base + k * 32u + lane_id) % (unsigned) P;
-                unsigned v, sp = 0;
-                while ((v = ring[cls * P + pos]) == kRingEmpty) {
-                    if (++sp > kPoolSpinLimit) { ps->error = 2; v = 0; break; }
-                }
-                ring[cls * P + pos] = (uint16_t) kRingEmpty;
-                claimed[k] = (int) v;
-            }
-        }
-#pragma unroll 1
-        for (unsigned sub = 0; sub < n_total; sub += 32u) {
-        const unsigned n = n_total - sub < 32u ? n_total - sub : 32u;
+        // ---- 1. claim a batch of up to 32 slots of one class ----
+        int cls, slot;
+        unsigned n;
+        if (!pool_claim<P, kFwdGroup0>(ps, ring, lane_id, idle_spins, cls, n, slot)) break;
         const bool has = lane_id < n;
-        int slot = 0;
-#pragma unroll
-        for (int k = 0; k < kPoolClaim / 32; ++k) if (sub == k * 32u) slot = claimed[k];
         __threadfence_block();
 
         // ---- 2.-3. run the stage ----
@@ -564,21 +613,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
         __threadfence_block();
 
         // ---- 4. append the slots to their next queues (one atomic per class and warp) ----
-#pragma unroll
-        for (int c = 0; c < C_COUNT; ++c) {
-            unsigned m = __ballot_sync(FULL, next == c);
-            if (m) {
-                int leader = __ffs(m) - 1;
-                unsigned b0 = 0;
-                if ((int) lane_id == leader) b0 = atomicAdd(&ps->tail[c], (unsigned) __popc(m));
-                b0 = __shfl_sync(FULL, b0, leader);
-                if (next == c) {
-                    unsigned pos = (b0 + (unsigned) __popc(m & ((1u << lane_id) - 1u))) % (unsigned) P;
-                    ring[c * P + pos] = (uint16_t) slot;
-                }
-            }
-        }
-        }   // sub-batches of the claim
+        pool_push<P>(ps, ring, lane_id, next, slot);
     }
 
     if (lp.mode == 1) {

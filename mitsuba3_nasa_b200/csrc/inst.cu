@@ -1,6 +1,7 @@
 // inst.cu -- one explicit instantiation of a walk kernel per object file.
-// Compiled as:  nvcc -DINST_FWD|-DINST_POOL -DINST_SPEC=s -DINST_MODE=m   or   nvcc -DINST_ADJ -DINST_SPEC=s   (see Makefile).
+// Compiled as:  nvcc -DINST_FWD|-DINST_POOL -DINST_SPEC=s -DINST_MODE=m   or   nvcc -DINST_ADJ|-DINST_APOOL -DINST_SPEC=s   (see Makefile).
 #include "kernels.cuh"
+#include "apool.cuh"
 
 namespace mib {
 #if defined(INST_FWD)
@@ -20,6 +21,17 @@ template <> void launch_k_forward_pool<INST_SPEC, INST_MODE>(const DScene &scene
     k_forward_pool<INST_SPEC, INST_MODE><<<blocks, threads, smem, st>>>(lp);
 }
 template <> int pool_slots<INST_SPEC, INST_MODE>() { return PoolL<INST_SPEC>::P; }
+#elif defined(INST_APOOL)
+template <> void launch_k_adjoint_pool<INST_SPEC>(const DScene &scene, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, unsigned threads, cudaStream_t st) {
+    static bool configured = false;
+    if (!configured) {
+        cudaFuncSetAttribute(k_adjoint_pool<INST_SPEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+        configured = true;
+    }
+    cudaMemcpyToSymbolAsync(sc, &scene, sizeof(DScene), 0, cudaMemcpyHostToDevice, st);
+    k_adjoint_pool<INST_SPEC><<<blocks, threads, apool_smem_bytes<INST_SPEC>(), st>>>(lp, ap);
+}
+template <> int adjoint_pool_slots<INST_SPEC>() { return APoolL<INST_SPEC>::P; }
 #elif defined(INST_ADJ)
 template <> void launch_k_adjoint<INST_SPEC>(const DScene &scene, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, cudaStream_t st) {
     cudaMemcpyToSymbolAsync(sc, &scene, sizeof(DScene), 0, cudaMemcpyHostToDevice, st);

@@ -7,7 +7,7 @@
 // inter-thread exchange.  Grid = ceil(lanes / spt / 128) CTAs of 128 threads; with
 // spt chosen by the host the grid is many multiples of 148 SMs x resident CTAs.
 #pragma once
-#include "adjoint.cuh"
+#include "astage.cuh"
 
 #ifndef MIB_MINB
 #define MIB_MINB 4          // __launch_bounds__(128, MIB_MINB): min resident CTAs per SM (register cap experiments)

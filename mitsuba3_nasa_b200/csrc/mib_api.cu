@@ -4,7 +4,7 @@
 // There is NO CPU fallback: every entry point needs a CUDA device and fails
 // with an error message otherwise.
 #include "kernels.cuh"
-#include "adjoint.cuh"
+#include "astage.cuh"
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
@@ -230,6 +230,8 @@ template <int SPEC, int MODE> void launch_k_forward(const DScene &sc, const Laun
 template <int SPEC, int MODE> void launch_k_forward_pool(const DScene &sc, const LaunchParams &lp, unsigned blocks, unsigned threads, cudaStream_t st);
 template <int SPEC, int MODE> int pool_slots();
 template <int SPEC> void launch_k_adjoint(const DScene &sc, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, cudaStream_t st);
+template <int SPEC> void launch_k_adjoint_pool(const DScene &sc, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, unsigned threads, cudaStream_t st);
+template <int SPEC> int adjoint_pool_slots();
 }
 
 static int env_int(const char *name, int dflt) {
@@ -315,7 +317,7 @@ static void fetch_counters(mib_scene *s, float ms, uint64_t launches) {
     s->last.n_lookups = c[0]; s->last.n_real = c[1]; s->last.n_null = c[2];
     s->last.n_nee_steps = c[3]; s->last.n_surface = c[4]; s->last.n_samples = c[5];
     s->last.kernel_ms = ms; s->last.n_launches = launches;
-    if (c[7]) throw std::runtime_error("k_forward_pool: queue watchdog fired (code " + std::to_string(c[7]) + "); results are invalid");
+    if (c[7]) throw std::runtime_error("path-pool kernel: queue watchdog fired (code " + std::to_string(c[7]) + ": 1 idle poll, 2 ring entry never arrived, 3 ring cell reused too early); results are invalid");
 }
 
 // mode 0: film, mode 1: sums, mode 2: per-sample dump into per_sample_dev

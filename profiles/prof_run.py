@@ -39,3 +39,19 @@ else:
         scene.device.render(k, 64, to_host=False)
         c = scene.device.counters()
         print('c1', c['kernel_ms'], 'ms', c['n_samples'] / c['kernel_ms'] / 1e3, 'Msamples/s')
+
+if len(sys.argv) > 3 and sys.argv[3] == 'check':
+    # pool kernel vs one-thread-one-path kernel at this size: per-lane results are schedule independent, so the event
+    # counters must agree exactly and the film / Stokes sums up to the order of the float atomics
+    res = {}
+    for k in ('pool', 'thread'):
+        os.environ['MIB_FORWARD_KERNEL'] = k
+        if which == 'c2':
+            out = scene.device.render_1(7, 1 << lg)
+        else:
+            out = np.asarray(scene.device.render(7, d['sensor']['sampler']['sample_count'] if which != 'c1' else 64, develop=False, to_host=True), dtype=np.float64)
+        c = scene.device.counters()
+        res[k] = (out, {kk: c[kk] for kk in ('n_samples', 'n_lookups', 'n_real', 'n_null', 'n_nee_steps', 'n_surface')})
+    same = res['pool'][1] == res['thread'][1]
+    err = np.abs(res['pool'][0] - res['thread'][0]).max() / max(np.abs(res['thread'][0]).max(), 1e-30)
+    print('CHECK', which, 'counters identical' if same else 'COUNTERS DIFFER %s %s' % (res['pool'][1], res['thread'][1]), 'max rel diff of sums %.3g' % err)
