@@ -85,6 +85,13 @@ class ClockSampler:
         return out
 
 
+def _lib_handle():
+    from mitsuba3_nasa_b200 import _lib
+    l = _lib.lib()
+    l.mib_sizeof_device_scene.restype = __import__('ctypes').c_size_t
+    return l
+
+
 def dist_env():
     return int(os.environ.get('RANK', 0)), int(os.environ.get('LOCAL_RANK', 0)), int(os.environ.get('WORLD_SIZE', 1))
 
@@ -225,13 +232,14 @@ def run_ours(args):
         "stokes": [float(x) for x in stokes_all],
         "wall_s_timed_region": wall,
         "clocks": clk,
-        "e2e": {"value": e2e, "unit": "Msamples/s", "h2d_bytes_per_step": ctypes.sizeof(_abi.SceneDesc),
+        "e2e": {"value": e2e, "unit": "Msamples/s",
+                "h2d_bytes_per_step": ctypes.sizeof(_abi.SceneDesc) + int(_lib_handle().mib_sizeof_device_scene()),
                 "d2h_bytes_per_step": 4 * 8 + ctypes.sizeof(_abi.Counters)},
         "gpu_launches": int(launches),
         "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": FP32_PEAK_TFLOPS, "unit": "TFLOP/s",
                      "frac": achieved_tf / FP32_PEAK_TFLOPS, "traffic": 201728,
                      "traffic_note": "dram bytes read (writes < 10 KB) by one k_forward<2,1> launch, ncu --set full (profiles/r01_ncu_c2_pol_volpathaos_summary.txt, 2^24 samples): the scene is analytic",
-                     "kernel": "k_forward<mono_polarized, volpathaos>",
+                     "kernel": "k_forward<mono_polarized, volpathaos> (one thread per path; the library picks the path-pool kernels for heterogeneous media)",
                      "note": "homogeneous medium: no grid traffic, FP32-pipe bound; peak = 148 SM x 128 lanes x 2 x 1.965 GHz "
                              "(derived, not in MEASURED_PEAKS.json); flops = documented per-event constants x exact event counters",
                      "events_per_launch": c1, "hbm_peak_gbs_measured": peaks.get("hbm_gbs")},
@@ -326,7 +334,7 @@ def adjoint_bench(device, rank, world):
     g = dev.grad_get(slot, scene.flat.buffers[slot].size)
     # bytes: primal pass look-ups + backward look-ups (32 B each) + gradient read-modify-write through 8 taps (64 B)
     alg_bytes = 32 * c['n_lookups'] + 64 * (c['n_lookups'] / 2)
-    return {"workload": "C4: C3 scene 512x512x64 spp, prb_volpathaos, render_1_backward wrt the 256^3 sigma_t grid",
+    return {"workload": "C4: C3 scene 512x512x64 spp, prb_volpathaos, render_1_backward wrt the 256^3 sigma_t grid", "kernel": "k_adjoint_pool<mono_polarized>",
             "msamples_per_s": n / (kernel_ms / 1e3) / 1e6, "kernel_ms_max_over_ranks": kernel_ms,
             "wall_ms_with_gradient_allreduce": wall_ms, "gradient_bytes": int(g.size * 4),
             "grad_abs_sum": float(np.abs(g.astype(np.float64)).sum()), "events_this_rank": c,

@@ -199,6 +199,9 @@ typedef struct mib_scene mib_scene;
 const char *mib_last_error(void);
 int  mib_abi_version(void);
 size_t mib_sizeof_scene_desc(void);
+/* bytes of the device-side scene block uploaded to the kernels' constant bank at every launch (descriptor + buffer
+ * pointers + table descriptors); reported by bench.py as part of the end-to-end host->device traffic */
+size_t mib_sizeof_device_scene(void);
 
 /* device = CUDA ordinal the scene lives on (one process per GPU). */
 int  mib_scene_create(const mib_scene_desc *desc, int device, mib_scene **out);

@@ -94,7 +94,7 @@ class Counters(C.Structure):
 
 # Every symbol include/mi_b200.h declares (tests check the library exports all of them).
 EXPORTS = [
-    "mib_last_error", "mib_abi_version", "mib_sizeof_scene_desc",
+    "mib_last_error", "mib_abi_version", "mib_sizeof_scene_desc", "mib_sizeof_device_scene",
     "mib_scene_create", "mib_scene_destroy", "mib_scene_set_buffer", "mib_scene_get_buffer",
     "mib_scene_buffer_dev", "mib_scene_set_desc", "mib_scene_commit", "mib_scene_get_desc",
     "mib_scene_set_lane_range", "mib_render", "mib_film_dev", "mib_film_develop", "mib_film_read",
@@ -108,6 +108,7 @@ EXPORTS = [
 def check_abi(lib):
     lib.mib_abi_version.restype = C.c_int
     lib.mib_sizeof_scene_desc.restype = C.c_size_t
+    lib.mib_sizeof_device_scene.restype = C.c_size_t
     if lib.mib_abi_version() != MIB_ABI_VERSION:
         raise RuntimeError("libmi_b200.so ABI version %d != python mirror %d" % (lib.mib_abi_version(), MIB_ABI_VERSION))
     if lib.mib_sizeof_scene_desc() != C.sizeof(SceneDesc):

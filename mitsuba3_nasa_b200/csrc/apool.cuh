@@ -36,7 +36,7 @@ template <int SPEC> struct APoolL {
     static constexpr int P = ((232448 - 256 - 2 * kPoolRings * kPoolRingSlack) / (F_COUNT * 4 + 2 * kPoolRings)) / 32 * 32;
 };
 constexpr uint32_t FL_BACKWARD = 0x4;                  // (the forward kernel's FL_SPEC_CHAIN bit: prb walks have no specular chain)
-constexpr unsigned kAdjGroup0 = (1u << C_MAIN) | (1u << C_NEE) | (1u << C_NEEG);
+constexpr unsigned kAdjGroup0 = (1u << C_MAIN) | (1u << C_MAINB) | (1u << C_NEE) | (1u << C_NEEG);
 
 template <int SPEC> __host__ __device__ constexpr size_t apool_smem_bytes() {
     return pool_state_offset(APoolL<SPEC>::P) + (size_t) APoolL<SPEC>::F_COUNT * APoolL<SPEC>::P * sizeof(uint32_t);
@@ -182,10 +182,11 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
                 for (int i = 0; i < NT; ++i) pm.sf(L::F_T + i, slot, st.T[i]);
 #pragma unroll
                 for (int r = 0; r < NR; ++r) pm.sf(L::F_L + r, slot, st.L[r]);
-                next = C_MAIN;
+                next = replay ? C_MAINB : C_MAIN;
             }
             break;
         }
+        case C_MAINB:            // MAIN of the replay in its own queue: a batch either scatters gradients or it does not
         case C_MAIN: {
             if (has) {
                 PrbState<SPEC> st;
@@ -219,7 +220,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
                     fl = (fl & ~(FL_NEEDS_INT | kNeeBits)) | (st.needs_intersection ? FL_NEEDS_INT : 0u);
                     pm.sv3(L::F_RAY, slot, st.ray.o); pm.sf(L::F_RAY + 6, slot, st.ray.maxt);
                     pm.store_si(L::F_SI, slot, st.si);
-                    if (ev == EV_NULL) next = C_MAIN;
+                    if (ev == EV_NULL) next = cls;
                     else if (ev == EV_SCATTER) { pm.sv3(L::F_SCP, slot, st.scatter_p); next = C_SCAT; }
                     else if (ev == EV_NEE) {
                         store_nee(slot, st.nee);
@@ -346,7 +347,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
                 for (int i = 0; i < NT; ++i) pm.sf(L::F_T + i, slot, st.T[i]);
                 pm.sv3(L::F_RAY, slot, st.ray.o); pm.sv3(L::F_RAY + 3, slot, st.ray.d); pm.sf(L::F_RAY + 6, slot, st.ray.maxt);
                 pm.su(L::F_FLAGS, slot, (fl & ~FL_NEEDS_INT) | (st.needs_intersection ? FL_NEEDS_INT : 0u));
-                next = C_MAIN;
+                next = (fl & FL_BACKWARD) ? C_MAINB : C_MAIN;
             }
             break;
         }
@@ -370,7 +371,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
                     pm.sv3(L::F_RAY, slot, st.ray.o); pm.sv3(L::F_RAY + 3, slot, st.ray.d); pm.sf(L::F_RAY + 6, slot, st.ray.maxt);
                     pm.su(L::F_DEPTH, slot, st.depth);
                     pm.su(L::F_FLAGS, slot, (fl & ~(FL_NEEDS_INT | 0xff00u)) | FL_NEEDS_INT | ((uint32_t) (st.medium + 1) << 8));
-                    next = C_MAIN;
+                    next = (fl & FL_BACKWARD) ? C_MAINB : C_MAIN;
                 } else next = C_START;
             }
             break;

@@ -42,6 +42,10 @@ constexpr int kPoolRings = MIB_POOL_RINGS;   // stage rings laid out in shared m
 // batch of a group could land on the cells a warp had just claimed when all other slots were queued in one class: lost
 // entries.)  pool_push checks that the cell it writes is empty and raises error 3 otherwise.
 constexpr int kPoolRingSlack = 512;
+#ifndef MIB_POOL_PATIENCE
+#define MIB_POOL_PATIENCE 0
+#endif
+constexpr int kPoolPatience = MIB_POOL_PATIENCE;   // polls (100 ns each) a warp waits for a full batch before it takes a partial one
 template <int P> __host__ __device__ constexpr int pool_ring_cap() { return P + kPoolRingSlack; }
 constexpr int kPoolChunk = 256;            // lanes per interleaved chunk
 #ifndef MIB_POOL_MAIN_ITERS
@@ -56,7 +60,7 @@ constexpr unsigned kPoolSpinLimit = 1u << 22;   // watchdog of the two wait loop
 constexpr uint32_t kNoLane = 0xffffffffu;
 constexpr unsigned kRingEmpty = 0xffffu;
 
-enum { C_START = 0, C_MAIN = 1, C_SCAT = 2, C_NEE = 3, C_PHASE = 4, C_BSDF = 5, C_NEEG = 6, C_COUNT = 6 };   // C_NEEG: adjoint only (apool.cuh)
+enum { C_START = 0, C_MAIN = 1, C_SCAT = 2, C_NEE = 3, C_PHASE = 4, C_BSDF = 5, C_NEEG = 6, C_MAINB = 7, C_COUNT = 6 };   // C_NEEG, C_MAINB: adjoint only (apool.cuh)
 constexpr unsigned kFwdGroup0 = (1u << C_MAIN) | (1u << C_NEE);
 
 // Field map of one slot (units: 32-bit words; word f of slot s lives at pw[f * P + s]).
@@ -169,49 +173,62 @@ template <int P, unsigned GROUP0>
 MIB_D bool pool_claim(PoolShared *ps, volatile uint16_t *ring, unsigned lane_id, unsigned &idle_spins, int &cls, unsigned &n, int &slot) {
     constexpr unsigned FULL = 0xffffffffu;
     int c_sel = -1;
-    unsigned base = 0, take = 0;
-    if (lane_id == 0) {
-        while (true) {
-            unsigned a[8], h[8];
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                h[c] = *(volatile unsigned *) &ps->head[c];
-                a[c] = *(volatile unsigned *) &ps->tail[c] - h[c];
-            }
-            int best = -1;
-#if MIB_POOL_GROUPS
-            const unsigned g = *(volatile unsigned *) &ps->group;
-            int best_in = -1, best_out = -1;
-            unsigned n_in = 0, n_out = 0;
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const bool in = (((GROUP0 >> c) & 1u) ? 0u : 1u) == g;
-                if (in) { if (a[c] > n_in) { n_in = a[c]; best_in = c; } }
-                else { if (a[c] > n_out) { n_out = a[c]; best_out = c; } }
-            }
-            if (n_in >= 32u || (n_in > 0u && n_out < 32u)) best = best_in;
-            else if (n_out > 0u) { ps->group = g ^ 1u; best = best_out; }
-#else
-            unsigned best_n = 0;
-#pragma unroll
-            for (int c = 0; c < 8; ++c) if (a[c] > best_n) { best_n = a[c]; best = c; }
-#endif
-            if (best >= 0) {
-                unsigned av = 0, hh = 0;
-#pragma unroll
-                for (int c = 0; c < 8; ++c) if (c == best) { av = a[c]; hh = h[c]; }
-                unsigned t = av < 32u ? av : 32u;
-                if (atomicCAS(&ps->head[best], hh, hh + t) == hh) { c_sel = best; base = hh; take = t; break; }
-                continue;
-            }
-            if (*(volatile unsigned *) &ps->retired >= (unsigned) P || *(volatile unsigned *) &ps->error) break;
-            __nanosleep(100);
-            if (++idle_spins > kPoolSpinLimit) { ps->error = 1; break; }
+    unsigned base = 0, take = 0, patience = 0;
+    // The whole warp runs the scan: lane c reads head / tail of class c, three shuffle steps find the fullest queue
+    // inside and outside the current group (a lane-0-only scan cost ~12 % of all issued instructions).
+    while (true) {
+        unsigned hv = 0, av = 0;
+        if (lane_id < 8u) {
+            hv = *(volatile unsigned *) &ps->head[lane_id];
+            av = *(volatile unsigned *) &ps->tail[lane_id] - hv;
         }
+#if MIB_POOL_GROUPS
+        const unsigned g = *(volatile unsigned *) &ps->group;
+        const bool in = lane_id < 8u && ((((GROUP0 >> lane_id) & 1u) ? 0u : 1u) == g);
+#else
+        const unsigned g = 0;
+        const bool in = lane_id < 8u;
+#endif
+        unsigned kin = in ? ((av << 3) | lane_id) : 0u, kout = (!in && lane_id < 8u) ? ((av << 3) | lane_id) : 0u;
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) {
+            kin = max(kin, __shfl_xor_sync(FULL, kin, o));
+            kout = max(kout, __shfl_xor_sync(FULL, kout, o));
+        }
+        kin = __shfl_sync(FULL, kin, 0);
+        kout = __shfl_sync(FULL, kout, 0);
+        const unsigned n_in = kin >> 3, n_out = kout >> 3;
+        int best = -1;
+        unsigned n_best = 0;
+        bool flip = false;
+        if (n_in >= 32u || (n_in > 0u && n_out < 32u)) { best = (int) (kin & 7u); n_best = n_in; }
+        else if (n_out > 0u) { best = (int) (kout & 7u); n_best = n_out; flip = true; }
+        if (best >= 0) {
+            // a batch that is not full costs as much instruction fetch as a full one: give the warps in flight a moment
+            // to refill the queues before settling for a partial batch
+            if (n_best < 32u && patience < (unsigned) kPoolPatience) { ++patience; __nanosleep(100); continue; }
+            const unsigned hh = __shfl_sync(FULL, hv, best);
+            const unsigned t = n_best < 32u ? n_best : 32u;
+            int ok = 0;
+            if (lane_id == 0) {
+                ok = atomicCAS(&ps->head[best], hh, hh + t) == hh;
+                if (ok && flip) ps->group = g ^ 1u;
+            }
+            ok = __shfl_sync(FULL, ok, 0);
+            if (ok) { c_sel = best; base = hh; take = t; break; }
+            continue;
+        }
+        int stop = 0;
+        if (lane_id == 0) {
+            stop = *(volatile unsigned *) &ps->retired >= (unsigned) P || *(volatile unsigned *) &ps->error;
+            if (!stop) {
+                __nanosleep(100);
+                if (++idle_spins > kPoolSpinLimit) { ps->error = 1; stop = 1; }
+            }
+        }
+        stop = __shfl_sync(FULL, stop, 0);
+        if (stop) break;
     }
-    c_sel = __shfl_sync(FULL, c_sel, 0);
-    base = __shfl_sync(FULL, base, 0);
-    take = __shfl_sync(FULL, take, 0);
     cls = c_sel; n = take; slot = 0;
     if (c_sel < 0) return false;
     if (lane_id < take) {
@@ -219,10 +236,7 @@ MIB_D bool pool_claim(PoolShared *ps, volatile uint16_t *ring, unsigned lane_id,
         unsigned pos = (base + lane_id) % R;
         unsigned v, sp = 0;
         while ((v = ring[c_sel * R + pos]) == kRingEmpty) {
-            if (++sp > kPoolSpinLimit) {
-                ps->error = 2;
-                v = 0; break;
-            }
+            if (++sp > kPoolSpinLimit) { ps->error = 2; v = 0; break; }
         }
         ring[c_sel * R + pos] = (uint16_t) kRingEmpty;
         slot = (int) v;

@@ -377,6 +377,7 @@ extern "C" {
 const char *mib_last_error(void) { return g_err.c_str(); }
 int mib_abi_version(void) { return MIB_ABI_VERSION; }
 size_t mib_sizeof_scene_desc(void) { return sizeof(mib_scene_desc); }
+size_t mib_sizeof_device_scene(void) { return sizeof(DScene); }
 
 int mib_scene_create(const mib_scene_desc *desc, int device, mib_scene **out) {
     MIB_TRY
