@@ -41,7 +41,7 @@
 extern "C" {
 #endif
 
-#define MIB_ABI_VERSION 4
+#define MIB_ABI_VERSION 5
 
 #define MIB_MAX_SHAPES   8
 #define MIB_MAX_MEDIA    4
@@ -165,6 +165,9 @@ typedef struct mib_integrator {
     int32_t hide_emitters;
     int32_t rng_arg_order;   /* MIB_RNG_ARGS_*  */
     int32_t double_phase_quirk; /* volpath multiplies phase_weight twice (volpath.cpp:244,251) */
+    int32_t majorant_res;    /* 0: reference behaviour (one global majorant per heterogeneous medium, heterogeneous.cpp:163-185);
+                              * M > 0: "fast" mode, M^3 supergrid of local majorants + DDA free-flight sampling:
+                              * unbiased, but no longer the reference's random sequence -- agreement is statistical only */
 } mib_integrator;
 
 typedef struct mib_scene_desc {
@@ -271,6 +274,8 @@ int  mib_scene_stream(mib_scene *scene, void **stream);
 int  mib_debug_sample_lanes(mib_scene *scene, uint32_t seed, uint32_t spp, uint64_t lane_begin,
                             uint64_t count, float *out_host /* [count][C] */);
 int  mib_debug_math(int op /*0 sincos,1 exp,2 log,3 cbrt,4 asin*/, const float *in_host, float *out_host, size_t n);
+/* fast mode: the majorant supergrid of a heterogeneous medium, [M][M][M] (z, y, x), scale included */
+int  mib_debug_supergrid(mib_scene *scene, int medium, float *out_host, size_t count);
 
 #ifdef __cplusplus
 }

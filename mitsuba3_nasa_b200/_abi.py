@@ -5,7 +5,7 @@ and the ABI version at load time so a drift fails loudly.
 """
 import ctypes as C
 
-MIB_ABI_VERSION = 4
+MIB_ABI_VERSION = 5
 MIB_MAX_SHAPES, MIB_MAX_MEDIA, MIB_MAX_PHASES = 8, 4, 4
 MIB_MAX_BSDFS, MIB_MAX_EMITTERS, MIB_MAX_BUFFERS = 8, 4, 16
 
@@ -70,7 +70,7 @@ class Sensor(C.Structure):
 
 class Integrator(C.Structure):
     _fields_ = [("type", i32), ("max_depth", i32), ("rr_depth", i32), ("hide_emitters", i32),
-                ("rng_arg_order", i32), ("double_phase_quirk", i32)]
+                ("rng_arg_order", i32), ("double_phase_quirk", i32), ("majorant_res", i32)]
 
 
 class SceneDesc(C.Structure):
@@ -101,7 +101,7 @@ EXPORTS = [
     "mib_render_1", "mib_render_1_raw", "mib_render_backward", "mib_render_1_backward",
     "mib_grad_get", "mib_grad_dev", "mib_grad_get_scalar", "mib_grad_scalar_dev", "mib_grad_zero",
     "mib_mie_tabulate", "mib_counters_get", "mib_scene_stream",
-    "mib_debug_sample_lanes", "mib_debug_math",
+    "mib_debug_sample_lanes", "mib_debug_math", "mib_debug_supergrid",
 ]
 
 

@@ -127,6 +127,13 @@ class DeviceScene:
         self._ck(f(self.h, C.c_uint32(seed), C.c_uint32(spp), _fp(out)))
         return out
 
+    def supergrid(self, medium=0):
+        """Majorant supergrid of a heterogeneous medium (fast mode, integrator 'majorant_resolution' > 0): [M, M, M] (z, y, x)."""
+        M = int(self.scene.desc.integrator.majorant_res)
+        out = np.empty(M * M * M, dtype=np.float32)
+        self._ck(self.l.mib_debug_supergrid(self.h, C.c_int(medium), _fp(out), C.c_size_t(out.size)))
+        return out.reshape(M, M, M)
+
     def sample_lanes(self, seed, spp, lane_begin, count):
         out = np.empty((count, self.raw_channels), np.float32)
         self._ck(self.l.mib_debug_sample_lanes(self.h, C.c_uint32(seed), C.c_uint32(spp), C.c_uint64(lane_begin),

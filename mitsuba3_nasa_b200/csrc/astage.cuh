@@ -160,6 +160,17 @@ MIB_D void prb_nee_step(Pcg32 &rng, Counters &cnt, Sink &sink, uint32_t channel,
     }
 #pragma unroll
     for (int c = 0; c < NC; ++c) tr[c] *= trm[c];
+    if (sc.super_res > 0 && active_medium) {                          // fast mode: roulette on a small transmittance (dscene.cuh);
+        float tm = fabsf(tr[0]);                                      // the gradient walk replays the same decisions
+#pragma unroll
+        for (int c = 1; c < NC; ++c) tm = fmaxf(tm, fabsf(tr[c]));
+        if (tm < kNeeRouletteThreshold && tm > 0.f) {
+            const float q = tm * (1.f / kNeeRouletteThreshold), u = rng.next();
+            const float k = u < q ? __fdividef(1.f, q) : 0.f;
+#pragma unroll
+            for (int c = 0; c < NC; ++c) tr[c] *= k;
+        }
+    }
     if (active_surface) ray = spawn_ray(si.p, si.n, ray.d);
     ray.maxt = remaining;
     needs_intersection = needs_intersection || active_surface;

@@ -27,6 +27,10 @@ struct DScene {
     float rf_coeff[10];                           // gaussian reconstruction filter polynomial (gaussian.cpp:50-98)
     float rf_inv_radius;                          // tent filter
     const float *weight_film;                     // [H*W] filter-weight film for the adjoint of non-box filters
+    // "fast" mode (mib_integrator.majorant_res > 0): per heterogeneous medium a supergrid of local
+    // majorants, super[m][(z*M + y)*M + x] = scale * max of the sigma_t texels any trilinear look-up inside the cell can touch
+    const float *super[MIB_MAX_MEDIA];
+    int super_res;                                // M (0: reference behaviour, one global majorant)
 };
 
 // The scene of the running launch.  One copy per translation unit (each kernel instantiation is its own object
@@ -273,6 +277,59 @@ template <int NC> struct MedIt {
 template <int NC> MIB_D bool valid(const MedIt<NC> &m) { return m.t != inf_f(); }
 template <int NC> MIB_D float ch(const float *s, uint32_t c) { return NC == 3 ? s[c] : s[0]; }
 
+// Free-flight sampling through the majorant supergrid ("fast" mode; no counterpart in the fork, whose heterogeneous medium
+// uses one global majorant, heterogeneous.cpp:163-185).  3D-DDA over the M^3 cells of the medium's local unit cube: the
+// optical-depth target tau = -log(1 - u) is spent cell by cell at the cell's local majorant; the collision lands where it
+// runs out.  Unbiased for any majorant that bounds sigma_t inside the cell; consumes one random number like the reference's
+// sample_interaction, but the tentative collisions fall elsewhere, so results agree with parity mode only statistically.
+struct DdaHit { float t, maj; bool hit; };
+// Fast mode only: Russian roulette on the transmittance of a shadow walk (ratio tracking never terminates by itself in an
+// optically thick region; the reference lets it run).  Unbiased; consumes one extra random number per step below the threshold.
+constexpr float kNeeRouletteThreshold = 0.1f;
+MIB_SUB_GEOM DdaHit supergrid_sample(int mi, Ray ray, float mint, float maxt, float tau) {
+    const mib_medium &m = sc.d.media[mi];
+    const mib_volume &v = m.sigma_t;
+    const int M = sc.super_res;
+    const float *__restrict__ sg = sc.super[mi];
+    const float fM = (float) M, cell = 1.f / fM;
+    V3 lo = xform_point_affine(v.to_local, ray_at(ray, mint)), ld = xform_vector(v.to_local, ray.d);
+    const float tlen = maxt - mint;
+    int c[3], step[3];
+    float tmax[3], tdelta[3];
+    // (approximate reciprocals: fast mode has no bit-parity contract, and a cell boundary that moves by an ulp is covered
+    // by the one-texel slack of the supergrid)
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        float o = comp(lo, a), d = comp(ld, a);
+        int ci = min(max((int) floorf(o * fM), 0), M - 1);
+        c[a] = ci;
+        const float inv = __fdividef(1.f, d);
+        if (d > 0.f) { step[a] = 1; tmax[a] = ((float) (ci + 1) * cell - o) * inv; tdelta[a] = cell * inv; }
+        else if (d < 0.f) { step[a] = -1; tmax[a] = ((float) ci * cell - o) * inv; tdelta[a] = -cell * inv; }
+        else { step[a] = 0; tmax[a] = inf_f(); tdelta[a] = inf_f(); }
+        tmax[a] = fmaxf(tmax[a], 0.f);
+    }
+    DdaHit r;
+    r.t = inf_f(); r.maj = m.max_density; r.hit = false;
+    float t_cur = 0.f;
+    for (int it = 0; it < 3 * M + 3; ++it) {
+        const float mu = __ldg(sg + ((c[2] * M + c[1]) * M + c[0]));
+        const float t_next = fminf(tmax[0], fminf(tmax[1], tmax[2]));
+        const float t_end = fminf(t_next, tlen);
+        const float seg = fmaxf(t_end - t_cur, 0.f);
+        if (mu > 0.f && mu * seg >= tau) { r.t = mint + (t_cur + __fdividef(tau, mu)); r.maj = mu; r.hit = true; break; }
+        tau -= mu * seg;
+        t_cur = t_end;
+        if (t_next >= tlen) break;
+        const int a = (tmax[0] <= tmax[1] && tmax[0] <= tmax[2]) ? 0 : (tmax[1] <= tmax[2] ? 1 : 2);
+        // (selects instead of dynamic indexing keep the arrays in registers)
+#pragma unroll
+        for (int b = 0; b < 3; ++b) if (b == a) { c[b] += step[b]; tmax[b] += tdelta[b]; }
+        if (c[0] < 0 || c[0] >= M || c[1] < 0 || c[1] >= M || c[2] < 0 || c[2] >= M) break;
+    }
+    return r;
+}
+
 template <bool TAPS> struct TapsOpt { GridTaps t; };       // the 8 taps travel with the result only for the adjoint
 template <> struct TapsOpt<false> {};
 template <int NC, bool TAPS> struct MedRes : TapsOpt<TAPS> {
@@ -308,8 +365,23 @@ MIB_SUB_GEOM MedRes<NC, TAPS> sample_interaction2(int mi, Ray ray, float sample,
         for (int c = 0; c < NC; ++c) mei.maj[c] = m.max_density;
     }
     float mj = ch<NC>(mei.maj, channel);
-    float sampled_t = mint + div_(-log_(1.f - sample), mj);
-    bool valid_mi = active && (sampled_t <= maxt);
+    float sampled_t;
+    bool valid_mi;
+    float maj_local = m.max_density;
+    if (m.type != MIB_MEDIUM_HOMOGENEOUS && sc.super_res > 0 && sc.super[mi] != nullptr) {
+        sampled_t = inf_f(); valid_mi = false;
+        if (active && maxt > mint) {
+            DdaHit h = supergrid_sample(mi, ray, mint, maxt, -log_(1.f - sample));
+            valid_mi = h.hit && h.t <= maxt;
+            sampled_t = valid_mi ? h.t : inf_f();
+            maj_local = h.maj;
+#pragma unroll
+            for (int c = 0; c < NC; ++c) mei.maj[c] = maj_local;
+        }
+    } else {
+        sampled_t = mint + div_(-log_(1.f - sample), mj);
+        valid_mi = active && (sampled_t <= maxt);
+    }
     mei.t = valid_mi ? sampled_t : inf_f();
     mei.p = ray_at(ray, sampled_t);
     mei.medium = mi;
@@ -336,7 +408,7 @@ MIB_SUB_GEOM MedRes<NC, TAPS> sample_interaction2(int mi, Ray ray, float sample,
         for (int c = 0; c < NC; ++c) {
             float st = m.scale * sv[c];
             mei.sigma_s[c] = st * av[c];
-            mei.sigma_n[c] = m.max_density - st;
+            mei.sigma_n[c] = maj_local - st;
             mei.sigma_t[c] = st;
         }
     }

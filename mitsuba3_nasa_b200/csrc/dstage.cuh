@@ -167,6 +167,17 @@ MIB_D void nee_step(Pcg32 &rng, Counters &cnt, uint32_t channel, NeeState<SPEC> 
     }
     ray.maxt = remaining;
     ns.needs_intersection = ns.needs_intersection || active_surface;
+    if (sc.super_res > 0 && active_medium) {                          // fast mode: roulette on a small transmittance
+        float tm = fabsf(tr[0]);
+#pragma unroll
+        for (int c = 1; c < NC; ++c) tm = fmaxf(tm, fabsf(tr[c]));
+        if (tm < kNeeRouletteThreshold && tm > 0.f) {
+            const float q = tm * (1.f / kNeeRouletteThreshold), u = rng.next();
+            const float k = u < q ? __fdividef(1.f, q) : 0.f;
+#pragma unroll
+            for (int c = 0; c < NC; ++c) tr[c] *= k;
+        }
+    }
     bool any_tr = false;
 #pragma unroll
     for (int c = 0; c < NC; ++c) any_tr = any_tr || tr[c] != 0.f;

@@ -121,6 +121,17 @@ MIB_D void sample_emitter(Pcg32 &rng, Counters &cnt, V3 ref_p, V3 ref_n, bool su
         }
         ray.maxt = remaining;
         needs_intersection = needs_intersection || active_surface;
+        if (sc.super_res > 0 && active_medium) {                      // fast mode: roulette on a small transmittance (dscene.cuh)
+            float tm = fabsf(tr[0]);
+#pragma unroll
+            for (int c = 1; c < NC; ++c) tm = fmaxf(tm, fabsf(tr[c]));
+            if (tm < kNeeRouletteThreshold && tm > 0.f) {
+                const float q = tm * (1.f / kNeeRouletteThreshold), u = rng.next();
+                const float k = u < q ? __fdividef(1.f, q) : 0.f;
+#pragma unroll
+                for (int c = 0; c < NC; ++c) tr[c] *= k;
+            }
+        }
         bool any_tr = false;
 #pragma unroll
         for (int c = 0; c < NC; ++c) any_tr = any_tr || tr[c] != 0.f;

@@ -368,6 +368,36 @@ __global__ void k_develop(const float *raw, float *out, size_t npix, uint32_t sp
     }
 }
 
+// Majorant supergrid ("fast" mode): one CTA per supercell.  A point of cell i along an axis has local coordinate in
+// [i/M, (i+1)/M], i.e. texel coordinate f = p*res - 0.5 in [i*res/M - 0.5, (i+1)*res/M - 0.5]; a trilinear look-up
+// touches texels floor(f) and floor(f)+1 (clamped), a nearest look-up floor(p*res): the cell's majorant is the maximum over
+// that index box, times scale, times (1 + 2^-20) against the rounding of the interpolation.
+static __global__ void k_supergrid(const float *data, int rx, int ry, int rz, int ch, int M, float scale, float *out) {
+    const int cx = blockIdx.x % M, cy = (blockIdx.x / M) % M, cz = blockIdx.x / (M * M);
+    auto range = [M](int c, int r, int &lo, int &hi) {
+        float a = (float) c * (float) r / (float) M - .5f, b = (float) (c + 1) * (float) r / (float) M - .5f;
+        lo = max((int) floorf(a) - 1, 0);                 // one texel of slack on both sides (float rounding of p*res)
+        hi = min((int) floorf(b) + 2, r - 1);
+    };
+    int x0, x1, y0, y1, z0, z1;
+    range(cx, rx, x0, x1); range(cy, ry, y0, y1); range(cz, rz, z0, z1);
+    const int nx = x1 - x0 + 1, ny = y1 - y0 + 1, nz = z1 - z0 + 1;
+    float mval = 0.f;
+    for (int i = threadIdx.x; i < nx * ny * nz; i += blockDim.x) {
+        int x = x0 + i % nx, y = y0 + (i / nx) % ny, z = z0 + i / (nx * ny);
+        size_t idx = (((size_t) z * ry + y) * rx + x) * ch;
+        for (int c = 0; c < ch; ++c) mval = fmaxf(mval, data[idx + c]);
+    }
+    for (int o = 16; o > 0; o >>= 1) mval = fmaxf(mval, __shfl_xor_sync(0xffffffffu, mval, o));
+    __shared__ float wm[32];
+    if ((threadIdx.x & 31) == 0) wm[threadIdx.x >> 5] = mval;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < (int) (blockDim.x >> 5); ++w) mval = fmaxf(mval, wm[w]);
+        out[blockIdx.x] = mval * scale * (1.f + 9.5367431640625e-07f);
+    }
+}
+
 // grid maximum (gridvolume m_max, grid.cpp:306-319): grid-stride max + one atomic per block
 static __global__ void k_max(const float *data, size_t n, unsigned int *out_bits) {
     float m = -inf_f();

@@ -42,6 +42,8 @@ struct mib_scene {
     size_t buf_n[MIB_MAX_BUFFERS] = {};
     float *grad[MIB_MAX_BUFFERS] = {};
     float *cdf[MIB_MAX_PHASES] = {};             // cdf of the m11 table per phase
+    float *super[MIB_MAX_MEDIA] = {};            // majorant supergrids (fast mode)
+    int super_n[MIB_MAX_MEDIA] = {};
     float *film_raw = nullptr, *film_dev = nullptr;
     size_t film_raw_n = 0, film_dev_n = 0;
     double *sums = nullptr;                      // [8] device
@@ -150,7 +152,27 @@ static void commit(mib_scene *s) {
             }
         }
         m.max_density = m.scale * m.sigma_t.max_value;           // heterogeneous.cpp:163,176-178
+        // fast mode: supergrid of local majorants (rebuilt at every commit, i.e. after every parameter update)
+        s->ds.super[i] = nullptr;
+        const int M = d.integrator.majorant_res;
+        const mib_volume &v = m.sigma_t;
+        const bool affine = v.to_local[12] == 0.f && v.to_local[13] == 0.f && v.to_local[14] == 0.f && v.to_local[15] == 1.f;
+        if (M > 0 && m.type != MIB_MEDIUM_HOMOGENEOUS && v.type == MIB_VOLUME_GRID && v.wrap == MIB_WRAP_CLAMP && affine) {
+            if (s->super_n[i] != M * M * M) {
+                if (s->super[i]) CK(cudaFree(s->super[i]));
+                CK(cudaMalloc(&s->super[i], (size_t) M * M * M * sizeof(float)));
+                s->super_n[i] = M * M * M;
+            }
+            // prb integrators: 25 % head room, so that the null-collision derivative -1 / (1 - sigma_t / majorant) stays bounded
+            // (a tight local majorant would make it heavy-tailed wherever the density is locally flat)
+            const bool prb = d.integrator.type == MIB_INTEG_PRBVOLPATH || d.integrator.type == MIB_INTEG_PRBVOLPATHAOS;
+            k_supergrid<<<M * M * M, 128, 0, s->stream>>>(s->buf[v.buffer], v.res[0], v.res[1], v.res[2], v.channels, M,
+                                                         m.scale * (prb ? 1.25f : 1.f), s->super[i]);
+            CK(cudaGetLastError());
+            s->ds.super[i] = s->super[i];
+        }
     }
+    s->ds.super_res = d.integrator.majorant_res;
     for (int i = 0; i < d.n_phases; ++i) {
         const mib_phase &p = d.phases[i];
         if (p.type == MIB_PHASE_TABPHASE || p.type == MIB_PHASE_TABPHASE_POLARIZED) {
@@ -411,6 +433,7 @@ int mib_scene_destroy(mib_scene *s) {
     cudaSetDevice(s->device);
     for (int i = 0; i < MIB_MAX_BUFFERS; ++i) { if (s->buf[i]) cudaFree(s->buf[i]); if (s->grad[i]) cudaFree(s->grad[i]); }
     for (int i = 0; i < MIB_MAX_PHASES; ++i) if (s->cdf[i]) cudaFree(s->cdf[i]);
+    for (int i = 0; i < MIB_MAX_MEDIA; ++i) if (s->super[i]) cudaFree(s->super[i]);
     if (s->film_raw) cudaFree(s->film_raw);
     if (s->film_dev) cudaFree(s->film_dev);
     if (s->lane_L) cudaFree(s->lane_L);

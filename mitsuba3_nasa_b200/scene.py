@@ -621,6 +621,10 @@ class Scene:
             pr.get(n)
         out.rng_arg_order = A.RNG_ARGS_LEFT_TO_RIGHT
         out.double_phase_quirk = 1 if it.type == 'volpath' else 0
+        # backend extension (not in the fork): M^3 supergrid of local majorants, 0 = the reference's global majorant
+        out.majorant_res = int(pr.get('majorant_resolution', 0))
+        if out.majorant_res < 0 or out.majorant_res > 128:
+            raise PluginError("\"majorant_resolution\" must be in [0, 128]")
         if it.type == 'prb_volpathaos' and self.spectrum != A.SPEC_MONO_POLARIZED:
             # prb_volpathaos.py:72-78
             raise PluginError("prb_volpathaos requires a monochromatic polarized variant")

@@ -92,8 +92,9 @@ def hg_table(g=0.85, n=1801):
 
 
 def c3_cloud(res=1024, spp=256, grid_res=256, max_depth=64, integrator='volpath', phase=None, grid=None,
-             optical_depth=20.0, albedo=0.99, rfilter='box'):
-    """C3: heterogeneous gridvolume cloud in the [-1,1]^3 cube, tabulated Mie phase."""
+             optical_depth=20.0, albedo=0.99, rfilter='box', majorant_resolution=0):
+    """C3: heterogeneous gridvolume cloud in the [-1,1]^3 cube, tabulated Mie phase.
+    majorant_resolution > 0 selects the backend's fast mode (supergrid of local majorants; not in the fork)."""
     if grid is None:
         grid = cloud_grid(grid_res)
     if phase is None:
@@ -104,7 +105,8 @@ def c3_cloud(res=1024, spp=256, grid_res=256, max_depth=64, integrator='volpath'
     scale = optical_depth / (2.0 * max(gmax, 1e-8))   # majorant optical depth across the cube (length 2)
     return {
         'type': 'scene',
-        'integrator': {'type': integrator, 'max_depth': max_depth, 'rr_depth': 5},
+        'integrator': dict({'type': integrator, 'max_depth': max_depth, 'rr_depth': 5},
+                           **({'majorant_resolution': majorant_resolution} if majorant_resolution else {})),
         'sensor': {
             'type': 'perspective', 'fov': 45.0,
             'to_world': T.look_at(origin=[0, 0, 5], target=[0, 0, 0], up=[0, 1, 0]),

@@ -8,7 +8,7 @@ spp = int(sys.argv[1]) if len(sys.argv) > 1 else 16
 gr = int(sys.argv[2]) if len(sys.argv) > 2 else 256
 pol = (sys.argv[3] != 'mono') if len(sys.argv) > 3 else True
 mi.set_variant('llvm_ad_mono_polarized' if pol else 'llvm_ad_mono')
-scene = mi.load_dict(scenes.c4_cloud_adjoint(spp=spp, grid_res=gr, polarized=pol))
+scene = mi.load_dict(scenes.c4_cloud_adjoint(spp=spp, grid_res=gr, polarized=pol, majorant_resolution=int(os.environ.get('MAJORANT_RES', '0'))))
 dev = scene.device
 for k in range(2):
     dev.grad_zero()

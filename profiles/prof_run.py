@@ -6,6 +6,7 @@ import mitsuba3_nasa_b200 as mi
 from mitsuba3_nasa_b200 import scenes
 
 which = sys.argv[1] if len(sys.argv) > 1 else 'c2'
+MR = int(os.environ.get('MAJORANT_RES', '0'))      # fast mode: majorant supergrid resolution (0 = parity mode)
 lg = int(sys.argv[2]) if len(sys.argv) > 2 else 24
 if which == 'c2':
     mi.set_variant('llvm_ad_mono_polarized')
@@ -17,7 +18,7 @@ if which == 'c2':
 elif which == 'c3':
     mi.set_variant('llvm_ad_mono')
     cost, val = scenes.hg_table(0.85, 1801)
-    d = scenes.c3_cloud(res=512, spp=max(1, (1 << lg) // (512 * 512)), grid_res=256, phase={'type': 'tabphase', 'cost': cost, 'values': val})
+    d = scenes.c3_cloud(res=512, spp=max(1, (1 << lg) // (512 * 512)), grid_res=256, phase={'type': 'tabphase', 'cost': cost, 'values': val}, majorant_resolution=MR)
     scene = mi.load_dict(d)
     for k in range(3):
         scene.device.render(k, 0 or d['sensor']['sampler']['sample_count'], develop=False, to_host=False)
@@ -26,7 +27,7 @@ elif which == 'c3':
 elif which == 'c3pol':
     # BASELINE C3 as specified: polarized, Mie x lognormal tabulated phase
     mi.set_variant('llvm_ad_mono_polarized')
-    d = scenes.c3_cloud(res=512, spp=max(1, (1 << lg) // (512 * 512)), grid_res=256)
+    d = scenes.c3_cloud(res=512, spp=max(1, (1 << lg) // (512 * 512)), grid_res=256, majorant_resolution=MR)
     scene = mi.load_dict(d)
     for k in range(3):
         scene.device.render(k, d['sensor']['sampler']['sample_count'], develop=False, to_host=False)
