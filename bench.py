@@ -294,6 +294,21 @@ def grid_roofline(device, peaks):
                "workload": "C3 scene (256^3 grid, Mie x lognormal table) at 512x512x16 spp, %s" % variant,
                "msamples_per_s": cnt['n_samples'] / t / 1e6, "ms": t * 1e3, "l2": "flushed between iterations (256 MiB write)",
                "events": cnt}
+        try:
+            fscene = mi.load_dict(scenes.c3_cloud(res=512, spp=16, grid_res=256, majorant_resolution=16), device=device)
+            fms = []
+            for k in range(3):
+                flush.zero_()
+                torch.cuda.synchronize()
+                fscene.device.render(k, 16, develop=False, to_host=False)
+                fc = fscene.device.counters()
+                if k > 0:
+                    fms.append(fc['kernel_ms'])
+            leg["fast_mode"] = {"majorant_resolution": 16, "msamples_per_s": fc['n_samples'] / (float(np.mean(fms)) / 1e3) / 1e6,
+                                "lookups_per_sample": fc['n_lookups'] / fc['n_samples'],
+                                "note": "majorant supergrid + DDA, roulette in shadow walks: unbiased, but not the reference's random sequence"}
+        except Exception as e:
+            leg["fast_mode"] = {"error": str(e)}
         if variant == 'llvm_ad_mono':
             out = leg
         else:
@@ -334,7 +349,26 @@ def adjoint_bench(device, rank, world):
     g = dev.grad_get(slot, scene.flat.buffers[slot].size)
     # bytes: primal pass look-ups + backward look-ups (32 B each) + gradient read-modify-write through 8 taps (64 B)
     alg_bytes = 32 * c['n_lookups'] + 64 * (c['n_lookups'] / 2)
+    fast = None
+    try:
+        # backend fast mode (majorant supergrid 16^3 + DDA, not the reference's random sequence): reported next to, never instead of, parity mode
+        fscene = mi.load_dict(scenes.c4_cloud_adjoint(majorant_resolution=16), device=device)
+        fsh = ShardedScene(fscene)
+        fsh.render_backward([1.0, 0.0, 0.0, 0.0], seed=99, spp=4, render_1=True)
+        fscene.device.grad_zero()
+        fsh.render_backward([1.0, 0.0, 0.0, 0.0], seed=0, spp=spp, render_1=True)
+        torch.cuda.synchronize()
+        fc = fscene.device.counters()
+        tf = torch.tensor([fc['kernel_ms']], dtype=torch.float64, device="cuda")
+        if world > 1:
+            torch.distributed.all_reduce(tf, op=torch.distributed.ReduceOp.MAX)
+        fg = fscene.device.grad_get(slot, fscene.flat.buffers[slot].size)
+        fast = {"majorant_resolution": 16, "msamples_per_s": n / (float(tf[0]) / 1e3) / 1e6, "kernel_ms_max_over_ranks": float(tf[0]),
+                "lookups_per_sample": fc['n_lookups'] / max(fc['n_samples'], 1), "grad_abs_sum": float(np.abs(fg.astype(np.float64)).sum())}
+    except Exception as e:
+        fast = {"error": str(e)}
     return {"workload": "C4: C3 scene 512x512x64 spp, prb_volpathaos, render_1_backward wrt the 256^3 sigma_t grid", "kernel": "k_adjoint_pool<mono_polarized>",
+            "fast_mode": fast, "lookups_per_sample": c['n_lookups'] / max(c['n_samples'], 1),
             "msamples_per_s": n / (kernel_ms / 1e3) / 1e6, "kernel_ms_max_over_ranks": kernel_ms,
             "wall_ms_with_gradient_allreduce": wall_ms, "gradient_bytes": int(g.size * 4),
             "grad_abs_sum": float(np.abs(g.astype(np.float64)).sum()), "events_this_rank": c,

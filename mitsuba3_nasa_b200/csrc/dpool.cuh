@@ -56,7 +56,7 @@ constexpr int kPoolChunk = 256;            // lanes per interleaved chunk
 #endif
 constexpr int kPoolMainIters = MIB_POOL_MAIN_ITERS;   // MAIN: null collisions handled per batch before the slot is re-queued
 constexpr int kPoolNeeIters = MIB_POOL_NEE_ITERS;     // NEE: shadow steps per batch
-constexpr unsigned kPoolSpinLimit = 1u << 22;   // watchdog of the two wait loops (idle poll: x 100 ns; ring entry: x ~50 ns)
+constexpr unsigned kPoolSpinLimit = 1u << 22;   // watchdog of the two wait loops (consecutive idle polls x 100 ns; ring entry polls x ~50 ns)
 constexpr uint32_t kNoLane = 0xffffffffu;
 constexpr unsigned kRingEmpty = 0xffffu;
 
@@ -215,7 +215,7 @@ MIB_D bool pool_claim(PoolShared *ps, volatile uint16_t *ring, unsigned lane_id,
                 if (ok && flip) ps->group = g ^ 1u;
             }
             ok = __shfl_sync(FULL, ok, 0);
-            if (ok) { c_sel = best; base = hh; take = t; break; }
+            if (ok) { c_sel = best; base = hh; take = t; idle_spins = 0; break; }      // the idle watchdog counts CONSECUTIVE polls
             continue;
         }
         int stop = 0;

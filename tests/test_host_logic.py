@@ -82,6 +82,17 @@ def test_parameter_validation_messages():
         S.load_dict(d, "llvm_ad_mono")
 
 
+def test_fast_mode_property():
+    """Backend extension: integrator property 'majorant_resolution' (0 = the reference's global majorant)."""
+    d = scenes.c3_cloud(res=8, spp=4, grid_res=8, phase={'type': 'isotropic'})
+    assert S.load_dict(d, "llvm_ad_mono").desc.integrator.majorant_res == 0
+    d = scenes.c3_cloud(res=8, spp=4, grid_res=8, phase={'type': 'isotropic'}, majorant_resolution=16)
+    assert S.load_dict(d, "llvm_ad_mono").desc.integrator.majorant_res == 16
+    d['integrator']['majorant_resolution'] = 1000
+    with pytest.raises(S.PluginError, match="majorant_resolution"):
+        S.load_dict(d, "llvm_ad_mono")
+
+
 def test_gridvolume_layout_and_param_keys():
     grid = np.arange(2 * 3 * 4, dtype=np.float32).reshape(2, 3, 4, 1)      # [z, y, x, c]
     f = S.load_dict(scenes.c3_cloud(res=8, spp=4, grid=grid, phase={'type': 'isotropic'}), "llvm_ad_mono")
