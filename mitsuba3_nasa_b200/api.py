@@ -118,7 +118,7 @@ class SceneParameters:
     def __init__(self, scene):
         self.scene = scene
         self._dirty = set()
-        self._grad_enabled = set()
+        self._torch = {}           # key -> torch tensor assigned by the user (leaf tensors make mi.render differentiable)
 
     def keys(self):
         return sorted(self.scene.flat.params.keys())
@@ -161,6 +161,28 @@ class SceneParameters:
     def __setitem__(self, key, value):
         if key not in self.scene.flat.params:
             raise KeyError(key)
+        if hasattr(value, 'detach') and hasattr(value, 'requires_grad'):     # torch tensor
+            self._torch[key] = value
+            value = value.detach().cpu().numpy()
+        else:
+            self._torch.pop(key, None)
+        self._assign(key, value)
+
+    def enable_grad(self, key):
+        """dr.enable_grad(params[key]): returns the leaf tensor whose .grad receives d(loss)/d(params[key])."""
+        import torch
+        from . import ad
+        if ad.grad_source(self.scene, key) is None:
+            raise RuntimeError("parameter '%s' is not differentiable in this backend (sigma_t / albedo of media are)" % key)
+        t = torch.tensor(np.asarray(self[key], dtype=np.float32), requires_grad=True)
+        self._torch[key] = t
+        self._assign(key, t.detach().numpy())
+        return t
+
+    def attached(self):
+        return {k: t for k, t in self._torch.items() if getattr(t, 'requires_grad', False)}
+
+    def _assign(self, key, value):
         acc = self.scene.flat.params[key]
         f = self.scene.flat
         kind = acc['kind']
@@ -177,7 +199,8 @@ class SceneParameters:
             col = np.broadcast_to(np.asarray(value, dtype=np.float64), (3,))
             getattr(acc[tgt], field)[:] = [float(x) for x in col]
             if kind == 'volume_const':
-                acc['vol'].channels = 3 if (f.spectrum == A.SPEC_RGB and len(set(col.tolist())) > 1) else 1
+                # (an attached RGB constant keeps three channels so that its gradient comes back per channel)
+                acc['vol'].channels = 3 if (f.spectrum == A.SPEC_RGB and (len(set(col.tolist())) > 1 or key in self._torch)) else 1
         elif kind == 'phase_g':
             acc['phase'].g = float(value)
         elif kind == 'medium_scale':
@@ -206,11 +229,28 @@ def traverse(scene):
     return SceneParameters(scene)
 
 
+def _differentiable(scene, params, seed, seed_grad, spp, spp_grad, one):
+    from . import ad
+    it = scene.flat.desc.integrator.type
+    if it not in (A.INTEG_PRBVOLPATH, A.INTEG_PRBVOLPATHAOS):
+        raise RuntimeError("differentiable rendering needs a prbvolpath / prb_volpathaos integrator")
+    att = params.attached()
+    keys = sorted(att)
+    if seed_grad == 0:
+        seed_grad = sample_tea_32(seed, 1)[0]                         # util.py:617-619
+    return ad.render_op().apply(scene, params, keys, int(seed), int(seed_grad), int(spp), int(spp_grad), one, *[att[k] for k in keys])
+
+
 def render(scene, params=None, sensor=0, integrator=None, seed=0, seed_grad=0, spp=0, spp_grad=0):
-    """mi.render (util.py:512-625), primal part; the differentiable wrapper lives in .ad"""
+    """mi.render (util.py:512-625).  With leaf tensors attached to `params` (SceneParameters.enable_grad, or
+    params[key] = tensor) the result is a torch tensor wired to them (ad.py); otherwise a numpy array."""
+    if params is not None and isinstance(params, SceneParameters) and params.attached():
+        return _differentiable(scene, params, seed, seed_grad, spp, spp_grad, False)
     return scene.integrator().render(scene, sensor, seed, spp, develop=True, evaluate=False)
 
 
 def render_1(scene, params=None, sensor=0, integrator=None, seed=0, seed_grad=0, spp=0, spp_grad=0):
     """mi.render_1 (util.py:627-670): one Spectrum / Mueller matrix (Stokes vector in column 0)."""
+    if params is not None and isinstance(params, SceneParameters) and params.attached():
+        return _differentiable(scene, params, seed, seed_grad, spp, spp_grad, True)
     return scene.integrator().render_1(scene, sensor, seed, spp)
