@@ -56,7 +56,9 @@ def test_c3_full_size_film_1024x1024x256():
     assert c['n_samples'] == 1024 * 1024 * 256
     # box filter: weight = number of samples that fell into the pixel = spp, except where fp32 rounds posx + jitter up
     # to the next pixel (jitter within 3e-5 of 1 at x ~ 1000; the reference's ImageBlock::put floors the same float)
-    assert raw.shape == (1024, 1024, 2) and raw[..., 1].sum() == 1024 * 1024 * 256 and np.abs(raw[..., 1] - 256.0).max() <= 3
+    # (and a few samples of the last column / row round up to x = 1024 and leave the film, as in the reference)
+    total = 1024 * 1024 * 256
+    assert raw.shape == (1024, 1024, 2) and total - 200 <= raw[..., 1].sum() <= total and np.abs(raw[..., 1] - 256.0).max() <= 3
     img = raw[..., 0] / raw[..., 1]
     assert np.isfinite(img).all() and img.min() >= 0.0
     # a non-absorbing-ish cloud (albedo 0.99) under a unit constant emitter: every pixel close to, and never above, 1
