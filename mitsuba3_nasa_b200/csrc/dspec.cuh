@@ -90,6 +90,12 @@ MIB_D void world_rotations(const Frame3 &fr, V3 in_l, V3 out_l, float &ci, float
     float2 ri = world_rotation1(fr, in_l), ro = world_rotation1(fr, out_l);
     ci = ri.x; si = ri.y; co = ro.x; so = ro.y;
 }
+// same with the rotation of the outgoing side given (cos, sin)
+MIB_D void m4_to_world_with(const Frame3 &fr, float *M, V3 in_l, float2 out_rot) {
+    const float2 ri = world_rotation1(fr, in_l);
+    m4_rot_left(M, out_rot.x, out_rot.y);
+    m4_rot_right_t(M, ri.x, ri.y);
+}
 MIB_D void m4_to_world(const Frame3 &fr, float *M, V3 in_l, V3 out_l) {
     float ci, si, co, so;
     world_rotations(fr, in_l, out_l, ci, si, co, so);

@@ -18,8 +18,10 @@ template <int SPEC> MIB_D float mis_weight(float a, float b) {               // 
 
 // Null-BSDF Mueller matrix in world space: to_world_mueller(I, wi, wi) -> 2x2 block (see dspec.cuh)
 MIB_D void null_block(const SurfIt &si, float &b11, float &b12, float &b21, float &b22) {
-    float ci, s_i, co, so;
-    world_rotations(si.sh, si.wi, si.wi, ci, s_i, co, so);
+    // in and out direction coincide (wo = -wi of a null BSDF is evaluated as to_world_mueller(I, wi, wi)): the two basis
+    // rotations are the same function of the same arguments, so one evaluation serves both (identical floats)
+    const float2 r = world_rotation1(si.sh, si.wi);
+    const float ci = r.x, s_i = r.y, co = r.x, so = r.y;
     // X = R_out * I, Y = X * R_in^T
     float x11 = co, x12 = so, x21 = -so, x22 = co;
     b11 = fma_(x12, s_i, x11 * ci); b12 = fma_(x12, ci, x11 * (-s_i));
@@ -264,13 +266,19 @@ MIB_D void path_step(Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
             const bool sample_emitters = md.sample_emitters != 0;
             specular_chain = !sample_emitters;
             float W[NT];
+            float2 out_rot = make_float2(1.f, 0.f);
+            bool have_out_rot = false;
             if (sample_emitters) {
                 DirSample<NC> ds;
                 float em[NC];
                 sample_emitter<SPEC, AOS>(rng, cnt, mei.p, v3(0.f), false, nullptr, medium, channel, ds, em);
                 V3 wo = to_local(mei.sh, ds.d);
                 float ppdf = phase_eval<SPEC>(phase, wo, W);
-                if constexpr (POL) m4_to_world(mei.sh, W, -wo, v3(0.f, 0.f, -1.f));
+                if constexpr (POL) {
+                    out_rot = world_rotation1(mei.sh, v3(0.f, 0.f, -1.f));
+                    have_out_rot = true;
+                    m4_to_world_with(mei.sh, W, -wo, out_rot);
+                }
                 float x[NR];
                 TW_col0<SPEC>(T, W, x);
                 if (AOS) {
@@ -288,7 +296,12 @@ MIB_D void path_step(Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
             (void) s1;
             V3 wo;
             float ppdf = phase_sample<SPEC>(phase, s2x, s2y, wo, W);
-            if constexpr (POL) m4_to_world(mei.sh, W, -wo, v3(0.f, 0.f, -1.f));
+            if constexpr (POL) {
+                // the rotation of the outgoing side (local (0,0,-1) in the frame of ray.d) does not depend on wo: the one
+                // computed for the emitter direction a few lines up is reused (identical floats)
+                if (!have_out_rot) out_rot = world_rotation1(mei.sh, v3(0.f, 0.f, -1.f));
+                m4_to_world_with(mei.sh, W, -wo, out_rot);
+            }
             if (!AOS) T_mul_W<SPEC>(T, W);                                   // volpath.cpp:244 (before the pdf test)
             act_scatter = act_scatter && ppdf > 0.f;
             if (act_scatter) {
