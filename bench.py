@@ -237,8 +237,10 @@ def run_ours(args):
                 "d2h_bytes_per_step": 4 * 8 + ctypes.sizeof(_abi.Counters)},
         "gpu_launches": int(launches),
         "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": FP32_PEAK_TFLOPS, "unit": "TFLOP/s",
-                     "frac": achieved_tf / FP32_PEAK_TFLOPS, "traffic": 201728,
-                     "traffic_note": "dram bytes read (writes < 10 KB) by one k_forward<2,1> launch, ncu --set full (profiles/r01_ncu_c2_pol_volpathaos_summary.txt, 2^24 samples): the scene is analytic",
+                     "frac": achieved_tf / FP32_PEAK_TFLOPS, "traffic": int(5466880 * SAMPLES_PER_GPU / float(1 << 24)),
+                     "traffic_note": "dram bytes read + written by one k_forward<2,1> launch: 0.77 MB + 4.69 MB at 2^24 samples in the ncu --set full capture "
+                                     "(profiles/r01_ncu_i_c2_kforward_thread.txt), scaled to this launch's sample count; the scene is analytic, the "
+                                     "writes are local-memory spills (224 B stack frame)",
                      "kernel": "k_forward<mono_polarized, volpathaos> (one thread per path; the library picks the path-pool kernels for heterogeneous media)",
                      "note": "homogeneous medium: no grid traffic, FP32-pipe bound; peak = 148 SM x 128 lanes x 2 x 1.965 GHz "
                              "(derived, not in MEASURED_PEAKS.json); flops = documented per-event constants x exact event counters",
