@@ -97,7 +97,7 @@ EXPORTS = [
     "mib_last_error", "mib_abi_version", "mib_sizeof_scene_desc", "mib_sizeof_device_scene",
     "mib_scene_create", "mib_scene_destroy", "mib_scene_set_buffer", "mib_scene_get_buffer",
     "mib_scene_buffer_dev", "mib_scene_set_desc", "mib_scene_commit", "mib_scene_get_desc",
-    "mib_scene_set_lane_range", "mib_render", "mib_film_dev", "mib_film_develop", "mib_film_read",
+    "mib_scene_set_lane_range", "mib_scene_set_lane_stripes", "mib_render", "mib_film_dev", "mib_film_develop", "mib_film_read",
     "mib_render_1", "mib_render_1_raw", "mib_render_backward", "mib_render_1_backward",
     "mib_grad_get", "mib_grad_dev", "mib_grad_get_scalar", "mib_grad_scalar_dev", "mib_grad_zero",
     "mib_mie_tabulate", "mib_counters_get", "mib_scene_stream",

@@ -80,6 +80,10 @@ class DeviceScene:
     def commit(self):
         self._ck(self.l.mib_scene_commit(self.h))
 
+    def set_lane_stripes(self, rank, world, chunk_lanes):
+        """Rank `rank` of `world` renders the lane chunks rank, rank + world, ... (chunk_lanes lanes each); world <= 1: off."""
+        self._ck(self.l.mib_scene_set_lane_stripes(self.h, C.c_uint32(rank), C.c_uint32(world), C.c_uint64(max(int(chunk_lanes), 1))))
+
     def set_lane_range(self, begin, end):
         self._ck(self.l.mib_scene_set_lane_range(self.h, C.c_uint64(begin), C.c_uint64(end)))
 

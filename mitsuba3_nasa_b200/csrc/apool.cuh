@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
                 else { pm.su(L::F_LANE, slot, kNoLane); atomicAdd(&ps->retired, 1u); }
             }
             if (replay || fresh) {
-                const uint64_t lane = lp.lane_begin + pool_lane(j, blockIdx.x, gridDim.x);
+                const uint64_t lane = stripe_map(lp, lp.lane_begin + pool_lane(j, blockIdx.x, gridDim.x));
                 // integrator.cpp:323-340 (lane -> pixel) + render_sample :1139-1170 (film position, sensor ray)
                 Pcg32 rng;
                 rng.seed_lane(lp.seed_value, (uint32_t) lane);

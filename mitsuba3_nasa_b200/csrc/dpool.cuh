@@ -315,6 +315,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
 
     // integrator.cpp:323-340 (lane -> pixel) + render_sample :1139-1170 (film position, sensor ray)
     auto start = [&](uint64_t lane, Pcg32 &rng, float &sx, float &sy) -> Ray {
+        lane = stripe_map(lp, lane);
         rng.seed_lane(lp.seed_value, (uint32_t) lane);
         uint32_t idx = (uint32_t) (lane / lp.spp);
         uint32_t py = idx / (uint32_t) sn.crop_width, px = idx - (uint32_t) sn.crop_width * py;

@@ -24,7 +24,9 @@ namespace mib {
 struct LaunchParams {
     uint32_t seed_value;       // sampler base seed + render seed
     uint32_t spp;
-    uint64_t lane_begin, lane_end;
+    uint64_t lane_begin, lane_end;   // lanes of this launch; with stripes: VIRTUAL lanes [0, n_local) of this rank
+    uint32_t stripe_rank, stripe_world;      // multi-GPU load balance: chunk c of stripe_chunk lanes belongs to rank c % world
+    uint64_t stripe_chunk;                   // (stripe_world <= 1: no striping, virtual lane = lane)
     uint32_t spt;              // lanes per thread
     int mode;                  // 0 = film accumulate, 1 = render_1 sums (double), 2 = per-sample dump
     float *film;               // [H*W*C]
@@ -32,6 +34,13 @@ struct LaunchParams {
     float *per_sample;         // [lanes*C] (mode 2)
     unsigned long long *counters; // [8]: lookups, real, null, nee_steps, surface, samples, -, pool error code
 };
+
+// virtual lane of a rank -> lane of the wavefront (mib_scene_set_lane_stripes)
+MIB_D uint64_t stripe_map(const LaunchParams &lp, uint64_t v) {
+    if (lp.stripe_world <= 1u) return v;
+    const uint64_t c = v / lp.stripe_chunk;
+    return (c * lp.stripe_world + lp.stripe_rank) * lp.stripe_chunk + (v - c * lp.stripe_chunk);
+}
 
 // launchers defined in inst.cu (one per object file)
 template <int SPEC, int MODE> void launch_k_forward(const DScene &scene, const LaunchParams &lp, unsigned blocks, cudaStream_t st);
@@ -166,6 +175,7 @@ __global__ void __launch_bounds__(128, MIB_MINB) k_forward(const __grid_constant
     };
     // integrator.cpp:323-340 (lane -> pixel) + render_sample :1139-1170 (film position, sensor ray)
     auto start = [&](uint64_t lane, Pcg32 &rng, float &sx, float &sy) -> Ray {
+        lane = stripe_map(lp, lane);
         rng.seed_lane(lp.seed_value, (uint32_t) lane);
         uint32_t idx = (uint32_t) (lane / lp.spp);
         uint32_t py = idx / (uint32_t) sn.crop_width, px = idx - (uint32_t) sn.crop_width * py;
@@ -287,7 +297,7 @@ __global__ void __launch_bounds__(128, MIB_MINB_ADJ) k_adjoint(const __grid_cons
                 prb_init<SPEC, AOS>(rng, ray0, true, Lp, dl, st);
                 pass = 1;
             } else if (lane < l1) {
-                uint64_t cur = lane++;
+                uint64_t cur = stripe_map(lp, lane++);
                 rng.seed_lane(lp.seed_value, (uint32_t) cur);
                 uint32_t idx = (uint32_t) (cur / lp.spp);
                 uint32_t py = idx / (uint32_t) sn.crop_width, px = idx - (uint32_t) sn.crop_width * py;

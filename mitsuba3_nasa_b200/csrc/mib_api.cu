@@ -53,6 +53,8 @@ struct mib_scene {
     float *lane_L = nullptr;                     // adjoint: per-lane primal radiance
     size_t lane_L_n = 0;
     uint64_t lane_begin = 0, lane_end = 0;
+    uint32_t stripe_rank = 0, stripe_world = 1;  // lane stripes (multi-GPU load balance), see mib_scene_set_lane_stripes
+    uint64_t stripe_chunk = 0;
     mib_counters last = {};
     bool committed = false;
     uint32_t last_spp = 1;
@@ -329,6 +331,18 @@ static void lane_range(mib_scene *s, uint32_t spp, uint64_t &b, uint64_t &e) {
     if (total > 0xffffffffull)
         throw std::runtime_error("Tried to perform a rendering with a total sample count that exceeds 2^32 "
                                  "(the upper limit for one pass). Please use fewer samples per pixel or render using multiple passes.");
+    if (s->stripe_world > 1) {
+        // this rank's chunks are c = rank, rank + world, ...; only the last chunk of the wavefront can be partial, and it is
+        // the last chunk of the rank that owns it, so the rank's lanes form the contiguous VIRTUAL range [0, n_local)
+        const uint64_t ch = s->stripe_chunk, chunks = (total + ch - 1) / ch;
+        uint64_t owned = chunks > s->stripe_rank ? (chunks - 1 - s->stripe_rank) / s->stripe_world + 1 : 0, n_local = 0;
+        if (owned) {
+            const uint64_t last = s->stripe_rank + (owned - 1) * s->stripe_world;
+            n_local = (owned - 1) * ch + (last == chunks - 1 ? total - last * ch : ch);
+        }
+        b = 0; e = n_local;
+        return;
+    }
     if (s->lane_begin == 0 && s->lane_end == 0) { b = 0; e = total; }
     else { b = std::min(s->lane_begin, total); e = std::min(s->lane_end, total); }
 }
@@ -354,7 +368,9 @@ static void run_forward(mib_scene *s, uint32_t seed, uint32_t spp, int mode, flo
     lp.seed_value = s->ds.d.sampler_base_seed + seed;
     lp.spp = spp;
     lane_range(s, spp, lp.lane_begin, lp.lane_end);
+    lp.stripe_rank = s->stripe_rank; lp.stripe_world = s->stripe_world; lp.stripe_chunk = s->stripe_chunk;
     lp.spt = pick_spt(lp.lane_end - lp.lane_begin, spp);
+    if (s->stripe_world > 1) while (s->stripe_chunk % lp.spt) --lp.spt;       // a thread's lanes stay inside one chunk
     lp.mode = mode;
     lp.film = s->film_raw;
     lp.sums = s->sums;
@@ -500,6 +516,16 @@ int mib_scene_set_lane_range(mib_scene *s, uint64_t b, uint64_t e) {
     MIB_CATCH
 }
 
+int mib_scene_set_lane_stripes(mib_scene *s, uint32_t rank, uint32_t world, uint64_t chunk_lanes) {
+    MIB_TRY
+    if (world <= 1) { s->stripe_rank = 0; s->stripe_world = 1; s->stripe_chunk = 0; return 0; }
+    if (rank >= world) throw std::runtime_error("mib_scene_set_lane_stripes: rank >= world");
+    if (chunk_lanes == 0) throw std::runtime_error("mib_scene_set_lane_stripes: chunk must be > 0");
+    s->stripe_rank = rank; s->stripe_world = world; s->stripe_chunk = chunk_lanes;
+    s->lane_begin = s->lane_end = 0;
+    MIB_CATCH
+}
+
 int mib_render(mib_scene *s, uint32_t seed, uint32_t spp, int do_develop, float *out_host) {
     MIB_TRY
     run_forward(s, seed, spp, 0, nullptr);
@@ -568,9 +594,10 @@ int mib_debug_sample_lanes(mib_scene *s, uint32_t seed, uint32_t spp, uint64_t l
     float *dev = nullptr;
     CK(cudaMalloc(&dev, count * C * sizeof(float)));
     uint64_t sb = s->lane_begin, se = s->lane_end;
-    s->lane_begin = lane_begin; s->lane_end = lane_begin + count;
-    try { run_forward(s, seed, spp, 2, dev); } catch (...) { s->lane_begin = sb; s->lane_end = se; cudaFree(dev); throw; }
-    s->lane_begin = sb; s->lane_end = se;
+    const uint32_t sw = s->stripe_world;
+    s->lane_begin = lane_begin; s->lane_end = lane_begin + count; s->stripe_world = 1;
+    try { run_forward(s, seed, spp, 2, dev); } catch (...) { s->lane_begin = sb; s->lane_end = se; s->stripe_world = sw; cudaFree(dev); throw; }
+    s->lane_begin = sb; s->lane_end = se; s->stripe_world = sw;
     CK(cudaMemcpy(out_host, dev, count * C * sizeof(float), cudaMemcpyDeviceToHost));
     CK(cudaFree(dev));
     MIB_CATCH

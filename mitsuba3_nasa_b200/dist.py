@@ -35,6 +35,18 @@ def lane_slice(n_pixels, spp, rank, world):
     return b, b + per + (1 if rank < rem else 0)
 
 
+STRIPE_PIXELS = 64     # pixels per stripe chunk
+
+
+def stripe_lanes(n_pixels, spp, rank, world, chunk_pixels=STRIPE_PIXELS):
+    """Lanes of `rank` under striping (host mirror of mib_scene_set_lane_stripes, for tests and documentation): chunk c of
+    chunk_pixels * spp lanes belongs to rank c % world.  Every rank samples the whole image, so the slowest rank is not the
+    one that happens to own the rows through the cloud (contiguous slices: 37 % strong-scaling efficiency on C5 at 8 GPUs)."""
+    total, chunk = int(n_pixels) * int(spp), int(chunk_pixels) * int(spp)
+    lanes = np.arange(total, dtype=np.int64)
+    return lanes[(lanes // chunk) % world == rank]
+
+
 class _DevArray:
     """Zero-copy view of a device buffer owned by the CUDA library."""
 
@@ -73,6 +85,11 @@ class ShardedScene:
     def _set_slice(self, spp):
         sn = self.scene.flat.desc.sensor
         n_pix = sn.crop_width * sn.crop_height
+        if self.world > 1 and n_pix >= 4 * STRIPE_PIXELS * self.world:
+            # films: interleaved stripes of 64 pixels, every rank samples the whole image (load balance)
+            self.scene.device.set_lane_stripes(self.rank, self.world, STRIPE_PIXELS * spp)
+            return
+        self.scene.device.set_lane_stripes(0, 1, 1)
         b, e = lane_slice(n_pix, spp, self.rank, self.world)
         if b == e:                        # empty slice: (total, total); (0, 0) would mean "everything"
             b = e = n_pix * spp

@@ -33,11 +33,8 @@ for lg in range(7, max_log + 1):
     ms, lookups, n, acc = 0.0, 0, 0, None
     t0 = time.perf_counter()
     for p, spp in enumerate(passes):
-        lanes = res * res * spp
-        per = (lanes + world - 1) // world
-        per = (per + spp - 1) // spp * spp                            # whole pixels per rank
-        b, e = min(rank * per, lanes), min((rank + 1) * per, lanes)
-        dev.set_lane_range(b, e) if world > 1 else dev.set_lane_range(0, 0)
+        if world > 1:
+            dev.set_lane_stripes(rank, world, 64 * spp)                   # interleaved stripes of 64 pixels: every rank samples the whole image
         raw = dev.render(p, spp, develop=False, to_host=(lg <= 8))     # seed + pass
         c = dev.counters()
         ms += c['kernel_ms']; lookups += c['n_lookups']; n += c['n_samples']

@@ -107,3 +107,17 @@ def test_world_size_2_gloo_matches_single_process(tmp_path):
     gi = np.random.default_rng(1).uniform(-1, 1, (6, 6, 3)).astype(np.float32)
     o3.render_backward(2, 8, gi, nthreads=2)
     assert np.allclose(got["grads"], o3.grad_get_scalar(0), rtol=1e-10, atol=1e-14)
+
+
+def test_stripe_lanes_partition_the_wavefront():
+    """Load-balanced sharding: interleaved stripes of 64 pixels tile the lane range exactly once (host mirror of
+    mib_scene_set_lane_stripes), for sizes that are not multiples of the chunk."""
+    from mitsuba3_nasa_b200.dist import stripe_lanes
+    for n_pix, spp, world in ((1000, 3, 4), (64 * 7 + 5, 8, 2), (512, 1, 8), (10, 4, 3)):
+        parts = [stripe_lanes(n_pix, spp, r, world) for r in range(world)]
+        allv = np.sort(np.concatenate(parts))
+        assert np.array_equal(allv, np.arange(n_pix * spp))
+        # whole pixels per rank, and every rank's lanes are spread over the whole range
+        for p in parts:
+            if p.size:
+                assert (p // spp).size == p.size and np.all(np.bincount(p // spp)[np.unique(p // spp)] == spp)

@@ -133,3 +133,43 @@ def test_adjoint_pool_equals_thread_kernel(variant, integ):
     scale = np.abs(out['thread'][0]).max()
     assert scale > 0
     assert np.abs(out['pool'][0] - out['thread'][0]).max() <= 1e-4 * scale      # float atomics in a different order
+
+
+@pytest.mark.parametrize("fk", ["pool", "thread"])
+def test_lane_stripes_add_up_to_the_whole_film(fk):
+    """mib_scene_set_lane_stripes (multi-GPU load balance): the ranks' striped renders sum to the whole film, every lane
+    is walked exactly once (counters add up), for a wavefront that is not a multiple of the stripe chunk."""
+    sc = S.load_dict(scenes.c3_cloud(res=40, spp=8, grid=scenes.cloud_grid(16), phase=_mie_free_phase()), 'llvm_ad_mono')
+    dev = _lib.DeviceScene(sc, 0)
+    with kernel('MIB_FORWARD_KERNEL', fk):
+        full = np.asarray(dev.render(6, 8, develop=False), dtype=np.float64)
+        c_full = dev.counters()
+        acc, cnt = np.zeros_like(full), {k: 0 for k in COUNTERS}
+        world = 3
+        for r in range(world):
+            dev.set_lane_stripes(r, world, 8 * 24)                 # 24 pixels per chunk: 1600 pixels = 66 chunks + 16 pixels
+            acc += dev.render(6, 8, develop=False)
+            c = dev.counters()
+            for k in COUNTERS:
+                cnt[k] += c[k]
+        dev.set_lane_stripes(0, 1, 1)
+    assert cnt == {k: c_full[k] for k in COUNTERS}
+    assert np.allclose(acc, full, rtol=1e-5, atol=1e-6)
+
+
+def test_lane_stripes_adjoint():
+    grid = scenes.cloud_grid(16)
+    d = scenes.c3_cloud(res=32, spp=16, grid=grid, phase=_mie_free_phase(), optical_depth=6.0, integrator='prbvolpath', max_depth=12)
+    sc = S.load_dict(d, 'llvm_ad_mono')
+    dev = _lib.DeviceScene(sc, 0)
+    slot = sc.desc.media[0].sigma_t.buffer
+    g_img = np.ones((32, 32, 1), dtype=np.float32)
+    dev.grad_zero(); dev.render_backward(2, 16, g_img)
+    whole = dev.grad_get(slot, grid.size).astype(np.float64)
+    dev.grad_zero()
+    for r in range(2):
+        dev.set_lane_stripes(r, 2, 16 * 10)
+        dev.render_backward(2, 16, g_img)                          # gradients accumulate over the two "ranks"
+    dev.set_lane_stripes(0, 1, 1)
+    parts = dev.grad_get(slot, grid.size).astype(np.float64)
+    assert np.abs(parts - whole).max() <= 1e-4 * np.abs(whole).max()
