@@ -85,6 +85,24 @@ class ClockSampler:
         return out
 
 
+_JSON_FD = None
+
+
+def _capture_stdout():
+    """Native libraries (NCCL's version banner, CUDA warnings) write to fd 1: route everything to stderr and keep the
+    original stdout for the ONE JSON line of the contract."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    os.write(_JSON_FD if _JSON_FD is not None else 1, (json.dumps(line) + "\n").encode())
+
+
 def _lib_handle():
     from mitsuba3_nasa_b200 import _lib
     l = _lib.lib()
@@ -135,7 +153,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_ours(args):
@@ -262,7 +280,7 @@ def run_ours(args):
         line["cpu_baseline"] = {"value": v, "unit": "Msamples/s", "cores": cores, "kind": "port",
                                 "sample": "%d of the 1e8 samples (%.1f s), std::thread over lane ranges" % (n_cpu, dt),
                                 "stokes": [float(x) for x in out]}
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -387,6 +405,7 @@ def main():
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
     ap.add_argument('--no-adjoint', action='store_true', help='skip the C4 adjoint leg')
     args = ap.parse_args()
+    _capture_stdout()
     if args.impl == 'reference':
         run_reference(args)
     else:
