@@ -224,9 +224,10 @@ int  mib_scene_get_desc(mib_scene *scene, mib_scene_desc *out);
 /* Restrict rendering to the global lane range [lane_begin, lane_end) of the
    wavefront (multi-GPU sharding by sample range). (0,0) = all. */
 int  mib_scene_set_lane_range(mib_scene *scene, uint64_t lane_begin, uint64_t lane_end);
-/* Multi-GPU load balance: instead of one contiguous range, rank r of `world` renders the chunks
- * c = r, r + world, r + 2 world, ... of `chunk_lanes` lanes each (a multiple of spp keeps pixels whole), so that every rank
- * samples the whole image.  world <= 1 switches striping off; setting stripes clears the lane range. */
+/* Multi-GPU load balance: instead of one contiguous range, the wavefront is cut into chunks of `chunk_lanes`
+ * lanes (a multiple of spp keeps pixels whole), dealt in groups of `world`: in group g rank r renders chunk
+ * g * world + ((r - g) mod world), so every rank samples the whole image (the rotation by g keeps a rank from always
+ * getting the same column band).  world <= 1 switches striping off; setting stripes clears the lane range. */
 int  mib_scene_set_lane_stripes(mib_scene *scene, uint32_t rank, uint32_t world, uint64_t chunk_lanes);
 
 /* Forward render into the raw accumulation film [H][W][C] (C = 4: R,G,B,W for

@@ -35,11 +35,14 @@ struct LaunchParams {
     unsigned long long *counters; // [8]: lookups, real, null, nee_steps, surface, samples, -, pool error code
 };
 
-// virtual lane of a rank -> lane of the wavefront (mib_scene_set_lane_stripes)
+// virtual lane of a rank -> lane of the wavefront (mib_scene_set_lane_stripes).  Chunks are dealt in groups of `world`:
+// in group g rank r owns chunk g * world + ((r - g) mod world) -- the rotation by g keeps a rank from always getting the
+// same column band when the row length is a multiple of world * chunk (512-pixel rows, 64-pixel chunks, 8 ranks).
 MIB_D uint64_t stripe_map(const LaunchParams &lp, uint64_t v) {
     if (lp.stripe_world <= 1u) return v;
-    const uint64_t c = v / lp.stripe_chunk;
-    return (c * lp.stripe_world + lp.stripe_rank) * lp.stripe_chunk + (v - c * lp.stripe_chunk);
+    const uint64_t g = v / lp.stripe_chunk, w = lp.stripe_world;
+    const uint64_t c = g * w + ((lp.stripe_rank + w - g % w) % w);
+    return c * lp.stripe_chunk + (v - g * lp.stripe_chunk);
 }
 
 // launchers defined in inst.cu (one per object file)

@@ -332,14 +332,15 @@ static void lane_range(mib_scene *s, uint32_t spp, uint64_t &b, uint64_t &e) {
         throw std::runtime_error("Tried to perform a rendering with a total sample count that exceeds 2^32 "
                                  "(the upper limit for one pass). Please use fewer samples per pixel or render using multiple passes.");
     if (s->stripe_world > 1) {
-        // this rank's chunks are c = rank, rank + world, ...; only the last chunk of the wavefront can be partial, and it is
-        // the last chunk of the rank that owns it, so the rank's lanes form the contiguous VIRTUAL range [0, n_local)
-        const uint64_t ch = s->stripe_chunk, chunks = (total + ch - 1) / ch;
-        uint64_t owned = chunks > s->stripe_rank ? (chunks - 1 - s->stripe_rank) / s->stripe_world + 1 : 0, n_local = 0;
-        if (owned) {
-            const uint64_t last = s->stripe_rank + (owned - 1) * s->stripe_world;
-            n_local = (owned - 1) * ch + (last == chunks - 1 ? total - last * ch : ch);
-        }
+        // chunks are dealt in groups of `world`; in group g this rank owns chunk g * world + ((rank - g) mod world)
+        // (kernels.cuh stripe_map).  Only the last chunk of the wavefront can be partial and only the last group incomplete,
+        // so the rank's lanes form the contiguous VIRTUAL range [0, n_local).
+        const uint64_t ch = s->stripe_chunk, chunks = (total + ch - 1) / ch, w = s->stripe_world;
+        const uint64_t full_groups = chunks / w, rem = chunks % w;
+        auto my_chunk = [&](uint64_t g) { return g * w + ((s->stripe_rank + w - g % w) % w); };
+        const uint64_t owned = full_groups + ((rem && my_chunk(full_groups) < chunks) ? 1 : 0);
+        uint64_t n_local = owned * ch;
+        if (owned && my_chunk(owned - 1) == chunks - 1) n_local -= ch - (total - (chunks - 1) * ch);   // the wavefront's last chunk
         b = 0; e = n_local;
         return;
     }
