@@ -11,23 +11,16 @@ template <> void launch_k_forward<INST_SPEC, INST_MODE>(const DScene &scene, con
 }
 #elif defined(INST_POOL)
 template <> void launch_k_forward_pool<INST_SPEC, INST_MODE>(const DScene &scene, const LaunchParams &lp, unsigned blocks, unsigned threads, cudaStream_t st) {
-    static bool configured = false;
     const size_t smem = pool_smem_bytes<INST_SPEC>();
-    if (!configured) {
-        cudaFuncSetAttribute(k_forward_pool<INST_SPEC, INST_MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
-        configured = true;
-    }
+    // per device and cheap: set at every launch (a process may hold scenes on several devices)
+    cudaFuncSetAttribute(k_forward_pool<INST_SPEC, INST_MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
     cudaMemcpyToSymbolAsync(sc, &scene, sizeof(DScene), 0, cudaMemcpyHostToDevice, st);
     k_forward_pool<INST_SPEC, INST_MODE><<<blocks, threads, smem, st>>>(lp);
 }
 template <> int pool_slots<INST_SPEC, INST_MODE>() { return PoolL<INST_SPEC>::P; }
 #elif defined(INST_APOOL)
 template <> void launch_k_adjoint_pool<INST_SPEC>(const DScene &scene, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, unsigned threads, cudaStream_t st) {
-    static bool configured = false;
-    if (!configured) {
-        cudaFuncSetAttribute(k_adjoint_pool<INST_SPEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
-        configured = true;
-    }
+    cudaFuncSetAttribute(k_adjoint_pool<INST_SPEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
     cudaMemcpyToSymbolAsync(sc, &scene, sizeof(DScene), 0, cudaMemcpyHostToDevice, st);
     k_adjoint_pool<INST_SPEC><<<blocks, threads, apool_smem_bytes<INST_SPEC>(), st>>>(lp, ap);
 }
