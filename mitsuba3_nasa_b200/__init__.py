@@ -9,3 +9,4 @@ from .transforms import ScalarTransform4f, Transform4f  # noqa: F401
 from .api import (set_variant, variant, variants, load_dict, traverse, render, render_1,  # noqa: F401
                   Scene, SceneParameters, Integrator, sample_tea_32)
 from .scene import PluginError  # noqa: F401
+from .exr import write_exr, read_exr  # noqa: F401
