@@ -200,6 +200,23 @@ MIB_DH void sample_emitter_direction(V3 ref_p, float sx, float sy, DirSample<NC>
 #pragma unroll
         for (int c2 = 0; c2 < NC; ++c2) spec[c2] = e.radiance[NC == 3 ? c2 : 0];
     }
+    else if (e.type == MIB_EMITTER_AREA) {
+        // area.cpp:119-143 (uniform radiance) -> Shape::sample_direction (shape.cpp:358-375) -> Rectangle::sample_position
+        // (rectangle.cpp:166-180); scene.py admits area emitters on rectangles only
+        const mib_shape &sh = sc.d.shapes[e.shape];
+        V3 p = xform_point_affine(sh.to_world, v3(sx * 2.f - 1.f, sy * 2.f - 1.f, 0.f));
+        V3 nn = v3(sh.frame_n[0], sh.frame_n[1], sh.frame_n[2]);
+        V3 d = p - ref_p;
+        float d2 = sqnorm(d), dist = sqrt_(d2);
+        d = d * rcp_(dist);                                  // Vector / Float = multiplication by rcp (array_router.h:226-229)
+        float dp = fabsf(dot(d, nn)), x = div_(d2, dp);
+        float pdf = sh.inv_surface_area * (isfinite(x) ? x : 0.f);
+        bool act = dot(d, nn) < 0.f && pdf != 0.f;
+        ds.p = p; ds.pdf = pdf; ds.delta = false; ds.d = d; ds.dist = dist;
+        float ip = rcp_(pdf);
+#pragma unroll
+        for (int c2 = 0; c2 < NC; ++c2) spec[c2] = act ? e.radiance[NC == 3 ? c2 : 0] * ip : 0.f;
+    }
     ds.emitter = index;
     if (n > 1) {
         ds.pdf *= pmf;
@@ -207,10 +224,27 @@ MIB_DH void sample_emitter_direction(V3 ref_p, float sx, float sy, DirSample<NC>
         for (int c2 = 0; c2 < NC; ++c2) spec[c2] *= weight;
     }
 }
-MIB_D float pdf_emitter_direction(int emitter) {          // scene.cpp:355-366
+// scene.cpp:355-366 with constant.cpp:139-144 / directional (0) / area.cpp:145-173: DirectionSample3f(scene, si, ref)
+// (d = (si.p - ref.p) / dist, n = si.sh_frame.n) and Shape::pdf_direction (shape.cpp:377-388)
+MIB_D float pdf_emitter_direction(int emitter, V3 ref_p, V3 si_p, V3 si_n) {
     const mib_emitter &e = sc.d.emitters[emitter];
     float pmf = sc.d.n_emitters > 1 ? rcp_((float) sc.d.n_emitters) : 1.f;
-    return (e.type == MIB_EMITTER_CONSTANT ? kInvFourPi : 0.f) * pmf;
+    float pdf = 0.f;
+    if (e.type == MIB_EMITTER_CONSTANT) pdf = kInvFourPi;
+    else if (e.type == MIB_EMITTER_AREA) {
+        V3 rel = si_p - ref_p;
+        float dist = norm(rel);
+        V3 d = rel * rcp_(dist);
+        float dp = dot(d, si_n), adp = fabsf(dp);
+        float v = sc.d.shapes[e.shape].inv_surface_area * (adp != 0.f ? div_(dist * dist, adp) : 0.f);
+        pdf = dp < 0.f ? v : 0.f;
+    }
+    return pdf * pmf;
+}
+// Emitter::eval at a hit, channel r: the area light is one-sided (area.cpp:83-90)
+template <int NC> MIB_D float emitter_eval(const mib_emitter &e, int r, float cos_theta_wi) {
+    if (e.type == MIB_EMITTER_AREA && !(cos_theta_wi > 0.f)) return 0.f;
+    return e.radiance[NC == 3 ? r : 0];
 }
 MIB_D int si_emitter(const SurfIt &si) {
     return valid(si) ? sc.d.shapes[si.shape].emitter : sc.d.environment;

@@ -84,7 +84,8 @@ template <int SPEC> struct PoolL {
     static constexpr int F_NDIST = F_NEV + NC;         // total_dist, max_dist, ds_dist
     static constexpr int F_NA = F_NDIST + 3;
     static constexpr int F_NW = F_NA + NR;
-    static constexpr int F_COUNT = F_NW + 1;
+    static constexpr int F_LSP = F_NW + 1;             // position of the last scattering event (3; used with area emitters only)
+    static constexpr int F_COUNT = F_LSP + 3;
     // slots per CTA: as many as fit into the 227 KB of opt-in shared memory (state words + one 16-bit entry per stage ring),
     // a compile-time constant so that every field access is one LDS / STS with an immediate offset
     static constexpr int P = ((232448 - 256 - 2 * kPoolRings * kPoolRingSlack) / (F_COUNT * 4 + 2 * kPoolRings)) / 32 * 32;
@@ -402,6 +403,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                                                 ((uint32_t) (st.medium + 1) << 8));
                     pm.sf(L::F_ETA, slot, 1.f);
                     pm.sf(L::F_LASTPDF, slot, 1.f);
+                    if (sc.has_area_emitter) pm.sv3(L::F_LSP, slot, v3(0.f));
                     pm.sv3(L::F_RAY, slot, ray0.o); pm.sv3(L::F_RAY + 3, slot, ray0.d); pm.sf(L::F_RAY + 6, slot, ray0.maxt);
                     pm.store_si(L::F_SI, slot, st.si);
 #pragma unroll
@@ -432,6 +434,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                 st.ray.o = pm.v3f(L::F_RAY, slot); st.ray.d = pm.v3f(L::F_RAY + 3, slot); st.ray.maxt = pm.f(L::F_RAY + 6, slot);
                 pm.load_si(L::F_SI, slot, st.si);
                 if (!st.needs_intersection && st.si.shape >= 0) si_finalize(st.ray.d, st.si);
+                st.last_p = sc.has_area_emitter ? pm.v3f(L::F_LSP, slot) : v3(0.f);
 #pragma unroll
                 for (int i = 0; i < NT; ++i) st.T[i] = pm.f(L::F_T + i, slot);
 #pragma unroll
@@ -460,6 +463,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                     if (ev == EV_NULL) next = C_MAIN;
                     else if (ev == EV_SCATTER) {
                         pm.sv3(L::F_SCP, slot, st.scatter_p);
+                        if (sc.has_area_emitter) pm.sv3(L::F_LSP, slot, st.last_p);
 #pragma unroll
                         for (int c = 0; c < NC; ++c) pm.sf(L::F_NEV + c, slot, u[c]);
                         next = C_SCAT;
@@ -606,6 +610,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                 st.specular_chain = fl & FL_SPEC_CHAIN;
                 st.depth = pm.u(L::F_DEPTH, slot);
                 st.last_pdf = pm.f(L::F_LASTPDF, slot);
+                st.last_p = sc.has_area_emitter ? pm.v3f(L::F_LSP, slot) : v3(0.f);
                 st.ray.o = pm.v3f(L::F_RAY, slot); st.ray.d = pm.v3f(L::F_RAY + 3, slot); st.ray.maxt = pm.f(L::F_RAY + 6, slot);
                 pm.load_si(L::F_SI, slot, st.si);
                 si_finalize(st.ray.d, st.si);
@@ -617,6 +622,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                 for (int i = 0; i < NT; ++i) pm.sf(L::F_T + i, slot, st.T[i]);
                 pm.sv3(L::F_RAY, slot, st.ray.o); pm.sv3(L::F_RAY + 3, slot, st.ray.d); pm.sf(L::F_RAY + 6, slot, st.ray.maxt);
                 pm.sf(L::F_LASTPDF, slot, st.last_pdf);
+                if (sc.has_area_emitter) pm.sv3(L::F_LSP, slot, st.last_p);
                 pm.su(L::F_DEPTH, slot, st.depth);
                 pm.su(L::F_FLAGS, slot, (fl & ~(FL_NEEDS_INT | FL_SPEC_CHAIN | 0xff00u)) | FL_NEEDS_INT |
                                             (st.specular_chain ? FL_SPEC_CHAIN : 0u) | ((uint32_t) (st.medium + 1) << 8));

@@ -31,6 +31,7 @@ struct DScene {
     // majorants, super[m][(z*M + y)*M + x] = scale * max of the sigma_t texels any trilinear look-up inside the cell can touch
     const float *super[MIB_MAX_MEDIA];
     int super_res;                                // M (0: reference behaviour, one global majorant)
+    int has_area_emitter;                         // pool kernels carry the last scattering position only when it is needed
 };
 
 // The scene of the running launch.  One copy per translation unit (each kernel instantiation is its own object

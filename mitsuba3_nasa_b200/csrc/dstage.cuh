@@ -43,6 +43,7 @@ template <int SPEC> struct WalkState {
     SurfIt si;
     float eta, last_pdf;
     V3 scatter_p;                 // mei.p of the real scatter being processed
+    V3 last_p;                    // position of the last scattering event (MIS pdf of an area light that is hit)
     int medium;
     uint32_t depth, channel;
     bool specular_chain, needs_intersection;
@@ -65,6 +66,7 @@ MIB_D void walk_init(Pcg32 &rng, const Ray &ray, WalkState<SPEC> &st) {
     if (SPEC == MIB_SPEC_RGB) st.channel = (uint32_t) fminf(rng.next() * 3.f, 2.f);
     st.si.t = inf_f(); st.si.shape = -1; st.si.face = 0; st.si.p = v3(0.f); st.si.wi = v3(0.f);
     st.last_pdf = 1.f;
+    st.last_p = v3(0.f);
     st.nee.active = false;
 }
 
@@ -283,6 +285,7 @@ MIB_D int stg_main(Pcg32 &rng, Counters &cnt, WalkState<SPEC> &st, float *u_out,
             for (int c = 0; c < NC; ++c) u_out[c] = div_(mei.sigma_s[c], mei.sigma_t[c]);
         }
         st.scatter_p = mei.p;
+        st.last_p = mei.p;
         return EV_SCATTER;
     }
     if (active_surface || escaped) {
@@ -292,14 +295,14 @@ MIB_D int stg_main(Pcg32 &rng, Counters &cnt, WalkState<SPEC> &st, float *u_out,
             int emitter = si_emitter(si);
             if (emitter >= 0 && !(st.depth == 0u && I.hide_emitters)) {
                 float emitter_pdf = 1.0f;
-                if (!count_direct) emitter_pdf = pdf_emitter_direction(emitter);
+                if (!count_direct) emitter_pdf = pdf_emitter_direction(emitter, st.last_p, si.p, si.sh.n);
                 const mib_emitter &e = sc.d.emitters[emitter];
                 float x[NR];
                 T_col0<SPEC>(T, x);
                 float w = mis_weight<SPEC>(st.last_pdf, emitter_pdf);
 #pragma unroll
                 for (int r = 0; r < NR; ++r) {
-                    float er = e.radiance[NC == 3 ? r : 0];
+                    float er = emitter_eval<NC>(e, r, si.wi.z);
                     R[r] += count_direct ? x[r] * er : (x[r] * w) * er;
                 }
                 R_dirty = true;
@@ -423,7 +426,7 @@ MIB_D void stg_bsdf(Pcg32 &rng, WalkState<SPEC> &st) {
     st.ray = spawn_ray(si.p, si.n, to_world(si.sh, wo_l));
     st.needs_intersection = true;
     bool non_null = !(sampled & kBsdfNull);
-    if (non_null) { st.depth += 1; st.last_pdf = bs_pdf; }
+    if (non_null) { st.depth += 1; st.last_pdf = bs_pdf; st.last_p = si.p; }
     st.specular_chain = st.specular_chain || (non_null && (sampled & kBsdfDelta));
     st.specular_chain = st.specular_chain && !(sampled & kBsdfSmooth);
     if (is_medium_transition(si)) st.medium = target_medium(si, st.ray.d);

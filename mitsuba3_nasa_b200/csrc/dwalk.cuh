@@ -156,6 +156,7 @@ template <int SPEC> struct PathState {
     Ray ray;
     SurfIt si;
     float eta, last_pdf;
+    V3 last_p;                    // position of the last scattering event (MIS pdf of an area light that is hit)
     int medium;
     uint32_t depth, channel;
     bool active, specular_chain, needs_intersection;
@@ -177,6 +178,7 @@ MIB_D void path_init(Pcg32 &rng, const Ray &ray, PathState<SPEC> &st) {
     if (SPEC == MIB_SPEC_RGB) st.channel = (uint32_t) fminf(rng.next() * 3.f, 2.f);
     st.si.t = inf_f(); st.si.shape = -1; st.si.wi = v3(0.f);
     st.last_pdf = 1.f;
+    st.last_p = v3(0.f);
 }
 
 // One iteration of the reference's while loop (volpath.cpp:121-328 / volpathaos.cpp:85-294).
@@ -241,7 +243,7 @@ MIB_D void path_step(Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
                     for (int c = 0; c < NC; ++c) u2[c] = (mei.sigma_n[c] * mjc) * isn;
                     T_mul_u<SPEC>(T, u2);
                 }
-                if (act_scatter) depth += 1;
+                if (act_scatter) { depth += 1; st.last_p = mei.p; }
             }
         }
         active = active && depth < maxd;
@@ -319,14 +321,14 @@ MIB_D void path_step(Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
             int emitter = si_emitter(si);
             if (emitter >= 0 && !(depth == 0u && I.hide_emitters)) {
                 float emitter_pdf = 1.0f;
-                if (!count_direct) emitter_pdf = pdf_emitter_direction(emitter);
+                if (!count_direct) emitter_pdf = pdf_emitter_direction(emitter, st.last_p, si.p, si.sh.n);
                 const mib_emitter &e = sc.d.emitters[emitter];
                 float x[NR];
                 T_col0<SPEC>(T, x);
                 float w = mis_weight<SPEC>(last_pdf, emitter_pdf);
 #pragma unroll
                 for (int r = 0; r < NR; ++r) {
-                    float er = e.radiance[NC == 3 ? r : 0];
+                    float er = emitter_eval<NC>(e, r, si.wi.z);
                     R[r] += count_direct ? x[r] * er : (x[r] * w) * er;
                 }
             }
@@ -384,7 +386,7 @@ MIB_D void path_step(Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
             ray = spawn_ray(si.p, si.n, to_world(si.sh, wo_l));
             needs_intersection = true;
             bool non_null = !(sampled & kBsdfNull);
-            if (non_null) { depth += 1; last_pdf = bs_pdf; }
+            if (non_null) { depth += 1; last_pdf = bs_pdf; st.last_p = si.p; }
             specular_chain = specular_chain || (non_null && (sampled & kBsdfDelta));
             specular_chain = specular_chain && !(sampled & kBsdfSmooth);
             if (is_medium_transition(si)) medium = target_medium(si, ray.d);

@@ -175,6 +175,8 @@ static void commit(mib_scene *s) {
         }
     }
     s->ds.super_res = d.integrator.majorant_res;
+    s->ds.has_area_emitter = 0;
+    for (int i = 0; i < d.n_emitters; ++i) if (d.emitters[i].type == MIB_EMITTER_AREA) s->ds.has_area_emitter = 1;
     for (int i = 0; i < d.n_phases; ++i) {
         const mib_phase &p = d.phases[i];
         if (p.type == MIB_PHASE_TABPHASE || p.type == MIB_PHASE_TABPHASE_POLARIZED) {

@@ -485,6 +485,9 @@ class Scene:
             out.radiance[:] = self._color(pr.child('radiance') or pr.get('radiance', 1.0), key)
             if shape < 0:
                 raise PluginError("area emitter must be attached to a shape")
+            if self.desc.shapes[shape].type != A.SHAPE_RECTANGLE:
+                raise PluginError("area emitters are supported on rectangle shapes only (emitter sampling of cube / sphere is not implemented)")
+            self.params[key + '.radiance.value'] = {'kind': 'emitter_radiance', 'emitter': out}
         else:
             raise PluginError("unsupported emitter '%s'" % e.type)
         pr.finish()

@@ -193,7 +193,21 @@ static inline Color<NC> sample_emitter_direction(const Scene &sc, Vec3 ref_p, fl
         ds.p = ref_p - d * dist; ds.n = d; ds.pdf = 1.f; ds.delta = true; ds.d = -d; ds.dist = dist;
         spec = emitter_radiance<NC>(e);
     } else {
-        throw std::runtime_error("oracle: area emitters not supported yet");
+        // area.cpp:119-143 (uniform radiance) -> Shape::sample_direction (shape.cpp:358-375) ->
+        // Rectangle::sample_position (rectangle.cpp:166-180)
+        const mib_shape &sh = sc.d.shapes[e.shape];
+        if (sh.type != MIB_SHAPE_RECTANGLE)
+            throw std::runtime_error("oracle: area emitters are supported on rectangles only");
+        Vec3 p = transform_point_affine(mat4_from(sh.to_world), Vec3(sx * 2.f - 1.f, sy * 2.f - 1.f, 0.f));
+        Vec3 n(sh.frame_n[0], sh.frame_n[1], sh.frame_n[2]);
+        Vec3 d = p - ref_p;
+        float dist_squared = squared_norm(d), dist = std::sqrt(dist_squared);
+        d = d * rcp(dist);                                   // Vector / Float = multiplication by rcp (array_router.h:226-229)
+        float dp = std::fabs(dot(d, n)), x = dist_squared / dp;
+        float pdf = sh.inv_surface_area * (std::isfinite(x) ? x : 0.f);
+        bool active = dot(d, n) < 0.f && pdf != 0.f;
+        ds.p = p; ds.n = n; ds.d = d; ds.dist = dist; ds.pdf = pdf; ds.delta = false;
+        spec = active ? div_scalar(emitter_radiance<NC>(e), pdf) : Color<NC>(0.f);
     }
     ds.emitter = index;
     if (n > 1) { ds.pdf *= pmf; spec = spec * emitter_weight; }
@@ -201,12 +215,31 @@ static inline Color<NC> sample_emitter_direction(const Scene &sc, Vec3 ref_p, fl
     return spec;
 }
 
-// scene.cpp:355-366 + constant.cpp:139-144 / directional.cpp pdf_direction (= 0)
-template <int NC> static inline float pdf_emitter_direction(const Scene &sc, int emitter) {
+// scene.cpp:355-366 + constant.cpp:139-144 / directional.cpp pdf_direction (= 0) / area.cpp:145-173 with
+// DirectionSample3f(scene, si, ref) (records.h: d = (si.p - ref.p) / dist, n = si.sh_frame.n) and
+// Shape::pdf_direction (shape.cpp:377-388)
+template <int NC> static inline float pdf_emitter_direction(const Scene &sc, int emitter, Vec3 ref_p, Vec3 si_p, Vec3 si_n) {
     const mib_emitter &e = sc.d.emitters[emitter];
     float pmf = sc.d.n_emitters > 1 ? rcp((float) sc.d.n_emitters) : 1.f;
-    float pdf = e.type == MIB_EMITTER_CONSTANT ? InvFourPi : 0.f;
+    float pdf = 0.f;
+    if (e.type == MIB_EMITTER_CONSTANT) pdf = InvFourPi;
+    else if (e.type == MIB_EMITTER_AREA) {
+        Vec3 rel = si_p - ref_p;
+        float dist = norm(rel);
+        Vec3 d = rel * rcp(dist);
+        float dp = dot(d, si_n);
+        float adp = std::fabs(dp);
+        float v = sc.d.shapes[e.shape].inv_surface_area * (adp != 0.f ? (dist * dist) / adp : 0.f);
+        pdf = dp < 0.f ? v : 0.f;
+    }
     return pdf * pmf;
+}
+
+// Emitter::eval at a hit: constant / area radiance; the area light is one-sided (area.cpp:83-90)
+template <int NC> static inline Color<NC> emitter_eval(const Scene &sc, int emitter, float cos_theta_wi) {
+    const mib_emitter &e = sc.d.emitters[emitter];
+    if (e.type == MIB_EMITTER_AREA && !(cos_theta_wi > 0.f)) return Color<NC>(0.f);
+    return emitter_radiance<NC>(e);
 }
 
 // si.emitter(scene): shape emitter if valid, else the environment (interaction.h)
