@@ -84,8 +84,10 @@ template <int SPEC> struct PoolL {
     static constexpr int F_NDIST = F_NEV + NC;         // total_dist, max_dist, ds_dist
     static constexpr int F_NA = F_NDIST + 3;
     static constexpr int F_NW = F_NA + NR;
-    static constexpr int F_LSP = F_NW + 1;             // position of the last scattering event (3; used with area emitters only)
-    static constexpr int F_COUNT = F_LSP + 3;
+    static constexpr int F_COUNT = F_NW + 1;
+    // The position of the last scattering event (MIS pdf of an area light that is hit) shares F_SCP: it IS scatter_p after a
+    // real scatter, and a non-null BSDF event overwrites it with si.p when scatter_p is dead (used with area emitters only).
+    static constexpr int F_LSP = F_SCP;
     // slots per CTA: as many as fit into the 227 KB of opt-in shared memory (state words + one 16-bit entry per stage ring),
     // a compile-time constant so that every field access is one LDS / STS with an immediate offset
     static constexpr int P = ((232448 - 256 - 2 * kPoolRings * kPoolRingSlack) / (F_COUNT * 4 + 2 * kPoolRings)) / 32 * 32;
@@ -463,7 +465,6 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                     if (ev == EV_NULL) next = C_MAIN;
                     else if (ev == EV_SCATTER) {
                         pm.sv3(L::F_SCP, slot, st.scatter_p);
-                        if (sc.has_area_emitter) pm.sv3(L::F_LSP, slot, st.last_p);
 #pragma unroll
                         for (int c = 0; c < NC; ++c) pm.sf(L::F_NEV + c, slot, u[c]);
                         next = C_SCAT;
