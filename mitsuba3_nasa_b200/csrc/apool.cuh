@@ -36,7 +36,6 @@ template <int SPEC> struct APoolL {
     static constexpr int P = ((232448 - 256 - 2 * kPoolRings * kPoolRingSlack) / (F_COUNT * 4 + 2 * kPoolRings)) / 32 * 32;
 };
 constexpr uint32_t FL_BACKWARD = 0x4;                  // (the forward kernel's FL_SPEC_CHAIN bit: prb walks have no specular chain)
-constexpr unsigned kAdjGroup0 = (1u << C_MAIN) | (1u << C_MAINB) | (1u << C_NEE) | (1u << C_NEEG);
 
 template <int SPEC> __host__ __device__ constexpr size_t apool_smem_bytes() {
     return pool_state_offset(APoolL<SPEC>::P) + (size_t) APoolL<SPEC>::F_COUNT * APoolL<SPEC>::P * sizeof(uint32_t);
@@ -100,7 +99,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
     while (true) {
         int cls, slot;
         unsigned n;
-        if (!pool_claim<P, kAdjGroup0>(ps, ring, lane_id, idle_spins, cls, n, slot)) break;
+        if (!pool_claim<P, kAdjGroupMap>(ps, ring, lane_id, idle_spins, cls, n, slot)) break;
         const bool has = lane_id < n;
         __threadfence_block();
         int next = -1;

@@ -30,7 +30,7 @@
 namespace mib {
 
 #ifndef MIB_POOL_GROUPS
-#define MIB_POOL_GROUPS 1
+#define MIB_POOL_GROUPS 5
 #endif
 #ifndef MIB_POOL_RINGS
 #define MIB_POOL_RINGS 8
@@ -61,7 +61,24 @@ constexpr uint32_t kNoLane = 0xffffffffu;
 constexpr unsigned kRingEmpty = 0xffffu;
 
 enum { C_START = 0, C_MAIN = 1, C_SCAT = 2, C_NEE = 3, C_PHASE = 4, C_BSDF = 5, C_NEEG = 6, C_MAINB = 7, C_COUNT = 6 };   // C_NEEG, C_MAINB: adjoint only (apool.cuh)
-constexpr unsigned kFwdGroup0 = (1u << C_MAIN) | (1u << C_NEE);
+// Group of every class, 4 bits per class (pool_claim): all warps of a CTA serve ONE group at a time.  The finer the groups
+// the better (B200, Msamples/s, c3 / c3 polarized / c2 / c1 / c4 adjoint; profiles/r01_ab_variants.md):
+//   MIB_POOL_GROUPS = 1  {MAIN, NEE, NEEG, MAINB} | rest                         275 / 173 / 313 /  910 / 37.3
+//                     2  ... | {SCATTER, PHASE} | {START, BSDF}                  293 / 180 / 313 /  916 / 38.4
+//                     3  {MAIN, MAINB} | {NEE, NEEG} | {SCATTER, PHASE} | {START, BSDF}   323 / 193 / 346 / 1050 / 40.3
+//                     5  {MAIN, MAINB} | {NEE, NEEG} | SCATTER | PHASE | START | BSDF     347 / 210 / 393 / 1127 / 41.7  (shipped)
+//                     4  every class alone                                        345 / 206 / 387 / 1127 / 42.4
+#if MIB_POOL_GROUPS == 4   // every class its own group: the CTA serves one stage at a time
+constexpr unsigned kFwdGroupMap = 0x76543210u, kAdjGroupMap = 0x76543210u;
+#elif MIB_POOL_GROUPS == 5 // {MAIN, MAINB} | {NEE, NEEG} | {SCATTER} | {PHASE} | {START} | {BSDF}
+constexpr unsigned kFwdGroupMap = 0x01531204u, kAdjGroupMap = 0x01531204u;
+#elif MIB_POOL_GROUPS == 3   // {MAIN, MAINB} | {NEE, NEEG} | {SCATTER, PHASE} | {START, BSDF}
+constexpr unsigned kFwdGroupMap = 0x01321203u, kAdjGroupMap = 0x01321203u;
+#elif MIB_POOL_GROUPS == 2
+constexpr unsigned kFwdGroupMap = 0x00210102u, kAdjGroupMap = 0x00210102u;
+#else
+constexpr unsigned kFwdGroupMap = 0x00110101u, kAdjGroupMap = 0x00110101u;
+#endif
 
 // Field map of one slot (units: 32-bit words; word f of slot s lives at pw[f * P + s]).
 template <int SPEC> struct PoolL {
@@ -156,7 +173,7 @@ MIB_D void pool_init(PoolShared *ps, volatile uint16_t *ring, unsigned total_loc
         ps->total_local = total_local;
         ps->retired = 0;
         ps->error = 0;
-        ps->group = 1;                                    // the start class is in group 1
+        ps->group = (kFwdGroupMap >> (4 * start_class)) & 15u;   // the group of the start class
     }
     constexpr int R = pool_ring_cap<P>();
     for (int i = threadIdx.x; i < kPoolRings * R; i += blockDim.x) {
@@ -167,12 +184,12 @@ MIB_D void pool_init(PoolShared *ps, volatile uint16_t *ring, unsigned total_loc
 
 // Claim up to 32 slots of ONE class: lane 0 scans the queues and moves one head with a CAS; every lane then takes
 // its slot id out of the ring (a producer that has reserved the position but not yet written it is waited for).
-// Policy (MIB_POOL_GROUPS): the classes form two groups, GROUP0 = the loops of the walk (MAIN, NEE: a slot is
-// executed several times in a row) and the rest.  All warps of the CTA serve the current group until it has no
+// Policy (MIB_POOL_GROUPS): the classes form groups (GROUPMAP) -- the loops of the walk (MAIN, NEE: a slot is executed
+// several times in a row), the scatter stages, and START / BSDF.  All warps of the CTA serve the current group until it has no
 // full batch left and then switch together, so that the code live in the instruction cache at any time is one
-// group's, not the whole kernel's (+8 ... +29 % measured, profiles/r01_ab_variants.md).
+// group's, not the whole kernel's (two groups: +8 ... +29 %, three: another +3 ... +7 %, profiles/r01_ab_variants.md).
 // Returns false when every slot of the CTA has retired (or the watchdog fired).
-template <int P, unsigned GROUP0>
+template <int P, unsigned GROUPMAP>
 MIB_D bool pool_claim(PoolShared *ps, volatile uint16_t *ring, unsigned lane_id, unsigned &idle_spins, int &cls, unsigned &n, int &slot) {
     constexpr unsigned FULL = 0xffffffffu;
     int c_sel = -1;
@@ -187,7 +204,7 @@ MIB_D bool pool_claim(PoolShared *ps, volatile uint16_t *ring, unsigned lane_id,
         }
 #if MIB_POOL_GROUPS
         const unsigned g = *(volatile unsigned *) &ps->group;
-        const bool in = lane_id < 8u && ((((GROUP0 >> lane_id) & 1u) ? 0u : 1u) == g);
+        const bool in = lane_id < 8u && (((GROUPMAP >> (4u * lane_id)) & 15u) == g);
 #else
         const unsigned g = 0;
         const bool in = lane_id < 8u;
@@ -215,7 +232,7 @@ MIB_D bool pool_claim(PoolShared *ps, volatile uint16_t *ring, unsigned lane_id,
             int ok = 0;
             if (lane_id == 0) {
                 ok = atomicCAS(&ps->head[best], hh, hh + t) == hh;
-                if (ok && flip) ps->group = g ^ 1u;
+                if (ok && flip) ps->group = (GROUPMAP >> (4u * (unsigned) best)) & 15u;
             }
             ok = __shfl_sync(FULL, ok, 0);
             if (ok) { c_sel = best; base = hh; take = t; idle_spins = 0; break; }      // the idle watchdog counts CONSECUTIVE polls
@@ -369,7 +386,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
         // ---- 1. claim a batch of up to 32 slots of one class ----
         int cls, slot;
         unsigned n;
-        if (!pool_claim<P, kFwdGroup0>(ps, ring, lane_id, idle_spins, cls, n, slot)) break;
+        if (!pool_claim<P, kFwdGroupMap>(ps, ring, lane_id, idle_spins, cls, n, slot)) break;
         const bool has = lane_id < n;
         __threadfence_block();
 
