@@ -1,12 +1,14 @@
 // dpool.cuh -- k_forward_pool: the forward walk as a persistent, CTA-resident path pool.
 //
 // One CTA per SM keeps P paths ("slots") in shared memory (structure of arrays, one 32-bit word
-// per field and slot).  Every slot sits in exactly one of six stage queues (rings of slot ids in
-// shared memory).  A warp repeatedly
-//     1. claims up to 32 slot ids from the fullest queue        (one CAS by lane 0),
+// per field and slot).  Every slot sits in exactly one stage queue (a ring of slot ids in shared
+// memory).  A warp repeatedly
+//     1. claims up to 32 slot ids from ONE queue (warp-wide scan of the queue heads, one CAS),
 //     2. loads the fields that stage needs into registers,
 //     3. runs the stage (dstage.cuh) -- all 32 lanes execute the SAME stage,
 //     4. stores the changed fields and appends the slot id to the queue of its next stage.
+// All warps of the CTA serve the same group of stages until it runs out of full batches and then
+// move on together (pool_claim): the twelve warps share the instruction-cache lines of one stage.
 // There is no CTA-wide barrier in the steady state; P is 2-3x the thread count so that a full
 // batch of 32 is (almost) always available.  A finished path goes back to START, which adds its
 // radiance to the film / render_1 sums and starts the next lane of the CTA in the same slot.
@@ -182,8 +184,8 @@ MIB_D void pool_init(PoolShared *ps, volatile uint16_t *ring, unsigned total_loc
     }
 }
 
-// Claim up to 32 slots of ONE class: lane 0 scans the queues and moves one head with a CAS; every lane then takes
-// its slot id out of the ring (a producer that has reserved the position but not yet written it is waited for).
+// Claim up to 32 slots of ONE class: the warp scans the queues (lane c reads class c), lane 0 moves one head with a CAS,
+// and every lane then takes its slot id out of the ring (a producer that has reserved the position but not yet written it is waited for).
 // Policy (MIB_POOL_GROUPS): the classes form groups (GROUPMAP) -- the loops of the walk (MAIN, NEE: a slot is executed
 // several times in a row), the scatter stages, and START / BSDF.  All warps of the CTA serve the current group until it has no
 // full batch left and then switch together, so that the code live in the instruction cache at any time is one
