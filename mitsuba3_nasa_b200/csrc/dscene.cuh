@@ -32,6 +32,11 @@ struct DScene {
     const float *super[MIB_MAX_MEDIA];
     int super_res;                                // M (0: reference behaviour, one global majorant)
     int has_area_emitter;                         // pool kernels carry the last scattering position only when it is needed
+    // Shading frames of the planar faces (rectangle: face 0; cube: 6 faces): s(3), t(3).  They are functions of scene constants
+    // only, so commit() evaluates them once ON THE DEVICE with the arithmetic of si_finalize2 (k_shape_frames) and every
+    // intersection reads them back instead of redoing two normalisations and a cross product (identical floats).
+    float face_frame[MIB_MAX_SHAPES][6][6];
+    int frames_ready;
 };
 
 // The scene of the running launch.  One copy per translation unit (each kernel instantiation is its own object
@@ -117,25 +122,41 @@ MIB_D float intersect_shape(int idx, const Ray &ray, int &face) {
 
 // finalize_surface_interaction (interaction.h:245-255, :464-484): n, shading frame and wi as functions of
 // (shape, face, p, ray.d) only -- the pool kernel keeps just those in shared memory and rebuilds the rest.
+// shading frame from the geometric normal and dp/du (interaction.h:464-484 with the rectangle / cube / sphere partials)
+MIB_D void frame_from_normal(V3 n, V3 dp_du, V3 &fs, V3 &ft) {
+    fs = normalize(vfma(n, -dot(n, dp_du), dp_du));
+    if (dp_du.x == 0.f && dp_du.y == 0.f && dp_du.z == 0.f) { V3 s2, t2; coordinate_system(n, s2, t2); fs = s2; }
+    ft = cross(n, fs);
+}
+MIB_D void face_normal_dpdu(int shape, int face, V3 &n, V3 &dp_du) {
+    const mib_shape &s = sc.d.shapes[shape];
+    dp_du = v3(0.f);
+    if (s.type == MIB_SHAPE_RECTANGLE) {
+        n = v3(s.frame_n[0], s.frame_n[1], s.frame_n[2]);
+        dp_du = v3(s.frame_s[0], s.frame_s[1], s.frame_s[2]);
+    } else {
+        const float *nn = sc.cube_normals[shape][face];
+        n = v3(nn[0], nn[1], nn[2]);
+    }
+}
 MIB_SUB_GEOM SurfIt si_finalize2(int shape, int face, float t, V3 p, V3 ray_d) {
     SurfIt si;
     si.t = t; si.shape = shape; si.face = face; si.p = p;
     const mib_shape &s = sc.d.shapes[shape];
     V3 dp_du = v3(0.f);
-    if (s.type == MIB_SHAPE_RECTANGLE) {
-        si.n = v3(s.frame_n[0], s.frame_n[1], s.frame_n[2]);
-        dp_du = v3(s.frame_s[0], s.frame_s[1], s.frame_s[2]);
-    } else if (s.type == MIB_SHAPE_CUBE) {
-        const float *nn = sc.cube_normals[shape][face];
-        si.n = v3(nn[0], nn[1], nn[2]);
-    } else {
+    if (s.type == MIB_SHAPE_SPHERE) {
         si.n = normalize(si.p - v3(s.center[0], s.center[1], s.center[2]));
+        si.sh.n = si.n;
+        frame_from_normal(si.n, dp_du, si.sh.s, si.sh.t);
+    } else {
+        face_normal_dpdu(shape, face, si.n, dp_du);
+        si.sh.n = si.n;
+        if (sc.frames_ready) {
+            const float *ff = sc.face_frame[shape][face];
+            si.sh.s = v3(ff[0], ff[1], ff[2]);
+            si.sh.t = v3(ff[3], ff[4], ff[5]);
+        } else frame_from_normal(si.n, dp_du, si.sh.s, si.sh.t);
     }
-    V3 n = si.n;
-    si.sh.n = n;
-    si.sh.s = normalize(vfma(n, -dot(n, dp_du), dp_du));
-    if (dp_du.x == 0.f && dp_du.y == 0.f && dp_du.z == 0.f) { V3 s2, t2; coordinate_system(n, s2, t2); si.sh.s = s2; }
-    si.sh.t = cross(n, si.sh.s);
     si.wi = to_local(si.sh, -ray_d);
     return si;
 }

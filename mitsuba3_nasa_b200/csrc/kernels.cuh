@@ -411,6 +411,19 @@ static __global__ void k_supergrid(const float *data, int rx, int ry, int rz, in
     }
 }
 
+// Shading frames of the planar faces, evaluated once per commit with the device's own arithmetic (dscene.cuh face_frame)
+static __global__ void k_shape_frames(float *out) {
+    const int shape = blockIdx.x, face = threadIdx.x;
+    if (shape >= sc.d.n_shapes || face >= 6) return;
+    float *o = out + (shape * 6 + face) * 6;
+    for (int i = 0; i < 6; ++i) o[i] = 0.f;
+    if (sc.d.shapes[shape].type == MIB_SHAPE_SPHERE) return;
+    V3 n, dp_du, fs, ft;
+    face_normal_dpdu(shape, face, n, dp_du);
+    frame_from_normal(n, dp_du, fs, ft);
+    o[0] = fs.x; o[1] = fs.y; o[2] = fs.z; o[3] = ft.x; o[4] = ft.y; o[5] = ft.z;
+}
+
 // grid maximum (gridvolume m_max, grid.cpp:306-319): grid-stride max + one atomic per block
 static __global__ void k_max(const float *data, size_t n, unsigned int *out_bits) {
     float m = -inf_f();

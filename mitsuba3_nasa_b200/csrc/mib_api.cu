@@ -230,6 +230,21 @@ static void commit(mib_scene *s) {
             s->ds.rf_inv_radius = 1.f / sn.rfilter_radius;
         }
     }
+    // planar shading frames, computed by the device (identical floats to the per-hit evaluation they replace)
+    {
+        std::lock_guard<std::mutex> launch_lock(g_launch_mutex);
+        s->ds.frames_ready = 0;
+        float *dframes = nullptr;
+        const size_t nb = sizeof(s->ds.face_frame);
+        CK(cudaMalloc(&dframes, nb));
+        CK(cudaMemcpyToSymbolAsync(sc, &s->ds, sizeof(DScene), 0, cudaMemcpyHostToDevice, s->stream));
+        k_shape_frames<<<MIB_MAX_SHAPES, 8, 0, s->stream>>>(dframes);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(s->ds.face_frame, dframes, nb, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+        CK(cudaFree(dframes));
+        s->ds.frames_ready = 1;
+    }
     s->ds.weight_film = nullptr;
     ensure_film(s);
     s->committed = true;
