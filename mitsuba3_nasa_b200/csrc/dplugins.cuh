@@ -37,9 +37,19 @@ MIB_D float eval_hg(float g, float cos_theta) {                             // h
 }
 MIB_D float rayleigh_pdf(float c) { return (3.f / 16.f) * kInvPi * (1.f + sqr_(c)); }
 // mueller.h:311-328, scaled matrix
-MIB_D void rayleigh_matrix(float cos_theta, float sin_theta, float rho, float *M) {
-    float r1 = div_(1.f - rho, 1.f + div_(rho, 2.f)), r2 = div_(1.f + rho, 1.f - rho),
-          r3 = div_(1.f - 2.f * rho, 1.f - rho);
+// The depolarization factors of mueller.h:311-328 depend on the phase function's parameter only: commit() evaluates them once
+// on the device (k_shape_frames -> sc.phase_const) and the walk reads them back (identical floats, 4 IEEE divisions saved
+// per evaluation).
+MIB_D void rayleigh_factors_compute(float rho, float &r1, float &r2, float &r3) {
+    r1 = div_(1.f - rho, 1.f + div_(rho, 2.f)); r2 = div_(1.f + rho, 1.f - rho); r3 = div_(1.f - 2.f * rho, 1.f - rho);
+}
+MIB_D void rayleigh_factors(int idx, float &r1, float &r2, float &r3) {
+    if (sc.frames_ready) { r1 = sc.phase_const[idx][0]; r2 = sc.phase_const[idx][1]; r3 = sc.phase_const[idx][2]; }
+    else rayleigh_factors_compute(sc.d.phases[idx].depolarization, r1, r2, r3);
+}
+MIB_D void rayleigh_matrix(float cos_theta, float sin_theta, int idx, float *M) {
+    float r1, r2, r3;
+    rayleigh_factors(idx, r1, r2, r3);
     float a = r2 + sqr_(cos_theta), b = 1.f + sqr_(cos_theta), c = -sqr_(sin_theta), d = 2.f * cos_theta;
     float k = (3.f / 16.f) * kInvPi * r1;
 #pragma unroll
@@ -67,11 +77,13 @@ MIB_DH float phase_eval(int idx, V3 wo, float *W) {
             float ct = dot(wo, -wi);
             pdf = rayleigh_pdf(ct);
             if constexpr (POL) {
-                rayleigh_matrix(ct, safe_sqrt_(1.0f - sqr_(ct)), p.depolarization, W);
+                rayleigh_matrix(ct, safe_sqrt_(1.0f - sqr_(ct)), idx, W);
                 m4_phase_rotate(W, wo, wi);
                 return pdf;
             } else {
-                float rho = p.depolarization, r1 = div_(1.f - rho, 1.f + div_(rho, 2.f)), r2 = div_(1.f + rho, 1.f - rho);
+                float r1, r2, r3;
+                rayleigh_factors(idx, r1, r2, r3);
+                (void) r3;
                 val = (3.f / 16.f) * kInvPi * r1 * (r2 + sqr_(ct));
             }
             break;
@@ -129,12 +141,14 @@ MIB_DH float phase_sample(int idx, float s2x, float s2y, V3 &wo, float *W) {
             pdf = rayleigh_pdf(ct);
             float ipdf = rcp_(pdf);
             if constexpr (POL) {
-                rayleigh_matrix(ct, st, p.depolarization, W);
+                rayleigh_matrix(ct, st, idx, W);
                 m4_phase_rotate(W, wo, v3(0.f, 0.f, -1.f));
 #pragma unroll
                 for (int i = 0; i < 16; ++i) W[i] *= ipdf;
             } else {
-                float rho = p.depolarization, r1 = div_(1.f - rho, 1.f + div_(rho, 2.f)), r2 = div_(1.f + rho, 1.f - rho);
+                float r1, r2, r3;
+                rayleigh_factors(idx, r1, r2, r3);
+                (void) r3;
                 float val = (3.f / 16.f) * kInvPi * r1 * (r2 + sqr_(ct));
                 for (int c = 0; c < NC; ++c) W[c] = val * ipdf;
             }

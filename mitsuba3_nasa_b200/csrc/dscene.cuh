@@ -36,6 +36,7 @@ struct DScene {
     // only, so commit() evaluates them once ON THE DEVICE with the arithmetic of si_finalize2 (k_shape_frames) and every
     // intersection reads them back instead of redoing two normalisations and a cross product (identical floats).
     float face_frame[MIB_MAX_SHAPES][6][6];
+    float phase_const[MIB_MAX_PHASES][4];          // rayleigh: the three depolarization factors of mueller.h:311-328
     int frames_ready;
 };
 

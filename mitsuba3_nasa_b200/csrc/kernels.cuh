@@ -412,8 +412,14 @@ static __global__ void k_supergrid(const float *data, int rx, int ry, int rz, in
 }
 
 // Shading frames of the planar faces, evaluated once per commit with the device's own arithmetic (dscene.cuh face_frame)
-static __global__ void k_shape_frames(float *out) {
+static __global__ void k_shape_frames(float *out, float *phase_out) {
     const int shape = blockIdx.x, face = threadIdx.x;
+    if (face == 7 && shape < MIB_MAX_PHASES) {                      // one spare thread per block: phase-function constants
+        float r1 = 0.f, r2 = 0.f, r3 = 0.f;
+        if (shape < sc.d.n_phases && sc.d.phases[shape].type == MIB_PHASE_RAYLEIGH)
+            rayleigh_factors_compute(sc.d.phases[shape].depolarization, r1, r2, r3);
+        phase_out[shape * 4 + 0] = r1; phase_out[shape * 4 + 1] = r2; phase_out[shape * 4 + 2] = r3; phase_out[shape * 4 + 3] = 0.f;
+    }
     if (shape >= sc.d.n_shapes || face >= 6) return;
     float *o = out + (shape * 6 + face) * 6;
     for (int i = 0; i < 6; ++i) o[i] = 0.f;

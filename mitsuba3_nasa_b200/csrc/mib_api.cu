@@ -235,12 +235,13 @@ static void commit(mib_scene *s) {
         std::lock_guard<std::mutex> launch_lock(g_launch_mutex);
         s->ds.frames_ready = 0;
         float *dframes = nullptr;
-        const size_t nb = sizeof(s->ds.face_frame);
-        CK(cudaMalloc(&dframes, nb));
+        const size_t nb = sizeof(s->ds.face_frame), np = sizeof(s->ds.phase_const);
+        CK(cudaMalloc(&dframes, nb + np));
         CK(cudaMemcpyToSymbolAsync(sc, &s->ds, sizeof(DScene), 0, cudaMemcpyHostToDevice, s->stream));
-        k_shape_frames<<<MIB_MAX_SHAPES, 8, 0, s->stream>>>(dframes);
+        k_shape_frames<<<MIB_MAX_SHAPES, 8, 0, s->stream>>>(dframes, dframes + nb / sizeof(float));
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(s->ds.face_frame, dframes, nb, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaMemcpyAsync(s->ds.phase_const, dframes + nb / sizeof(float), np, cudaMemcpyDeviceToHost, s->stream));
         CK(cudaStreamSynchronize(s->stream));
         CK(cudaFree(dframes));
         s->ds.frames_ready = 1;
