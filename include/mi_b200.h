@@ -282,6 +282,17 @@ int  mib_debug_math(int op /*0 sincos,1 exp,2 log,3 cbrt,4 asin*/, const float *
 /* fast mode: the majorant supergrid of a heterogeneous medium, [M][M][M] (z, y, x), scale included */
 int  mib_debug_supergrid(mib_scene *scene, int medium, float *out_host, size_t count);
 
+/* Allocation-free variant of mib_debug_sample_lanes.  NO COUNTERPART IN THE REFERENCE: added
+   for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+   Same arguments, same per-lane values; the per-lane scratch is a static device array of MIB_NOALLOC_MAX_FLOATS floats
+   (4 MiB per GPU that loads the library, held until exit), so count * C must not exceed it (C = raw film channels:
+   2 mono [I,W], 4 rgb [R,G,B,W], 4 polarized [I,Q,U,V]); larger requests fail with a message in mib_last_error().
+   The call performs no cudaMalloc / cudaFree.  Every call shares the array: calls that overlap on one GPU (from several
+   processes, or issued outside this library's own per-process lock) race. */
+#define MIB_NOALLOC_MAX_FLOATS (1u << 20)
+int  mib_sample_lanes_noalloc(mib_scene *scene, uint32_t seed, uint32_t spp, uint64_t lane_begin,
+                              uint64_t count, float *out_host /* [count][C] */);
+
 #ifdef __cplusplus
 }
 #endif

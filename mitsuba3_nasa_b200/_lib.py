@@ -144,6 +144,16 @@ class DeviceScene:
                                                C.c_uint64(count), _fp(out)))
         return out
 
+    NOALLOC_MAX_FLOATS = 1 << 20
+
+    def sample_lanes_noalloc(self, seed, spp, lane_begin, count):
+        """mib_sample_lanes_noalloc: sample_lanes() with its scratch in the library's static device array (no cudaMalloc);
+        count * raw_channels <= NOALLOC_MAX_FLOATS (mi_b200.h)."""
+        out = np.empty((count, self.raw_channels), np.float32)
+        self._ck(self.l.mib_sample_lanes_noalloc(self.h, C.c_uint32(seed), C.c_uint32(spp), C.c_uint64(lane_begin),
+                                                 C.c_uint64(count), _fp(out)))
+        return out
+
     # -- adjoint --
     def render_backward(self, seed, spp, grad_in):
         g = np.ascontiguousarray(grad_in, dtype=np.float32)

@@ -624,5 +624,58 @@ int mib_debug_sample_lanes(mib_scene *s, uint32_t seed, uint32_t spp, uint64_t l
 
 } // extern "C"
 
+// ---------------------------------------------------------------------------
+// Allocation-free per-lane sampling (no counterpart in the reference).
+//
+// mib_debug_sample_lanes() above cudaMalloc()s its per-lane scratch on every call, which callers under CUDA graph
+// capture, tight serving loops or harnesses that forbid allocation cannot afford.  This variant keeps the scratch in a
+// file-scope device array of MIB_NOALLOC_MAX_FLOATS floats (4 MiB, held by every GPU that loads the library until the
+// process exits).  In host code the array's NAME is only a host-side stand-in, not a device address, so the address
+// is resolved once per device with cudaGetSymbolAddress() (that device current) and that pointer goes to the kernel.
+// All calls share the array and it keeps the last call's contents: the part a call uses is cleared first.  Calls that
+// overlap on one GPU race; g_noalloc_mutex serialises the calls of this process only.
+// ---------------------------------------------------------------------------
+static __device__ __align__(256) float g_noalloc_lanes[MIB_NOALLOC_MAX_FLOATS];
+static constexpr int kNoallocMaxDevices = 64;
+static float *g_noalloc_ptr[kNoallocMaxDevices] = {};
+static std::mutex g_noalloc_mutex;
+
+// Device address of g_noalloc_lanes on `device`, which must be the current device.
+static float *noalloc_scratch(int device) {
+    if (device < 0 || device >= kNoallocMaxDevices) throw std::runtime_error("mib_sample_lanes_noalloc: device index out of range");
+    if (!g_noalloc_ptr[device]) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_lanes);
+        if (e != cudaSuccess || !p)
+            throw std::runtime_error(std::string("mib_sample_lanes_noalloc: cudaGetSymbolAddress failed: ") + cudaGetErrorString(e));
+        g_noalloc_ptr[device] = static_cast<float *>(p);
+    }
+    return g_noalloc_ptr[device];
+}
+
+extern "C" int mib_sample_lanes_noalloc(mib_scene *s, uint32_t seed, uint32_t spp, uint64_t lane_begin, uint64_t count, float *out_host) {
+    MIB_TRY
+    if (!s || !out_host) throw std::runtime_error("mib_sample_lanes_noalloc: null argument");
+    const uint64_t C = (uint64_t) raw_channels(s->ds.d.spectrum);
+    if (count == 0) throw std::runtime_error("mib_sample_lanes_noalloc: count must be > 0");
+    if (count > MIB_NOALLOC_MAX_FLOATS / C)
+        throw std::runtime_error("mib_sample_lanes_noalloc: " + std::to_string(count) + " lanes x " + std::to_string(C) +
+                                 " channels exceed the static scratch of " + std::to_string((unsigned long long) MIB_NOALLOC_MAX_FLOATS) +
+                                 " floats (MIB_NOALLOC_MAX_FLOATS); split the lane range or use mib_debug_sample_lanes");
+    std::lock_guard<std::mutex> call_lock(g_noalloc_mutex);
+    CK(cudaSetDevice(s->device));
+    float *dev = noalloc_scratch(s->device);
+    const size_t bytes = (size_t) (count * C) * sizeof(float);
+    CK(cudaMemsetAsync(dev, 0, bytes, s->stream));               // the array keeps the previous call's lanes
+    const uint64_t sb = s->lane_begin, se = s->lane_end;
+    const uint32_t sw = s->stripe_world;
+    s->lane_begin = lane_begin; s->lane_end = lane_begin + count; s->stripe_world = 1;
+    try { run_forward(s, seed, spp, 2, dev); } catch (...) { s->lane_begin = sb; s->lane_end = se; s->stripe_world = sw; throw; }
+    s->lane_begin = sb; s->lane_end = se; s->stripe_world = sw;
+    CK(cudaMemcpyAsync(out_host, dev, bytes, cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    MIB_CATCH
+}
+
 #include "mib_api_adjoint.inc"
 #include "mib_api_debug.inc"
