@@ -293,7 +293,6 @@ MIB_D bool bbox_intersect(const float *bmin, const float *bmax, const Ray &ray, 
 template <int NC> struct MedIt {
     float t, mint;
     V3 p;
-    Frame3 sh;                    // Frame(ray.d); wi = (0,0,-1)
     float sigma_s[NC], sigma_n[NC], sigma_t[NC], maj[NC];
     int medium;
 };
@@ -371,7 +370,6 @@ MIB_SUB_GEOM MedRes<NC, TAPS> sample_interaction2(int mi, Ray ray, float sample,
         for (int k = 0; k < 8; ++k) { res.t.idx[k] = 0; res.t.w[k] = 0.f; }
     }
     const mib_medium &m = sc.d.media[mi];
-    mei.sh = make_frame(ray.d);
     bool active = true;
     float mint = 0.f, maxt = inf_f();
     if (m.type != MIB_MEDIUM_HOMOGENEOUS)

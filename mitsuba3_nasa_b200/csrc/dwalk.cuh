@@ -265,6 +265,7 @@ MIB_D void path_step(Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
             (void) not_spectral;
             T_mul_u<SPEC>(T, u);
             const int phase = md.phase;
+            const Frame3 mei_sh = make_frame(ray.d);   // the reference's mei.sh_frame = Frame(ray.d), wi = (0,0,-1) (medium.cpp:60)
             const bool sample_emitters = md.sample_emitters != 0;
             specular_chain = !sample_emitters;
             float W[NT];
@@ -274,12 +275,12 @@ MIB_D void path_step(Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
                 DirSample<NC> ds;
                 float em[NC];
                 sample_emitter<SPEC, AOS>(rng, cnt, mei.p, v3(0.f), false, nullptr, medium, channel, ds, em);
-                V3 wo = to_local(mei.sh, ds.d);
+                V3 wo = to_local(mei_sh, ds.d);
                 float ppdf = phase_eval<SPEC>(phase, wo, W);
                 if constexpr (POL) {
-                    out_rot = world_rotation1(mei.sh, v3(0.f, 0.f, -1.f));
+                    out_rot = world_rotation1(mei_sh, v3(0.f, 0.f, -1.f));
                     have_out_rot = true;
-                    m4_to_world_with(mei.sh, W, -wo, out_rot);
+                    m4_to_world_with(mei_sh, W, -wo, out_rot);
                 }
                 float x[NR];
                 TW_col0<SPEC>(T, W, x);
@@ -301,14 +302,14 @@ MIB_D void path_step(Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
             if constexpr (POL) {
                 // the rotation of the outgoing side (local (0,0,-1) in the frame of ray.d) does not depend on wo: the one
                 // computed for the emitter direction a few lines up is reused (identical floats)
-                if (!have_out_rot) out_rot = world_rotation1(mei.sh, v3(0.f, 0.f, -1.f));
-                m4_to_world_with(mei.sh, W, -wo, out_rot);
+                if (!have_out_rot) out_rot = world_rotation1(mei_sh, v3(0.f, 0.f, -1.f));
+                m4_to_world_with(mei_sh, W, -wo, out_rot);
             }
             if (!AOS) T_mul_W<SPEC>(T, W);                                   // volpath.cpp:244 (before the pdf test)
             act_scatter = act_scatter && ppdf > 0.f;
             if (act_scatter) {
                 if (AOS || I.double_phase_quirk) T_mul_W<SPEC>(T, W);        // volpathaos.cpp:211 / volpath.cpp:251
-                ray = spawn_ray(mei.p, v3(0.f), to_world(mei.sh, wo));
+                ray = spawn_ray(mei.p, v3(0.f), to_world(mei_sh, wo));
                 needs_intersection = true;
                 last_pdf = ppdf;
             }
