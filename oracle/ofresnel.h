@@ -1,0 +1,115 @@
+// ofresnel.h -- TEST INFRASTRUCTURE (CPU oracle).  Fresnel building blocks of the
+// atmosphere-ocean interface: groundwork for the `dielectric` BSDF and the
+// refractive NEE branch of volpathaos (volpathaos.cpp:232-290,312-337).  Nothing on the
+// product path calls this yet; the blocks are pinned against the reference headers first
+// (tests/test_oracle_vs_ref.py, blocks "fresnel*", "specular_*", "refract").
+//
+// Restates, for real-valued eta:
+//   fresnel                 include/mitsuba/render/fresnel.h:34-71
+//   fresnel_polarized       include/mitsuba/render/fresnel.h:149-190
+//   reflect / refract       include/mitsuba/render/fresnel.h:274-316
+//   specular_reflection     include/mitsuba/render/mueller.h:198-224
+//   specular_transmission   include/mitsuba/render/mueller.h:240-268
+// with the complex arithmetic of ext/drjit/include/drjit/complex.h (operator* :80-87,
+// rcp :101-103, sqrt :161-173, sincos_arg_diff :149-154).
+#pragma once
+#include "ospec.h"
+#include "omie.h"   // Cx and its complex.h arithmetic
+
+namespace orc {
+
+static inline Cx cmul(Cx a, Cx b) { return a * b; }
+static inline Cx cconj(Cx a) { return { a.re, -a.im }; }
+// squared_norm(Array<T,2>) is an fma chain in the JIT variants (the parity target); the reference's *scalar* instantiation
+// sums the products left to right.  Likewise rsqrt: sqrt(1/x) in the LLVM backend (omath.h), rcp(sqrt(x)) in the scalar
+// headers (array_utils.h:216-218).  g_fresnel_scalar_forms (test-only, orc_fresnel_scalar_forms) switches to the scalar forms:
+// with it the blocks equal the reference's scalar headers bit for bit, which proves that these two are the only differences.
+static int g_fresnel_scalar_forms = 0;
+static inline float csqnorm(Cx a) { return g_fresnel_scalar_forms ? a.re * a.re + a.im * a.im : cx_sqnorm(a); }
+static inline float crsqrt(float a) { return g_fresnel_scalar_forms ? 1.f / std::sqrt(a) : rsqrt(a); }
+static inline Cx cdiv(Cx a, Cx b) { float r = rcp(csqnorm(b)); return a * Cx{ b.re * r, -b.im * r }; }
+// complex.h:161-173
+static inline Cx csqrt(Cx z) {
+    float n  = std::sqrt(csqnorm(z)),
+          t1 = std::sqrt(.5f * (n + std::fabs(z.re))),
+          t2 = .5f * z.im / t1;
+    bool zero = n == 0.f, m = z.re >= 0.f;
+    return { m ? t1 : std::fabs(t2), zero ? 0.f : (m ? t2 : (z.im >= 0.f ? t1 : -t1)) };
+}
+
+struct Fresnel { float r, cos_theta_t, eta_it, eta_ti; };
+
+// fresnel.h:34-71
+static inline Fresnel fresnel(float cos_theta_i, float eta) {
+    bool outside = cos_theta_i >= 0.f;
+    float rcp_eta = rcp(eta), eta_it = outside ? eta : rcp_eta, eta_ti = outside ? rcp_eta : eta;
+    float cos_theta_t_sqr = fnmadd(fnmadd(cos_theta_i, cos_theta_i, 1.f), eta_ti * eta_ti, 1.f);
+    float ci = std::fabs(cos_theta_i), ct = safe_sqrt(cos_theta_t_sqr);
+    bool index_matched = eta == 1.f, special = index_matched || ci == 0.f;
+    float a_s = fnmadd(eta_it, ct, ci) / fmadd(eta_it, ct, ci);
+    float a_p = fnmadd(eta_it, ci, ct) / fmadd(eta_it, ci, ct);
+    float r = 0.5f * (sqr(a_s) + sqr(a_p));
+    if (special) r = index_matched ? 0.f : 1.f;
+    return { r, mulsign_neg_ad(ct, cos_theta_i), eta_it, eta_ti };
+}
+
+struct FresnelPol { Cx a_s, a_p; float cos_theta_t, eta_it, eta_ti; };
+
+// fresnel.h:149-190
+static inline FresnelPol fresnel_polarized(float cos_theta_i, float eta) {
+    bool outside = cos_theta_i >= 0.f;
+    float rcp_eta = rcp(eta), eta_it = outside ? eta : rcp_eta, eta_ti = outside ? rcp_eta : eta;
+    float cos_theta_t_sqr = fnmadd(fnmadd(cos_theta_i, cos_theta_i, 1.f), eta_ti * eta_ti, 1.f);
+    float ci = std::fabs(cos_theta_i);
+    Cx ct = csqrt(Cx{ cos_theta_t_sqr, 0.f });
+    // sign of the root under total internal reflection; llvm_ad (is_diff) forms of mulsign / copysign: select(v2 >= 0, ...)
+    ct = { mulsign_ad(ct.re, cos_theta_t_sqr), mulsign_ad(ct.im, cos_theta_t_sqr) };
+    Cx e_ct = { eta_it * ct.re, eta_it * ct.im };
+    Cx a_s = cdiv(Cx{ ci - e_ct.re, 0.f - e_ct.im }, Cx{ ci + e_ct.re, 0.f + e_ct.im });
+    Cx a_p = cdiv(Cx{ eta_it * ci - ct.re, 0.f - ct.im }, Cx{ eta_it * ci + ct.re, 0.f + ct.im });
+    if (eta == 1.f || eta == 0.f) { a_s = { 0.f, 0.f }; a_p = { 0.f, 0.f }; }
+    float ct_signed = cos_theta_t_sqr >= 0.f ? mulsign_neg_ad(ct.re, cos_theta_i) : 0.f;
+    return { a_s, a_p, ct_signed, eta_it, eta_ti };
+}
+
+// mueller.h:198-224
+static inline Mueller specular_reflection(float cos_theta_i, float eta) {
+    FresnelPol f = fresnel_polarized(cos_theta_i, eta);
+    // sincos_arg_diff(a_p, a_s), complex.h:149-154
+    float normalization = crsqrt(csqnorm(f.a_p) * csqnorm(f.a_s));
+    Cx v = cmul(f.a_p, cconj(f.a_s));
+    float sin_delta = v.im * normalization, cos_delta = v.re * normalization;
+    Cx s2 = cmul(f.a_s, f.a_s), p2 = cmul(f.a_p, f.a_p);
+    float r_s = std::sqrt(csqnorm(s2)), r_p = std::sqrt(csqnorm(p2)),
+          a = 0.5f * (r_s + r_p), b = 0.5f * (r_s - r_p), c = std::sqrt(r_s * r_p);
+    if (c == 0.f) { sin_delta = 0.f; cos_delta = 0.f; }
+    Mueller M;
+    M.m[0][0] = a; M.m[0][1] = b; M.m[1][0] = b; M.m[1][1] = a;
+    M.m[2][2] = c * cos_delta; M.m[2][3] = -c * sin_delta;
+    M.m[3][2] = c * sin_delta; M.m[3][3] = c * cos_delta;
+    return M;
+}
+
+// mueller.h:240-268
+static inline Mueller specular_transmission(float cos_theta_i, float eta) {
+    FresnelPol f = fresnel_polarized(cos_theta_i, eta);
+    float factor = -f.eta_it * (std::fabs(cos_theta_i) > 1e-8f ? f.cos_theta_t / cos_theta_i : 0.f);
+    float a_s_r = 1.f + f.a_s.re, a_p_r = (1.f + f.a_p.re) * f.eta_ti;
+    float t_s = sqr(a_s_r), t_p = sqr(a_p_r),
+          a = 0.5f * factor * (t_s + t_p), b = 0.5f * factor * (t_s - t_p), c = factor * std::sqrt(t_s * t_p);
+    Mueller M;
+    M.m[0][0] = a; M.m[0][1] = b; M.m[1][0] = b; M.m[1][1] = a; M.m[2][2] = c; M.m[3][3] = c;
+    return M;
+}
+
+// fresnel.h:274-278 (local frame)
+static inline Vec3 reflect(Vec3 wi) { return { -wi.x, -wi.y, wi.z }; }
+// fresnel.h:296-299 (local frame; cos_theta_t and eta_ti as returned by fresnel())
+static inline Vec3 refract(Vec3 wi, float cos_theta_t, float eta_ti) { return { -eta_ti * wi.x, -eta_ti * wi.y, cos_theta_t }; }
+// fresnel.h:313-316: refract wi with respect to a normal m
+static inline Vec3 refract(Vec3 wi, Vec3 m, float cos_theta_t, float eta_ti) {
+    float s = fmadd(dot(wi, m), eta_ti, cos_theta_t);
+    return { fmsub(m.x, s, wi.x * eta_ti), fmsub(m.y, s, wi.y * eta_ti), fmsub(m.z, s, wi.z * eta_ti) };
+}
+
+} // namespace orc

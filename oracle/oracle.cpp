@@ -16,6 +16,7 @@
 #include "owalk.h"
 #include "oadjoint.h"
 #include "omie.h"
+#include "ofresnel.h"
 #include <thread>
 #include <mutex>
 #include <atomic>

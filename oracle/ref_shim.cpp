@@ -13,6 +13,7 @@
 #include <mitsuba/core/transform.h>
 #include <mitsuba/core/distr_1d.h>
 #include <mitsuba/render/mueller.h>
+#include <mitsuba/render/fresnel.h>
 #include <mitsuba/render/interaction.h>
 #include <drjit/math.h>
 #include <drjit/random.h>
@@ -131,6 +132,32 @@ void ref_transform_vector(const float *m16, const float *p3, float *o3, size_t n
     for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) M(r, c) = m16[4*r + c];
     Transform<Point<float, 4>> T(M);
     for (size_t i = 0; i < n; ++i) { V3 v = T * V3(p3[3*i], p3[3*i+1], p3[3*i+2]); for (int k = 0; k < 3; ++k) o3[3*i+k] = v[k]; }
+}
+void ref_fresnel(const float *ci, float eta, float *out4, size_t n) {
+    for (size_t i = 0; i < n; ++i) {
+        auto [r, ct, eit, eti] = fresnel<float>(ci[i], eta);
+        out4[4*i] = r; out4[4*i+1] = ct; out4[4*i+2] = eit; out4[4*i+3] = eti;
+    }
+}
+void ref_fresnel_polarized(const float *ci, float eta, float *out7, size_t n) {
+    for (size_t i = 0; i < n; ++i) {
+        auto [a_s, a_p, ct, eit, eti] = fresnel_polarized<float>(ci[i], eta); float *o = out7 + 7*i;
+        o[0] = dr::real(a_s); o[1] = dr::imag(a_s); o[2] = dr::real(a_p); o[3] = dr::imag(a_p); o[4] = ct; o[5] = eit; o[6] = eti;
+    }
+}
+void ref_specular_reflection(const float *ci, float eta, float *m16, size_t n) {
+    for (size_t i = 0; i < n; ++i) store(mueller::specular_reflection<float>(ci[i], eta), m16 + 16*i);
+}
+void ref_specular_transmission(const float *ci, float eta, float *m16, size_t n) {
+    for (size_t i = 0; i < n; ++i) store(mueller::specular_transmission<float>(ci[i], eta), m16 + 16*i);
+}
+void ref_refract(const float *wi3, const float *m3, float eta, float *o3, size_t n) {
+    for (size_t i = 0; i < n; ++i) {
+        V3 wi(wi3[3*i], wi3[3*i+1], wi3[3*i+2]); Normal<float, 3> m(m3[3*i], m3[3*i+1], m3[3*i+2]);
+        auto [r, ct, eit, eti] = fresnel<float>(dr::dot(wi, m), eta);
+        V3 o = ct == 0.f ? V3(0.f) : refract(wi, m, ct, eti);
+        for (int k = 0; k < 3; ++k) o3[3*i+k] = o[k];
+    }
 }
 
 } // extern "C"

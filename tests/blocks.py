@@ -177,6 +177,40 @@ def _xform(name):
     return run
 
 
+# Ocean-interface Fresnel blocks (oracle/ofresnel.h).  eta = 1.33 (water seen from the air side) and its
+# reciprocal; cos_theta_i spans both hemispheres, grazing angles, normal incidence and total internal reflection.
+_ETAS = (1.33, 1.0 / 1.33, 1.5, 1.0)
+
+
+def _cos_theta(seed, n):
+    c = np.random.default_rng(seed).uniform(-1, 1, n).astype(np.float32)
+    c[:10] = [1.0, -1.0, 0.0, 1e-9, -1e-9, 1e-4, -1e-4, 0.5, -0.5, 0.6593]
+    return c
+
+
+def _fresnel_block(name, width, seed):
+    def run(lib, prefix, n):
+        ci = _cos_theta(seed, n)
+        out = {}
+        for k, eta in enumerate(_ETAS):
+            o = np.zeros((n, width), np.float32)
+            getattr(lib, prefix + name)(_p(ci), C.c_float(eta), _p(o), C.c_size_t(n))
+            out["o%d" % k] = o
+        return out
+    return run
+
+
+def b_refract(lib, prefix, n):
+    rng = np.random.default_rng(33)
+    wi, m = _unit(rng, n), _unit(rng, n)
+    out = {}
+    for k, eta in enumerate(_ETAS):
+        o = np.zeros((n, 3), np.float32)
+        getattr(lib, prefix + "refract")(_p(wi), _p(m), C.c_float(eta), _p(o), C.c_size_t(n))
+        out["o%d" % k] = o
+    return out
+
+
 # name -> (function, tolerance)
 BLOCKS = {
     "exp": (_unary("exp", -90, 90, 21), None),
@@ -198,6 +232,14 @@ BLOCKS = {
     "irregular": (b_irregular, None),
     "transform_point": (_xform("transform_point"), 4e-6),
     "transform_vector": (_xform("transform_vector"), 4e-6),
+    "fresnel": (_fresnel_block("fresnel", 4, 30), None),
+    # under total internal reflection the complex amplitudes go through squared_norm (fma chain vs left-to-right sum) and
+    # rsqrt (sqrt(1/x) vs 1/sqrt(x)); with the oracle switched to the scalar forms these two blocks are bit-exact
+    # (test_fresnel_blocks_bit_exact_in_scalar_forms)
+    "fresnel_polarized": (_fresnel_block("fresnel_polarized", 7, 31), 5e-7),
+    "specular_reflection": (_fresnel_block("specular_reflection", 16, 32), 1e-6),
+    "specular_transmission": (_fresnel_block("specular_transmission", 16, 34), None),
+    "refract": (b_refract, 5e-5),   # dot(wi, m): fma chain vs left-to-right sum, amplified by sqrt near the critical angle
 }
 
 

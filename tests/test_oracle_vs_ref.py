@@ -48,6 +48,57 @@ def test_oracle_matches_live_reference_headers(name):
     assert ok, msg
 
 
+@pytest.mark.parametrize("name", ["fresnel", "fresnel_polarized", "specular_reflection", "specular_transmission"])
+def test_fresnel_blocks_bit_exact_in_scalar_forms(name, golden):
+    """The oracle follows the JIT variants (fma-chain squared_norm, rsqrt = sqrt(1/x)); switched to the scalar forms of
+    the same two operations it reproduces the reference's scalar headers bit for bit (golden, and live when present)."""
+    fn, _ = blocks.BLOCKS[name]
+    n = int(golden["n"][0])
+    lib = oracle_lib()
+    lib.orc_fresnel_scalar_forms(1)
+    try:
+        got = fn(lib, "orc_", n)
+        want = {k.split("/", 1)[1]: golden[k] for k in golden.files if k.startswith(name + "/")}
+        assert want
+        ok, msg = blocks.compare(name, got, want, None)
+        assert ok, msg
+        ref = ref_lib()
+        if ref is not None:
+            ok, msg = blocks.compare(name, fn(lib, "orc_", 20000), fn(ref, "ref_", 20000), None)
+            assert ok, msg
+    finally:
+        lib.orc_fresnel_scalar_forms(0)
+
+
+def test_fresnel_physics():
+    """Energy conservation and the textbook limits (mueller.h:198-268; test_mueller.py / test_fresnel.py hold the same
+    identities): R + T = 1 in the intensity entry, normal incidence R = ((eta-1)/(eta+1))^2, Brewster angle kills r_p,
+    total internal reflection gives R = 1, T = 0 and a pure retarder (|M22|^2 + |M23|^2 = 1)."""
+    lib = oracle_lib()
+    eta = 1.33
+    ci = np.linspace(-1, 1, 2001).astype(np.float32)
+    ci = ci[np.abs(ci) > 1e-3]
+    n = len(ci)
+    R, T, F = np.empty((n, 16), np.float32), np.empty((n, 16), np.float32), np.empty((n, 4), np.float32)
+    lib.orc_specular_reflection(fp(ci), C.c_float(eta), fp(R), C.c_size_t(n))
+    lib.orc_specular_transmission(fp(ci), C.c_float(eta), fp(T), C.c_size_t(n))
+    lib.orc_fresnel(fp(ci), C.c_float(eta), fp(F), C.c_size_t(n))
+    assert np.abs(R[:, 0] + T[:, 0] - 1).max() < 2e-6
+    assert np.abs(R[:, 0] - F[:, 0]).max() < 2e-6          # unpolarized fresnel() equals the intensity entry
+    one = np.array([1.0], np.float32)
+    r1 = np.empty((1, 16), np.float32)
+    lib.orc_specular_reflection(fp(one), C.c_float(eta), fp(r1), C.c_size_t(1))
+    assert abs(r1[0, 0] - ((eta - 1) / (eta + 1)) ** 2) < 1e-7
+    brewster = np.array([np.cos(np.arctan(eta))], np.float32)
+    lib.orc_specular_reflection(fp(brewster), C.c_float(eta), fp(r1), C.c_size_t(1))
+    assert abs(r1[0, 0] - r1[0, 1]) < 1e-7                  # r_p = 0: a = b
+    tir = (ci < 0) & (1 - ci.astype(np.float64) ** 2 > (1 / eta) ** 2 + 1e-3)
+    assert tir.any()
+    assert np.abs(R[tir, 0] - 1).max() < 1e-6 and np.abs(T[tir, 0]).max() == 0
+    assert np.abs(R[tir, 10] ** 2 + R[tir, 11] ** 2 - 1).max() < 1e-5
+    assert (np.abs(R[tir, 11]) > 0).any()                    # a real phase shift between s and p
+
+
 # ---------------------------------------------------------------------------
 # Known answers from the reference's own tests
 # ---------------------------------------------------------------------------
