@@ -43,6 +43,27 @@ struct Sink {
     }
 };
 
+// One gradient contribution to a grid voxel.  Shipped: one red.global.add.f32 per lane and tap.
+// Variant MIB_GRAD_WARP_AGG (A/B only, `make EXTRA=-DMIB_GRAD_WARP_AGG B=build_wagg OUT=../libmi_b200_wagg.so`, see
+// profiles/ab.sh): lanes of the converged group that hit the same voxel are found with match.any, their values are
+// summed by shuffles and the lowest lane issues one atomic.  Not the default: on C4 the ncu capture of k_adjoint_pool shows
+// the atomics at 7 of 32 lanes and < 2 % of issued instructions, and consecutive lanes (same pixel) only share
+// voxels up to their first scatter, so the match.any round trip (8 per collision) costs more than the atomics it saves.
+MIB_D void grad_add(float *addr, float v) {
+#ifdef MIB_GRAD_WARP_AGG
+    const unsigned act = __activemask();
+    const unsigned peers = __match_any_sync(act, (unsigned long long) addr);
+    const unsigned lane = threadIdx.x & 31u;
+    if (peers != (1u << lane)) {
+        float sum = 0.f;
+        for (unsigned m = peers; m; m &= m - 1) sum += __shfl_sync(peers, v, __ffs(m) - 1);
+        if (lane != (unsigned) (__ffs(peers) - 1)) return;
+        v = sum;
+    }
+#endif
+    atomicAdd(addr, v);
+}
+
 // d(loss) += coeff[c] * d(volume value at the taps, channel c)
 template <int NC>
 MIB_D void sink_volume(Sink &sink, const mib_volume &v, int medium, bool is_albedo, const GridTaps &taps, const float *coeff) {
@@ -56,12 +77,12 @@ MIB_D void sink_volume(Sink &sink, const mib_volume &v, int medium, bool is_albe
             for (int c = 1; c < NC; ++c) s += coeff[c];
             if (s == 0.f) return;
 #ifndef MIB_NO_GRAD_ATOMICS
-            for (int k = 0; k < n; ++k) atomicAdd(g + taps.idx[k], s * taps.w[k]);
+            for (int k = 0; k < n; ++k) grad_add(g + taps.idx[k], s * taps.w[k]);
 #endif
         } else {
             for (int k = 0; k < n; ++k)
 #pragma unroll
-                for (int c = 0; c < NC; ++c) atomicAdd(g + taps.idx[k] + c, coeff[c] * taps.w[k]);
+                for (int c = 0; c < NC; ++c) grad_add(g + taps.idx[k] + c, coeff[c] * taps.w[k]);
         }
     } else {
 #pragma unroll
