@@ -6,7 +6,8 @@
     stokes = mi.render_1(scene, spp=1 << 20)      # Mueller matrix, Stokes vector in column 0
 """
 from .transforms import ScalarTransform4f, Transform4f  # noqa: F401
-from .api import (set_variant, variant, variants, load_dict, traverse, render, render_1,  # noqa: F401
+from .api import (set_variant, variant, variants, load_dict, load_string, load_file, traverse, render, render_1,  # noqa: F401
                   Scene, SceneParameters, Integrator, sample_tea_32)
 from .scene import PluginError  # noqa: F401
 from .exr import write_exr, read_exr  # noqa: F401
+from .xmlscene import xml_to_dict, XMLError  # noqa: F401

@@ -112,6 +112,28 @@ def load_dict(d, parallel=True, device=0):
     return Scene(_scene.load_dict(d, _variant), device)
 
 
+def load_string(string, parallel=True, device=0, **kwargs):
+    """mi.load_string (src/core/python/xml_v.cpp:88-109): an XML scene description; keyword arguments fill `$name` parameters."""
+    if _variant is None:
+        raise ImportError("set_variant() must be called before load_string()")
+    from . import xmlscene
+    return Scene(_scene.load_dict(xmlscene.xml_to_dict(string, None, **kwargs), _variant), device)
+
+
+def load_file(path, update_scene=False, parallel=True, device=0, **kwargs):
+    """mi.load_file (src/core/python/xml_v.cpp:64-85).  Relative `filename` properties and <include> tags are resolved against
+    the directory of the scene file, as the reference's file resolver does."""
+    if _variant is None:
+        raise ImportError("set_variant() must be called before load_file()")
+    import os
+    from . import xmlscene
+    if not os.path.exists(path):
+        raise FileNotFoundError('"%s": file does not exist!' % path)
+    with open(path, 'r') as f:
+        d = xmlscene.xml_to_dict(f.read(), os.path.dirname(os.path.abspath(path)), **kwargs)
+    return Scene(_scene.load_dict(d, _variant), device)
+
+
 class SceneParameters:
     """Dictionary-like parameter map (util.py:20-290): params[key] = value; params.update()."""
 

@@ -1,0 +1,266 @@
+"""XML scene descriptions (mi.load_string / mi.load_file) against the equivalent load_dict dictionaries.
+
+Reference behaviour followed: src/core/xml.cpp (tags :70-107, `$param` substitution and <default> :470-497,:588-607,
+transform operations multiplied from the left in document order :846-925, unnamed children `_arg_N` :419-423, error
+messages), src/core/tests/test_xml.py (the same checks: defaults, unused / undefined parameters, invalid ids, duplicate
+properties, transforms, nested references).  Host logic only -- no GPU, no oracle.  Scenes are compared on the bytes of
+the flattened C-ABI descriptor (`mib_scene_desc`) and on the data buffers, i.e. on everything the kernels get to see."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from mitsuba3_nasa_b200 import scene as S
+from mitsuba3_nasa_b200 import scenes
+from mitsuba3_nasa_b200.transforms import ScalarTransform4f as T
+from mitsuba3_nasa_b200.volumegrid import VolumeGrid
+from mitsuba3_nasa_b200.xmlscene import xml_to_dict, XMLError
+
+
+def _same(a, b):
+    assert bytes(C.string_at(C.addressof(a.desc), C.sizeof(a.desc))) == bytes(C.string_at(C.addressof(b.desc), C.sizeof(b.desc)))
+    assert sorted(a.buffers) == sorted(b.buffers)
+    for k in a.buffers:
+        assert np.array_equal(a.buffers[k], b.buffers[k])
+    assert sorted(a.params) == sorted(b.params)
+
+
+C1_XML = """
+<scene version="3.0.0">
+    <default name="res" value="32"/>
+    <default name="spp" value="16"/>
+    <integrator type="volpath" id="integrator">
+        <integer name="max_depth" value="64"/>
+        <integer name="rr_depth" value="5"/>
+    </integrator>
+    <sensor type="perspective" id="sensor">
+        <float name="fov" value="45"/>
+        <transform name="to_world">
+            <lookat origin="0, 0, 5" target="0, 0, 0" up="0, 1, 0"/>
+        </transform>
+        <film type="hdrfilm">
+            <integer name="width" value="$res"/>
+            <integer name="height" value="$res"/>
+            <string name="pixel_format" value="rgb"/>
+            <string name="component_format" value="float32"/>
+            <rfilter type="box"/>
+        </film>
+        <sampler type="independent">
+            <integer name="sample_count" value="$spp"/>
+        </sampler>
+    </sensor>
+    <medium type="homogeneous" id="medium1">
+        <float name="sigma_t" value="2.0"/>
+        <rgb name="albedo" value="0.9, 0.8, 0.7"/>
+        <boolean name="has_spectral_extinction" value="false"/>
+        <phase type="hg">
+            <float name="g" value="0.7"/>
+        </phase>
+    </medium>
+    <shape type="cube" id="object">
+        <bsdf type="null"/>
+        <ref id="medium1" name="interior"/>
+    </shape>
+    <emitter type="constant" id="emitter">
+        <float name="radiance" value="1.0"/>
+    </emitter>
+</scene>
+"""
+
+
+@pytest.mark.parametrize("variant", ["llvm_ad_rgb", "llvm_ad_mono"])
+def test_c1_xml_equals_dict(variant):
+    a = S.load_dict(xml_to_dict(C1_XML), variant)
+    b = S.load_dict(scenes.c1_homogeneous_cube(res=32, spp=16), variant)
+    _same(a, b)
+    # keyword arguments override <default>
+    a = S.load_dict(xml_to_dict(C1_XML, res=8, spp=4), variant)
+    b = S.load_dict(scenes.c1_homogeneous_cube(res=8, spp=4), variant)
+    _same(a, b)
+
+
+C2_XML = """
+<scene version="3.0.0">
+    <integrator type="volpathaos" id="integrator">
+        <integer name="max_depth" value="64"/>
+        <integer name="rr_depth" value="5"/>
+    </integrator>
+    <sensor type="distant" id="sensor">
+        <vector name="direction" x="0.5" y="0.0" z="-0.8660254"/>
+        <point name="target" value="0.0 0.0 1.0"/>
+        <film type="hdrfilm">
+            <integer name="width" value="1"/>
+            <integer name="height" value="1"/>
+            <rfilter type="box"/>
+        </film>
+        <sampler type="independent">
+            <integer name="sample_count" value="4"/>
+        </sampler>
+    </sensor>
+    <!-- the reference to a_medium comes before its declaration -->
+    <shape type="rectangle" id="top">
+        <bsdf type="null"/>
+        <transform name="to_world">
+            <scale x="$scale" y="$scale" z="1"/>
+            <translate z="1"/>
+        </transform>
+        <ref id="a_medium" name="interior"/>
+    </shape>
+    <medium type="homogeneous" id="a_medium">
+        <float name="sigma_t" value="0.5"/>
+        <float name="albedo" value="1.0"/>
+        <boolean name="has_spectral_extinction" value="false"/>
+        <phase type="rayleigh">
+            <float name="depolarization" value="0.0"/>
+        </phase>
+    </medium>
+    <shape type="rectangle" id="bottom">
+        <bsdf type="diffuse">
+            <float name="reflectance" value="0.3"/>
+        </bsdf>
+        <transform name="to_world">
+            <scale value="$scale $scale 1"/>
+        </transform>
+        <ref id="a_medium" name="exterior"/>
+    </shape>
+    <emitter type="directional" id="light">
+        <vector name="direction" value="-0.5, 0.0, -0.8660254"/>
+        <float name="irradiance" value="1.0"/>
+    </emitter>
+</scene>
+"""
+
+
+def test_c2_xml_equals_dict():
+    """Polarized Rayleigh slab (BASELINE config 2): forward reference, <vector>/<point> in both spellings, and a transform
+    whose operations are listed in application order (scale first, then translate = translate @ scale)."""
+    a = S.load_dict(xml_to_dict(C2_XML, scale=10000.0), "llvm_ad_mono_polarized")
+    b = S.load_dict(scenes.c2_rayleigh_slab(spp=4), "llvm_ad_mono_polarized")
+    _same(a, b)
+
+
+def test_transform_ops_compose_from_the_left():
+    x = """<scene version="3.0.0"><shape type="rectangle"><transform name="to_world">
+             <rotate x="0" y="1" z="0" angle="30"/><scale value="2"/><translate x="1" y="2" z="3"/>
+             <matrix value="1 0 0 0  0 1 0 0  0 0 1 5  0 0 0 1"/>
+           </transform></shape></scene>"""
+    m = xml_to_dict(x)['_arg_0']['to_world'].matrix
+    want = (T.translate([0, 0, 5]) @ T.translate([1, 2, 3]) @ T.scale(2) @ T.rotate([0, 1, 0], 30)).matrix
+    assert np.allclose(m, want, atol=1e-12)
+    # lookat without "up": the first tangent of coordinate_system(normalize(target - origin)) (xml.cpp:886-888)
+    x = """<scene version="3.0.0"><sensor type="perspective"><transform name="to_world">
+             <lookat origin="1, 2, 3" target="0, 0, 0"/></transform></sensor></scene>"""
+    m = xml_to_dict(x)['_arg_0']['to_world'].matrix
+    d = -np.array([1, 2, 3.0]) / np.linalg.norm([1, 2, 3.0])
+    assert np.allclose(m[:3, 2], d) and np.allclose(m[:3, 3], [1, 2, 3])
+    assert np.allclose(m[:3, :3].T @ m[:3, :3], np.eye(3), atol=1e-12) and np.linalg.det(m[:3, :3]) > 0
+
+
+def test_gridvolume_from_file_and_include(tmp_path):
+    """A heterogeneous medium whose density comes from a .vol file next to the scene, pulled in through <include>."""
+    grid = np.random.default_rng(3).uniform(0, 1, (6, 5, 4, 1)).astype(np.float32)
+    VolumeGrid(grid).write(str(tmp_path / "density.vol"))
+    (tmp_path / "medium.xml").write_text("""
+<scene version="3.0.0">
+    <medium type="heterogeneous" id="cloud">
+        <volume type="gridvolume" name="sigma_t">
+            <string name="filename" value="density.vol"/>
+            <transform name="to_world"><scale value="2"/><translate value="-1"/></transform>
+        </volume>
+        <float name="albedo" value="0.9"/>
+        <float name="scale" value="$density_scale"/>
+        <phase type="isotropic"/>
+    </medium>
+</scene>""")
+    (tmp_path / "scene.xml").write_text("""
+<scene version="3.0.0">
+    <default name="density_scale" value="3.5"/>
+    <integrator type="volpath" id="integrator"/>
+    <sensor type="perspective" id="sensor">
+        <transform name="to_world"><lookat origin="0, 0, 5" target="0, 0, 0" up="0, 1, 0"/></transform>
+        <film type="hdrfilm"><integer name="width" value="8"/><integer name="height" value="8"/><rfilter type="box"/></film>
+        <sampler type="independent"><integer name="sample_count" value="2"/></sampler>
+    </sensor>
+    <include filename="medium.xml"/>
+    <shape type="cube" id="shape"><bsdf type="null"/><ref id="cloud" name="interior"/></shape>
+    <emitter type="constant" id="emitter"/>
+</scene>""")
+    with open(tmp_path / "scene.xml") as f:
+        a = S.load_dict(xml_to_dict(f.read(), str(tmp_path)), "llvm_ad_mono")
+    b = S.load_dict({
+        'type': 'scene',
+        'integrator': {'type': 'volpath'},
+        'sensor': {'type': 'perspective', 'to_world': T.look_at([0, 0, 5], [0, 0, 0], [0, 1, 0]),
+                   'film': {'type': 'hdrfilm', 'width': 8, 'height': 8, 'rfilter': {'type': 'box'}},
+                   'sampler': {'type': 'independent', 'sample_count': 2}},
+        'cloud': {'type': 'heterogeneous',
+                  'sigma_t': {'type': 'gridvolume', 'grid': VolumeGrid(grid),
+                              'to_world': T.translate([-1, -1, -1]) @ T.scale(2)},
+                  'albedo': 0.9, 'scale': 3.5, 'phase': {'type': 'isotropic'}},
+        'shape': {'type': 'cube', 'bsdf': {'type': 'null'}, 'interior': {'type': 'ref', 'id': 'cloud'}},
+        'emitter': {'type': 'constant'},
+    }, "llvm_ad_mono")
+    _same(a, b)
+
+
+@pytest.mark.parametrize("xml,msg", [
+    ('<scene><integrator type="volpath"/></scene>', 'missing version attribute'),
+    ('<float version="3.0.0" name="a" value="1"/>', 'must be an object'),
+    ('<scene version="3.0.0"><integrator type="volpath"><float name="x" value="$nope"/></integrator></scene>', 'undefined parameter'),
+    ('<scene version="3.0.0"><integrator type="volpath"><float name="x" value="abc"/></integrator></scene>', 'could not parse floating point'),
+    ('<scene version="3.0.0"><integrator type="volpath"><integer name="x" value="1.5"/></integrator></scene>', 'could not parse integer'),
+    ('<scene version="3.0.0"><integrator type="volpath"><boolean name="x" value="yes"/></integrator></scene>', 'could not parse boolean'),
+    ('<scene version="3.0.0"><shape type="cube" id="_private"/></scene>', 'leading underscores are reserved'),
+    ('<scene version="3.0.0"><shape type="cube"><float name="a" value="1"/><float name="a" value="2"/></shape></scene>', 'specified multiple times'),
+    ('<scene version="3.0.0"><shape type="cube"><translate x="1"/></shape></scene>', 'can only occur in a transform node'),
+    ('<scene version="3.0.0"><shape type="cube"><transform name="t"><float name="a" value="1"/></transform></shape></scene>', 'only contain transform operations'),
+    ('<scene version="3.0.0"><shape type="cube"><rgb name="c" value="1 2"/></shape></scene>', "one or three values"),
+    ('<scene version="3.0.0"><shape type="cube"><float name="a" value="1" extra="2"/></shape></scene>', 'unexpected attribute'),
+    ('<scene version="3.0.0"><shape type="cube"', 'Error while loading XML'),
+])
+def test_xml_errors(xml, msg):
+    with pytest.raises(XMLError, match=msg):
+        xml_to_dict(xml)
+
+
+def test_unused_parameter_is_an_error():
+    with pytest.raises(XMLError, match='Unused parameter "spp2"'):
+        xml_to_dict(C1_XML, spp2=4)
+
+
+def test_unknown_plugin_and_unreferenced_property_surface_as_for_load_dict():
+    x = '<scene version="3.0.0"><integrator type="path"/></scene>'
+    with pytest.raises(S.PluginError, match='Plugin "path" not found'):
+        S.load_dict(xml_to_dict(x), "llvm_ad_rgb")
+    x = C1_XML.replace('<float name="g" value="0.7"/>', '<float name="g" value="0.7"/><float name="gg" value="1"/>')
+    with pytest.raises(S.PluginError, match="unreferenced propert"):
+        S.load_dict(xml_to_dict(x), "llvm_ad_rgb")
+
+
+def test_spectrum_and_rgb_tags():
+    x = """<scene version="3.0.0"><bsdf type="diffuse"><spectrum name="reflectance" value="0.4"/></bsdf>
+           <bsdf type="diffuse"><rgb name="reflectance" value="0.25"/></bsdf>
+           <bsdf type="diffuse"><spectrum name="reflectance" value="400:0.1, 700:0.3"/></bsdf></scene>"""
+    with pytest.raises(XMLError, match="wavelength:value"):
+        xml_to_dict(x)
+    d = xml_to_dict(x.replace('<bsdf type="diffuse"><spectrum name="reflectance" value="400:0.1, 700:0.3"/></bsdf>', ''))
+    assert d['_arg_0']['reflectance'] == {'type': 'uniform', 'value': 0.4}
+    assert d['_arg_1']['reflectance'] == {'type': 'rgb', 'value': [0.25, 0.25, 0.25]}
+
+
+@pytest.mark.gpu
+def test_load_string_and_load_file_render_like_load_dict(tmp_path):
+    """mi.load_string / mi.load_file (xml_v.cpp:64-109) hand the kernels the same descriptor as mi.load_dict, so the films
+    agree (same seed, same spp)."""
+    import mitsuba3_nasa_b200 as mi
+    mi.set_variant('llvm_ad_rgb')
+    want = np.asarray(mi.render(mi.load_dict(scenes.c1_homogeneous_cube(res=16, spp=8)), seed=2, spp=8))
+    got = np.asarray(mi.render(mi.load_string(C1_XML, res=16, spp=8), seed=2, spp=8))
+    assert np.allclose(got, want, rtol=1e-5, atol=1e-6)     # float atomics on the film: summation order only
+    path = tmp_path / "c1.xml"
+    path.write_text(C1_XML)
+    got = np.asarray(mi.render(mi.load_file(str(path), res=16, spp=8), seed=2, spp=8))
+    assert np.allclose(got, want, rtol=1e-5, atol=1e-6)
+    with pytest.raises(FileNotFoundError):
+        mi.load_file(str(tmp_path / "missing.xml"))
