@@ -3,7 +3,7 @@
 Mirrors the parser of the reference, src/core/xml.cpp:
   * tags (:70-107): plugin objects (scene, integrator, sensor, film, sampler, rfilter, shape, bsdf, medium, phase, volume,
     emitter, texture, sizedistr ...), properties float / integer / boolean / string / point / vector / rgb / spectrum /
-    transform (translate, rotate, scale, lookat, matrix), ref, default, include;
+    transform (translate, rotate, scale, lookat, matrix), ref, default, include, path;
   * `$name` parameter substitution from keyword arguments and <default> tags (:588-607, :470-497);
   * transform operations are applied in document order, each one multiplied from the LEFT (:846-925);
   * unnamed child objects get the argument names `_arg_0`, `_arg_1`, ... (:419-423).
@@ -57,7 +57,7 @@ class _Parser:
         self.params = dict(params)          # name -> string
         self.used = set()
         self.base_dir = base_dir
-        self.unnamed = 0
+        self.search = [base_dir] if base_dir else []      # file resolver paths: the scene's directory, then every <path>
 
     # -- `$name` substitution (xml.cpp:470-497): longest names first, unknown -> error --
     def subst(self, node):
@@ -71,6 +71,14 @@ class _Parser:
             if '$' in v:
                 raise XMLError('undefined parameter(s) in "%s" of <%s>' % (v, node.tag))
             node.attrib[k] = v
+
+    def resolve(self, path):
+        """FileResolver::resolve: the first search directory that holds the file, else the path as given."""
+        if not os.path.isabs(path):
+            for d in self.search:
+                if os.path.exists(os.path.join(d, path)):
+                    return os.path.join(d, path)
+        return path
 
     def check(self, node, allowed, required=None):
         for k in node.attrib:
@@ -152,8 +160,19 @@ class _Parser:
             t = _tokens(node.attrib['value']) if has_value else []
             if len(t) == 1:
                 return {'type': 'uniform', 'value': _float(t[0], 'spectrum')}
-            raise XMLError("'spectrum' tag: wavelength:value lists need the spectral upsampling of the reference, which is "
-                           "outside the mono / rgb hot path of this build")
+            if has_file:
+                raise XMLError("'spectrum' tag: spectrum files are not supported by this build")
+            # wavelength:value pairs (xml.cpp:806-826).  The reference turns them into a texture through its spectral
+            # upsampling; that is outside the mono / rgb hot path, so the list is handed on as the `irregular` spectrum
+            # plugin and load_dict refuses it like any other plugin that does not exist in this build.
+            wl, val = [], []
+            for tok in t:
+                pair = tok.split(':')
+                if len(pair) != 2:
+                    raise XMLError('invalid spectrum (expected wavelength:value pairs)')
+                wl.append(_float(pair[0], 'spectrum'))
+                val.append(_float(pair[1], 'spectrum'))
+            return {'type': 'irregular', 'wavelengths': wl, 'values': val}
         self.check(node, ('name', 'value'))
         v = node.attrib['value']
         if tag == 'float':
@@ -168,9 +187,8 @@ class _Parser:
                 raise XMLError('could not parse boolean value "%s" -- must be "true" or "false"' % v)
             return v.lower() == 'true'
         if tag == 'string':
-            if node.attrib['name'] == 'filename' and not os.path.isabs(v) and self.base_dir and \
-                    os.path.exists(os.path.join(self.base_dir, v)):
-                return os.path.join(self.base_dir, v)       # the scene's directory is on the file resolver's path
+            if node.attrib['name'] == 'filename':
+                return self.resolve(v)
             return v
         if tag == 'rgb':
             t = _tokens(v)
@@ -203,9 +221,7 @@ class _Parser:
                 continue
             if tag == 'include':
                 self.check(ch, ('filename',))
-                path = ch.attrib['filename']
-                if not os.path.isabs(path) and self.base_dir:
-                    path = os.path.join(self.base_dir, path)
+                path = self.resolve(ch.attrib['filename'])
                 if not os.path.exists(path):
                     raise XMLError('included file "%s" not found' % ch.attrib['filename'])
                 sub = ET.parse(path).getroot()
@@ -219,8 +235,18 @@ class _Parser:
                     d[self._key(sub, d, arg)] = self.obj(sub)
                     arg += 1
                 continue
-            if tag in ('alias', 'path'):
-                raise XMLError('<%s> is not supported by this build' % tag)
+            if tag == 'path':
+                # xml.cpp:609-627: add a directory to the file resolver (relative to the scene file)
+                self.check(ch, ('value',))
+                path = ch.attrib['value']
+                if not os.path.isabs(path) and self.base_dir:
+                    path = os.path.join(self.base_dir, path)
+                if not os.path.exists(path):
+                    raise XMLError('<path>: folder "%s" not found' % ch.attrib['value'])
+                self.search.append(os.path.normpath(path))
+                continue
+            if tag == 'alias':
+                raise XMLError('<alias> is not supported by this build')
             if tag == 'ref':
                 self.check(ch, ('name', 'id'), ('id',))
                 name = ch.attrib.get('name') or self._arg(d, arg)
