@@ -2,8 +2,9 @@
 src/films/hdrfilm.cpp:420-590, for the float32 case): uncompressed, one scanline per chunk, FLOAT channels.
 
 Written from the OpenEXR file-layout specification (magic, version, attribute list, line-offset table, chunks); files
-open in any EXR viewer.  The reader understands the files this writer produces (tests, round trips) -- the PIZ-compressed
-reference images of the fork's test suite need a real decoder and are out of scope.
+open in any EXR viewer.  The reader understands single-part scanline files with HALF / FLOAT / UINT channels,
+uncompressed or RLE / ZIPS / ZIP / PIZ compressed -- PIZ is what the reference writes, so `film.write()` outputs and the reference
+images of the fork's test-suite can be read back for comparisons.
 """
 import struct
 
@@ -62,12 +63,259 @@ def _cstr(buf, pos):
     return buf[pos:end].decode(), end + 1
 
 
+# ----------------------------------------------------------------------------------------------------------------
+# Block decoders.  Written from the published OpenEXR file layout and the description of its codecs (the pinned
+# third-party dependency of the reference is ext/openexr, OpenEXR 2.5: IlmImf/ImfPizCompressor.cpp, ImfHuf.cpp,
+# ImfWav.cpp, ImfZip.cpp, ImfRle.cpp); validated against that library's own test images of one picture stored with
+# every codec (tests/test_exr.py).  Every decoder returns the block in the uncompressed chunk layout: per scanline,
+# channel after channel, little-endian samples.
+# ----------------------------------------------------------------------------------------------------------------
+_LINES_PER_BLOCK = {0: 1, 1: 1, 2: 1, 3: 16, 4: 32}          # NONE, RLE, ZIPS, ZIP, PIZ
+_SAMPLE_BYTES = {0: 4, 1: 2, 2: 4}                            # UINT, HALF, FLOAT
+_SAMPLE_DTYPE = {0: "<u4", 1: "<f2", 2: "<f4"}
+
+
+def _unpredict(raw):
+    """Inverse of the byte predictor + de-interleave shared by the ZIP and RLE codecs."""
+    a = np.frombuffer(raw, dtype=np.uint8).astype(np.int64)
+    a[1:] -= 128
+    a = (np.cumsum(a) & 0xff).astype(np.uint8)
+    half = (len(a) + 1) // 2
+    out = np.empty(len(a), np.uint8)
+    out[0::2] = a[:half]
+    out[1::2] = a[half:]
+    return out.tobytes()
+
+
+def _rle_decode(data, expected):
+    out, p = bytearray(), 0
+    while p < len(data):
+        n = data[p] - 256 if data[p] > 127 else data[p]
+        p += 1
+        if n < 0:
+            out += data[p:p - n]
+            p += -n
+        else:
+            out += bytes([data[p]]) * (n + 1)
+            p += 1
+    if len(out) != expected:
+        raise ValueError("read_exr: corrupt RLE block")
+    return bytes(out)
+
+
+class _Bits:
+    """MSB-first bit reader over a bytes object."""
+    def __init__(self, data, pos=0):
+        self.d, self.p, self.buf, self.n = data, pos, 0, 0
+
+    def get(self, k):
+        while self.n < k:
+            self.buf = (self.buf << 8) | self.d[self.p]
+            self.p += 1
+            self.n += 8
+        self.n -= k
+        return (self.buf >> self.n) & ((1 << k) - 1)
+
+
+_HUF_ENCSIZE = (1 << 16) + 1       # 65536 values + the run-length symbol
+_HUF_TABLE_BITS = 12
+
+
+def _huf_uncompress(data, n_raw):
+    """Canonical Huffman code with 6-bit packed code lengths (runs of zero lengths are run-length coded), the symbol with
+    the highest index standing for "repeat the previous output value <next 8 bits> times"."""
+    if len(data) < 20:
+        if n_raw:
+            raise ValueError("read_exr: truncated PIZ block")
+        return np.zeros(0, np.uint16)
+    im, i_max, _, n_bits, _ = struct.unpack_from("<5I", data, 0)
+    if im >= _HUF_ENCSIZE or i_max >= _HUF_ENCSIZE:
+        raise ValueError("read_exr: corrupt Huffman table")
+    # code lengths
+    lengths = np.zeros(_HUF_ENCSIZE, np.int64)
+    br = _Bits(data, 20)
+    sym = im
+    while sym <= i_max:
+        l = br.get(6)
+        if l == 63:
+            sym += br.get(8) + 6
+        elif l >= 59:
+            sym += l - 59 + 2
+        else:
+            lengths[sym] = l
+            sym += 1
+    start = br.p                                     # the code data starts at the next whole byte
+    # canonical codes: within one length in symbol order; shorter codes have the numerically larger prefixes
+    count = np.bincount(lengths, minlength=59)
+    base = [0] * 59
+    c = 0
+    for l in range(58, 0, -1):
+        nc = (c + int(count[l])) >> 1
+        base[l] = c
+        c = nc
+    syms_of = {l: np.nonzero(lengths == l)[0].tolist() for l in range(1, 59) if count[l]}
+    # prefix table for the short codes
+    T = _HUF_TABLE_BITS
+    tab_sym, tab_len = [0] * (1 << T), [0] * (1 << T)
+    for l, syms in syms_of.items():
+        if l > T:
+            continue
+        for k, sy in enumerate(syms):
+            lo = (base[l] + k) << (T - l)
+            for j in range(lo, lo + (1 << (T - l))):
+                tab_sym[j], tab_len[j] = sy, l
+    long_lengths = sorted(l for l in syms_of if l > T)
+    out = [0] * n_raw
+    n_out = 0
+    d = data
+    pos, buf, nb = start, 0, 0
+    end_bits = n_bits
+    used = 0
+    size = len(d)
+    while used < end_bits and n_out <= n_raw:
+        while nb < 58 and pos < size:                # keep at least 58 bits (longest code) in the window when possible
+            buf = ((buf << 8) | d[pos]) & 0xffffffffffffffffffffffff
+            pos += 1
+            nb += 8
+        if nb >= T:
+            idx = (buf >> (nb - T)) & ((1 << T) - 1)
+        else:
+            idx = (buf << (T - nb)) & ((1 << T) - 1)
+        l = tab_len[idx]
+        if l:
+            sy = tab_sym[idx]
+        else:
+            sy = -1
+            for l in long_lengths:
+                if nb < l:
+                    break
+                code = (buf >> (nb - l)) & ((1 << l) - 1)
+                k = code - base[l]
+                if 0 <= k < len(syms_of[l]):
+                    sy = syms_of[l][k]
+                    break
+            if sy < 0:
+                raise ValueError("read_exr: corrupt Huffman data")
+        nb -= l
+        used += l
+        if sy == i_max:                              # run of the previous value
+            if nb < 8:
+                buf = ((buf << 8) | d[pos]) & 0xffffffffffffffffffffffff
+                pos += 1
+                nb += 8
+            run = (buf >> (nb - 8)) & 0xff
+            nb -= 8
+            used += 8
+            if n_out == 0 or n_out + run > n_raw:
+                raise ValueError("read_exr: corrupt Huffman data")
+            out[n_out:n_out + run] = [out[n_out - 1]] * run
+            n_out += run
+        else:
+            if n_out >= n_raw:
+                raise ValueError("read_exr: corrupt Huffman data")
+            out[n_out] = sy
+            n_out += 1
+    if n_out != n_raw:
+        raise ValueError("read_exr: Huffman data ended early")
+    return np.array(out, dtype=np.uint16)
+
+
+def _wdec14(l, h):
+    ls, hs = l.astype(np.int16).astype(np.int32), h.astype(np.int16).astype(np.int32)
+    ai = ls + (hs & 1) + (hs >> 1)
+    return ai.astype(np.uint16), (ai - hs).astype(np.uint16)          # wraps like the C shorts
+
+
+def _wdec16(l, h):
+    m, d = l.astype(np.int32), h.astype(np.int32)
+    bb = (m - (d >> 1)) & 0xffff
+    aa = (d + bb - 0x8000) & 0xffff
+    return aa.astype(np.uint16), bb.astype(np.uint16)
+
+
+def _wav2_decode(a, max_value):
+    """Inverse of the 2-D Haar-like integer wavelet, in place on a [ny, nx] uint16 array (one 16-bit plane of one channel).
+    Every level touches disjoint 2x2 cells with stride p2, so a level is four strided array operations."""
+    ny, nx = a.shape
+    dec = _wdec14 if max_value < (1 << 14) else _wdec16
+    n = min(nx, ny)
+    p = 1
+    while p <= n:
+        p <<= 1
+    p >>= 1
+    p2 = p
+    p >>= 1
+    while p >= 1:
+        cy = (ny - p2) // p2 + 1 if ny >= p2 else 0      # cells with a full 2x2 footprint
+        cx = (nx - p2) // p2 + 1 if nx >= p2 else 0
+        ys, xs = slice(0, cy * p2, p2), slice(0, cx * p2, p2)
+        ys1, xs1 = slice(p, p + cy * p2, p2), slice(p, p + cx * p2, p2)
+        if cy and cx:
+            i00, i10 = dec(a[ys, xs], a[ys1, xs])
+            i01, i11 = dec(a[ys, xs1], a[ys1, xs1])
+            a[ys, xs], a[ys, xs1] = dec(i00, i01)
+            a[ys1, xs], a[ys1, xs1] = dec(i10, i11)
+        if (nx & p) and cy:                              # odd column: 1-D step in y at x = cx * p2
+            x = cx * p2
+            a[ys, x], a[ys1, x] = dec(a[ys, x], a[ys1, x])
+        if (ny & p) and cx:                              # odd line: 1-D step in x at y = cy * p2
+            y = cy * p2
+            a[y, xs], a[y, xs1] = dec(a[y, xs], a[y, xs1])
+        p2 = p
+        p >>= 1
+
+
+def _piz_decode(data, nx, ny, sample_words):
+    """PIZ: value-range bitmap -> look-up table, Huffman-coded wavelet coefficients, one plane set per channel."""
+    min_nz, max_nz = struct.unpack_from("<HH", data, 0)
+    pos = 4
+    bitmap = np.zeros(8192, np.uint8)
+    if min_nz <= max_nz:
+        if max_nz >= 8192:
+            raise ValueError("read_exr: corrupt PIZ bitmap")
+        bitmap[min_nz:max_nz + 1] = np.frombuffer(data, np.uint8, max_nz - min_nz + 1, pos)
+        pos += max_nz - min_nz + 1
+    present = np.unpackbits(bitmap, bitorder="little").astype(bool)
+    present[0] = True                                     # zero is always part of the table
+    lut = np.zeros(65536, np.uint16)
+    values = np.nonzero(present)[0]
+    lut[:len(values)] = values
+    max_value = len(values) - 1
+    (length,) = struct.unpack_from("<i", data, pos)
+    pos += 4
+    if length < 0 or pos + length > len(data):
+        raise ValueError("read_exr: truncated PIZ block")
+    total = sum(nx * ny * w for w in sample_words)
+    words = _huf_uncompress(data[pos:pos + length], total)
+    out = np.empty((ny, sum(nx * w for w in sample_words)), np.uint16)
+    start, col = 0, 0
+    for w in sample_words:
+        plane = words[start:start + nx * ny * w].reshape(ny, nx, w).copy()
+        for j in range(w):
+            sub = np.ascontiguousarray(plane[:, :, j])
+            _wav2_decode(sub, max_value)
+            plane[:, :, j] = sub
+        out[:, col:col + nx * w] = lut[plane.reshape(ny, nx * w)]
+        start += nx * ny * w
+        col += nx * w
+    return out.astype("<u2").tobytes()
+
+
 def read_exr(path):
-    """Reads an uncompressed FLOAT scanline file (as written by write_exr).  Returns (image [H, W, C], channel names in
-    file order)."""
+    """See _read_exr; damaged files raise ValueError."""
+    try:
+        return _read_exr(path)
+    except (IndexError, struct.error, KeyError) as e:
+        raise ValueError("read_exr: corrupt or truncated file (%s: %s)" % (type(e).__name__, e))
+
+
+def _read_exr(path):
+    """Reads a single-part scanline OpenEXR file: HALF / FLOAT / UINT channels, stored uncompressed or with the RLE, ZIPS, ZIP
+    or PIZ codec (PIZ is what the reference's `Bitmap::write` produces, i.e. every `film.write()` output and every reference
+    image of the fork's test-suite).  Returns (image [H, W, C] float32, channel names in file order)."""
     buf = open(path, "rb").read()
     magic, version = struct.unpack_from("<ii", buf, 0)
-    if magic != _MAGIC or (version & 0xff) != 2 or (version & ~0xff):
+    if magic != _MAGIC or (version & 0xff) != 2 or (version & ~0xff & ~0x400):
         raise ValueError("read_exr: not a single-part scanline OpenEXR file")
     pos, attrs = 8, {}
     while buf[pos] != 0:
@@ -77,24 +325,49 @@ def read_exr(path):
         attrs[name] = (typ, buf[pos + 4:pos + 4 + size])
         pos += 4 + size
     pos += 1
-    if attrs["compression"][1] != b"\0":
-        raise ValueError("read_exr: only uncompressed files are supported")
+    comp = attrs["compression"][1][0]
+    if comp not in _LINES_PER_BLOCK:
+        raise ValueError("read_exr: compression %d is not supported (NONE, RLE, ZIPS, ZIP and PIZ are)" % comp)
     xmin, ymin, xmax, ymax = struct.unpack("<4i", attrs["dataWindow"][1])
     w, h = xmax - xmin + 1, ymax - ymin + 1
-    names, p, ch = [], 0, attrs["channels"][1]
+    names, types, p, ch = [], [], 0, attrs["channels"][1]
     while ch[p] != 0:
         n, p = _cstr(ch, p)
-        ptype, = struct.unpack_from("<i", ch, p)
-        if ptype != _FLOAT:
-            raise ValueError("read_exr: only FLOAT channels are supported")
+        ptype, _lin, xs, ys = struct.unpack_from("<iB3xii", ch, p)
+        if ptype not in _SAMPLE_BYTES or xs != 1 or ys != 1:
+            raise ValueError("read_exr: unsupported channel '%s' (pixel type %d, sampling %d x %d)" % (n, ptype, xs, ys))
         p += 16
         names.append(n)
+        types.append(ptype)
     c = len(names)
-    offsets = np.frombuffer(buf, dtype="<u8", count=h, offset=pos)
+    line_bytes = w * sum(_SAMPLE_BYTES[t] for t in types)
+    lines = _LINES_PER_BLOCK[comp]
+    n_blocks = (h + lines - 1) // lines
+    offsets = np.frombuffer(buf, dtype="<u8", count=n_blocks, offset=pos)
     img = np.empty((h, w, c), dtype=np.float32)
-    for k in range(h):
+    for k in range(n_blocks):
         o = int(offsets[k])
         y, size = struct.unpack_from("<ii", buf, o)
-        row = np.frombuffer(buf, dtype="<f4", count=w * c, offset=o + 8).reshape(c, w)
-        img[y - ymin] = row.T
+        ny = min(lines, ymax - y + 1)
+        raw_size = ny * line_bytes
+        data = buf[o + 8:o + 8 + size]
+        if len(data) != size:
+            raise ValueError("read_exr: truncated file")
+        if size == raw_size and comp != 0:
+            pass                                           # the writer keeps a block raw when the codec does not shrink it
+        elif comp in (2, 3):
+            import zlib
+            data = _unpredict(zlib.decompress(data))
+        elif comp == 1:
+            data = _unpredict(_rle_decode(data, raw_size))
+        elif comp == 4:
+            data = _piz_decode(data, w, ny, [_SAMPLE_BYTES[t] // 2 for t in types])
+        if len(data) != raw_size:
+            raise ValueError("read_exr: block of scanline %d has %d bytes, expected %d" % (y, len(data), raw_size))
+        off = 0
+        block = np.frombuffer(data, np.uint8).reshape(ny, line_bytes)
+        for i, t in enumerate(types):
+            nb = w * _SAMPLE_BYTES[t]
+            img[y - ymin:y - ymin + ny, :, i] = np.ascontiguousarray(block[:, off:off + nb]).view(_SAMPLE_DTYPE[t]).astype(np.float32)
+            off += nb
     return img, names

@@ -1,4 +1,5 @@
-"""EXR writer / reader round trips (uncompressed float32 scanline files; the role of HDRFilm::write for developed films)."""
+"""EXR writer / reader: round trips of the uncompressed writer (the role of HDRFilm::write for developed films) and the reader's
+codecs (RLE, ZIPS, ZIP, PIZ) against the OpenEXR test images that ship with the reference."""
 import struct
 
 import numpy as np
@@ -40,3 +41,103 @@ def test_errors(tmp_path):
         write_exr(str(tmp_path / "c.exr"), np.zeros((2, 2, 2), np.float32), channel_names=["A", "A"])
     with pytest.raises(ValueError):
         write_exr(str(tmp_path / "d.exr"), np.zeros(4, np.float32))
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Compressed files: the reference writes PIZ, so its film.write() outputs and the reference images
+# of its test-suite need the codecs.  Ground truth: the pinned OpenEXR dependency of the reference (ext/openexr) ships
+# ONE picture stored with every codec (IlmImfTest/comp_*.exr) -- the decoded compressed files must equal the
+# uncompressed one bit for bit.  Those files live in the reference checkout (build container only).
+# ---------------------------------------------------------------------------------------------------------------
+import os
+import zlib
+
+IMF_TEST = "/root/reference/ext/openexr/OpenEXR/IlmImfTest"
+REF_IMAGES = "/root/reference/resources/data/tests/scenes/participating_media/refs"
+needs_reference = pytest.mark.skipif(not os.path.isdir(IMF_TEST), reason="reference checkout absent (build container only)")
+
+
+@needs_reference
+@pytest.mark.parametrize("codec", ["rle", "zips", "zip", "piz"])
+def test_codecs_against_the_openexr_test_images(codec):
+    want, names = read_exr(os.path.join(IMF_TEST, "comp_none.exr"))
+    got, names2 = read_exr(os.path.join(IMF_TEST, "comp_%s.exr" % codec))
+    assert names == names2 == ["A", "B", "G", "R"] and want.shape == (675, 587, 4)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))          # HALF data: bit-exact after widening
+
+
+@needs_reference
+@pytest.mark.parametrize("name", ["comp_bad_bounds_piz.exr", "comp_early_eof_piz.exr", "comp_short_decode_piz.exr",
+                                  "comp_bad_pos_bounds_piz.exr", "comp_invalid_unknown.exr"])
+def test_damaged_files_raise(name):
+    """OpenEXR's own fuzz cases: no crash, no hang, a ValueError."""
+    with pytest.raises(ValueError):
+        read_exr(os.path.join(IMF_TEST, name))
+
+
+@needs_reference
+def test_reads_the_reference_images_of_the_participating_media_tests():
+    """FLOAT channels, PIZ (with the writer's raw fallback for blocks that do not shrink).  The rgb and mono references of
+    one scene are renders of the same radiance field (the mono file holds a colour-converted luminance, so the scale differs
+    by some 10 %): the pictures are strongly correlated pixel by pixel, which a wrong word order or plane layout would destroy."""
+    import glob
+    files = sorted(glob.glob(os.path.join(REF_IMAGES, "*_ref_rgb.exr")))
+    assert len(files) >= 10
+    for f in files:
+        rgb, names = read_exr(f)
+        mono, _ = read_exr(f.replace("_ref_rgb", "_ref_mono"))
+        assert names == ["B", "G", "R"] and rgb.shape == mono.shape == (48, 48, 3)
+        assert np.isfinite(rgb).all() and (rgb >= 0).all() and rgb.mean() > 0
+        lum = 0.212671 * rgb[..., 2] + 0.715160 * rgb[..., 1] + 0.072169 * rgb[..., 0]
+        assert np.corrcoef(lum.ravel(), mono[..., 1].ravel())[0, 1] > 0.9, f
+        assert 0.7 < mono[..., 1].mean() / lum.mean() < 1.1, f
+    # a FLOAT file that PIZ really shrinks (16 KiB for 128 KiB of pixels): values come back in the picture's range
+    img, names = read_exr("/root/reference/tutorials/scenes/references/starmoon.exr")
+    assert names == ["Y"] and img.shape == (128, 256, 1) and 0.2 < img.min() <= img.max() < 0.35
+
+
+def _write_zip_exr(path, img, lines):
+    """Test helper: ZIPS (lines = 1) / ZIP (lines = 16) writer -- predictor, byte de-interleave, deflate."""
+    h, w, c = img.shape
+    names = ["B", "G", "R"][:c]
+    chlist = b"".join(n.encode() + b"\0" + struct.pack("<iB3xii", 2, 0, 1, 1) for n in names) + b"\0"
+    box = struct.pack("<4i", 0, 0, w - 1, h - 1)
+
+    def attr(n, t, d):
+        return n.encode() + b"\0" + t.encode() + b"\0" + struct.pack("<i", len(d)) + d
+    header = (struct.pack("<ii", 20000630, 2) + attr("channels", "chlist", chlist) +
+              attr("compression", "compression", bytes([2 if lines == 1 else 3])) + attr("dataWindow", "box2i", box) +
+              attr("displayWindow", "box2i", box) + attr("lineOrder", "lineOrder", b"\0") +
+              attr("pixelAspectRatio", "float", struct.pack("<f", 1.0)) + attr("screenWindowCenter", "v2f", struct.pack("<2f", 0, 0)) +
+              attr("screenWindowWidth", "float", struct.pack("<f", 1.0)) + b"\0")
+    chunks = []
+    for y0 in range(0, h, lines):
+        raw = np.ascontiguousarray(img[y0:y0 + lines].transpose(0, 2, 1)).astype("<f4").tobytes()
+        a = np.frombuffer(raw, np.uint8)
+        t = np.concatenate([a[0::2], a[1::2]]).astype(np.int64)
+        t[1:] = (t[1:] - t[:-1] + 128 + 256) & 0xff
+        z = zlib.compress(t.astype(np.uint8).tobytes())
+        data = z if len(z) < len(raw) else raw
+        chunks.append(struct.pack("<ii", y0, len(data)) + data)
+    pos = len(header) + 8 * len(chunks)
+    with open(path, "wb") as f:
+        f.write(header)
+        for ch in chunks:
+            f.write(struct.pack("<Q", pos))
+            pos += len(ch)
+        for ch in chunks:
+            f.write(ch)
+
+
+@pytest.mark.parametrize("lines", [1, 16])
+def test_zip_round_trip_without_the_reference(tmp_path, lines):
+    """Travels to machines without the reference checkout: smooth data (deflate shrinks it) and noise (raw fallback)."""
+    rng = np.random.default_rng(5)
+    y, x = np.mgrid[0:37, 0:29]
+    smooth = np.stack([np.sin(x / 9.0) + y / 40.0, np.floor(x / 8.0), np.zeros_like(x, dtype=float)], axis=-1).astype(np.float32)
+    noise = rng.uniform(0, 1, (37, 29, 3)).astype(np.float32)
+    for k, img in enumerate((smooth, noise)):
+        p = str(tmp_path / ("z%d.exr" % k))
+        _write_zip_exr(p, img, lines)
+        got, names = read_exr(p)
+        assert names == ["B", "G", "R"] and np.array_equal(got, img)
