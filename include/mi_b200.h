@@ -279,6 +279,13 @@ int  mib_scene_stream(mib_scene *scene, void **stream);
 int  mib_debug_sample_lanes(mib_scene *scene, uint32_t seed, uint32_t spp, uint64_t lane_begin,
                             uint64_t count, float *out_host /* [count][C] */);
 int  mib_debug_math(int op /*0 sincos,1 exp,2 log,3 cbrt,4 asin*/, const float *in_host, float *out_host, size_t n);
+/* Fresnel blocks of the ocean interface on the device (csrc/dfresnel.cuh; groundwork for the `dielectric` BSDF):
+   fresnel / fresnel_polarized (include/mitsuba/render/fresnel.h:34-71,149-190), mueller::specular_reflection /
+   specular_transmission (include/mitsuba/render/mueller.h:198-268), refract (fresnel.h:313-316).
+   op 0: in = cos_theta_i [n] -> (F, cos_theta_t, eta_it, eta_ti) [n][4];  1: -> (re a_s, im a_s, re a_p, im a_p, cos_theta_t,
+   eta_it, eta_ti) [n][7];  2 / 3: -> row-major 4x4 Mueller matrix [n][16];  4: in = (wi, m) [n][6] -> refracted direction [n][3]
+   (zero under total internal reflection). */
+int  mib_debug_fresnel(int op, const float *in_host, float eta, float *out_host, size_t n);
 /* fast mode: the majorant supergrid of a heterogeneous medium, [M][M][M] (z, y, x), scale included */
 int  mib_debug_supergrid(mib_scene *scene, int medium, float *out_host, size_t count);
 

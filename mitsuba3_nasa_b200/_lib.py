@@ -219,3 +219,16 @@ def debug_math(op, x):
     if rc != 0:
         raise RuntimeError(l.mib_last_error().decode())
     return out
+
+
+def debug_fresnel(op, x, eta):
+    """Run a Fresnel block of csrc/dfresnel.cuh on an array (op: 0 fresnel, 1 fresnel_polarized, 2 specular_reflection,
+    3 specular_transmission, 4 refract with x = [n, 6] rows of (wi, m))."""
+    l = lib()
+    x = np.ascontiguousarray(x, np.float32)
+    n = x.size // (6 if op == 4 else 1)
+    out = np.empty((n, {0: 4, 1: 7, 2: 16, 3: 16, 4: 3}[op]), np.float32)
+    rc = l.mib_debug_fresnel(C.c_int(op), _fp(x), C.c_float(eta), _fp(out), C.c_size_t(n))
+    if rc != 0:
+        raise RuntimeError(l.mib_last_error().decode())
+    return out

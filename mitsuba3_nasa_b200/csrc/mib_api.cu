@@ -5,6 +5,7 @@
 // with an error message otherwise.
 #include "kernels.cuh"
 #include "astage.cuh"
+#include "dfresnel.cuh"
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
