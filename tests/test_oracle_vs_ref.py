@@ -99,6 +99,69 @@ def test_fresnel_physics():
     assert (np.abs(R[tir, 11]) > 0).any()                    # a real phase shift between s and p
 
 
+def _fres(ci, eta):
+    a, o = np.array([ci], np.float32), np.empty((1, 4), np.float32)
+    oracle_lib().orc_fresnel(fp(a), C.c_float(eta), fp(o), C.c_size_t(1))
+    return o[0].astype(np.float64)
+
+
+def _fres_pol(ci, eta):
+    a, o = np.array([ci], np.float32), np.empty((1, 7), np.float32)
+    oracle_lib().orc_fresnel_polarized(fp(a), C.c_float(eta), fp(o), C.c_size_t(1))
+    o = o[0].astype(np.float64)
+    return complex(o[0], o[1]), complex(o[2], o[3]), o[4]
+
+
+def test_fresnel_known_answers():
+    """src/render/tests/test_fresnel.py:6-37 (test01_fresnel): normal / grazing incidence and the two hyperphysics spot checks."""
+    close = lambda a, b: np.allclose(a, b, rtol=1e-5, atol=1e-6)
+    assert close(_fres(1, 1.5), (0.04, -1, 1.5, 1 / 1.5)) and close(_fres(-1, 1.5), (0.04, 1, 1 / 1.5, 1.5))
+    assert close(_fres(1, 1 / 1.5), (0.04, -1, 1 / 1.5, 1.5)) and close(_fres(-1, 1 / 1.5), (0.04, 1, 1.5, 1 / 1.5))
+    assert close(_fres(0, 1.5), (1, -np.sqrt(1 - 1 / 1.5 ** 2), 1.5, 1 / 1.5)) and close(_fres(0, 1 / 1.5), (1, 0, 1 / 1.5, 1.5))
+    c45 = np.cos(np.radians(45))
+    F, ct, _, scale = _fres(c45, 1.5)
+    assert close((scale * np.sqrt(1 - c45 ** 2)) ** 2 + ct ** 2, 1) and close(ct, -np.cos(np.radians(28.1255057020557)))
+    assert close(F, 0.5 * (0.09201336304552442 ** 2 + 0.3033370452904235 ** 2))
+    F, ct, _, _ = _fres(c45, 1 / 1.5)
+    assert close(F, 1) and close(ct, 0)
+    c10 = np.cos(np.radians(10))
+    F, ct, _, scale = _fres(c10, 1 / 1.5)
+    assert close(ct, -np.cos(np.radians(15.098086605159006))) and close(F, 0.5 * (0.19046797197779405 ** 2 + 0.20949431963852014 ** 2))
+    # test02_fresnel_polarized_vec :49-53: eta = 1 reflects nothing and leaves the direction alone
+    for ci in np.linspace(-1, 1, 20):
+        F, ct, _, _ = _fres(ci, 1.0)
+        assert F == 0 and abs(ct + ci) < 5e-7
+
+
+def test_fresnel_polarized_known_answers():
+    """src/render/tests/test_fresnel.py:39-46 (Brewster), :78-140 (Hecht Fig. 4.49 / 4.50: signs and relative phases of the
+    amplitudes for external and internal reflection), :142-170 (Azzam 2004: phases under total internal reflection)."""
+    a_s, a_p, _ = _fres_pol(np.cos(np.radians(56.3099)), 1.5)
+    assert np.isclose((a_s * a_s).real, 0.3846150939598947 ** 2, rtol=1e-5) and np.isclose((a_p * a_p).real, 0, atol=1e-6)
+    dphi = lambda p, s: abs(np.angle(p) - np.angle(s))
+    for eta, sign in ((1.5, -1), (1 / 1.5, +1)):
+        brewster = np.arctan(eta)
+        a_s, a_p, _ = _fres_pol(1, eta)                                  # normal incidence: opposite signs
+        assert sign * a_s.real > 0 and sign * a_p.real < 0 and a_s.imag == 0 and a_p.imag == 0 and np.isclose(dphi(a_p, a_s), np.pi, atol=1e-5)
+        a_s, a_p, _ = _fres_pol(np.cos(brewster - 0.01), eta)
+        assert sign * a_s.real > 0 and sign * a_p.real < 0 and np.isclose(dphi(a_p, a_s), np.pi, atol=1e-5)
+        a_s, a_p, _ = _fres_pol(np.cos(brewster), eta)                   # Brewster: no p-polarized reflection
+        assert abs(a_p.real) < 1e-5 and sign * a_s.real > 0 and a_s.imag == 0 and a_p.imag == 0
+        a_s, a_p, _ = _fres_pol(np.cos(brewster + 0.01), eta)            # beyond: same sign, no relative phase
+        assert sign * a_s.real > 0 and sign * a_p.real > 0 and np.isclose(dphi(a_p, a_s), 0, atol=1e-5)
+    a_s, a_p, _ = _fres_pol(0, 1 / 1.5)                                  # grazing: both amplitudes -> -1
+    assert np.isclose(a_s.real, -1, atol=1e-3) and np.isclose(a_p.real, -1, atol=1e-3) and a_s.imag == 0 and a_p.imag == 0
+    eta = 1 / 1.5
+    a_s, a_p, _ = _fres_pol(np.cos(np.arcsin(eta)), eta)                 # critical angle: both -> +1, phases 0
+    assert np.isclose(a_s.real, 1, atol=1e-3) and np.isclose(a_p.real, 1, atol=1e-3)
+    assert np.isclose(np.angle(a_s), 0, atol=2e-3) and np.isclose(np.angle(a_p), 0, atol=2e-3)
+    a_s, a_p, _ = _fres_pol(0, eta)
+    assert np.isclose(abs(np.angle(a_s)), np.pi, atol=1e-5) and np.isclose(abs(np.angle(a_p)), np.pi, atol=1e-5)
+    cos_max = np.sqrt((1 - eta ** 2) / (1 + eta ** 2))                   # Azzam Eq. (11): the largest phase difference
+    a_s, a_p, ct = _fres_pol(cos_max, eta)
+    assert ct == 0 and np.isclose(np.angle(a_p) - np.angle(a_s), 2 * np.arctan((1 - eta ** 2) / (2 * eta)), rtol=1e-5)
+
+
 # ---------------------------------------------------------------------------
 # Known answers from the reference's own tests
 # ---------------------------------------------------------------------------
