@@ -112,4 +112,57 @@ static inline Vec3 refract(Vec3 wi, Vec3 m, float cos_theta_t, float eta_ti) {
     return { fmsub(m.x, s, wi.x * eta_ti), fmsub(m.y, s, wi.y * eta_ti), fmsub(m.z, s, wi.z * eta_ti) };
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// SmoothDielectric::sample, src/bsdfs/dielectric.cpp:247-371, TransportMode::Radiance, specular_reflectance /
+// specular_transmittance as plain factors.  has_reflection / has_transmission mirror ctx.is_enabled (volpathaos' refractive
+// NEE asks for transmission only, volpathaos.cpp:320-326).  eval() and pdf() of this BSDF are zero (delta lobes,
+// dielectric.cpp:374-421 returns 0 for the smooth case).
+// ---------------------------------------------------------------------------------------------------------------
+enum : uint32_t { BSDF_DeltaReflection = 0x20, BSDF_DeltaTransmission = 0x40 };
+
+struct DielectricSample {
+    Vec3 wo; float pdf = 0.f, eta = 1.f; uint32_t sampled_type = 0;
+    float weight = 0.f;      // unpolarized variants
+    Mueller weight_pol;      // polarized variants (rotated to the implicit Stokes bases of -wo_hat and wi_hat)
+};
+
+static inline DielectricSample dielectric_sample(Vec3 wi, float eta, float sample1, bool has_reflection, bool has_transmission,
+                                                 float reflectance = 1.f, float transmittance = 1.f) {
+    DielectricSample bs;
+    Fresnel f = fresnel(wi.z, eta);
+    float r_i = f.r, t_i = 1.f - r_i;
+    bool selected_r;
+    if (has_reflection && has_transmission) { selected_r = sample1 <= r_i; bs.pdf = selected_r ? r_i : t_i; }
+    else if (has_reflection || has_transmission) { selected_r = has_reflection; bs.pdf = 1.f; }
+    else return bs;
+    bs.sampled_type = selected_r ? BSDF_DeltaReflection : BSDF_DeltaTransmission;
+    bs.wo = selected_r ? reflect(wi) : refract(wi, f.cos_theta_t, f.eta_ti);
+    bs.eta = selected_r ? 1.f : f.eta_it;
+
+    // polarized weight (:296-339): light arrives along -wo_hat and leaves along +wi_hat
+    Vec3 wo_hat = bs.wo, wi_hat = wi;
+    Mueller R = specular_reflection(wo_hat.z, eta), T = specular_transmission(wo_hat.z, eta);
+    Mueller W = selected_r ? R : T;
+    if (has_reflection && has_transmission)
+        for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) W.m[i][j] = W.m[i][j] / bs.pdf;
+    Vec3 n(0.f, 0.f, 1.f);
+    Vec3 s_axis_in = cross(n, -wo_hat), s_axis_out = cross(n, wi_hat);
+    bool collinear = s_axis_in.x == 0.f && s_axis_in.y == 0.f && s_axis_in.z == 0.f;
+    s_axis_in  = collinear ? Vec3(1.f, 0.f, 0.f) : normalize(s_axis_in);
+    s_axis_out = collinear ? Vec3(1.f, 0.f, 0.f) : normalize(s_axis_out);
+    W = rotate_mueller_basis(W, -wo_hat, s_axis_in, stokes_basis(-wo_hat), wi_hat, s_axis_out, stokes_basis(wi_hat));
+    W = W * (selected_r ? reflectance : transmittance);
+
+    // unpolarized weight (:341-362)
+    float w = (has_reflection && has_transmission) ? 1.f : (has_reflection ? r_i : t_i);
+    w *= selected_r ? reflectance : transmittance;
+
+    if (!selected_r) {          // solid-angle compression across the interface (:364-369)
+        float fac = sqr(f.eta_ti);
+        w *= fac; W = W * fac;
+    }
+    bs.weight = w; bs.weight_pol = W;
+    return bs;
+}
+
 } // namespace orc
