@@ -17,6 +17,7 @@
 #include "oadjoint.h"
 #include "omie.h"
 #include "ofresnel.h"
+#include "omicrofacet.h"
 #include <thread>
 #include <mutex>
 #include <atomic>

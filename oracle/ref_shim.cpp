@@ -14,6 +14,7 @@
 #include <mitsuba/core/distr_1d.h>
 #include <mitsuba/render/mueller.h>
 #include <mitsuba/render/fresnel.h>
+#include <mitsuba/render/microfacet.h>
 #include <mitsuba/render/interaction.h>
 #include <drjit/math.h>
 #include <drjit/random.h>
@@ -157,6 +158,24 @@ void ref_refract(const float *wi3, const float *m3, float eta, float *o3, size_t
         auto [r, ct, eit, eti] = fresnel<float>(dr::dot(wi, m), eta);
         V3 o = ct == 0.f ? V3(0.f) : refract(wi, m, ct, eti);
         for (int k = 0; k < 3; ++k) o3[3*i+k] = o[k];
+    }
+}
+void ref_erf(const float *x, float *y, size_t n) { for (size_t i = 0; i < n; ++i) y[i] = dr::erf(x[i]); }
+void ref_erfinv(const float *x, float *y, size_t n) { for (size_t i = 0; i < n; ++i) y[i] = dr::erfinv(x[i]); }
+void ref_exp2(const float *x, float *y, size_t n) { for (size_t i = 0; i < n; ++i) y[i] = dr::exp2(x[i]); }
+using MD = MicrofacetDistribution<float, Color<float, 1>>;
+void ref_microfacet_eval(int type, float alpha_u, float alpha_v, const float *wi3, const float *m3, float *out3, size_t n) {
+    MD d(type == 0 ? MicrofacetType::Beckmann : MicrofacetType::GGX, alpha_u, alpha_v, true);
+    for (size_t i = 0; i < n; ++i) {
+        V3 wi(wi3[3*i], wi3[3*i+1], wi3[3*i+2]), m(m3[3*i], m3[3*i+1], m3[3*i+2]);
+        out3[3*i] = d.eval(m); out3[3*i+1] = d.smith_g1(wi, m); out3[3*i+2] = d.pdf(wi, m);
+    }
+}
+void ref_microfacet_sample(int type, float alpha_u, float alpha_v, const float *wi3, const float *s2, float *out4, size_t n) {
+    MD d(type == 0 ? MicrofacetType::Beckmann : MicrofacetType::GGX, alpha_u, alpha_v, true);
+    for (size_t i = 0; i < n; ++i) {
+        auto [m, pdf] = d.sample(V3(wi3[3*i], wi3[3*i+1], wi3[3*i+2]), P2(s2[2*i], s2[2*i+1]));
+        out4[4*i] = m[0]; out4[4*i+1] = m[1]; out4[4*i+2] = m[2]; out4[4*i+3] = pdf;
     }
 }
 

@@ -211,6 +211,43 @@ def b_refract(lib, prefix, n):
     return out
 
 
+# Microfacet distribution of the rough ocean interface (oracle/omicrofacet.h): Beckmann (what the fork's tests use) and GGX,
+# isotropic alpha = 0.1 / 0.5 and one anisotropic pair; directions on the upper hemisphere of wi, normals around +z.
+_MICROFACETS = ((0, 0.1, 0.1), (0, 0.5, 0.5), (1, 0.1, 0.1), (1, 0.3, 0.6), (0, 0.2, 0.4))
+
+
+def _upper(rng, n):
+    v = _unit(rng, n)
+    v[:, 2] = np.abs(v[:, 2]) + np.float32(1e-3)
+    return np.ascontiguousarray((v / np.linalg.norm(v, axis=1, keepdims=True)).astype(np.float32))
+
+
+def b_microfacet_eval(lib, prefix, n):
+    rng = np.random.default_rng(40)
+    wi = _upper(rng, n)
+    m = _unit(rng, n) * np.float32(0.3) + np.array([0, 0, 1], np.float32)
+    m = np.ascontiguousarray((m / np.linalg.norm(m, axis=1, keepdims=True)).astype(np.float32))
+    out = {}
+    for k, (t, au, av) in enumerate(_MICROFACETS):
+        o = np.zeros((n, 3), np.float32)
+        getattr(lib, prefix + "microfacet_eval")(C.c_int(t), C.c_float(au), C.c_float(av), _p(wi), _p(m), _p(o), C.c_size_t(n))
+        out["o%d" % k] = o
+    return out
+
+
+def b_microfacet_sample(lib, prefix, n):
+    rng = np.random.default_rng(41)
+    wi = _upper(rng, n)
+    s = rng.uniform(0, 1, (n, 2)).astype(np.float32)
+    out = {}
+    for k, (t, au, av) in enumerate(_MICROFACETS):
+        o = np.zeros((n, 4), np.float32)
+        getattr(lib, prefix + "microfacet_sample")(C.c_int(t), C.c_float(au), C.c_float(av), _p(wi), _p(s), _p(o), C.c_size_t(n))
+        out["m%d" % k] = np.ascontiguousarray(o[:, :3])
+        out["p%d" % k] = np.ascontiguousarray(o[:, 3] / (1 + np.abs(o[:, 3])))     # densities reach 1e2: compare them on a relative scale
+    return out
+
+
 # name -> (function, tolerance)
 BLOCKS = {
     "exp": (_unary("exp", -90, 90, 21), None),
@@ -239,6 +276,15 @@ BLOCKS = {
     "fresnel_polarized": (_fresnel_block("fresnel_polarized", 7, 31), 5e-7),
     "specular_reflection": (_fresnel_block("specular_reflection", 16, 32), 1e-6),
     "specular_transmission": (_fresnel_block("specular_transmission", 16, 34), None),
+    "erf": (_unary("erf", -6, 6, 42), None),
+    "erfinv": (_unary("erfinv", -0.999999, 0.999999, 43), None),
+    "exp2": (_unary("exp2", -130, 130, 44), None),
+    # dot(wi, m) and rsqrt in their JIT forms (oracle) vs scalar forms (reference headers); bit-exact once the oracle is
+    # switched to the scalar forms (test_fresnel_blocks_bit_exact_in_scalar_forms).  D reaches 1 / (pi alpha^2) = 32.
+    "microfacet_eval": (b_microfacet_eval, 5e-5),
+    # visible-normal sampling: the scalar headers' normalize() of the stretched direction differs from every fma / sum
+    # order tried by an ulp in 4 % of the samples, and GGX amplifies that near grazing incidence
+    "microfacet_sample": (b_microfacet_sample, 1e-4),
     "refract": (b_refract, 5e-5),   # dot(wi, m): fma chain vs left-to-right sum, amplified by sqrt near the critical angle
 }
 

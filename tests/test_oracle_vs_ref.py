@@ -48,7 +48,7 @@ def test_oracle_matches_live_reference_headers(name):
     assert ok, msg
 
 
-@pytest.mark.parametrize("name", ["fresnel", "fresnel_polarized", "specular_reflection", "specular_transmission"])
+@pytest.mark.parametrize("name", ["fresnel", "fresnel_polarized", "specular_reflection", "specular_transmission", "microfacet_eval"])
 def test_fresnel_blocks_bit_exact_in_scalar_forms(name, golden):
     """The oracle follows the JIT variants (fma-chain squared_norm, rsqrt = sqrt(1/x)); switched to the scalar forms of
     the same two operations it reproduces the reference's scalar headers bit for bit (golden, and live when present)."""
@@ -160,6 +160,34 @@ def test_fresnel_polarized_known_answers():
     cos_max = np.sqrt((1 - eta ** 2) / (1 + eta ** 2))                   # Azzam Eq. (11): the largest phase difference
     a_s, a_p, ct = _fres_pol(cos_max, eta)
     assert ct == 0 and np.isclose(np.angle(a_p) - np.angle(a_s), 2 * np.arctan((1 - eta ** 2) / (2 * eta)), rtol=1e-5)
+
+
+def test_microfacet_sampling_is_consistent_with_its_density():
+    """microfacet.h:219-226 vs :311-324: the density returned by sample() is pdf(wi, m) of the sampled normal, the sampled
+    normals are unit vectors on the upper hemisphere, and D(m) cos(theta_m) integrates to one (Beckmann and GGX)."""
+    lib = oracle_lib()
+    n = 4000
+    rng = np.random.default_rng(50)
+    wi = blocks._upper(rng, n)
+    s = rng.uniform(0, 1, (n, 2)).astype(np.float32)
+    for t, au, av in blocks._MICROFACETS:
+        o = np.zeros((n, 4), np.float32)
+        lib.orc_microfacet_sample(C.c_int(t), C.c_float(au), C.c_float(av), fp(wi), fp(s), fp(o), C.c_size_t(n))
+        m = np.ascontiguousarray(o[:, :3])
+        assert np.allclose(np.linalg.norm(m, axis=1), 1, atol=1e-6) and (m[:, 2] > 0).all()
+        e = np.zeros((n, 3), np.float32)
+        lib.orc_microfacet_eval(C.c_int(t), C.c_float(au), C.c_float(av), fp(wi), fp(m), fp(e), C.c_size_t(n))
+        assert np.allclose(e[:, 2], o[:, 3], rtol=1e-5, atol=1e-7)
+        # quadrature of D(m) cos(theta) over the hemisphere in slope space-friendly coordinates
+        th = (np.arange(4000) + 0.5) / 4000 * (np.pi / 2)
+        ph = (np.arange(64) + 0.5) / 64 * 2 * np.pi
+        T, P = np.meshgrid(th, ph, indexing="ij")
+        mm = np.stack([np.sin(T) * np.cos(P), np.sin(T) * np.sin(P), np.cos(T)], -1).reshape(-1, 3).astype(np.float32)
+        ee = np.zeros((len(mm), 3), np.float32)
+        up = np.tile(np.array([[0, 0, 1]], np.float32), (len(mm), 1))
+        lib.orc_microfacet_eval(C.c_int(t), C.c_float(au), C.c_float(av), fp(up), fp(np.ascontiguousarray(mm)), fp(ee), C.c_size_t(len(mm)))
+        integral = (ee[:, 0].astype(np.float64) * np.cos(T).ravel() * np.sin(T).ravel()).sum() * (np.pi / 2 / 4000) * (2 * np.pi / 64)
+        assert abs(integral - 1) < 2e-3, (t, au, av, integral)
 
 
 # ---------------------------------------------------------------------------
