@@ -18,6 +18,7 @@
 #include "omie.h"
 #include "ofresnel.h"
 #include "omicrofacet.h"
+#include "oroughdielectric.h"
 #include <thread>
 #include <mutex>
 #include <atomic>
