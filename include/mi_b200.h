@@ -286,6 +286,12 @@ int  mib_debug_math(int op /*0 sincos,1 exp,2 log,3 cbrt,4 asin*/, const float *
    eta_it, eta_ti) [n][7];  2 / 3: -> row-major 4x4 Mueller matrix [n][16];  4: in = (wi, m) [n][6] -> refracted direction [n][3]
    (zero under total internal reflection). */
 int  mib_debug_fresnel(int op, const float *in_host, float eta, float *out_host, size_t n);
+/* Microfacet distribution of the rough ocean interface on the device (csrc/dmicrofacet.cuh; groundwork for `roughdielectric`,
+   SURVEY 8f rank 2): MicrofacetDistribution eval / smith_g1 / pdf / visible-normal sample (include/mitsuba/render/microfacet.h:
+   185-440) and Dr.Jit's erf / erfinv / exp2 (ext/drjit/include/drjit/math.h:756-820,1473-1552).  type 0 = beckmann, 1 = ggx.
+   op 0: in = (wi, m) [n][6] -> (eval, smith_g1, pdf) [n][3];  1: in = (wi, sample2) [n][5] -> (m, pdf) [n][4];
+   2 / 3 / 4: in = x [n] -> erf(x) / erfinv(x) / exp2(x) [n] (type and alphas ignored). */
+int  mib_debug_microfacet(int op, int type, float alpha_u, float alpha_v, const float *in_host, float *out_host, size_t n);
 /* fast mode: the majorant supergrid of a heterogeneous medium, [M][M][M] (z, y, x), scale included */
 int  mib_debug_supergrid(mib_scene *scene, int medium, float *out_host, size_t count);
 

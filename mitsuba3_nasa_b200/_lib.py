@@ -232,3 +232,16 @@ def debug_fresnel(op, x, eta):
     if rc != 0:
         raise RuntimeError(l.mib_last_error().decode())
     return out
+
+
+def debug_microfacet(op, x, type_=0, alpha_u=0.1, alpha_v=0.1):
+    """Run a block of csrc/dmicrofacet.cuh on an array (op: 0 eval/smith_g1/pdf with x = [n, 6] rows of (wi, m); 1 visible-normal
+    sampling with x = [n, 5] rows of (wi, sample2); 2 erf, 3 erfinv, 4 exp2 with x = [n])."""
+    l = lib()
+    x = np.ascontiguousarray(x, np.float32)
+    n = x.size // {0: 6, 1: 5}.get(op, 1)
+    out = np.empty((n, {0: 3, 1: 4}.get(op, 1)), np.float32)
+    rc = l.mib_debug_microfacet(C.c_int(op), C.c_int(type_), C.c_float(alpha_u), C.c_float(alpha_v), _fp(x), _fp(out), C.c_size_t(n))
+    if rc != 0:
+        raise RuntimeError(l.mib_last_error().decode())
+    return out

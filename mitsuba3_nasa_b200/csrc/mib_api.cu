@@ -6,6 +6,7 @@
 #include "kernels.cuh"
 #include "astage.cuh"
 #include "dfresnel.cuh"
+#include "dmicrofacet.cuh"
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
