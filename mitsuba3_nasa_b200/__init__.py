@@ -11,3 +11,4 @@ from .api import (set_variant, variant, variants, load_dict, load_string, load_f
 from .scene import PluginError  # noqa: F401
 from .exr import write_exr, read_exr  # noqa: F401
 from .xmlscene import xml_to_dict, XMLError  # noqa: F401
+from .ztest import z_test, images_agree  # noqa: F401
