@@ -12,6 +12,7 @@ import numpy as np
 
 _MAGIC = 20000630
 _FLOAT = 2
+_LINES_PER_BLOCK = {0: 1, 1: 1, 2: 1, 3: 16, 4: 32}          # scanlines per chunk: NONE, RLE, ZIPS, ZIP, PIZ
 
 
 def _attr(name, typ, data):
@@ -22,8 +23,9 @@ def default_channel_names(n):
     return {1: ["Y"], 3: ["R", "G", "B"], 4: ["I", "Q", "U", "V"]}.get(n, ["C%d" % i for i in range(n)])
 
 
-def write_exr(path, image, channel_names=None):
-    """image: [H, W] or [H, W, C] array (stored as float32).  C = 1 -> Y, 3 -> R,G,B, 4 -> Stokes I,Q,U,V by default."""
+def write_exr(path, image, channel_names=None, compression="none"):
+    """image: [H, W] or [H, W, C] array (stored as float32).  C = 1 -> Y, 3 -> R,G,B, 4 -> Stokes I,Q,U,V by default.
+    compression: "none" (one scanline per chunk), "zips" (deflate, one scanline) or "zip" (deflate, 16 scanlines)."""
     img = np.asarray(image, dtype=np.float32)
     if img.ndim == 2:
         img = img[..., None]
@@ -36,9 +38,12 @@ def write_exr(path, image, channel_names=None):
     order = sorted(range(c), key=lambda i: names[i])               # the channel list is sorted by name
     chlist = b"".join(names[i].encode() + b"\0" + struct.pack("<iB3xii", _FLOAT, 0, 1, 1) for i in order) + b"\0"
     box = struct.pack("<4i", 0, 0, w - 1, h - 1)
+    if compression not in ("none", "zips", "zip"):
+        raise ValueError("write_exr: compression must be 'none', 'zips' or 'zip'")
+    comp = {"none": 0, "zips": 2, "zip": 3}[compression]
     header = (struct.pack("<ii", _MAGIC, 2) +
               _attr("channels", "chlist", chlist) +
-              _attr("compression", "compression", b"\0") +
+              _attr("compression", "compression", bytes([comp])) +
               _attr("dataWindow", "box2i", box) +
               _attr("displayWindow", "box2i", box) +
               _attr("lineOrder", "lineOrder", b"\0") +
@@ -46,16 +51,34 @@ def write_exr(path, image, channel_names=None):
               _attr("screenWindowCenter", "v2f", struct.pack("<2f", 0.0, 0.0)) +
               _attr("screenWindowWidth", "float", struct.pack("<f", 1.0)) +
               b"\0")
-    row_bytes = 4 * w * c
-    first = len(header) + 8 * h
-    offsets = np.arange(h, dtype=np.uint64) * np.uint64(8 + row_bytes) + np.uint64(first)
     planar = np.ascontiguousarray(img[:, :, order].transpose(0, 2, 1))   # per scanline: channel after channel
+    lines = _LINES_PER_BLOCK[comp]
+    chunks = []
+    for y0 in range(0, h, lines):
+        raw = planar[y0:y0 + lines].astype("<f4").tobytes()
+        data = raw
+        if comp:
+            data = _deflate_block(raw)
+            if len(data) >= len(raw):
+                data = raw                                               # a block that does not shrink is stored as it is
+        chunks.append(struct.pack("<ii", y0, len(data)) + data)
+    pos = len(header) + 8 * len(chunks)
     with open(path, "wb") as f:
         f.write(header)
-        f.write(offsets.astype("<u8").tobytes())
-        for y in range(h):
-            f.write(struct.pack("<ii", y, row_bytes))
-            f.write(planar[y].astype("<f4").tobytes())
+        for ch in chunks:
+            f.write(struct.pack("<Q", pos))
+            pos += len(ch)
+        for ch in chunks:
+            f.write(ch)
+
+
+def _deflate_block(raw):
+    """ZIP / ZIPS: split the bytes into even and odd halves, delta-code them (+128), deflate."""
+    import zlib
+    a = np.frombuffer(raw, np.uint8)
+    t = np.concatenate([a[0::2], a[1::2]]).astype(np.int64)
+    t[1:] = (t[1:] - t[:-1] + 128) & 0xff
+    return zlib.compress(t.astype(np.uint8).tobytes())
 
 
 def _cstr(buf, pos):
@@ -70,7 +93,6 @@ def _cstr(buf, pos):
 # every codec (tests/test_exr.py).  Every decoder returns the block in the uncompressed chunk layout: per scanline,
 # channel after channel, little-endian samples.
 # ----------------------------------------------------------------------------------------------------------------
-_LINES_PER_BLOCK = {0: 1, 1: 1, 2: 1, 3: 16, 4: 32}          # NONE, RLE, ZIPS, ZIP, PIZ
 _SAMPLE_BYTES = {0: 4, 1: 2, 2: 4}                            # UINT, HALF, FLOAT
 _SAMPLE_DTYPE = {0: "<u4", 1: "<f2", 2: "<f4"}
 

@@ -141,3 +141,22 @@ def test_zip_round_trip_without_the_reference(tmp_path, lines):
         _write_zip_exr(p, img, lines)
         got, names = read_exr(p)
         assert names == ["B", "G", "R"] and np.array_equal(got, img)
+
+
+@pytest.mark.parametrize("compression", ["none", "zips", "zip"])
+def test_writer_compression_round_trip(tmp_path, compression):
+    """write_exr(compression=...) against read_exr, whose ZIP path is pinned on OpenEXR's comp_zip.exr / comp_zips.exr; the
+    independent test writer above produces the same chunk bytes for smooth data."""
+    rng = np.random.default_rng(9)
+    y, x = np.mgrid[0:37, 0:29]
+    img = np.stack([np.sin(x / 9.0) + y / 40.0, np.floor(x / 8.0), rng.uniform(0, 1, x.shape)], axis=-1).astype(np.float32)
+    p = str(tmp_path / "w.exr")
+    write_exr(p, img, compression=compression)
+    got, names = read_exr(p)
+    assert names == ["B", "G", "R"] and np.array_equal(got[..., ::-1], img)
+    if compression != "none":
+        raw = str(tmp_path / "raw.exr")
+        write_exr(raw, img)
+        assert os.path.getsize(p) < os.path.getsize(raw)
+    with pytest.raises(ValueError):
+        write_exr(p, img, compression="piz")
