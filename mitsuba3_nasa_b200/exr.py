@@ -1,5 +1,5 @@
 """Minimal OpenEXR scanline writer / reader for developed films (the role of `Bitmap::write` / `HDRFilm::write`,
-src/films/hdrfilm.cpp:420-590, for the float32 case): uncompressed, one scanline per chunk, FLOAT channels.
+src/films/hdrfilm.cpp:420-590, for the float32 case): FLOAT channels, uncompressed or ZIPS / ZIP / PIZ compressed.
 
 Written from the OpenEXR file-layout specification (magic, version, attribute list, line-offset table, chunks); files
 open in any EXR viewer.  The reader understands single-part scanline files with HALF / FLOAT / UINT channels,
@@ -25,7 +25,8 @@ def default_channel_names(n):
 
 def write_exr(path, image, channel_names=None, compression="none"):
     """image: [H, W] or [H, W, C] array (stored as float32).  C = 1 -> Y, 3 -> R,G,B, 4 -> Stokes I,Q,U,V by default.
-    compression: "none" (one scanline per chunk), "zips" (deflate, one scanline) or "zip" (deflate, 16 scanlines)."""
+    compression: "none" (one scanline per chunk), "zips" (deflate, one scanline), "zip" (deflate, 16 scanlines) or "piz"
+    (wavelet + Huffman, 32 scanlines; the reference's default)."""
     img = np.asarray(image, dtype=np.float32)
     if img.ndim == 2:
         img = img[..., None]
@@ -38,9 +39,9 @@ def write_exr(path, image, channel_names=None, compression="none"):
     order = sorted(range(c), key=lambda i: names[i])               # the channel list is sorted by name
     chlist = b"".join(names[i].encode() + b"\0" + struct.pack("<iB3xii", _FLOAT, 0, 1, 1) for i in order) + b"\0"
     box = struct.pack("<4i", 0, 0, w - 1, h - 1)
-    if compression not in ("none", "zips", "zip"):
-        raise ValueError("write_exr: compression must be 'none', 'zips' or 'zip'")
-    comp = {"none": 0, "zips": 2, "zip": 3}[compression]
+    if compression not in ("none", "zips", "zip", "piz"):
+        raise ValueError("write_exr: compression must be 'none', 'zips', 'zip' or 'piz'")
+    comp = {"none": 0, "zips": 2, "zip": 3, "piz": 4}[compression]
     header = (struct.pack("<ii", _MAGIC, 2) +
               _attr("channels", "chlist", chlist) +
               _attr("compression", "compression", bytes([comp])) +
@@ -57,7 +58,12 @@ def write_exr(path, image, channel_names=None, compression="none"):
     for y0 in range(0, h, lines):
         raw = planar[y0:y0 + lines].astype("<f4").tobytes()
         data = raw
-        if comp:
+        if comp == 4:
+            ny = min(lines, h - y0)
+            data = _piz_encode(np.frombuffer(raw, "<u2").reshape(ny, w * c * 2), w, ny, [2] * c)
+            if len(data) >= len(raw):
+                data = raw
+        elif comp:
             data = _deflate_block(raw)
             if len(data) >= len(raw):
                 data = raw                                               # a block that does not shrink is stored as it is
@@ -393,3 +399,169 @@ def _read_exr(path):
             img[y - ymin:y - ymin + ny, :, i] = np.ascontiguousarray(block[:, off:off + nb]).view(_SAMPLE_DTYPE[t]).astype(np.float32)
             off += nb
     return img, names
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# PIZ encoder (the reference's default for Bitmap::write): forward of _piz_decode.  Checked by decoding its output with the
+# decoder above, which is pinned on OpenEXR's own PIZ test image.
+# ----------------------------------------------------------------------------------------------------------------
+def _wenc14(a, b):
+    a_s, b_s = a.astype(np.int16).astype(np.int32), b.astype(np.int16).astype(np.int32)
+    return ((a_s + b_s) >> 1).astype(np.uint16), (a_s - b_s).astype(np.uint16)
+
+
+def _wenc16(a, b):
+    ao = (a.astype(np.int32) + 0x8000) & 0xffff
+    bi = b.astype(np.int32)
+    m = (ao + bi) >> 1
+    d = ao - bi
+    m = np.where(d < 0, (m + 0x8000) & 0xffff, m)
+    return m.astype(np.uint16), (d & 0xffff).astype(np.uint16)
+
+
+def _wav2_encode(a, max_value):
+    ny, nx = a.shape
+    enc = _wenc14 if max_value < (1 << 14) else _wenc16
+    n = min(nx, ny)
+    p, p2 = 1, 2
+    while p2 <= n:
+        cy, cx = (ny - p2) // p2 + 1, (nx - p2) // p2 + 1
+        ys, xs = slice(0, cy * p2, p2), slice(0, cx * p2, p2)
+        ys1, xs1 = slice(p, p + cy * p2, p2), slice(p, p + cx * p2, p2)
+        i00, i01 = enc(a[ys, xs], a[ys, xs1])
+        i10, i11 = enc(a[ys1, xs], a[ys1, xs1])
+        a[ys, xs], a[ys1, xs] = enc(i00, i10)
+        a[ys, xs1], a[ys1, xs1] = enc(i01, i11)
+        if nx & p:
+            x = cx * p2
+            a[ys, x], a[ys1, x] = enc(a[ys, x], a[ys1, x])
+        if ny & p:
+            y = cy * p2
+            a[y, xs], a[y, xs1] = enc(a[y, xs], a[y, xs1])
+        p = p2
+        p2 <<= 1
+
+
+def _huf_lengths(freq):
+    """Code lengths of a Huffman code for the symbols with freq > 0 (standard two-queue merge on a heap)."""
+    import heapq
+    syms = np.nonzero(freq)[0]
+    lengths = np.zeros(len(freq), np.int64)
+    if len(syms) == 1:
+        lengths[syms[0]] = 1
+        return lengths
+    heap = [(int(freq[s]), int(s), None) for s in syms]
+    heapq.heapify(heap)
+    parent, counter = {}, len(freq)
+    while len(heap) > 1:
+        fa, a, _ = heapq.heappop(heap)
+        fb, b, _ = heapq.heappop(heap)
+        parent[a] = parent[b] = counter
+        heapq.heappush(heap, (fa + fb, counter, None))
+        counter += 1
+    depth = {heap[0][1]: 0}
+    for node in sorted(parent, reverse=True):          # children have smaller ids than their parents
+        depth[node] = depth[parent[node]] + 1
+    for s in syms:
+        lengths[s] = depth[int(s)]
+    if lengths.max() > 58:
+        raise ValueError("write_exr: Huffman code longer than 58 bits")
+    return lengths
+
+
+def _huf_compress(words):
+    """Inverse of _huf_uncompress (no run symbols are emitted; the run symbol still gets a code, as the reference does)."""
+    n = len(words)
+    freq = np.bincount(words, minlength=_HUF_ENCSIZE).astype(np.int64)
+    im = int(np.nonzero(freq)[0][0])
+    i_max = int(np.nonzero(freq)[0][-1]) + 1           # pseudo-symbol for run-length coding
+    freq[i_max] = 1
+    lengths = _huf_lengths(freq)
+    count = np.bincount(lengths, minlength=59)
+    base, c = [0] * 59, 0
+    for l in range(58, 0, -1):
+        nc = (c + int(count[l])) >> 1
+        base[l] = c
+        c = nc
+    codes = np.zeros(_HUF_ENCSIZE, np.uint64)
+    for l in range(1, 59):
+        if count[l]:
+            s = np.nonzero(lengths == l)[0]
+            codes[s] = np.uint64(base[l]) + np.arange(len(s), dtype=np.uint64)
+    # packed table: 6 bits per length, runs of zero lengths as 59..62 (2..5) or 63 + 8 bits (6..261)
+    tl, tc = [], []
+    s = im
+    while s <= i_max:
+        l = int(lengths[s])
+        if l == 0:
+            run = 1
+            while s + run <= i_max and lengths[s + run] == 0 and run < 261:
+                run += 1
+            if run >= 6:
+                tl += [6, 8]; tc += [63, run - 6]
+                s += run
+                continue
+            if run >= 2:
+                tl.append(6); tc.append(59 + run - 2)
+                s += run
+                continue
+        tl.append(6); tc.append(l)
+        s += 1
+    table = _pack_bits(np.array(tc, np.uint64), np.array(tl, np.int64))
+    data_len = lengths[words]
+    data = _pack_bits(codes[words], data_len)
+    n_bits = int(data_len.sum())
+    return struct.pack("<5I", im, i_max, len(table), n_bits, 0) + table + data
+
+
+def _pack_bits(codes, lengths):
+    """MSB-first concatenation of codes[i] in lengths[i] bits."""
+    total = int(lengths.sum())
+    if total == 0:
+        return b""
+    off = np.cumsum(lengths) - lengths
+    idx = np.repeat(np.arange(len(codes)), lengths)
+    within = np.arange(total) - np.repeat(off, lengths)
+    shift = (lengths[idx] - 1 - within).astype(np.uint64)
+    bits = ((codes[idx] >> shift) & np.uint64(1)).astype(np.uint8)
+    return np.packbits(bits).tobytes()
+
+
+def _piz_encode(block_words, nx, ny, sample_words):
+    """block_words: the chunk in its uncompressed layout as uint16 [ny, sum(nx * w)]."""
+    head, words = _piz_forward(block_words, nx, ny, sample_words)
+    huf = _huf_compress(words)
+    return head + struct.pack("<i", len(huf)) + huf
+
+
+def _piz_forward(block_words, nx, ny, sample_words):
+    """Everything before the entropy coder: (bitmap header bytes, LUT-mapped wavelet coefficients).  Deterministic, so it can
+    be compared with the coefficients stored in a file written by OpenEXR itself."""
+    planes, col = [], 0
+    for w in sample_words:
+        planes.append(np.ascontiguousarray(block_words[:, col:col + nx * w]).reshape(ny, nx, w))
+        col += nx * w
+    allw = np.concatenate([p.ravel() for p in planes])
+    present = np.zeros(65536, bool)
+    present[allw] = True
+    present0 = present.copy()
+    present0[0] = False                                # zero is implicit
+    nz = np.nonzero(present0)[0]
+    bitmap = np.packbits(present0, bitorder="little")
+    present[0] = True
+    fwd = (np.cumsum(present) - 1).astype(np.uint16)   # value -> index among the present values
+    max_value = int(present.sum()) - 1
+    out = []
+    for p_ in planes:
+        q = fwd[p_]
+        for j in range(q.shape[2]):
+            sub = np.ascontiguousarray(q[:, :, j])
+            _wav2_encode(sub, max_value)
+            q[:, :, j] = sub
+        out.append(q.ravel())
+    if len(nz):
+        lo, hi = int(nz[0]) >> 3, int(nz[-1]) >> 3
+        head = struct.pack("<HH", lo, hi) + bitmap[lo:hi + 1].tobytes()
+    else:
+        head = struct.pack("<HH", 8191, 0)
+    return head, np.concatenate(out)
