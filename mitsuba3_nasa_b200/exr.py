@@ -23,10 +23,14 @@ def default_channel_names(n):
     return {1: ["Y"], 3: ["R", "G", "B"], 4: ["I", "Q", "U", "V"]}.get(n, ["C%d" % i for i in range(n)])
 
 
-def write_exr(path, image, channel_names=None, compression="none"):
+def write_exr(path, image, channel_names=None, compression="none", component_format="float32"):
     """image: [H, W] or [H, W, C] array (stored as float32).  C = 1 -> Y, 3 -> R,G,B, 4 -> Stokes I,Q,U,V by default.
     compression: "none" (one scanline per chunk), "zips" (deflate, one scanline), "zip" (deflate, 16 scanlines) or "piz"
-    (wavelet + Huffman, 32 scanlines; the reference's default)."""
+    (wavelet + Huffman, 32 scanlines; the reference's default).  component_format: "float32" or "float16" (hdrfilm's
+    default, src/films/hdrfilm.cpp:60-64: HALF channels)."""
+    if component_format not in ("float32", "float16"):
+        raise ValueError("write_exr: component_format must be 'float32' or 'float16'")
+    half = component_format == "float16"
     img = np.asarray(image, dtype=np.float32)
     if img.ndim == 2:
         img = img[..., None]
@@ -37,7 +41,7 @@ def write_exr(path, image, channel_names=None, compression="none"):
     if len(names) != c or len(set(names)) != c:
         raise ValueError("write_exr: need %d distinct channel names" % c)
     order = sorted(range(c), key=lambda i: names[i])               # the channel list is sorted by name
-    chlist = b"".join(names[i].encode() + b"\0" + struct.pack("<iB3xii", _FLOAT, 0, 1, 1) for i in order) + b"\0"
+    chlist = b"".join(names[i].encode() + b"\0" + struct.pack("<iB3xii", 1 if half else _FLOAT, 0, 1, 1) for i in order) + b"\0"
     box = struct.pack("<4i", 0, 0, w - 1, h - 1)
     if compression not in ("none", "zips", "zip", "piz"):
         raise ValueError("write_exr: compression must be 'none', 'zips', 'zip' or 'piz'")
@@ -56,11 +60,11 @@ def write_exr(path, image, channel_names=None, compression="none"):
     lines = _LINES_PER_BLOCK[comp]
     chunks = []
     for y0 in range(0, h, lines):
-        raw = planar[y0:y0 + lines].astype("<f4").tobytes()
+        raw = planar[y0:y0 + lines].astype("<f2" if half else "<f4").tobytes()
         data = raw
         if comp == 4:
             ny = min(lines, h - y0)
-            data = _piz_encode(np.frombuffer(raw, "<u2").reshape(ny, w * c * 2), w, ny, [2] * c)
+            data = _piz_encode(np.frombuffer(raw, "<u2").reshape(ny, -1), w, ny, [1 if half else 2] * c)
             if len(data) >= len(raw):
                 data = raw
         elif comp:

@@ -203,3 +203,20 @@ def test_piz_forward_transform_reproduces_the_coefficients_of_an_openexr_file():
     (length,) = struct.unpack_from("<i", data, hl)
     stored = E._huf_uncompress(data[hl + 4:hl + 4 + length], nx * ny * 4)
     assert np.array_equal(words, stored)
+
+
+@pytest.mark.parametrize("compression", ["none", "zip", "piz"])
+def test_half_precision_output(tmp_path, compression):
+    """component_format='float16' (hdrfilm's default): HALF channels; values come back as the nearest half floats."""
+    rng = np.random.default_rng(13)
+    img = rng.uniform(0, 4, (40, 31, 3)).astype(np.float32)
+    img[5:30, 3:20] = 0.5
+    p = str(tmp_path / "h.exr")
+    write_exr(p, img, compression=compression, component_format="float16")
+    got, names = read_exr(p)
+    assert names == ["B", "G", "R"] and np.array_equal(got[..., ::-1], img.astype(np.float16).astype(np.float32))
+    f = str(tmp_path / "f.exr")
+    write_exr(f, img, compression=compression)
+    assert os.path.getsize(p) < 0.62 * os.path.getsize(f)
+    with pytest.raises(ValueError):
+        write_exr(p, img, component_format="uint32")
