@@ -64,6 +64,49 @@ class Integrator:
         (scene or self._scene)._render_1_backward(seed, spp, grad_in)
 
 
+class Film:
+    """The part of mi.Film the render tests use (src/films/hdrfilm.cpp): size(), bitmap() = the last developed image,
+    write() = an OpenEXR file in the film's component_format, PIZ-compressed as Bitmap::write does."""
+
+    def __init__(self, scene):
+        self._scene = scene
+
+    def size(self):
+        s = self._scene.flat.desc.sensor
+        return (int(s.film_width), int(s.film_height))
+
+    def crop_size(self):
+        s = self._scene.flat.desc.sensor
+        return (int(s.crop_width), int(s.crop_height))
+
+    def bitmap(self, raw=False):
+        img = self._scene._last_image
+        if img is None:
+            raise RuntimeError("No storage allocated, was prepare() called first?")       # hdrfilm.cpp develop() without a render
+        return img
+
+    def write(self, path):
+        from .exr import write_exr
+        fmt = self._scene.flat.film_component_format
+        if fmt == 'uint32':
+            raise RuntimeError("Film.write: component_format 'uint32' is not supported by this build")
+        write_exr(path, np.asarray(self.bitmap()), compression="piz", component_format=fmt)
+
+
+class Sensor:
+    """scene.sensors()[i]: film() plus read access to the flattened sensor record (crop_width, to_world, ...)."""
+
+    def __init__(self, scene):
+        self._scene = scene
+        self._film = Film(scene)
+
+    def film(self):
+        return self._film
+
+    def __getattr__(self, name):
+        return getattr(self._scene.flat.desc.sensor, name)
+
+
 class Scene:
     """mi.Scene stand-in: the flattened description + its device replica."""
 
@@ -71,18 +114,23 @@ class Scene:
         self.flat = flat
         self.device = DeviceScene(flat, device)
         self._integrator = Integrator(self)
+        self._last_image = None
+        self._sensor = Sensor(self)
 
     def integrator(self):
         return self._integrator
 
     def sensors(self):
-        return [self.flat.desc.sensor]
+        return [self._sensor]
 
     def _spp(self, spp):
         return int(spp) if spp else int(self.flat.sample_count)
 
     def _render(self, seed, spp, develop=True):
-        return self.device.render(int(seed), self._spp(spp), develop=develop)
+        img = self.device.render(int(seed), self._spp(spp), develop=develop)
+        if develop:
+            self._last_image = img
+        return img
 
     def _render_1(self, seed, spp):
         out = self.device.render_1(int(seed), self._spp(spp))

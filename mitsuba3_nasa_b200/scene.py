@@ -159,6 +159,7 @@ class Scene:
         self._media_index = {}
         self._phase_index = {}
         self._bsdf_index = {}
+        self.film_component_format = 'float16'
         self._flatten()
 
     # ------------------------------------------------------------------
@@ -514,8 +515,13 @@ class Scene:
             crop = (int(fp.get('crop_offset_x', 0)), int(fp.get('crop_offset_y', 0)),
                     int(fp.get('crop_width', fw)), int(fp.get('crop_height', fh)))
             sample_border = bool(fp.get('sample_border', False))
-            for n in ('pixel_format', 'component_format', 'file_format', 'compensate'):
+            for n in ('pixel_format', 'file_format', 'compensate'):
                 fp.get(n)
+            # hdrfilm.cpp:60-64: float16 by default; only used when the film is written to disk (api.Film.write)
+            self.film_component_format = str(fp.get('component_format', 'float16'))
+            if self.film_component_format not in ('float16', 'float32', 'uint32'):
+                raise PluginError("The \"component_format\" parameter must either be equal to \"float16\", \"float32\", or \"uint32\"."
+                                  " Found %s instead." % self.film_component_format)
             for k, c in fp.children_of('rfilter'):
                 rp = _Props(c)
                 if c.type == 'box':

@@ -166,3 +166,33 @@ def test_variants_and_seed_helper():
     mi.set_variant('scalar_spectral', 'llvm_ad_mono_polarized')
     assert mi.variant() == 'llvm_ad_mono_polarized'
     assert mi.sample_tea_32(1, 1)[1] >> 9 | 0x3f800000 == np.array([0.5424730777740479 + 1], np.float32).view(np.uint32)[0]
+
+
+def test_film_wrapper_writes_the_last_developed_image(tmp_path):
+    """api.Film (hdrfilm.cpp: size / bitmap / write) on a stand-in scene -- no device involved.  component_format defaults to
+    float16 as in the reference; the file is PIZ-compressed like Bitmap::write's output."""
+    from types import SimpleNamespace
+    from mitsuba3_nasa_b200 import api
+    from mitsuba3_nasa_b200.exr import read_exr
+    flat = S.load_dict(scenes.c1_homogeneous_cube(res=16, spp=4), "llvm_ad_rgb")
+    assert flat.film_component_format == 'float32'                 # the C1 scene asks for float32
+    d = scenes.c1_homogeneous_cube(res=16, spp=4)
+    del d['sensor']['film']['component_format']
+    flat16 = S.load_dict(d, "llvm_ad_rgb")
+    assert flat16.film_component_format == 'float16'
+    d['sensor']['film']['component_format'] = 'float8'
+    with pytest.raises(S.PluginError, match='component_format'):
+        S.load_dict(d, "llvm_ad_rgb")
+    img = np.random.default_rng(0).uniform(0, 2, (16, 16, 3)).astype(np.float32)
+    for f, want in ((flat, img), (flat16, img.astype(np.float16).astype(np.float32))):
+        fake = SimpleNamespace(flat=f, _last_image=None)
+        sensor = api.Sensor(fake)
+        film = sensor.film()
+        assert film.size() == (16, 16) and film.crop_size() == (16, 16) and sensor.crop_width == 16
+        with pytest.raises(RuntimeError):
+            film.bitmap()
+        fake._last_image = img
+        p = str(tmp_path / "film.exr")
+        film.write(p)
+        got, names = read_exr(p)
+        assert names == ["B", "G", "R"] and np.array_equal(got[..., ::-1], want)
