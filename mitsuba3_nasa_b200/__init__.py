@@ -10,5 +10,5 @@ from .api import (set_variant, variant, variants, load_dict, load_string, load_f
                   Scene, SceneParameters, Integrator, sample_tea_32)
 from .scene import PluginError  # noqa: F401
 from .exr import write_exr, read_exr  # noqa: F401
-from .xmlscene import xml_to_dict, XMLError  # noqa: F401
+from .xmlscene import xml_to_dict, dict_to_xml, XMLError  # noqa: F401
 from .ztest import z_test, images_agree  # noqa: F401

@@ -300,3 +300,81 @@ def xml_to_dict(string, base_dir=None, **kwargs):
         if k not in p.used:
             raise XMLError('Unused parameter "%s"!' % k)        # xml.cpp:976-981
     return d
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# The other direction: a load_dict() dictionary as an XML document the reference can load (the role of
+# mi.xml.dict_to_xml, src/python/python/xml.py).  Grids held in memory are written as .vol files next to the scene.
+# ----------------------------------------------------------------------------------------------------------------
+def _fmt(v):
+    return repr(float(v))
+
+
+def _emit(lines, indent, key, v, out_dir, counter):
+    pad = "    " * indent
+    name = '' if key is None or key.startswith('_arg_') else ' name="%s"' % key
+    if isinstance(v, dict):
+        t = v.get('type')
+        if t == 'ref':
+            lines.append('%s<ref id="%s"%s/>' % (pad, v['id'], name))
+            return
+        if t == 'rgb':
+            lines.append('%s<rgb%s value="%s"/>' % (pad, name, ", ".join(_fmt(x) for x in np.broadcast_to(np.asarray(v['value'], float), (3,)))))
+            return
+        if t == 'scene':
+            tag, attrs = 'scene', ' version="3.0.0"'
+        else:
+            cat = Plugin.CATEGORY.get(t)
+            if cat is None:
+                raise XMLError('dict_to_xml: unknown plugin "%s"' % t)
+            tag = 'spectrum' if cat == 'texture' else cat
+            attrs = ' type="%s"' % t
+            if 'id' in v:
+                attrs += ' id="%s"' % v['id']
+            elif indent == 1 and key is not None and not key.startswith('_arg_'):
+                attrs += ' id="%s"' % key               # top-level objects: the dictionary key is what <ref> points at
+            elif name:
+                attrs += name
+        body = []
+        for k, c in v.items():
+            if k in ('type', 'id'):
+                continue
+            _emit(body, indent + 1, k, c, out_dir, counter)
+        if body:
+            lines.append('%s<%s%s>' % (pad, tag, attrs))
+            lines.extend(body)
+            lines.append('%s</%s>' % (pad, tag))
+        else:
+            lines.append('%s<%s%s/>' % (pad, tag, attrs))
+    elif isinstance(v, ScalarTransform4f):
+        lines.append('%s<transform%s>' % (pad, name))
+        lines.append('%s    <matrix value="%s"/>' % (pad, " ".join(_fmt(x) for x in v.matrix.reshape(-1))))
+        lines.append('%s</transform>' % pad)
+    elif isinstance(v, bool):
+        lines.append('%s<boolean%s value="%s"/>' % (pad, name, 'true' if v else 'false'))
+    elif isinstance(v, (int, np.integer)):
+        lines.append('%s<integer%s value="%d"/>' % (pad, name, int(v)))
+    elif isinstance(v, (float, np.floating)):
+        lines.append('%s<float%s value="%s"/>' % (pad, name, _fmt(v)))
+    elif isinstance(v, str):
+        lines.append('%s<string%s value="%s"/>' % (pad, name, v))
+    elif key in ('grid', 'data') and (hasattr(v, 'channel_count') or (isinstance(v, np.ndarray) and v.ndim in (3, 4))):
+        # gridvolume data held in memory (a VolumeGrid or a [z, y, x, c] array): the reference takes it as a .vol file
+        if out_dir is None:
+            raise XMLError('dict_to_xml: the scene holds a grid in memory; pass out_dir so that it can be written as a .vol file')
+        from .volumegrid import VolumeGrid
+        counter[0] += 1
+        fname = 'grid_%d.vol' % counter[0]
+        (v if hasattr(v, 'channel_count') else VolumeGrid(np.asarray(v, np.float32))).write(os.path.join(out_dir, fname))
+        lines.append('%s<string name="filename" value="%s"/>' % (pad, fname))
+    elif isinstance(v, (list, tuple, np.ndarray)) and np.asarray(v).shape == (3,):
+        lines.append('%s<vector%s value="%s"/>' % (pad, name, ", ".join(_fmt(x) for x in v)))
+    else:
+        raise XMLError('dict_to_xml: cannot express property "%s" (%s) in XML' % (key, type(v).__name__))
+
+
+def dict_to_xml(d, out_dir=None):
+    """Returns the XML text of a load_dict() dictionary.  xml_to_dict(dict_to_xml(d)) flattens to the same scene."""
+    lines = []
+    _emit(lines, 0, None, d, out_dir, [0])
+    return "\n".join(lines) + "\n"

@@ -316,3 +316,21 @@ def test_film_write_after_a_render(tmp_path):
     film.write(path)
     got, names = mi.read_exr(path)
     assert names == ["B", "G", "R"] and np.array_equal(got[..., ::-1], img.astype(np.float32))
+
+
+def test_dict_to_xml_round_trip(tmp_path):
+    """dict_to_xml (the role of mi.xml.dict_to_xml): the XML text of a load_dict dictionary flattens to the same scene;
+    grids held in memory travel as .vol files next to the scene."""
+    from mitsuba3_nasa_b200.xmlscene import dict_to_xml
+    for d, variant in ((scenes.c1_homogeneous_cube(res=8, spp=2), "llvm_ad_rgb"),
+                       (scenes.c2_rayleigh_slab(), "llvm_ad_mono_polarized")):
+        _same(S.load_dict(xml_to_dict(dict_to_xml(d)), variant), S.load_dict(d, variant))
+    grid = np.random.default_rng(0).uniform(0, 1, (6, 5, 4, 1)).astype(np.float32)
+    d = scenes.c3_cloud(res=8, spp=2, grid=grid, phase={'type': 'rayleigh'})
+    with pytest.raises(XMLError, match="out_dir"):
+        dict_to_xml(d)
+    text = dict_to_xml(d, str(tmp_path))
+    assert os.listdir(str(tmp_path)) == ["grid_1.vol"] and '<string name="filename" value="grid_1.vol"/>' in text
+    _same(S.load_dict(xml_to_dict(text, str(tmp_path)), "llvm_ad_mono_polarized"), S.load_dict(d, "llvm_ad_mono_polarized"))
+    with pytest.raises(XMLError, match="unknown plugin"):
+        dict_to_xml({'type': 'scene', 'x': {'type': 'nonsense'}})
