@@ -33,7 +33,7 @@ template <int SPEC> struct APoolL {
     static constexpr int F_NDIST = F_NEV + NC;         // total_dist, max_dist
     static constexpr int F_NA = F_NDIST + 2;           // contribution per unit emitted radiance, then the contribution
     static constexpr int F_COUNT = F_NA + NR;
-    static constexpr int P = ((232448 - 256 - 2 * kPoolRings * kPoolRingSlack) / (F_COUNT * 4 + 2 * kPoolRings)) / 32 * 32;
+    static constexpr int P = pool_slots_for(F_COUNT);
 };
 constexpr uint32_t FL_BACKWARD = 0x4;                  // (the forward kernel's FL_SPEC_CHAIN bit: prb walks have no specular chain)
 
@@ -50,14 +50,13 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
     constexpr int P = L::P;
     static_assert(apool_smem_bytes<SPEC>() <= 232448, "pool does not fit the shared memory of sm_100");
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    PoolShared *ps = reinterpret_cast<PoolShared *>(smem_raw);
-    volatile uint16_t *ring = reinterpret_cast<volatile uint16_t *>(smem_raw + pool_ring_offset());
     PoolMem<P> pm;
     pm.pw = reinterpret_cast<uint32_t *>(smem_raw + pool_state_offset(P));
     const mib_sensor &sn = sc.d.sensor;
     const unsigned lane_id = threadIdx.x & 31;
-    const uint64_t total_local = pool_local_total(lp.lane_end - lp.lane_begin, blockIdx.x, gridDim.x);
-    pool_init<P>(ps, ring, (unsigned) total_local, C_START);
+    PoolQ<P, kAdjGroupMap> q;
+    q.init(smem_raw, lp.lane_end - lp.lane_begin, lp.counters + 6, C_START);
+    PoolShared *ps = q.ps;
     for (int s = threadIdx.x; s < P; s += blockDim.x) { pm.su(L::F_LANE, s, kNoLane); pm.su(L::F_FLAGS, s, 0u); }
     __syncthreads();
 
@@ -95,13 +94,10 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
     };
     constexpr uint32_t kNeeBits = FL_NEE_ACTIVE | FL_NEE_NEEDS_INT | FL_NEE_SURFACE | 0xff0000u;
 
-    unsigned idle_spins = 0;
     while (true) {
         int cls, slot;
-        unsigned n;
-        if (!pool_claim<P, kAdjGroupMap>(ps, ring, lane_id, idle_spins, cls, n, slot)) break;
-        const bool has = lane_id < n;
-        __threadfence_block();
+        bool has;
+        if (!q.claim(cls, has, slot)) break;
         int next = -1;
         switch (cls) {
         case C_START: {
@@ -113,18 +109,14 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
                 replay = j != kNoLane && !(pm.u(L::F_FLAGS, slot) & FL_BACKWARD);
             }
             const bool need = has && !replay;
-            const unsigned m = __ballot_sync(FULL, need);
-            unsigned b0 = 0;
-            if (m && (int) lane_id == __ffs(m) - 1) b0 = atomicAdd(&ps->next_local, (unsigned) __popc(m));
-            if (m) b0 = __shfl_sync(FULL, b0, __ffs(m) - 1);
+            const uint32_t jn = q.take_lanes(need);
             bool fresh = false;
             if (need) {
-                uint32_t jn = b0 + (uint32_t) __popc(m & ((1u << lane_id) - 1u));
-                if (jn < ps->total_local) { j = jn; fresh = true; }
-                else { pm.su(L::F_LANE, slot, kNoLane); atomicAdd(&ps->retired, 1u); }
+                if (jn != kNoLane) { j = jn; fresh = true; }
+                else { pm.su(L::F_LANE, slot, kNoLane); q.retire(); }
             }
             if (replay || fresh) {
-                const uint64_t lane = stripe_map(lp, lp.lane_begin + pool_lane(j, blockIdx.x, gridDim.x));
+                const uint64_t lane = stripe_map(lp, lp.lane_begin + q.lane_of(j));
                 // integrator.cpp:323-340 (lane -> pixel) + render_sample :1139-1170 (film position, sensor ray)
                 Pcg32 rng;
                 rng.seed_lane(lp.seed_value, (uint32_t) lane);
@@ -376,7 +368,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
             break;
         }
         }
-        pool_push<P>(ps, ring, lane_id, next, slot);
+        q.push(next, slot);
     }
 
     sink.flush();

@@ -62,6 +62,28 @@ constexpr unsigned kPoolSpinLimit = 1u << 22;   // watchdog of the two wait loop
 constexpr uint32_t kNoLane = 0xffffffffu;
 constexpr unsigned kRingEmpty = 0xffffu;
 
+// Slot bookkeeping (MIB_POOL_BOS):
+//   1 (shipped)  bank-owned slots: slot s belongs to shared-memory bank s % 32 and is only ever touched by lane s % 32 of some
+//                warp, so every field access of a warp (pw[f * P + s], P % 32 == 0) hits 32 distinct banks by construction.
+//                Per (class, bank) one 32-bit mask of waiting slots; claim = the lane clears one bit of ITS bank's mask
+//                (atomicAnd), hand-over = atomicOr.  No rings, no head CAS, no waiting for a producer.
+//   0            one ring of slot ids per class (round 1): a warp's 32 slot ids are arbitrary -> 49 % of the shared-memory
+//                wavefronts were bank conflicts (profiles/r01_ncu_l_c2_kforward_pool.txt).
+#ifndef MIB_POOL_BOS
+#define MIB_POOL_BOS 1
+#endif
+#if MIB_POOL_BOS
+constexpr int kPoolHeaderBytes = 64 + 8 * 32 * 4;      // PoolShared + masks[8][32]
+__host__ __device__ constexpr int pool_slots_for(int f_count) {
+    int p = ((232448 - kPoolHeaderBytes) / (f_count * 4)) / 32 * 32;
+    return p > 1024 ? 1024 : p;                        // at most 32 slots per bank (one mask word)
+}
+#else
+__host__ __device__ constexpr int pool_slots_for(int f_count) {
+    return ((232448 - 256 - 2 * kPoolRings * kPoolRingSlack) / (f_count * 4 + 2 * kPoolRings)) / 32 * 32;
+}
+#endif
+
 enum { C_START = 0, C_MAIN = 1, C_SCAT = 2, C_NEE = 3, C_PHASE = 4, C_BSDF = 5, C_NEEG = 6, C_MAINB = 7, C_COUNT = 6 };   // C_NEEG, C_MAINB: adjoint only (apool.cuh)
 // Group of every class, 4 bits per class (pool_claim): all warps of a CTA serve ONE group at a time.  The finer the groups
 // the better (B200, Msamples/s, c3 / c3 polarized / c2 / c1 / c4 adjoint; profiles/r01_ab_variants.md):
@@ -109,7 +131,7 @@ template <int SPEC> struct PoolL {
     static constexpr int F_LSP = F_SCP;
     // slots per CTA: as many as fit into the 227 KB of opt-in shared memory (state words + one 16-bit entry per stage ring),
     // a compile-time constant so that every field access is one LDS / STS with an immediate offset
-    static constexpr int P = ((232448 - 256 - 2 * kPoolRings * kPoolRingSlack) / (F_COUNT * 4 + 2 * kPoolRings)) / 32 * 32;
+    static constexpr int P = pool_slots_for(F_COUNT);
 };
 
 // flags word
@@ -118,6 +140,14 @@ constexpr uint32_t FL_CHANNEL = 0x3, FL_SPEC_CHAIN = 0x4, FL_NEEDS_INT = 0x8, FL
 MIB_D uint32_t fl_medium(uint32_t f) { return (f >> 8) & 0xff; }         // medium + 1
 MIB_D uint32_t fl_nee_medium(uint32_t f) { return (f >> 16) & 0xff; }    // nee.medium + 1
 
+#if MIB_POOL_BOS
+struct PoolShared {
+    unsigned retired, error, group, pad[13];
+};
+static_assert(sizeof(PoolShared) == 64, "PoolShared");
+__host__ __device__ constexpr size_t pool_ring_offset() { return sizeof(PoolShared); }                       // the masks
+__host__ __device__ constexpr size_t pool_state_offset(int) { return (size_t) kPoolHeaderBytes; }
+#else
 struct PoolShared {
     unsigned head[8], tail[8];
     unsigned next_local, total_local, retired, error;
@@ -126,6 +156,7 @@ struct PoolShared {
 
 __host__ __device__ constexpr size_t pool_ring_offset() { return (sizeof(PoolShared) + 15) & ~(size_t) 15; }
 __host__ __device__ constexpr size_t pool_state_offset(int P) { return (pool_ring_offset() + (size_t) kPoolRings * (P + kPoolRingSlack) * sizeof(uint16_t) + 15) & ~(size_t) 15; }
+#endif
 template <int SPEC> __host__ __device__ constexpr size_t pool_smem_bytes() {
     return pool_state_offset(PoolL<SPEC>::P) + (size_t) PoolL<SPEC>::F_COUNT * PoolL<SPEC>::P * sizeof(uint32_t);
 }
@@ -162,6 +193,139 @@ template <int P> struct PoolMem {
     }
 };
 
+#if MIB_POOL_BOS
+// ---------------------------------------------------------------------------------------------
+// Slot bookkeeping shared by the forward and the adjoint pool kernels: bank-owned slots.
+//
+// masks[c * 32 + b], bit j set  <=>  slot j * 32 + b waits in class c.  A slot waits in at most one class; while a lane works
+// on it, its bit is clear everywhere.  Lane b of ANY warp of the CTA serves bank b:
+//   claim  every lane reads the 8 masks of its bank, 8 ballots give the number of banks with a waiting slot per class, the
+//          warp picks ONE class (group policy below), and each lane clears one bit of masks[class][its bank] with atomicAnd.
+//          Lanes whose bank has nothing in that class sit the batch out.
+//   push   atomicOr of the slot's bit into masks[next class][its bank] -- one instruction for the warp, 32 distinct words.
+// __threadfence_block() orders the state stores before the atomicOr and the atomicAnd before the state loads.
+//
+// Group policy (MIB_POOL_GROUPS, as in round 1): all warps of the CTA serve the classes of ONE group until fewer than
+// kPoolFull banks have a waiting slot there, and then switch together, so that the code live in the instruction cache is one
+// group's and the warps share its lines.
+//
+// Lanes: the warps draw chunks of kPoolChunk consecutive lanes from ONE counter in global memory (lp.counters[6]), so a CTA
+// that happens to get short paths simply takes more chunks (no static deal, no per-CTA tail), and at any time all CTAs work
+// on neighbouring rows of the film (grid and gradient lines are shared through the L2).  Per-lane seeds depend only on the
+// lane index (integrator.cpp:323-340), so the result does not depend on which warp walked a lane.
+// ---------------------------------------------------------------------------------------------
+#ifndef MIB_POOL_FULL
+#define MIB_POOL_FULL 32
+#endif
+constexpr unsigned kPoolFull = MIB_POOL_FULL;     // banks with a waiting slot that count as a full batch
+template <int P, unsigned GROUPMAP> struct PoolQ {
+    static constexpr unsigned FULL = 0xffffffffu;
+    PoolShared *ps;
+    unsigned *masks;
+    unsigned lane_id, idle_spins, rot;
+    uint64_t w_next, w_end, n_lanes;                   // the warp's current chunk of lanes, the launch's lane count
+    unsigned long long *chunk_counter;
+
+    MIB_D void init(unsigned char *smem_raw, uint64_t n, unsigned long long *counter, int start_class) {
+        ps = reinterpret_cast<PoolShared *>(smem_raw);
+        masks = reinterpret_cast<unsigned *>(smem_raw + pool_ring_offset());
+        lane_id = threadIdx.x & 31; idle_spins = 0; rot = threadIdx.x >> 5;
+        w_next = w_end = 0; n_lanes = n; chunk_counter = counter;
+        if (threadIdx.x == 0) {
+            ps->retired = 0; ps->error = 0;
+            ps->group = (GROUPMAP >> (4 * start_class)) & 15u;
+        }
+        constexpr unsigned per_bank = P / 32;
+        for (int i = threadIdx.x; i < 8 * 32; i += blockDim.x)
+            masks[i] = (i >> 5) == start_class ? (per_bank >= 32u ? FULL : ((1u << per_bank) - 1u)) : 0u;
+    }
+
+    // Returns false when every slot of the CTA has retired (or the watchdog fired).  has: this lane holds a slot.
+    MIB_D bool claim(int &cls, bool &has, int &slot) {
+        volatile unsigned *vm = masks;
+        while (true) {
+            unsigned kin = 0, kout = 0;
+#if MIB_POOL_GROUPS
+            const unsigned g = *(volatile unsigned *) &ps->group;
+#else
+            const unsigned g = 0;
+#endif
+#pragma unroll
+            for (unsigned c = 0; c < 8; ++c) {
+                const unsigned n = (unsigned) __popc(__ballot_sync(FULL, vm[c * 32 + lane_id] != 0u));
+                const unsigned key = n ? ((n << 3) | c) : 0u;
+                if (((GROUPMAP >> (4u * c)) & 15u) == g) kin = max(kin, key); else kout = max(kout, key);
+            }
+            const unsigned n_in = kin >> 3, n_out = kout >> 3;
+            int best = -1;
+            bool flip = false;
+            if (n_in >= kPoolFull || (n_in > 0u && n_out < kPoolFull)) best = (int) (kin & 7u);
+            else if (n_out > 0u) { best = (int) (kout & 7u); flip = true; }
+            if (best >= 0) {
+                unsigned m = vm[best * 32 + lane_id];
+                bool ok = false;
+                int s = 0;
+                while (m) {
+                    // start the search at a rotating bit: no slot of a bank waits for ever behind busier ones
+                    const unsigned r = rot & 31u, mr = __funnelshift_r(m, m, r);
+                    const unsigned j = ((unsigned) __ffs(mr) - 1u + r) & 31u;
+                    const unsigned old = atomicAnd(&masks[best * 32 + lane_id], ~(1u << j));
+                    if ((old >> j) & 1u) { ok = true; s = (int) (j * 32u + lane_id); break; }
+                    m = old & ~(1u << j);
+                }
+                if (__any_sync(FULL, ok)) {
+                    if (flip && lane_id == 0) ps->group = (GROUPMAP >> (4u * (unsigned) best)) & 15u;
+                    ++rot;
+                    idle_spins = 0;                    // the idle watchdog counts CONSECUTIVE polls
+                    cls = best; has = ok; slot = s;
+                    __threadfence_block();
+                    return true;
+                }
+                continue;                              // other warps took the slots between the look and the claim
+            }
+            int stop = 0;
+            if (lane_id == 0) {
+                stop = *(volatile unsigned *) &ps->retired >= (unsigned) P || *(volatile unsigned *) &ps->error;
+                if (!stop) {
+                    __nanosleep(100);
+                    if (++idle_spins > kPoolSpinLimit) { ps->error = 1; stop = 1; }
+                }
+            }
+            stop = __shfl_sync(FULL, stop, 0);
+            if (stop) { cls = -1; has = false; slot = 0; return false; }
+        }
+    }
+
+    // Hand the lane's slot to class `next` (< 0: the lane held no slot).
+    MIB_D void push(int next, int slot) {
+        __threadfence_block();
+        if (next >= 0) atomicOr(&masks[next * 32 + (int) lane_id], 1u << ((unsigned) slot >> 5));
+    }
+
+    // START: the lanes with `need` take the next lanes of the launch; kNoLane when the launch has run out of lanes.
+    MIB_D uint32_t take_lanes(bool need) {
+        const unsigned m = __ballot_sync(FULL, need);
+        const unsigned want = (unsigned) __popc(m), rank = (unsigned) __popc(m & ((1u << lane_id) - 1u));
+        uint32_t j = kNoLane;
+        unsigned base = 0;
+        while (base < want) {
+            if (w_next >= w_end) {
+                unsigned long long v = 0;
+                if (lane_id == 0) v = atomicAdd(chunk_counter, (unsigned long long) kPoolChunk);
+                v = __shfl_sync(FULL, v, 0);
+                if (v >= n_lanes) break;
+                w_next = v; w_end = min((uint64_t) v + kPoolChunk, n_lanes);
+            }
+            const unsigned take = (unsigned) min((uint64_t) (want - base), w_end - w_next);
+            if (need && rank >= base && rank < base + take) j = (uint32_t) (w_next + (rank - base));
+            w_next += take; base += take;
+        }
+        return j;
+    }
+    MIB_D uint64_t lane_of(uint32_t j) const { return j; }          // index within the launch -> (virtual) lane of the rank
+    MIB_D void retire() { atomicAdd(&ps->retired, 1u); }
+};
+#else
 // ---------------------------------------------------------------------------------------------
 // Queue machinery shared by the forward and the adjoint pool kernels.
 // ---------------------------------------------------------------------------------------------
@@ -305,6 +469,40 @@ MIB_D uint64_t pool_lane(uint32_t i, uint32_t cta, uint32_t n_cta) {
     return chunk * kPoolChunk + (i % kPoolChunk);
 }
 
+// the round-1 rings behind the interface of the bank-owned bookkeeping
+template <int P, unsigned GROUPMAP> struct PoolQ {
+    static constexpr unsigned FULL = 0xffffffffu;
+    PoolShared *ps;
+    volatile uint16_t *ring;
+    unsigned lane_id, idle_spins;
+    MIB_D void init(unsigned char *smem_raw, uint64_t n, unsigned long long *, int start_class) {
+        ps = reinterpret_cast<PoolShared *>(smem_raw);
+        ring = reinterpret_cast<volatile uint16_t *>(smem_raw + pool_ring_offset());
+        lane_id = threadIdx.x & 31; idle_spins = 0;
+        pool_init<P>(ps, ring, (unsigned) pool_local_total(n, blockIdx.x, gridDim.x), start_class);
+    }
+    MIB_D bool claim(int &cls, bool &has, int &slot) {
+        unsigned n;
+        const bool ok = pool_claim<P, GROUPMAP>(ps, ring, lane_id, idle_spins, cls, n, slot);
+        has = ok && lane_id < n;
+        __threadfence_block();
+        return ok;
+    }
+    MIB_D void push(int next, int slot) { pool_push<P>(ps, ring, lane_id, next, slot); }
+    MIB_D uint32_t take_lanes(bool need) {
+        const unsigned m = __ballot_sync(FULL, need);
+        unsigned b0 = 0;
+        if (m && (int) lane_id == __ffs(m) - 1) b0 = atomicAdd(&ps->next_local, (unsigned) __popc(m));
+        if (m) b0 = __shfl_sync(FULL, b0, __ffs(m) - 1);
+        if (!need) return kNoLane;
+        const uint32_t jn = b0 + (uint32_t) __popc(m & ((1u << lane_id) - 1u));
+        return jn < ps->total_local ? jn : kNoLane;
+    }
+    MIB_D uint64_t lane_of(uint32_t j) const { return pool_lane(j, blockIdx.x, gridDim.x); }
+    MIB_D void retire() { atomicAdd(&ps->retired, 1u); }
+};
+#endif
+
 template <int SPEC, int MODE>
 __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_constant__ LaunchParams lp) {
     using L = PoolL<SPEC>;
@@ -314,16 +512,14 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int P = L::P;
     static_assert(pool_smem_bytes<SPEC>() <= 232448, "pool does not fit the shared memory of sm_100");
-    PoolShared *ps = reinterpret_cast<PoolShared *>(smem_raw);
-    volatile uint16_t *ring = reinterpret_cast<volatile uint16_t *>(smem_raw + pool_ring_offset());
     PoolMem<P> pm;
     pm.pw = reinterpret_cast<uint32_t *>(smem_raw + pool_state_offset(P));
     const mib_sensor &sn = sc.d.sensor;
     const unsigned lane_id = threadIdx.x & 31;
 
-    // ---- lanes of this CTA ----
-    const uint64_t total_local = pool_local_total(lp.lane_end - lp.lane_begin, blockIdx.x, gridDim.x);
-    pool_init<P>(ps, ring, (unsigned) total_local, C_START);
+    PoolQ<P, kFwdGroupMap> q;
+    q.init(smem_raw, lp.lane_end - lp.lane_begin, lp.counters + 6, C_START);
+    PoolShared *ps = q.ps;
     for (int s = threadIdx.x; s < P; s += blockDim.x) pm.su(L::F_LANE, s, kNoLane);
     __syncthreads();
 
@@ -383,14 +579,11 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
         }
     };
 
-    unsigned idle_spins = 0;
     while (true) {
         // ---- 1. claim a batch of up to 32 slots of one class ----
         int cls, slot;
-        unsigned n;
-        if (!pool_claim<P, kFwdGroupMap>(ps, ring, lane_id, idle_spins, cls, n, slot)) break;
-        const bool has = lane_id < n;
-        __threadfence_block();
+        bool has;
+        if (!q.claim(cls, has, slot)) break;
 
         // ---- 2.-3. run the stage ----
         int next = -1;
@@ -403,18 +596,15 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                     float R[NR];
 #pragma unroll
                     for (int r = 0; r < NR; ++r) R[r] = pm.f(L::F_R + r, slot);
-                    finish(lp.lane_begin + pool_lane(j, blockIdx.x, gridDim.x), R);
+                    finish(lp.lane_begin + q.lane_of(j), R);
                 }
             }
-            unsigned b0 = 0;
-            if (lane_id == 0) b0 = atomicAdd(&ps->next_local, n);
-            b0 = __shfl_sync(FULL, b0, 0);
+            const uint32_t j = q.take_lanes(has);
             if (has) {
-                uint32_t j = b0 + lane_id;
-                if (j < ps->total_local) {
+                if (j != kNoLane) {
                     Pcg32 rng;
                     float sx, sy;
-                    Ray ray0 = start(lp.lane_begin + pool_lane(j, blockIdx.x, gridDim.x), rng, sx, sy);
+                    Ray ray0 = start(lp.lane_begin + q.lane_of(j), rng, sx, sy);
                     WalkState<SPEC> st;
                     walk_init<SPEC>(rng, ray0, st);
                     pm.store_rng(slot, rng);
@@ -434,7 +624,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                     next = C_MAIN;
                 } else {
                     pm.su(L::F_LANE, slot, kNoLane);
-                    atomicAdd(&ps->retired, 1u);
+                    q.retire();
                 }
             }
             break;
@@ -651,10 +841,8 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
             break;
         }
         }
-        __threadfence_block();
-
-        // ---- 4. append the slots to their next queues (one atomic per class and warp) ----
-        pool_push<P>(ps, ring, lane_id, next, slot);
+        // ---- 4. hand the slots to their next classes ----
+        q.push(next, slot);
     }
 
     if (lp.mode == 1) {
