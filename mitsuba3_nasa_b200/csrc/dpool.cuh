@@ -209,9 +209,9 @@ template <int P> struct PoolMem {
 // kPoolFull banks have a waiting slot there, and then switch together, so that the code live in the instruction cache is one
 // group's and the warps share its lines.
 //
-// Lanes: the warps draw chunks of kPoolChunk consecutive lanes from ONE counter in global memory (lp.counters[6]), so a CTA
-// that happens to get short paths simply takes more chunks (no static deal, no per-CTA tail), and at any time all CTAs work
-// on neighbouring rows of the film (grid and gradient lines are shared through the L2).  Per-lane seeds depend only on the
+// Lanes: the warps draw their next lanes from ONE counter in global memory (lp.counters[6], one atomicAdd per START batch),
+// so a CTA that happens to get short paths simply takes more lanes (no static deal, no per-CTA tail), and at any time all
+// CTAs work on neighbouring pixels (grid and gradient lines are shared through the L2).  Per-lane seeds depend only on the
 // lane index (integrator.cpp:323-340), so the result does not depend on which warp walked a lane.
 // ---------------------------------------------------------------------------------------------
 #ifndef MIB_POOL_FULL
@@ -223,14 +223,14 @@ template <int P, unsigned GROUPMAP> struct PoolQ {
     PoolShared *ps;
     unsigned *masks;
     unsigned lane_id, idle_spins, rot;
-    uint64_t w_next, w_end, n_lanes;                   // the warp's current chunk of lanes, the launch's lane count
-    unsigned long long *chunk_counter;
+    uint64_t n_lanes;                                  // lanes of the launch
+    unsigned long long *lane_counter;                  // next lane of the launch (global memory, zeroed by the host)
 
     MIB_D void init(unsigned char *smem_raw, uint64_t n, unsigned long long *counter, int start_class) {
         ps = reinterpret_cast<PoolShared *>(smem_raw);
         masks = reinterpret_cast<unsigned *>(smem_raw + pool_ring_offset());
         lane_id = threadIdx.x & 31; idle_spins = 0; rot = threadIdx.x >> 5;
-        w_next = w_end = 0; n_lanes = n; chunk_counter = counter;
+        n_lanes = n; lane_counter = counter;
         if (threadIdx.x == 0) {
             ps->retired = 0; ps->error = 0;
             ps->group = (GROUPMAP >> (4 * start_class)) & 15u;
@@ -302,25 +302,17 @@ template <int P, unsigned GROUPMAP> struct PoolQ {
         if (next >= 0) atomicOr(&masks[next * 32 + (int) lane_id], 1u << ((unsigned) slot >> 5));
     }
 
-    // START: the lanes with `need` take the next lanes of the launch; kNoLane when the launch has run out of lanes.
+    // START: the lanes with `need` take the next lanes of the launch (one atomic per warp on the launch's lane counter);
+    // kNoLane when the launch has run out of lanes.  Consecutive lanes are samples of one pixel, so a warp's batch starts
+    // out as 32 neighbouring primary rays.
     MIB_D uint32_t take_lanes(bool need) {
         const unsigned m = __ballot_sync(FULL, need);
+        if (!m) return kNoLane;
         const unsigned want = (unsigned) __popc(m), rank = (unsigned) __popc(m & ((1u << lane_id) - 1u));
-        uint32_t j = kNoLane;
-        unsigned base = 0;
-        while (base < want) {
-            if (w_next >= w_end) {
-                unsigned long long v = 0;
-                if (lane_id == 0) v = atomicAdd(chunk_counter, (unsigned long long) kPoolChunk);
-                v = __shfl_sync(FULL, v, 0);
-                if (v >= n_lanes) break;
-                w_next = v; w_end = min((uint64_t) v + kPoolChunk, n_lanes);
-            }
-            const unsigned take = (unsigned) min((uint64_t) (want - base), w_end - w_next);
-            if (need && rank >= base && rank < base + take) j = (uint32_t) (w_next + (rank - base));
-            w_next += take; base += take;
-        }
-        return j;
+        unsigned long long v = 0;
+        if (lane_id == 0) v = atomicAdd(lane_counter, (unsigned long long) want);
+        v = __shfl_sync(FULL, v, 0) + rank;
+        return (need && v < n_lanes) ? (uint32_t) v : kNoLane;
     }
     MIB_D uint64_t lane_of(uint32_t j) const { return j; }          // index within the launch -> (virtual) lane of the rank
     MIB_D void retire() { atomicAdd(&ps->retired, 1u); }

@@ -367,6 +367,10 @@ def _emit(lines, indent, key, v, out_dir, counter):
         fname = 'grid_%d.vol' % counter[0]
         (v if hasattr(v, 'channel_count') else VolumeGrid(np.asarray(v, np.float32))).write(os.path.join(out_dir, fname))
         lines.append('%s<string name="filename" value="%s"/>' % (pad, fname))
+    elif key in ('cost', 'values', 'm11', 'm12', 'm33', 'm34') and isinstance(v, (list, tuple, np.ndarray)):
+        # phase tables given as arrays (an extension of this package): the reference takes comma-separated strings
+        # (tabphase.cpp:44-60); 9 significant digits round-trip a float32
+        lines.append('%s<string%s value="%s"/>' % (pad, name, ", ".join('%.9g' % float(x) for x in np.asarray(v, np.float32))))
     elif isinstance(v, (list, tuple, np.ndarray)) and np.asarray(v).shape == (3,):
         lines.append('%s<vector%s value="%s"/>' % (pad, name, ", ".join(_fmt(x) for x in v)))
     else:

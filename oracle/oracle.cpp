@@ -55,9 +55,10 @@ Mueller to_sensor_mueller(const Ray &ray, const Mueller &spec) {
 struct LaneSetup { uint32_t px, py; float sample_x, sample_y; Ray ray; };
 
 // integrator.cpp:323-340 + :1139-1170
-LaneSetup setup_lane(const Scene &sc, Sampler &sampler, uint32_t seed, uint64_t lane, uint32_t spp) {
+// reseed = false: the sampler keeps its stream (scalar variants: one stream per pixel, integrator.cpp:1110-1123)
+LaneSetup setup_lane(const Scene &sc, Sampler &sampler, uint32_t seed, uint64_t lane, uint32_t spp, bool reseed = true) {
     const mib_sensor &s = sc.d.sensor;
-    sampler.seed_llvm(sc.d.sampler_base_seed + seed, (uint32_t) lane);
+    if (reseed) sampler.seed_llvm(sc.d.sampler_base_seed + seed, (uint32_t) lane);
     uint32_t idx = (uint32_t) (lane / spp);
     LaneSetup L;
     L.py = idx / (uint32_t) s.crop_width;
@@ -289,6 +290,32 @@ int orc_sample_lanes(void *h, uint32_t seed, uint32_t spp, uint64_t lane_begin, 
         const int C = n_raw_channels(os->sc.d.spectrum);
         std::vector<double> film(npix * C, 0.0);
         dispatch_render(os, seed, spp, lane_begin, lane_begin + count, nthreads, film.data(), out);
+    } catch (const std::exception &e) { g_error = e.what(); return 1; }
+    return 0;
+}
+
+// Scalar-variant seeding (the scheme of the reference's scalar_* variants, which oracle/_ref/scalar can run):
+// pixel k = pixel_index[k] (row-major) draws its spp samples from ONE PCG32 stream seeded with
+// base_seed + pixel_seed[k] (sampler.cpp:131-133, integrator.cpp:1110-1123).  out[(k * spp + j) * C + c].
+int orc_sample_pixels_scalar(void *h, const uint32_t *pixel_index, const uint32_t *pixel_seed, uint32_t n_pixels, uint32_t spp, float *out) {
+    OScene *os = (OScene *) h;
+    try {
+        const Scene &sc = os->sc;
+        const int spec = sc.d.spectrum, C = n_raw_channels(spec);
+        Counters cnt;
+        Sampler sampler;
+        for (uint32_t k = 0; k < n_pixels; ++k) {
+            sampler.seed_scalar(sc.d.sampler_base_seed + pixel_seed[k]);
+            for (uint32_t j = 0; j < spp; ++j) {
+                LaneSetup L = setup_lane(sc, sampler, 0, (uint64_t) pixel_index[k] * spp + j, spp, false);
+                float aovs[4];
+                if (spec == MIB_SPEC_MONO) sample_aovs<0>(sc, sampler, cnt, L.ray, aovs);
+                else if (spec == MIB_SPEC_RGB) sample_aovs<1>(sc, sampler, cnt, L.ray, aovs);
+                else sample_aovs<2>(sc, sampler, cnt, L.ray, aovs);
+                for (int c = 0; c < C; ++c) out[((size_t) k * spp + j) * C + c] = aovs[c];
+            }
+        }
+        os->counters = cnt;
     } catch (const std::exception &e) { g_error = e.what(); return 1; }
     return 0;
 }

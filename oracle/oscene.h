@@ -241,6 +241,13 @@ static inline float intersect_shape(const Scene &sc, int idx, const Ray &ray, in
     }
 }
 
+// TEST-ONLY switch (orc_set_scalar_shapes): reproduce the branches of the reference that only its NON-differentiable
+// variants take, so that the oracle can be compared with the scalar_* build of the reference (oracle/_ref/scalar):
+//   rectangle.cpp:549-553  the hit is re-projected onto the rectangle ("to improve accuracy"); the *_ad_* variants -- the
+//                          parity target of the kernels -- take p = ray(t) (:541-546).
+// Off by default; the kernels and every other oracle entry point follow the llvm_ad_* branches.
+static bool g_scalar_shapes = false;
+
 static inline SurfaceInteraction ray_intersect(const Scene &sc, const Ray &ray) {
     SurfaceInteraction si;
     float best = Inf; int best_shape = -1, best_face = 0;
@@ -257,6 +264,11 @@ static inline SurfaceInteraction ray_intersect(const Scene &sc, const Ray &ray) 
     if (s.type == MIB_SHAPE_RECTANGLE) {
         si.n = Vec3(s.frame_n[0], s.frame_n[1], s.frame_n[2]);
         dp_du = Vec3(s.frame_s[0], s.frame_s[1], s.frame_s[2]);
+        if (g_scalar_shapes) {
+            Vec3 tr(s.to_world[3], s.to_world[7], s.to_world[11]), w = tr - si.p;
+            float dist = (w.x * si.n.x + w.y * si.n.y) + w.z * si.n.z;        // scalar Array dot: left to right, no fma
+            si.p = Vec3(si.p.x + dist * si.n.x, si.p.y + dist * si.n.y, si.p.z + dist * si.n.z);
+        }
     } else if (s.type == MIB_SHAPE_CUBE) {
         si.n = sc.cube_normals[best_shape][best_face];
         dp_du = Vec3(0.f);

@@ -46,6 +46,9 @@ struct Sampler {
         sample_tea_32(seed_value, lane, &v0, &v1);
         rng.seed((uint64_t) v0, (uint64_t) v1);
     }
+    // scalar_* seeding (sampler.cpp:131-133): PCG32(initstate = seed_value, initseq = PCG32_DEFAULT_STREAM); one stream
+    // per pixel, continued over the pixel's samples (integrator.cpp:1110-1123: sampler->seed(seed + i), then spp samples)
+    void seed_scalar(uint32_t seed_value) { rng.seed((uint64_t) seed_value, 0xda3e39cb94b95bdbULL); }
     float next_1d() { return rng.next_float32(); }
     void next_2d(float *a, float *b) { *a = next_1d(); *b = next_1d(); }
 };

@@ -90,6 +90,14 @@ class OracleScene:
                                               C.c_uint64(count), C.c_int(nthreads), fp(out)))
         return out
 
+    def sample_pixels_scalar(self, pixel_index, pixel_seed, spp):
+        """Per-sample aovs under the seeding of the reference's scalar_* variants: [pixel][sample][C]."""
+        pi = np.ascontiguousarray(pixel_index, np.uint32)
+        ps = np.ascontiguousarray(pixel_seed, np.uint32)
+        out = np.zeros((pi.size, spp, self.raw_channels), np.float32)
+        self._check(self.lib.orc_sample_pixels_scalar(self.h, fp(pi), fp(ps), C.c_uint32(pi.size), C.c_uint32(spp), fp(out)))
+        return out
+
     def render_1(self, seed, spp, lanes=(0, 0), nthreads=8, normalize=True):
         out = np.zeros(4, np.float64)
         self._check(self.lib.orc_render_1(self.h, C.c_uint32(seed), C.c_uint32(spp), C.c_uint64(lanes[0]), C.c_uint64(lanes[1]),

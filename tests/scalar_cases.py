@@ -1,0 +1,114 @@
+"""Scenes of the integrator-level pin (shared by tests/golden/make_scalar_golden.py and
+tests/test_oracle_vs_scalar_ref.py).  Every case is a load_dict dictionary small enough for the reference's scalar
+variants (oracle/_ref/scalar, built by oracle/build_ref_scalar.sh) to dump all of its samples in a second.
+
+A case: name -> dict(variant=..., scene=<load_dict dictionary>, spp=..., seed=..., kind='samples' | 'render1').
+Seeds follow the reference's scalar render loop (integrator.cpp:230, 1103-1123): the film is one block, pixel (x, y) is
+pixel i = morton_encode(x, y) of the block and draws its spp samples from PCG32(initstate = seed * W * H + i, default
+stream).  render_1 (integrator.cpp:510-551 with one thread): one stream seeded `seed`, spp samples."""
+import numpy as np
+
+from mitsuba3_nasa_b200 import scenes
+from mitsuba3_nasa_b200.transforms import ScalarTransform4f as T
+
+
+def morton_encode(x, y):
+    r = 0
+    for b in range(16):
+        r |= ((x >> b) & 1) << (2 * b) | ((y >> b) & 1) << (2 * b + 1)
+    return r
+
+
+def pixel_seeds(W, H, seed):
+    """(row-major pixel index, per-pixel seed) in the order the reference visits the pixels."""
+    px = [(morton_encode(x, y), y * W + x) for y in range(H) for x in range(W)]
+    px.sort()
+    return np.array([p for _, p in px], np.uint32), np.array([seed * W * H + i for i, _ in px], np.uint32)
+
+
+def polarized_table(n=181):
+    cost = np.linspace(-1, 1, n).astype(np.float32)
+    m11 = (1.0 + 0.5 * cost ** 2 + 0.8 * np.exp(4 * (cost - 1))).astype(np.float32)
+    m12 = (-0.4 * (1 - cost ** 2)).astype(np.float32)
+    m33 = (0.9 * cost).astype(np.float32)
+    m34 = (0.1 * (1 - cost ** 2)).astype(np.float32)
+    k = np.float32(1.0 / (2 * np.pi * np.trapezoid(m11.astype(np.float64), cost.astype(np.float64))))
+    return {'type': 'tabphase_polarized', 'cost': cost, 'm11': m11 * k, 'm12': m12 * k, 'm33': m33 * k, 'm34': m34 * k}
+
+
+def _grid(n, seed, lo=0.0, channels=1):
+    return np.random.default_rng(seed).uniform(lo, 1.0, (n, n, n, channels)).astype(np.float32)
+
+
+def cloud_no_plateau(n=32):
+    """The C3 blob field without its clipped plateau.  Where the field sits at its maximum over a whole cell, sigma_n =
+    majorant - sigma_t is 0 or one ulp depending on how the eight trilinear weights round, and ratio tracking stops or goes
+    on accordingly: the number of random draws then hangs on the last bit of the look-up position, which differs between the
+    reference's scalar and JIT arithmetic (left-to-right sums vs fma chains).  A ramp makes the maximum a single texel."""
+    g = scenes.cloud_grid(n)
+    ramp = 1.0 - 0.3 * (np.arange(n, dtype=np.float32) + 0.5) / n
+    return (g * ramp[None, None, :, None]).astype(np.float32)
+
+
+def cases():
+    c = {}
+    # C1 (BASELINE configs[0]) at 32 x 32 x 16: homogeneous HG cube, volpath, rgb
+    c['c1_rgb'] = dict(variant='scalar_rgb', scene=scenes.c1_homogeneous_cube(res=32, spp=16), spp=16, seed=0, kind='samples')
+    c['c1_mono_seed3'] = dict(variant='scalar_mono', scene=scenes.c1_homogeneous_cube(res=8, spp=8, max_depth=12), spp=8, seed=3, kind='samples')
+    # C2 (configs[1]): polarized Rayleigh slab, volpathaos, distant sensor: render_1 at 2e4 samples + the first 2048 samples
+    c['c2_pol_aos_render1'] = dict(variant='scalar_mono_polarized', scene=scenes.c2_rayleigh_slab(spp=4, depolarization=0.03), spp=20000, seed=1, kind='render1')
+    c['c2_pol_aos'] = dict(variant='scalar_mono_polarized', scene=scenes.c2_rayleigh_slab(spp=4, depolarization=0.03), spp=2048, seed=1, kind='samples')
+    c['c2_pol_volpath_sky'] = dict(variant='scalar_mono_polarized', scene=scenes.c2_rayleigh_slab(spp=4, integrator='volpath', sun=False), spp=1024, seed=2, kind='samples')
+    c['c2_mono_aos'] = dict(variant='scalar_mono', scene=scenes.c2_rayleigh_slab(spp=4), spp=1024, seed=4, kind='samples')
+    # heterogeneous 32^3 grid, tabulated polarized phase (the C3 / C4 plugin set), volpath, polarized
+    d = scenes.c3_cloud(res=12, spp=8, grid=cloud_no_plateau(32), phase=polarized_table(), optical_depth=6.0)
+    c['het_pol_tab'] = dict(variant='scalar_mono_polarized', scene=d, spp=8, seed=0, kind='samples')
+    cost, val = scenes.hg_table(0.8, 257)
+    d = scenes.c3_cloud(res=16, spp=8, grid=cloud_no_plateau(32), phase={'type': 'tabphase', 'cost': cost, 'values': val}, optical_depth=8.0)
+    c['het_mono_tab'] = dict(variant='scalar_mono', scene=d, spp=8, seed=5, kind='samples')
+    d = scenes.c3_cloud(res=10, spp=4, grid=_grid(10, 2), phase={'type': 'rayleigh'}, optical_depth=6.0, integrator='volpathaos')
+    d['emitter'] = {'type': 'directional', 'direction': [0.3, -0.2, -1.0], 'irradiance': 1.0}
+    c['het_pol_aos_sun'] = dict(variant='scalar_mono_polarized', scene=d, spp=4, seed=0, kind='samples')
+    # rgb: 3-channel albedo grid + spectral extinction through a 3-channel sigma_t scale
+    d = scenes.c3_cloud(res=10, spp=8, grid=_grid(8, 3), phase={'type': 'hg', 'g': 0.5}, optical_depth=5.0)
+    d['object']['interior']['albedo'] = {'type': 'gridvolume', 'data': _grid(6, 4, lo=0.3, channels=3),
+                                         'to_world': T.translate([-1, -1, -1]) @ T.scale(2.0)}
+    c['het_rgb_albedo_grid'] = dict(variant='scalar_rgb', scene=d, spp=8, seed=1, kind='samples')
+    d = scenes.c1_homogeneous_cube(res=10, spp=8, max_depth=16)
+    d['medium1']['sigma_t'] = {'type': 'rgb', 'value': [0.3, 0.6, 0.9]}     # (the reference refuses rgb values above 1)
+    d['medium1']['scale'] = 3.0
+    d['medium1']['has_spectral_extinction'] = True
+    c['homog_rgb_spectral_extinction'] = dict(variant='scalar_rgb', scene=d, spp=8, seed=2, kind='samples')
+    # plugin coverage: sphere container, isotropic phase, hide_emitters, nearest filter, repeat / mirror wrap
+    d = scenes.c1_homogeneous_cube(res=10, spp=8, max_depth=16)
+    d['object'] = {'type': 'sphere', 'center': [0.1, -0.1, 0.0], 'radius': 1.2, 'bsdf': {'type': 'null'}, 'interior': {'type': 'ref', 'id': 'medium1'}}
+    d['medium1']['phase'] = {'type': 'isotropic'}
+    c['sphere_isotropic'] = dict(variant='scalar_rgb', scene=d, spp=8, seed=0, kind='samples')
+    d = scenes.c1_homogeneous_cube(res=10, spp=8, max_depth=16)
+    d['integrator']['hide_emitters'] = True
+    c['hide_emitters'] = dict(variant='scalar_rgb', scene=d, spp=8, seed=0, kind='samples')
+    for wrap in ('repeat', 'mirror'):
+        d = scenes.c3_cloud(res=8, spp=8, grid=_grid(6, 5), phase={'type': 'isotropic'}, optical_depth=5.0)
+        v = d['object']['interior']['sigma_t']
+        v['wrap_mode'] = wrap
+        v['to_world'] = T.translate([-0.4, -0.5, -0.3]) @ T.scale(0.7)     # the cube spans several periods of the texture
+        d['object']['interior']['scale'] = 2.0
+        c['wrap_' + wrap] = dict(variant='scalar_mono', scene=d, spp=8, seed=0, kind='samples')
+    d = scenes.c3_cloud(res=8, spp=8, grid=_grid(6, 6), phase={'type': 'isotropic'}, optical_depth=5.0)
+    d['object']['interior']['sigma_t']['filter_type'] = 'nearest'
+    c['filter_nearest'] = dict(variant='scalar_mono', scene=d, spp=8, seed=0, kind='samples')
+    # area emitter on a rectangle above the cube (NEE + MIS of a hit), diffuse floor
+    d = scenes.c1_homogeneous_cube(res=10, spp=8, max_depth=12)
+    del d['emitter']
+    d['lamp'] = {'type': 'rectangle', 'to_world': T.translate([0, 0, 3.0]) @ T.rotate([1, 0, 0], 180.0) @ T.scale(0.8),
+                 'emitter': {'type': 'area', 'radiance': {'type': 'rgb', 'value': [6.0, 5.0, 4.0]}}}
+    d['floor'] = {'type': 'rectangle', 'to_world': T.translate([0, 0, -1.5]) @ T.scale(4.0),
+                  'bsdf': {'type': 'diffuse', 'reflectance': {'type': 'rgb', 'value': [0.5, 0.6, 0.7]}}}
+    c['area_emitter'] = dict(variant='scalar_rgb', scene=d, spp=8, seed=0, kind='samples')
+    # radiancemeter looking through the cube
+    d = scenes.c1_homogeneous_cube(res=1, spp=64, max_depth=16)
+    d['sensor'] = {'type': 'radiancemeter', 'origin': [0.2, 0.1, 4.0], 'direction': [-0.05, 0.0, -1.0],
+                   'film': {'type': 'hdrfilm', 'width': 1, 'height': 1, 'rfilter': {'type': 'box'}},
+                   'sampler': {'type': 'independent', 'sample_count': 64}}
+    c['radiancemeter'] = dict(variant='scalar_rgb', scene=d, spp=64, seed=0, kind='samples')
+    return c
