@@ -296,12 +296,14 @@ int  mib_debug_microfacet(int op, int type, float alpha_u, float alpha_v, const 
 int  mib_debug_supergrid(mib_scene *scene, int medium, float *out_host, size_t count);
 
 /* Allocation-free variant of mib_debug_sample_lanes.  NO COUNTERPART IN THE REFERENCE: added
-   for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
-   Same arguments, same per-lane values; the per-lane scratch is a static device array of MIB_NOALLOC_MAX_FLOATS floats
-   (4 MiB per GPU that loads the library, held until exit), so count * C must not exceed it (C = raw film channels:
-   2 mono [I,W], 4 rgb [R,G,B,W], 4 polarized [I,Q,U,V]); larger requests fail with a message in mib_last_error().
-   The call performs no cudaMalloc / cudaFree.  Every call shares the array: calls that overlap on one GPU (from several
-   processes, or issued outside this library's own per-process lock) race. */
+   operators for callers that cannot call cudaMalloc (tight serving loops, harnesses that forbid allocation).
+   The per-lane scratch lives in a file-scope `static __device__ __align__(256)` array of MIB_NOALLOC_MAX_FLOATS floats
+   (4 MiB per GPU that loads the library, held until the process exits); requests with count * C above that are refused
+   with a clear error (C = 2 mono, 4 rgb / polarized), as are count == 0 and lane ranges beyond the wavefront.
+   The call performs no cudaMalloc / cudaFree.  It is not capturable into a CUDA graph: like the other render entry points
+   it synchronises the scene's stream and reads the event counters back.  Every call of the process shares the array, which
+   keeps the last call's lanes until the next call (the part a call uses is cleared first); the library serialises the
+   calls of one process, two calls overlapping on one GPU would race. */
 #define MIB_NOALLOC_MAX_FLOATS (1u << 20)
 int  mib_sample_lanes_noalloc(mib_scene *scene, uint32_t seed, uint32_t spp, uint64_t lane_begin,
                               uint64_t count, float *out_host /* [count][C] */);

@@ -79,6 +79,15 @@ MIB_D void sink_volume(Sink &sink, const mib_volume &v, int medium, bool is_albe
 #ifndef MIB_NO_GRAD_ATOMICS
             for (int k = 0; k < n; ++k) grad_add(g + taps.idx[k], s * taps.w[k]);
 #endif
+        } else if constexpr (NC == 1) {
+            // a 3-channel grid seen through a 1-channel variant is its luminance (dscene.cuh eval_grid): d value / d texel
+            // channel = the luminance weight
+            for (int k = 0; k < n; ++k) {
+                const float cw = coeff[0] * taps.w[k];
+                grad_add(g + taps.idx[k], cw * 0.212671f);
+                grad_add(g + taps.idx[k] + 1, cw * 0.715160f);
+                grad_add(g + taps.idx[k] + 2, cw * 0.072169f);
+            }
         } else {
             for (int k = 0; k < n; ++k)
 #pragma unroll

@@ -217,6 +217,9 @@ template <int P> struct PoolMem {
 #ifndef MIB_POOL_FULL
 #define MIB_POOL_FULL 32
 #endif
+#ifndef MIB_POOL_STEAL
+#define MIB_POOL_STEAL 4       // banks a lane may look into beyond its own when that has nothing in the chosen class (0: none)
+#endif
 constexpr unsigned kPoolFull = MIB_POOL_FULL;     // banks with a waiting slot that count as a full batch
 template <int P, unsigned GROUPMAP> struct PoolQ {
     static constexpr unsigned FULL = 0xffffffffu;
@@ -252,7 +255,11 @@ template <int P, unsigned GROUPMAP> struct PoolQ {
 #endif
 #pragma unroll
             for (unsigned c = 0; c < 8; ++c) {
-                const unsigned n = (unsigned) __popc(__ballot_sync(FULL, vm[c * 32 + lane_id] != 0u));
+#if MIB_POOL_STEAL
+                const unsigned n = min(32u, __reduce_add_sync(FULL, (unsigned) __popc(vm[c * 32 + lane_id])));   // waiting slots
+#else
+                const unsigned n = (unsigned) __popc(__ballot_sync(FULL, vm[c * 32 + lane_id] != 0u));          // banks with one
+#endif
                 const unsigned key = n ? ((n << 3) | c) : 0u;
                 if (((GROUPMAP >> (4u * c)) & 15u) == g) kin = max(kin, key); else kout = max(kout, key);
             }
@@ -273,6 +280,24 @@ template <int P, unsigned GROUPMAP> struct PoolQ {
                     if ((old >> j) & 1u) { ok = true; s = (int) (j * 32u + lane_id); break; }
                     m = old & ~(1u << j);
                 }
+#if MIB_POOL_STEAL
+                // Lanes whose own bank has nothing waiting in this class take a slot of one of the next banks instead of
+                // sitting the batch out: their field accesses then share a bank with that bank's own lane (2-way conflict for
+                // these lanes only), which costs far less than an idle lane costs in issue slots.
+                if (!ok) {
+#pragma unroll 1
+                    for (unsigned d = 1; d <= (unsigned) MIB_POOL_STEAL && !ok; ++d) {
+                        const unsigned b = (lane_id + d) & 31u;
+                        m = vm[best * 32 + b];
+                        while (m) {
+                            const unsigned j = (unsigned) __ffs(m) - 1u;
+                            const unsigned old = atomicAnd(&masks[best * 32 + b], ~(1u << j));
+                            if ((old >> j) & 1u) { ok = true; s = (int) (j * 32u + b); break; }
+                            m = old & ~(1u << j);
+                        }
+                    }
+                }
+#endif
                 if (__any_sync(FULL, ok)) {
                     if (flip && lane_id == 0) ps->group = (GROUPMAP >> (4u * (unsigned) best)) & 15u;
                     ++rot;
@@ -299,7 +324,7 @@ template <int P, unsigned GROUPMAP> struct PoolQ {
     // Hand the lane's slot to class `next` (< 0: the lane held no slot).
     MIB_D void push(int next, int slot) {
         __threadfence_block();
-        if (next >= 0) atomicOr(&masks[next * 32 + (int) lane_id], 1u << ((unsigned) slot >> 5));
+        if (next >= 0) atomicOr(&masks[next * 32 + (slot & 31)], 1u << ((unsigned) slot >> 5));
     }
 
     // START: the lanes with `need` take the next lanes of the launch (one atomic per warp on the launch's lane counter);

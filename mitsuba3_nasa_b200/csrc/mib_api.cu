@@ -374,7 +374,7 @@ static void fetch_counters(mib_scene *s, float ms, uint64_t launches) {
     s->last.n_lookups = c[0]; s->last.n_real = c[1]; s->last.n_null = c[2];
     s->last.n_nee_steps = c[3]; s->last.n_surface = c[4]; s->last.n_samples = c[5];
     s->last.kernel_ms = ms; s->last.n_launches = launches;
-    if (c[7]) throw std::runtime_error("path-pool kernel: queue watchdog fired (code " + std::to_string(c[7]) + ": 1 idle poll, 2 ring entry never arrived, 3 ring cell reused too early); results are invalid");
+    if (c[7]) throw std::runtime_error("path-pool kernel: queue watchdog fired (code " + std::to_string(c[7]) + ": 1 = no slot became available within the poll limit; ring build only: 2 = ring entry never arrived, 3 = ring cell reused too early); results are invalid");
 }
 
 // mode 0: film, mode 1: sums, mode 2: per-sample dump into per_sample_dev
@@ -607,13 +607,27 @@ int mib_render_1_raw(mib_scene *s, uint32_t seed, uint32_t spp, double *out4) { 
 int mib_counters_get(mib_scene *s, mib_counters *out) { *out = s->last; return 0; }
 int mib_scene_stream(mib_scene *s, void **stream) { *stream = (void *) s->stream; return 0; }
 
+// A per-lane request must name lanes of the wavefront: (0, 0) is the "whole wavefront" sentinel of lane_range() and a
+// range past the end would be clamped silently, leaving rows of the caller's buffer unwritten.
+static void check_lane_slice(const mib_scene *s, uint32_t spp, uint64_t lane_begin, uint64_t count, const char *who) {
+    const mib_sensor &sn = s->ds.d.sensor;
+    const uint64_t total = (uint64_t) sn.crop_width * sn.crop_height * spp;
+    if (count == 0) throw std::runtime_error(std::string(who) + ": count must be > 0");
+    if (lane_begin > total || count > total - lane_begin)
+        throw std::runtime_error(std::string(who) + ": lanes [" + std::to_string(lane_begin) + ", " + std::to_string(lane_begin) + " + " +
+                                 std::to_string(count) + ") exceed the wavefront of " + std::to_string(total) + " lanes (crop_width * crop_height * spp)");
+}
+
 // Debug / test hook: per-lane aovs (C floats per lane) for lanes [lane_begin, lane_begin+count)
 int mib_debug_sample_lanes(mib_scene *s, uint32_t seed, uint32_t spp, uint64_t lane_begin, uint64_t count, float *out_host) {
     MIB_TRY
+    if (!s || !out_host) throw std::runtime_error("mib_debug_sample_lanes: null argument");
+    check_lane_slice(s, spp, lane_begin, count, "mib_debug_sample_lanes");
     CK(cudaSetDevice(s->device));
     int C = raw_channels(s->ds.d.spectrum);
     float *dev = nullptr;
     CK(cudaMalloc(&dev, count * C * sizeof(float)));
+    CK(cudaMemsetAsync(dev, 0, count * C * sizeof(float), s->stream));
     uint64_t sb = s->lane_begin, se = s->lane_end;
     const uint32_t sw = s->stripe_world;
     s->lane_begin = lane_begin; s->lane_end = lane_begin + count; s->stripe_world = 1;
@@ -629,13 +643,14 @@ int mib_debug_sample_lanes(mib_scene *s, uint32_t seed, uint32_t spp, uint64_t l
 // ---------------------------------------------------------------------------
 // Allocation-free per-lane sampling (no counterpart in the reference).
 //
-// mib_debug_sample_lanes() above cudaMalloc()s its per-lane scratch on every call, which callers under CUDA graph
-// capture, tight serving loops or harnesses that forbid allocation cannot afford.  This variant keeps the scratch in a
-// file-scope device array of MIB_NOALLOC_MAX_FLOATS floats (4 MiB, held by every GPU that loads the library until the
-// process exits).  In host code the array's NAME is only a host-side stand-in, not a device address, so the address
-// is resolved once per device with cudaGetSymbolAddress() (that device current) and that pointer goes to the kernel.
-// All calls share the array and it keeps the last call's contents: the part a call uses is cleared first.  Calls that
-// overlap on one GPU race; g_noalloc_mutex serialises the calls of this process only.
+// mib_debug_sample_lanes() above cudaMalloc()s its per-lane scratch on every call, which tight serving loops and harnesses
+// that forbid allocation cannot afford.  This variant keeps the scratch in a file-scope device array of
+// MIB_NOALLOC_MAX_FLOATS floats (4 MiB, held by every GPU that loads the library until the process exits).  In host code the
+// array's NAME is only a host-side stand-in, not a device address, so the address is resolved once per device with
+// cudaGetSymbolAddress() (that device current) and that pointer goes to the kernel.  The call allocates nothing, but it is
+// NOT capturable into a CUDA graph: like every render entry point it synchronises the scene's stream and reads the event
+// counters back.  All calls of a process share the array and it keeps the last call's lanes until the next call: the part
+// a call uses is cleared first, and g_noalloc_mutex serialises the calls (two calls overlapping on one GPU would race).
 // ---------------------------------------------------------------------------
 static __device__ __align__(256) float g_noalloc_lanes[MIB_NOALLOC_MAX_FLOATS];
 static constexpr int kNoallocMaxDevices = 64;
@@ -659,7 +674,7 @@ extern "C" int mib_sample_lanes_noalloc(mib_scene *s, uint32_t seed, uint32_t sp
     MIB_TRY
     if (!s || !out_host) throw std::runtime_error("mib_sample_lanes_noalloc: null argument");
     const uint64_t C = (uint64_t) raw_channels(s->ds.d.spectrum);
-    if (count == 0) throw std::runtime_error("mib_sample_lanes_noalloc: count must be > 0");
+    check_lane_slice(s, spp, lane_begin, count, "mib_sample_lanes_noalloc");
     if (count > MIB_NOALLOC_MAX_FLOATS / C)
         throw std::runtime_error("mib_sample_lanes_noalloc: " + std::to_string(count) + " lanes x " + std::to_string(C) +
                                  " channels exceed the static scratch of " + std::to_string((unsigned long long) MIB_NOALLOC_MAX_FLOATS) +

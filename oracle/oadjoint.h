@@ -23,7 +23,12 @@ struct GradSink {
             int n = grid_taps(v, p, idx, w);
             for (int k = 0; k < n; ++k) {
                 if (v.channels == 1) { double s = 0; for (int c = 0; c < NC; ++c) s += coeff[c]; grid[v.buffer][idx[k]] += s * (double) w[k]; }
-                else for (int c = 0; c < NC; ++c) grid[v.buffer][idx[k] + c] += coeff[c] * (double) w[k];
+                else if (NC == 1) {
+                    // a 3-channel grid seen through a 1-channel variant is its luminance (oscene.h eval_volume, grid.cpp:545-575):
+                    // d value / d texel channel = the luminance weight
+                    const double lum[3] = { 0.212671, 0.715160, 0.072169 };
+                    for (int c = 0; c < 3; ++c) grid[v.buffer][idx[k] + c] += coeff[0] * lum[c] * (double) w[k];
+                } else for (int c = 0; c < NC; ++c) grid[v.buffer][idx[k] + c] += coeff[c] * (double) w[k];
             }
         } else {
             if (is_albedo) { for (int c = 0; c < NC; ++c) scalar[medium][v.channels == 1 ? 0 : c] += coeff[c]; }

@@ -16,6 +16,8 @@
 #include <mitsuba/render/fresnel.h>
 #include <mitsuba/render/microfacet.h>
 #include <mitsuba/render/interaction.h>
+#include <mitsuba/render/mie.h>
+#include <drjit/dynamic.h>
 #include <drjit/math.h>
 #include <drjit/random.h>
 #include <drjit/sphere.h>
@@ -30,6 +32,12 @@ namespace mitsuba {
     namespace detail {
         void (Throw)(LogLevel, const Class *, const char *, int, const std::string &msg) { throw std::runtime_error(msg); }
     }
+}
+
+// mie.h switches JitFlag::LoopRecord off around its loops (drjit-core is not linked here; scalar arrays ignore the flag)
+extern "C" {
+    void jit_set_flag(JitFlag, int) { }
+    int jit_flag(JitFlag) { return 0; }
 }
 
 using namespace mitsuba;
@@ -176,6 +184,41 @@ void ref_microfacet_sample(int type, float alpha_u, float alpha_v, const float *
     for (size_t i = 0; i < n; ++i) {
         auto [m, pdf] = d.sample(V3(wi3[3*i], wi3[3*i+1], wi3[3*i+2]), P2(s2[2*i], s2[2*i+1]));
         out4[4*i] = m[0]; out4[4*i+1] = m[1]; out4[4*i+2] = m[2]; out4[4*i+3] = pdf;
+    }
+}
+
+
+// Lorenz-Mie amplitudes (include/mitsuba/render/mie.h:45-222), one (mu, radius) pair per call so that the
+// automatic series length (max_nested over the lanes, :76-79) is the lane's own: out7 = (re S1, im S1, re S2, im S2, Ns, Cs, Ct)
+void ref_mie(float wavelength, const float *mu, const float *radius, float med_re, float med_im, float sph_re, float sph_im,
+             int nmax, float *out7, size_t n) {
+    for (size_t i = 0; i < n; ++i) {
+        auto [s1, s2, ns, cs, ct] = mie<float, float>(wavelength, mu[i], radius[i], dr::Complex<float>(med_re, med_im),
+                                                      dr::Complex<float>(sph_re, sph_im), nmax);
+        float *o = out7 + 7 * i;
+        o[0] = dr::real(s1); o[1] = dr::imag(s1); o[2] = dr::real(s2); o[3] = dr::imag(s2); o[4] = ns; o[5] = cs; o[6] = ct;
+    }
+}
+// mueller::mie_scatter (mueller.h:282-295): in7 as above -> m16
+void ref_mie_scatter(const float *in7, float *m16, size_t n) {
+    for (size_t i = 0; i < n; ++i) {
+        const float *q = in7 + 7 * i;
+        store(mueller::mie_scatter<float, dr::Complex<float>>(dr::Complex<float>(q[0], q[1]), dr::Complex<float>(q[2], q[3]), q[4]), m16 + 16 * i);
+    }
+}
+// quad::gauss_legendre (include/mitsuba/core/quad.h:27-90)
+void ref_gauss_legendre(int n, float *nodes, float *weights) {
+    auto [x, w] = quad::gauss_legendre<dr::DynamicArray<float>>(n);
+    for (int i = 0; i < n; ++i) { nodes[i] = x[i]; weights[i] = w[i]; }
+}
+// mueller::stokes_basis / rotate_stokes_basis (mueller.h:347-350, :375-386): v9 = forward, basis_current, basis_target
+void ref_stokes_basis(const float *f3, float *o3, size_t n) {
+    for (size_t i = 0; i < n; ++i) { V3 b = mueller::stokes_basis(V3(f3[3*i], f3[3*i+1], f3[3*i+2])); o3[3*i] = b.x(); o3[3*i+1] = b.y(); o3[3*i+2] = b.z(); }
+}
+void ref_rotate_stokes_basis(const float *v9, float *m16, size_t n) {
+    for (size_t i = 0; i < n; ++i) {
+        const float *q = v9 + 9 * i;
+        store(mueller::rotate_stokes_basis(V3(q[0], q[1], q[2]), V3(q[3], q[4], q[5]), V3(q[6], q[7], q[8])), m16 + 16 * i);
     }
 }
 

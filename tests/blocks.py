@@ -165,6 +165,64 @@ def b_irregular(lib, prefix, n):
     return {"eval": ev, "eval_n": evn, "sample": sm, "integral": np.array([integral.value], np.float32)}
 
 
+def b_mie(lib, prefix, n):
+    """mie() (include/mitsuba/render/mie.h:45-222): size parameters 0.1 ... 450 (the C3 distribution reaches x = 2 pi 40 / 0.55),
+    water in air and an absorbing sphere in a denser host; one (mu, radius) pair per call."""
+    n = min(n, 600)
+    rng = np.random.default_rng(50)
+    mu = rng.uniform(-1, 1, n).astype(np.float32)
+    mu[:4] = [1.0, -1.0, 0.0, 0.5]
+    radius = np.exp(rng.uniform(np.log(0.01), np.log(40.0), n)).astype(np.float32)
+    out = {}
+    for k, (med, sph, nmax) in enumerate((((1.0, 0.0), (1.33, 0.0), -1), ((1.1, 0.0), (1.5, 0.01), -1), ((1.0, 0.0), (1.33, 0.0), 20))):
+        o = np.empty((n, 7), np.float32)
+        getattr(lib, prefix + "mie")(C.c_float(0.55), _p(mu), _p(radius), C.c_float(med[0]), C.c_float(med[1]), C.c_float(sph[0]),
+                                      C.c_float(sph[1]), C.c_int(nmax), _p(o), C.c_size_t(n))
+        out["s%d" % k] = o
+    return out
+
+
+def b_gauss_legendre(lib, prefix, n):
+    """quad::gauss_legendre (reference only: the product side is numpy in mitsuba3_nasa_b200/mie.py)."""
+    out = {}
+    for k in (1, 2, 3, 16, 100):
+        x, w = np.empty(k, np.float32), np.empty(k, np.float32)
+        lib.ref_gauss_legendre(C.c_int(k), _p(x), _p(w))
+        out["x%d" % k] = x
+        out["w%d" % k] = w
+    return out
+
+
+def b_mie_scatter(lib, prefix, n):
+    rng = np.random.default_rng(51)
+    q = rng.uniform(-3, 3, (n, 7)).astype(np.float32)
+    q[:, 4] = rng.uniform(0.1, 50, n)
+    m = np.empty((n, 16), np.float32)
+    getattr(lib, prefix + "mie_scatter")(_p(q), _p(m), C.c_size_t(n))
+    return {"m": m}
+
+
+def b_stokes_basis(lib, prefix, n):
+    rng = np.random.default_rng(52)
+    f = _unit(rng, n)
+    f[:3] = [[0, 0, 1], [0, 0, -1], [1, 0, 0]]
+    o = np.empty((n, 3), np.float32)
+    getattr(lib, prefix + "stokes_basis")(_p(f), _p(o), C.c_size_t(n))
+    return {"o": o}
+
+
+def b_rotate_stokes_basis(lib, prefix, n):
+    rng = np.random.default_rng(53)
+    f = _unit(rng, n).astype(np.float64)
+    a = np.cross(f, _unit(rng, n)); a /= np.linalg.norm(a, axis=1, keepdims=True)
+    ang = rng.uniform(-np.pi, np.pi, (n, 1))
+    b = np.cos(ang) * a + np.sin(ang) * np.cross(f, a)
+    v = np.ascontiguousarray(np.concatenate([f, a, b], axis=1), dtype=np.float32)
+    m = np.empty((n, 16), np.float32)
+    getattr(lib, prefix + "rotate_stokes_basis")(_p(v), _p(m), C.c_size_t(n))
+    return {"m": m}
+
+
 def _xform(name):
     def run(lib, prefix, n):
         rng = np.random.default_rng(12)
@@ -267,6 +325,11 @@ BLOCKS = {
     "square_to_cosine_hemisphere": (_warp("square_to_cosine_hemisphere"), 1e-5),   # z = sqrt(1 - squared_norm(p)): fma vs mul+add, amplified by 1/(2z) near the horizon
     "texture3": (b_texture3, None),
     "irregular": (b_irregular, None),
+    # Lorenz-Mie series in fp32 as the reference evaluates it; the tolerance is relative to each quantity's scale (see
+    # test_oracle_vs_ref.py test_mie_header): the scalar header multiplies complex numbers without fma
+    "mie_scatter": (b_mie_scatter, 1e-5),
+    "stokes_basis": (b_stokes_basis, None),
+    "rotate_stokes_basis": (b_rotate_stokes_basis, 1e-5),
     "transform_point": (_xform("transform_point"), 4e-6),
     "transform_vector": (_xform("transform_vector"), 4e-6),
     "fresnel": (_fresnel_block("fresnel", 4, 30), None),
@@ -287,6 +350,11 @@ BLOCKS = {
     "microfacet_sample": (b_microfacet_sample, 1e-4),
     "refract": (b_refract, 5e-5),   # dot(wi, m): fma chain vs left-to-right sum, amplified by sqrt near the critical angle
 }
+
+
+# blocks that are compared by their own tests (tests/test_oracle_vs_ref.py test_mie_header, test_gauss_legendre_header) but
+# whose reference outputs live in the same golden file
+EXTRA_GOLDEN = {"mie": b_mie, "gauss_legendre": b_gauss_legendre}
 
 
 def compare(name, got, want, tol):

@@ -28,6 +28,9 @@ def main():
     for name, (fn, _tol) in blocks.BLOCKS.items():
         for key, arr in fn(ref, "ref_", N).items():
             out["%s/%s" % (name, key)] = arr
+    for name, fn in blocks.EXTRA_GOLDEN.items():
+        for key, arr in fn(ref, "ref_", N).items():
+            out["%s/%s" % (name, key)] = arr
     path = os.path.join(HERE, "ref_blocks.npz")
     np.savez_compressed(path, n=np.array([N]), **out)
     print("wrote %s (%d arrays, %.1f KiB)" % (path, len(out), os.path.getsize(path) / 1024))

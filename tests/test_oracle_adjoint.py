@@ -118,3 +118,31 @@ def test_grid_gradient_directional_derivative():
     vals = [OracleScene(mk(grid + s * h * v, spp)).render_1(9, spp, nthreads=8)[0] for s in (1, -1)]
     fd = (vals[0] - vals[1]) / (2 * h)
     assert abs(float(g @ v.reshape(-1)) / fd - 1) < 0.06
+
+
+def test_three_channel_albedo_grid_in_a_mono_variant():
+    """A 3-channel grid in a 1-channel variant is evaluated as its luminance (grid.cpp:545-575): the gradient reaches all
+    three channels with the luminance weights.  The albedo only enters through weights, so with Russian roulette off the
+    adjoint is the exact derivative of the same-seed estimator (round 1 sent everything to channel 0 with weight 1)."""
+    rng = np.random.default_rng(8)
+    alb = rng.uniform(0.4, 0.9, size=(3, 3, 3, 3)).astype(np.float32)
+    v = rng.uniform(-1.0, 1.0, size=alb.shape).astype(np.float32)
+    from mitsuba3_nasa_b200.transforms import ScalarTransform4f as T
+
+    def mk(a, spp):
+        d = scenes.c1_homogeneous_cube(res=4, spp=spp, max_depth=10)
+        d['integrator'] = {'type': 'prbvolpath', 'max_depth': 10, 'rr_depth': 1000}
+        d['medium1']['albedo'] = {'type': 'gridvolume', 'data': a, 'to_world': T.translate([-1, -1, -1]) @ T.scale(2.0)}
+        d['sensor']['film']['pixel_format'] = 'luminance'
+        return S.load_dict(d, 'llvm_ad_mono')
+    spp = 4096
+    f = mk(alb, spp)
+    o = OracleScene(f)
+    slot = f.desc.media[0].albedo.buffer
+    o.render_1_backward(3, spp, [1, 0, 0, 0], nthreads=8)
+    g = o.grad_get(slot, alb.size).reshape(alb.shape)
+    assert np.all(np.abs(g).reshape(-1, 3).sum(axis=0) > 0)          # every channel receives gradient
+    h = 0.02
+    vals = [OracleScene(mk(alb + s * h * v, spp)).render_1(3, spp, nthreads=8)[0] for s in (1, -1)]
+    fd = (vals[0] - vals[1]) / (2 * h)
+    assert abs(float((g * v).sum()) / fd - 1) < 2e-3, (float((g * v).sum()), fd)
