@@ -295,6 +295,11 @@ int  mib_debug_microfacet(int op, int type, float alpha_u, float alpha_v, const 
 /* fast mode: the majorant supergrid of a heterogeneous medium, [M][M][M] (z, y, x), scale included */
 int  mib_debug_supergrid(mib_scene *scene, int medium, float *out_host, size_t count);
 
+/* Measured FP32 roof of a device (no reference counterpart; bench.py's `roofline.peak` for the homogeneous scenes, SURVEY 8d
+   "builder measures both with an FMA microbenchmark"): independent FFMA chains on every SM, CUDA-event timed, best of `reps`
+   launches, in TFLOP/s with FMA = 2 flops. */
+int  mib_debug_fp32_peak(int device, int reps, double *tflops_out);
+
 /* Allocation-free variant of mib_debug_sample_lanes.  NO COUNTERPART IN THE REFERENCE: added
    for callers that cannot call cudaMalloc (tight serving loops, harnesses that forbid allocation).
    The per-lane scratch lives in a file-scope `static __device__ __align__(256)` array of MIB_NOALLOC_MAX_FLOATS floats

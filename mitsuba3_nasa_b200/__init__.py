@@ -12,3 +12,4 @@ from .scene import PluginError  # noqa: F401
 from .exr import write_exr, read_exr  # noqa: F401
 from .xmlscene import xml_to_dict, dict_to_xml, XMLError  # noqa: F401
 from .ztest import z_test, images_agree  # noqa: F401
+from . import dr  # noqa: F401,E402  (dr.enable_grad / dr.backward / dr.grad over torch autograd)

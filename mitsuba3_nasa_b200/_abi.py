@@ -101,7 +101,7 @@ EXPORTS = [
     "mib_render_1", "mib_render_1_raw", "mib_render_backward", "mib_render_1_backward",
     "mib_grad_get", "mib_grad_dev", "mib_grad_get_scalar", "mib_grad_scalar_dev", "mib_grad_zero",
     "mib_mie_tabulate", "mib_counters_get", "mib_scene_stream",
-    "mib_debug_sample_lanes", "mib_debug_math", "mib_debug_fresnel", "mib_debug_microfacet", "mib_debug_supergrid",
+    "mib_debug_sample_lanes", "mib_debug_math", "mib_debug_fresnel", "mib_debug_microfacet", "mib_debug_supergrid", "mib_debug_fp32_peak",
     "mib_sample_lanes_noalloc",
 ]
 

@@ -245,3 +245,13 @@ def debug_microfacet(op, x, type_=0, alpha_u=0.1, alpha_v=0.1):
     if rc != 0:
         raise RuntimeError(l.mib_last_error().decode())
     return out
+
+
+def fp32_peak(device=0, reps=5):
+    """Measured FP32 FMA roof of the device in TFLOP/s (mib_debug_fp32_peak)."""
+    l = lib()
+    out = C.c_double()
+    rc = l.mib_debug_fp32_peak(C.c_int(device), C.c_int(reps), C.byref(out))
+    if rc != 0:
+        raise RuntimeError(l.mib_last_error().decode())
+    return out.value

@@ -182,6 +182,34 @@ def load_file(path, update_scene=False, parallel=True, device=0, **kwargs):
     return Scene(_scene.load_dict(d, _variant), device)
 
 
+class ParamArray(np.ndarray):
+    """What params[key] returns for array-valued parameters: a numpy array that remembers where it came from, so that
+    dr.enable_grad(params[key]) / dr.grad(params[key]) (dr.py) can find the parameter, as the Dr.Jit arrays of the
+    reference carry their own AD index."""
+    _mi_params = None
+    _mi_key = None
+
+    def __array_finalize__(self, obj):
+        # results of arithmetic are plain data: only the object handed out by params[key] names a parameter
+        self._mi_params = None
+        self._mi_key = None
+
+
+class ParamScalar(float):
+    """Scalar-valued parameter with the same back-reference."""
+    _mi_params = None
+    _mi_key = None
+
+
+def _tag(value, params, key):
+    if isinstance(value, np.ndarray):
+        out = value.view(ParamArray)
+    else:
+        out = ParamScalar(value)
+    out._mi_params, out._mi_key = params, key
+    return out
+
+
 class SceneParameters:
     """Dictionary-like parameter map (util.py:20-290): params[key] = value; params.update()."""
 
@@ -206,6 +234,9 @@ class SceneParameters:
         return [(k, self[k]) for k in self.keys()]
 
     def __getitem__(self, key):
+        return _tag(self._value(key), self, key)
+
+    def _value(self, key):
         if key not in self.scene.flat.params:
             raise KeyError(key)
         acc = self.scene.flat.params[key]
@@ -244,7 +275,7 @@ class SceneParameters:
         from . import ad
         if ad.grad_source(self.scene, key) is None:
             raise RuntimeError("parameter '%s' is not differentiable in this backend (sigma_t / albedo of media are)" % key)
-        t = torch.tensor(np.asarray(self[key], dtype=np.float32), requires_grad=True)
+        t = torch.tensor(np.array(self._value(key), dtype=np.float32), requires_grad=True)
         self._torch[key] = t
         self._assign(key, t.detach().numpy())
         return t
@@ -308,6 +339,8 @@ def _differentiable(scene, params, seed, seed_grad, spp, spp_grad, one):
     keys = sorted(att)
     if seed_grad == 0:
         seed_grad = sample_tea_32(seed, 1)[0]                         # util.py:617-619
+    elif seed_grad == seed:                                           # util.py:620-622
+        raise Exception('The primal and differential seed should be different to ensure unbiased gradient computation!')
     return ad.render_op().apply(scene, params, keys, int(seed), int(seed_grad), int(spp), int(spp_grad), one, *[att[k] for k in keys])
 
 

@@ -2,9 +2,8 @@
 mib_debug_microfacet) against the oracle restatement (oracle/ofresnel.h, oracle/omicrofacet.h), which tests/test_oracle_vs_ref.py pins on the reference's own headers.  Tolerance: bit-exact (the same
 fused multiply-adds, IEEE division and square root on both sides), as for the device math in test_gpu_parity_forward.py.
 
-These tests were written after the round's GPU minutes were spent and have not run on a GPU yet; until they have, a
-mismatch is reported as an expected failure instead of stopping the suite (non-strict xfail: a pass shows up as XPASS).
-No walk kernel depends on these functions yet."""
+First GPU run: round 2 driver run GPUTEST_r01 (11 XPASS); the expected-failure markers of round 1 are gone.
+"""
 import ctypes as C
 
 import numpy as np
@@ -14,8 +13,7 @@ import blocks
 from mitsuba3_nasa_b200 import _lib
 from orc import oracle_lib
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.xfail(strict=False, reason="new device code, first GPU run pending (see module docstring)")]
+pytestmark = pytest.mark.gpu
 
 N = 20000
 

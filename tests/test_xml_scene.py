@@ -302,7 +302,6 @@ def test_load_string_and_load_file_render_like_load_dict(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.xfail(strict=False, reason="written after the round's GPU minutes were spent; first GPU run pending")
 def test_film_write_after_a_render(tmp_path):
     """scene.sensors()[0].film().write(): the developed film of the last render as a PIZ EXR file (host-side wrapper around
     the same mi.render call as above)."""
