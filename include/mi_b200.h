@@ -41,7 +41,7 @@
 extern "C" {
 #endif
 
-#define MIB_ABI_VERSION 5
+#define MIB_ABI_VERSION 6
 
 #define MIB_MAX_SHAPES   8
 #define MIB_MAX_MEDIA    4
@@ -55,7 +55,8 @@ enum { MIB_SPEC_MONO = 0, MIB_SPEC_RGB = 1, MIB_SPEC_MONO_POLARIZED = 2 };
 enum { MIB_INTEG_VOLPATH = 0, MIB_INTEG_VOLPATHAOS = 1,
        MIB_INTEG_PRBVOLPATH = 2, MIB_INTEG_PRBVOLPATHAOS = 3 };
 enum { MIB_SHAPE_CUBE = 0, MIB_SHAPE_RECTANGLE = 1, MIB_SHAPE_SPHERE = 2 };
-enum { MIB_BSDF_NULL = 0, MIB_BSDF_DIFFUSE = 1 };
+enum { MIB_BSDF_NULL = 0, MIB_BSDF_DIFFUSE = 1, MIB_BSDF_DIELECTRIC = 2, MIB_BSDF_ROUGHDIELECTRIC = 3 };
+enum { MIB_MICROFACET_BECKMANN = 0, MIB_MICROFACET_GGX = 1 };
 enum { MIB_MEDIUM_HOMOGENEOUS = 0, MIB_MEDIUM_HETEROGENEOUS = 1 };
 enum { MIB_VOLUME_CONST = 0, MIB_VOLUME_GRID = 1 };
 enum { MIB_FILTER_NEAREST = 0, MIB_FILTER_TRILINEAR = 1 };
@@ -79,7 +80,8 @@ typedef struct mib_volume {
     float   to_local[16];    /* world -> [0,1]^3 (src/render/volume.cpp:13-17) */
     float   bbox_min[3];
     float   bbox_max[3];
-    float   max_value;       /* filled by mib_scene_commit (grid.cpp:306-319) */
+    float   max_value;       /* filled by mib_scene_commit (grid.cpp:306-319) unless fixed_max is set */
+    int32_t fixed_max;       /* gridvolume `max_value` property (grid.cpp:296-297): max_value is the caller's and is kept */
 } mib_volume;
 
 typedef struct mib_phase {
@@ -108,6 +110,13 @@ typedef struct mib_medium {
 typedef struct mib_bsdf {
     int32_t type;            /* MIB_BSDF_* */
     float   reflectance[3];  /* diffuse (src/bsdfs/diffuse.cpp) */
+    /* the ocean interface of the fork's atmosphere-ocean scenes: */
+    float   eta;             /* dielectric / roughdielectric: int_ior / ext_ior (src/bsdfs/dielectric.cpp:210-222) */
+    float   inv_eta;         /* dielectric: ext_ior / int_ior (:223); roughdielectric: rcp(eta) (roughdielectric.cpp:245) */
+    float   alpha_u;         /* roughdielectric roughness (src/bsdfs/roughdielectric.cpp:196-218) */
+    float   alpha_v;
+    int32_t distribution;    /* MIB_MICROFACET_* (roughdielectric.cpp:182-193) */
+    int32_t sample_visible;  /* roughdielectric.cpp:195 (only 1, the plugin's default, is implemented) */
 } mib_bsdf;
 
 typedef struct mib_shape {
@@ -272,6 +281,9 @@ int  mib_mie_tabulate(int device, float wavelength, float ior_med_re, float ior_
                       const float *mu, int n_mu, float *m11, float *m12, float *m33, float *m34);
 
 int  mib_counters_get(mib_scene *scene, mib_counters *out);
+/* which kernel family mib_render / mib_render_1 will launch for this scene: 1 = path pool (k_forward_pool), 0 = one thread per
+   path (k_forward); bench.py names the measured kernel with it (no reference counterpart) */
+int  mib_scene_forward_kernel(mib_scene *scene, int *is_pool);
 /* The CUDA stream the scene launches on (cudaStream_t as void*). */
 int  mib_scene_stream(mib_scene *scene, void **stream);
 
@@ -299,6 +311,10 @@ int  mib_debug_supergrid(mib_scene *scene, int medium, float *out_host, size_t c
    "builder measures both with an FMA microbenchmark"): independent FFMA chains on every SM, CUDA-event timed, best of `reps`
    launches, in TFLOP/s with FMA = 2 flops. */
 int  mib_debug_fp32_peak(int device, int reps, double *tflops_out);
+/* Measured L2 roof of a device (no reference counterpart): all SMs stream one L2-resident 32 MiB buffer with 16-byte loads,
+   best of `reps` launches, in GB/s.  bench.py reports the grid look-ups of the heterogeneous scenes against it (they hit the
+   L2, so the HBM peak is not the roof they can reach). */
+int  mib_debug_l2_peak(int device, int reps, double *gbs_out);
 
 /* Allocation-free variant of mib_debug_sample_lanes.  NO COUNTERPART IN THE REFERENCE: added
    for callers that cannot call cudaMalloc (tight serving loops, harnesses that forbid allocation).

@@ -5,14 +5,15 @@ and the ABI version at load time so a drift fails loudly.
 """
 import ctypes as C
 
-MIB_ABI_VERSION = 5
+MIB_ABI_VERSION = 6
 MIB_MAX_SHAPES, MIB_MAX_MEDIA, MIB_MAX_PHASES = 8, 4, 4
 MIB_MAX_BSDFS, MIB_MAX_EMITTERS, MIB_MAX_BUFFERS = 8, 4, 16
 
 SPEC_MONO, SPEC_RGB, SPEC_MONO_POLARIZED = 0, 1, 2
 INTEG_VOLPATH, INTEG_VOLPATHAOS, INTEG_PRBVOLPATH, INTEG_PRBVOLPATHAOS = 0, 1, 2, 3
 SHAPE_CUBE, SHAPE_RECTANGLE, SHAPE_SPHERE = 0, 1, 2
-BSDF_NULL, BSDF_DIFFUSE = 0, 1
+BSDF_NULL, BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_ROUGHDIELECTRIC = 0, 1, 2, 3
+MICROFACET_BECKMANN, MICROFACET_GGX = 0, 1
 MEDIUM_HOMOGENEOUS, MEDIUM_HETEROGENEOUS = 0, 1
 VOLUME_CONST, VOLUME_GRID = 0, 1
 FILTER_NEAREST, FILTER_TRILINEAR = 0, 1
@@ -29,7 +30,7 @@ i32, f32 = C.c_int32, C.c_float
 class Volume(C.Structure):
     _fields_ = [("type", i32), ("channels", i32), ("value", f32 * 3), ("res", i32 * 3),
                 ("filter", i32), ("wrap", i32), ("buffer", i32), ("to_local", f32 * 16),
-                ("bbox_min", f32 * 3), ("bbox_max", f32 * 3), ("max_value", f32)]
+                ("bbox_min", f32 * 3), ("bbox_max", f32 * 3), ("max_value", f32), ("fixed_max", i32)]
 
 
 class Phase(C.Structure):
@@ -43,7 +44,8 @@ class Medium(C.Structure):
 
 
 class Bsdf(C.Structure):
-    _fields_ = [("type", i32), ("reflectance", f32 * 3)]
+    _fields_ = [("type", i32), ("reflectance", f32 * 3), ("eta", f32), ("inv_eta", f32), ("alpha_u", f32), ("alpha_v", f32),
+                ("distribution", i32), ("sample_visible", i32)]
 
 
 class Shape(C.Structure):
@@ -100,8 +102,8 @@ EXPORTS = [
     "mib_scene_set_lane_range", "mib_scene_set_lane_stripes", "mib_render", "mib_film_dev", "mib_film_develop", "mib_film_read",
     "mib_render_1", "mib_render_1_raw", "mib_render_backward", "mib_render_1_backward",
     "mib_grad_get", "mib_grad_dev", "mib_grad_get_scalar", "mib_grad_scalar_dev", "mib_grad_zero",
-    "mib_mie_tabulate", "mib_counters_get", "mib_scene_stream",
-    "mib_debug_sample_lanes", "mib_debug_math", "mib_debug_fresnel", "mib_debug_microfacet", "mib_debug_supergrid", "mib_debug_fp32_peak",
+    "mib_mie_tabulate", "mib_counters_get", "mib_scene_forward_kernel", "mib_scene_stream",
+    "mib_debug_sample_lanes", "mib_debug_math", "mib_debug_fresnel", "mib_debug_microfacet", "mib_debug_supergrid", "mib_debug_fp32_peak", "mib_debug_l2_peak",
     "mib_sample_lanes_noalloc",
 ]
 

@@ -255,3 +255,13 @@ def fp32_peak(device=0, reps=5):
     if rc != 0:
         raise RuntimeError(l.mib_last_error().decode())
     return out.value
+
+
+def l2_peak(device=0, reps=3):
+    """Measured L2 streaming-read roof of the device in GB/s (mib_debug_l2_peak)."""
+    l = lib()
+    out = C.c_double()
+    rc = l.mib_debug_l2_peak(C.c_int(device), C.c_int(reps), C.byref(out))
+    if rc != 0:
+        raise RuntimeError(l.mib_last_error().decode())
+    return out.value

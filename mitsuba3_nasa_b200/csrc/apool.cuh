@@ -52,6 +52,9 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
     extern __shared__ __align__(16) unsigned char smem_raw[];
     PoolMem<P> pm;
     pm.pw = reinterpret_cast<uint32_t *>(smem_raw + pool_state_offset(P));
+#ifdef MIB_POOL_DEBUG
+    pm.n_fields = L::F_COUNT;
+#endif
     const mib_sensor &sn = sc.d.sensor;
     const unsigned lane_id = threadIdx.x & 31;
     PoolQ<P, kAdjGroupMap> q;

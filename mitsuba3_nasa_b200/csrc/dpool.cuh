@@ -23,6 +23,7 @@
 // a warp sit in different branches of a 200 KB loop body.  Here a warp fetches one stage's code once
 // for 32 paths.
 #pragma once
+#include <cstdio>
 #include "dstage.cuh"
 
 #ifndef MIB_POOL_NT
@@ -164,10 +165,18 @@ template <int SPEC> __host__ __device__ constexpr size_t pool_smem_bytes() {
 // slot accessors
 template <int P> struct PoolMem {
     uint32_t *pw;
-    MIB_D float f(int field, int slot) const { return __uint_as_float(pw[field * P + slot]); }
-    MIB_D uint32_t u(int field, int slot) const { return pw[field * P + slot]; }
-    MIB_D void sf(int field, int slot, float v) const { pw[field * P + slot] = __float_as_uint(v); }
-    MIB_D void su(int field, int slot, uint32_t v) const { pw[field * P + slot] = v; }
+#ifdef MIB_POOL_DEBUG
+    int n_fields;
+    MIB_D void chk(int field, int slot) const {
+        if (field < 0 || field >= n_fields || slot < 0 || slot >= P) { printf("POOL OOB field %d slot %d (fields %d, P %d) cta %d thread %d\n", field, slot, n_fields, P, blockIdx.x, threadIdx.x); __trap(); }
+    }
+#else
+    MIB_D void chk(int, int) const { }
+#endif
+    MIB_D float f(int field, int slot) const { chk(field, slot); return __uint_as_float(pw[field * P + slot]); }
+    MIB_D uint32_t u(int field, int slot) const { chk(field, slot); return pw[field * P + slot]; }
+    MIB_D void sf(int field, int slot, float v) const { chk(field, slot); pw[field * P + slot] = __float_as_uint(v); }
+    MIB_D void su(int field, int slot, uint32_t v) const { chk(field, slot); pw[field * P + slot] = v; }
     MIB_D V3 v3f(int field, int slot) const { return v3(f(field, slot), f(field + 1, slot), f(field + 2, slot)); }
     MIB_D void sv3(int field, int slot, V3 v) const { sf(field, slot, v.x); sf(field + 1, slot, v.y); sf(field + 2, slot, v.z); }
     MIB_D void load_rng(int slot, Pcg32 &r) const {
@@ -226,6 +235,9 @@ template <int P, unsigned GROUPMAP> struct PoolQ {
     PoolShared *ps;
     unsigned *masks;
     unsigned lane_id, idle_spins, rot;
+#ifdef MIB_POOL_DEBUG
+    unsigned dbg_iters = 0;
+#endif
     uint64_t n_lanes;                                  // lanes of the launch
     unsigned long long *lane_counter;                  // next lane of the launch (global memory, zeroed by the host)
 
@@ -323,6 +335,15 @@ template <int P, unsigned GROUPMAP> struct PoolQ {
 
     // Hand the lane's slot to class `next` (< 0: the lane held no slot).
     MIB_D void push(int next, int slot) {
+#ifdef MIB_POOL_DEBUG
+        if (next >= 8 || slot < 0 || slot >= P) { printf("POOL bad push next %d slot %d\n", next, slot); __trap(); }
+        if (next >= 0) for (int c = 0; c < 8; ++c) if (masks[c * 32 + (slot & 31)] & (1u << ((unsigned) slot >> 5))) { printf("POOL slot %d pushed to %d while waiting in %d\n", slot, next, c); __trap(); }
+        if (++dbg_iters > 4000000u && lane_id == 0) {
+            printf("POOL stuck cta %d warp %d: retired %u of %d, group %u, waiting per class:", blockIdx.x, threadIdx.x >> 5, ps->retired, P, ps->group);
+            for (int c = 0; c < 8; ++c) { unsigned n = 0; for (int b = 0; b < 32; ++b) n += __popc(masks[c * 32 + b]); printf(" %u", n); }
+            printf("\n"); __trap();
+        }
+#endif
         __threadfence_block();
         if (next >= 0) atomicOr(&masks[next * 32 + (slot & 31)], 1u << ((unsigned) slot >> 5));
     }
@@ -531,6 +552,9 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
     static_assert(pool_smem_bytes<SPEC>() <= 232448, "pool does not fit the shared memory of sm_100");
     PoolMem<P> pm;
     pm.pw = reinterpret_cast<uint32_t *>(smem_raw + pool_state_offset(P));
+#ifdef MIB_POOL_DEBUG
+    pm.n_fields = L::F_COUNT;
+#endif
     const mib_sensor &sn = sc.d.sensor;
     const unsigned lane_id = threadIdx.x & 31;
 

@@ -149,7 +149,7 @@ static void commit(mib_scene *s) {
                 size_t n = (size_t) v->res[0] * v->res[1] * v->res[2] * v->channels;
                 if (v->buffer < 0 || v->buffer >= MIB_MAX_BUFFERS || !s->buf[v->buffer] || s->buf_n[v->buffer] < n)
                     throw std::runtime_error("gridvolume: data buffer missing or too small");
-                v->max_value = device_max(s, s->buf[v->buffer], n);
+                if (!v->fixed_max) v->max_value = device_max(s, s->buf[v->buffer], n);      // grid.cpp:296-297: a fixed max_value is kept
             } else {
                 v->max_value = v->value[0];
                 for (int c = 1; c < v->channels; ++c) v->max_value = fmaxf(v->max_value, v->value[c]);
@@ -301,17 +301,23 @@ static void launch_forward_pool(mib_scene *s, LaunchParams lp) {
     CK(cudaGetLastError());
 }
 
+// Forward kernel family for a scene (volpath / volpathaos): the path-pool kernel; MIB_FORWARD_KERNEL = thread | pool overrides
+// (A/B runs, tests).  Round 1 kept the one-thread-one-path kernel for homogeneous scenes (C2 433 vs 178 Msamples/s); with
+// bank-owned slots the pool kernel is ahead there too (profiles/r02_ab_pool.md).
+static bool forward_uses_pool(const mib_scene *s) {
+    const int integ = s->ds.d.integrator.type;
+    if (integ != MIB_INTEG_VOLPATH && integ != MIB_INTEG_VOLPATHAOS) return false;     // prb primal passes: per-thread kernel
+    const char *k = getenv("MIB_FORWARD_KERNEL");
+    bool pool = true;
+    if (k && strcmp(k, "thread") == 0) pool = false;
+    if (k && strcmp(k, "pool") == 0) pool = true;
+    return pool;
+}
+
 template <int SPEC, int MODE>
 static void launch_forward(mib_scene *s, const LaunchParams &lp) {
     if constexpr (MODE <= 1) {
-        // auto: the pool kernel when the scene has a heterogeneous medium (long walks of null collisions and shadow steps:
-        // C3 211 vs 126 Msamples/s), the one-thread-one-path kernel for homogeneous scenes (few, heavy events: C2 433 vs 178).
-        const char *k = getenv("MIB_FORWARD_KERNEL");
-        bool pool = false;
-        for (int m = 0; m < s->ds.d.n_media; ++m) pool = pool || s->ds.d.media[m].type != MIB_MEDIUM_HOMOGENEOUS;
-        if (k && strcmp(k, "thread") == 0) pool = false;
-        if (k && strcmp(k, "pool") == 0) pool = true;
-        if (pool) { launch_forward_pool<SPEC, MODE>(s, lp); return; }
+        if (forward_uses_pool(s)) { launch_forward_pool<SPEC, MODE>(s, lp); return; }
     }
     uint64_t lanes = lp.lane_end - lp.lane_begin;
     uint64_t threads = (lanes + lp.spt - 1) / lp.spt;
@@ -605,6 +611,7 @@ int mib_render_1(mib_scene *s, uint32_t seed, uint32_t spp, double *out4) { retu
 int mib_render_1_raw(mib_scene *s, uint32_t seed, uint32_t spp, double *out4) { return render_1_impl(s, seed, spp, out4, false); }
 
 int mib_counters_get(mib_scene *s, mib_counters *out) { *out = s->last; return 0; }
+int mib_scene_forward_kernel(mib_scene *s, int *is_pool) { *is_pool = forward_uses_pool(s) ? 1 : 0; return 0; }
 int mib_scene_stream(mib_scene *s, void **stream) { *stream = (void *) s->stream; return 0; }
 
 // A per-lane request must name lanes of the wavefront: (0, 0) is the "whole wavefront" sentinel of lane_range() and a

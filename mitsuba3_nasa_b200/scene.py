@@ -17,6 +17,22 @@ from .transforms import ScalarTransform4f, coordinate_system
 RAY_EPSILON = 1500.0 * 2.0 ** -24   # include/mitsuba/core/math.h:17-23
 
 
+# include/mitsuba/render/ior.h:22-48 (named indices of refraction)
+_IOR = {"vacuum": 1.0, "helium": 1.000036, "hydrogen": 1.000132, "air": 1.000277, "carbon dioxide": 1.00045, "water": 1.3330,
+        "acetone": 1.36, "ethanol": 1.361, "carbon tetrachloride": 1.461, "glycerol": 1.4729, "benzene": 1.501,
+        "silicone oil": 1.52045, "bromine": 1.661, "water ice": 1.31, "fused quartz": 1.458, "pyrex": 1.470,
+        "acrylic glass": 1.49, "polypropylene": 1.49, "bk7": 1.5046, "sodium chloride": 1.544, "amber": 1.55, "pet": 1.5750,
+        "diamond": 2.419}
+
+
+def _lookup_ior(v):
+    if isinstance(v, str):
+        if v.lower() not in _IOR:
+            raise PluginError("Unable to find an IOR value for \"%s\"! Valid choices are: %s" % (v, ", ".join(_IOR)))
+        return _IOR[v.lower()]
+    return float(v)
+
+
 class PluginError(RuntimeError):
     pass
 
@@ -40,7 +56,7 @@ class Plugin:
         'perspective': 'sensor', 'distant': 'sensor', 'radiancemeter': 'sensor',
         'constant': 'emitter', 'directional': 'emitter', 'area': 'emitter',
         'cube': 'shape', 'rectangle': 'shape', 'sphere': 'shape',
-        'null': 'bsdf', 'diffuse': 'bsdf',
+        'null': 'bsdf', 'diffuse': 'bsdf', 'dielectric': 'bsdf', 'roughdielectric': 'bsdf',
         'uniform': 'texture', 'srgb': 'texture', 'rgb': 'texture', 'd65': 'texture',
         'scene': 'scene',
     }
@@ -258,8 +274,10 @@ class Scene:
             corners = np.array([to_world @ [x, y, z] for x in (0, 1) for y in (0, 1) for z in (0, 1)])
             out.bbox_min[:] = corners.min(0).astype(np.float32).tolist()
             out.bbox_max[:] = corners.max(0).astype(np.float32).tolist()
-            if fixed_max is not None:
-                out.max_value = float(fixed_max)   # NOTE: commit() recomputes unless fixed; kept host-side
+            out.fixed_max = 0
+            if fixed_max is not None:                             # grid.cpp:296-297: m_fixed_max, used as the majorant as it is
+                out.max_value = float(fixed_max)
+                out.fixed_max = 1
             self.params[key + '.data'] = {'kind': 'buffer', 'slot': out.buffer}
             return
         # constvolume (explicit plugin, bare float or texture)
@@ -396,6 +414,42 @@ class Scene:
             out.type = A.BSDF_DIFFUSE
             out.reflectance[:] = self._color(pr.child('reflectance') or pr.get('reflectance', 0.5), key)
             self.params[key + '.reflectance.value'] = {'kind': 'bsdf_reflectance', 'bsdf': out}
+        elif b.type in ('dielectric', 'roughdielectric'):
+            # src/bsdfs/dielectric.cpp:210-222, roughdielectric.cpp:166-218 (the ocean interface of the AOS scenes)
+            int_ior = _lookup_ior(pr.get('int_ior', 'bk7'))
+            ext_ior = _lookup_ior(pr.get('ext_ior', 'air'))
+            if int_ior < 0 or ext_ior < 0 or (b.type == 'roughdielectric' and int_ior == ext_ior):
+                raise PluginError("The interior and exterior indices of refraction must be positive and differ!")
+            out.eta = float(np.float32(int_ior) / np.float32(ext_ior))
+            out.inv_eta = float(np.float32(ext_ior) / np.float32(int_ior)) if b.type == 'dielectric' else float(np.float32(1.0) / np.float32(out.eta))
+            for name in ('specular_reflectance', 'specular_transmittance'):
+                v = pr.child(name) or pr.get(name)
+                if v is not None and any(abs(c - 1.0) > 0 for c in self._color(v, key)):
+                    raise PluginError("%s: only %s = 1 is supported" % (b.type, name))
+            if b.type == 'dielectric':
+                out.type = A.BSDF_DIELECTRIC
+            else:
+                out.type = A.BSDF_ROUGHDIELECTRIC
+                distr = str(pr.get('distribution', 'beckmann')).lower()
+                if distr not in ('beckmann', 'ggx'):
+                    raise PluginError("Specified an invalid distribution \"%s\", must be \"beckmann\" or \"ggx\"!" % distr)
+                out.distribution = A.MICROFACET_BECKMANN if distr == 'beckmann' else A.MICROFACET_GGX
+                out.sample_visible = int(bool(pr.get('sample_visible', True)))
+                if not out.sample_visible:
+                    raise PluginError("roughdielectric: sample_visible = false is not implemented")
+                if pr.has('alpha_sq'):
+                    if pr.has('alpha'):
+                        raise PluginError("Microfacet model: please specify either 'alpha' or 'alpha_sq'.")
+                    au = av = float(np.sqrt(np.float32(pr.get('alpha_sq'))))
+                elif pr.has('alpha_u') or pr.has('alpha_v'):
+                    if not (pr.has('alpha_u') and pr.has('alpha_v')):
+                        raise PluginError("Microfacet model: both 'alpha_u' and 'alpha_v' must be specified.")
+                    if pr.has('alpha'):
+                        raise PluginError("Microfacet model: please specifyeither 'alpha' or 'alpha_u'/'alpha_v'.")
+                    au, av = float(pr.get('alpha_u')), float(pr.get('alpha_v'))
+                else:
+                    au = av = float(pr.get('alpha', 0.1))
+                out.alpha_u, out.alpha_v = au, av
         else:
             raise PluginError("unsupported BSDF '%s'" % b.type)
         pr.finish()

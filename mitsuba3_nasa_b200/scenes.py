@@ -66,6 +66,44 @@ def c2_rayleigh_slab(spp=4, integrator='volpathaos', max_depth=64, scale=1.0e4, 
     return d
 
 
+def aos_ocean(spp=4, integrator='volpathaos', max_depth=32, scale=100.0, rough=True, alpha=0.15, distribution='beckmann',
+              sun=True, ocean_albedo=0.6, view_zenith_deg=30.0):
+    """Coupled atmosphere-ocean system of the fork (the scenes volpathaos.cpp:232-290,312-337 is written
+    for): a Rayleigh atmosphere slab (z in [0, 1]) over a (rough) dielectric ocean surface at z = 0, a scattering ocean layer
+    (z in [-1, 0]) and a diffuse sea floor.  All interfaces are horizontal rectangles, as the integrator assumes."""
+    import math
+    cz = math.cos(math.radians(view_zenith_deg)); sz = math.sin(math.radians(view_zenith_deg))
+    surface = ({'type': 'roughdielectric', 'int_ior': 'water', 'ext_ior': 'air', 'distribution': distribution, 'alpha': alpha}
+               if rough else {'type': 'dielectric', 'int_ior': 'water', 'ext_ior': 'air'})
+    d = {
+        'type': 'scene',
+        'integrator': {'type': integrator, 'max_depth': max_depth, 'rr_depth': 5},
+        'sensor': {
+            'type': 'distant', 'direction': [sz, 0.0, -cz], 'target': [0.0, 0.0, 1.0],
+            'film': {'type': 'hdrfilm', 'width': 1, 'height': 1, 'rfilter': {'type': 'box'}},
+            'sampler': {'type': 'independent', 'sample_count': spp},
+        },
+        'atmosphere': {'type': 'homogeneous', 'sigma_t': 0.3, 'albedo': 1.0, 'has_spectral_extinction': False,
+                       'phase': {'type': 'rayleigh', 'depolarization': 0.03}},
+        'ocean': {'type': 'homogeneous', 'sigma_t': 1.5, 'albedo': ocean_albedo, 'has_spectral_extinction': False,
+                  'phase': {'type': 'hg', 'g': 0.8}},
+        'top': {'type': 'rectangle', 'bsdf': {'type': 'null'},
+                'to_world': T.translate([0.0, 0.0, 1.0]) @ T.scale([scale, scale, 1.0]),
+                'interior': {'type': 'ref', 'id': 'atmosphere'}},
+        'surface': {'type': 'rectangle', 'bsdf': surface,
+                    'to_world': T.scale([scale, scale, 1.0]),
+                    'interior': {'type': 'ref', 'id': 'ocean'}, 'exterior': {'type': 'ref', 'id': 'atmosphere'}},
+        'floor': {'type': 'rectangle', 'bsdf': {'type': 'diffuse', 'reflectance': 0.2},
+                  'to_world': T.translate([0.0, 0.0, -1.0]) @ T.scale([scale, scale, 1.0]),
+                  'exterior': {'type': 'ref', 'id': 'ocean'}},
+    }
+    if sun:
+        d['light'] = {'type': 'directional', 'direction': [-0.5, 0.2, -0.8], 'irradiance': 1.0}
+    else:
+        d['light'] = {'type': 'constant', 'radiance': 1.0}
+    return d
+
+
 def cloud_grid(n=256, seed=1234, blobs=64):
     """sum of Gaussian blobs clipped to [0,1], zeroed below 0.02; [z,y,x,1] fp32."""
     rng = np.random.default_rng(seed)

@@ -115,8 +115,7 @@ static inline Vec3 refract(Vec3 wi, Vec3 m, float cos_theta_t, float eta_ti) {
 // ---------------------------------------------------------------------------------------------------------------
 // SmoothDielectric::sample, src/bsdfs/dielectric.cpp:247-371, TransportMode::Radiance, specular_reflectance /
 // specular_transmittance as plain factors.  has_reflection / has_transmission mirror ctx.is_enabled (volpathaos' refractive
-// NEE asks for transmission only, volpathaos.cpp:320-326).  eval() and pdf() of this BSDF are zero (delta lobes,
-// dielectric.cpp:374-421 returns 0 for the smooth case).
+// NEE asks for transmission only, volpathaos.cpp:320-326).  pdf() of this BSDF is zero (:465-468); eval() is dielectric_eval below.
 // ---------------------------------------------------------------------------------------------------------------
 enum : uint32_t { BSDF_DeltaReflection = 0x20, BSDF_DeltaTransmission = 0x40 };
 
@@ -163,6 +162,34 @@ static inline DielectricSample dielectric_sample(Vec3 wi, float eta, float sampl
     }
     bs.weight = w; bs.weight_pol = W;
     return bs;
+}
+
+// SmoothDielectric::eval, src/bsdfs/dielectric.cpp:374-463.  In the fork this is NOT zero: it returns the weight of the lobe
+// that (wi, wo) falls into as if the delta function had been hit -- volpathaos' refractive NEE aims its shadow ray so that it
+// is (volpathaos.cpp:312-337, :423-431).  Quirks kept: no Fresnel factor and no division by a pdf in the unpolarized form
+// (`weight = 1` for every lane when both lobes are enabled, including lanes with cos_theta_i == 0); no special case for
+// wo parallel to the normal in the polarized form (normalize(0) -> NaN).
+static inline void dielectric_eval(Vec3 wi, Vec3 wo, float eta, float inv_eta, bool has_reflection, bool has_transmission, float *value, Mueller *value_pol) {
+    float cos_theta_i = wi.z, cos_theta_o = wo.z;
+    bool active = cos_theta_i != 0.f;
+    bool reflect = cos_theta_i * cos_theta_o > 0.f;
+    float inv_eta_side = cos_theta_i > 0.f ? inv_eta : eta;          // m_inv_eta = ext_ior / int_ior (:223)
+    float F = fresnel(cos_theta_i, eta).r;
+    bool eval_r = has_reflection && reflect && active, eval_t = has_transmission && !reflect && active;
+    // unpolarized (:442-454)
+    float w = 0.f;
+    if (has_reflection && has_transmission) w = 1.f;
+    else if (has_reflection || has_transmission) w = has_reflection ? F : 1.f - F;
+    // polarized (:409-440)
+    Vec3 wo_hat = wo, wi_hat = wi;
+    Mueller W;                                                        // zero
+    if (eval_r) W = specular_reflection(wo_hat.z, eta);
+    if (eval_t) W = specular_transmission(wo_hat.z, eta);
+    Vec3 n(0.f, 0.f, 1.f);
+    Vec3 s_axis_in = normalize(cross(n, -wo_hat)), s_axis_out = normalize(cross(n, wi_hat));
+    W = rotate_mueller_basis(W, -wo_hat, s_axis_in, stokes_basis(-wo_hat), wi_hat, s_axis_out, stokes_basis(wi_hat));
+    if (eval_t) { float fac = sqr(inv_eta_side); w *= fac; W = W * fac; }
+    *value = w; *value_pol = W;
 }
 
 } // namespace orc

@@ -248,58 +248,7 @@ static inline int si_emitter(const Scene &sc, const SurfaceInteraction &si) {
     return sc.d.environment;
 }
 
-// ------------------------------------------------------------------
-// BSDFs: null (null.cpp:36-86), diffuse (diffuse.cpp:101-160)
-// ------------------------------------------------------------------
-enum : uint32_t { BSDF_Null = 0x1, BSDF_DiffuseReflection = 0x2, BSDF_Smooth = 0x2 | 0x4 | 0x8 | 0x10,
-                  BSDF_Delta = 0x1 | 0x20 | 0x40 };
-static inline uint32_t bsdf_flags(const mib_bsdf &b) { return b.type == MIB_BSDF_NULL ? (uint32_t) BSDF_Null : (uint32_t) BSDF_DiffuseReflection; }
-
-template <typename Spec> struct BSDFSample { Vec3 wo; float pdf = 0.f, eta = 1.f; uint32_t sampled_type = 0; Spec value; };
-
-template <int SPEC> struct BSDF {
-    using Tr = SpecTraits<SPEC>;
-    using Spec = typename Tr::Spec;
-    using USpec = typename Tr::USpec;
-    static USpec reflectance(const mib_bsdf &b) { USpec r; for (int c = 0; c < Tr::NC; ++c) r.v[c] = b.reflectance[Tr::NC == 3 ? c : 0]; return r; }
-
-    static BSDFSample<Spec> sample(const mib_bsdf &b, const SurfaceInteraction &si, float /*s1*/, float s2x, float s2y) {
-        BSDFSample<Spec> bs;
-        bs.value = Spec(0.f);
-        if constexpr (Tr::POL) bs.value = Mueller();
-        if (b.type == MIB_BSDF_NULL) {
-            bs.wo = -si.wi; bs.sampled_type = BSDF_Null; bs.eta = 1.f; bs.pdf = 1.f;
-            bs.value = Spec(1.f); // identity in polarized modes (null.cpp:57-63)
-            return bs;
-        }
-        // JIT variants have no early exit: all fields are written for every lane and
-        // only the value is masked by (cos_theta_i > 0 && pdf > 0) (diffuse.cpp:101-126)
-        float cos_theta_i = si.wi.z;
-        bs.wo = square_to_cosine_hemisphere(s2x, s2y);
-        bs.pdf = InvPi * bs.wo.z;
-        bs.eta = 1.f;
-        bs.sampled_type = BSDF_DiffuseReflection;
-        bs.value = Depol<Spec, Tr::NC>::make((cos_theta_i > 0.f && bs.pdf > 0.f) ? reflectance(b) : USpec(0.f));
-        return bs;
-    }
-    static Spec eval(const mib_bsdf &b, const SurfaceInteraction &si, Vec3 wo) {
-        Spec zero = Depol<Spec, Tr::NC>::make(USpec(0.f));
-        if (b.type == MIB_BSDF_NULL) return zero;
-        float cos_theta_i = si.wi.z, cos_theta_o = wo.z;
-        if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) return zero;
-        USpec value = reflectance(b) * InvPi * cos_theta_o;
-        return Depol<Spec, Tr::NC>::make(value);
-    }
-    static float pdf(const mib_bsdf &b, const SurfaceInteraction &si, Vec3 wo) {
-        if (b.type == MIB_BSDF_NULL) return 0.f;
-        float cos_theta_i = si.wi.z, cos_theta_o = wo.z;
-        return (cos_theta_i > 0.f && cos_theta_o > 0.f) ? InvPi * wo.z : 0.f;
-    }
-    static Spec eval_null_transmission(const mib_bsdf &b) {
-        if (b.type == MIB_BSDF_NULL) return Spec(1.f);
-        return Depol<Spec, Tr::NC>::make(USpec(0.f)); // bsdf.h default: 0
-    }
-};
+// (BSDFs: obsdf.h)
 
 // ------------------------------------------------------------------
 // Sensors (perspective.cpp:201-235, distant.cpp:193-235)

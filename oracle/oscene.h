@@ -126,7 +126,7 @@ struct Scene {
             for (mib_volume *v : vols) {
                 if (v->type == MIB_VOLUME_GRID) {
                     size_t n = (size_t) v->res[0] * v->res[1] * v->res[2] * v->channels;
-                    v->max_value = grid_max(buffers[v->buffer], n);
+                    if (!v->fixed_max) v->max_value = grid_max(buffers[v->buffer], n);      // grid.cpp:296-297
                 } else {
                     v->max_value = v->value[0];
                     for (int c = 1; c < v->channels; ++c) v->max_value = maximum(v->max_value, v->value[c]);

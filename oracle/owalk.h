@@ -5,7 +5,7 @@
 // with the masked-lane semantics of the llvm_ad_* variants (a PCG32 stream only
 // advances when its lane's mask is set, ext/drjit/include/drjit/random.h:78-88).
 #pragma once
-#include "oplugins.h"
+#include "obsdf.h"
 
 namespace orc {
 
@@ -318,9 +318,10 @@ template <int SPEC> struct Walk {
     }
 
     // ------------------------------------------------------------------
-    // volpathaos.cpp:299-455 (no refractive BSDF in scope: refractive_bsdf == nullptr)
+    // volpathaos.cpp:299-455.  refractive_bsdf: index of the refractive BSDF between this interaction and the sensor
+    // (-1: none) -- then the shadow ray leaves in a direction that the interface refracts toward the emitter (:312-337).
     // ------------------------------------------------------------------
-    Spec sample_emitter_aos(Vec3 ref_p, Vec3 ref_n, int medium, uint32_t channel, DS *ds_out) {
+    Spec sample_emitter_aos(Vec3 ref_p, Vec3 ref_n, int medium, uint32_t channel, DS *ds_out, int refractive_bsdf = -1) {
         Spec transmittance = Spec(1.0f);
         float sx, sy; sampler.next_2d(&sx, &sy);
         DS ds;
@@ -330,6 +331,17 @@ template <int SPEC> struct Walk {
         bool active = true;
         if (ds.pdf == 0.f) emitter_val = zero_spec();
         active = active && ds.pdf != 0.f;
+        if (active && refractive_bsdf >= 0) {
+            // a direction that the interface (normal (0, 0, 1) in world space) refracts into emitter_d: the BSDF is sampled
+            // with wi = emitter_d and the transmission lobe only
+            SurfaceInteraction rsi;
+            rsi.wi = emitter_d;
+            float s1, s2x, s2y; draw_1d_2d(&s1, &s2x, &s2y);
+            BSDFSample<Spec> bs = Bs::sample(sc.d.bsdfs[refractive_bsdf], rsi, s1, s2x, s2y, 2);
+            bool valid_sample = bs.pdf > EpsilonF;                       // dr::Epsilon<Float> (:329)
+            if (!valid_sample) emitter_val = zero_spec();
+            else { ds.d = -bs.wo; emitter_val = mul_f(emitter_val, rcp(bs.pdf)); }     // Spectrum / Float = * rcp
+        }
         *ds_out = ds;
         if (!active) return emitter_val;
 
@@ -425,6 +437,7 @@ template <int SPEC> struct Walk {
         SurfaceInteraction si;
         bool needs_intersection = true;
         const uint32_t maxd = max_depth();
+        int refractive_bsdf = -1;            // volpathaos.cpp:80: the BSDF of the interface while the path is below it
 
         while (active) {
             active = active && any_neq0(unpol(throughput));
@@ -490,7 +503,7 @@ template <int SPEC> struct Walk {
                 specular_chain = !sample_emitters;
                 if (sample_emitters) {
                     DS ds;
-                    Spec emitted = sample_emitter_aos(mei.p, Vec3(0.f), medium, channel, &ds);
+                    Spec emitted = sample_emitter_aos(mei.p, Vec3(0.f), medium, channel, &ds, refractive_bsdf);
                     Vec3 wo = mei.sh_frame.to_local(ds.d);
                     PhaseEval<Spec> pe = Ph::eval_pdf(sc, phase, wo, mei.wi);
                     Spec phase_val = mei_to_world_mueller(mei, pe.val, -wo, mei.wi);
@@ -518,10 +531,11 @@ template <int SPEC> struct Walk {
                 bool active_e = (flags & BSDF_Smooth) && (depth + 1 < maxd);
                 if (active_e) {
                     bool diffuse = (flags & BSDF_DiffuseReflection) != 0;
-                    bool reflect_e = diffuse; // no refractive BSDFs in scope
+                    bool refractive = (flags & BSDF_Transmission) != 0;          // volpathaos.cpp:234-236
+                    bool reflect_e = diffuse || (refractive && si.wi.z > 0.f);
                     if (reflect_e) {
                         DS ds;
-                        Spec emitted = sample_emitter_aos(si.p, si.n, medium, channel, &ds);
+                        Spec emitted = sample_emitter_aos(si.p, si.n, medium, channel, &ds, refractive_bsdf);
                         Vec3 wo = si.sh_frame.to_local(ds.d);
                         Spec bsdf_val = Bs::eval(bsdf, si, wo);
                         bsdf_val = si_to_world_mueller(si, bsdf_val, -wo, si.wi);
@@ -535,8 +549,12 @@ template <int SPEC> struct Walk {
                 eta *= bs.eta;
                 bool non_null_bsdf = !(bs.sampled_type & BSDF_Null);
                 if (non_null_bsdf) depth += 1;
-                ray = spawn_ray(si.p, si.n, si.sh_frame.to_world(bs.wo));
+                Ray bsdf_ray = spawn_ray(si.p, si.n, si.sh_frame.to_world(bs.wo));
+                // "Refraction occurred, intentionally or not.  Assumes surface is aligned with x-y plane in world space" (:262-267)
+                bool refracted = non_null_bsdf && (ray.d.z * bsdf_ray.d.z > 0.f);
+                ray = bsdf_ray;
                 needs_intersection = true;
+                if (refracted) refractive_bsdf = refractive_bsdf < 0 ? sc.d.shapes[si.shape].bsdf : -1;     // :282-285
                 valid_ray = valid_ray || non_null_bsdf;
                 specular_chain = specular_chain || (non_null_bsdf && (bs.sampled_type & BSDF_Delta));
                 specular_chain = specular_chain && !(bs.sampled_type & BSDF_Smooth);

@@ -10,9 +10,10 @@
 //       SamplingIntegrator::render_sample (integrator.cpp:1139-1240) + sampler->advance() -- the loop body of
 //       render_block (integrator.cpp:1110-1123).  out.bin: float32 [line][sample][4] = the aovs render_sample
 //       fills: R,G,B,alpha|1 (rgb), I,-,-,- (mono), I,Q,U,V in the sensor frame (mono_polarized).
-//   ref_driver <variant> <scene.xml> render1 <seed> <spp> <out.bin>
-//       SamplingIntegrator::render_1 (integrator.cpp:399-743) with thread_count = 1: float32 [16] (Mueller matrix,
-//       row-major; Stokes vector = column 0) or [1] (mono).
+//   ref_driver <variant> <scene.xml> render1 <seed> <spp> <out.bin> [threads]
+//       SamplingIntegrator::render_1 (integrator.cpp:399-743), thread_count = threads (default 1): float32 [16] (Mueller
+//       matrix, row-major; Stokes vector = column 0) or [1] (mono).  Prints "RENDER1_SECONDS <s> THREADS <n>" to stderr: the
+//       wall time of the render_1 call alone (bench.py --impl reference times the reference's own CPU path with it).
 //   ref_driver <variant> <scene.xml> render <seed> <spp> <out.bin>
 //       Integrator::render with one thread, developed film: float32 [H][W][C].
 //
@@ -37,6 +38,7 @@
 #include <mitsuba/render/sampler.h>
 #include <mitsuba/render/scene.h>
 #include <mitsuba/render/sensor.h>
+#include <chrono>
 #include <cstdio>
 #include <fstream>
 #include <vector>
@@ -94,7 +96,14 @@ void run(Object *scene_, int argc, char **argv) {
             Throw("render_1 does not support rgb variants");
         } else {
             const uint32_t seed = (uint32_t) strtoul(argv[4], nullptr, 10), spp = (uint32_t) strtoul(argv[5], nullptr, 10);
-            Spectrum s = integrator->render_1(scene, sensor, seed, spp, false, true, 1);
+            // optional 7th argument: host threads (default 1: the fixtures need one stream); with threads the reference splits the
+            // samples into one range per thread (integrator.cpp:510-551).  The wall time of the call goes to stderr for bench.py.
+            const size_t threads = argc > 7 ? (size_t) strtoul(argv[7], nullptr, 10) : 1;
+            if (threads > 1) Thread::set_thread_count(threads);
+            auto t0 = std::chrono::steady_clock::now();
+            Spectrum s = integrator->render_1(scene, sensor, seed, spp, false, true, threads);
+            fprintf(stderr, "RENDER1_SECONDS %.6f THREADS %zu\n",
+                    std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(), threads);
             std::vector<float> out;
             if constexpr (is_polarized_v<Spectrum>) {
                 for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) out.push_back((float) s(r, c)[0]);

@@ -105,6 +105,13 @@ def cases():
     d['floor'] = {'type': 'rectangle', 'to_world': T.translate([0, 0, -1.5]) @ T.scale(4.0),
                   'bsdf': {'type': 'diffuse', 'reflectance': {'type': 'rgb', 'value': [0.5, 0.6, 0.7]}}}
     c['area_emitter'] = dict(variant='scalar_rgb', scene=d, spp=8, seed=0, kind='samples')
+    # the coupled atmosphere-ocean system: rough / smooth dielectric ocean surface under a Rayleigh atmosphere,
+    # scattering ocean below, refractive NEE (volpathaos.cpp:232-290,312-337)
+    c['ocean_rough_pol'] = dict(variant='scalar_mono_polarized', scene=scenes.aos_ocean(rough=True), spp=1024, seed=3, kind='samples')
+    c['ocean_rough_ggx_mono'] = dict(variant='scalar_mono', scene=scenes.aos_ocean(rough=True, distribution='ggx', alpha=0.3), spp=512, seed=5, kind='samples')
+    c['ocean_smooth_pol'] = dict(variant='scalar_mono_polarized', scene=scenes.aos_ocean(rough=False), spp=1024, seed=3, kind='samples')
+    c['ocean_smooth_mono'] = dict(variant='scalar_mono', scene=scenes.aos_ocean(rough=False, view_zenith_deg=55.0), spp=512, seed=1, kind='samples')
+    c['ocean_rough_pol_render1'] = dict(variant='scalar_mono_polarized', scene=scenes.aos_ocean(rough=True), spp=20000, seed=2, kind='render1')
     # radiancemeter looking through the cube
     d = scenes.c1_homogeneous_cube(res=1, spp=64, max_depth=16)
     d['sensor'] = {'type': 'radiancemeter', 'origin': [0.2, 0.1, 4.0], 'direction': [-0.05, 0.0, -1.0],
