@@ -38,7 +38,7 @@ template <int SPEC> struct APoolL {
 constexpr uint32_t FL_BACKWARD = 0x4;                  // (the forward kernel's FL_SPEC_CHAIN bit: prb walks have no specular chain)
 
 template <int SPEC> __host__ __device__ constexpr size_t apool_smem_bytes() {
-    return pool_state_offset(APoolL<SPEC>::P) + (size_t) APoolL<SPEC>::F_COUNT * APoolL<SPEC>::P * sizeof(uint32_t);
+    return pool_state_offset(APoolL<SPEC>::P) + (size_t) APoolL<SPEC>::F_COUNT * APoolL<SPEC>::P * sizeof(uint32_t) + kPoolDebugBytes;
 }
 
 template <int SPEC>
@@ -59,6 +59,9 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
     const unsigned lane_id = threadIdx.x & 31;
     PoolQ<P, kAdjGroupMap> q;
     q.init(smem_raw, lp.lane_end - lp.lane_begin, lp.counters + 6, C_START);
+#ifdef MIB_POOL_DEBUG
+    q.dbg_init(smem_raw + pool_state_offset(P) + (size_t) L::F_COUNT * P * sizeof(uint32_t), C_START);
+#endif
     PoolShared *ps = q.ps;
     for (int s = threadIdx.x; s < P; s += blockDim.x) { pm.su(L::F_LANE, s, kNoLane); pm.su(L::F_FLAGS, s, 0u); }
     __syncthreads();
@@ -116,7 +119,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
             bool fresh = false;
             if (need) {
                 if (jn != kNoLane) { j = jn; fresh = true; }
-                else { pm.su(L::F_LANE, slot, kNoLane); q.retire(); }
+                else { pm.su(L::F_LANE, slot, kNoLane); q.retire(slot); }
             }
             if (replay || fresh) {
                 const uint64_t lane = stripe_map(lp, lp.lane_begin + q.lane_of(j));

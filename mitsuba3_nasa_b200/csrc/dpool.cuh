@@ -75,8 +75,13 @@ constexpr unsigned kRingEmpty = 0xffffu;
 #endif
 #if MIB_POOL_BOS
 constexpr int kPoolHeaderBytes = 64 + 8 * 32 * 4;      // PoolShared + masks[8][32]
+#ifdef MIB_POOL_DEBUG
+constexpr int kPoolDebugBytes = 2048;                  // MIB_POOL_DEBUG: one state byte + one class byte per slot, behind the state words
+#else
+constexpr int kPoolDebugBytes = 0;
+#endif
 __host__ __device__ constexpr int pool_slots_for(int f_count) {
-    int p = ((232448 - kPoolHeaderBytes) / (f_count * 4)) / 32 * 32;
+    int p = ((232448 - kPoolHeaderBytes - kPoolDebugBytes) / (f_count * 4)) / 32 * 32;
     return p > 1024 ? 1024 : p;                        // at most 32 slots per bank (one mask word)
 }
 #else
@@ -159,7 +164,7 @@ __host__ __device__ constexpr size_t pool_ring_offset() { return (sizeof(PoolSha
 __host__ __device__ constexpr size_t pool_state_offset(int P) { return (pool_ring_offset() + (size_t) kPoolRings * (P + kPoolRingSlack) * sizeof(uint16_t) + 15) & ~(size_t) 15; }
 #endif
 template <int SPEC> __host__ __device__ constexpr size_t pool_smem_bytes() {
-    return pool_state_offset(PoolL<SPEC>::P) + (size_t) PoolL<SPEC>::F_COUNT * PoolL<SPEC>::P * sizeof(uint32_t);
+    return pool_state_offset(PoolL<SPEC>::P) + (size_t) PoolL<SPEC>::F_COUNT * PoolL<SPEC>::P * sizeof(uint32_t) + kPoolDebugBytes;
 }
 
 // slot accessors
@@ -223,6 +228,12 @@ template <int P> struct PoolMem {
 // CTAs work on neighbouring pixels (grid and gradient lines are shared through the L2).  Per-lane seeds depend only on the
 // lane index (integrator.cpp:323-340), so the result does not depend on which warp walked a lane.
 // ---------------------------------------------------------------------------------------------
+#ifndef MIB_POOL_DEBUG_SPINS
+#define MIB_POOL_DEBUG_SPINS 30000000u     // MIB_POOL_DEBUG: claim-loop passes of one warp before the kernel prints its state and traps
+#endif
+#ifndef MIB_POOL_DEBUG_ITERS
+#define MIB_POOL_DEBUG_ITERS 3000000u      //                 batches of one warp
+#endif
 #ifndef MIB_POOL_FULL
 #define MIB_POOL_FULL 32
 #endif
@@ -236,11 +247,23 @@ template <int P, unsigned GROUPMAP> struct PoolQ {
     unsigned *masks;
     unsigned lane_id, idle_spins, rot;
 #ifdef MIB_POOL_DEBUG
-    unsigned dbg_iters = 0;
+    unsigned dbg_iters = 0, dbg_spins = 0;
 #endif
     uint64_t n_lanes;                                  // lanes of the launch
     unsigned long long *lane_counter;                  // next lane of the launch (global memory, zeroed by the host)
 
+#ifdef MIB_POOL_DEBUG
+    volatile unsigned char *dbg_state, *dbg_class;     // per slot: 0 waiting / 1 in flight / 2 retired; class it waits in / runs
+    MIB_D void dbg_init(unsigned char *end_of_state, int start_class) {
+        dbg_state = end_of_state; dbg_class = end_of_state + 1024;
+        for (int i = threadIdx.x; i < P; i += blockDim.x) { dbg_state[i] = 0; dbg_class[i] = (unsigned char) start_class; }
+    }
+    MIB_D void dbg_fail(const char *what, int slot, int cls) {
+        printf("POOL %s: slot %d class %d (recorded state %d class %d) cta %d warp %d lane %d iters %u\n", what, slot, cls,
+               (int) dbg_state[slot], (int) dbg_class[slot], blockIdx.x, threadIdx.x >> 5, threadIdx.x & 31, dbg_iters);
+        __trap();
+    }
+#endif
     MIB_D void init(unsigned char *smem_raw, uint64_t n, unsigned long long *counter, int start_class) {
         ps = reinterpret_cast<PoolShared *>(smem_raw);
         masks = reinterpret_cast<unsigned *>(smem_raw + pool_ring_offset());
@@ -259,9 +282,24 @@ template <int P, unsigned GROUPMAP> struct PoolQ {
     MIB_D bool claim(int &cls, bool &has, int &slot) {
         volatile unsigned *vm = masks;
         while (true) {
+#ifdef MIB_POOL_DEBUG
+            if (++dbg_spins > MIB_POOL_DEBUG_SPINS) {
+                if (lane_id == 0) {
+                    printf("POOL claim spins cta %d warp %d: retired %u of %d, error %u, group %u, iters %u, waiting per class:", blockIdx.x, threadIdx.x >> 5, ps->retired, P, ps->error, ps->group, dbg_iters);
+                    for (int c = 0; c < 8; ++c) { unsigned n = 0; for (int b = 0; b < 32; ++b) n += __popc(masks[c * 32 + b]); printf(" %u", n); }
+                    printf("\n");
+                    int shown = 0;
+                    for (int i = 0; i < P && shown < 12; ++i)
+                        if (dbg_state[i] == 1) { printf("  slot %d in flight since class %d\n", i, (int) dbg_class[i]); ++shown; }
+                }
+                __trap();
+            }
+#endif
             unsigned kin = 0, kout = 0;
 #if MIB_POOL_GROUPS
-            const unsigned g = *(volatile unsigned *) &ps->group;
+            // lane 0's view of the group for the whole warp: other warps change ps->group while this one reads it, and the
+            // class chosen below must be the same for all 32 lanes
+            const unsigned g = __shfl_sync(FULL, *(volatile unsigned *) &ps->group, 0);
 #else
             const unsigned g = 0;
 #endif
@@ -310,6 +348,13 @@ template <int P, unsigned GROUPMAP> struct PoolQ {
                     }
                 }
 #endif
+#ifdef MIB_POOL_DEBUG
+                if (ok) {
+                    if (dbg_state[s] != 0) dbg_fail("claimed a slot that is not waiting", s, best);
+                    if (dbg_class[s] != best) dbg_fail("claimed a slot in the wrong class", s, best);
+                    dbg_state[s] = 1;
+                }
+#endif
                 if (__any_sync(FULL, ok)) {
                     if (flip && lane_id == 0) ps->group = (GROUPMAP >> (4u * (unsigned) best)) & 15u;
                     ++rot;
@@ -338,15 +383,30 @@ template <int P, unsigned GROUPMAP> struct PoolQ {
 #ifdef MIB_POOL_DEBUG
         if (next >= 8 || slot < 0 || slot >= P) { printf("POOL bad push next %d slot %d\n", next, slot); __trap(); }
         if (next >= 0) for (int c = 0; c < 8; ++c) if (masks[c * 32 + (slot & 31)] & (1u << ((unsigned) slot >> 5))) { printf("POOL slot %d pushed to %d while waiting in %d\n", slot, next, c); __trap(); }
-        if (++dbg_iters > 4000000u && lane_id == 0) {
+        if (++dbg_iters > MIB_POOL_DEBUG_ITERS && lane_id == 0) {
             printf("POOL stuck cta %d warp %d: retired %u of %d, group %u, waiting per class:", blockIdx.x, threadIdx.x >> 5, ps->retired, P, ps->group);
             for (int c = 0; c < 8; ++c) { unsigned n = 0; for (int b = 0; b < 32; ++b) n += __popc(masks[c * 32 + b]); printf(" %u", n); }
             printf("\n"); __trap();
         }
 #endif
+#ifdef MIB_POOL_DEBUG
+        if (next >= 0) {
+            if (dbg_state[slot] != 1) dbg_fail("pushed a slot that is not in flight", slot, next);
+            dbg_class[slot] = (unsigned char) next; dbg_state[slot] = 0;
+        }
+#endif
         __threadfence_block();
         if (next >= 0) atomicOr(&masks[next * 32 + (slot & 31)], 1u << ((unsigned) slot >> 5));
     }
+#ifdef MIB_POOL_DEBUG
+    MIB_D void retire(int slot) {
+        if (dbg_state[slot] != 1) dbg_fail("retired a slot that is not in flight", slot, -1);
+        dbg_state[slot] = 2;
+        atomicAdd(&ps->retired, 1u);
+    }
+#else
+    MIB_D void retire(int) { atomicAdd(&ps->retired, 1u); }
+#endif
 
     // START: the lanes with `need` take the next lanes of the launch (one atomic per warp on the launch's lane counter);
     // kNoLane when the launch has run out of lanes.  Consecutive lanes are samples of one pixel, so a warp's batch starts
@@ -361,7 +421,6 @@ template <int P, unsigned GROUPMAP> struct PoolQ {
         return (need && v < n_lanes) ? (uint32_t) v : kNoLane;
     }
     MIB_D uint64_t lane_of(uint32_t j) const { return j; }          // index within the launch -> (virtual) lane of the rank
-    MIB_D void retire() { atomicAdd(&ps->retired, 1u); }
 };
 #else
 // ---------------------------------------------------------------------------------------------
@@ -537,7 +596,7 @@ template <int P, unsigned GROUPMAP> struct PoolQ {
         return jn < ps->total_local ? jn : kNoLane;
     }
     MIB_D uint64_t lane_of(uint32_t j) const { return pool_lane(j, blockIdx.x, gridDim.x); }
-    MIB_D void retire() { atomicAdd(&ps->retired, 1u); }
+    MIB_D void retire(int) { atomicAdd(&ps->retired, 1u); }
 };
 #endif
 
@@ -560,6 +619,9 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
 
     PoolQ<P, kFwdGroupMap> q;
     q.init(smem_raw, lp.lane_end - lp.lane_begin, lp.counters + 6, C_START);
+#ifdef MIB_POOL_DEBUG
+    q.dbg_init(smem_raw + pool_state_offset(P) + (size_t) L::F_COUNT * P * sizeof(uint32_t), C_START);
+#endif
     PoolShared *ps = q.ps;
     for (int s = threadIdx.x; s < P; s += blockDim.x) pm.su(L::F_LANE, s, kNoLane);
     __syncthreads();
@@ -665,7 +727,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                     next = C_MAIN;
                 } else {
                     pm.su(L::F_LANE, slot, kNoLane);
-                    q.retire();
+                    q.retire(slot);
                 }
             }
             break;
