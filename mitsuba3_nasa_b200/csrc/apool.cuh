@@ -41,7 +41,7 @@ template <int SPEC> __host__ __device__ constexpr size_t apool_smem_bytes() {
     return pool_state_offset(APoolL<SPEC>::P) + (size_t) APoolL<SPEC>::F_COUNT * APoolL<SPEC>::P * sizeof(uint32_t) + kPoolDebugBytes;
 }
 
-template <int SPEC>
+template <int SPEC, int V>
 __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_constant__ LaunchParams lp, const __grid_constant__ AdjParams ap) {
     using L = APoolL<SPEC>;
     constexpr int NR = ST<SPEC>::NR, NC = ST<SPEC>::NC, NT = ST<SPEC>::NT, Cd = SPEC == MIB_SPEC_MONO ? 1 : (SPEC == MIB_SPEC_RGB ? 3 : 4);
@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
                         for (int c = 0; c < Cd; ++c) dl[c] = ap.grad1[c] * nf;
                     } else {
                         int ix = (int) floorf(sx) - sn.crop_offset_x, iy = (int) floorf(sy) - sn.crop_offset_y;
-                        if (sn.rfilter != MIB_RFILTER_BOX) {
+                        if ((MIB_FT(FT_FILTER) && sn.rfilter != MIB_RFILTER_BOX)) {
                             // adjoint of splat + weight division (hdrfilm.cpp:304-418): dL_c = sum_p grad[p,c] / W[p] * w_p
                             filter_footprint(lp.spp, sx, sy, [&](size_t pixel, float w) {
                                 float W = __ldg(sc.weight_film + pixel), dv = W == 0.f ? 1.f : W;
@@ -388,7 +388,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
     if (threadIdx.x == 0 && ps->error) atomicExch((unsigned int *) (lp.counters + 7), ps->error);
 }
 
-template <int SPEC> void launch_k_adjoint_pool(const DScene &scene, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, unsigned threads, cudaStream_t st);
+template <int SPEC, int V> void launch_k_adjoint_pool(const DScene &scene, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, unsigned threads, cudaStream_t st);
 template <int SPEC> int adjoint_pool_slots();
 
 } // namespace mib

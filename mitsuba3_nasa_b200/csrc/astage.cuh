@@ -160,7 +160,7 @@ MIB_D void prb_nee_step(Pcg32 &rng, Counters &cnt, Sink &sink, uint32_t channel,
     }
 #pragma unroll
     for (int c = 0; c < NC; ++c) tr[c] *= trm[c];
-    if (sc.super_res > 0 && active_medium) {                          // fast mode: roulette on a small transmittance (dscene.cuh);
+    if (MIB_FT(FT_FAST) && sc.super_res > 0 && active_medium) {       // fast mode: roulette on a small transmittance (dscene.cuh);
         float tm = fabsf(tr[0]);                                      // the gradient walk replays the same decisions
 #pragma unroll
         for (int c = 1; c < NC; ++c) tm = fmaxf(tm, fabsf(tr[c]));

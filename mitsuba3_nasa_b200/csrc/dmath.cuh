@@ -7,6 +7,21 @@
 // decision (real vs. null collision, hit vs. miss) is taken on the same float
 // as in the reference.
 #pragma once
+// ---------------------------------------------------------------------------------------------
+// Scene-specialised instantiations.  Every walk kernel is compiled once with all features (MIB_FEAT = all bits) and again
+// for the feature sets that the BASELINE scenes use; ft(F) is a compile-time constant, so `if (ft(F) && ...)` removes the
+// code of a plugin the scene does not hold.  The host picks the most specific instantiation whose set covers the scene
+// (mib_api.cu scene_features / pick_variant).  Fewer live branches and a smaller hot loop is the point: the walk kernels are
+// bound by instruction supply, not by arithmetic or memory.
+// ---------------------------------------------------------------------------------------------
+#ifndef MIB_FEAT
+#define MIB_FEAT 0xffffffffu
+#endif
+enum : unsigned {
+    FT_HOMOG = 1u, FT_GRID = 2u, FT_FAST = 4u, FT_AREA = 8u, FT_TAB = 16u, FT_ANALYTIC = 32u, FT_SPHERE = 64u, FT_CUBE = 128u,
+    FT_RECT = 256u, FT_FILTER = 512u, FT_SPECEXT = 1024u, FT_ALL = 0xffffffffu
+};
+#define MIB_FT(f) (((MIB_FEAT) & (f)) != 0u)
 #include <cuda_runtime.h>
 #include <stdint.h>
 

@@ -65,7 +65,10 @@ MIB_DH float phase_eval(int idx, V3 wo, float *W) {
     const mib_phase &p = sc.d.phases[idx];
     const V3 wi = v3(0.f, 0.f, -1.f);
     float val, pdf;
-    switch (p.type) {
+    int ptype = p.type;
+    if (!MIB_FT(FT_TAB) && (ptype == MIB_PHASE_TABPHASE || ptype == MIB_PHASE_TABPHASE_POLARIZED)) ptype = MIB_PHASE_ISOTROPIC;   // not in this instantiation
+    if (!MIB_FT(FT_ANALYTIC) && ptype != MIB_PHASE_TABPHASE) ptype = MIB_PHASE_TABPHASE_POLARIZED;
+    switch (ptype) {
         case MIB_PHASE_ISOTROPIC: val = pdf = kInvFourPi; break;                        // isotropic.cpp:51-58
         case MIB_PHASE_HG: val = pdf = eval_hg(p.g, dot(wo, wi)); break;                 // hg.cpp:96-104
         case MIB_PHASE_TABPHASE: {                                                       // tabphase.cpp:121-133
@@ -115,7 +118,10 @@ MIB_DH float phase_sample(int idx, float s2x, float s2y, V3 &wo, float *W) {
     constexpr int NC = ST<SPEC>::NC;
     const mib_phase &p = sc.d.phases[idx];
     float pdf, ct, sp, cp;
-    switch (p.type) {
+    int ptype = p.type;
+    if (!MIB_FT(FT_TAB) && (ptype == MIB_PHASE_TABPHASE || ptype == MIB_PHASE_TABPHASE_POLARIZED)) ptype = MIB_PHASE_ISOTROPIC;   // not in this instantiation
+    if (!MIB_FT(FT_ANALYTIC) && ptype != MIB_PHASE_TABPHASE) ptype = MIB_PHASE_TABPHASE_POLARIZED;
+    switch (ptype) {
         case MIB_PHASE_ISOTROPIC:                                                        // isotropic.cpp:40-49
             wo = square_to_uniform_sphere(s2x, s2y);
             pdf = kInvFourPi;
@@ -214,7 +220,7 @@ MIB_DH void sample_emitter_direction(V3 ref_p, float sx, float sy, DirSample<NC>
 #pragma unroll
         for (int c2 = 0; c2 < NC; ++c2) spec[c2] = e.radiance[NC == 3 ? c2 : 0];
     }
-    else if (e.type == MIB_EMITTER_AREA) {
+    else if (MIB_FT(FT_AREA) && e.type == MIB_EMITTER_AREA) {
         // area.cpp:119-143 (uniform radiance) -> Shape::sample_direction (shape.cpp:358-375) -> Rectangle::sample_position
         // (rectangle.cpp:166-180); scene.py admits area emitters on rectangles only
         const mib_shape &sh = sc.d.shapes[e.shape];
@@ -245,7 +251,7 @@ MIB_D float pdf_emitter_direction(int emitter, V3 ref_p, V3 si_p, V3 si_n) {
     float pmf = sc.d.n_emitters > 1 ? rcp_((float) sc.d.n_emitters) : 1.f;
     float pdf = 0.f;
     if (e.type == MIB_EMITTER_CONSTANT) pdf = kInvFourPi;
-    else if (e.type == MIB_EMITTER_AREA) {
+    else if (MIB_FT(FT_AREA) && e.type == MIB_EMITTER_AREA) {
         V3 rel = si_p - ref_p;
         float dist = norm(rel);
         V3 d = rel * rcp_(dist);
@@ -257,7 +263,7 @@ MIB_D float pdf_emitter_direction(int emitter, V3 ref_p, V3 si_p, V3 si_n) {
 }
 // Emitter::eval at a hit, channel r: the area light is one-sided (area.cpp:83-90)
 template <int NC> MIB_D float emitter_eval(const mib_emitter &e, int r, float cos_theta_wi) {
-    if (e.type == MIB_EMITTER_AREA && !(cos_theta_wi > 0.f)) return 0.f;
+    if (MIB_FT(FT_AREA) && e.type == MIB_EMITTER_AREA && !(cos_theta_wi > 0.f)) return 0.f;
     return e.radiance[NC == 3 ? r : 0];
 }
 MIB_D int si_emitter(const SurfIt &si) {

@@ -238,7 +238,7 @@ template <int P> struct PoolMem {
 #define MIB_POOL_FULL 32
 #endif
 #ifndef MIB_POOL_STEAL
-#define MIB_POOL_STEAL 4       // banks a lane may look into beyond its own when that has nothing in the chosen class (0: none)
+#define MIB_POOL_STEAL 0       // banks a lane may look into beyond its own when that has nothing in the chosen class (0: none)
 #endif
 constexpr unsigned kPoolFull = MIB_POOL_FULL;     // banks with a waiting slot that count as a full batch
 template <int P, unsigned GROUPMAP> struct PoolQ {
@@ -600,7 +600,8 @@ template <int P, unsigned GROUPMAP> struct PoolQ {
 };
 #endif
 
-template <int SPEC, int MODE>
+// V: id of the scene-specialised instantiation (inst.cu compiles one per MIB_FEAT set; 0 = every feature)
+template <int SPEC, int MODE, int V>
 __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_constant__ LaunchParams lp) {
     using L = PoolL<SPEC>;
     constexpr int C = RawChannels<SPEC>::C, NR = ST<SPEC>::NR, NC = ST<SPEC>::NC, NT = ST<SPEC>::NT;
@@ -663,7 +664,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
             for (int c = 0; c < C; ++c) lp.per_sample[(lane - lp.lane_begin) * C + c] = aov[c];
             return;
         }
-        if (lp.mode == 0 && sn.rfilter != MIB_RFILTER_BOX) {
+        if (lp.mode == 0 && (MIB_FT(FT_FILTER) && sn.rfilter != MIB_RFILTER_BOX)) {
             filter_footprint(lp.spp, sx, sy, [&](size_t pixel, float w) {
 #pragma unroll
                 for (int c = 0; c < C; ++c) atomicAdd(lp.film + pixel * C + c, aov[c] * w);
@@ -717,7 +718,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                                                 ((uint32_t) (st.medium + 1) << 8));
                     pm.sf(L::F_ETA, slot, 1.f);
                     pm.sf(L::F_LASTPDF, slot, 1.f);
-                    if (sc.has_area_emitter) pm.sv3(L::F_LSP, slot, v3(0.f));
+                    if ((MIB_FT(FT_AREA) && sc.has_area_emitter)) pm.sv3(L::F_LSP, slot, v3(0.f));
                     pm.sv3(L::F_RAY, slot, ray0.o); pm.sv3(L::F_RAY + 3, slot, ray0.d); pm.sf(L::F_RAY + 6, slot, ray0.maxt);
                     pm.store_si(L::F_SI, slot, st.si);
 #pragma unroll
@@ -748,7 +749,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                 st.ray.o = pm.v3f(L::F_RAY, slot); st.ray.d = pm.v3f(L::F_RAY + 3, slot); st.ray.maxt = pm.f(L::F_RAY + 6, slot);
                 pm.load_si(L::F_SI, slot, st.si);
                 if (!st.needs_intersection && st.si.shape >= 0) si_finalize(st.ray.d, st.si);
-                st.last_p = sc.has_area_emitter ? pm.v3f(L::F_LSP, slot) : v3(0.f);
+                st.last_p = (MIB_FT(FT_AREA) && sc.has_area_emitter) ? pm.v3f(L::F_LSP, slot) : v3(0.f);
 #pragma unroll
                 for (int i = 0; i < NT; ++i) st.T[i] = pm.f(L::F_T + i, slot);
 #pragma unroll
@@ -923,7 +924,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                 st.specular_chain = fl & FL_SPEC_CHAIN;
                 st.depth = pm.u(L::F_DEPTH, slot);
                 st.last_pdf = pm.f(L::F_LASTPDF, slot);
-                st.last_p = sc.has_area_emitter ? pm.v3f(L::F_LSP, slot) : v3(0.f);
+                st.last_p = (MIB_FT(FT_AREA) && sc.has_area_emitter) ? pm.v3f(L::F_LSP, slot) : v3(0.f);
                 st.ray.o = pm.v3f(L::F_RAY, slot); st.ray.d = pm.v3f(L::F_RAY + 3, slot); st.ray.maxt = pm.f(L::F_RAY + 6, slot);
                 pm.load_si(L::F_SI, slot, st.si);
                 si_finalize(st.ray.d, st.si);
@@ -935,7 +936,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
                 for (int i = 0; i < NT; ++i) pm.sf(L::F_T + i, slot, st.T[i]);
                 pm.sv3(L::F_RAY, slot, st.ray.o); pm.sv3(L::F_RAY + 3, slot, st.ray.d); pm.sf(L::F_RAY + 6, slot, st.ray.maxt);
                 pm.sf(L::F_LASTPDF, slot, st.last_pdf);
-                if (sc.has_area_emitter) pm.sv3(L::F_LSP, slot, st.last_p);
+                if ((MIB_FT(FT_AREA) && sc.has_area_emitter)) pm.sv3(L::F_LSP, slot, st.last_p);
                 pm.su(L::F_DEPTH, slot, st.depth);
                 pm.su(L::F_FLAGS, slot, (fl & ~(FL_NEEDS_INT | FL_SPEC_CHAIN | 0xff00u)) | FL_NEEDS_INT |
                                             (st.specular_chain ? FL_SPEC_CHAIN : 0u) | ((uint32_t) (st.medium + 1) << 8));
@@ -966,7 +967,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_forward_pool(const __grid_co
     if (threadIdx.x == 0 && ps->error) atomicExch((unsigned int *) (lp.counters + 7), ps->error);
 }
 
-template <int SPEC, int MODE> void launch_k_forward_pool(const DScene &scene, const LaunchParams &lp, unsigned blocks, unsigned threads, cudaStream_t st);
+template <int SPEC, int MODE, int V> void launch_k_forward_pool(const DScene &scene, const LaunchParams &lp, unsigned blocks, unsigned threads, cudaStream_t st);
 template <int SPEC, int MODE> int pool_slots();   // paths resident per CTA (PoolL<SPEC>::P)
 
 } // namespace mib

@@ -85,12 +85,15 @@ MIB_D float intersect_shape(int idx, const Ray &ray, int &face) {
     const mib_shape &s = sc.d.shapes[idx];
     V3 o = xform_point_affine(s.to_object, ray.o), d = xform_vector(s.to_object, ray.d);
     face = 0;
-    if (s.type == MIB_SHAPE_RECTANGLE) {
+    // (shape kinds outside this instantiation's feature set never occur: the host picks a covering instantiation)
+    const bool is_rect = MIB_FT(FT_RECT) && (s.type == MIB_SHAPE_RECTANGLE || !(MIB_FT(FT_CUBE) || MIB_FT(FT_SPHERE)));
+    const bool is_cube = MIB_FT(FT_CUBE) && (s.type == MIB_SHAPE_CUBE || !MIB_FT(FT_SPHERE));
+    if (is_rect) {
         float t = div_(-o.z, d.z);
         float lx = fma_(d.x, t, o.x), ly = fma_(d.y, t, o.y);
         bool hit = t >= 0.f && t <= ray.maxt && fabsf(lx) <= 1.f && fabsf(ly) <= 1.f;
         return hit ? t : inf_f();
-    } else if (s.type == MIB_SHAPE_CUBE) {
+    } else if (is_cube) {
         float tn = -inf_f(), tf = inf_f();
         int fn = 0, ff = 0;
 #pragma unroll
@@ -132,7 +135,7 @@ MIB_D void frame_from_normal(V3 n, V3 dp_du, V3 &fs, V3 &ft) {
 MIB_D void face_normal_dpdu(int shape, int face, V3 &n, V3 &dp_du) {
     const mib_shape &s = sc.d.shapes[shape];
     dp_du = v3(0.f);
-    if (s.type == MIB_SHAPE_RECTANGLE) {
+    if (MIB_FT(FT_RECT) && (s.type == MIB_SHAPE_RECTANGLE || !MIB_FT(FT_CUBE))) {
         n = v3(s.frame_n[0], s.frame_n[1], s.frame_n[2]);
         dp_du = v3(s.frame_s[0], s.frame_s[1], s.frame_s[2]);
     } else {
@@ -145,7 +148,7 @@ MIB_SUB_GEOM SurfIt si_finalize2(int shape, int face, float t, V3 p, V3 ray_d) {
     si.t = t; si.shape = shape; si.face = face; si.p = p;
     const mib_shape &s = sc.d.shapes[shape];
     V3 dp_du = v3(0.f);
-    if (s.type == MIB_SHAPE_SPHERE) {
+    if (MIB_FT(FT_SPHERE) && s.type == MIB_SHAPE_SPHERE) {
         si.n = normalize(si.p - v3(s.center[0], s.center[1], s.center[2]));
         si.sh.n = si.n;
         frame_from_normal(si.n, dp_du, si.sh.s, si.sh.t);
@@ -260,7 +263,7 @@ MIB_DH void eval_grid(const mib_volume &v, V3 p, float *out, GridTaps *taps) {
 
 template <int NC>
 MIB_D void eval_volume(const mib_volume &v, V3 p, float *out, Counters &cnt, GridTaps *taps = nullptr) {
-    if (v.type == MIB_VOLUME_CONST) {
+    if (!MIB_FT(FT_GRID) || v.type == MIB_VOLUME_CONST) {
 #pragma unroll
         for (int c = 0; c < NC; ++c) out[c] = v.value[v.channels == 1 ? 0 : c];
         return;
@@ -370,15 +373,17 @@ MIB_SUB_GEOM MedRes<NC, TAPS> sample_interaction2(int mi, Ray ray, float sample,
         for (int k = 0; k < 8; ++k) { res.t.idx[k] = 0; res.t.w[k] = 0.f; }
     }
     const mib_medium &m = sc.d.media[mi];
+    // media kinds outside this instantiation's feature set never occur
+    const bool homog = MIB_FT(FT_HOMOG) && (m.type == MIB_MEDIUM_HOMOGENEOUS || !MIB_FT(FT_GRID));
     bool active = true;
     float mint = 0.f, maxt = inf_f();
-    if (m.type != MIB_MEDIUM_HOMOGENEOUS)
+    if (!homog)
         active = bbox_intersect(m.sigma_t.bbox_min, m.sigma_t.bbox_max, ray, mint, maxt);
     active = active && (isfinite(mint) || isfinite(maxt));
     if (!active) { mint = 0.f; maxt = inf_f(); }
     mint = fmaxf(0.f, mint);
     maxt = fminf(ray.maxt, maxt);
-    if (m.type == MIB_MEDIUM_HOMOGENEOUS) {
+    if (homog) {
 #pragma unroll
         for (int c = 0; c < NC; ++c) mei.maj[c] = active ? m.sigma_t.value[m.sigma_t.channels == 1 ? 0 : c] * m.scale : 0.f;
     } else {
@@ -389,7 +394,7 @@ MIB_SUB_GEOM MedRes<NC, TAPS> sample_interaction2(int mi, Ray ray, float sample,
     float sampled_t;
     bool valid_mi;
     float maj_local = m.max_density;
-    if (m.type != MIB_MEDIUM_HOMOGENEOUS && sc.super_res > 0 && sc.super[mi] != nullptr) {
+    if (MIB_FT(FT_FAST) && !homog && sc.super_res > 0 && sc.super[mi] != nullptr) {
         sampled_t = inf_f(); valid_mi = false;
         if (active && maxt > mint) {
             DdaHit h = supergrid_sample(mi, ray, mint, maxt, -log_(1.f - sample));
@@ -407,7 +412,7 @@ MIB_SUB_GEOM MedRes<NC, TAPS> sample_interaction2(int mi, Ray ray, float sample,
     mei.p = ray_at(ray, sampled_t);
     mei.medium = mi;
     mei.mint = mint;
-    if (m.type == MIB_MEDIUM_HOMOGENEOUS) {
+    if (homog) {
         float alb[NC];
 #pragma unroll
         for (int c = 0; c < NC; ++c) alb[c] = 0.f;

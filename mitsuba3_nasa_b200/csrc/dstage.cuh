@@ -122,7 +122,7 @@ MIB_D void nee_step(Pcg32 &rng, Counters &cnt, uint32_t channel, NeeState<SPEC> 
         if (ns.needs_intersection) ray_intersect(ray, si);
         if (si.t < mei.t) mei.t = inf_f();
         ns.needs_intersection = ns.needs_intersection && !valid(si);
-        const bool is_spectral = md.has_spectral_extinction != 0;
+        const bool is_spectral = (MIB_FT(FT_SPECEXT) && md.has_spectral_extinction != 0);
         if (is_spectral) {
             float t = fminf(remaining, fminf(mei.t, si.t)) - mei.mint;
             float trv[NC], ffp[NC];
@@ -169,7 +169,7 @@ MIB_D void nee_step(Pcg32 &rng, Counters &cnt, uint32_t channel, NeeState<SPEC> 
     }
     ray.maxt = remaining;
     ns.needs_intersection = ns.needs_intersection || active_surface;
-    if (sc.super_res > 0 && active_medium) {                          // fast mode: roulette on a small transmittance
+    if (MIB_FT(FT_FAST) && sc.super_res > 0 && active_medium) {                          // fast mode: roulette on a small transmittance
         float tm = fabsf(tr[0]);
 #pragma unroll
         for (int c = 1; c < NC; ++c) tm = fmaxf(tm, fabsf(tr[c]));
@@ -234,7 +234,7 @@ MIB_D int stg_main(Pcg32 &rng, Counters &cnt, WalkState<SPEC> &st, float *u_out,
     MedIt<NC> mei;
     if (active_medium) {
         const mib_medium &md = sc.d.media[st.medium];
-        is_spectral = md.has_spectral_extinction != 0;
+        is_spectral = (MIB_FT(FT_SPECEXT) && md.has_spectral_extinction != 0);
         sample_interaction<NC>(st.medium, ray, rng.next(), channel, mei, cnt);
         if (md.type == MIB_MEDIUM_HOMOGENEOUS && valid(mei)) ray.maxt = mei.t;
         if (st.needs_intersection) ray_intersect(ray, si);

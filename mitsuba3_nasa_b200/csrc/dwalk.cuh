@@ -74,7 +74,7 @@ MIB_D void sample_emitter(Pcg32 &rng, Counters &cnt, V3 ref_p, V3 ref_n, bool su
             if (needs_intersection) ray_intersect(ray, si);
             if (si.t < mei.t) mei.t = inf_f();
             needs_intersection = needs_intersection && !valid(si);
-            bool is_spectral = md.has_spectral_extinction != 0, not_spectral = !is_spectral;
+            bool is_spectral = (MIB_FT(FT_SPECEXT) && md.has_spectral_extinction != 0), not_spectral = !is_spectral;
             if (is_spectral) {
                 float t = fminf(remaining, fminf(mei.t, si.t)) - mei.mint;
                 float trv[NC], ffp[NC];
@@ -123,7 +123,7 @@ MIB_D void sample_emitter(Pcg32 &rng, Counters &cnt, V3 ref_p, V3 ref_n, bool su
         }
         ray.maxt = remaining;
         needs_intersection = needs_intersection || active_surface;
-        if (sc.super_res > 0 && active_medium) {                      // fast mode: roulette on a small transmittance (dscene.cuh)
+        if (MIB_FT(FT_FAST) && sc.super_res > 0 && active_medium) {                      // fast mode: roulette on a small transmittance (dscene.cuh)
             float tm = fabsf(tr[0]);
 #pragma unroll
             for (int c = 1; c < NC; ++c) tm = fmaxf(tm, fabsf(tr[c]));
@@ -211,7 +211,7 @@ MIB_D void path_step(Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
         bool act_null = false, act_scatter = false, escaped = false, is_spectral = false, not_spectral = false;
         if (active_medium) {
             const mib_medium &md = sc.d.media[medium];
-            is_spectral = md.has_spectral_extinction != 0;
+            is_spectral = (MIB_FT(FT_SPECEXT) && md.has_spectral_extinction != 0);
             not_spectral = !is_spectral;
             sample_interaction<NC>(medium, ray, rng.next(), channel, mei, cnt);
             if (md.type == MIB_MEDIUM_HOMOGENEOUS && valid(mei)) ray.maxt = mei.t;

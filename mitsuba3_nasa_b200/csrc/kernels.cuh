@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(128, MIB_MINB) k_forward(const __grid_constant
             for (int c = 0; c < C; ++c) lp.per_sample[(lane - lp.lane_begin) * C + c] = aov[c];
             return;
         }
-        if (lp.mode == 0 && sn.rfilter != MIB_RFILTER_BOX) {
+        if (lp.mode == 0 && (MIB_FT(FT_FILTER) && sn.rfilter != MIB_RFILTER_BOX)) {
             filter_footprint(lp.spp, sx, sy, [&](size_t pixel, float w) {
 #pragma unroll
                 for (int c = 0; c < C; ++c) atomicAdd(lp.film + pixel * C + c, aov[c] * w);
@@ -318,7 +318,7 @@ __global__ void __launch_bounds__(128, MIB_MINB_ADJ) k_adjoint(const __grid_cons
                     for (int c = 0; c < Cd; ++c) dl[c] = ap.grad1[c] * nf;
                 } else {
                     int ix = (int) floorf(sx) - sn.crop_offset_x, iy = (int) floorf(sy) - sn.crop_offset_y;
-                    if (sn.rfilter != MIB_RFILTER_BOX) {
+                    if ((MIB_FT(FT_FILTER) && sn.rfilter != MIB_RFILTER_BOX)) {
                         // adjoint of splat + weight division (hdrfilm.cpp:304-418): dL_c = sum_p grad[p,c] / W[p] * w_p
                         filter_footprint(lp.spp, sx, sy, [&](size_t pixel, float w) {
                             float W = __ldg(sc.weight_film + pixel), dv = W == 0.f ? 1.f : W;

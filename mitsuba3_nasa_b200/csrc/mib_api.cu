@@ -140,6 +140,10 @@ static void build_table(mib_scene *s, int phase, int which, int buf_nodes, int b
 
 static void commit(mib_scene *s) {
     mib_scene_desc &d = s->ds.d;
+    for (int i = 0; i < d.n_bsdfs; ++i)
+        if (d.bsdfs[i].type == MIB_BSDF_DIELECTRIC || d.bsdfs[i].type == MIB_BSDF_ROUGHDIELECTRIC)
+            throw std::runtime_error("dielectric / roughdielectric BSDFs (the ocean interface, SURVEY 8f rank 2) are described by the scene "
+                                     "format and implemented by the parity oracle, but the CUDA kernels do not walk them yet");
     for (int i = 0; i < MIB_MAX_BUFFERS; ++i) { s->ds.buffers[i] = s->buf[i]; s->ds.grad[i] = s->grad[i]; }
     for (int i = 0; i < d.n_media; ++i) {
         mib_medium &m = d.media[i];
@@ -271,11 +275,50 @@ static uint32_t pick_spt(uint64_t lanes, uint32_t spp) {
 // library builds in parallel; this file only sees their launchers.
 namespace mib {
 template <int SPEC, int MODE> void launch_k_forward(const DScene &sc, const LaunchParams &lp, unsigned blocks, cudaStream_t st);
-template <int SPEC, int MODE> void launch_k_forward_pool(const DScene &sc, const LaunchParams &lp, unsigned blocks, unsigned threads, cudaStream_t st);
+template <int SPEC, int MODE, int V> void launch_k_forward_pool(const DScene &sc, const LaunchParams &lp, unsigned blocks, unsigned threads, cudaStream_t st);
 template <int SPEC, int MODE> int pool_slots();
 template <int SPEC> void launch_k_adjoint(const DScene &sc, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, cudaStream_t st);
-template <int SPEC> void launch_k_adjoint_pool(const DScene &sc, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, unsigned threads, cudaStream_t st);
+template <int SPEC, int V> void launch_k_adjoint_pool(const DScene &sc, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, unsigned threads, cudaStream_t st);
 template <int SPEC> int adjoint_pool_slots();
+}
+
+// ---------------------------------------------------------------------------
+// Scene-specialised instantiations of the pool kernels (dmath.cuh MIB_FEAT; csrc/Makefile VARIANTS): the feature bits a scene
+// needs, and the most specific compiled set that covers them.  MIB_VARIANT=<id> forces one (A/B runs; 0 = every feature).
+// ---------------------------------------------------------------------------
+static const unsigned kVariantMask[] = { 0xffffffffu, 417u, 146u, 150u };      // id -> MIB_FEAT of the object files
+static const int kVariantOrder[] = { 1, 2, 3, 0 };                              // most specific first
+static unsigned scene_features(const mib_scene *s) {
+    const mib_scene_desc &d = s->ds.d;
+    unsigned f = 0;
+    for (int i = 0; i < d.n_media; ++i) {
+        const mib_medium &m = d.media[i];
+        f |= m.type == MIB_MEDIUM_HOMOGENEOUS ? FT_HOMOG : FT_GRID;
+        if (m.sigma_t.type == MIB_VOLUME_GRID || m.albedo.type == MIB_VOLUME_GRID) f |= FT_GRID;
+        if (m.has_spectral_extinction) f |= FT_SPECEXT;
+    }
+    if (d.integrator.majorant_res > 0) f |= FT_FAST;
+    for (int i = 0; i < d.n_emitters; ++i) if (d.emitters[i].type == MIB_EMITTER_AREA) f |= FT_AREA;
+    for (int i = 0; i < d.n_phases; ++i)
+        f |= (d.phases[i].type == MIB_PHASE_TABPHASE || d.phases[i].type == MIB_PHASE_TABPHASE_POLARIZED) ? FT_TAB : FT_ANALYTIC;
+    for (int i = 0; i < d.n_shapes; ++i)
+        f |= d.shapes[i].type == MIB_SHAPE_RECTANGLE ? FT_RECT : (d.shapes[i].type == MIB_SHAPE_CUBE ? FT_CUBE : FT_SPHERE);
+    if (d.sensor.rfilter != MIB_RFILTER_BOX) f |= FT_FILTER;
+    return f;
+}
+static int pick_variant(const mib_scene *s) {
+    const char *v = getenv("MIB_VARIANT");
+    const unsigned need = scene_features(s);
+    if (v && *v) {
+        const int id = atoi(v);
+        if (id < 0 || id >= (int) (sizeof(kVariantMask) / sizeof(kVariantMask[0])))
+            throw std::runtime_error("MIB_VARIANT: no such instantiation");
+        if ((kVariantMask[id] & need) != need)
+            throw std::runtime_error("MIB_VARIANT: the scene needs features this instantiation was compiled without");
+        return id;
+    }
+    for (int id : kVariantOrder) if ((kVariantMask[id] & need) == need) return id;
+    return 0;
 }
 
 static int env_int(const char *name, int dflt) {
@@ -297,7 +340,12 @@ static void launch_forward_pool(mib_scene *s, LaunchParams lp) {
     const int slots = pool_slots<SPEC, MODE>();
     uint64_t blocks = (lanes + 2ull * slots - 1) / (2ull * slots);
     blocks = std::max<uint64_t>(1, std::min<uint64_t>(blocks, (uint64_t) n_sm * env_int("MIB_POOL_CTAS_PER_SM", 1)));
-    launch_k_forward_pool<SPEC, MODE>(s->ds, lp, (unsigned) blocks, (unsigned) threads, s->stream);
+    switch (pick_variant(s)) {
+        case 1: launch_k_forward_pool<SPEC, MODE, 1>(s->ds, lp, (unsigned) blocks, (unsigned) threads, s->stream); break;
+        case 2: launch_k_forward_pool<SPEC, MODE, 2>(s->ds, lp, (unsigned) blocks, (unsigned) threads, s->stream); break;
+        case 3: launch_k_forward_pool<SPEC, MODE, 3>(s->ds, lp, (unsigned) blocks, (unsigned) threads, s->stream); break;
+        default: launch_k_forward_pool<SPEC, MODE, 0>(s->ds, lp, (unsigned) blocks, (unsigned) threads, s->stream); break;
+    }
     CK(cudaGetLastError());
 }
 
