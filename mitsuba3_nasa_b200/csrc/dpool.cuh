@@ -237,6 +237,9 @@ template <int P> struct PoolMem {
 #ifndef MIB_POOL_FULL
 #define MIB_POOL_FULL 32
 #endif
+#ifndef MIB_POOL_STAY
+#define MIB_POOL_STAY 24       // lanes a batch of the current stage group must still fill for the CTA to stay with that group (0: round-1 rule)
+#endif
 #ifndef MIB_POOL_STEAL
 #define MIB_POOL_STEAL 0       // banks a lane may look into beyond its own when that has nothing in the chosen class (0: none)
 #endif
@@ -316,8 +319,15 @@ template <int P, unsigned GROUPMAP> struct PoolQ {
             const unsigned n_in = kin >> 3, n_out = kout >> 3;
             int best = -1;
             bool flip = false;
+#if MIB_POOL_STAY
+            // stay with the current group while it still fills kPoolStay lanes, or nothing outside would fill more; otherwise
+            // move the CTA on to the fullest class (round 1's rule drained a group to its last slot: half-empty batches)
+            if (n_in >= (unsigned) MIB_POOL_STAY || (n_in > 0u && n_in >= n_out)) best = (int) (kin & 7u);
+            else if (n_out > 0u) { best = (int) (kout & 7u); flip = true; }
+#else
             if (n_in >= kPoolFull || (n_in > 0u && n_out < kPoolFull)) best = (int) (kin & 7u);
             else if (n_out > 0u) { best = (int) (kout & 7u); flip = true; }
+#endif
             if (best >= 0) {
                 unsigned m = vm[best * 32 + lane_id];
                 bool ok = false;

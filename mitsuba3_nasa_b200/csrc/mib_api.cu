@@ -335,7 +335,7 @@ static void launch_forward_pool(mib_scene *s, LaunchParams lp) {
     if (lanes == 0) return;
     int n_sm = 0;
     CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, s->device));
-    int threads = env_int("MIB_POOL_NT", 384);
+    int threads = env_int("MIB_POOL_NT", MIB_POOL_NT);
     threads = std::max(32, std::min(threads, MIB_POOL_NT)) & ~31;
     const int slots = pool_slots<SPEC, MODE>();
     uint64_t blocks = (lanes + 2ull * slots - 1) / (2ull * slots);
@@ -729,11 +729,11 @@ extern "C" int mib_sample_lanes_noalloc(mib_scene *s, uint32_t seed, uint32_t sp
     MIB_TRY
     if (!s || !out_host) throw std::runtime_error("mib_sample_lanes_noalloc: null argument");
     const uint64_t C = (uint64_t) raw_channels(s->ds.d.spectrum);
-    check_lane_slice(s, spp, lane_begin, count, "mib_sample_lanes_noalloc");
     if (count > MIB_NOALLOC_MAX_FLOATS / C)
         throw std::runtime_error("mib_sample_lanes_noalloc: " + std::to_string(count) + " lanes x " + std::to_string(C) +
                                  " channels exceed the static scratch of " + std::to_string((unsigned long long) MIB_NOALLOC_MAX_FLOATS) +
                                  " floats (MIB_NOALLOC_MAX_FLOATS); split the lane range or use mib_debug_sample_lanes");
+    check_lane_slice(s, spp, lane_begin, count, "mib_sample_lanes_noalloc");
     std::lock_guard<std::mutex> call_lock(g_noalloc_mutex);
     CK(cudaSetDevice(s->device));
     float *dev = noalloc_scratch(s->device);
