@@ -173,15 +173,18 @@ class ReferenceCPU:
                 self._run(0, 1000)
                 self.kind = 'reference'
             except Exception as e:
-                print("bench.py: the prebuilt scalar reference did not run (%s); using the oracle port" % e, file=sys.stderr)
+                print("bench.py: the prebuilt scalar reference did not run (%s; stderr: %s); using the oracle port"
+                      % (e, (getattr(e, 'stderr', '') or '').strip()[-400:]), file=sys.stderr)
         if self.kind == 'port':
             from mitsuba3_nasa_b200 import scene as S
             self.flat = S.load_dict(d, 'llvm_ad_mono_polarized')
 
     def _run(self, seed, n):
         out = os.path.join(self.tmp, 'o.bin')
+        # libmitsuba.so carries the RUNPATH of the build tree it came from; its own dependencies sit next to it
+        env = dict(os.environ, LD_LIBRARY_PATH=os.path.dirname(self.driver) + os.pathsep + os.environ.get('LD_LIBRARY_PATH', ''))
         r = subprocess.run([self.driver, 'scalar_mono_polarized', self.xml, 'render1', str(seed), str(n), out, str(self.cores)],
-                           stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True, check=True)
+                           stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True, check=True, env=env)
         secs = [float(l.split()[1]) for l in r.stderr.splitlines() if l.startswith('RENDER1_SECONDS')]
         if not secs:
             raise RuntimeError("no timing line from ref_driver")
