@@ -131,6 +131,12 @@ class DeviceScene:
         self._ck(f(self.h, C.c_uint32(seed), C.c_uint32(spp), _fp(out)))
         return out
 
+    def forward_kernel(self):
+        """'pool' or 'thread': the kernel family render() / render_1() launch for this scene (mib_scene_forward_kernel)."""
+        k = C.c_int(0)
+        self._ck(self.l.mib_scene_forward_kernel(self.h, C.byref(k)))
+        return 'pool' if k.value else 'thread'
+
     def supergrid(self, medium=0):
         """Majorant supergrid of a heterogeneous medium (fast mode, integrator 'majorant_resolution' > 0): [M, M, M] (z, y, x)."""
         M = int(self.scene.desc.integrator.majorant_res)

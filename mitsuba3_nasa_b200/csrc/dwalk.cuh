@@ -158,6 +158,7 @@ template <int SPEC> struct PathState {
     float eta, last_pdf;
     V3 last_p;                    // position of the last scattering event (MIS pdf of an area light that is hit)
     int medium;
+    int refractive_bsdf;          // docean.cuh: BSDF of the interface while the path is below it (volpathaos.cpp:80), else -1
     uint32_t depth, channel;
     bool active, specular_chain, needs_intersection;
 };
@@ -171,6 +172,7 @@ MIB_D void path_init(Pcg32 &rng, const Ray &ray, PathState<SPEC> &st) {
     st.ray = ray;
     st.eta = 1.f;
     st.medium = sc.d.sensor.medium;
+    st.refractive_bsdf = -1;
     st.active = true;
     st.specular_chain = !sc.d.integrator.hide_emitters;
     st.needs_intersection = true;

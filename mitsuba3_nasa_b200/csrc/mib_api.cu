@@ -138,12 +138,19 @@ static void build_table(mib_scene *s, int phase, int which, int buf_nodes, int b
     }
 }
 
+static bool has_dielectric(const mib_scene *s) {
+    const mib_scene_desc &d = s->ds.d;
+    for (int i = 0; i < d.n_bsdfs; ++i)
+        if (d.bsdfs[i].type == MIB_BSDF_DIELECTRIC || d.bsdfs[i].type == MIB_BSDF_ROUGHDIELECTRIC) return true;
+    return false;
+}
+
 static void commit(mib_scene *s) {
     mib_scene_desc &d = s->ds.d;
-    for (int i = 0; i < d.n_bsdfs; ++i)
-        if (d.bsdfs[i].type == MIB_BSDF_DIELECTRIC || d.bsdfs[i].type == MIB_BSDF_ROUGHDIELECTRIC)
-            throw std::runtime_error("dielectric / roughdielectric BSDFs (the ocean interface, SURVEY 8f rank 2) are described by the scene "
-                                     "format and implemented by the parity oracle, but the CUDA kernels do not walk them yet");
+    // the ocean interface: walked by the forward volpathaos kernel of docean.cuh only
+    if (has_dielectric(s) && d.integrator.type != MIB_INTEG_VOLPATHAOS)
+        throw std::runtime_error("dielectric / roughdielectric BSDFs (the ocean interface) are walked by the volpathaos kernel only: "
+                                 "volpath, prbvolpath and prb_volpathaos (the adjoint has no refractive next-event estimation) refuse them");
     for (int i = 0; i < MIB_MAX_BUFFERS; ++i) { s->ds.buffers[i] = s->buf[i]; s->ds.grad[i] = s->grad[i]; }
     for (int i = 0; i < d.n_media; ++i) {
         mib_medium &m = d.media[i];
@@ -355,6 +362,7 @@ static void launch_forward_pool(mib_scene *s, LaunchParams lp) {
 static bool forward_uses_pool(const mib_scene *s) {
     const int integ = s->ds.d.integrator.type;
     if (integ != MIB_INTEG_VOLPATH && integ != MIB_INTEG_VOLPATHAOS) return false;     // prb primal passes: per-thread kernel
+    if (has_dielectric(s)) return false;                                               // docean.cuh: per-thread kernel
     const char *k = getenv("MIB_FORWARD_KERNEL");
     bool pool = true;
     if (k && strcmp(k, "thread") == 0) pool = false;
@@ -384,6 +392,10 @@ static void dispatch_forward(mib_scene *s, const LaunchParams &lp) {
             if (spec == 0) launch_forward<0, 0>(s, lp); else if (spec == 1) launch_forward<1, 0>(s, lp); else launch_forward<2, 0>(s, lp);
             break;
         case MIB_INTEG_VOLPATHAOS:
+            if (has_dielectric(s)) {
+                if (spec == 0) launch_forward<0, 4>(s, lp); else if (spec == 1) launch_forward<1, 4>(s, lp); else launch_forward<2, 4>(s, lp);
+                break;
+            }
             if (spec == 0) launch_forward<0, 1>(s, lp); else if (spec == 1) launch_forward<1, 1>(s, lp); else launch_forward<2, 1>(s, lp);
             break;
         case MIB_INTEG_PRBVOLPATH:

@@ -21,7 +21,7 @@ import scalar_cases
 pytestmark = pytest.mark.gpu
 
 LLVM = {'scalar_rgb': 'llvm_ad_rgb', 'scalar_mono': 'llvm_ad_mono', 'scalar_mono_polarized': 'llvm_ad_mono_polarized'}
-# (the ocean-interface scenes are pinned in the oracle only: the kernels refuse dielectric BSDFs, test below)
+# (the ocean-interface scenes have their own file: tests/test_gpu_ocean.py)
 CASES = {n: c for n, c in scalar_cases.cases().items() if c['kind'] == 'samples' and not n.startswith('ocean_')}
 
 
@@ -129,9 +129,3 @@ def test_three_channel_albedo_grid_gradient_in_a_mono_variant():
     g, o = dev.grad_get(slot, alb.size).astype(np.float64), orc.grad_get(slot, alb.size)
     assert np.all(np.abs(o).reshape(-1, 3).sum(axis=0) > 0)
     assert np.abs(g - o).max() <= 1e-3 * np.abs(o).max()
-
-
-def test_dielectric_scenes_are_refused_by_the_kernels():
-    sc = S.load_dict(scenes.aos_ocean(), "llvm_ad_mono_polarized")
-    with pytest.raises(RuntimeError, match="dielectric"):
-        _lib.DeviceScene(sc, 0)
