@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
                 for (int c = 0; c < 4; ++c) st.dl[c] = pm.f(L::F_DL + c, slot);
                 st.dl_sum = (AOS && st.backward) ? ((st.dl[0] + st.dl[1]) + st.dl[2]) + st.dl[3] : 0.f;
                 int ev = EV_NULL;
-                for (int it = 0; it < kPoolMainIters && ev == EV_NULL; ++it) ev = prb_main<SPEC, AOS>(rng, cnt, sink, st);
+                for (int it = 0; it < kAdjMainIters && ev == EV_NULL; ++it) ev = prb_main<SPEC, AOS>(rng, cnt, sink, st);
                 if (ev == EV_DONE) next = C_START;
                 else {
                     pm.store_rng_state(slot, rng);
@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
                 uint32_t fl = pm.u(L::F_FLAGS, slot);
                 st.channel = fl & FL_CHANNEL;
                 load_nee(slot, fl, st.nee);
-                for (int it = 0; it < kPoolNeeIters && st.nee.active; ++it)
+                for (int it = 0; it < kAdjNeeIters && st.nee.active; ++it)
                     prb_nee_step<SPEC, AOS>(rng, cnt, sink, st.channel, st.nee, false, nullptr, nullptr);
                 pm.store_rng_state(slot, rng);
                 if (st.nee.active) {
@@ -315,7 +315,7 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
                 for (int r = 0; r < NR; ++r) adj[r] = pm.f(L::F_NA + r, slot);
 #pragma unroll
                 for (int c = 0; c < 4; ++c) dl[c] = pm.f(L::F_DL + c, slot);
-                for (int it = 0; it < kPoolNeeIters && ns.active; ++it)
+                for (int it = 0; it < kAdjNeeIters && ns.active; ++it)
                     prb_nee_step<SPEC, AOS>(grng, cnt, sink, fl & FL_CHANNEL, ns, true, adj, dl);
                 if (ns.active) {
                     pm.su(L::F_NRNG, slot, (uint32_t) grng.state); pm.su(L::F_NRNG + 1, slot, (uint32_t) (grng.state >> 32));

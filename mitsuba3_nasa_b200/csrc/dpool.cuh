@@ -59,6 +59,16 @@ constexpr int kPoolChunk = 256;            // lanes per interleaved chunk
 #endif
 constexpr int kPoolMainIters = MIB_POOL_MAIN_ITERS;   // MAIN: null collisions handled per batch before the slot is re-queued
 constexpr int kPoolNeeIters = MIB_POOL_NEE_ITERS;     // NEE: shadow steps per batch
+// The adjoint pool wants shorter batches (profiles/r02_ab_pool.md run 10: C4 +19 % with 2 / 1): its steps are heavier (grid
+// look-up + 8 gradient atomics), so re-queueing a slot costs relatively less than the lanes idling while the longest walk of
+// the batch finishes; the forward kernels lose 4-10 % with shorter batches.
+#ifndef MIB_APOOL_MAIN_ITERS
+#define MIB_APOOL_MAIN_ITERS 1
+#endif
+#ifndef MIB_APOOL_NEE_ITERS
+#define MIB_APOOL_NEE_ITERS 2
+#endif
+constexpr int kAdjMainIters = MIB_APOOL_MAIN_ITERS, kAdjNeeIters = MIB_APOOL_NEE_ITERS;
 constexpr unsigned kPoolSpinLimit = 1u << 22;   // watchdog of the two wait loops (consecutive idle polls x 100 ns; ring entry polls x ~50 ns)
 constexpr uint32_t kNoLane = 0xffffffffu;
 constexpr unsigned kRingEmpty = 0xffffu;
@@ -366,6 +376,11 @@ template <int P, unsigned GROUPMAP> struct PoolQ {
                 }
 #endif
                 if (__any_sync(FULL, ok)) {
+#ifdef MIB_POOL_STATS
+                    // batches and claimed lanes per class behind the event counters (mib_api.cu prints them: MIB_POOL_STATS build only)
+                    { const unsigned nb = (unsigned) __popc(__ballot_sync(FULL, ok));
+                      if (lane_id == 0) { atomicAdd(lane_counter + 2 + 2 * best, 1ull); atomicAdd(lane_counter + 3 + 2 * best, (unsigned long long) nb); } }
+#endif
                     if (flip && lane_id == 0) ps->group = (GROUPMAP >> (4u * (unsigned) best)) & 15u;
                     ++rot;
                     idle_spins = 0;                    // the idle watchdog counts CONSECUTIVE polls

@@ -435,8 +435,13 @@ static void lane_range(mib_scene *s, uint32_t spp, uint64_t &b, uint64_t &e) {
 }
 
 static void fetch_counters(mib_scene *s, float ms, uint64_t launches) {
-    unsigned long long c[8];
+    unsigned long long c[24];
     CK(cudaMemcpy(c, s->counters, sizeof(c), cudaMemcpyDeviceToHost));
+#ifdef MIB_POOL_STATS
+    fprintf(stderr, "pool batches per class (batches, mean lanes):");
+    for (int k = 0; k < 8; ++k) fprintf(stderr, " %d: %llu, %.1f |", k, c[8 + 2 * k], c[8 + 2 * k] ? (double) c[9 + 2 * k] / (double) c[8 + 2 * k] : 0.0);
+    fprintf(stderr, "\n");
+#endif
     s->last.n_lookups = c[0]; s->last.n_real = c[1]; s->last.n_null = c[2];
     s->last.n_nee_steps = c[3]; s->last.n_surface = c[4]; s->last.n_samples = c[5];
     s->last.kernel_ms = ms; s->last.n_launches = launches;
@@ -463,7 +468,7 @@ static void run_forward(mib_scene *s, uint32_t seed, uint32_t spp, int mode, flo
     lp.sums = s->sums;
     lp.per_sample = per_sample_dev;
     lp.counters = s->counters;
-    CK(cudaMemsetAsync(s->counters, 0, 8 * sizeof(unsigned long long), s->stream));
+    CK(cudaMemsetAsync(s->counters, 0, 24 * sizeof(unsigned long long), s->stream));
     if (mode == 0) CK(cudaMemsetAsync(s->film_raw, 0, s->film_raw_n * sizeof(float), s->stream));
     if (mode == 1) CK(cudaMemsetAsync(s->sums, 0, 8 * sizeof(double), s->stream));
     CK(cudaEventRecord(s->ev0, s->stream));
@@ -522,7 +527,7 @@ int mib_scene_create(const mib_scene_desc *desc, int device, mib_scene **out) {
     CK(cudaEventCreate(&s->ev0));
     CK(cudaEventCreate(&s->ev1));
     CK(cudaMalloc(&s->sums, 8 * sizeof(double)));
-    CK(cudaMalloc(&s->counters, 8 * sizeof(unsigned long long)));
+    CK(cudaMalloc(&s->counters, 24 * sizeof(unsigned long long)));      // 8 counters + 16 words of pool statistics (MIB_POOL_STATS builds)
     CK(cudaMalloc(&s->maxbits, sizeof(unsigned int)));
     CK(cudaMalloc(&s->grad_scalar, MIB_MAX_MEDIA * 4 * sizeof(double)));
     CK(cudaMemset(s->grad_scalar, 0, MIB_MAX_MEDIA * 4 * sizeof(double)));
