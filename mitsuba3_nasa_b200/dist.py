@@ -35,7 +35,10 @@ def lane_slice(n_pixels, spp, rank, world):
     return b, b + per + (1 if rank < rem else 0)
 
 
-STRIPE_PIXELS = 64     # pixels per stripe chunk
+# pixels per stripe chunk.  Measured on the C4 adjoint by running every rank's share on one GPU (profiles/dist_balance.py,
+# profiles/r02_dist_balance.log): slowest / mean rank time 1.17 (N=2), 1.15 (N=4) with 64-pixel chunks -- with the rotation below a
+# 512-pixel row still gives a rank the same column bands in every row when N < 8 -- against 1.03 / 1.01 with 4-pixel chunks.
+STRIPE_PIXELS = 4
 
 
 def stripe_lanes(n_pixels, spp, rank, world, chunk_pixels=STRIPE_PIXELS):
@@ -88,7 +91,7 @@ class ShardedScene:
         sn = self.scene.flat.desc.sensor
         n_pix = sn.crop_width * sn.crop_height
         if self.world > 1 and n_pix >= 4 * STRIPE_PIXELS * self.world:
-            # films: interleaved stripes of 64 pixels, every rank samples the whole image (load balance)
+            # films: interleaved stripes of STRIPE_PIXELS pixels, every rank samples the whole image (load balance)
             self.scene.device.set_lane_stripes(self.rank, self.world, STRIPE_PIXELS * spp)
             return
         self.scene.device.set_lane_stripes(0, 1, 1)
