@@ -51,15 +51,22 @@ def algorithmic_bytes(c, film_channels=4):
 
 
 def lib_sha16():
+    """Identity of the kernel build: sha256 over the sources libmi_b200.so is compiled from (csrc/*.cu, *.cuh, *.inc, the Makefile and
+    the C header), in name order.  (The binary itself is no stable key: two nvcc builds of the same sources differ.)"""
+    import glob
     import hashlib
-    from mitsuba3_nasa_b200 import _lib
-    return hashlib.sha256(open(_lib.LIB_PATH, 'rb').read()).hexdigest()[:16]
+    h = hashlib.sha256()
+    src = os.path.join(ROOT, 'mitsuba3_nasa_b200', 'csrc')
+    files = sorted(glob.glob(os.path.join(src, '*.cu')) + glob.glob(os.path.join(src, '*.cuh')) + glob.glob(os.path.join(src, '*.inc')))
+    for f in files + [os.path.join(src, 'Makefile'), os.path.join(ROOT, 'include', 'mi_b200.h')]:
+        h.update(os.path.basename(f).encode() + b'\0' + open(f, 'rb').read())
+    return h.hexdigest()[:16]
 
 
 def measured_traffic(kernel_key, n_samples):
     """dram__bytes_read.sum + dram__bytes_write.sum of one launch from the `ncu --set full` capture of THIS build
     (profiles/r02_traffic.json, written by profiles/ncu_traffic.py next to the capture): bytes per sample x this launch's
-    samples.  None when the capture on file is of another build (sha of libmi_b200.so differs) or absent."""
+    samples.  None when the capture on file is of other kernel sources (lib_sha16 differs) or absent."""
     try:
         rec = json.load(open(os.path.join(ROOT, 'profiles', 'r02_traffic.json')))
         if rec.get('lib_sha16') != lib_sha16() or kernel_key not in rec['kernels']:
@@ -355,7 +362,7 @@ def run_ours(args):
                      "frac": achieved_tf / peak_tf,
                      "traffic": measured_traffic("c2_forward", c1['n_samples']),
                      "traffic_note": "dram bytes of one launch from the ncu --set full capture of this very build (profiles/r02_traffic.json, "
-                                     "keyed by the sha256 of libmi_b200.so), scaled to this launch's samples; null when no capture of this build is on file",
+                                     "keyed by the sha256 of the kernel sources), scaled to this launch's samples; null when no capture of this build is on file",
                      "peak_source": "measured in this run: independent FFMA chains on all SMs (mib_debug_fp32_peak), best of 5" if fp32_peak else
                                     "fallback: 148 SM x 128 lanes x 2 x 1.965 GHz (derived)",
                      "peak_derived_at_max_clock": FP32_PEAK_DERIVED_TFLOPS,

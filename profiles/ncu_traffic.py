@@ -1,8 +1,8 @@
 """Writes profiles/r02_traffic.json: DRAM bytes of one launch per benchmarked kernel, taken from `ncu --set full` captures of
-ONE build of libmi_b200.so, keyed by the sha256 of that library so that bench.py only reports `roofline.traffic` when the
-capture on file is of the very build it is timing.
+ONE state of the kernel sources, keyed by bench.lib_sha16() (sha256 over csrc/ sources + Makefile + mi_b200.h) so that bench.py
+only reports `roofline.traffic` when the capture on file is of the kernels it is timing.
 
-    python profiles/ncu_traffic.py <lib_sha16> key=report.ncu-rep:n_samples [key=...]
+    python profiles/ncu_traffic.py <lib_sha16 | auto> key=report.ncu-rep:n_samples [key=...]
 
 keys used by bench.py: c2_forward, c3_forward_mono, c3_forward_mono_polarized, c4_adjoint."""
 import csv
@@ -28,6 +28,10 @@ def dram_bytes(rep):
 
 def main():
     sha = sys.argv[1]
+    if sha == 'auto':
+        sys.path.insert(0, os.path.dirname(HERE))
+        import bench
+        sha = bench.lib_sha16()
     out = {"lib_sha16": sha, "kernels": {}}
     for arg in sys.argv[2:]:
         key, rest = arg.split('=', 1)

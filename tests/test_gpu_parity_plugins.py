@@ -72,6 +72,24 @@ def test_rng_arg_order_right_to_left(name, kernel):
     _compare(sc, 1, case['spp'], 0, W * H * case['spp'])
 
 
+def test_fixed_max_value_is_the_majorant(kernel):
+    """grid.cpp:296-297: a gridvolume given `max_value` uses it as the majorant as it is (more null collisions, different
+    random sequence than with the data's own maximum): lane by lane against the oracle."""
+    d = scenes.c3_cloud(res=8, spp=8, grid=np.random.default_rng(9).uniform(0.0, 1.0, (6, 6, 6, 1)).astype(np.float32),
+                        phase={'type': 'isotropic'}, optical_depth=4.0)
+    d['object']['interior']['sigma_t']['max_value'] = 1.5
+    sc = S.load_dict(d, "llvm_ad_mono")
+    assert sc.desc.media[0].sigma_t.fixed_max == 1
+    _compare(sc, 0, 8, 0, 8 * 8 * 8)
+    e = scenes.c3_cloud(res=8, spp=8, grid=np.random.default_rng(9).uniform(0.0, 1.0, (6, 6, 6, 1)).astype(np.float32),
+                        phase={'type': 'isotropic'}, optical_depth=4.0)
+    a = _lib.DeviceScene(sc, 0)
+    a.sample_lanes(0, 8, 0, 512)
+    b = _lib.DeviceScene(S.load_dict(e, "llvm_ad_mono"), 0)
+    b.sample_lanes(0, 8, 0, 512)
+    assert a.counters()['n_null'] > b.counters()['n_null']
+
+
 @pytest.mark.parametrize("variant", ["llvm_ad_mono", "llvm_ad_mono_polarized"])
 def test_c3_real_scene_lane_slices(variant):
     """BASELINE configs[2] as specified: 1024 x 1024 x 256 spp film over the 256^3 cloud, Mie x lognormal table with 1801
