@@ -41,20 +41,22 @@
 extern "C" {
 #endif
 
-#define MIB_ABI_VERSION 6
+#define MIB_ABI_VERSION 7
 
-#define MIB_MAX_SHAPES   8
+#define MIB_MAX_SHAPES   12
 #define MIB_MAX_MEDIA    4
 #define MIB_MAX_PHASES   4
 #define MIB_MAX_BSDFS    8
 #define MIB_MAX_EMITTERS 4
-#define MIB_MAX_BUFFERS  16
+#define MIB_MAX_BUFFERS  24
 
 /* ---- enums (plugin types become tags) ---- */
 enum { MIB_SPEC_MONO = 0, MIB_SPEC_RGB = 1, MIB_SPEC_MONO_POLARIZED = 2 };
 enum { MIB_INTEG_VOLPATH = 0, MIB_INTEG_VOLPATHAOS = 1,
        MIB_INTEG_PRBVOLPATH = 2, MIB_INTEG_PRBVOLPATHAOS = 3 };
-enum { MIB_SHAPE_CUBE = 0, MIB_SHAPE_RECTANGLE = 1, MIB_SHAPE_SPHERE = 2 };
+enum { MIB_SHAPE_CUBE = 0, MIB_SHAPE_RECTANGLE = 1, MIB_SHAPE_SPHERE = 2, MIB_SHAPE_MESH = 3 };
+enum { MIB_MESH_HAS_NORMALS = 1, MIB_MESH_HAS_TEXCOORDS = 2 };
+enum { MIB_TEXTURE_UNIFORM = 0, MIB_TEXTURE_CHECKERBOARD = 1 };
 enum { MIB_BSDF_NULL = 0, MIB_BSDF_DIFFUSE = 1, MIB_BSDF_DIELECTRIC = 2, MIB_BSDF_ROUGHDIELECTRIC = 3 };
 enum { MIB_MICROFACET_BECKMANN = 0, MIB_MICROFACET_GGX = 1 };
 enum { MIB_MEDIUM_HOMOGENEOUS = 0, MIB_MEDIUM_HETEROGENEOUS = 1 };
@@ -117,6 +119,12 @@ typedef struct mib_bsdf {
     float   alpha_v;
     int32_t distribution;    /* MIB_MICROFACET_* (roughdielectric.cpp:182-193) */
     int32_t sample_visible;  /* roughdielectric.cpp:195 (only 1, the plugin's default, is implemented) */
+    /* diffuse reflectance as a checkerboard texture (src/textures/checkerboard.cpp:66-84; SURVEY 8f rank 3: the background
+       plane of the fork's participating_media test scenes): color0 where the two uv cells agree, color1 elsewhere */
+    int32_t texture;         /* MIB_TEXTURE_*; UNIFORM: `reflectance` */
+    float   color0[3];
+    float   color1[3];
+    float   to_uv[6];        /* rows 0 and 1 of the 3 x 3 `to_uv` transform (uv' = to_uv * (u, v, 1)) */
 } mib_bsdf;
 
 typedef struct mib_shape {
@@ -135,6 +143,16 @@ typedef struct mib_shape {
     /* sphere (src/shapes/sphere.cpp): world-space center / radius */
     float   center[3];
     float   radius;
+    /* triangle mesh (`obj`, src/shapes/obj.cpp, include/mitsuba/render/mesh.h), world space, packed into ONE
+       float buffer: positions [3 V] | normals [3 V] (HAS_NORMALS) | texcoords [2 V] (HAS_TEXCOORDS) | faces [3 F] (uint32
+       bit patterns) | BVH nodes [8 N]: bbox min (3), bbox max (3), then for an inner node (left child, right child | 0x80000000)
+       and for a leaf (first entry of the order table, count) -- as uint32 bit patterns | order table [F]: face indices in leaf
+       order (uint32 bit patterns).  Built by the host side (mitsuba3_nasa_b200/mesh.py); node 0 is the root. */
+    int32_t mesh_buffer;     /* buffer slot, -1: not a mesh */
+    int32_t mesh_vertices;   /* V */
+    int32_t mesh_faces;      /* F */
+    int32_t mesh_nodes;      /* N */
+    int32_t mesh_flags;      /* MIB_MESH_HAS_* */
 } mib_shape;
 
 typedef struct mib_emitter {

@@ -5,13 +5,15 @@ and the ABI version at load time so a drift fails loudly.
 """
 import ctypes as C
 
-MIB_ABI_VERSION = 6
-MIB_MAX_SHAPES, MIB_MAX_MEDIA, MIB_MAX_PHASES = 8, 4, 4
-MIB_MAX_BSDFS, MIB_MAX_EMITTERS, MIB_MAX_BUFFERS = 8, 4, 16
+MIB_ABI_VERSION = 7
+MIB_MAX_SHAPES, MIB_MAX_MEDIA, MIB_MAX_PHASES = 12, 4, 4
+MIB_MAX_BSDFS, MIB_MAX_EMITTERS, MIB_MAX_BUFFERS = 8, 4, 24
 
 SPEC_MONO, SPEC_RGB, SPEC_MONO_POLARIZED = 0, 1, 2
 INTEG_VOLPATH, INTEG_VOLPATHAOS, INTEG_PRBVOLPATH, INTEG_PRBVOLPATHAOS = 0, 1, 2, 3
-SHAPE_CUBE, SHAPE_RECTANGLE, SHAPE_SPHERE = 0, 1, 2
+SHAPE_CUBE, SHAPE_RECTANGLE, SHAPE_SPHERE, SHAPE_MESH = 0, 1, 2, 3
+MESH_HAS_NORMALS, MESH_HAS_TEXCOORDS = 1, 2
+TEXTURE_UNIFORM, TEXTURE_CHECKERBOARD = 0, 1
 BSDF_NULL, BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_ROUGHDIELECTRIC = 0, 1, 2, 3
 MICROFACET_BECKMANN, MICROFACET_GGX = 0, 1
 MEDIUM_HOMOGENEOUS, MEDIUM_HETEROGENEOUS = 0, 1
@@ -45,14 +47,16 @@ class Medium(C.Structure):
 
 class Bsdf(C.Structure):
     _fields_ = [("type", i32), ("reflectance", f32 * 3), ("eta", f32), ("inv_eta", f32), ("alpha_u", f32), ("alpha_v", f32),
-                ("distribution", i32), ("sample_visible", i32)]
+                ("distribution", i32), ("sample_visible", i32),
+                ("texture", i32), ("color0", f32 * 3), ("color1", f32 * 3), ("to_uv", f32 * 6)]
 
 
 class Shape(C.Structure):
     _fields_ = [("type", i32), ("bsdf", i32), ("interior_medium", i32), ("exterior_medium", i32),
                 ("emitter", i32), ("to_world", f32 * 16), ("to_object", f32 * 16),
                 ("frame_s", f32 * 3), ("frame_t", f32 * 3), ("frame_n", f32 * 3), ("inv_surface_area", f32),
-                ("center", f32 * 3), ("radius", f32)]
+                ("center", f32 * 3), ("radius", f32),
+                ("mesh_buffer", i32), ("mesh_vertices", i32), ("mesh_faces", i32), ("mesh_nodes", i32), ("mesh_flags", i32)]
 
 
 class Emitter(C.Structure):

@@ -15,11 +15,11 @@
 // bound by instruction supply, not by arithmetic or memory.
 // ---------------------------------------------------------------------------------------------
 #ifndef MIB_FEAT
-#define MIB_FEAT 0xffffffffu
+#define MIB_FEAT 0xfffff7ffu        // everything but FT_MESH: only the forward one-thread-one-path kernels carry meshes (Makefile)
 #endif
 enum : unsigned {
     FT_HOMOG = 1u, FT_GRID = 2u, FT_FAST = 4u, FT_AREA = 8u, FT_TAB = 16u, FT_ANALYTIC = 32u, FT_SPHERE = 64u, FT_CUBE = 128u,
-    FT_RECT = 256u, FT_FILTER = 512u, FT_SPECEXT = 1024u, FT_ALL = 0xffffffffu
+    FT_RECT = 256u, FT_FILTER = 512u, FT_SPECEXT = 1024u, FT_MESH = 2048u /* obj meshes, uv textures */, FT_ALL = 0xffffffffu
 };
 #define MIB_FT(f) (((MIB_FEAT) & (f)) != 0u)
 #include <cuda_runtime.h>

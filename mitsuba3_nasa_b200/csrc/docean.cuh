@@ -237,13 +237,19 @@ MIB_D void bsdf_sample(const mib_bsdf &b, const SurfIt &si, float s1, float s2x,
         if constexpr (!POL) { for (int c = 0; c < NC; ++c) V[c] = w; }
         return;
     }
+    if (!has_r) {                                                      // diffuse.cpp:108-111: the diffuse lobe is disabled
+        bs.wo = v3(0.f); bs.pdf = 0.f; bs.eta = 0.f; bs.sampled = 0;
+        if constexpr (POL) m4_zero(V);
+        else { for (int c = 0; c < NC; ++c) V[c] = 0.f; }
+        return;
+    }
     bs.wo = square_to_cosine_hemisphere(s2x, s2y);                     // diffuse.cpp:101-126
     bs.pdf = kInvPi * bs.wo.z;
     bs.eta = 1.f;
     bs.sampled = kBsdfDiffuseRefl;
     const bool ok = si.wi.z > 0.f && bs.pdf > 0.f;
-    if constexpr (POL) { m4_zero(V); V[0] = ok ? b.reflectance[0] : 0.f; }
-    else { for (int c = 0; c < NC; ++c) V[c] = ok ? b.reflectance[NC == 3 ? c : 0] : 0.f; }
+    if constexpr (POL) { m4_zero(V); V[0] = ok ? bsdf_reflectance(b, si, 0) : 0.f; }
+    else { for (int c = 0; c < NC; ++c) V[c] = ok ? bsdf_reflectance(b, si, NC == 3 ? c : 0) : 0.f; }
 }
 template <int SPEC>
 MIB_D void bsdf_eval(const mib_bsdf &b, const SurfIt &si, V3 wo, float *V) {
@@ -257,8 +263,8 @@ MIB_D void bsdf_eval(const mib_bsdf &b, const SurfIt &si, V3 wo, float *V) {
         return;
     }
     const bool ok = b.type != MIB_BSDF_NULL && si.wi.z > 0.f && wo.z > 0.f;     // diffuse.cpp:128-160; null: 0
-    if constexpr (POL) { m4_zero(V); V[0] = ok ? b.reflectance[0] * kInvPi * wo.z : 0.f; }
-    else { for (int c = 0; c < NC; ++c) V[c] = ok ? b.reflectance[NC == 3 ? c : 0] * kInvPi * wo.z : 0.f; }
+    if constexpr (POL) { m4_zero(V); V[0] = ok ? bsdf_reflectance(b, si, 0) * kInvPi * wo.z : 0.f; }
+    else { for (int c = 0; c < NC; ++c) V[c] = ok ? bsdf_reflectance(b, si, NC == 3 ? c : 0) * kInvPi * wo.z : 0.f; }
 }
 
 // R += first column of (T * V) * Em, Em = the emitted Stokes vector as a matrix whose only non-zero column is the first

@@ -6,6 +6,7 @@
 #pragma once
 #include "dmath.cuh"
 #include "../../include/mi_b200.h"
+#include "dmesh.cuh"
 
 namespace mib {
 
@@ -58,6 +59,7 @@ struct SurfIt {
     V3 p, n, wi;
     Frame3 sh;
     int shape, face;
+    float tu, tv;          // texture coordinates (meshes, rectangles; only with FT_MESH)
 };
 MIB_D bool valid(const SurfIt &si) { return si.t != inf_f(); }
 
@@ -166,23 +168,44 @@ MIB_SUB_GEOM SurfIt si_finalize2(int shape, int face, float t, V3 p, V3 ray_d) {
 }
 MIB_D void si_finalize(V3 ray_d, SurfIt &si) { si = si_finalize2(si.shape, si.face, si.t, si.p, ray_d); }
 
-// Scene::ray_intersect: nearest analytic hit over the (few) shapes of the scene
+// Scene::ray_intersect: nearest hit over the (few) shapes of the scene -- analytic shapes, and triangle meshes (dmesh.cuh)
 MIB_SUB_GEOM SurfIt ray_intersect2(Ray ray) {
-    float best = inf_f();
+    float best = inf_f(), bu = 0.f, bv = 0.f;
     int bs = -1, bf = 0;
     for (int i = 0; i < sc.d.n_shapes; ++i) {
-        int face;
-        float t = intersect_shape(i, ray, face);
-        if (t < best) { best = t; bs = i; bf = face; }
+        int face = 0;
+        float t, u = 0.f, v = 0.f;
+        if (MIB_FT(FT_MESH) && sc.d.shapes[i].type == MIB_SHAPE_MESH)
+            t = intersect_mesh(sc.d.shapes[i], sc.buffers[sc.d.shapes[i].mesh_buffer], ray.o, ray.d, ray.maxt, face, u, v);
+        else
+            t = intersect_shape(i, ray, face);
+        if (t < best) { best = t; bs = i; bf = face; bu = u; bv = v; }
     }
     if (bs < 0) {
         SurfIt si;
-        si.t = best; si.shape = -1; si.face = 0;
+        si.t = best; si.shape = -1; si.face = 0; si.tu = 0.f; si.tv = 0.f;
         si.p = v3(0.f); si.n = v3(0.f); si.sh.s = v3(0.f); si.sh.t = v3(0.f); si.sh.n = v3(0.f);
         si.wi = -ray.d;
         return si;
     }
-    return si_finalize2(bs, bf, best, ray_at(ray, best), ray.d);
+    if (MIB_FT(FT_MESH) && sc.d.shapes[bs].type == MIB_SHAPE_MESH) {
+        SurfIt si;
+        si.t = best; si.shape = bs; si.face = bf;
+        const V3 dp_du = mesh_surface_interaction(sc.d.shapes[bs], sc.buffers[sc.d.shapes[bs].mesh_buffer], bf, bu, bv, si.p, si.n, si.sh.n, si.tu, si.tv);
+        frame_from_normal(si.sh.n, dp_du, si.sh.s, si.sh.t);
+        si.wi = to_local(si.sh, -ray.d);
+        return si;
+    }
+    SurfIt si = si_finalize2(bs, bf, best, ray_at(ray, best), ray.d);
+    si.tu = 0.f; si.tv = 0.f;
+    if (MIB_FT(FT_MESH) && sc.d.shapes[bs].type == MIB_SHAPE_RECTANGLE) {
+        // rectangle.cpp:559-560: uv = prim_uv * 0.5 + 0.5, prim_uv = the local hit position of the intersection routine
+        const mib_shape &s = sc.d.shapes[bs];
+        const V3 o = xform_point_affine(s.to_object, ray.o), d = xform_vector(s.to_object, ray.d);
+        si.tu = fma_(fma_(d.x, best, o.x), .5f, .5f);
+        si.tv = fma_(fma_(d.y, best, o.y), .5f, .5f);
+    }
+    return si;
 }
 MIB_D void ray_intersect(const Ray &ray, SurfIt &si) { si = ray_intersect2(ray); }
 

@@ -16,6 +16,17 @@ template <int SPEC> MIB_D float mis_weight(float a, float b) {               // 
     return isfinite(w) ? w : 0.f;
 }
 
+// Diffuse reflectance of channel c: a constant, or the checkerboard texture at the hit's uv (src/textures/checkerboard.cpp:66-84)
+MIB_D float bsdf_reflectance(const mib_bsdf &b, const SurfIt &si, int c) {
+    if (MIB_FT(FT_MESH) && b.texture == MIB_TEXTURE_CHECKERBOARD) {
+        const float u = fma_(b.to_uv[1], si.tv, fma_(b.to_uv[0], si.tu, b.to_uv[2])),
+                    v = fma_(b.to_uv[4], si.tv, fma_(b.to_uv[3], si.tu, b.to_uv[5]));
+        const bool mx = u - floorf(u) > .5f, my = v - floorf(v) > .5f;
+        return mx == my ? b.color0[c] : b.color1[c];
+    }
+    return b.reflectance[c];
+}
+
 // Null-BSDF Mueller matrix in world space: to_world_mueller(I, wi, wi) -> 2x2 block (see dspec.cuh)
 MIB_D void null_block(const SurfIt &si, float &b11, float &b12, float &b21, float &b22) {
     // in and out direction coincide (wo = -wi of a null BSDF is evaluated as to_world_mueller(I, wi, wi)): the two basis
@@ -113,7 +124,7 @@ MIB_D void sample_emitter(Pcg32 &rng, Counters &cnt, V3 ref_p, V3 ref_n, bool su
                 V3 wo = to_local(si.sh, emitter_d);
                 bool ok = si.wi.z > 0.f && wo.z > 0.f;
 #pragma unroll
-                for (int c = 0; c < NC; ++c) tr[c] *= ok ? bsdf.reflectance[NC == 3 ? c : 0] * kInvPi * wo.z : 0.f;
+                for (int c = 0; c < NC; ++c) tr[c] *= ok ? bsdf_reflectance(bsdf, si, NC == 3 ? c : 0) * kInvPi * wo.z : 0.f;
                 ray.d = emitter_d;
             } else {
 #pragma unroll
@@ -355,7 +366,7 @@ MIB_D void path_step(Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
                 float w = AOS ? 1.f : mis_weight<SPEC>(ds.pdf, ds.delta ? 0.f : bsdf_pdf);
 #pragma unroll
                 for (int r = 0; r < NR; ++r) {
-                    float bv = ok ? bsdf.reflectance[NC == 3 ? r : 0] * kInvPi * wo.z : 0.f;
+                    float bv = ok ? bsdf_reflectance(bsdf, si, NC == 3 ? r : 0) * kInvPi * wo.z : 0.f;
                     // (T * depol(bv)) col 0 = T(r,0) * bv
                     if (AOS) R[r] += (x[r] * bv) * emis<SPEC>(em, r);
                     else R[r] += ((x[r] * bv) * w) * emis<SPEC>(em, r);
@@ -382,7 +393,7 @@ MIB_D void path_step(Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
                 bool ok = si.wi.z > 0.f && bs_pdf > 0.f;
                 float v[NC];
 #pragma unroll
-                for (int c = 0; c < NC; ++c) v[c] = ok ? bsdf.reflectance[NC == 3 ? c : 0] : 0.f;
+                for (int c = 0; c < NC; ++c) v[c] = ok ? bsdf_reflectance(bsdf, si, NC == 3 ? c : 0) : 0.f;
                 T_mul_depol<SPEC>(T, v);
             }
             eta *= bs_eta;

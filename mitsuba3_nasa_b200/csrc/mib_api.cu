@@ -145,12 +145,51 @@ static bool has_dielectric(const mib_scene *s) {
     return false;
 }
 
+// triangle meshes / uv textures: walked by the forward one-thread-one-path kernels only (dmesh.cuh)
+static bool has_mesh(const mib_scene *s) {
+    const mib_scene_desc &d = s->ds.d;
+    for (int i = 0; i < d.n_shapes; ++i) if (d.shapes[i].type == MIB_SHAPE_MESH) return true;
+    for (int i = 0; i < d.n_bsdfs; ++i) if (d.bsdfs[i].texture != MIB_TEXTURE_UNIFORM) return true;
+    return false;
+}
+
+// volpathaos.cpp:262-285: ANY non-null BSDF event after which the ray keeps the sign of its z component counts as a
+// refraction through "the" interface and switches the refractive next-event estimation on or off -- meant for the ocean surface,
+// but a diffuse bounce off a surface that is not horizontal qualifies too.  Scenes where that can happen (a dielectric, or a
+// non-null BSDF on anything but a horizontal rectangle) are walked by the kernel that carries this state (docean.cuh).
+static bool aos_interface_state_needed(const mib_scene *s) {
+    const mib_scene_desc &d = s->ds.d;
+    if (has_dielectric(s)) return true;
+    for (int i = 0; i < d.n_shapes; ++i) {
+        const mib_shape &sh = d.shapes[i];
+        if (d.bsdfs[sh.bsdf].type == MIB_BSDF_NULL) continue;
+        if (sh.type != MIB_SHAPE_RECTANGLE) return true;
+        if (!(sh.frame_n[0] == 0.f && sh.frame_n[1] == 0.f && fabsf(sh.frame_n[2]) == 1.f)) return true;
+    }
+    return false;
+}
+
 static void commit(mib_scene *s) {
     mib_scene_desc &d = s->ds.d;
+    if (has_mesh(s) && d.integrator.type != MIB_INTEG_VOLPATH && d.integrator.type != MIB_INTEG_VOLPATHAOS)
+        throw std::runtime_error("triangle meshes and textured BSDFs are walked by the forward integrators (volpath, volpathaos) only");
+    for (int i = 0; i < d.n_shapes; ++i) {
+        const mib_shape &sh = d.shapes[i];
+        if (sh.type != MIB_SHAPE_MESH) continue;
+        const size_t V = (size_t) sh.mesh_vertices, F = (size_t) sh.mesh_faces, N = (size_t) sh.mesh_nodes;
+        const size_t need = 3 * V + ((sh.mesh_flags & MIB_MESH_HAS_NORMALS) ? 3 * V : 0) + ((sh.mesh_flags & MIB_MESH_HAS_TEXCOORDS) ? 2 * V : 0) + 3 * F + 8 * N + F;
+        if (sh.mesh_buffer < 0 || sh.mesh_buffer >= MIB_MAX_BUFFERS || !s->buf[sh.mesh_buffer] || s->buf_n[sh.mesh_buffer] < need || V == 0 || F == 0 || N == 0)
+            throw std::runtime_error("mesh: data buffer missing or too small for its vertex / face / node counts");
+        if (sh.emitter >= 0) throw std::runtime_error("mesh: area emitters on meshes are not implemented");
+    }
     // the ocean interface: walked by the forward volpathaos kernel of docean.cuh only
     if (has_dielectric(s) && d.integrator.type != MIB_INTEG_VOLPATHAOS)
         throw std::runtime_error("dielectric / roughdielectric BSDFs (the ocean interface) are walked by the volpathaos kernel only: "
                                  "volpath, prbvolpath and prb_volpathaos (the adjoint has no refractive next-event estimation) refuse them");
+    if (d.integrator.type == MIB_INTEG_PRBVOLPATHAOS && aos_interface_state_needed(s))
+        throw std::runtime_error("prb_volpathaos: scenes with a non-null BSDF on anything but a horizontal rectangle need the interface state of "
+                                 "volpathaos (a bounce that keeps the sign of d.z counts as a refraction, volpathaos.cpp:262-285); the adjoint "
+                                 "kernels do not carry it");
     for (int i = 0; i < MIB_MAX_BUFFERS; ++i) { s->ds.buffers[i] = s->buf[i]; s->ds.grad[i] = s->grad[i]; }
     for (int i = 0; i < d.n_media; ++i) {
         mib_medium &m = d.media[i];
@@ -362,7 +401,8 @@ static void launch_forward_pool(mib_scene *s, LaunchParams lp) {
 static bool forward_uses_pool(const mib_scene *s) {
     const int integ = s->ds.d.integrator.type;
     if (integ != MIB_INTEG_VOLPATH && integ != MIB_INTEG_VOLPATHAOS) return false;     // prb primal passes: per-thread kernel
-    if (has_dielectric(s)) return false;                                               // docean.cuh: per-thread kernel
+    if (integ == MIB_INTEG_VOLPATHAOS && aos_interface_state_needed(s)) return false;  // docean.cuh: per-thread kernel
+    if (has_mesh(s)) return false;                                                     // dmesh.cuh: per-thread kernel
     const char *k = getenv("MIB_FORWARD_KERNEL");
     bool pool = true;
     if (k && strcmp(k, "thread") == 0) pool = false;
@@ -392,7 +432,7 @@ static void dispatch_forward(mib_scene *s, const LaunchParams &lp) {
             if (spec == 0) launch_forward<0, 0>(s, lp); else if (spec == 1) launch_forward<1, 0>(s, lp); else launch_forward<2, 0>(s, lp);
             break;
         case MIB_INTEG_VOLPATHAOS:
-            if (has_dielectric(s)) {
+            if (aos_interface_state_needed(s)) {
                 if (spec == 0) launch_forward<0, 4>(s, lp); else if (spec == 1) launch_forward<1, 4>(s, lp); else launch_forward<2, 4>(s, lp);
                 break;
             }

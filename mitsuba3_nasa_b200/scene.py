@@ -9,6 +9,8 @@ defaults are those of the reference (citations next to each plugin below).
 `Scene.flatten()` turns the tree into the POD `mib_scene_desc` + float buffers
 consumed by the C ABI (include/mi_b200.h).
 """
+import os
+
 import numpy as np
 
 from . import _abi as A
@@ -42,6 +44,11 @@ def _luminance(rgb):
     return float(rgb[0] * 0.212671 + rgb[1] * 0.715160 + rgb[2] * 0.072169)
 
 
+# directories searched for relative file names of `obj` shapes (the role of the reference's FileResolver; the XML front end
+# resolves file names itself, xmlscene.py)
+SEARCH_PATHS = []
+
+
 class Plugin:
     """One instantiated plugin.  `props` holds the parameters (defaults applied)."""
     CATEGORY = {
@@ -55,9 +62,9 @@ class Plugin:
         'box': 'rfilter', 'gaussian': 'rfilter', 'tent': 'rfilter',
         'perspective': 'sensor', 'distant': 'sensor', 'radiancemeter': 'sensor',
         'constant': 'emitter', 'directional': 'emitter', 'area': 'emitter',
-        'cube': 'shape', 'rectangle': 'shape', 'sphere': 'shape',
+        'cube': 'shape', 'rectangle': 'shape', 'sphere': 'shape', 'obj': 'shape',
         'null': 'bsdf', 'diffuse': 'bsdf', 'dielectric': 'bsdf', 'roughdielectric': 'bsdf',
-        'uniform': 'texture', 'srgb': 'texture', 'rgb': 'texture', 'd65': 'texture',
+        'uniform': 'texture', 'srgb': 'texture', 'rgb': 'texture', 'd65': 'texture', 'checkerboard': 'texture',
         'scene': 'scene',
     }
 
@@ -412,8 +419,23 @@ class Scene:
             out.type = A.BSDF_NULL
         elif b.type == 'diffuse':
             out.type = A.BSDF_DIFFUSE
-            out.reflectance[:] = self._color(pr.child('reflectance') or pr.get('reflectance', 0.5), key)
-            self.params[key + '.reflectance.value'] = {'kind': 'bsdf_reflectance', 'bsdf': out}
+            refl = pr.child('reflectance')
+            if refl is not None and refl.type == 'checkerboard':
+                # src/textures/checkerboard.cpp:58-84
+                tp = _Props(refl)
+                out.texture = A.TEXTURE_CHECKERBOARD
+                out.color0[:] = self._color(tp.child('color0') or tp.get('color0', 0.4), key)
+                out.color1[:] = self._color(tp.child('color1') or tp.get('color1', 0.2), key)
+                to_uv = tp.get('to_uv')
+                m = np.eye(3) if to_uv is None else np.asarray(getattr(to_uv, 'matrix', to_uv), dtype=np.float64)
+                if m.shape == (4, 4):                  # the XML parser reads every <transform> as 4 x 4: keep the 2D affine part
+                    m = np.array([[m[0, 0], m[0, 1], m[0, 3]], [m[1, 0], m[1, 1], m[1, 3]], [0, 0, 1.0]])
+                out.to_uv[:] = m[:2, :].astype(np.float32).reshape(-1).tolist()
+                out.reflectance[:] = [0.5 * (a + b) for a, b in zip(out.color0[:], out.color1[:])]      # mean()
+                tp.finish()
+            else:
+                out.reflectance[:] = self._color(refl or pr.get('reflectance', 0.5), key)
+                self.params[key + '.reflectance.value'] = {'kind': 'bsdf_reflectance', 'bsdf': out}
         elif b.type in ('dielectric', 'roughdielectric'):
             # src/bsdfs/dielectric.cpp:210-222, roughdielectric.cpp:166-218 (the ocean interface of the AOS scenes)
             int_ior = _lookup_ior(pr.get('int_ior', 'bk7'))
@@ -466,7 +488,26 @@ class Scene:
         to_world = _to_transform(pr.get('to_world'))
         if pr.get('flip_normals', False):
             to_world = to_world @ ScalarTransform4f.scale([1, 1, -1])
-        out.type = {'cube': A.SHAPE_CUBE, 'rectangle': A.SHAPE_RECTANGLE, 'sphere': A.SHAPE_SPHERE}[s.type]
+        out.type = {'cube': A.SHAPE_CUBE, 'rectangle': A.SHAPE_RECTANGLE, 'sphere': A.SHAPE_SPHERE, 'obj': A.SHAPE_MESH}[s.type]
+        out.mesh_buffer = -1
+        mesh = None
+        if s.type == 'obj':
+            # src/shapes/obj.cpp: world-space triangle mesh + our BVH in one buffer (mesh.py)
+            from . import mesh as M
+            fname = pr.get('filename', required=True)
+            if not os.path.isabs(fname) and not os.path.exists(fname):
+                for d in self.search_paths:
+                    if os.path.exists(os.path.join(d, fname)):
+                        fname = os.path.join(d, fname)
+                        break
+            try:
+                mesh = M.load_obj(fname, to_world.matrix, face_normals=bool(pr.get('face_normals', False)),
+                                  flip_tex_coords=bool(pr.get('flip_tex_coords', True)))
+            except (FileNotFoundError, ValueError) as e:
+                raise PluginError(str(e))
+            slot = self._new_buffer(mesh.pack())
+            out.mesh_buffer, out.mesh_vertices, out.mesh_faces = slot, len(mesh.positions), len(mesh.faces)
+            out.mesh_nodes, out.mesh_flags = len(mesh.nodes), mesh.flags
         if s.type == 'sphere':
             c = np.asarray(pr.get('center', [0, 0, 0]), dtype=np.float64)
             r = float(pr.get('radius', 1.0))
@@ -495,7 +536,10 @@ class Scene:
             out.emitter = self._emitter(ems[0][1], key + '.emitter', shape=i)
         pr.finish()
         # world-space bbox corners for the scene bounding sphere
-        if s.type == 'rectangle':
+        if s.type == 'obj':
+            lo, hi = mesh.bbox()
+            pts = [lo.astype(np.float64), hi.astype(np.float64)]
+        elif s.type == 'rectangle':
             pts = [to_world @ [x, y, 0] for x in (-1, 1) for y in (-1, 1)]
         elif s.type == 'cube':
             pts = [to_world @ [x, y, z] for x in (-1, 1) for y in (-1, 1) for z in (-1, 1)]
@@ -699,6 +743,7 @@ class Scene:
         d.spectrum = self.spectrum
         d.environment = -1
         self._bbox_pts = []
+        self.search_paths = list(SEARCH_PATHS)
         root = self.root
         integrator = sensor = None
         pending_emitters = []

@@ -327,7 +327,7 @@ def _emit(lines, indent, key, v, out_dir, counter):
             cat = Plugin.CATEGORY.get(t)
             if cat is None:
                 raise XMLError('dict_to_xml: unknown plugin "%s"' % t)
-            tag = 'spectrum' if cat == 'texture' else cat
+            tag = 'spectrum' if cat == 'texture' and t != 'checkerboard' else cat
             attrs = ' type="%s"' % t
             if 'id' in v:
                 attrs += ' id="%s"' % v['id']

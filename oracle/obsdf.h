@@ -28,7 +28,18 @@ template <int SPEC> struct BSDF {
     using Tr = SpecTraits<SPEC>;
     using Spec = typename Tr::Spec;
     using USpec = typename Tr::USpec;
-    static USpec reflectance(const mib_bsdf &b) { USpec r; for (int c = 0; c < Tr::NC; ++c) r.v[c] = b.reflectance[Tr::NC == 3 ? c : 0]; return r; }
+    // diffuse reflectance: a constant, or the checkerboard texture (src/textures/checkerboard.cpp:66-84) at si.uv
+    static USpec reflectance(const mib_bsdf &b, const SurfaceInteraction &si) {
+        const float *src = b.reflectance;
+        if (b.texture == MIB_TEXTURE_CHECKERBOARD) {
+            // Transform3f::transform_affine(Point2f): column 2, then fmadd of columns 0 and 1
+            float u = fmadd(b.to_uv[1], si.uv[1], fmadd(b.to_uv[0], si.uv[0], b.to_uv[2])),
+                  v = fmadd(b.to_uv[4], si.uv[1], fmadd(b.to_uv[3], si.uv[0], b.to_uv[5]));
+            bool mx = u - std::floor(u) > .5f, my = v - std::floor(v) > .5f;
+            src = mx == my ? b.color0 : b.color1;
+        }
+        USpec r; for (int c = 0; c < Tr::NC; ++c) r.v[c] = src[Tr::NC == 3 ? c : 0]; return r;
+    }
     static Spec pick(float w, const Mueller &W) { if constexpr (Tr::POL) return W; else { (void) W; return Spec(w); } }
     static RoughDielectric rough(const mib_bsdf &b) { return RoughDielectric{ b.distribution, b.alpha_u, b.alpha_v, b.eta }; }
 
@@ -51,6 +62,10 @@ template <int SPEC> struct BSDF {
             bs.wo = d.wo; bs.pdf = d.pdf; bs.eta = d.eta; bs.sampled_type = d.sampled_type; bs.value = pick(d.weight, d.weight_pol);
             return bs;
         }
+        // diffuse.cpp:108-111: nothing is sampled when the context disables the diffuse reflection lobe -- volpathaos asks any
+        // BSDF it took for "the refractive one" for its transmission lobes only (volpathaos.cpp:262-285,318-326: a diffuse
+        // bounce off a surface that is not horizontal counts as a refraction there)
+        if (!(ctx_mask & 1)) return bs;
         // JIT variants have no early exit: all fields are written for every lane and
         // only the value is masked by (cos_theta_i > 0 && pdf > 0) (diffuse.cpp:101-126)
         float cos_theta_i = si.wi.z;
@@ -58,7 +73,7 @@ template <int SPEC> struct BSDF {
         bs.pdf = InvPi * bs.wo.z;
         bs.eta = 1.f;
         bs.sampled_type = BSDF_DiffuseReflection;
-        bs.value = Depol<Spec, Tr::NC>::make((cos_theta_i > 0.f && bs.pdf > 0.f) ? reflectance(b) : USpec(0.f));
+        bs.value = Depol<Spec, Tr::NC>::make((cos_theta_i > 0.f && bs.pdf > 0.f) ? reflectance(b, si) : USpec(0.f));
         return bs;
     }
     static Spec eval(const mib_bsdf &b, const SurfaceInteraction &si, Vec3 wo) {
@@ -76,7 +91,7 @@ template <int SPEC> struct BSDF {
         }
         float cos_theta_i = si.wi.z, cos_theta_o = wo.z;
         if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) return zero;
-        USpec value = reflectance(b) * InvPi * cos_theta_o;
+        USpec value = reflectance(b, si) * InvPi * cos_theta_o;
         return Depol<Spec, Tr::NC>::make(value);
     }
     static float pdf(const mib_bsdf &b, const SurfaceInteraction &si, Vec3 wo) {

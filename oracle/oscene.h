@@ -170,6 +170,7 @@ struct SurfaceInteraction {
     Vec3 p, n, wi;
     Frame sh_frame;
     int shape = -1;
+    float uv[2] = { 0.f, 0.f };         // texture coordinates (meshes, rectangles)
     bool is_valid() const { return t != Inf; }
 };
 
@@ -198,6 +199,10 @@ static inline void finalize_si(SurfaceInteraction &si, Vec3 dp_du, const Ray &ra
     si.sh_frame.t = cross(n, si.sh_frame.s);
     si.wi = si.sh_frame.to_local(-ray.d);
 }
+
+} // namespace orc
+#include "omesh.h"
+namespace orc {
 
 // Shapes.  rectangle: src/shapes/rectangle.cpp:449-470,497-568 (AD branch: p = ray(t)).
 // cube / sphere: analytic (the reference's cube is a 12-triangle mesh traced by
@@ -250,18 +255,32 @@ static bool g_scalar_shapes = false;
 
 static inline SurfaceInteraction ray_intersect(const Scene &sc, const Ray &ray) {
     SurfaceInteraction si;
-    float best = Inf; int best_shape = -1, best_face = 0;
+    float best = Inf, best_u = 0.f, best_v = 0.f; int best_shape = -1, best_face = 0;
     for (int i = 0; i < sc.d.n_shapes; ++i) {
-        int face;
-        float t = intersect_shape(sc, i, ray, &face);
-        if (t < best) { best = t; best_shape = i; best_face = face; }
+        int face = 0;
+        float t, bu = 0.f, bv = 0.f;
+        if (sc.d.shapes[i].type == MIB_SHAPE_MESH)
+            t = intersect_mesh(sc.d.shapes[i], sc.buffers[sc.d.shapes[i].mesh_buffer], ray, ray.maxt, &face, &bu, &bv);
+        else
+            t = intersect_shape(sc, i, ray, &face);
+        if (t < best) { best = t; best_shape = i; best_face = face; best_u = bu; best_v = bv; }
     }
     if (best_shape < 0) { si.wi = -ray.d; return si; }
     const mib_shape &s = sc.d.shapes[best_shape];
     si.t = best; si.shape = best_shape;
     si.p = ray.at(best);
     Vec3 dp_du;
+    if (s.type == MIB_SHAPE_MESH) {
+        dp_du = mesh_surface_interaction(s, sc.buffers[s.mesh_buffer], best_face, best_u, best_v, &si.p, &si.n, &si.sh_frame.n, si.uv);
+        finalize_si(si, dp_du, ray);
+        return si;
+    }
     if (s.type == MIB_SHAPE_RECTANGLE) {
+        {   // rectangle.cpp:559-560: uv = prim_uv * 0.5 + 0.5, prim_uv = the local hit position of the intersection routine
+            const Mat4 &T = sc.shape_to_object[best_shape];
+            Vec3 local = fmadd(transform_vector(T, ray.d), best, transform_point_affine(T, ray.o));
+            si.uv[0] = fmadd(local.x, .5f, .5f); si.uv[1] = fmadd(local.y, .5f, .5f);
+        }
         si.n = Vec3(s.frame_n[0], s.frame_n[1], s.frame_n[2]);
         dp_du = Vec3(s.frame_s[0], s.frame_s[1], s.frame_s[2]);
         if (g_scalar_shapes) {

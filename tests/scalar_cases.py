@@ -6,6 +6,8 @@ A case: name -> dict(variant=..., scene=<load_dict dictionary>, spp=..., seed=..
 Seeds follow the reference's scalar render loop (integrator.cpp:230, 1103-1123): the film is one block, pixel (x, y) is
 pixel i = morton_encode(x, y) of the block and draws its spp samples from PCG32(initstate = seed * W * H + i, default
 stream).  render_1 (integrator.cpp:510-551 with one thread): one stream seeded `seed`, spp samples."""
+import os
+
 import numpy as np
 
 from mitsuba3_nasa_b200 import scenes
@@ -48,6 +50,39 @@ def cloud_no_plateau(n=32):
     g = scenes.cloud_grid(n)
     ramp = 1.0 - 0.3 * (np.arange(n, dtype=np.float32) + 0.5) / n
     return (g * ramp[None, None, :, None]).astype(np.float32)
+
+
+MESH_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "meshes")
+
+
+def mesh_scene(hetero=False, res=16):
+    m = lambda n: os.path.join(MESH_DIR, n)
+    if hetero:
+        medium = {'type': 'heterogeneous', 'scale': 3.0, 'albedo': 0.9, 'phase': {'type': 'hg', 'g': 0.4},
+                  'sigma_t': {'type': 'gridvolume', 'data': _grid(8, 11), 'to_world': T.translate([-1, -1, 0.2]) @ T.scale(2.0)}}
+    else:
+        medium = {'type': 'homogeneous', 'scale': 1.5, 'sigma_t': {'type': 'rgb', 'value': [0.5, 0.7, 1.0]},
+                  'albedo': {'type': 'rgb', 'value': [0.9, 0.8, 0.6]}, 'phase': {'type': 'isotropic'}}
+    return {
+        'type': 'scene',
+        'integrator': {'type': 'volpath', 'max_depth': 8, 'rr_depth': 5},
+        'sensor': {'type': 'perspective', 'fov': 40.0, 'near_clip': 0.1, 'far_clip': 100.0,
+                   'to_world': T.look_at(origin=[6.0, -5.0, 4.0], target=[0.0, 0.0, 0.8], up=[0, 0, 1]),
+                   'film': {'type': 'hdrfilm', 'width': res, 'height': res, 'rfilter': {'type': 'box'}},
+                   'sampler': {'type': 'independent', 'sample_count': 16}},
+        'emitter': {'type': 'constant', 'radiance': {'type': 'rgb', 'value': [1.0, 0.9, 0.8]}},
+        'medium1': medium,
+        'container': {'type': 'obj', 'filename': m('box.obj'), 'to_world': T.translate([0, 0, 1.2]), 'bsdf': {'type': 'null'},
+                      'interior': {'type': 'ref', 'id': 'medium1'}},
+        'ball': {'type': 'obj', 'filename': m('sphere.obj'), 'to_world': T.translate([2.2, 0.5, 0.7]) @ T.scale(0.7),
+                 'bsdf': {'type': 'diffuse', 'reflectance': {'type': 'rgb', 'value': [0.7, 0.3, 0.2]}}},
+        'crate': {'type': 'obj', 'filename': m('box_no_normals.obj'), 'to_world': T.translate([-2.0, 1.5, 0.4]) @ T.rotate([0, 0, 1], 30.0) @ T.scale(0.4),
+                  'bsdf': {'type': 'diffuse', 'reflectance': {'type': 'rgb', 'value': [0.2, 0.5, 0.7]}}},
+        'floor': {'type': 'obj', 'filename': m('ground.obj'),
+                  'bsdf': {'type': 'diffuse', 'reflectance': {'type': 'checkerboard', 'color0': {'type': 'rgb', 'value': [0.2, 0.2, 0.2]},
+                                                               'color1': {'type': 'rgb', 'value': [0.8, 0.8, 0.8]},
+                                                               'to_uv': T.scale([8, 8, 8])}}},
+    }
 
 
 def cases():
@@ -112,6 +147,16 @@ def cases():
     c['ocean_smooth_pol'] = dict(variant='scalar_mono_polarized', scene=scenes.aos_ocean(rough=False), spp=1024, seed=3, kind='samples')
     c['ocean_smooth_mono'] = dict(variant='scalar_mono', scene=scenes.aos_ocean(rough=False, view_zenith_deg=55.0), spp=512, seed=1, kind='samples')
     c['ocean_rough_pol_render1'] = dict(variant='scalar_mono_polarized', scene=scenes.aos_ocean(rough=True), spp=20000, seed=2, kind='render1')
+    # triangle meshes (tests/golden/meshes, written by tests/golden/make_meshes.py): a box of quads with
+    # per-face normals bounding a homogeneous medium, a smooth uv-sphere, a textured ground quad with a checkerboard, a box
+    # without normals; perspective sensor
+    c['mesh_medium'] = dict(variant='scalar_rgb', scene=mesh_scene(), spp=16, seed=0, kind='samples')
+    c['mesh_hetero_mono'] = dict(variant='scalar_mono', scene=mesh_scene(hetero=True, res=12), spp=8, seed=3, kind='samples')
+    d = mesh_scene(res=12)
+    d['integrator']['type'] = 'volpathaos'
+    d['emitter'] = {'type': 'directional', 'direction': [0.3, 0.2, -1.0], 'irradiance': 2.0}
+    d['medium1']['phase'] = {'type': 'rayleigh'}
+    c['mesh_aos_pol_sun'] = dict(variant='scalar_mono_polarized', scene=d, spp=16, seed=5, kind='samples')
     # radiancemeter looking through the cube
     d = scenes.c1_homogeneous_cube(res=1, spp=64, max_depth=16)
     d['sensor'] = {'type': 'radiancemeter', 'origin': [0.2, 0.1, 4.0], 'direction': [-0.05, 0.0, -1.0],

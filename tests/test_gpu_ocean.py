@@ -70,6 +70,27 @@ def test_render_1_agrees_with_the_reference_render_1():
     assert np.abs(stokes - ref).max() <= 0.05 * ref[0]
 
 
+def test_a_diffuse_bounce_that_keeps_the_sign_of_dz_counts_as_a_refraction():
+    """volpathaos.cpp:262-285 applies its "refraction occurred" test to every non-null BSDF event: after a diffuse bounce off a
+    surface that is not horizontal the next-event estimation asks the diffuse BSDF for a transmission lobe and gets nothing
+    (diffuse.cpp:108-111).  Pinned on the reference's scalar build (tests/scalar_cases.py mesh_aos_pol_sun); here with an
+    analytic sphere: the kernel that carries the interface state must be the one that runs, and it must equal the oracle."""
+    from mitsuba3_nasa_b200.transforms import ScalarTransform4f as T
+    d = scenes.c2_rayleigh_slab(spp=4)
+    d['ball'] = {'type': 'sphere', 'center': [0.0, 0.0, 0.5], 'radius': 0.3,
+                 'bsdf': {'type': 'diffuse', 'reflectance': 0.8}}
+    sc = S.load_dict(d, "llvm_ad_mono_polarized")
+    dev = _lib.DeviceScene(sc, 0)
+    assert dev.forward_kernel() == "thread"
+    g = dev.sample_lanes(1, 4096, 0, 4096).astype(np.float64)
+    o = OracleScene(sc).sample_lanes(1, 4096, 0, 4096).astype(np.float64)
+    bad = (np.abs(g - o) > 1e-4 * np.maximum(np.abs(o).max(axis=1, keepdims=True), 1e-6)).any(axis=1)
+    print("over tolerance", bad.sum())
+    assert bad.mean() <= 2e-3
+    # and the plain C2 scene (horizontal diffuse ground only) stays on the pool kernel
+    assert _lib.DeviceScene(S.load_dict(scenes.c2_rayleigh_slab(spp=4), "llvm_ad_mono_polarized"), 0).forward_kernel() == "pool"
+
+
 @pytest.mark.parametrize("integrator", ["volpath", "prb_volpathaos"])
 def test_other_integrators_refuse_dielectrics(integrator):
     d = scenes.aos_ocean()
