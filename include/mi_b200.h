@@ -65,7 +65,8 @@ enum { MIB_FILTER_NEAREST = 0, MIB_FILTER_TRILINEAR = 1 };
 enum { MIB_WRAP_REPEAT = 0, MIB_WRAP_MIRROR = 1, MIB_WRAP_CLAMP = 2 };
 enum { MIB_PHASE_ISOTROPIC = 0, MIB_PHASE_HG = 1, MIB_PHASE_RAYLEIGH = 2,
        MIB_PHASE_TABPHASE = 3, MIB_PHASE_TABPHASE_POLARIZED = 4 };
-enum { MIB_EMITTER_CONSTANT = 0, MIB_EMITTER_DIRECTIONAL = 1, MIB_EMITTER_AREA = 2 };
+enum { MIB_EMITTER_CONSTANT = 0, MIB_EMITTER_DIRECTIONAL = 1, MIB_EMITTER_AREA = 2, MIB_EMITTER_ENVMAP = 3 };
+#define MIB_MAX_ENV_LEVELS 16
 enum { MIB_SENSOR_PERSPECTIVE = 0, MIB_SENSOR_DISTANT = 1, MIB_SENSOR_RADIANCEMETER = 2 };
 enum { MIB_RFILTER_BOX = 0, MIB_RFILTER_GAUSSIAN = 1, MIB_RFILTER_TENT = 2 };
 enum { MIB_RNG_ARGS_LEFT_TO_RIGHT = 0, MIB_RNG_ARGS_RIGHT_TO_LEFT = 1 };
@@ -162,6 +163,20 @@ typedef struct mib_emitter {
     float   bsphere_center[3];
     float   bsphere_radius;  /* after set_scene (constant.cpp:70-85, directional.cpp:98-108) */
     int32_t shape;           /* area emitter: owning shape */
+    /* environment map (src/emitters/envmap.cpp), ONE float buffer: texels [H][W][3] (W = file width + 1: the
+       last column repeats the first, envmap.cpp:217-224; mono variants hold the luminance in all three channels) followed by the
+       levels of the luminance warp (Hierarchical2D<Float, 0>, include/mitsuba/core/distr_2d.h:344-500): level 0 = the
+       normalised W x H interpolant, levels 1.. = the 2 x 2-blocked MIP hierarchy of patch integrals, each level at
+       env_level_offset[l] (in floats from the start of the buffer) with row pitch env_level_width[l].  Built by the host
+       side (mitsuba3_nasa_b200/envmap.py). */
+    int32_t env_buffer;      /* buffer slot, -1: not an envmap */
+    int32_t env_res[2];      /* W, H */
+    float   env_scale;
+    float   env_to_world[16];
+    float   env_to_local[16];
+    int32_t env_levels;      /* number of levels incl. level 0 */
+    int32_t env_level_offset[MIB_MAX_ENV_LEVELS];
+    int32_t env_level_width[MIB_MAX_ENV_LEVELS];
 } mib_emitter;
 
 typedef struct mib_sensor {

@@ -4,6 +4,7 @@
 // src/sensors/{perspective,distant,radiancemeter}.cpp, include/mitsuba/core/warp.h.
 #pragma once
 #include "dspec.cuh"
+#include "denvmap.cuh"
 
 namespace mib {
 
@@ -213,6 +214,27 @@ MIB_DH void sample_emitter_direction(V3 ref_p, float sx, float sy, DirSample<NC>
         float ip = rcp_(ds.pdf);
 #pragma unroll
         for (int c2 = 0; c2 < NC; ++c2) spec[c2] = e.radiance[NC == 3 ? c2 : 0] * ip;
+    } else if (MIB_FT(FT_MESH) && e.type == MIB_EMITTER_ENVMAP) {
+        // envmap.cpp:404-446
+        const float *buf = sc.buffers[e.env_buffer];
+        float u, v, pdf;
+        env_warp_sample(e, buf, sx, sy, u, v, pdf);
+        u += div_(.5f, (float) (e.env_res[0] - 1));
+        const bool act = pdf > 0.f;
+        float st, ct, sp, cp;
+        sincos_(v * kPi, st, ct); sincos_(u * kTwoPi, sp, cp);
+        const V3 dl = v3(sp * st, ct, -(cp * st));
+        V3 c = v3(e.bsphere_center[0], e.bsphere_center[1], e.bsphere_center[2]);
+        float radius = fmaxf(e.bsphere_radius, norm(ref_p - c)), dist = 2.f * radius;
+        const float inv_sin_theta = env_inv_sin_theta(dl);
+        const V3 d = xform_vector(e.env_to_world, dl);
+        ds.p = vfma(d, dist, ref_p); ds.delta = false; ds.d = d; ds.dist = dist;
+        ds.pdf = act ? pdf * inv_sin_theta * (1.f / (2.f * kPi * kPi)) : 0.f;
+        float val[NC];
+        env_eval_spectrum<NC>(e, buf, u, v, val);
+        const float ip = rcp_(ds.pdf);
+#pragma unroll
+        for (int c2 = 0; c2 < NC; ++c2) spec[c2] = act ? val[c2] * ip : 0.f;
     } else if (e.type == MIB_EMITTER_DIRECTIONAL) {
         V3 d = v3(e.direction[0], e.direction[1], e.direction[2]);
         float dist = inf_f();
@@ -246,11 +268,20 @@ MIB_DH void sample_emitter_direction(V3 ref_p, float sx, float sy, DirSample<NC>
 }
 // scene.cpp:355-366 with constant.cpp:139-144 / directional (0) / area.cpp:145-173: DirectionSample3f(scene, si, ref)
 // (d = (si.p - ref.p) / dist, n = si.sh_frame.n) and Shape::pdf_direction (shape.cpp:377-388)
-MIB_D float pdf_emitter_direction(int emitter, V3 ref_p, V3 si_p, V3 si_n) {
+MIB_D float pdf_emitter_direction(int emitter, V3 ref_p, V3 si_p, V3 si_n, V3 minus_wi) {
     const mib_emitter &e = sc.d.emitters[emitter];
     float pmf = sc.d.n_emitters > 1 ? rcp_((float) sc.d.n_emitters) : 1.f;
     float pdf = 0.f;
     if (e.type == MIB_EMITTER_CONSTANT) pdf = kInvFourPi;
+    else if (MIB_FT(FT_MESH) && e.type == MIB_EMITTER_ENVMAP) {
+        // envmap.cpp:448-463 with ds.d = -si.wi of the ray that left the scene
+        float u, v;
+        V3 d;
+        env_dir_to_uv(e, minus_wi, u, v, d);
+        u -= div_(.5f, (float) (e.env_res[0] - 1));
+        u -= floorf(u); v -= floorf(v);
+        pdf = env_warp_eval(e, sc.buffers[e.env_buffer], u, v) * env_inv_sin_theta(d) * (1.f / (2.f * kPi * kPi));
+    }
     else if (MIB_FT(FT_AREA) && e.type == MIB_EMITTER_AREA) {
         V3 rel = si_p - ref_p;
         float dist = norm(rel);
@@ -262,8 +293,15 @@ MIB_D float pdf_emitter_direction(int emitter, V3 ref_p, V3 si_p, V3 si_n) {
     return pdf * pmf;
 }
 // Emitter::eval at a hit, channel r: the area light is one-sided (area.cpp:83-90)
-template <int NC> MIB_D float emitter_eval(const mib_emitter &e, int r, float cos_theta_wi) {
+template <int NC> MIB_D float emitter_eval(const mib_emitter &e, int r, float cos_theta_wi, V3 minus_wi) {
     if (MIB_FT(FT_AREA) && e.type == MIB_EMITTER_AREA && !(cos_theta_wi > 0.f)) return 0.f;
+    if (MIB_FT(FT_MESH) && e.type == MIB_EMITTER_ENVMAP) {                   // envmap.cpp:343-354
+        float u, v, val[NC];
+        V3 l;
+        env_dir_to_uv(e, minus_wi, u, v, l);
+        env_eval_spectrum<NC>(e, sc.buffers[e.env_buffer], u, v, val);
+        return val[NC == 3 ? r : 0];
+    }
     return e.radiance[NC == 3 ? r : 0];
 }
 MIB_D int si_emitter(const SurfIt &si) {

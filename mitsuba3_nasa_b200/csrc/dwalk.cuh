@@ -335,14 +335,14 @@ MIB_D void path_step(Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
             int emitter = si_emitter(si);
             if (emitter >= 0 && !(depth == 0u && I.hide_emitters)) {
                 float emitter_pdf = 1.0f;
-                if (!count_direct) emitter_pdf = pdf_emitter_direction(emitter, st.last_p, si.p, si.sh.n);
+                if (!count_direct) emitter_pdf = pdf_emitter_direction(emitter, st.last_p, si.p, si.sh.n, -si.wi);
                 const mib_emitter &e = sc.d.emitters[emitter];
                 float x[NR];
                 T_col0<SPEC>(T, x);
                 float w = mis_weight<SPEC>(last_pdf, emitter_pdf);
 #pragma unroll
                 for (int r = 0; r < NR; ++r) {
-                    float er = emitter_eval<NC>(e, r, si.wi.z);
+                    float er = emitter_eval<NC>(e, r, si.wi.z, -si.wi);
                     R[r] += count_direct ? x[r] * er : (x[r] * w) * er;
                 }
             }

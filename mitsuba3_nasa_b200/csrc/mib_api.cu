@@ -150,6 +150,7 @@ static bool has_mesh(const mib_scene *s) {
     const mib_scene_desc &d = s->ds.d;
     for (int i = 0; i < d.n_shapes; ++i) if (d.shapes[i].type == MIB_SHAPE_MESH) return true;
     for (int i = 0; i < d.n_bsdfs; ++i) if (d.bsdfs[i].texture != MIB_TEXTURE_UNIFORM) return true;
+    for (int i = 0; i < d.n_emitters; ++i) if (d.emitters[i].type == MIB_EMITTER_ENVMAP) return true;
     return false;
 }
 
@@ -172,7 +173,7 @@ static bool aos_interface_state_needed(const mib_scene *s) {
 static void commit(mib_scene *s) {
     mib_scene_desc &d = s->ds.d;
     if (has_mesh(s) && d.integrator.type != MIB_INTEG_VOLPATH && d.integrator.type != MIB_INTEG_VOLPATHAOS)
-        throw std::runtime_error("triangle meshes and textured BSDFs are walked by the forward integrators (volpath, volpathaos) only");
+        throw std::runtime_error("triangle meshes, textured BSDFs and environment maps are walked by the forward integrators (volpath, volpathaos) only");
     for (int i = 0; i < d.n_shapes; ++i) {
         const mib_shape &sh = d.shapes[i];
         if (sh.type != MIB_SHAPE_MESH) continue;
@@ -181,6 +182,15 @@ static void commit(mib_scene *s) {
         if (sh.mesh_buffer < 0 || sh.mesh_buffer >= MIB_MAX_BUFFERS || !s->buf[sh.mesh_buffer] || s->buf_n[sh.mesh_buffer] < need || V == 0 || F == 0 || N == 0)
             throw std::runtime_error("mesh: data buffer missing or too small for its vertex / face / node counts");
         if (sh.emitter >= 0) throw std::runtime_error("mesh: area emitters on meshes are not implemented");
+    }
+    for (int i = 0; i < d.n_emitters; ++i) {
+        const mib_emitter &e = d.emitters[i];
+        if (e.type != MIB_EMITTER_ENVMAP) continue;
+        const size_t texels = (size_t) 3 * (size_t) e.env_res[0] * (size_t) e.env_res[1];
+        if (e.env_buffer < 0 || e.env_buffer >= MIB_MAX_BUFFERS || !s->buf[e.env_buffer] || e.env_res[0] < 3 || e.env_res[1] < 3 ||
+            e.env_levels < 2 || e.env_levels > MIB_MAX_ENV_LEVELS || (size_t) e.env_level_offset[0] != texels ||
+            s->buf_n[e.env_buffer] < texels + (size_t) e.env_res[0] * (size_t) e.env_res[1])
+            throw std::runtime_error("envmap: data buffer missing or inconsistent with its resolution / warp levels");
     }
     // the ocean interface: walked by the forward volpathaos kernel of docean.cuh only
     if (has_dielectric(s) && d.integrator.type != MIB_INTEG_VOLPATHAOS)

@@ -61,7 +61,7 @@ class Plugin:
         'independent': 'sampler', 'hdrfilm': 'film',
         'box': 'rfilter', 'gaussian': 'rfilter', 'tent': 'rfilter',
         'perspective': 'sensor', 'distant': 'sensor', 'radiancemeter': 'sensor',
-        'constant': 'emitter', 'directional': 'emitter', 'area': 'emitter',
+        'constant': 'emitter', 'directional': 'emitter', 'area': 'emitter', 'envmap': 'emitter',
         'cube': 'shape', 'rectangle': 'shape', 'sphere': 'shape', 'obj': 'shape',
         'null': 'bsdf', 'diffuse': 'bsdf', 'dielectric': 'bsdf', 'roughdielectric': 'bsdf',
         'uniform': 'texture', 'srgb': 'texture', 'rgb': 'texture', 'd65': 'texture', 'checkerboard': 'texture',
@@ -557,8 +557,46 @@ class Scene:
         self.desc.n_emitters += 1
         out = self.desc.emitters[i]
         out.shape = shape
+        out.env_buffer = -1
         pr = _Props(e)
-        if e.type == 'constant':
+        if e.type == 'envmap':
+            # src/emitters/envmap.cpp:108-232: texels + luminance warp in one buffer (envmap.py)
+            from . import envmap as EM, exr
+            out.type = A.EMITTER_ENVMAP
+            if self.desc.environment >= 0:
+                raise PluginError("Only one environment emitter can be specified per scene.")
+            self.desc.environment = i
+            if pr.has('data'):
+                rgb = np.asarray(pr.get('data'), np.float32)
+            else:
+                fname = pr.get('filename', required=True)
+                if not os.path.isabs(fname) and not os.path.exists(fname):
+                    for d_ in self.search_paths:
+                        if os.path.exists(os.path.join(d_, fname)):
+                            fname = os.path.join(d_, fname)
+                            break
+                if not os.path.exists(fname):
+                    raise PluginError('envmap: file "%s" not found' % fname)
+                img, names = exr.read_exr(fname)
+                idx = [names.index(c) for c in ('R', 'G', 'B')] if all(c in names for c in 'RGB') else [0] * 3
+                rgb = np.ascontiguousarray(img[..., idx], np.float32)
+            if rgb.ndim != 3 or rgb.shape[2] != 3:
+                raise PluginError("envmap: expected an RGB image")
+            try:
+                buf, W, H, offs, widths = EM.build(rgb, mono=self.spectrum != A.SPEC_RGB)
+            except ValueError as ex:
+                raise PluginError("envmap: %s" % ex)
+            out.env_buffer = self._new_buffer(buf)
+            out.env_res[:] = [W, H]
+            out.env_scale = float(pr.get('scale', 1.0))
+            tw = _to_transform(pr.get('to_world'))
+            out.env_to_world[:] = tw.f32().reshape(-1).tolist()
+            out.env_to_local[:] = tw.inverse().f32().reshape(-1).tolist()
+            out.env_levels = len(offs)
+            for k, (o_, w_) in enumerate(zip(offs, widths)):
+                out.env_level_offset[k], out.env_level_width[k] = int(o_), int(w_)
+            pr.get('mis_compensation', False)
+        elif e.type == 'constant':
             out.type = A.EMITTER_CONSTANT
             out.radiance[:] = self._color(pr.child('radiance') or pr.get('radiance', 1.0), key)
             if self.desc.environment >= 0:

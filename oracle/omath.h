@@ -186,6 +186,37 @@ static inline float asin_(float x) {
     return copysign_bits(r, x);
 }
 
+// ext/drjit/include/drjit/math.h:459-506 (acos, single precision), array_router.h:2032-2042 (safe_acos)
+static inline float acos_(float x) {
+    float xa = std::fabs(x), x2 = sqr(x);
+    bool big = xa > 0.5f;
+    float x1 = 0.5f * (1.f - xa);
+    float x3 = big ? x1 : x2;
+    float x4 = big ? std::sqrt(x1) : xa;
+    static const float c[5] = { 1.666675242e-1f, 7.4953002686e-2f, 4.5470025998e-2f, 2.4181311049e-2f, 4.2163199048e-2f };
+    float z1 = estrin(x3, c, 5);
+    z1 = fmadd(z1, x3 * x4, x4);
+    float z2 = z1 + z1;
+    z2 = x < 0.f ? Pi - z2 : z2;
+    float z3 = (Pi * .5f) - copysign_bits(z1, x);
+    return big ? z2 : z3;
+}
+static inline float safe_acos_(float a) { return acos_(maximum(minimum(a, 1.f), -1.f)); }
+// math.h:517-594 (atan2, single precision)
+static inline float atan2_(float y, float x) {
+    float abs_x = std::fabs(x), abs_y = std::fabs(y), min_val = minimum(abs_y, abs_x), max_val = maximum(abs_x, abs_y),
+          scaled_min = min_val / max_val, z = sqr(scaled_min);
+    static const float c[7] = { (float) 0.99999934166683966009, (float) -0.33326497518773606976, (float) 0.19881342388439013552,
+                                (float) -0.13486708938456973185, (float) 0.083863120428809689910, (float) -0.037006525670417265220,
+                                (float) 0.0078613793713198150252 };
+    float t = estrin(z, c, 7);
+    t = t * scaled_min;
+    t = abs_y > abs_x ? Pi * .5f - t : t;
+    t = x < 0.f ? Pi - t : t;
+    float r = y < 0.f ? -t : t;
+    return max_val != 0.f ? r : 0.f;
+}
+
 // ------------------------------------------------------------------
 // 3-vectors with the arithmetic of Vector<DiffArray<LLVMArray<float>>,3>
 // ------------------------------------------------------------------

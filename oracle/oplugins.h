@@ -163,6 +163,92 @@ template <int NC> static inline Color<NC> emitter_radiance(const mib_emitter &e)
     Color<NC> r; for (int c = 0; c < NC; ++c) r.v[c] = e.radiance[NC == 3 ? c : 0]; return r;
 }
 
+// ---- environment map (src/emitters/envmap.cpp:343-560; Hierarchical2D<Float, 0>, include/mitsuba/core/distr_2d.h) ----
+static inline float lerp_(float a, float b, float t) { return fmadd(b, t, fnmadd(a, t, a)); }         // array_router.h lerp
+// warp.h:447-453
+static inline float interval_to_linear(float v0, float v1, float sample) {
+    return std::fabs(v0 - v1) > 1e-4f * (v0 + v1) ? (v0 - safe_sqrt(lerp_(sqr(v0), sqr(v1), sample))) / (v0 - v1) : sample;
+}
+static inline uint32_t env_level_index(uint32_t x, uint32_t y, uint32_t width) {                      // distr_2d.h:766-770
+    return ((x & 1u) | (((x & ~1u) | (y & 1u)) << 1)) + ((y & ~1u) * width);
+}
+static inline float clamp01(float v) { return minimum(maximum(v, 0.f), 1.f); }
+// Hierarchical2D::sample (distr_2d.h:492-575): -> uv in [0,1]^2 and the density
+static inline void env_warp_sample(const mib_emitter &e, const float *buf, float sx, float sy, float *u_out, float *v_out, float *pdf_out) {
+    sx = clamp01(sx); sy = clamp01(sy);
+    uint32_t ox = 0, oy = 0;
+    for (int l = e.env_levels - 2; l > 0; --l) {
+        const float *lv = buf + e.env_level_offset[l];
+        ox <<= 1; oy <<= 1;
+        uint32_t i = env_level_index(ox, oy, (uint32_t) e.env_level_width[l]);
+        float v00 = lv[i], v10 = lv[i + 1], v01 = lv[i + 2], v11 = lv[i + 3];
+        sx = clamp01(sx); sy = clamp01(sy);
+        float r0 = v00 + v10, r1 = v01 + v11;
+        sy *= r0 + r1;
+        bool mask = sy > r0;
+        if (mask) { oy += 1u; sy -= r0; }
+        sy /= mask ? r1 : r0;
+        float c0 = mask ? v01 : v00, c1 = mask ? v11 : v10;
+        sx *= c0 + c1;
+        mask = sx > c0;
+        if (mask) sx -= c0;
+        sx /= mask ? c1 : c0;
+        if (mask) ox += 1u;
+    }
+    const float *l0 = buf + e.env_level_offset[0];
+    const uint32_t w = (uint32_t) e.env_level_width[0], i = ox + oy * w;
+    float v00 = l0[i], v10 = l0[i + 1], v01 = l0[i + w], v11 = l0[i + w + 1];
+    // warp::square_to_bilinear (warp.h:480-494)
+    float r0 = v00 + v10, r1 = v01 + v11;
+    sy = interval_to_linear(r0, r1, sy);
+    float c0 = lerp_(v00, v01, sy), c1 = lerp_(v10, v11, sy);
+    sx = interval_to_linear(c0, c1, sx);
+    *pdf_out = lerp_(c0, c1, sx);
+    const float psx = 1.f / (float) (e.env_res[0] - 1), psy = 1.f / (float) (e.env_res[1] - 1);      // m_patch_size = 1 / n_patches
+    *u_out = ((float) (int) ox + sx) * psx;
+    *v_out = ((float) (int) oy + sy) * psy;
+}
+// Hierarchical2D::eval (distr_2d.h:668-700)
+static inline float env_warp_eval(const mib_emitter &e, const float *buf, float px, float py) {
+    px = clamp01(px); py = clamp01(py);
+    px *= (float) (e.env_res[0] - 1); py *= (float) (e.env_res[1] - 1);
+    uint32_t ox = std::min((uint32_t) (int) px, (uint32_t) (e.env_res[0] - 2)), oy = std::min((uint32_t) (int) py, (uint32_t) (e.env_res[1] - 2));
+    px -= (float) (int) ox; py -= (float) (int) oy;
+    const float *l0 = buf + e.env_level_offset[0];
+    const uint32_t w = (uint32_t) e.env_level_width[0], i = ox + oy * w;
+    float v00 = l0[i], v10 = l0[i + 1], v01 = l0[i + w], v11 = l0[i + w + 1];
+    return lerp_(lerp_(v00, v10, px), lerp_(v01, v11, px), py);                                      // square_to_bilinear_pdf
+}
+// envmap.cpp:517-576 (rgb / mono branch): bilinear look-up of the texel array
+template <int NC> static inline Color<NC> env_eval_spectrum(const mib_emitter &e, const float *buf, float u, float v) {
+    const uint32_t rx = (uint32_t) e.env_res[0], ry = (uint32_t) e.env_res[1];
+    u -= .5f / (float) (rx - 1u);
+    u -= std::floor(u); v -= std::floor(v);
+    u *= (float) (rx - 1u); v *= (float) (ry - 1u);
+    uint32_t px = std::min((uint32_t) u, rx - 2u), py = std::min((uint32_t) v, ry - 2u);
+    float w1x = u - (float) px, w1y = v - (float) py, w0x = 1.f - w1x, w0y = 1.f - w1y;
+    uint32_t index = py * rx + px;
+    Color<NC> out;
+    for (int c = 0; c < NC; ++c) {
+        float v00 = buf[3 * index + c], v10 = buf[3 * (index + 1) + c], v01 = buf[3 * (index + rx) + c], v11 = buf[3 * (index + rx + 1) + c];
+        float v0 = fmadd(w0x, v00, w1x * v10), v1 = fmadd(w0x, v01, w1x * v11);
+        out.v[c] = fmadd(w0y, v0, w1y * v1) * e.env_scale;
+    }
+    return out;
+}
+static inline void env_dir_to_uv(const mib_emitter &e, Vec3 d_world, float *u, float *v, Vec3 *local) {
+    Vec3 d = transform_vector(mat4_from(e.env_to_local), d_world);
+    *u = atan2_(d.x, -d.z) * InvTwoPi;
+    *v = safe_acos_(d.y) * InvPi;
+    *local = d;
+}
+// envmap.cpp:343-354 eval(si): si.wi is the world-space direction back along the ray for a ray that left the scene
+template <int NC> static inline Color<NC> env_eval(const Scene &sc, const mib_emitter &e, Vec3 minus_wi) {
+    float u, v; Vec3 l;
+    env_dir_to_uv(e, minus_wi, &u, &v, &l);
+    return env_eval_spectrum<NC>(e, sc.buffers[e.env_buffer], u, v);
+}
+
 // Returns the UNPOLARIZED spectrum; callers wrap with depolarizer<Spectrum>()
 template <int NC>
 static inline Color<NC> sample_emitter_direction(const Scene &sc, Vec3 ref_p, float sx, float sy, DirectionSample<NC> *ds_out) {
@@ -187,6 +273,23 @@ static inline Color<NC> sample_emitter_direction(const Scene &sc, Vec3 ref_p, fl
         float radius = maximum(e.bsphere_radius, norm(ref_p - c)), dist = 2.f * radius;
         ds.p = fmadd(d, dist, ref_p); ds.n = -d; ds.pdf = InvFourPi; ds.delta = false; ds.d = d; ds.dist = dist;
         spec = div_scalar(emitter_radiance<NC>(e), ds.pdf);
+    } else if (e.type == MIB_EMITTER_ENVMAP) {
+        // envmap.cpp:404-446
+        const float *buf = sc.buffers[e.env_buffer];
+        float u, v, pdf;
+        env_warp_sample(e, buf, sx, sy, &u, &v, &pdf);
+        u += .5f / (float) (e.env_res[0] - 1);
+        bool active = pdf > 0.f;
+        float theta = v * Pi, phi = u * TwoPi, st, ct, sp, cp;
+        sincos(theta, &st, &ct); sincos(phi, &sp, &cp);
+        Vec3 dl(sp * st, ct, -(cp * st));                              // sphdir -> (y, z, -x)
+        float radius = maximum(e.bsphere_radius, norm(ref_p - c)), dist = 2.f * radius;
+        float inv_sin_theta = rsqrt(maximum(maximum(sqr(dl.x) + sqr(dl.z), sqr(EpsilonF)), 0.f));
+        Vec3 d = transform_vector(mat4_from(e.env_to_world), dl);
+        ds.p = fmadd(d, dist, ref_p); ds.n = -d; ds.delta = false; ds.d = d; ds.dist = dist;
+        ds.pdf = active ? pdf * inv_sin_theta * (1.f / (2.f * sqr(Pi))) : 0.f;
+        Color<NC> w = div_scalar(env_eval_spectrum<NC>(e, buf, u, v), ds.pdf);
+        spec = active ? w : Color<NC>(0.f);
     } else if (e.type == MIB_EMITTER_DIRECTIONAL) {
         Vec3 d(e.direction[0], e.direction[1], e.direction[2]);
         float dist = Inf;
@@ -218,11 +321,20 @@ static inline Color<NC> sample_emitter_direction(const Scene &sc, Vec3 ref_p, fl
 // scene.cpp:355-366 + constant.cpp:139-144 / directional.cpp pdf_direction (= 0) / area.cpp:145-173 with
 // DirectionSample3f(scene, si, ref) (records.h: d = (si.p - ref.p) / dist, n = si.sh_frame.n) and
 // Shape::pdf_direction (shape.cpp:377-388)
-template <int NC> static inline float pdf_emitter_direction(const Scene &sc, int emitter, Vec3 ref_p, Vec3 si_p, Vec3 si_n) {
+template <int NC> static inline float pdf_emitter_direction(const Scene &sc, int emitter, Vec3 ref_p, Vec3 si_p, Vec3 si_n, Vec3 minus_wi = Vec3(0.f)) {
     const mib_emitter &e = sc.d.emitters[emitter];
     float pmf = sc.d.n_emitters > 1 ? rcp((float) sc.d.n_emitters) : 1.f;
     float pdf = 0.f;
     if (e.type == MIB_EMITTER_CONSTANT) pdf = InvFourPi;
+    else if (e.type == MIB_EMITTER_ENVMAP) {
+        // envmap.cpp:448-463 with ds.d = -si.wi of the ray that left the scene (records.h DirectionSample(scene, si, ref))
+        float u, v; Vec3 d;
+        env_dir_to_uv(e, minus_wi, &u, &v, &d);
+        u -= .5f / (float) (e.env_res[0] - 1);
+        u -= std::floor(u); v -= std::floor(v);
+        float inv_sin_theta = rsqrt(maximum(maximum(sqr(d.x) + sqr(d.z), sqr(EpsilonF)), 0.f));
+        pdf = env_warp_eval(e, sc.buffers[e.env_buffer], u, v) * inv_sin_theta * (1.f / (2.f * sqr(Pi)));
+    }
     else if (e.type == MIB_EMITTER_AREA) {
         Vec3 rel = si_p - ref_p;
         float dist = norm(rel);
@@ -236,8 +348,9 @@ template <int NC> static inline float pdf_emitter_direction(const Scene &sc, int
 }
 
 // Emitter::eval at a hit: constant / area radiance; the area light is one-sided (area.cpp:83-90)
-template <int NC> static inline Color<NC> emitter_eval(const Scene &sc, int emitter, float cos_theta_wi) {
+template <int NC> static inline Color<NC> emitter_eval(const Scene &sc, int emitter, float cos_theta_wi, Vec3 minus_wi = Vec3(0.f)) {
     const mib_emitter &e = sc.d.emitters[emitter];
+    if (e.type == MIB_EMITTER_ENVMAP) return env_eval<NC>(sc, e, minus_wi);
     if (e.type == MIB_EMITTER_AREA && !(cos_theta_wi > 0.f)) return Color<NC>(0.f);
     return emitter_radiance<NC>(e);
 }

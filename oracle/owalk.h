@@ -270,8 +270,8 @@ template <int SPEC> struct Walk {
                 bool active_e = emitter >= 0 && !(depth == 0u && I.hide_emitters);
                 if (active_e) {
                     float emitter_pdf = 1.0f;
-                    if (!count_direct) emitter_pdf = pdf_emitter_direction<NC>(sc, emitter, last_scatter_p, si.p, si.sh_frame.n);
-                    Spec emitted = depol(emitter_eval<NC>(sc, emitter, si.wi.z));
+                    if (!count_direct) emitter_pdf = pdf_emitter_direction<NC>(sc, emitter, last_scatter_p, si.p, si.sh_frame.n, -si.wi);
+                    Spec emitted = depol(emitter_eval<NC>(sc, emitter, si.wi.z, -si.wi));
                     Spec contrib = count_direct ? smul(throughput, emitted)
                                                 : smul(mul_f(throughput, mis_weight(last_scatter_direction_pdf, emitter_pdf)), emitted);
                     result = result + contrib;

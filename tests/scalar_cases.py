@@ -157,6 +157,14 @@ def cases():
     d['emitter'] = {'type': 'directional', 'direction': [0.3, 0.2, -1.0], 'irradiance': 2.0}
     d['medium1']['phase'] = {'type': 'rayleigh'}
     c['mesh_aos_pol_sun'] = dict(variant='scalar_mono_polarized', scene=d, spp=16, seed=5, kind='samples')
+    # environment map (src/emitters/envmap.cpp): importance sampling through the luminance warp, MIS of rays that leave the scene
+    tex = os.path.join(os.path.dirname(MESH_DIR), "textures", "sky.exr")
+    d = scenes.c1_homogeneous_cube(res=12, spp=16, max_depth=8)
+    d['emitter'] = {'type': 'envmap', 'filename': tex}
+    c['envmap_homog_rgb'] = dict(variant='scalar_rgb', scene=d, spp=16, seed=0, kind='samples')
+    d = mesh_scene(hetero=True, res=12)
+    d['emitter'] = {'type': 'envmap', 'filename': tex, 'scale': 1.5, 'to_world': T.rotate([1, 0, 0], 90.0) @ T.rotate([0, 1, 0], 40.0)}
+    c['envmap_mesh_mono'] = dict(variant='scalar_mono', scene=d, spp=8, seed=2, kind='samples')
     # radiancemeter looking through the cube
     d = scenes.c1_homogeneous_cube(res=1, spp=64, max_depth=16)
     d['sensor'] = {'type': 'radiancemeter', 'origin': [0.2, 0.1, 4.0], 'direction': [-0.05, 0.0, -1.0],

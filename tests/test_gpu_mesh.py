@@ -62,6 +62,25 @@ def test_checkerboard_on_a_rectangle():
     _compare(S.load_dict(d, "llvm_ad_rgb"), 0, 8, 12 * 12 * 8)
 
 
+@pytest.mark.parametrize("name,variant", [("envmap_homog_rgb", "llvm_ad_rgb"), ("envmap_homog_rgb", "llvm_ad_mono_polarized"),
+                                          ("envmap_mesh_mono", "llvm_ad_mono"), ("envmap_mesh_mono", "llvm_ad_rgb")])
+def test_environment_map_lane_by_lane(name, variant):
+    """src/emitters/envmap.cpp: importance sampling through the hierarchical luminance warp, bilinear texel look-up, MIS of the
+    rays that leave the scene.  The oracle reproduces the reference's scalar build on these scenes sample by sample
+    (tests/test_oracle_vs_scalar_ref.py envmap_*)."""
+    case = scalar_cases.cases()[name]
+    sc = S.load_dict(case['scene'], variant)
+    sn = sc.desc.sensor
+    _compare(sc, 3, 16, sn.crop_width * sn.crop_height * 16)
+
+
+def test_environment_map_in_volpathaos():
+    d = scalar_cases.cases()["envmap_homog_rgb"]['scene']
+    d['integrator']['type'] = 'volpathaos'
+    d['medium1']['phase'] = {'type': 'rayleigh'}
+    _compare(S.load_dict(d, "llvm_ad_mono_polarized"), 1, 16, 12 * 12 * 16)
+
+
 @pytest.mark.parametrize("integrator", ["prbvolpath"])
 def test_adjoint_integrators_refuse_meshes(integrator):
     d = scalar_cases.mesh_scene(res=8)
