@@ -49,10 +49,49 @@ def _luminance(rgb):
 SEARCH_PATHS = []
 
 
+def _parse_fov(pr, aspect):
+    """parse_fov (src/render/sensor.cpp:149-203): the horizontal field of view in degrees from 'fov' + 'fov_axis' or from
+    'focal_length' (default "50mm": a 35 mm film's DIAGONAL field of view)."""
+    import math
+    if pr.has('fov') and pr.has('focal_length'):
+        raise PluginError("Please specify either a focal length ('focal_length') or a field of view ('fov')!")
+    if pr.has('fov'):
+        fov = float(pr.get('fov'))
+        axis = str(pr.get('fov_axis', 'x')).lower()
+        if axis == 'smaller':
+            axis = 'y' if aspect > 1 else 'x'
+        elif axis == 'larger':
+            axis = 'x' if aspect > 1 else 'y'
+    else:
+        f = str(pr.get('focal_length', '50mm'))
+        if f.endswith('mm'):
+            f = f[:-2]
+        try:
+            value = float(f)
+        except ValueError:
+            raise PluginError("Could not parse the focal length (must be of the form <x>mm, where <x> is a positive integer)!")
+        fov = 2.0 * math.degrees(math.atan(math.sqrt(36.0 * 36 + 24 * 24) / (2.0 * value)))
+        axis = 'diagonal'
+    if axis == 'x':
+        result = fov
+    elif axis == 'y':
+        result = math.degrees(2.0 * math.atan(math.tan(0.5 * math.radians(fov)) * aspect))
+    elif axis == 'diagonal':
+        diagonal = 2.0 * math.tan(0.5 * math.radians(fov))
+        width = diagonal / math.sqrt(1.0 + 1.0 / (aspect * aspect))
+        result = math.degrees(2.0 * math.atan(width * 0.5))
+    else:
+        raise PluginError("The 'fov_axis' parameter must be set to one of 'smaller', 'larger', 'diagonal', 'x', or 'y'!")
+    if result <= 0.0 or result >= 180.0:
+        raise PluginError("The horizontal field of view must be in the range [0, 180]!")
+    return result
+
+
 class Plugin:
     """One instantiated plugin.  `props` holds the parameters (defaults applied)."""
     CATEGORY = {
         'volpath': 'integrator', 'volpathaos': 'integrator', 'prbvolpath': 'integrator', 'prb_volpathaos': 'integrator',
+        'moment': 'integrator',
         'homogeneous': 'medium', 'heterogeneous': 'medium',
         'gridvolume': 'volume', 'constvolume': 'volume',
         'hg': 'phase', 'rayleigh': 'phase', 'isotropic': 'phase', 'tabphase': 'phase', 'tabphase_polarized': 'phase',
@@ -691,8 +730,7 @@ class Scene:
         if s.type == 'perspective':               # src/sensors/perspective.cpp:120-199
             out.type = A.SENSOR_PERSPECTIVE
             tw = _to_transform(pr.get('to_world'))
-            fov = float(pr.get('fov', 39.3077))   # default focal length 50mm equivalent
-            pr.get('fov_axis', 'x')
+            fov = _parse_fov(pr, fw / fh)
             near, far = float(pr.get('near_clip', 1e-2)), float(pr.get('far_clip', 1e4))
             ppx = float(pr.get('principal_point_offset_x', 0.0))
             ppy = float(pr.get('principal_point_offset_y', 0.0))
@@ -750,6 +788,13 @@ class Scene:
     # -- integrators: src/render/integrator.cpp:24-27,1281-1298; common.py:32-41 --
     def _integrator(self, it):
         out = self.desc.integrator
+        if it.type == 'moment':
+            # src/integrators/moment.cpp wraps integrators and adds their second moments as AOVs (the fork's render tests use
+            # it to get variance images); the radiance channels are those of the first nested integrator, which is what runs here
+            nested = [c for c in it.children.values() if c.category == 'integrator']
+            if len(nested) != 1:
+                raise PluginError("moment: exactly one nested integrator is supported")
+            return self._integrator(nested[0])
         out.type = {'volpath': A.INTEG_VOLPATH, 'volpathaos': A.INTEG_VOLPATHAOS,
                     'prbvolpath': A.INTEG_PRBVOLPATH, 'prb_volpathaos': A.INTEG_PRBVOLPATHAOS}[it.type]
         pr = _Props(it)

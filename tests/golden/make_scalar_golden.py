@@ -58,6 +58,20 @@ def run_case(name, case, tmp):
     return samples
 
 
+def run_xml_case(name, case, tmp):
+    """Samples of a scene FILE (the fork's own render-test scenes): 48 x 48 film, `spp` samples per pixel."""
+    W = H = 48
+    pix, seeds = scalar_cases.pixel_seeds(W, H, case['seed'])
+    px_path = os.path.join(tmp, name + ".px")
+    with open(px_path, "w") as f:
+        for p, s in zip(pix, seeds):
+            f.write("%d %d %d\n" % (p % W, p // W, s))
+    out_bin = os.path.join(tmp, name + ".bin")
+    env = dict(os.environ, LD_LIBRARY_PATH=os.path.dirname(DRIVER))
+    subprocess.check_call([DRIVER, case['variant'], case['file'], 'samples', px_path, str(case['spp']), out_bin], env=env)
+    return np.fromfile(out_bin, np.float32).reshape(W * H, case['spp'], 4)
+
+
 def main():
     if not os.path.exists(DRIVER):
         sys.exit("oracle/_ref/scalar/ref_driver is missing: run oracle/build_ref_scalar.sh first")
@@ -66,6 +80,9 @@ def main():
         for name, case in scalar_cases.cases().items():
             print(name, case['variant'], case['kind'])
             out[name] = run_case(name, case, tmp)
+        for name, case in scalar_cases.xml_cases().items():
+            print(name, case['variant'], case['file'])
+            out[name] = run_xml_case(name, case, tmp)
     np.savez_compressed(os.path.join(HERE, "scalar_ref.npz"), **out)
     print("wrote", os.path.join(HERE, "scalar_ref.npz"), os.path.getsize(os.path.join(HERE, "scalar_ref.npz")), "bytes")
 

@@ -85,6 +85,21 @@ def mesh_scene(hetero=False, res=16):
     }
 
 
+PM_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "participating_media")
+
+
+def xml_cases():
+    """The fork's own render-test scenes (resources/data/tests/scenes/participating_media, copied with their meshes, grids,
+    the museum environment map and the reference images into tests/golden/): name -> dict(variant, file, spp, seed).  The
+    homogeneous one is pinned sample by sample; the two heterogeneous ones hold a plateau of 231 grid cells that sit exactly
+    at the majorant, where the reference's scalar and JIT arithmetic decide null collisions differently,
+    so only a fraction bound is asserted for them."""
+    return {
+        'xml_homo_null_envmap': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_homo_null_envmap_volpath.xml'), spp=2, seed=0, max_flips=0.005),
+        'xml_hetero_sigmat': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_hetero_sigmat_volpath.xml'), spp=2, seed=0, max_flips=0.05),
+    }
+
+
 def cases():
     c = {}
     # C1 (BASELINE configs[0]) at 32 x 32 x 16: homogeneous HG cube, volpath, rgb

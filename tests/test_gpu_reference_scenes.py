@@ -1,0 +1,40 @@
+"""The fork's own render tests on the CUDA path (src/render/tests/test_renders.py:179-236): the three
+participating-media scenes this backend covers -- `obj` meshes, `envmap`, `checkerboard`, heterogeneous `.vol` grids, the `moment`
+wrapper -- loaded from their XML files with mi.load_file, rendered at the reference's budget of 2e6 samples per image and
+compared with the reference's own images by its own Z-test.  Plus lane-by-lane parity with the oracle on the same scenes."""
+import os
+
+import numpy as np
+import pytest
+
+import mitsuba3_nasa_b200 as mi
+from mitsuba3_nasa_b200 import scene as S, _lib
+from orc import OracleScene
+import scalar_cases
+from test_reference_scenes import load, z_test_against_reference, PM
+
+pytestmark = pytest.mark.gpu
+STEMS = ['test_hetero_sigmat', 'test_hetero_sigmat_albedo', 'test_homo_null_envmap']
+
+
+@pytest.mark.parametrize("stem", STEMS)
+def test_render_passes_the_reference_z_test(stem):
+    mi.set_variant('llvm_ad_rgb')
+    spp = int(2e6) // (48 * 48)
+    scene = mi.load_file(os.path.join(PM, stem + '_volpath.xml'), spp=spp)
+    img = np.asarray(mi.render(scene, seed=0, spp=spp))
+    ok, pmin, alpha = z_test_against_reference(img, spp, stem)
+    print("%s: min p-value %.3g, Sidak level %.3g" % (stem, pmin, alpha))
+    assert ok
+
+
+@pytest.mark.parametrize("stem", STEMS)
+def test_lanes_equal_the_oracle(stem):
+    sc = load(os.path.join(PM, stem + '_volpath.xml'), 'llvm_ad_rgb', spp=4)
+    dev, orc = _lib.DeviceScene(sc, 0), OracleScene(sc)
+    n = 48 * 48 * 4
+    g = dev.sample_lanes(0, 4, 0, n).astype(np.float64)
+    o = orc.sample_lanes(0, 4, 0, n).astype(np.float64)
+    bad = (np.abs(g - o) > 1e-4 * np.maximum(np.abs(o).max(axis=1, keepdims=True), 1e-6)).any(axis=1)
+    print("%s: lanes %d, bit-equal %s, over tolerance %d" % (stem, n, np.array_equal(g, o), bad.sum()))
+    assert bad.mean() <= 2e-3
