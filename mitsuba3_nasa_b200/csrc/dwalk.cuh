@@ -6,7 +6,7 @@
 // PCG32 stream in the reference's order so a lane reproduces the
 // reference lane with the same seed.
 #pragma once
-#include "dplugins.cuh"
+#include "dbsdf.cuh"
 
 namespace mib {
 
@@ -14,17 +14,6 @@ template <int SPEC> MIB_D float mis_weight(float a, float b) {               // 
     a *= a; b *= b;
     float w = div_(a, a + b);
     return isfinite(w) ? w : 0.f;
-}
-
-// Diffuse reflectance of channel c: a constant, or the checkerboard texture at the hit's uv (src/textures/checkerboard.cpp:66-84)
-MIB_D float bsdf_reflectance(const mib_bsdf &b, const SurfIt &si, int c) {
-    if (MIB_FT(FT_MESH) && b.texture == MIB_TEXTURE_CHECKERBOARD) {
-        const float u = fma_(b.to_uv[1], si.tv, fma_(b.to_uv[0], si.tu, b.to_uv[2])),
-                    v = fma_(b.to_uv[4], si.tv, fma_(b.to_uv[3], si.tu, b.to_uv[5]));
-        const bool mx = u - floorf(u) > .5f, my = v - floorf(v) > .5f;
-        return mx == my ? b.color0[c] : b.color1[c];
-    }
-    return b.reflectance[c];
 }
 
 // Null-BSDF Mueller matrix in world space: to_world_mueller(I, wi, wi) -> 2x2 block (see dspec.cuh)
@@ -351,6 +340,40 @@ MIB_D void path_step(Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
         if (active_surface) {
             cnt.n_surface++;
             const mib_bsdf &bsdf = sc.d.bsdfs[sc.d.shapes[si.shape].bsdf];
+            if (MIB_FT(FT_MESH) && (bsdf.type == MIB_BSDF_DIELECTRIC || bsdf.type == MIB_BSDF_ROUGHDIELECTRIC)) {
+                // every other BSDF kind through the general interface (dbsdf.cuh): volpath.cpp:281-326 as written
+                const uint32_t gflags = bsdf_flags(bsdf);
+                float V[NT];
+                if ((gflags & kBsdfSmooth) && (depth + 1 < maxd)) {
+                    DirSample<NC> ds;
+                    float em[NC];
+                    sample_emitter<SPEC, AOS>(rng, cnt, si.p, si.n, true, &si, medium, channel, ds, em);
+                    const V3 wo = to_local(si.sh, ds.d);
+                    bsdf_eval<SPEC>(bsdf, si, wo, V);
+                    if constexpr (POL) m4_to_world(si.sh, V, -wo, si.wi);
+                    const float w = AOS ? 1.f : mis_weight<SPEC>(ds.pdf, ds.delta ? 0.f : bsdf_pdf(bsdf, si, wo));
+                    float x[NR];
+                    TW_col0<SPEC>(T, V, x);
+#pragma unroll
+                    for (int r = 0; r < NR; ++r) R[r] += AOS ? x[r] * emis<SPEC>(em, r) : (x[r] * w) * emis<SPEC>(em, r);
+                }
+                float g1, g2x, g2y;
+                if (ltr) { g1 = rng.next(); g2x = rng.next(); g2y = rng.next(); }
+                else { g2x = rng.next(); g2y = rng.next(); g1 = rng.next(); }
+                BsdfS bs;
+                bsdf_sample<SPEC>(bsdf, si, g1, g2x, g2y, true, true, bs, V);
+                if constexpr (POL) m4_to_world(si.sh, V, -bs.wo, si.wi);
+                T_mul_W<SPEC>(T, V);
+                eta *= bs.eta;
+                ray = spawn_ray(si.p, si.n, to_world(si.sh, bs.wo));
+                needs_intersection = true;
+                depth += 1; last_pdf = bs.pdf; st.last_p = si.p;
+                specular_chain = specular_chain || ((bs.sampled & kBsdfDelta) != 0);
+                specular_chain = specular_chain && !(bs.sampled & kBsdfSmooth);
+                if (is_medium_transition(si)) medium = target_medium(si, ray.d);
+                active = active && (active_surface || active_medium);
+                return;
+            }
             const bool is_null = bsdf.type == MIB_BSDF_NULL;
             const uint32_t flags = is_null ? kBsdfNull : kBsdfDiffuseRefl;
             bool active_e = (flags & kBsdfSmooth) && (depth + 1 < maxd);

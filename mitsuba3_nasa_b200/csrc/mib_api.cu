@@ -193,9 +193,10 @@ static void commit(mib_scene *s) {
             throw std::runtime_error("envmap: data buffer missing or inconsistent with its resolution / warp levels");
     }
     // the ocean interface: walked by the forward volpathaos kernel of docean.cuh only
-    if (has_dielectric(s) && d.integrator.type != MIB_INTEG_VOLPATHAOS)
-        throw std::runtime_error("dielectric / roughdielectric BSDFs (the ocean interface) are walked by the volpathaos kernel only: "
-                                 "volpath, prbvolpath and prb_volpathaos (the adjoint has no refractive next-event estimation) refuse them");
+    if (has_dielectric(s) && d.integrator.type != MIB_INTEG_VOLPATHAOS && d.integrator.type != MIB_INTEG_VOLPATH)
+        throw std::runtime_error("dielectric / roughdielectric BSDFs are walked by the forward integrators only (volpath: general BSDF "
+                                 "interface of dwalk.cuh; volpathaos: the interface kernel of docean.cuh with refractive next-event estimation); "
+                                 "prbvolpath and prb_volpathaos refuse them");
     if (d.integrator.type == MIB_INTEG_PRBVOLPATHAOS && aos_interface_state_needed(s))
         throw std::runtime_error("prb_volpathaos: scenes with a non-null BSDF on anything but a horizontal rectangle need the interface state of "
                                  "volpathaos (a bounce that keeps the sign of d.z counts as a refraction, volpathaos.cpp:262-285); the adjoint "
@@ -413,6 +414,7 @@ static bool forward_uses_pool(const mib_scene *s) {
     if (integ != MIB_INTEG_VOLPATH && integ != MIB_INTEG_VOLPATHAOS) return false;     // prb primal passes: per-thread kernel
     if (integ == MIB_INTEG_VOLPATHAOS && aos_interface_state_needed(s)) return false;  // docean.cuh: per-thread kernel
     if (has_mesh(s)) return false;                                                     // dmesh.cuh: per-thread kernel
+    if (has_dielectric(s)) return false;                                               // dbsdf.cuh: per-thread kernel
     const char *k = getenv("MIB_FORWARD_KERNEL");
     bool pool = true;
     if (k && strcmp(k, "thread") == 0) pool = false;

@@ -91,7 +91,19 @@ def test_a_diffuse_bounce_that_keeps_the_sign_of_dz_counts_as_a_refraction():
     assert _lib.DeviceScene(S.load_dict(scenes.c2_rayleigh_slab(spp=4), "llvm_ad_mono_polarized"), 0).forward_kernel() == "pool"
 
 
-@pytest.mark.parametrize("integrator", ["volpath", "prb_volpathaos"])
+@pytest.mark.parametrize("variant", ["llvm_ad_mono_polarized", "llvm_ad_rgb"])
+@pytest.mark.parametrize("rough", [True, False])
+def test_dielectrics_under_volpath(variant, rough):
+    """volpath.cpp:281-326 with a dielectric / roughdielectric BSDF (no refractive next-event estimation there: a smooth
+    interface hides the sun from everything below it, a rough one is sampled by its BSDF with MIS): the general BSDF
+    interface of the one-thread-one-path kernel against the oracle."""
+    d = scenes.aos_ocean(rough=rough)
+    d['integrator']['type'] = 'volpath'
+    d['emitter'] = {'type': 'constant', 'radiance': 1.0}
+    _compare(S.load_dict(d, variant), 4, 4096, 4096)
+
+
+@pytest.mark.parametrize("integrator", ["prb_volpathaos"])
 def test_other_integrators_refuse_dielectrics(integrator):
     d = scenes.aos_ocean()
     d['integrator']['type'] = integrator
