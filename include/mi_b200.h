@@ -65,7 +65,7 @@ enum { MIB_FILTER_NEAREST = 0, MIB_FILTER_TRILINEAR = 1 };
 enum { MIB_WRAP_REPEAT = 0, MIB_WRAP_MIRROR = 1, MIB_WRAP_CLAMP = 2 };
 enum { MIB_PHASE_ISOTROPIC = 0, MIB_PHASE_HG = 1, MIB_PHASE_RAYLEIGH = 2,
        MIB_PHASE_TABPHASE = 3, MIB_PHASE_TABPHASE_POLARIZED = 4 };
-enum { MIB_EMITTER_CONSTANT = 0, MIB_EMITTER_DIRECTIONAL = 1, MIB_EMITTER_AREA = 2, MIB_EMITTER_ENVMAP = 3 };
+enum { MIB_EMITTER_CONSTANT = 0, MIB_EMITTER_DIRECTIONAL = 1, MIB_EMITTER_AREA = 2, MIB_EMITTER_ENVMAP = 3, MIB_EMITTER_SPOT = 4 };
 #define MIB_MAX_ENV_LEVELS 16
 enum { MIB_SENSOR_PERSPECTIVE = 0, MIB_SENSOR_DISTANT = 1, MIB_SENSOR_RADIANCEMETER = 2 };
 enum { MIB_RFILTER_BOX = 0, MIB_RFILTER_GAUSSIAN = 1, MIB_RFILTER_TENT = 2 };
@@ -177,6 +177,12 @@ typedef struct mib_emitter {
     int32_t env_levels;      /* number of levels incl. level 0 */
     int32_t env_level_offset[MIB_MAX_ENV_LEVELS];
     int32_t env_level_width[MIB_MAX_ENV_LEVELS];
+    /* spot light (src/emitters/spot.cpp:89-151,177-214): `radiance` = intensity, position = translation of env_to_world,
+       env_to_local = its inverse; falloff between beam_width and cutoff_angle (radians) */
+    float   spot_cutoff_angle;
+    float   spot_cos_cutoff;
+    float   spot_cos_beam;
+    float   spot_inv_transition;
 } mib_emitter;
 
 typedef struct mib_sensor {

@@ -21,7 +21,7 @@ VOLUME_CONST, VOLUME_GRID = 0, 1
 FILTER_NEAREST, FILTER_TRILINEAR = 0, 1
 WRAP_REPEAT, WRAP_MIRROR, WRAP_CLAMP = 0, 1, 2
 PHASE_ISOTROPIC, PHASE_HG, PHASE_RAYLEIGH, PHASE_TABPHASE, PHASE_TABPHASE_POLARIZED = 0, 1, 2, 3, 4
-EMITTER_CONSTANT, EMITTER_DIRECTIONAL, EMITTER_AREA, EMITTER_ENVMAP = 0, 1, 2, 3
+EMITTER_CONSTANT, EMITTER_DIRECTIONAL, EMITTER_AREA, EMITTER_ENVMAP, EMITTER_SPOT = 0, 1, 2, 3, 4
 MIB_MAX_ENV_LEVELS = 16
 SENSOR_PERSPECTIVE, SENSOR_DISTANT, SENSOR_RADIANCEMETER = 0, 1, 2
 RFILTER_BOX, RFILTER_GAUSSIAN, RFILTER_TENT = 0, 1, 2
@@ -64,7 +64,8 @@ class Emitter(C.Structure):
     _fields_ = [("type", i32), ("radiance", f32 * 3), ("direction", f32 * 3),
                 ("bsphere_center", f32 * 3), ("bsphere_radius", f32), ("shape", i32),
                 ("env_buffer", i32), ("env_res", i32 * 2), ("env_scale", f32), ("env_to_world", f32 * 16), ("env_to_local", f32 * 16),
-                ("env_levels", i32), ("env_level_offset", i32 * 16), ("env_level_width", i32 * 16)]
+                ("env_levels", i32), ("env_level_offset", i32 * 16), ("env_level_width", i32 * 16),
+                ("spot_cutoff_angle", f32), ("spot_cos_cutoff", f32), ("spot_cos_beam", f32), ("spot_inv_transition", f32)]
 
 
 class Sensor(C.Structure):

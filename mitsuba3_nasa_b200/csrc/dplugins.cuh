@@ -235,6 +235,20 @@ MIB_DH void sample_emitter_direction(V3 ref_p, float sx, float sy, DirSample<NC>
         const float ip = rcp_(ds.pdf);
 #pragma unroll
         for (int c2 = 0; c2 < NC; ++c2) spec[c2] = act ? val[c2] * ip : 0.f;
+    } else if (MIB_FT(FT_MESH) && e.type == MIB_EMITTER_SPOT) {
+        // spot.cpp:177-214, falloff_curve :143-151
+        const V3 pos = v3(e.env_to_world[3], e.env_to_world[7], e.env_to_world[11]);
+        V3 d = pos - ref_p;
+        const float dist = norm(d), inv_dist = rcp_(dist);
+        d = d * inv_dist;
+        const V3 local = normalize(xform_vector(e.env_to_local, -d));
+        const float cos_theta = local.z;
+        const float beam_res = cos_theta >= e.spot_cos_beam ? 1.f : (e.spot_cutoff_angle - acos_(cos_theta)) * e.spot_inv_transition;
+        const float falloff = cos_theta > e.spot_cos_cutoff ? beam_res : 0.f;
+        ds.p = pos; ds.pdf = 1.f; ds.delta = true; ds.d = d; ds.dist = dist;
+        const float k = falloff * (inv_dist * inv_dist);
+#pragma unroll
+        for (int c2 = 0; c2 < NC; ++c2) spec[c2] = falloff > 0.f ? e.radiance[NC == 3 ? c2 : 0] * k : 0.f;
     } else if (e.type == MIB_EMITTER_DIRECTIONAL) {
         V3 d = v3(e.direction[0], e.direction[1], e.direction[2]);
         float dist = inf_f();

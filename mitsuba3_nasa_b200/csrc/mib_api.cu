@@ -150,7 +150,7 @@ static bool has_mesh(const mib_scene *s) {
     const mib_scene_desc &d = s->ds.d;
     for (int i = 0; i < d.n_shapes; ++i) if (d.shapes[i].type == MIB_SHAPE_MESH) return true;
     for (int i = 0; i < d.n_bsdfs; ++i) if (d.bsdfs[i].texture != MIB_TEXTURE_UNIFORM) return true;
-    for (int i = 0; i < d.n_emitters; ++i) if (d.emitters[i].type == MIB_EMITTER_ENVMAP) return true;
+    for (int i = 0; i < d.n_emitters; ++i) if (d.emitters[i].type == MIB_EMITTER_ENVMAP || d.emitters[i].type == MIB_EMITTER_SPOT) return true;
     return false;
 }
 
@@ -173,7 +173,7 @@ static bool aos_interface_state_needed(const mib_scene *s) {
 static void commit(mib_scene *s) {
     mib_scene_desc &d = s->ds.d;
     if (has_mesh(s) && d.integrator.type != MIB_INTEG_VOLPATH && d.integrator.type != MIB_INTEG_VOLPATHAOS)
-        throw std::runtime_error("triangle meshes, textured BSDFs and environment maps are walked by the forward integrators (volpath, volpathaos) only");
+        throw std::runtime_error("triangle meshes, textured BSDFs, environment maps and spot lights are walked by the forward integrators (volpath, volpathaos) only");
     for (int i = 0; i < d.n_shapes; ++i) {
         const mib_shape &sh = d.shapes[i];
         if (sh.type != MIB_SHAPE_MESH) continue;

@@ -100,7 +100,7 @@ class Plugin:
         'independent': 'sampler', 'hdrfilm': 'film',
         'box': 'rfilter', 'gaussian': 'rfilter', 'tent': 'rfilter',
         'perspective': 'sensor', 'distant': 'sensor', 'radiancemeter': 'sensor',
-        'constant': 'emitter', 'directional': 'emitter', 'area': 'emitter', 'envmap': 'emitter',
+        'constant': 'emitter', 'directional': 'emitter', 'area': 'emitter', 'envmap': 'emitter', 'spot': 'emitter',
         'cube': 'shape', 'rectangle': 'shape', 'sphere': 'shape', 'obj': 'shape',
         'null': 'bsdf', 'diffuse': 'bsdf', 'dielectric': 'bsdf', 'roughdielectric': 'bsdf',
         'uniform': 'texture', 'srgb': 'texture', 'rgb': 'texture', 'd65': 'texture', 'checkerboard': 'texture',
@@ -635,6 +635,24 @@ class Scene:
             for k, (o_, w_) in enumerate(zip(offs, widths)):
                 out.env_level_offset[k], out.env_level_width[k] = int(o_), int(w_)
             pr.get('mis_compensation', False)
+        elif e.type == 'spot':
+            # src/emitters/spot.cpp:89-116
+            out.type = A.EMITTER_SPOT
+            out.radiance[:] = self._color(pr.child('intensity') or pr.get('intensity', 1.0), key)
+            if pr.child('texture') is not None or pr.has('texture'):
+                raise PluginError("spot: projection textures are not supported")
+            cutoff = np.float32(pr.get('cutoff_angle', 20.0))
+            beam = np.float32(pr.get('beam_width', float(cutoff * np.float32(3.0) / np.float32(4.0))))
+            cutoff_r, beam_r = np.float32(np.deg2rad(np.float64(cutoff))), np.float32(np.deg2rad(np.float64(beam)))
+            if cutoff_r < beam_r:
+                raise PluginError("spot: cutoff_angle must not be smaller than beam_width")
+            out.spot_cutoff_angle = float(cutoff_r)
+            out.spot_inv_transition = float(np.float32(1.0) / (cutoff_r - beam_r))
+            out.spot_cos_cutoff, out.spot_cos_beam = float(np.float32(np.cos(np.float64(cutoff_r)))), float(np.float32(np.cos(np.float64(beam_r))))
+            tw = _to_transform(pr.get('to_world'))
+            out.env_to_world[:] = tw.f32().reshape(-1).tolist()
+            out.env_to_local[:] = tw.inverse().f32().reshape(-1).tolist()
+            self.params[key + '.intensity.value'] = {'kind': 'emitter_radiance', 'emitter': out}
         elif e.type == 'constant':
             out.type = A.EMITTER_CONSTANT
             out.radiance[:] = self._color(pr.child('radiance') or pr.get('radiance', 1.0), key)

@@ -290,6 +290,18 @@ static inline Color<NC> sample_emitter_direction(const Scene &sc, Vec3 ref_p, fl
         ds.pdf = active ? pdf * inv_sin_theta * (1.f / (2.f * sqr(Pi))) : 0.f;
         Color<NC> w = div_scalar(env_eval_spectrum<NC>(e, buf, u, v), ds.pdf);
         spec = active ? w : Color<NC>(0.f);
+    } else if (e.type == MIB_EMITTER_SPOT) {
+        // spot.cpp:177-214, falloff_curve :143-151
+        Vec3 pos(e.env_to_world[3], e.env_to_world[7], e.env_to_world[11]);
+        Vec3 d = pos - ref_p;
+        float dist = norm(d), inv_dist = rcp(dist);
+        d = d * inv_dist;
+        Vec3 local = normalize(transform_vector(mat4_from(e.env_to_local), -d));
+        float cos_theta = local.z;
+        float beam_res = cos_theta >= e.spot_cos_beam ? 1.f : (e.spot_cutoff_angle - acos_(cos_theta)) * e.spot_inv_transition;
+        float falloff = cos_theta > e.spot_cos_cutoff ? beam_res : 0.f;
+        ds.p = pos; ds.n = Vec3(0.f); ds.pdf = 1.f; ds.delta = true; ds.d = d; ds.dist = dist;
+        spec = falloff > 0.f ? emitter_radiance<NC>(e) * (falloff * sqr(inv_dist)) : Color<NC>(0.f);
     } else if (e.type == MIB_EMITTER_DIRECTIONAL) {
         Vec3 d(e.direction[0], e.direction[1], e.direction[2]);
         float dist = Inf;
