@@ -55,9 +55,9 @@ enum { MIB_SPEC_MONO = 0, MIB_SPEC_RGB = 1, MIB_SPEC_MONO_POLARIZED = 2 };
 enum { MIB_INTEG_VOLPATH = 0, MIB_INTEG_VOLPATHAOS = 1,
        MIB_INTEG_PRBVOLPATH = 2, MIB_INTEG_PRBVOLPATHAOS = 3 };
 enum { MIB_SHAPE_CUBE = 0, MIB_SHAPE_RECTANGLE = 1, MIB_SHAPE_SPHERE = 2, MIB_SHAPE_MESH = 3 };
-enum { MIB_MESH_HAS_NORMALS = 1, MIB_MESH_HAS_TEXCOORDS = 2 };
+enum { MIB_MESH_HAS_NORMALS = 1, MIB_MESH_HAS_TEXCOORDS = 2, MIB_MESH_HAS_AREA_TABLE = 4 };
 enum { MIB_TEXTURE_UNIFORM = 0, MIB_TEXTURE_CHECKERBOARD = 1 };
-enum { MIB_BSDF_NULL = 0, MIB_BSDF_DIFFUSE = 1, MIB_BSDF_DIELECTRIC = 2, MIB_BSDF_ROUGHDIELECTRIC = 3 };
+enum { MIB_BSDF_NULL = 0, MIB_BSDF_DIFFUSE = 1, MIB_BSDF_DIELECTRIC = 2, MIB_BSDF_ROUGHDIELECTRIC = 3, MIB_BSDF_THINDIELECTRIC = 4 };
 enum { MIB_MICROFACET_BECKMANN = 0, MIB_MICROFACET_GGX = 1 };
 enum { MIB_MEDIUM_HOMOGENEOUS = 0, MIB_MEDIUM_HETEROGENEOUS = 1 };
 enum { MIB_VOLUME_CONST = 0, MIB_VOLUME_GRID = 1 };
@@ -148,7 +148,9 @@ typedef struct mib_shape {
        float buffer: positions [3 V] | normals [3 V] (HAS_NORMALS) | texcoords [2 V] (HAS_TEXCOORDS) | faces [3 F] (uint32
        bit patterns) | BVH nodes [8 N]: bbox min (3), bbox max (3), then for an inner node (left child, right child | 0x80000000)
        and for a leaf (first entry of the order table, count) -- as uint32 bit patterns | order table [F]: face indices in leaf
-       order (uint32 bit patterns).  Built by the host side (mitsuba3_nasa_b200/mesh.py); node 0 is the root. */
+       order (uint32 bit patterns) | with HAS_AREA_TABLE (meshes that carry an area emitter): triangle areas [F] | their running
+       sum [F] (DiscreteDistribution, distr_1d.h:243-262; `inv_surface_area` = 1 / total).  Built by the host side
+       (mitsuba3_nasa_b200/mesh.py); node 0 is the root. */
     int32_t mesh_buffer;     /* buffer slot, -1: not a mesh */
     int32_t mesh_vertices;   /* V */
     int32_t mesh_faces;      /* F */

@@ -12,9 +12,9 @@ MIB_MAX_BSDFS, MIB_MAX_EMITTERS, MIB_MAX_BUFFERS = 8, 4, 24
 SPEC_MONO, SPEC_RGB, SPEC_MONO_POLARIZED = 0, 1, 2
 INTEG_VOLPATH, INTEG_VOLPATHAOS, INTEG_PRBVOLPATH, INTEG_PRBVOLPATHAOS = 0, 1, 2, 3
 SHAPE_CUBE, SHAPE_RECTANGLE, SHAPE_SPHERE, SHAPE_MESH = 0, 1, 2, 3
-MESH_HAS_NORMALS, MESH_HAS_TEXCOORDS = 1, 2
+MESH_HAS_NORMALS, MESH_HAS_TEXCOORDS, MESH_HAS_AREA_TABLE = 1, 2, 4
 TEXTURE_UNIFORM, TEXTURE_CHECKERBOARD = 0, 1
-BSDF_NULL, BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_ROUGHDIELECTRIC = 0, 1, 2, 3
+BSDF_NULL, BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_ROUGHDIELECTRIC, BSDF_THINDIELECTRIC = 0, 1, 2, 3, 4
 MICROFACET_BECKMANN, MICROFACET_GGX = 0, 1
 MEDIUM_HOMOGENEOUS, MEDIUM_HETEROGENEOUS = 0, 1
 VOLUME_CONST, VOLUME_GRID = 0, 1

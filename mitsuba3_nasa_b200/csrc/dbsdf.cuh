@@ -32,6 +32,7 @@ MIB_D uint32_t bsdf_flags(const mib_bsdf &b) {
         case MIB_BSDF_NULL: return kBsdfNull;
         case MIB_BSDF_DIELECTRIC: return kBsdfDeltaRefl | kBsdfDeltaTrans;
         case MIB_BSDF_ROUGHDIELECTRIC: return kBsdfGlossyRefl | kBsdfGlossyTrans;
+        case MIB_BSDF_THINDIELECTRIC: return kBsdfDeltaRefl | kBsdfNull;
         default: return kBsdfDiffuseRefl;
     }
 }
@@ -226,6 +227,19 @@ MIB_D void rough_eval(const mib_bsdf &b, V3 wi, V3 wo, float &w_out, float *W) {
     }
 }
 
+// ---- ThinDielectric (thindielectric.cpp:137-224): reflection + a NULL transmission lobe ------------------------------
+MIB_D float thin_reflectance(const mib_bsdf &b, const SurfIt &si) {
+    float r = fresnel_(fabsf(si.wi.z), b.eta).x;
+    r *= div_(2.f, 1.f + r);                       // r' = r + trt + tr^3t + ...
+    return r;
+}
+// eval_null_transmission of any BSDF, unpolarized value (null: 1, thindielectric: 1 - r', others: 0)
+MIB_D float bsdf_null_transmission(const mib_bsdf &b, const SurfIt &si) {
+    if (b.type == MIB_BSDF_NULL) return 1.f;
+    if (b.type == MIB_BSDF_THINDIELECTRIC) return 1.f - thin_reflectance(b, si);
+    return 0.f;
+}
+
 // ---- BSDF dispatch: V = value in the layout of the throughput (NC channels, or a 4x4 Mueller matrix in the local frame) -
 template <int SPEC>
 MIB_D void bsdf_sample(const mib_bsdf &b, const SurfIt &si, float s1, float s2x, float s2y, bool has_r, bool has_t, BsdfS &bs, float *V) {
@@ -235,6 +249,22 @@ MIB_D void bsdf_sample(const mib_bsdf &b, const SurfIt &si, float s1, float s2x,
         bs.wo = -si.wi; bs.sampled = kBsdfNull; bs.eta = 1.f; bs.pdf = 1.f;
         if constexpr (POL) m4_identity(V, 1.f);
         else { for (int c = 0; c < NC; ++c) V[c] = 1.f; }
+        return;
+    }
+    if (b.type == MIB_BSDF_THINDIELECTRIC) {
+        const float r = thin_reflectance(b, si), t = 1.f - r;
+        float weight;
+        bool sel_r;
+        bs.wo = v3(0.f); bs.pdf = 0.f; bs.eta = 1.f; bs.sampled = 0;
+        if (has_r && has_t) { sel_r = s1 <= r; weight = 1.f; bs.pdf = sel_r ? r : t; }
+        else if (has_r || has_t) { sel_r = has_r; weight = has_r ? r : t; bs.pdf = 1.f; }
+        else { sel_r = false; weight = 0.f; }
+        if (has_r || has_t) {
+            bs.wo = sel_r ? v3(-si.wi.x, -si.wi.y, si.wi.z) : -si.wi;
+            bs.sampled = sel_r ? kBsdfDeltaRefl : kBsdfNull;
+        }
+        if constexpr (POL) { m4_zero(V); V[0] = weight; }
+        else { for (int c = 0; c < NC; ++c) V[c] = weight; }
         return;
     }
     if (b.type == MIB_BSDF_DIELECTRIC || b.type == MIB_BSDF_ROUGHDIELECTRIC) {
@@ -269,7 +299,7 @@ MIB_D void bsdf_eval(const mib_bsdf &b, const SurfIt &si, V3 wo, float *V) {
         if constexpr (!POL) { for (int c = 0; c < NC; ++c) V[c] = w; }
         return;
     }
-    const bool ok = b.type != MIB_BSDF_NULL && si.wi.z > 0.f && wo.z > 0.f;     // diffuse.cpp:128-160; null: 0
+    const bool ok = b.type == MIB_BSDF_DIFFUSE && si.wi.z > 0.f && wo.z > 0.f;  // diffuse.cpp:128-160; null, thindielectric: 0
     if constexpr (POL) { m4_zero(V); V[0] = ok ? bsdf_reflectance(b, si, 0) * kInvPi * wo.z : 0.f; }
     else { for (int c = 0; c < NC; ++c) V[c] = ok ? bsdf_reflectance(b, si, NC == 3 ? c : 0) * kInvPi * wo.z : 0.f; }
 }
@@ -292,7 +322,7 @@ MIB_D float rough_pdf(const mib_bsdf &b, V3 wi, V3 wo) {
     return active ? prob * fabsf(dwh_dwo) : 0.f;
 }
 MIB_D float bsdf_pdf(const mib_bsdf &b, const SurfIt &si, V3 wo) {
-    if (b.type == MIB_BSDF_NULL || b.type == MIB_BSDF_DIELECTRIC) return 0.f;
+    if (b.type == MIB_BSDF_NULL || b.type == MIB_BSDF_DIELECTRIC || b.type == MIB_BSDF_THINDIELECTRIC) return 0.f;
     if (b.type == MIB_BSDF_ROUGHDIELECTRIC) return rough_pdf(b, si.wi, wo);
     return (si.wi.z > 0.f && wo.z > 0.f) ? kInvPi * wo.z : 0.f;
 }

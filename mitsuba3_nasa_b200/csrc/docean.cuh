@@ -129,11 +129,18 @@ MIB_D void sample_emitter_ocean(Pcg32 &rng, Counters &cnt, V3 ref_p, V3 ref_n, i
         active_surface = active_surface && valid(si) && !active_medium;
         if (active_surface) {
             const mib_bsdf &bsdf = sc.d.bsdfs[sc.d.shapes[si.shape].bsdf];
-            if (bsdf.type == MIB_BSDF_NULL) {
-                if constexpr (POL) {                                   // eval_null_transmission in world space (:417-421)
-                    float b11, b12, b21, b22;
-                    null_block(si, b11, b12, b21, b22);
-                    m4_mul_right_block(tr, b11, b12, b21, b22);
+            if (bsdf_flags(bsdf) & kBsdfNull) {
+                if (bsdf.type == MIB_BSDF_NULL) {
+                    if constexpr (POL) {                               // eval_null_transmission in world space (:417-421)
+                        float b11, b12, b21, b22;
+                        null_block(si, b11, b12, b21, b22);
+                        m4_mul_right_block(tr, b11, b12, b21, b22);
+                    }
+                } else {                                               // thindielectric: depolarizer(1 - r') (thindielectric.cpp:202-215)
+                    float v[NC];
+#pragma unroll
+                    for (int c = 0; c < NC; ++c) v[c] = bsdf_null_transmission(bsdf, si);
+                    T_mul_depol<SPEC>(tr, v);
                 }
             } else {                                                   // bsdf->eval(ctx, si, to_local(emitter_d)) (:423-431)
                 const V3 wo = to_local(si.sh, emitter_d);

@@ -260,8 +260,42 @@ MIB_DH void sample_emitter_direction(V3 ref_p, float sx, float sy, DirSample<NC>
         // area.cpp:119-143 (uniform radiance) -> Shape::sample_direction (shape.cpp:358-375) -> Rectangle::sample_position
         // (rectangle.cpp:166-180); scene.py admits area emitters on rectangles only
         const mib_shape &sh = sc.d.shapes[e.shape];
-        V3 p = xform_point_affine(sh.to_world, v3(sx * 2.f - 1.f, sy * 2.f - 1.f, 0.f));
-        V3 nn = v3(sh.frame_n[0], sh.frame_n[1], sh.frame_n[2]);
+        V3 p, nn;
+        if (MIB_FT(FT_MESH) && sh.type == MIB_SHAPE_MESH) {
+            // Mesh::sample_position (mesh.cpp:742-795): a triangle by area (DiscreteDistribution::sample_reuse, distr_1d.h:116-182),
+            // a uniform point on it (warp.h:153-156), the interpolated vertex normal when the mesh has normals
+            const MeshView m = mesh_view(sh, sc.buffers[sh.mesh_buffer]);
+            const uint32_t F = (uint32_t) sh.mesh_faces;
+            const float *area = reinterpret_cast<const float *>(m.order + F), *cdf = area + F;
+            const float sum = __ldg(cdf + F - 1), normalization = sh.inv_surface_area;
+            uint32_t first = 0, last = F - 1;
+            while (first < F && !(__ldg(area + first) > 0.f)) ++first;
+            while (last > 0 && !(__ldg(area + last) > 0.f)) --last;
+            const float value = sy * sum;
+            uint32_t start = first, end = last;
+            const uint32_t iterations = start < end ? (uint32_t) (31 - __clz((int) (end - start))) + 1u : 0u;
+            for (uint32_t it = 0; it < iterations; ++it) {
+                const uint32_t middle = (start + end) >> 1;
+                if (__ldg(cdf + middle) < value) start = min(middle + 1u, end); else end = middle;
+            }
+            const uint32_t f = start;
+            const float pmf = __ldg(area + f) * normalization, c0 = f > 0 ? __ldg(cdf + f - 1) * normalization : 0.f;
+            const float ry = div_(sy - c0, pmf);
+            const uint32_t *fi = m.faces + 3 * (size_t) f;
+            const uint32_t i0 = __ldg(fi), i1 = __ldg(fi + 1), i2 = __ldg(fi + 2);
+            const V3 p0 = mesh_vec3(m.pos, i0), p1 = mesh_vec3(m.pos, i1), p2 = mesh_vec3(m.pos, i2);
+            const V3 e0 = p1 - p0, e1 = p2 - p0;
+            const float t = safe_sqrt_(1.f - sx), bx = 1.f - t, by = t * ry;
+            p = vfma(e0, bx, vfma(e1, by, p0));
+            if (m.nrm) {
+                const V3 n0 = mesh_vec3(m.nrm, i0), n1 = mesh_vec3(m.nrm, i1), n2 = mesh_vec3(m.nrm, i2);
+                nn = vfma(n0, 1.f - bx - by, vfma(n1, bx, n2 * by));
+            } else nn = cross(e0, e1);
+            nn = normalize(nn);
+        } else {
+            p = xform_point_affine(sh.to_world, v3(sx * 2.f - 1.f, sy * 2.f - 1.f, 0.f));
+            nn = v3(sh.frame_n[0], sh.frame_n[1], sh.frame_n[2]);
+        }
         V3 d = p - ref_p;
         float d2 = sqnorm(d), dist = sqrt_(d2);
         d = d * rcp_(dist);                                  // Vector / Float = multiplication by rcp (array_router.h:226-229)

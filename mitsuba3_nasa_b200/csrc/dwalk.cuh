@@ -116,8 +116,9 @@ MIB_D void sample_emitter(Pcg32 &rng, Counters &cnt, V3 ref_p, V3 ref_n, bool su
                 for (int c = 0; c < NC; ++c) tr[c] *= ok ? bsdf_reflectance(bsdf, si, NC == 3 ? c : 0) * kInvPi * wo.z : 0.f;
                 ray.d = emitter_d;
             } else {
+                const float nt = MIB_FT(FT_MESH) ? bsdf_null_transmission(bsdf, si) : 0.f;      // thindielectric: 1 - r'
 #pragma unroll
-                for (int c = 0; c < NC; ++c) tr[c] *= 0.f;          // eval_null_transmission of a non-null BSDF
+                for (int c = 0; c < NC; ++c) tr[c] *= nt;           // eval_null_transmission of a non-null BSDF
             }
             ray = spawn_ray(si.p, si.n, ray.d);
         }
@@ -340,7 +341,7 @@ MIB_D void path_step(Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
         if (active_surface) {
             cnt.n_surface++;
             const mib_bsdf &bsdf = sc.d.bsdfs[sc.d.shapes[si.shape].bsdf];
-            if (MIB_FT(FT_MESH) && (bsdf.type == MIB_BSDF_DIELECTRIC || bsdf.type == MIB_BSDF_ROUGHDIELECTRIC)) {
+            if (MIB_FT(FT_MESH) && (bsdf.type == MIB_BSDF_DIELECTRIC || bsdf.type == MIB_BSDF_ROUGHDIELECTRIC || bsdf.type == MIB_BSDF_THINDIELECTRIC)) {
                 // every other BSDF kind through the general interface (dbsdf.cuh): volpath.cpp:281-326 as written
                 const uint32_t gflags = bsdf_flags(bsdf);
                 float V[NT];
@@ -367,8 +368,9 @@ MIB_D void path_step(Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
                 eta *= bs.eta;
                 ray = spawn_ray(si.p, si.n, to_world(si.sh, bs.wo));
                 needs_intersection = true;
-                depth += 1; last_pdf = bs.pdf; st.last_p = si.p;
-                specular_chain = specular_chain || ((bs.sampled & kBsdfDelta) != 0);
+                const bool gnon_null = !(bs.sampled & kBsdfNull);
+                if (gnon_null) { depth += 1; last_pdf = bs.pdf; st.last_p = si.p; }
+                specular_chain = specular_chain || (gnon_null && (bs.sampled & kBsdfDelta));
                 specular_chain = specular_chain && !(bs.sampled & kBsdfSmooth);
                 if (is_medium_transition(si)) medium = target_medium(si, ray.d);
                 active = active && (active_surface || active_medium);

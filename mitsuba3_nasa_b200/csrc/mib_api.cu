@@ -141,7 +141,7 @@ static void build_table(mib_scene *s, int phase, int which, int buf_nodes, int b
 static bool has_dielectric(const mib_scene *s) {
     const mib_scene_desc &d = s->ds.d;
     for (int i = 0; i < d.n_bsdfs; ++i)
-        if (d.bsdfs[i].type == MIB_BSDF_DIELECTRIC || d.bsdfs[i].type == MIB_BSDF_ROUGHDIELECTRIC) return true;
+        if (d.bsdfs[i].type == MIB_BSDF_DIELECTRIC || d.bsdfs[i].type == MIB_BSDF_ROUGHDIELECTRIC || d.bsdfs[i].type == MIB_BSDF_THINDIELECTRIC) return true;
     return false;
 }
 
@@ -178,10 +178,11 @@ static void commit(mib_scene *s) {
         const mib_shape &sh = d.shapes[i];
         if (sh.type != MIB_SHAPE_MESH) continue;
         const size_t V = (size_t) sh.mesh_vertices, F = (size_t) sh.mesh_faces, N = (size_t) sh.mesh_nodes;
-        const size_t need = 3 * V + ((sh.mesh_flags & MIB_MESH_HAS_NORMALS) ? 3 * V : 0) + ((sh.mesh_flags & MIB_MESH_HAS_TEXCOORDS) ? 2 * V : 0) + 3 * F + 8 * N + F;
+        const size_t need = 3 * V + ((sh.mesh_flags & MIB_MESH_HAS_NORMALS) ? 3 * V : 0) + ((sh.mesh_flags & MIB_MESH_HAS_TEXCOORDS) ? 2 * V : 0) + 3 * F + 8 * N + F +
+                            ((sh.mesh_flags & MIB_MESH_HAS_AREA_TABLE) ? 2 * F : 0);
         if (sh.mesh_buffer < 0 || sh.mesh_buffer >= MIB_MAX_BUFFERS || !s->buf[sh.mesh_buffer] || s->buf_n[sh.mesh_buffer] < need || V == 0 || F == 0 || N == 0)
             throw std::runtime_error("mesh: data buffer missing or too small for its vertex / face / node counts");
-        if (sh.emitter >= 0) throw std::runtime_error("mesh: area emitters on meshes are not implemented");
+        if (sh.emitter >= 0 && !(sh.mesh_flags & MIB_MESH_HAS_AREA_TABLE)) throw std::runtime_error("mesh: an area emitter needs the mesh's area table");
     }
     for (int i = 0; i < d.n_emitters; ++i) {
         const mib_emitter &e = d.emitters[i];

@@ -40,7 +40,21 @@ class Mesh:
     def bbox(self):
         return self.positions.min(axis=0), self.positions.max(axis=0)
 
-    def pack(self):
+    def area_table(self):
+        """Mesh::build_pmf (mesh.cpp:430-462) + DiscreteDistribution::compute_cdf_scalar (distr_1d.h:243-262): float32 triangle
+        areas, their running sum accumulated in double and stored as float32, and the normalisation 1 / total."""
+        p = self.positions
+        p0, p1, p2 = p[self.faces[:, 0]], p[self.faces[:, 1]], p[self.faces[:, 2]]
+        e0, e1 = (p1 - p0).astype(np.float32), (p2 - p0).astype(np.float32)
+        c = np.stack([_fms32(e0[:, 1], e1[:, 2], e0[:, 2] * e1[:, 1]), _fms32(e0[:, 2], e1[:, 0], e0[:, 0] * e1[:, 2]),
+                      _fms32(e0[:, 0], e1[:, 1], e0[:, 1] * e1[:, 0])], axis=1)
+        area = (np.float32(0.5) * np.sqrt((c.astype(np.float32) ** 2).sum(axis=1, dtype=np.float32), dtype=np.float32)).astype(np.float32)
+        cdf = np.cumsum(area.astype(np.float64)).astype(np.float32)
+        if not cdf[-1] > 0:
+            raise ValueError("DiscreteDistribution: no probability mass found!")
+        return area, cdf, float(np.float32(1.0) / cdf[-1])
+
+    def pack(self, with_area_table=False):
         parts = [self.positions.reshape(-1)]
         if self.normals is not None:
             parts.append(self.normals.reshape(-1))
@@ -49,12 +63,20 @@ class Mesh:
         parts.append(self.faces.reshape(-1).view(np.float32))
         parts.append(self.nodes.reshape(-1))
         parts.append(self.order.view(np.float32))
+        if with_area_table:
+            area, cdf, _ = self.area_table()
+            parts += [area, cdf]
         return np.ascontiguousarray(np.concatenate(parts), np.float32)
 
 
 def _fma32(a, b, c):
     """float32 fused multiply-add of arrays (a * b is exact in float64)."""
     return (a.astype(np.float64) * b.astype(np.float64) + c.astype(np.float64)).astype(np.float32)
+
+
+def _fms32(a, b, c):
+    """float32 fused multiply-subtract a * b - c."""
+    return (a.astype(np.float64) * b.astype(np.float64) - c.astype(np.float64)).astype(np.float32)
 
 
 def _transform_point(M, p):

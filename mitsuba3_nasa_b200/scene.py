@@ -102,7 +102,7 @@ class Plugin:
         'perspective': 'sensor', 'distant': 'sensor', 'radiancemeter': 'sensor',
         'constant': 'emitter', 'directional': 'emitter', 'area': 'emitter', 'envmap': 'emitter', 'spot': 'emitter',
         'cube': 'shape', 'rectangle': 'shape', 'sphere': 'shape', 'obj': 'shape',
-        'null': 'bsdf', 'diffuse': 'bsdf', 'dielectric': 'bsdf', 'roughdielectric': 'bsdf',
+        'null': 'bsdf', 'diffuse': 'bsdf', 'dielectric': 'bsdf', 'roughdielectric': 'bsdf', 'thindielectric': 'bsdf',
         'uniform': 'texture', 'srgb': 'texture', 'rgb': 'texture', 'd65': 'texture', 'checkerboard': 'texture',
         'scene': 'scene',
     }
@@ -475,6 +475,18 @@ class Scene:
             else:
                 out.reflectance[:] = self._color(refl or pr.get('reflectance', 0.5), key)
                 self.params[key + '.reflectance.value'] = {'kind': 'bsdf_reflectance', 'bsdf': out}
+        elif b.type == 'thindielectric':
+            # src/bsdfs/thindielectric.cpp:100-130
+            int_ior = _lookup_ior(pr.get('int_ior', 'bk7'))
+            ext_ior = _lookup_ior(pr.get('ext_ior', 'air'))
+            if int_ior < 0 or ext_ior < 0:
+                raise PluginError("The interior and exterior indices of refraction must be positive!")
+            out.type = A.BSDF_THINDIELECTRIC
+            out.eta = float(np.float32(int_ior) / np.float32(ext_ior))
+            for name in ('specular_reflectance', 'specular_transmittance'):
+                v = pr.child(name) or pr.get(name)
+                if v is not None and any(abs(c - 1.0) > 0 for c in self._color(v, key)):
+                    raise PluginError("%s: only %s = 1 is supported" % (b.type, name))
         elif b.type in ('dielectric', 'roughdielectric'):
             # src/bsdfs/dielectric.cpp:210-222, roughdielectric.cpp:166-218 (the ocean interface of the AOS scenes)
             int_ior = _lookup_ior(pr.get('int_ior', 'bk7'))
@@ -544,9 +556,15 @@ class Scene:
                                   flip_tex_coords=bool(pr.get('flip_tex_coords', True)))
             except (FileNotFoundError, ValueError) as e:
                 raise PluginError(str(e))
-            slot = self._new_buffer(mesh.pack())
+            is_emitter = bool(pr.children_of('emitter'))
+            try:
+                slot = self._new_buffer(mesh.pack(with_area_table=is_emitter))
+                if is_emitter:
+                    out.inv_surface_area = mesh.area_table()[2]
+            except ValueError as e:
+                raise PluginError(str(e))
             out.mesh_buffer, out.mesh_vertices, out.mesh_faces = slot, len(mesh.positions), len(mesh.faces)
-            out.mesh_nodes, out.mesh_flags = len(mesh.nodes), mesh.flags
+            out.mesh_nodes, out.mesh_flags = len(mesh.nodes), mesh.flags | (A.MESH_HAS_AREA_TABLE if is_emitter else 0)
         if s.type == 'sphere':
             c = np.asarray(pr.get('center', [0, 0, 0]), dtype=np.float64)
             r = float(pr.get('radius', 1.0))
@@ -679,8 +697,8 @@ class Scene:
             out.radiance[:] = self._color(pr.child('radiance') or pr.get('radiance', 1.0), key)
             if shape < 0:
                 raise PluginError("area emitter must be attached to a shape")
-            if self.desc.shapes[shape].type != A.SHAPE_RECTANGLE:
-                raise PluginError("area emitters are supported on rectangle shapes only (emitter sampling of cube / sphere is not implemented)")
+            if self.desc.shapes[shape].type not in (A.SHAPE_RECTANGLE, A.SHAPE_MESH):
+                raise PluginError("area emitters are supported on rectangle and obj shapes only (emitter sampling of cube / sphere is not implemented)")
             self.params[key + '.radiance.value'] = {'kind': 'emitter_radiance', 'emitter': out}
         else:
             raise PluginError("unsupported emitter '%s'" % e.type)

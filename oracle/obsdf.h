@@ -3,6 +3,7 @@
 //   diffuse          src/bsdfs/diffuse.cpp:101-160
 //   dielectric       src/bsdfs/dielectric.cpp:247-468      (ofresnel.h dielectric_sample / dielectric_eval; pdf is zero)
 //   roughdielectric  src/bsdfs/roughdielectric.cpp:248-603 (oroughdielectric.h; the fork's G = 1 in eval)
+//   thindielectric   src/bsdfs/thindielectric.cpp:137-224  (reflection lobe + a NULL transmission lobe of weight 1 - r')
 // The two refractive ones are the ocean interface of the fork's atmosphere-ocean scenes (volpathaos.cpp:232-290,312-337).
 // ctx_mask: bit 0 = reflection lobes enabled, bit 1 = transmission lobes enabled (BSDFContext::type_mask; volpathaos'
 // refractive NEE asks for transmission only).
@@ -18,6 +19,7 @@ static inline uint32_t bsdf_flags(const mib_bsdf &b) {
         case MIB_BSDF_NULL: return BSDF_Null;
         case MIB_BSDF_DIELECTRIC: return BSDF_DeltaReflection | BSDF_DeltaTransmission;
         case MIB_BSDF_ROUGHDIELECTRIC: return BSDF_GlossyReflection | BSDF_GlossyTransmission;
+        case MIB_BSDF_THINDIELECTRIC: return BSDF_DeltaReflection | BSDF_Null;
         default: return BSDF_DiffuseReflection;
     }
 }
@@ -52,6 +54,22 @@ template <int SPEC> struct BSDF {
             bs.value = Spec(1.f); // identity in polarized modes (null.cpp:57-63)
             return bs;
         }
+        if (b.type == MIB_BSDF_THINDIELECTRIC) {
+            // thindielectric.cpp:137-190; r' = r + trt + tr^3t + ... accounts for the internal reflections
+            bool has_r = (ctx_mask & 1) != 0, has_t = (ctx_mask & 2) != 0;       // (the transmission lobe is BSDFFlags::Null)
+            float r = fresnel(std::fabs(si.wi.z), b.eta).r;
+            r *= 2.f / (1.f + r);
+            float t = 1.f - r, weight;
+            bool selected_r;
+            if (has_r && has_t) { selected_r = s1 <= r; weight = 1.f; bs.pdf = selected_r ? r : t; }
+            else if (has_r || has_t) { selected_r = has_r; weight = has_r ? r : t; bs.pdf = 1.f; }
+            else return bs;
+            bs.wo = selected_r ? reflect(si.wi) : -si.wi;
+            bs.eta = 1.f;
+            bs.sampled_type = selected_r ? (uint32_t) BSDF_DeltaReflection : (uint32_t) BSDF_Null;
+            bs.value = Depol<Spec, Tr::NC>::make(USpec(weight));
+            return bs;
+        }
         if (b.type == MIB_BSDF_DIELECTRIC) {
             DielectricSample d = dielectric_sample(si.wi, b.eta, s1, (ctx_mask & 1) != 0, (ctx_mask & 2) != 0);
             bs.wo = d.wo; bs.pdf = d.pdf; bs.eta = d.eta; bs.sampled_type = d.sampled_type; bs.value = pick(d.weight, d.weight_pol);
@@ -78,7 +96,7 @@ template <int SPEC> struct BSDF {
     }
     static Spec eval(const mib_bsdf &b, const SurfaceInteraction &si, Vec3 wo) {
         Spec zero = Depol<Spec, Tr::NC>::make(USpec(0.f));
-        if (b.type == MIB_BSDF_NULL) return zero;
+        if (b.type == MIB_BSDF_NULL || b.type == MIB_BSDF_THINDIELECTRIC) return zero;
         if (b.type == MIB_BSDF_DIELECTRIC) {
             float v; Mueller V;
             dielectric_eval(si.wi, wo, b.eta, b.inv_eta, true, true, &v, &V);
@@ -95,13 +113,18 @@ template <int SPEC> struct BSDF {
         return Depol<Spec, Tr::NC>::make(value);
     }
     static float pdf(const mib_bsdf &b, const SurfaceInteraction &si, Vec3 wo) {
-        if (b.type == MIB_BSDF_NULL || b.type == MIB_BSDF_DIELECTRIC) return 0.f;
+        if (b.type == MIB_BSDF_NULL || b.type == MIB_BSDF_DIELECTRIC || b.type == MIB_BSDF_THINDIELECTRIC) return 0.f;
         if (b.type == MIB_BSDF_ROUGHDIELECTRIC) return rough(b).pdf(si.wi, wo, true, true);
         float cos_theta_i = si.wi.z, cos_theta_o = wo.z;
         return (cos_theta_i > 0.f && cos_theta_o > 0.f) ? InvPi * wo.z : 0.f;
     }
-    static Spec eval_null_transmission(const mib_bsdf &b) {
+    static Spec eval_null_transmission(const mib_bsdf &b, const SurfaceInteraction &si) {
         if (b.type == MIB_BSDF_NULL) return Spec(1.f);
+        if (b.type == MIB_BSDF_THINDIELECTRIC) {                     // thindielectric.cpp:202-215
+            float r = fresnel(std::fabs(si.wi.z), b.eta).r;
+            r *= 2.f / (1.f + r);
+            return Depol<Spec, Tr::NC>::make(USpec(1.f - r));
+        }
         return Depol<Spec, Tr::NC>::make(USpec(0.f)); // bsdf.h default: 0
     }
 };

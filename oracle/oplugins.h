@@ -311,10 +311,41 @@ static inline Color<NC> sample_emitter_direction(const Scene &sc, Vec3 ref_p, fl
         // area.cpp:119-143 (uniform radiance) -> Shape::sample_direction (shape.cpp:358-375) ->
         // Rectangle::sample_position (rectangle.cpp:166-180)
         const mib_shape &sh = sc.d.shapes[e.shape];
-        if (sh.type != MIB_SHAPE_RECTANGLE)
-            throw std::runtime_error("oracle: area emitters are supported on rectangles only");
-        Vec3 p = transform_point_affine(mat4_from(sh.to_world), Vec3(sx * 2.f - 1.f, sy * 2.f - 1.f, 0.f));
-        Vec3 n(sh.frame_n[0], sh.frame_n[1], sh.frame_n[2]);
+        Vec3 p, n;
+        if (sh.type == MIB_SHAPE_MESH) {
+            // Mesh::sample_position (mesh.cpp:742-795): a triangle by area (DiscreteDistribution::sample_reuse, distr_1d.h:116-182),
+            // a uniform point on it (warp.h:153-156), the interpolated vertex normal when the mesh has normals
+            MeshView m = mesh_view(sh, sc.buffers[sh.mesh_buffer]);
+            const uint32_t F = (uint32_t) sh.mesh_faces;
+            const float *area = reinterpret_cast<const float *>(m.order + F), *cdf = area + F;
+            const float sum = cdf[F - 1], normalization = sh.inv_surface_area;
+            uint32_t first = 0, last = F - 1;
+            while (first < F && !(area[first] > 0.f)) ++first;                       // m_valid: first / last bin with mass
+            while (last > 0 && !(area[last] > 0.f)) --last;
+            float value = sy * sum;
+            uint32_t start = first, end = last;                                       // dr::binary_search (array_router.h)
+            uint32_t iterations = start < end ? (uint32_t) (31 - __builtin_clz(end - start)) + 1u : 0u;
+            for (uint32_t it = 0; it < iterations; ++it) {
+                uint32_t middle = (start + end) >> 1;
+                if (cdf[middle] < value) start = std::min(middle + 1u, end); else end = middle;
+            }
+            const uint32_t f = start;
+            float pmf = area[f] * normalization, c0 = f > 0 ? cdf[f - 1] * normalization : 0.f;
+            float ry = (sy - c0) / pmf;
+            const uint32_t *fi = m.faces + 3 * (size_t) f;
+            Vec3 p0 = mesh_vec3(m.pos, fi[0]), p1 = mesh_vec3(m.pos, fi[1]), p2 = mesh_vec3(m.pos, fi[2]);
+            Vec3 e0 = p1 - p0, e1 = p2 - p0;
+            float t = safe_sqrt(1.f - sx), bx = 1.f - t, by = t * ry;
+            p = fmadd(e0, bx, fmadd(e1, by, p0));
+            if (m.nrm) {
+                Vec3 n0 = mesh_vec3(m.nrm, fi[0]), n1 = mesh_vec3(m.nrm, fi[1]), n2 = mesh_vec3(m.nrm, fi[2]);
+                n = fmadd(n0, 1.f - bx - by, fmadd(n1, bx, n2 * by));
+            } else n = cross(e0, e1);
+            n = normalize(n);
+        } else if (sh.type == MIB_SHAPE_RECTANGLE) {
+            p = transform_point_affine(mat4_from(sh.to_world), Vec3(sx * 2.f - 1.f, sy * 2.f - 1.f, 0.f));
+            n = Vec3(sh.frame_n[0], sh.frame_n[1], sh.frame_n[2]);
+        } else throw std::runtime_error("oracle: area emitters are supported on rectangles and meshes only");
         Vec3 d = p - ref_p;
         float dist_squared = squared_norm(d), dist = std::sqrt(dist_squared);
         d = d * rcp(dist);                                   // Vector / Float = multiplication by rcp (array_router.h:226-229)

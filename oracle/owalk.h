@@ -136,7 +136,7 @@ template <int SPEC> struct Walk {
             active_surface = active_surface && si.is_valid() && active && !active_medium;
             if (active_surface) {
                 const mib_bsdf &bsdf = sc.d.bsdfs[sc.d.shapes[si.shape].bsdf];
-                Spec bsdf_val = Bs::eval_null_transmission(bsdf);
+                Spec bsdf_val = Bs::eval_null_transmission(bsdf, si);
                 bsdf_val = si_to_world_mueller(si, bsdf_val, si.wi, si.wi);
                 transmittance = smul(transmittance, bsdf_val);
             }
@@ -399,7 +399,7 @@ template <int SPEC> struct Walk {
                 Vec3 wo = si.sh_frame.to_local(emitter_d);
                 bool is_null = (bsdf_flags(bsdf) & BSDF_Null) != 0;
                 if (is_null) {
-                    Spec bsdf_val = Bs::eval_null_transmission(bsdf);
+                    Spec bsdf_val = Bs::eval_null_transmission(bsdf, si);
                     bsdf_val = si_to_world_mueller(si, bsdf_val, si.wi, si.wi);
                     transmittance = smul(transmittance, bsdf_val);
                 } else {

@@ -98,6 +98,7 @@ def xml_cases():
         'xml_homo_null_envmap': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_homo_null_envmap_volpath.xml'), spp=2, seed=0, max_flips=0.005),
         'xml_homo_dielectric_envmap': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_homo_dielectric_envmap_volpath.xml'), spp=2, seed=0, max_flips=0.005),
         'xml_homo_roughdielectric_spot': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_homo_roughdielectric_spot_volpath.xml'), spp=2, seed=0, max_flips=0.005),
+        'xml_homo_area_light': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_homo_area_light_volpath.xml'), spp=2, seed=0, max_flips=0.005),
         'xml_hetero_sigmat': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_hetero_sigmat_volpath.xml'), spp=2, seed=0, max_flips=0.05),
     }
 

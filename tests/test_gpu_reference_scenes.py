@@ -1,6 +1,7 @@
-"""The fork's own render tests on the CUDA path (src/render/tests/test_renders.py:179-236): the five
+"""The fork's own render tests on the CUDA path (src/render/tests/test_renders.py:179-236): the six
 participating-media scenes this backend covers -- `obj` meshes, `envmap`, `checkerboard`, heterogeneous `.vol` grids, a smooth
-`dielectric` and a `roughdielectric` sphere filled with a medium, a `spot` light, the `moment` wrapper -- loaded from their XML files with mi.load_file, rendered at the reference's budget of 2e6 samples per image and
+`dielectric` and a `roughdielectric` sphere filled with a medium, a `spot` light, a mesh area light behind a
+`thindielectric` shell, the `moment` wrapper -- loaded from their XML files with mi.load_file, rendered at the reference's budget of 2e6 samples per image and
 compared with the reference's own images by its own Z-test.  Plus lane-by-lane parity with the oracle on the same scenes."""
 import os
 
@@ -14,7 +15,7 @@ import scalar_cases
 from test_reference_scenes import load, z_test_against_reference, PM
 
 pytestmark = pytest.mark.gpu
-STEMS = ['test_hetero_sigmat', 'test_hetero_sigmat_albedo', 'test_homo_null_envmap', 'test_homo_dielectric_envmap', 'test_homo_roughdielectric_spot']
+STEMS = ['test_hetero_sigmat', 'test_hetero_sigmat_albedo', 'test_homo_null_envmap', 'test_homo_dielectric_envmap', 'test_homo_roughdielectric_spot', 'test_homo_area_light']
 
 
 @pytest.mark.parametrize("stem", STEMS)
