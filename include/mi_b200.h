@@ -53,7 +53,8 @@ extern "C" {
 /* ---- enums (plugin types become tags) ---- */
 enum { MIB_SPEC_MONO = 0, MIB_SPEC_RGB = 1, MIB_SPEC_MONO_POLARIZED = 2 };
 enum { MIB_INTEG_VOLPATH = 0, MIB_INTEG_VOLPATHAOS = 1,
-       MIB_INTEG_PRBVOLPATH = 2, MIB_INTEG_PRBVOLPATHAOS = 3 };
+       MIB_INTEG_PRBVOLPATH = 2, MIB_INTEG_PRBVOLPATHAOS = 3,
+       MIB_INTEG_VOLPATHMIS = 4 /* src/integrators/volpathmis.cpp with use_spectral_mis; forward, unpolarized */ };
 enum { MIB_SHAPE_CUBE = 0, MIB_SHAPE_RECTANGLE = 1, MIB_SHAPE_SPHERE = 2, MIB_SHAPE_MESH = 3 };
 enum { MIB_MESH_HAS_NORMALS = 1, MIB_MESH_HAS_TEXCOORDS = 2, MIB_MESH_HAS_AREA_TABLE = 4 };
 enum { MIB_TEXTURE_UNIFORM = 0, MIB_TEXTURE_CHECKERBOARD = 1 };

@@ -10,7 +10,7 @@ MIB_MAX_SHAPES, MIB_MAX_MEDIA, MIB_MAX_PHASES = 12, 4, 4
 MIB_MAX_BSDFS, MIB_MAX_EMITTERS, MIB_MAX_BUFFERS = 8, 4, 24
 
 SPEC_MONO, SPEC_RGB, SPEC_MONO_POLARIZED = 0, 1, 2
-INTEG_VOLPATH, INTEG_VOLPATHAOS, INTEG_PRBVOLPATH, INTEG_PRBVOLPATHAOS = 0, 1, 2, 3
+INTEG_VOLPATH, INTEG_VOLPATHAOS, INTEG_PRBVOLPATH, INTEG_PRBVOLPATHAOS, INTEG_VOLPATHMIS = 0, 1, 2, 3, 4
 SHAPE_CUBE, SHAPE_RECTANGLE, SHAPE_SPHERE, SHAPE_MESH = 0, 1, 2, 3
 MESH_HAS_NORMALS, MESH_HAS_TEXCOORDS, MESH_HAS_AREA_TABLE = 1, 2, 4
 TEXTURE_UNIFORM, TEXTURE_CHECKERBOARD = 0, 1

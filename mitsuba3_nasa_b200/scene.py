@@ -91,7 +91,7 @@ class Plugin:
     """One instantiated plugin.  `props` holds the parameters (defaults applied)."""
     CATEGORY = {
         'volpath': 'integrator', 'volpathaos': 'integrator', 'prbvolpath': 'integrator', 'prb_volpathaos': 'integrator',
-        'moment': 'integrator',
+        'moment': 'integrator', 'volpathmis': 'integrator',
         'homogeneous': 'medium', 'heterogeneous': 'medium',
         'gridvolume': 'volume', 'constvolume': 'volume',
         'hg': 'phase', 'rayleigh': 'phase', 'isotropic': 'phase', 'tabphase': 'phase', 'tabphase_polarized': 'phase',
@@ -831,7 +831,7 @@ class Scene:
             if len(nested) != 1:
                 raise PluginError("moment: exactly one nested integrator is supported")
             return self._integrator(nested[0])
-        out.type = {'volpath': A.INTEG_VOLPATH, 'volpathaos': A.INTEG_VOLPATHAOS,
+        out.type = {'volpath': A.INTEG_VOLPATH, 'volpathaos': A.INTEG_VOLPATHAOS, 'volpathmis': A.INTEG_VOLPATHMIS,
                     'prbvolpath': A.INTEG_PRBVOLPATH, 'prb_volpathaos': A.INTEG_PRBVOLPATHAOS}[it.type]
         pr = _Props(it)
         is_prb = it.type.startswith('prb')
@@ -845,6 +845,11 @@ class Scene:
         out.hide_emitters = int(bool(pr.get('hide_emitters', False)))
         for n in ('timeout', 'block_size', 'samples_per_pass'):
             pr.get(n)
+        if it.type == 'volpathmis':
+            if self.spectrum == A.SPEC_MONO_POLARIZED:
+                raise PluginError("This integrator currently does not support polarized mode!")      # volpathmis.cpp:134-136
+            if not bool(pr.get('use_spectral_mis', True)):
+                raise PluginError("volpathmis: only use_spectral_mis = true (the plugin's default) is implemented")
         out.rng_arg_order = A.RNG_ARGS_LEFT_TO_RIGHT
         out.double_phase_quirk = 1 if it.type == 'volpath' else 0
         # backend extension (not in the fork): M^3 supergrid of local majorants, 0 = the reference's global majorant

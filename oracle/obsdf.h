@@ -87,6 +87,7 @@ template <int SPEC> struct BSDF {
         // JIT variants have no early exit: all fields are written for every lane and
         // only the value is masked by (cos_theta_i > 0 && pdf > 0) (diffuse.cpp:101-126)
         float cos_theta_i = si.wi.z;
+        if (g_scalar_shapes && !(cos_theta_i > 0.f)) return bs;      // scalar variants' early exit (test-only switch, oscene.h)
         bs.wo = square_to_cosine_hemisphere(s2x, s2y);
         bs.pdf = InvPi * bs.wo.z;
         bs.eta = 1.f;

@@ -82,6 +82,7 @@ typename SpecTraits<SPEC>::Spec trace(const Scene &sc, Sampler &sampler, Counter
     int t = sc.d.integrator.type;
     if (t == MIB_INTEG_VOLPATH) return w.sample_volpath(ray, sc.d.sensor.medium, valid);
     if (t == MIB_INTEG_VOLPATHAOS) return w.sample_volpathaos(ray, sc.d.sensor.medium, valid);
+    if (t == MIB_INTEG_VOLPATHMIS) return w.sample_volpathmis(ray, sc.d.sensor.medium, valid);
     Adjoint<SPEC> a(sc, sampler, cnt);
     if (t == MIB_INTEG_PRBVOLPATH) return a.primal_prbvolpath(ray, sc.d.sensor.medium, valid);
     return a.primal_prbvolpathaos(ray, sc.d.sensor.medium, valid);

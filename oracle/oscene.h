@@ -250,6 +250,9 @@ static inline float intersect_shape(const Scene &sc, int idx, const Ray &ray, in
 // variants take, so that the oracle can be compared with the scalar_* build of the reference (oracle/_ref/scalar):
 //   rectangle.cpp:549-553  the hit is re-projected onto the rectangle ("to improve accuracy"); the *_ad_* variants -- the
 //                          parity target of the kernels -- take p = ray(t) (:541-546).
+//   diffuse.cpp:108-111    `none_or<false>(active)` is an early exit in scalar variants only: a hit on the back side
+//                          returns a zeroed sample (pdf 0); JIT variants fill pdf / wo and mask the value (volpathmis
+//                          stops on pdf == 0, so the two differ by one Russian-roulette draw there).
 // Off by default; the kernels and every other oracle entry point follow the llvm_ad_* branches.
 static bool g_scalar_shapes = false;
 

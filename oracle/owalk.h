@@ -566,6 +566,8 @@ template <int SPEC> struct Walk {
         *valid_out = valid_ray;
         return result;
     }
+
+#include "owalkmis.inc"
 };
 
 } // namespace orc

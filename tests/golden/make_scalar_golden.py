@@ -76,11 +76,19 @@ def main():
     if not os.path.exists(DRIVER):
         sys.exit("oracle/_ref/scalar/ref_driver is missing: run oracle/build_ref_scalar.sh first")
     out = {}
+    only = set(sys.argv[1:])                       # names given: regenerate those, keep the rest of the file
+    npz = os.path.join(HERE, "scalar_ref.npz")
+    if only:
+        out = dict(np.load(npz))
     with tempfile.TemporaryDirectory() as tmp:
         for name, case in scalar_cases.cases().items():
+            if only and name not in only:
+                continue
             print(name, case['variant'], case['kind'])
             out[name] = run_case(name, case, tmp)
         for name, case in scalar_cases.xml_cases().items():
+            if only and name not in only:
+                continue
             print(name, case['variant'], case['file'])
             out[name] = run_xml_case(name, case, tmp)
     np.savez_compressed(os.path.join(HERE, "scalar_ref.npz"), **out)

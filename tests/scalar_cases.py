@@ -99,6 +99,8 @@ def xml_cases():
         'xml_homo_dielectric_envmap': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_homo_dielectric_envmap_volpath.xml'), spp=2, seed=0, max_flips=0.005),
         'xml_homo_roughdielectric_spot': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_homo_roughdielectric_spot_volpath.xml'), spp=2, seed=0, max_flips=0.005),
         'xml_homo_area_light': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_homo_area_light_volpath.xml'), spp=2, seed=0, max_flips=0.005),
+        'xml_homo_spectral_sigmat_mis': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_homo_spectral_sigmat_volpathmis.xml'), spp=2, seed=0, max_flips=0.005),
+        'xml_hetero_spectral_sigmat_mis': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_hetero_spectral_sigmat_volpathmis.xml'), spp=2, seed=0, max_flips=0.05),
         'xml_hetero_sigmat': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_hetero_sigmat_volpath.xml'), spp=2, seed=0, max_flips=0.05),
     }
 
@@ -183,6 +185,16 @@ def cases():
     d = mesh_scene(hetero=True, res=12)
     d['emitter'] = {'type': 'envmap', 'filename': tex, 'scale': 1.5, 'to_world': T.rotate([1, 0, 0], 90.0) @ T.rotate([0, 1, 0], 40.0)}
     c['envmap_mesh_mono'] = dict(variant='scalar_mono', scene=d, spp=8, seed=2, kind='samples')
+    # volpathmis (src/integrators/volpathmis.cpp with use_spectral_mis): spectrally varying and grey
+    # extinction, heterogeneous medium with an albedo grid, area emitter + diffuse floor (surface NEE / emitter-hit MIS), mono
+    for k in ('c1_rgb', 'homog_rgb_spectral_extinction', 'het_rgb_albedo_grid', 'area_emitter', 'c1_mono_seed3', 'envmap_homog_rgb'):
+        import copy
+        m = copy.deepcopy(c[k])
+        m['scene']['integrator']['type'] = 'volpathmis'
+        if k == 'c1_rgb':
+            m['scene'] = scenes.c1_homogeneous_cube(res=12, spp=16)
+            m['scene']['integrator']['type'] = 'volpathmis'
+        c['mis_' + k] = m
     # radiancemeter looking through the cube
     d = scenes.c1_homogeneous_cube(res=1, spp=64, max_depth=16)
     d['sensor'] = {'type': 'radiancemeter', 'origin': [0.2, 0.1, 4.0], 'direction': [-0.05, 0.0, -1.0],
