@@ -8,7 +8,9 @@
 // spt chosen by the host the grid is many multiples of 148 SMs x resident CTAs.
 #pragma once
 #include "astage.cuh"
+#include <type_traits>
 #include "docean.cuh"
+#include "dmis.cuh"
 
 #ifndef MIB_MINB
 #define MIB_MINB 4          // __launch_bounds__(128, MIB_MINB): min resident CTAs per SM (register cap experiments)
@@ -120,9 +122,10 @@ MIB_D void filter_footprint(uint32_t spp, float pos_x, float pos_y, Fn &&fn) {
     }
 }
 
-// MODE: 0 volpath, 1 volpathaos, 2 prbvolpath (primal), 3 prb_volpathaos (primal), 4 volpathaos with a dielectric interface (docean.cuh)
+// MODE: 0 volpath, 1 volpathaos, 2 prbvolpath (primal), 3 prb_volpathaos (primal), 4 volpathaos with a dielectric interface (docean.cuh),
+//       5 volpathmis (dmis.cuh)
 template <int SPEC, int MODE>
-__global__ void __launch_bounds__(128, MODE == 4 ? 2 : MIB_MINB) k_forward(const __grid_constant__ LaunchParams lp) {
+__global__ void __launch_bounds__(128, MODE >= 4 ? 2 : MIB_MINB) k_forward(const __grid_constant__ LaunchParams lp) {
     constexpr int C = RawChannels<SPEC>::C, NR = ST<SPEC>::NR;
     const mib_sensor &sn = sc.d.sensor;
     uint64_t tid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
@@ -192,10 +195,10 @@ __global__ void __launch_bounds__(128, MODE == 4 ? 2 : MIB_MINB) k_forward(const
         return sensor_ray(ax, ay, apx, apy);
     };
 
-    if constexpr (MODE <= 1 || MODE == 4) {
+    if constexpr (MODE <= 1 || MODE >= 4) {
         // Flat loop with lane regeneration: a thread starts its next lane as soon as its current
         // path ends instead of idling until the longest path of the warp is finished.
-        PathState<SPEC> st;
+        typename std::conditional<MODE == 5, MisState<SPEC>, PathState<SPEC>>::type st;
         st.active = false;
         Pcg32 rng;
         Ray ray0;
@@ -208,10 +211,11 @@ __global__ void __launch_bounds__(128, MODE == 4 ? 2 : MIB_MINB) k_forward(const
             if (!st.active && lane < l1) {
                 cur = lane++;
                 ray0 = start(cur, rng, sx, sy);
-                path_init<SPEC>(rng, ray0, st);
+                if constexpr (MODE == 5) mis_init<SPEC>(rng, ray0, st); else path_init<SPEC>(rng, ray0, st);
             }
             if (st.active) {
-                if constexpr (MODE == 4) ocean_step<SPEC>(rng, cnt, st);
+                if constexpr (MODE == 5) mis_step<SPEC>(rng, cnt, st);
+                else if constexpr (MODE == 4) ocean_step<SPEC>(rng, cnt, st);
                 else path_step<SPEC, MODE == 1>(rng, cnt, st);
                 if (!st.active) finish(cur, ray0, sx, sy, st.R);
             }
@@ -222,9 +226,10 @@ __global__ void __launch_bounds__(128, MODE == 4 ? 2 : MIB_MINB) k_forward(const
                 if (lane >= l1) break;
                 cur = lane++;
                 ray0 = start(cur, rng, sx, sy);
-                path_init<SPEC>(rng, ray0, st);
+                if constexpr (MODE == 5) mis_init<SPEC>(rng, ray0, st); else path_init<SPEC>(rng, ray0, st);
             }
-            if constexpr (MODE == 4) ocean_step<SPEC>(rng, cnt, st);
+            if constexpr (MODE == 5) mis_step<SPEC>(rng, cnt, st);
+            else if constexpr (MODE == 4) ocean_step<SPEC>(rng, cnt, st);
             else path_step<SPEC, MODE == 1>(rng, cnt, st);
             if (!st.active) finish(cur, ray0, sx, sy, st.R);
         }

@@ -172,8 +172,11 @@ static bool aos_interface_state_needed(const mib_scene *s) {
 
 static void commit(mib_scene *s) {
     mib_scene_desc &d = s->ds.d;
-    if (has_mesh(s) && d.integrator.type != MIB_INTEG_VOLPATH && d.integrator.type != MIB_INTEG_VOLPATHAOS)
-        throw std::runtime_error("triangle meshes, textured BSDFs, environment maps and spot lights are walked by the forward integrators (volpath, volpathaos) only");
+    const bool forward_integrator = d.integrator.type == MIB_INTEG_VOLPATH || d.integrator.type == MIB_INTEG_VOLPATHAOS || d.integrator.type == MIB_INTEG_VOLPATHMIS;
+    if (has_mesh(s) && !forward_integrator)
+        throw std::runtime_error("triangle meshes, textured BSDFs, environment maps and spot lights are walked by the forward integrators (volpath, volpathaos, volpathmis) only");
+    if (d.integrator.type == MIB_INTEG_VOLPATHMIS && d.spectrum == MIB_SPEC_MONO_POLARIZED)
+        throw std::runtime_error("This integrator currently does not support polarized mode!");                  // volpathmis.cpp:134-136
     for (int i = 0; i < d.n_shapes; ++i) {
         const mib_shape &sh = d.shapes[i];
         if (sh.type != MIB_SHAPE_MESH) continue;
@@ -194,7 +197,7 @@ static void commit(mib_scene *s) {
             throw std::runtime_error("envmap: data buffer missing or inconsistent with its resolution / warp levels");
     }
     // the ocean interface: walked by the forward volpathaos kernel of docean.cuh only
-    if (has_dielectric(s) && d.integrator.type != MIB_INTEG_VOLPATHAOS && d.integrator.type != MIB_INTEG_VOLPATH)
+    if (has_dielectric(s) && !forward_integrator)
         throw std::runtime_error("dielectric / roughdielectric BSDFs are walked by the forward integrators only (volpath: general BSDF "
                                  "interface of dwalk.cuh; volpathaos: the interface kernel of docean.cuh with refractive next-event estimation); "
                                  "prbvolpath and prb_volpathaos refuse them");
@@ -458,6 +461,10 @@ static void dispatch_forward(mib_scene *s, const LaunchParams &lp) {
         case MIB_INTEG_PRBVOLPATHAOS:
             if (spec != 2) throw std::runtime_error("prb_volpathaos requires a monochromatic polarized variant");
             launch_forward<2, 3>(s, lp);
+            break;
+        case MIB_INTEG_VOLPATHMIS:
+            if (spec == 2) throw std::runtime_error("This integrator currently does not support polarized mode!");   // volpathmis.cpp:134-136
+            if (spec == 0) launch_forward<0, 5>(s, lp); else launch_forward<1, 5>(s, lp);
             break;
         default: throw std::runtime_error("unknown integrator type");
     }
