@@ -41,7 +41,7 @@
 extern "C" {
 #endif
 
-#define MIB_ABI_VERSION 7
+#define MIB_ABI_VERSION 8
 
 #define MIB_MAX_SHAPES   12
 #define MIB_MAX_MEDIA    4
@@ -58,7 +58,9 @@ enum { MIB_INTEG_VOLPATH = 0, MIB_INTEG_VOLPATHAOS = 1,
 enum { MIB_SHAPE_CUBE = 0, MIB_SHAPE_RECTANGLE = 1, MIB_SHAPE_SPHERE = 2, MIB_SHAPE_MESH = 3 };
 enum { MIB_MESH_HAS_NORMALS = 1, MIB_MESH_HAS_TEXCOORDS = 2, MIB_MESH_HAS_AREA_TABLE = 4 };
 enum { MIB_TEXTURE_UNIFORM = 0, MIB_TEXTURE_CHECKERBOARD = 1 };
-enum { MIB_BSDF_NULL = 0, MIB_BSDF_DIFFUSE = 1, MIB_BSDF_DIELECTRIC = 2, MIB_BSDF_ROUGHDIELECTRIC = 3, MIB_BSDF_THINDIELECTRIC = 4 };
+enum { MIB_BSDF_NULL = 0, MIB_BSDF_DIFFUSE = 1, MIB_BSDF_DIELECTRIC = 2, MIB_BSDF_ROUGHDIELECTRIC = 3, MIB_BSDF_THINDIELECTRIC = 4,
+       MIB_BSDF_PLASTIC = 5, MIB_BSDF_ROUGHPLASTIC = 6 };
+#define MIB_ROUGH_TRANSMITTANCE_RES 64   /* MI_ROUGH_TRANSMITTANCE_RES, include/mitsuba/render/microfacet.h:22 */
 enum { MIB_MICROFACET_BECKMANN = 0, MIB_MICROFACET_GGX = 1 };
 enum { MIB_MEDIUM_HOMOGENEOUS = 0, MIB_MEDIUM_HETEROGENEOUS = 1 };
 enum { MIB_VOLUME_CONST = 0, MIB_VOLUME_GRID = 1 };
@@ -127,6 +129,16 @@ typedef struct mib_bsdf {
     float   color0[3];
     float   color1[3];
     float   to_uv[6];        /* rows 0 and 1 of the 3 x 3 `to_uv` transform (uv' = to_uv * (u, v, 1)) */
+    /* plastic / roughplastic (src/bsdfs/plastic.cpp:151-200, roughplastic.cpp:169-253; ABI 8): `reflectance` is the
+       diffuse_reflectance, `eta` / `alpha_u` / `distribution` as above; the derived members are filled by the host side
+       (mitsuba3_nasa_b200/plastic.py) as the plugins' parameters_changed() does */
+    float   specular_reflectance[3];
+    int32_t has_specular_reflectance;
+    int32_t nonlinear;
+    float   inv_eta_2;                  /* 1 / eta^2 */
+    float   specular_sampling_weight;   /* s_mean / (d_mean + s_mean) */
+    float   internal_reflectance;       /* plastic: fresnel_diffuse_reflectance(1 / eta); roughplastic: m_internal_reflectance */
+    float   ext_transmittance[MIB_ROUGH_TRANSMITTANCE_RES];   /* roughplastic: eval_transmittance over mu = linspace(0, 1, 64) */
 } mib_bsdf;
 
 typedef struct mib_shape {

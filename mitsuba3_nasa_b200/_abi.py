@@ -5,7 +5,7 @@ and the ABI version at load time so a drift fails loudly.
 """
 import ctypes as C
 
-MIB_ABI_VERSION = 7
+MIB_ABI_VERSION = 8
 MIB_MAX_SHAPES, MIB_MAX_MEDIA, MIB_MAX_PHASES = 12, 4, 4
 MIB_MAX_BSDFS, MIB_MAX_EMITTERS, MIB_MAX_BUFFERS = 8, 4, 24
 
@@ -14,7 +14,8 @@ INTEG_VOLPATH, INTEG_VOLPATHAOS, INTEG_PRBVOLPATH, INTEG_PRBVOLPATHAOS, INTEG_VO
 SHAPE_CUBE, SHAPE_RECTANGLE, SHAPE_SPHERE, SHAPE_MESH = 0, 1, 2, 3
 MESH_HAS_NORMALS, MESH_HAS_TEXCOORDS, MESH_HAS_AREA_TABLE = 1, 2, 4
 TEXTURE_UNIFORM, TEXTURE_CHECKERBOARD = 0, 1
-BSDF_NULL, BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_ROUGHDIELECTRIC, BSDF_THINDIELECTRIC = 0, 1, 2, 3, 4
+BSDF_NULL, BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_ROUGHDIELECTRIC, BSDF_THINDIELECTRIC, BSDF_PLASTIC, BSDF_ROUGHPLASTIC = 0, 1, 2, 3, 4, 5, 6
+MIB_ROUGH_TRANSMITTANCE_RES = 64
 MICROFACET_BECKMANN, MICROFACET_GGX = 0, 1
 MEDIUM_HOMOGENEOUS, MEDIUM_HETEROGENEOUS = 0, 1
 VOLUME_CONST, VOLUME_GRID = 0, 1
@@ -49,7 +50,9 @@ class Medium(C.Structure):
 class Bsdf(C.Structure):
     _fields_ = [("type", i32), ("reflectance", f32 * 3), ("eta", f32), ("inv_eta", f32), ("alpha_u", f32), ("alpha_v", f32),
                 ("distribution", i32), ("sample_visible", i32),
-                ("texture", i32), ("color0", f32 * 3), ("color1", f32 * 3), ("to_uv", f32 * 6)]
+                ("texture", i32), ("color0", f32 * 3), ("color1", f32 * 3), ("to_uv", f32 * 6),
+                ("specular_reflectance", f32 * 3), ("has_specular_reflectance", i32), ("nonlinear", i32), ("inv_eta_2", f32),
+                ("specular_sampling_weight", f32), ("internal_reflectance", f32), ("ext_transmittance", f32 * MIB_ROUGH_TRANSMITTANCE_RES)]
 
 
 class Shape(C.Structure):

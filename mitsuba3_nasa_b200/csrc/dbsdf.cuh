@@ -1,6 +1,9 @@
 // dbsdf.cuh -- BSDFs of the path on the device beyond null / diffuse:
 //   SmoothDielectric   src/bsdfs/dielectric.cpp:247-468         (sample; the fork's non-zero eval; pdf = 0)
 //   RoughDielectric    src/bsdfs/roughdielectric.cpp:248-603    (sample / eval with G = 1 / pdf)
+//   SmoothPlastic      src/bsdfs/plastic.cpp:202-352            (delta reflection + diffuse base with internal scattering)
+//   RoughPlastic       src/bsdfs/roughplastic.cpp:256-515       (microfacet reflection + diffuse base; the transmittance table
+//                                                                and internal reflectance come from the host, plastic.py)
 //   diffuse reflectance through a checkerboard texture          src/textures/checkerboard.cpp:66-84
 // and the dispatch over all BSDF kinds (bsdf_sample / bsdf_eval / bsdf_pdf) in the layout of the throughput.  The reference's
 // quirks are kept (SmoothDielectric::eval without Fresnel factor, eval with G = 1, the polarized sampling weight's mixed
@@ -33,6 +36,8 @@ MIB_D uint32_t bsdf_flags(const mib_bsdf &b) {
         case MIB_BSDF_DIELECTRIC: return kBsdfDeltaRefl | kBsdfDeltaTrans;
         case MIB_BSDF_ROUGHDIELECTRIC: return kBsdfGlossyRefl | kBsdfGlossyTrans;
         case MIB_BSDF_THINDIELECTRIC: return kBsdfDeltaRefl | kBsdfNull;
+        case MIB_BSDF_PLASTIC: return kBsdfDeltaRefl | kBsdfDiffuseRefl;
+        case MIB_BSDF_ROUGHPLASTIC: return kBsdfGlossyRefl | kBsdfDiffuseRefl;
         default: return kBsdfDiffuseRefl;
     }
 }
@@ -240,6 +245,118 @@ MIB_D float bsdf_null_transmission(const mib_bsdf &b, const SurfIt &si) {
     return 0.f;
 }
 
+// ---- plastic / roughplastic (unpolarized values; polarized variants wrap them in a depolarizer) -------------------------
+MIB_D float plastic_lerp_gather(const float *data, float x) {                          // roughplastic.cpp:392-402
+    x *= (float) (MIB_ROUGH_TRANSMITTANCE_RES - 1);
+    const uint32_t index = min((uint32_t) x, (uint32_t) (MIB_ROUGH_TRANSMITTANCE_RES - 2));
+    return lerp_(data[index], data[index + 1], x - (float) index);
+}
+// diffuse base seen through the interface: diff / (1 - internal reflections)
+MIB_D float plastic_base(const mib_bsdf &b, int c) {
+    const float diff = b.reflectance[c];
+    return div_(diff, b.nonlinear ? 1.f - diff * b.internal_reflectance : 1.f - b.internal_reflectance);
+}
+MIB_D float rough_prob_specular(const mib_bsdf &b, float cos_theta_i) {
+    const float t_i = plastic_lerp_gather(b.ext_transmittance, cos_theta_i);
+    const float ps = (1.f - t_i) * b.specular_sampling_weight, pd = t_i * (1.f - b.specular_sampling_weight);
+    return div_(ps, ps + pd);
+}
+template <int NC> MIB_D void roughplastic_eval(const mib_bsdf &b, V3 wi, V3 wo, float *v) {
+    const float cos_theta_i = wi.z, cos_theta_o = wo.z;
+    if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) { for (int c = 0; c < NC; ++c) v[c] = 0.f; return; }
+    const Microfacet distr(b.distribution, b.alpha_u, b.alpha_v);
+    const V3 H = normalize(wo + wi);
+    const float D = distr.eval(H), F = fresnel_(dot(wi, H), b.eta).x, G = distr.smith_g1(wi, H) * distr.smith_g1(wo, H);
+    const float spec = div_(F * D * G, 4.f * cos_theta_i);
+    const float t_i = plastic_lerp_gather(b.ext_transmittance, cos_theta_i), t_o = plastic_lerp_gather(b.ext_transmittance, cos_theta_o);
+    const float k = kInvPi * b.inv_eta_2 * cos_theta_o * t_i * t_o;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+        const int cc = NC == 3 ? c : 0;
+        v[c] = (b.has_specular_reflectance ? spec * b.specular_reflectance[cc] : spec) + plastic_base(b, cc) * k;
+    }
+}
+MIB_D float roughplastic_pdf(const mib_bsdf &b, V3 wi, V3 wo) {
+    const float cos_theta_i = wi.z, cos_theta_o = wo.z;
+    if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) return 0.f;
+    const float prob_specular = rough_prob_specular(b, cos_theta_i), prob_diffuse = 1.f - prob_specular;
+    const Microfacet distr(b.distribution, b.alpha_u, b.alpha_v);
+    const V3 H = normalize(wo + wi);
+    float result = div_(distr.eval(H) * distr.smith_g1(wi, H), 4.f * cos_theta_i);
+    result *= prob_specular;
+    result += prob_diffuse * (kInvPi * wo.z);
+    return result;
+}
+template <int NC> MIB_D void plastic_eval(const mib_bsdf &b, V3 wi, V3 wo, float *v) {
+    const float cos_theta_i = wi.z, cos_theta_o = wo.z;
+    if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) { for (int c = 0; c < NC; ++c) v[c] = 0.f; return; }
+    const float f_i = fresnel_(cos_theta_i, b.eta).x, f_o = fresnel_(cos_theta_o, b.eta).x;
+    const float k = (kInvPi * cos_theta_o) * b.inv_eta_2 * (1.f - f_i) * (1.f - f_o);
+#pragma unroll
+    for (int c = 0; c < NC; ++c) v[c] = plastic_base(b, NC == 3 ? c : 0) * k;
+}
+MIB_D float plastic_pdf(const mib_bsdf &b, V3 wi, V3 wo) {
+    const float cos_theta_i = wi.z, cos_theta_o = wo.z;
+    if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) return 0.f;
+    const float f_i = fresnel_(cos_theta_i, b.eta).x, ps = f_i * b.specular_sampling_weight;
+    float pd = (1.f - f_i) * (1.f - b.specular_sampling_weight);
+    pd = div_(pd, ps + pd);
+    return (kInvPi * cos_theta_o) * pd;
+}
+// sample of both (plastic.cpp:202-264, roughplastic.cpp:256-311); a hit on the back side returns the zeroed sample
+template <int NC> MIB_D void plastic_sample(const mib_bsdf &b, V3 wi, float s1, float s2x, float s2y, bool has_r, BsdfS &bs, float *v) {
+    bs.wo = v3(0.f); bs.pdf = 0.f; bs.eta = 1.f; bs.sampled = 0;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) v[c] = 0.f;
+    const float cos_theta_i = wi.z;
+    if (!has_r || !(cos_theta_i > 0.f)) return;
+    const bool rough = b.type == MIB_BSDF_ROUGHPLASTIC;
+    float f_i = 0.f, prob_specular;
+    if (rough) prob_specular = rough_prob_specular(b, cos_theta_i);
+    else {
+        f_i = fresnel_(cos_theta_i, b.eta).x;
+        const float ps = f_i * b.specular_sampling_weight, pd = (1.f - f_i) * (1.f - b.specular_sampling_weight);
+        prob_specular = div_(ps, ps + pd);
+    }
+    const float prob_diffuse = 1.f - prob_specular;
+    const bool sample_specular = s1 < prob_specular;
+    if (rough) {
+        if (sample_specular) {
+            const Microfacet distr(b.distribution, b.alpha_u, b.alpha_v);
+            float mpdf;
+            const V3 m = distr.sample(wi, s2x, s2y, mpdf);
+            const float d2 = 2.f * dot(wi, m);
+            bs.wo = v3(fms_(m.x, d2, wi.x), fms_(m.y, d2, wi.y), fms_(m.z, d2, wi.z));
+            bs.sampled = kBsdfGlossyRefl;
+        } else {
+            bs.wo = square_to_cosine_hemisphere(s2x, s2y);
+            bs.sampled = kBsdfDiffuseRefl;
+        }
+        bs.pdf = roughplastic_pdf(b, wi, bs.wo);
+        if (bs.pdf > 0.f) {
+            roughplastic_eval<NC>(b, wi, bs.wo, v);
+            const float ip = rcp_(bs.pdf);
+#pragma unroll
+            for (int c = 0; c < NC; ++c) v[c] *= ip;
+        }
+    } else if (sample_specular) {
+        bs.wo = v3(-wi.x, -wi.y, wi.z);
+        bs.pdf = prob_specular;
+        bs.sampled = kBsdfDeltaRefl;
+        const float w = div_(f_i, bs.pdf);
+#pragma unroll
+        for (int c = 0; c < NC; ++c) v[c] = b.has_specular_reflectance ? w * b.specular_reflectance[NC == 3 ? c : 0] : w;
+    } else {
+        bs.wo = square_to_cosine_hemisphere(s2x, s2y);
+        bs.pdf = prob_diffuse * (kInvPi * bs.wo.z);
+        bs.sampled = kBsdfDiffuseRefl;
+        const float f_o = fresnel_(bs.wo.z, b.eta).x;
+        const float k = div_(b.inv_eta_2 * (1.f - f_i) * (1.f - f_o), prob_diffuse);
+#pragma unroll
+        for (int c = 0; c < NC; ++c) v[c] = plastic_base(b, NC == 3 ? c : 0) * k;
+    }
+}
+
 // ---- BSDF dispatch: V = value in the layout of the throughput (NC channels, or a 4x4 Mueller matrix in the local frame) -
 template <int SPEC>
 MIB_D void bsdf_sample(const mib_bsdf &b, const SurfIt &si, float s1, float s2x, float s2y, bool has_r, bool has_t, BsdfS &bs, float *V) {
@@ -265,6 +382,13 @@ MIB_D void bsdf_sample(const mib_bsdf &b, const SurfIt &si, float s1, float s2x,
         }
         if constexpr (POL) { m4_zero(V); V[0] = weight; }
         else { for (int c = 0; c < NC; ++c) V[c] = weight; }
+        return;
+    }
+    if (b.type == MIB_BSDF_PLASTIC || b.type == MIB_BSDF_ROUGHPLASTIC) {
+        float v[NC];
+        plastic_sample<NC>(b, si.wi, s1, s2x, s2y, has_r, bs, v);
+        if constexpr (POL) { m4_zero(V); V[0] = v[0]; }
+        else { for (int c = 0; c < NC; ++c) V[c] = v[c]; }
         return;
     }
     if (b.type == MIB_BSDF_DIELECTRIC || b.type == MIB_BSDF_ROUGHDIELECTRIC) {
@@ -299,6 +423,14 @@ MIB_D void bsdf_eval(const mib_bsdf &b, const SurfIt &si, V3 wo, float *V) {
         if constexpr (!POL) { for (int c = 0; c < NC; ++c) V[c] = w; }
         return;
     }
+    if (b.type == MIB_BSDF_PLASTIC || b.type == MIB_BSDF_ROUGHPLASTIC) {
+        float v[NC];
+        if (b.type == MIB_BSDF_PLASTIC) plastic_eval<NC>(b, si.wi, wo, v);
+        else roughplastic_eval<NC>(b, si.wi, wo, v);
+        if constexpr (POL) { m4_zero(V); V[0] = v[0]; }
+        else { for (int c = 0; c < NC; ++c) V[c] = v[c]; }
+        return;
+    }
     const bool ok = b.type == MIB_BSDF_DIFFUSE && si.wi.z > 0.f && wo.z > 0.f;  // diffuse.cpp:128-160; null, thindielectric: 0
     if constexpr (POL) { m4_zero(V); V[0] = ok ? bsdf_reflectance(b, si, 0) * kInvPi * wo.z : 0.f; }
     else { for (int c = 0; c < NC; ++c) V[c] = ok ? bsdf_reflectance(b, si, NC == 3 ? c : 0) * kInvPi * wo.z : 0.f; }
@@ -324,6 +456,8 @@ MIB_D float rough_pdf(const mib_bsdf &b, V3 wi, V3 wo) {
 MIB_D float bsdf_pdf(const mib_bsdf &b, const SurfIt &si, V3 wo) {
     if (b.type == MIB_BSDF_NULL || b.type == MIB_BSDF_DIELECTRIC || b.type == MIB_BSDF_THINDIELECTRIC) return 0.f;
     if (b.type == MIB_BSDF_ROUGHDIELECTRIC) return rough_pdf(b, si.wi, wo);
+    if (b.type == MIB_BSDF_PLASTIC) return plastic_pdf(b, si.wi, wo);
+    if (b.type == MIB_BSDF_ROUGHPLASTIC) return roughplastic_pdf(b, si.wi, wo);
     return (si.wi.z > 0.f && wo.z > 0.f) ? kInvPi * wo.z : 0.f;
 }
 

@@ -341,7 +341,7 @@ MIB_D void path_step(Pcg32 &rng, Counters &cnt, PathState<SPEC> &st) {
         if (active_surface) {
             cnt.n_surface++;
             const mib_bsdf &bsdf = sc.d.bsdfs[sc.d.shapes[si.shape].bsdf];
-            if (MIB_FT(FT_MESH) && (bsdf.type == MIB_BSDF_DIELECTRIC || bsdf.type == MIB_BSDF_ROUGHDIELECTRIC || bsdf.type == MIB_BSDF_THINDIELECTRIC)) {
+            if (MIB_FT(FT_MESH) && bsdf.type >= MIB_BSDF_DIELECTRIC) {        // dielectric, roughdielectric, thindielectric, plastic, roughplastic
                 // every other BSDF kind through the general interface (dbsdf.cuh): volpath.cpp:281-326 as written
                 const uint32_t gflags = bsdf_flags(bsdf);
                 float V[NT];

@@ -141,7 +141,7 @@ static void build_table(mib_scene *s, int phase, int which, int buf_nodes, int b
 static bool has_dielectric(const mib_scene *s) {
     const mib_scene_desc &d = s->ds.d;
     for (int i = 0; i < d.n_bsdfs; ++i)
-        if (d.bsdfs[i].type == MIB_BSDF_DIELECTRIC || d.bsdfs[i].type == MIB_BSDF_ROUGHDIELECTRIC || d.bsdfs[i].type == MIB_BSDF_THINDIELECTRIC) return true;
+        if (d.bsdfs[i].type >= MIB_BSDF_DIELECTRIC) return true;       // every BSDF beyond null / diffuse: dbsdf.cuh's general interface
     return false;
 }
 
@@ -198,7 +198,7 @@ static void commit(mib_scene *s) {
     }
     // the ocean interface: walked by the forward volpathaos kernel of docean.cuh only
     if (has_dielectric(s) && !forward_integrator)
-        throw std::runtime_error("dielectric / roughdielectric BSDFs are walked by the forward integrators only (volpath: general BSDF "
+        throw std::runtime_error("dielectric / roughdielectric / thindielectric / plastic / roughplastic BSDFs are walked by the forward integrators only (volpath: general BSDF "
                                  "interface of dwalk.cuh; volpathaos: the interface kernel of docean.cuh with refractive next-event estimation); "
                                  "prbvolpath and prb_volpathaos refuse them");
     if (d.integrator.type == MIB_INTEG_PRBVOLPATHAOS && aos_interface_state_needed(s))

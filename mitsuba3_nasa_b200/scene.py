@@ -13,7 +13,7 @@ import os
 
 import numpy as np
 
-from . import _abi as A
+from . import _abi as A, plastic
 from .transforms import ScalarTransform4f, coordinate_system
 
 RAY_EPSILON = 1500.0 * 2.0 ** -24   # include/mitsuba/core/math.h:17-23
@@ -37,6 +37,14 @@ def _lookup_ior(v):
 
 class PluginError(RuntimeError):
     pass
+
+
+def _mean32(values):
+    # dr::mean of a Color in float32 (sum left to right, times 1 / n)
+    acc = np.float32(values[0])
+    for v in values[1:]:
+        acc = np.float32(acc + np.float32(v))
+    return np.float32(acc * (np.float32(1.0) / np.float32(len(values))))
 
 
 def _luminance(rgb):
@@ -102,7 +110,7 @@ class Plugin:
         'perspective': 'sensor', 'distant': 'sensor', 'radiancemeter': 'sensor',
         'constant': 'emitter', 'directional': 'emitter', 'area': 'emitter', 'envmap': 'emitter', 'spot': 'emitter',
         'cube': 'shape', 'rectangle': 'shape', 'sphere': 'shape', 'obj': 'shape',
-        'null': 'bsdf', 'diffuse': 'bsdf', 'dielectric': 'bsdf', 'roughdielectric': 'bsdf', 'thindielectric': 'bsdf',
+        'null': 'bsdf', 'diffuse': 'bsdf', 'dielectric': 'bsdf', 'roughdielectric': 'bsdf', 'thindielectric': 'bsdf', 'plastic': 'bsdf', 'roughplastic': 'bsdf',
         'uniform': 'texture', 'srgb': 'texture', 'rgb': 'texture', 'd65': 'texture', 'checkerboard': 'texture',
         'scene': 'scene',
     }
@@ -116,6 +124,25 @@ class Plugin:
 
     def __repr__(self):
         return "%s[%s]" % (self.type, ", ".join("%s=%r" % kv for kv in self.props.items()))
+
+
+def _properties_less(a, b):
+    """Properties' SortKey (src/core/properties.cpp:48-71): the order in which a plugin sees its child objects -- byte order, except
+    that a trailing run of digits after the common prefix compares as a number ("_arg_2" < "_arg_10")."""
+    i = 0
+    while i < len(a) and i < len(b) and a[i] == b[i]:
+        i += 1
+    while i > 0 and a[i - 1].isdigit():
+        i -= 1
+    ta, tb = a[i:], b[i:]
+    if ta[:1].isdigit() and tb[:1].isdigit() and ta.isdigit() and tb.isdigit():
+        return int(ta) < int(tb)
+    return ta < tb
+
+
+def properties_order(names):
+    import functools
+    return sorted(names, key=functools.cmp_to_key(lambda a, b: -1 if _properties_less(a, b) else (1 if _properties_less(b, a) else 0)))
 
 
 class _Loader:
@@ -147,7 +174,7 @@ class _Loader:
         if t == 'scene' and self.root_dict is None:
             self.root_dict = d
         for k, v in d.items():
-            if k in ('type', 'id'):
+            if k in ('type', 'id', '_document_order'):
                 continue
             if isinstance(v, dict):
                 if t == 'scene' and k in self.by_id:
@@ -157,6 +184,7 @@ class _Loader:
             else:
                 props[k] = v
         p = Plugin(t, props, children, d.get('id', name))
+        p.document_order = bool(d.get('_document_order', False))     # xmlscene.py: children already in the parser's `_arg_N` order
         if p.id is not None and p.id not in self.by_id:
             self.by_id[p.id] = p
         return p
@@ -440,7 +468,7 @@ class Scene:
         return i
 
     # -- bsdfs: src/bsdfs/null.cpp, diffuse.cpp --
-    def _bsdf(self, b, key):
+    def _bsdf(self, b, key, emitter=False):
         if b is not None and id(b) in self._bsdf_index:
             return self._bsdf_index[id(b)]
         i = self.desc.n_bsdfs
@@ -448,9 +476,9 @@ class Scene:
             raise PluginError("too many BSDFs")
         self.desc.n_bsdfs += 1
         out = self.desc.bsdfs[i]
-        if b is None:                     # default BSDF of a shape: diffuse (shape.cpp)
+        if b is None:                     # default BSDF of a shape: diffuse, black on a shape that emits (shape.cpp:64-70)
             out.type = A.BSDF_DIFFUSE
-            out.reflectance[:] = [0.5] * 3
+            out.reflectance[:] = [0.0 if emitter else 0.5] * 3
             return i
         self._bsdf_index[id(b)] = i
         pr = _Props(b)
@@ -523,6 +551,52 @@ class Scene:
                 else:
                     au = av = float(pr.get('alpha', 0.1))
                 out.alpha_u, out.alpha_v = au, av
+        elif b.type in ('plastic', 'roughplastic'):
+            # src/bsdfs/plastic.cpp:151-200, src/bsdfs/roughplastic.cpp:169-253
+            int_ior = _lookup_ior(pr.get('int_ior', 'polypropylene'))
+            ext_ior = _lookup_ior(pr.get('ext_ior', 'air'))
+            rough = b.type == 'roughplastic'
+            if int_ior < 0 or ext_ior < 0 or (rough and int_ior == ext_ior):
+                raise PluginError("The interior and exterior indices of refraction must be positive%s!" % (" and differ" if rough else ""))
+            f32 = np.float32
+            eta = f32(int_ior) / f32(ext_ior)
+            out.type = A.BSDF_ROUGHPLASTIC if rough else A.BSDF_PLASTIC
+            out.eta = float(eta)
+            out.inv_eta_2 = float(f32(1.0) / (eta * eta))
+            for name in ('diffuse_reflectance', 'specular_reflectance'):
+                c = pr.child(name)
+                if c is not None and c.type not in ('rgb', 'srgb', 'uniform', 'd65'):
+                    raise PluginError("%s: textured %s is not supported" % (b.type, name))
+            diff = self._color(pr.child('diffuse_reflectance') or pr.get('diffuse_reflectance', 0.5), key)
+            out.reflectance[:] = diff
+            d_mean = _mean32(diff if self.spectrum == A.SPEC_RGB else diff[:1])
+            s_mean = f32(1.0)
+            spec = pr.child('specular_reflectance') or pr.get('specular_reflectance')
+            out.specular_reflectance[:] = [1.0] * 3
+            if spec is not None:
+                sr = self._color(spec, key)
+                out.has_specular_reflectance = 1
+                out.specular_reflectance[:] = sr
+                s_mean = _mean32(sr if self.spectrum == A.SPEC_RGB else sr[:1])
+            out.specular_sampling_weight = float(s_mean / (d_mean + s_mean))
+            out.nonlinear = int(bool(pr.get('nonlinear', False)))
+            if rough:
+                distr = str(pr.get('distribution', 'beckmann')).lower()
+                if distr not in ('beckmann', 'ggx'):
+                    raise PluginError("Specified an invalid distribution \"%s\", must be \"beckmann\" or \"ggx\"!" % distr)
+                out.distribution = A.MICROFACET_BECKMANN if distr == 'beckmann' else A.MICROFACET_GGX
+                out.sample_visible = int(bool(pr.get('sample_visible', True)))
+                if not out.sample_visible:
+                    raise PluginError("eval_transmittance(): requires visible normal sampling!")       # microfacet.h:520-521
+                if pr.has('alpha_u') or pr.has('alpha_v'):
+                    raise PluginError("The 'roughplastic' plugin currently does not support anisotropic microfacet distributions!")
+                alpha = float(np.sqrt(f32(pr.get('alpha_sq')))) if pr.has('alpha_sq') else float(pr.get('alpha', 0.1))
+                out.alpha_u = out.alpha_v = alpha
+                ext, internal = plastic.rough_tables(out.distribution, alpha, out.eta)
+                out.ext_transmittance[:] = ext.tolist()
+                out.internal_reflectance = float(internal)
+            else:
+                out.internal_reflectance = float(plastic.fresnel_diffuse_reflectance(f32(1.0) / eta))
         else:
             raise PluginError("unsupported BSDF '%s'" % b.type)
         pr.finish()
@@ -583,7 +657,7 @@ class Scene:
             out.frame_n[:] = n.astype(np.float32).tolist()
             out.inv_surface_area = float(1.0 / np.linalg.norm(np.cross(dp_du, dp_dv)))
         bsdfs = pr.children_of('bsdf')
-        out.bsdf = self._bsdf(bsdfs[0][1] if bsdfs else None, key + '.bsdf')
+        out.bsdf = self._bsdf(bsdfs[0][1] if bsdfs else None, key + '.bsdf', emitter=bool(pr.children_of('emitter')))
         interior, exterior = pr.child('interior'), pr.child('exterior')
         out.interior_medium = self._medium(interior, key + '.interior_medium') if interior else -1
         out.exterior_medium = self._medium(exterior, key + '.exterior_medium') if exterior else -1
@@ -870,8 +944,12 @@ class Scene:
         self.search_paths = list(SEARCH_PATHS)
         root = self.root
         integrator = sensor = None
-        pending_emitters = []
-        for name, c in root.children.items():
+        # Scene::Scene walks props.objects() (scene.cpp:27-66), i.e. the children sorted by their property names (load_dict: the
+        # dictionary keys; XML: `_arg_N` in document order); emitters are numbered in that order -- an area light when its shape
+        # comes up -- and Scene::sample_emitter_direction picks among them by index
+        names = list(root.children) if getattr(root, 'document_order', False) else properties_order(root.children)
+        for name in names:
+            c = root.children[name]
             if c.category == 'integrator':
                 integrator = c
             elif c.category == 'sensor':
@@ -879,13 +957,11 @@ class Scene:
             elif c.category == 'shape':
                 self._shape(c, name)
             elif c.category == 'emitter':
-                pending_emitters.append((name, c))
+                self._emitter(c, name)
             elif c.category in ('medium', 'bsdf', 'phase', 'texture', 'volume'):
                 pass  # only instantiated when referenced
             else:
                 raise PluginError("unexpected top-level object '%s' of type '%s'" % (name, c.type))
-        for name, c in pending_emitters:
-            self._emitter(c, name)
         if integrator is None:
             integrator = Plugin('volpath', {}, {})
         if sensor is None:

@@ -299,6 +299,8 @@ def xml_to_dict(string, base_dir=None, **kwargs):
     for k in kwargs:
         if k not in p.used:
             raise XMLError('Unused parameter "%s"!' % k)        # xml.cpp:976-981
+    if d.get('type') == 'scene':
+        d['_document_order'] = True          # scene.py: the children are in the parser's `_arg_N` order, not to be re-sorted by key
     return d
 
 
@@ -336,10 +338,16 @@ def _emit(lines, indent, key, v, out_dir, counter):
             elif name:
                 attrs += name
         body = []
-        for k, c in v.items():
-            if k in ('type', 'id'):
+        keys = list(v)
+        if t == 'scene' and not v.get('_document_order', False):
+            # the reference's load_dict hands the scene its children sorted by key (properties.cpp:48-71); its XML parser in
+            # document order: write them sorted, so that both front ends build the same scene (emitter indices)
+            from .scene import properties_order
+            keys = properties_order(keys)
+        for k in keys:
+            if k in ('type', 'id', '_document_order'):
                 continue
-            _emit(body, indent + 1, k, c, out_dir, counter)
+            _emit(body, indent + 1, k, v[k], out_dir, counter)
         if body:
             lines.append('%s<%s%s>' % (pad, tag, attrs))
             lines.extend(body)

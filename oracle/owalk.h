@@ -15,6 +15,10 @@ struct Counters {
         n_null += o.n_null; n_nee_steps += o.n_nee_steps; n_surface += o.n_surface; }
 };
 
+// ORC_TRACE=1 in the environment: sample_volpath prints its loop iterations and BSDF samples to stderr (debugging aid; a traced
+// copy of the reference's volpath.cpp prints the same lines, which is how the integrator-level differences were found)
+static const bool g_trace = getenv("ORC_TRACE") != nullptr;
+
 template <int SPEC> struct Walk {
     using Tr = SpecTraits<SPEC>;
     using Spec = typename Tr::Spec;
@@ -182,6 +186,7 @@ template <int SPEC> struct Walk {
             if (perform_rr) throughput = mul_f(throughput, rcp(q));
             active = active && depth < maxd;
             if (!active) break;
+            if (g_trace) fprintf(stderr, " it depth %u medium %d o %g %g %g d %g %g %g T %g res %g\n", depth, medium, ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z, unpol(throughput).v[0], unpol(result).v[0]);
 
             bool active_medium = active && medium >= 0;
             bool active_surface = active && !active_medium;
@@ -293,6 +298,7 @@ template <int SPEC> struct Walk {
                 }
                 float s1, s2x, s2y; draw_1d_2d(&s1, &s2x, &s2y);
                 BSDFSample<Spec> bs = Bs::sample(bsdf, si, s1, s2x, s2y);
+                if (g_trace) fprintf(stderr, "  surf depth %u wi.z %g wo %g %g %g pdf %g type %x val %g (shape %d bsdf %d)\n", depth, si.wi.z, bs.wo.x, bs.wo.y, bs.wo.z, bs.pdf, bs.sampled_type, unpol(bs.value).v[0], si.shape, bsdf.type);
                 Spec bsdf_val = si_to_world_mueller(si, bs.value, -bs.wo, si.wi);
                 throughput = smul(throughput, bsdf_val);
                 eta *= bs.eta;

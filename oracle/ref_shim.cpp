@@ -187,6 +187,19 @@ void ref_microfacet_sample(int type, float alpha_u, float alpha_v, const float *
     }
 }
 
+// eval_transmittance / eval_reflectance (microfacet.h:464-568): the tables roughplastic precomputes (roughplastic.cpp:231-250);
+// n must be a multiple of the packet size.  fresnel_diffuse_reflectance (fresnel.h:328-355).
+void ref_rough_transmittance(int type, float alpha, float eta, const float *mu, float *out_t, float *out_r_inv_eta, size_t n) {
+    using FloatP = dr::Packet<float>;
+    using FloatX = dr::DynamicArray<float>;
+    MicrofacetDistribution<FloatP, Color<float, 1>> d(type == 0 ? MicrofacetType::Beckmann : MicrofacetType::GGX, alpha);
+    FloatX m = dr::zeros<FloatX>(n), zero = dr::zeros<FloatX>(n);
+    for (size_t i = 0; i < n; ++i) m[i] = mu[i];
+    Vector<FloatX, 3> wi(dr::sqrt(1 - m * m), zero, m);
+    FloatX t = eval_transmittance(d, wi, eta), r = eval_reflectance(d, wi, 1.f / eta);
+    for (size_t i = 0; i < n; ++i) { out_t[i] = t[i]; out_r_inv_eta[i] = r[i]; }
+}
+float ref_fresnel_diffuse_reflectance(float eta) { return fresnel_diffuse_reflectance(eta); }
 
 // Lorenz-Mie amplitudes (include/mitsuba/render/mie.h:45-222), one (mu, radius) pair per call so that the
 // automatic series length (max_nested over the lanes, :76-79) is the lane's own: out7 = (re S1, im S1, re S2, im S2, Ns, Cs, Ct)

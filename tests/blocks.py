@@ -193,6 +193,27 @@ def b_gauss_legendre(lib, prefix, n):
     return out
 
 
+PLASTIC_TABLES = [(0, 0.1, 1.49 / 1.000277), (1, 0.3, 1.5), (0, 0.5, 1.33), (1, 0.05, 1.9)]       # (distribution, alpha, eta)
+PLASTIC_ETAS = [1.49 / 1.000277, 1.000277 / 1.49, 1.33, 0.7, 2.5]
+
+
+def b_plastic_tables(lib, prefix, n):
+    """eval_transmittance / eval_reflectance over roughplastic's 64 cosines and fresnel_diffuse_reflectance (reference only: the
+    product side is numpy in mitsuba3_nasa_b200/plastic.py)."""
+    out = {}
+    mu = np.maximum(np.float32(1e-6), np.linspace(0, 1, 64, dtype=np.float32))
+    lib.ref_rough_transmittance.argtypes = [C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+    for k, (kind, alpha, eta) in enumerate(PLASTIC_TABLES):
+        t, r = np.zeros(64, np.float32), np.zeros(64, np.float32)
+        lib.ref_rough_transmittance(kind, alpha, np.float32(eta), _p(mu), _p(t), _p(r), 64)
+        out["t%d" % k] = t
+        out["r%d" % k] = r
+    lib.ref_fresnel_diffuse_reflectance.restype = C.c_float
+    lib.ref_fresnel_diffuse_reflectance.argtypes = [C.c_float]
+    out["fdr"] = np.array([lib.ref_fresnel_diffuse_reflectance(np.float32(e)) for e in PLASTIC_ETAS], np.float32)
+    return out
+
+
 def b_mie_scatter(lib, prefix, n):
     rng = np.random.default_rng(51)
     q = rng.uniform(-3, 3, (n, 7)).astype(np.float32)
@@ -354,7 +375,7 @@ BLOCKS = {
 
 # blocks that are compared by their own tests (tests/test_oracle_vs_ref.py test_mie_header, test_gauss_legendre_header) but
 # whose reference outputs live in the same golden file
-EXTRA_GOLDEN = {"mie": b_mie, "gauss_legendre": b_gauss_legendre}
+EXTRA_GOLDEN = {"mie": b_mie, "gauss_legendre": b_gauss_legendre, "plastic_tables": b_plastic_tables}
 
 
 def compare(name, got, want, tol):

@@ -99,6 +99,8 @@ def xml_cases():
         'xml_homo_dielectric_envmap': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_homo_dielectric_envmap_volpath.xml'), spp=2, seed=0, max_flips=0.005),
         'xml_homo_roughdielectric_spot': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_homo_roughdielectric_spot_volpath.xml'), spp=2, seed=0, max_flips=0.005),
         'xml_homo_area_light': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_homo_area_light_volpath.xml'), spp=2, seed=0, max_flips=0.005),
+        'xml_homo_obj_inside_medium': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_homo_obj_inside_medium_volpath.xml'), spp=2, seed=0, max_flips=0.005),
+        'xml_surf_area_light': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_surf_area_light_volpath.xml'), spp=2, seed=0, max_flips=0.005),
         'xml_homo_spectral_sigmat_mis': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_homo_spectral_sigmat_volpathmis.xml'), spp=2, seed=0, max_flips=0.005),
         'xml_hetero_spectral_sigmat_mis': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_hetero_spectral_sigmat_volpathmis.xml'), spp=2, seed=0, max_flips=0.05),
         'xml_hetero_sigmat': dict(variant='scalar_rgb', file=os.path.join(PM_DIR, 'test_hetero_sigmat_volpath.xml'), spp=2, seed=0, max_flips=0.05),
@@ -187,14 +189,32 @@ def cases():
     c['envmap_mesh_mono'] = dict(variant='scalar_mono', scene=d, spp=8, seed=2, kind='samples')
     # volpathmis (src/integrators/volpathmis.cpp with use_spectral_mis): spectrally varying and grey
     # extinction, heterogeneous medium with an albedo grid, area emitter + diffuse floor (surface NEE / emitter-hit MIS), mono
+    import copy
     for k in ('c1_rgb', 'homog_rgb_spectral_extinction', 'het_rgb_albedo_grid', 'area_emitter', 'c1_mono_seed3', 'envmap_homog_rgb'):
-        import copy
         m = copy.deepcopy(c[k])
         m['scene']['integrator']['type'] = 'volpathmis'
         if k == 'c1_rgb':
             m['scene'] = scenes.c1_homogeneous_cube(res=12, spp=16)
             m['scene']['integrator']['type'] = 'volpathmis'
         c['mis_' + k] = m
+    # plastic / roughplastic (src/bsdfs/plastic.cpp, roughplastic.cpp): a plastic floor under the lamp of `area_emitter`, a
+    # rough plastic ball beside the cube (ggx and beckmann, with and without a specular tint, nonlinear colour shift)
+    def plastic_scene(integrator='volpath', distribution='beckmann', alpha=0.1, tint=False, nonlinear=False):
+        d = copy.deepcopy(c['area_emitter']['scene'])
+        d['integrator']['type'] = integrator
+        d['floor']['bsdf'] = {'type': 'plastic', 'diffuse_reflectance': {'type': 'rgb', 'value': [0.5, 0.3, 0.2]}, 'nonlinear': nonlinear}
+        d['ball'] = {'type': 'sphere', 'center': [1.6, 0.3, -0.6], 'radius': 0.7,
+                     'bsdf': {'type': 'roughplastic', 'distribution': distribution, 'alpha': alpha, 'nonlinear': nonlinear,
+                              'diffuse_reflectance': {'type': 'rgb', 'value': [0.2, 0.7, 0.7]}}}
+        if tint:
+            d['floor']['bsdf']['specular_reflectance'] = {'type': 'rgb', 'value': [0.9, 0.8, 0.6]}
+            d['ball']['bsdf']['specular_reflectance'] = {'type': 'rgb', 'value': [0.7, 0.9, 0.8]}
+            d['ball']['bsdf']['int_ior'] = 1.9
+        return d
+    c['plastic_rgb'] = dict(variant='scalar_rgb', scene=plastic_scene(), spp=16, seed=0, kind='samples')
+    c['plastic_ggx_tint_nonlinear_rgb'] = dict(variant='scalar_rgb', scene=plastic_scene(distribution='ggx', alpha=0.35, tint=True, nonlinear=True), spp=16, seed=1, kind='samples')
+    c['plastic_mono_mis'] = dict(variant='scalar_mono', scene=plastic_scene(integrator='volpathmis', alpha=0.25), spp=16, seed=2, kind='samples')
+    c['plastic_pol'] = dict(variant='scalar_mono_polarized', scene=plastic_scene(alpha=0.2), spp=16, seed=3, kind='samples')
     # radiancemeter looking through the cube
     d = scenes.c1_homogeneous_cube(res=1, spp=64, max_depth=16)
     d['sensor'] = {'type': 'radiancemeter', 'origin': [0.2, 0.1, 4.0], 'direction': [-0.05, 0.0, -1.0],

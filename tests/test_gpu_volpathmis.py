@@ -23,7 +23,7 @@ from test_gpu_mesh import _compare
 pytestmark = pytest.mark.gpu
 MIS_CASES = [n for n in scalar_cases.cases() if n.startswith('mis_')]
 VOLPATH_STEMS = ['test_hetero_sigmat', 'test_hetero_sigmat_albedo', 'test_homo_null_envmap', 'test_homo_dielectric_envmap',
-                 'test_homo_roughdielectric_spot', 'test_homo_area_light']
+                 'test_homo_roughdielectric_spot', 'test_homo_area_light', 'test_homo_obj_inside_medium', 'test_surf_area_light']
 MIS_STEMS = ['test_homo_spectral_sigmat', 'test_hetero_spectral_sigmat']
 
 

@@ -317,3 +317,18 @@ def test_gauss_legendre_header(golden):
         sd = mie.SizeDistribution({'min_radius': -1.0, 'max_radius': 1.0, 'gauss_points': n})
         x, w = golden["gauss_legendre/x%d" % n], golden["gauss_legendre/w%d" % n]
         assert np.abs(sd.nodes - x).max() <= 1e-7 and np.abs(sd.weights - w).max() <= 1e-7, n
+
+
+def test_plastic_tables_header(golden):
+    """The tables roughplastic precomputes (roughplastic.cpp:231-250): eval_transmittance / eval_reflectance of
+    include/mitsuba/render/microfacet.h:464-568 (float32 packets, 32 x 32 or 128 x 128 Gauss-Legendre nodes) against the host's
+    numpy restatement (mitsuba3_nasa_b200/plastic.py, float64 integrand), and fresnel_diffuse_reflectance (fresnel.h:328-355)."""
+    from mitsuba3_nasa_b200 import plastic
+    mu = np.maximum(np.float32(1e-6), np.linspace(0, 1, 64, dtype=np.float32))
+    for k, (kind, alpha, eta) in enumerate(blocks.PLASTIC_TABLES):
+        ext, internal = plastic.rough_tables(kind, alpha, np.float32(eta))
+        t, r = golden["plastic_tables/t%d" % k], golden["plastic_tables/r%d" % k]
+        assert np.abs(ext - t).max() <= 4e-6, (k, np.abs(ext - t).max())
+        assert abs(float(internal) - float(np.float32((r * mu).mean(dtype=np.float32) * 2))) <= 4e-6
+    for e, want in zip(blocks.PLASTIC_ETAS, golden["plastic_tables/fdr"]):
+        assert plastic.fresnel_diffuse_reflectance(np.float32(e)) == want

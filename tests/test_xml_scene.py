@@ -98,14 +98,16 @@ C2_XML = """
             <integer name="sample_count" value="4"/>
         </sampler>
     </sensor>
-    <!-- the reference to a_medium comes before its declaration -->
-    <shape type="rectangle" id="top">
-        <bsdf type="null"/>
+    <!-- the reference to a_medium comes before its declaration; shapes in the order load_dict sees the dictionary
+         keys of scenes.c2_rayleigh_slab (sorted: "bottom" < "top", properties.cpp:48-71) -->
+    <shape type="rectangle" id="bottom">
+        <bsdf type="diffuse">
+            <float name="reflectance" value="0.3"/>
+        </bsdf>
         <transform name="to_world">
-            <scale x="$scale" y="$scale" z="1"/>
-            <translate z="1"/>
+            <scale value="$scale $scale 1"/>
         </transform>
-        <ref id="a_medium" name="interior"/>
+        <ref id="a_medium" name="exterior"/>
     </shape>
     <medium type="homogeneous" id="a_medium">
         <float name="sigma_t" value="0.5"/>
@@ -115,14 +117,13 @@ C2_XML = """
             <float name="depolarization" value="0.0"/>
         </phase>
     </medium>
-    <shape type="rectangle" id="bottom">
-        <bsdf type="diffuse">
-            <float name="reflectance" value="0.3"/>
-        </bsdf>
+    <shape type="rectangle" id="top">
+        <bsdf type="null"/>
         <transform name="to_world">
-            <scale value="$scale $scale 1"/>
+            <scale x="$scale" y="$scale" z="1"/>
+            <translate z="1"/>
         </transform>
-        <ref id="a_medium" name="exterior"/>
+        <ref id="a_medium" name="interior"/>
     </shape>
     <emitter type="directional" id="light">
         <vector name="direction" value="-0.5, 0.0, -0.8660254"/>
@@ -260,8 +261,9 @@ REF_SCENES = "/root/reference/resources/data/tests/scenes/participating_media"
 def test_parser_reads_the_reference_test_scenes():
     """The fork's own participating-media test scenes (test_renders.py) go through the parser: <path>, nested <include>
     with <default>s defined in the included preamble, version 2 files, unnamed children, textures.  Those that need only
-    what this backend has (`obj`, `envmap`, `checkerboard`, `moment` included) load; the others are refused by load_dict with the
-    name of the missing plugin (plastic, thindielectric, spot, volpathmis ...)."""
+    what this backend has (`obj`, `envmap`, `checkerboard`, `moment`, `spot`, the dielectric and plastic BSDFs, `volpathmis`) load --
+    ten of the eleven; `test_homo_emitter_inside_medium` gives its area light a tabulated spectrum, whose conversion to RGB needs the
+    CIE 1931 observer tables this repository does not carry, and is refused by load_dict with the name of the missing plugin."""
     import glob
     files = sorted(glob.glob(os.path.join(REF_SCENES, "*.xml")))
     assert len(files) >= 10
@@ -279,7 +281,7 @@ def test_parser_reads_the_reference_test_scenes():
             loaded.append(os.path.basename(f))
         except S.PluginError as e:
             assert 'not found' in str(e) or 'unsupported' in str(e) or 'supported' in str(e), str(e)
-    assert {'test_hetero_sigmat_volpath.xml', 'test_hetero_sigmat_albedo_volpath.xml', 'test_homo_null_envmap_volpath.xml'} <= set(loaded)
+    assert len(loaded) == len(files) - 1 and 'test_homo_emitter_inside_medium_volpath.xml' not in loaded, loaded
     with open(os.path.join(REF_SCENES, "test_hetero_sigmat_volpath.xml")) as fh:
         d = xml_to_dict(fh.read(), REF_SCENES, integrator="volpath")
     vol = d['medium1']['sigma_t']
