@@ -231,6 +231,7 @@ typedef struct mib_integrator {
     int32_t majorant_res;    /* 0: reference behaviour (one global majorant per heterogeneous medium, heterogeneous.cpp:163-185);
                               * M > 0: "fast" mode, M^3 supergrid of local majorants + DDA free-flight sampling:
                               * unbiased, but no longer the reference's random sequence -- agreement is statistical only */
+    int32_t spectral_mis;    /* volpathmis: `use_spectral_mis` (volpathmis.cpp:93, default 1): n x n weight matrices; 0: one spectrum */
 } mib_integrator;
 
 typedef struct mib_scene_desc {

@@ -9,8 +9,18 @@
 
 namespace mib {
 
-// volpathmis.cpp:506-527 (SpectralMis branch): W[i][j] *= p[j] / f[i], non-finite ratios and NaN products become 0
-template <int NC> MIB_D void mis_update(float *W, const float *p, const float *f) {
+// volpathmis.cpp:506-527.  SpectralMis: W[i][j] *= p[j] / f[i], non-finite ratios and NaN products become 0; otherwise
+// (mib_integrator.spectral_mis = 0) the weights are one spectrum, kept in row 0: W[j] *= p[channel] / f[j], non-finite -> 0
+template <int NC> MIB_D void mis_update(float *W, const float *p, const float *f, uint32_t channel) {
+    if (!sc.d.integrator.spectral_mis) {
+        const float pdf = ch<NC>(p, channel);
+#pragma unroll
+        for (int j = 0; j < NC; ++j) {
+            const float ratio = W[j] * div_(pdf, f[j]);
+            W[j] = isfinite(ratio) ? ratio : 0.f;
+        }
+        return;
+    }
 #pragma unroll
     for (int i = 0; i < NC; ++i) {
         const float inv_f = rcp_(f[i]);
@@ -23,20 +33,28 @@ template <int NC> MIB_D void mis_update(float *W, const float *p, const float *f
         }
     }
 }
-template <int NC> MIB_D void mis_update(float *W, float p, const float *f) {
+template <int NC> MIB_D void mis_update(float *W, float p, const float *f, uint32_t channel) {
     float pv[NC];
 #pragma unroll
     for (int c = 0; c < NC; ++c) pv[c] = p;
-    mis_update<NC>(W, pv, f);
+    mis_update<NC>(W, pv, f, channel);
 }
-template <int NC> MIB_D void mis_update(float *W, float p, float f) {
+template <int NC> MIB_D void mis_update(float *W, float p, float f, uint32_t channel) {
     float pv[NC], fv[NC];
 #pragma unroll
     for (int c = 0; c < NC; ++c) { pv[c] = p; fv[c] = f; }
-    mis_update<NC>(W, pv, fv);
+    mis_update<NC>(W, pv, fv, channel);
 }
 // :530-543 / :546-563
 template <int NC> MIB_D void mis_weights(const float *W, float *w) {
+    if (!sc.d.integrator.spectral_mis) {
+        float mn = fabsf(W[0]);
+#pragma unroll
+        for (int j = 1; j < NC; ++j) mn = fminf(mn, fabsf(W[j]));
+#pragma unroll
+        for (int j = 0; j < NC; ++j) w[j] = mn == 0.f ? 0.f : div_(1.f, W[j]);
+        return;
+    }
 #pragma unroll
     for (int i = 0; i < NC; ++i) {
         float s = W[i * NC];
@@ -46,6 +64,14 @@ template <int NC> MIB_D void mis_weights(const float *W, float *w) {
     }
 }
 template <int NC> MIB_D void mis_weights(const float *A, const float *B, float *w) {
+    if (!sc.d.integrator.spectral_mis) {
+        float sum[NC], mn = 0.f;
+#pragma unroll
+        for (int j = 0; j < NC; ++j) { sum[j] = A[j] + B[j]; mn = j == 0 ? fabsf(sum[0]) : fminf(mn, fabsf(sum[j])); }
+#pragma unroll
+        for (int j = 0; j < NC; ++j) w[j] = mn == 0.f ? 0.f : div_(1.f, sum[j]);
+        return;
+    }
 #pragma unroll
     for (int i = 0; i < NC; ++i) {
         float s = A[i * NC] + B[i * NC];
@@ -109,7 +135,7 @@ MIB_D void sample_emitter_mis(Pcg32 &rng, Counters &cnt, V3 ref_p, V3 ref_n, con
     for (int c = 0; c < NC; ++c) emitted[c] = ds.pdf == 0.f ? 0.f : emitted[c] * ds.pdf;
     bool active = ds.pdf != 0.f;
     if (!active) return;
-    mis_update<NC>(Wn, ds.pdf, 1.f);
+    mis_update<NC>(Wn, ds.pdf, 1.f, channel);
 
     Ray ray = spawn_ray_to(ref_p, ref_n, ds.p);
     const float max_dist = ray.maxt;
@@ -140,8 +166,8 @@ MIB_D void sample_emitter_mis(Pcg32 &rng, Counters &cnt, V3 ref_p, V3 ref_n, con
                 float trv[NC], ffp[NC];
 #pragma unroll
                 for (int c = 0; c < NC; ++c) { trv[c] = exp_(-t * mei.maj[c]); ffp[c] = surf ? trv[c] : trv[c] * mei.maj[c]; }
-                mis_update<NC>(Wn, ffp, trv);
-                mis_update<NC>(Wu, ffp, trv);
+                mis_update<NC>(Wn, ffp, trv, channel);
+                mis_update<NC>(Wu, ffp, trv, channel);
             }
             if ((mei.t > remaining) && valid(mei)) total_dist = ds.dist;
             if (mei.t > remaining) mei.t = inf_f();
@@ -154,8 +180,8 @@ MIB_D void sample_emitter_mis(Pcg32 &rng, Counters &cnt, V3 ref_p, V3 ref_n, con
                 float r[NC];
 #pragma unroll
                 for (int c = 0; c < NC; ++c) r[c] = div_(mei.sigma_n[c], mei.maj[c]);
-                if (is_spectral) { mis_update<NC>(Wn, 1.f, mei.sigma_n); mis_update<NC>(Wu, r, mei.sigma_n); }
-                else { mis_update<NC>(Wn, 1.f, r); mis_update<NC>(Wu, mei.sigma_n, mei.sigma_n); }
+                if (is_spectral) { mis_update<NC>(Wn, 1.f, mei.sigma_n, channel); mis_update<NC>(Wu, r, mei.sigma_n, channel); }
+                else { mis_update<NC>(Wn, 1.f, r, channel); mis_update<NC>(Wu, mei.sigma_n, mei.sigma_n, channel); }
             }
         }
         if (active_surface && needs_intersection) ray_intersect(ray, si);
@@ -165,13 +191,20 @@ MIB_D void sample_emitter_mis(Pcg32 &rng, Counters &cnt, V3 ref_p, V3 ref_n, con
         if (active_surface) {
             const mib_bsdf &bsdf = sc.d.bsdfs[sc.d.shapes[si.shape].bsdf];
             const float nt = bsdf_null_transmission(bsdf, si);
-            mis_update<NC>(Wn, 1.f, nt);
-            mis_update<NC>(Wu, 1.f, nt);
+            mis_update<NC>(Wn, 1.f, nt, channel);
+            mis_update<NC>(Wu, 1.f, nt, channel);
             ray = spawn_ray(si.p, si.n, ray.d);
         }
         ray.maxt = remaining;
         needs_intersection = needs_intersection || active_surface;
-        active = active && (active_medium || active_surface) && mis_any<NC>(Wu);
+        bool go;
+        if (sc.d.integrator.spectral_mis) go = mis_any<NC>(Wu);
+        else {
+            go = false;
+#pragma unroll
+            for (int j = 0; j < NC; ++j) go = go || Wu[j] != 0.f || Wn[j] != 0.f;
+        }
+        active = active && (active_medium || active_surface) && go;
         if (active_surface && is_medium_transition(si)) medium = target_medium(si, ray.d);
     }
 }
@@ -203,7 +236,7 @@ MIB_D void mis_step(Pcg32 &rng, Counters &cnt, MisState<SPEC> &st) {
         const bool perform_rr = !st.last_event_was_null && depth > rrd;
         const float u = rng.next();
         active = !(u >= q && perform_rr);
-        if (perform_rr) mis_update<NC>(W, q, 1.f);
+        if (perform_rr) mis_update<NC>(W, q, 1.f, channel);
         st.last_event_was_null = false;
         active = active && depth < maxd;
         active = active && mis_any<NC>(W);
@@ -226,8 +259,8 @@ MIB_D void mis_step(Pcg32 &rng, Counters &cnt, MisState<SPEC> &st) {
             float trv[NC], ffp[NC];
 #pragma unroll
             for (int c = 0; c < NC; ++c) { trv[c] = exp_(-t * mei.maj[c]); ffp[c] = surf ? trv[c] : trv[c] * mei.maj[c]; }
-            mis_update<NC>(W, ffp, trv);
-            mis_update<NC>(Wnee, ffp, trv);
+            mis_update<NC>(W, ffp, trv, channel);
+            mis_update<NC>(Wnee, ffp, trv, channel);
         }
         escaped = !valid(mei);
         active_medium = valid(mei);
@@ -249,8 +282,8 @@ MIB_D void mis_step(Pcg32 &rng, Counters &cnt, MisState<SPEC> &st) {
             float r[NC];
 #pragma unroll
             for (int c = 0; c < NC; ++c) r[c] = div_(mei.sigma_n[c], mei.maj[c]);
-            if (is_spectral) { mis_update<NC>(W, r, mei.sigma_n); mis_update<NC>(Wnee, 1.f, mei.sigma_n); }
-            else { mis_update<NC>(W, mei.sigma_n, mei.sigma_n); mis_update<NC>(Wnee, 1.f, r); }
+            if (is_spectral) { mis_update<NC>(W, r, mei.sigma_n, channel); mis_update<NC>(Wnee, 1.f, mei.sigma_n, channel); }
+            else { mis_update<NC>(W, mei.sigma_n, mei.sigma_n, channel); mis_update<NC>(Wnee, 1.f, r, channel); }
             ray.o = mei.p;
             si.t = si.t - mei.t;
         }
@@ -260,8 +293,8 @@ MIB_D void mis_step(Pcg32 &rng, Counters &cnt, MisState<SPEC> &st) {
                 float r[NC];
 #pragma unroll
                 for (int c = 0; c < NC; ++c) r[c] = div_(mei.sigma_t[c], mei.maj[c]);
-                mis_update<NC>(W, r, mei.sigma_s);
-            } else mis_update<NC>(W, mei.sigma_t, mei.sigma_s);
+                mis_update<NC>(W, r, mei.sigma_s, channel);
+            } else mis_update<NC>(W, mei.sigma_t, mei.sigma_s, channel);
             const int phase = md.phase;
             const Frame3 mei_sh = make_frame(ray.d);
             float P[NC];
@@ -271,8 +304,8 @@ MIB_D void mis_step(Pcg32 &rng, Counters &cnt, MisState<SPEC> &st) {
                 sample_emitter_mis<SPEC>(rng, cnt, mei.p, v3(0.f), nullptr, medium, channel, W, Wn, Wu, ds, em);
                 const V3 wo = to_local(mei_sh, ds.d);
                 const float ppdf = phase_eval<SPEC>(phase, wo, P);
-                mis_update<NC>(Wn, 1.f, P);
-                mis_update<NC>(Wu, ds.delta ? 0.f : ppdf, P);
+                mis_update<NC>(Wn, 1.f, P, channel);
+                mis_update<NC>(Wu, ds.delta ? 0.f : ppdf, P, channel);
                 mis_weights<NC>(Wn, Wu, w);
 #pragma unroll
                 for (int c = 0; c < NC; ++c) R[c] += w[c] * em[c];
@@ -289,8 +322,8 @@ MIB_D void mis_step(Pcg32 &rng, Counters &cnt, MisState<SPEC> &st) {
             needs_intersection = true;
 #pragma unroll
             for (int c = 0; c < NC; ++c) P[c] *= ppdf;
-            mis_update<NC>(W, ppdf, P);
-            mis_update<NC>(Wnee, 1.f, P);
+            mis_update<NC>(W, ppdf, P, channel);
+            mis_update<NC>(Wnee, 1.f, P, channel);
         }
     }
 
@@ -300,7 +333,7 @@ MIB_D void mis_step(Pcg32 &rng, Counters &cnt, MisState<SPEC> &st) {
         const bool count_direct = depth == 0u || specular_chain;
         const int emitter = si_emitter(si);
         if (emitter >= 0 && !(depth == 0u && I.hide_emitters)) {
-            if (!count_direct) mis_update<NC>(Wnee, pdf_emitter_direction(emitter, st.last_p, si.p, si.sh.n, -si.wi), 1.f);
+            if (!count_direct) mis_update<NC>(Wnee, pdf_emitter_direction(emitter, st.last_p, si.p, si.sh.n, -si.wi), 1.f, channel);
             const mib_emitter &e = sc.d.emitters[emitter];
             float w[NC];
             if (count_direct) mis_weights<NC>(W, w);
@@ -321,8 +354,8 @@ MIB_D void mis_step(Pcg32 &rng, Counters &cnt, MisState<SPEC> &st) {
             const V3 wo = to_local(si.sh, ds.d);
             bsdf_eval<SPEC>(bsdf, si, wo, V);
             const float bpdf = bsdf_pdf(bsdf, si, wo);
-            mis_update<NC>(Wn, 1.f, V);
-            mis_update<NC>(Wu, ds.delta ? 0.f : bpdf, V);
+            mis_update<NC>(Wn, 1.f, V, channel);
+            mis_update<NC>(Wu, ds.delta ? 0.f : bpdf, V, channel);
             mis_weights<NC>(Wn, Wu, w);
 #pragma unroll
             for (int c = 0; c < NC; ++c) R[c] += w[c] * em[c];
@@ -348,8 +381,8 @@ MIB_D void mis_step(Pcg32 &rng, Counters &cnt, MisState<SPEC> &st) {
         }
 #pragma unroll
         for (int c = 0; c < NC; ++c) V[c] *= bs.pdf;
-        if (active_surface) mis_update<NC>(W, bs.pdf, V);
-        if (non_null) mis_update<NC>(Wnee, 1.f, V);
+        if (active_surface) mis_update<NC>(W, bs.pdf, V, channel);
+        if (non_null) mis_update<NC>(Wnee, 1.f, V, channel);
         if (active_surface && is_medium_transition(si)) medium = target_medium(si, ray.d);
     }
     active = active && (active_surface || active_medium);

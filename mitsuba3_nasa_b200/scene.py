@@ -922,8 +922,7 @@ class Scene:
         if it.type == 'volpathmis':
             if self.spectrum == A.SPEC_MONO_POLARIZED:
                 raise PluginError("This integrator currently does not support polarized mode!")      # volpathmis.cpp:134-136
-            if not bool(pr.get('use_spectral_mis', True)):
-                raise PluginError("volpathmis: only use_spectral_mis = true (the plugin's default) is implemented")
+            out.spectral_mis = int(bool(pr.get('use_spectral_mis', True)))                          # volpathmis.cpp:93
         out.rng_arg_order = A.RNG_ARGS_LEFT_TO_RIGHT
         out.double_phase_quirk = 1 if it.type == 'volpath' else 0
         # backend extension (not in the fork): M^3 supergrid of local majorants, 0 = the reference's global majorant

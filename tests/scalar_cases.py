@@ -197,6 +197,11 @@ def cases():
             m['scene'] = scenes.c1_homogeneous_cube(res=12, spp=16)
             m['scene']['integrator']['type'] = 'volpathmis'
         c['mis_' + k] = m
+    # volpathmis with use_spectral_mis = false (volpathmis.cpp:519-525,539-542,558-560): one weight spectrum instead of the matrices
+    for k in ('homog_rgb_spectral_extinction', 'het_rgb_albedo_grid', 'area_emitter'):
+        m = copy.deepcopy(c[k])
+        m['scene']['integrator'].update(type='volpathmis', use_spectral_mis=False)
+        c['mis_plain_' + k] = m
     # plastic / roughplastic (src/bsdfs/plastic.cpp, roughplastic.cpp): a plastic floor under the lamp of `area_emitter`, a
     # rough plastic ball beside the cube (ggx and beckmann, with and without a specular tint, nonlinear colour shift)
     def plastic_scene(integrator='volpath', distribution='beckmann', alpha=0.1, tint=False, nonlinear=False):

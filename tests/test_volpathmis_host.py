@@ -30,9 +30,9 @@ def test_polarized_variant_is_refused_like_the_reference():
         S.load_dict(_cube(), 'llvm_ad_mono_polarized')
 
 
-def test_plain_mis_is_not_built():
-    with pytest.raises(PluginError, match="use_spectral_mis"):
-        S.load_dict(_cube(use_spectral_mis=False), 'llvm_ad_rgb')
+def test_use_spectral_mis_reaches_the_descriptor():
+    assert S.load_dict(_cube(), 'llvm_ad_rgb').desc.integrator.spectral_mis == 1                     # volpathmis.cpp:93
+    assert S.load_dict(_cube(use_spectral_mis=False), 'llvm_ad_rgb').desc.integrator.spectral_mis == 0
 
 
 def test_grey_medium_same_expectation_as_volpath():
