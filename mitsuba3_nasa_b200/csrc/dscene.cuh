@@ -176,7 +176,8 @@ MIB_SUB_GEOM SurfIt ray_intersect2(Ray ray) {
         int face = 0;
         float t, u = 0.f, v = 0.f;
         if (MIB_FT(FT_MESH) && sc.d.shapes[i].type == MIB_SHAPE_MESH)
-            t = intersect_mesh(sc.d.shapes[i], sc.buffers[sc.d.shapes[i].mesh_buffer], ray.o, ray.d, ray.maxt, face, u, v);
+            // the search is cut at the nearest hit of the shapes before this one (a later shape only wins with a strictly smaller t)
+            t = intersect_mesh(sc.d.shapes[i], sc.buffers[sc.d.shapes[i].mesh_buffer], ray.o, ray.d, fminf(ray.maxt, best), face, u, v);
         else
             t = intersect_shape(i, ray, face);
         if (t < best) { best = t; bs = i; bf = face; bu = u; bv = v; }

@@ -263,7 +263,9 @@ static inline SurfaceInteraction ray_intersect(const Scene &sc, const Ray &ray) 
         int face = 0;
         float t, bu = 0.f, bv = 0.f;
         if (sc.d.shapes[i].type == MIB_SHAPE_MESH)
-            t = intersect_mesh(sc.d.shapes[i], sc.buffers[sc.d.shapes[i].mesh_buffer], ray, ray.maxt, &face, &bu, &bv);
+            // (the search is cut at the nearest hit of the shapes before this one: same result -- a later shape only wins with a
+            //  strictly smaller t -- and the kernels prune their traversal the same way)
+            t = intersect_mesh(sc.d.shapes[i], sc.buffers[sc.d.shapes[i].mesh_buffer], ray, minimum(ray.maxt, best), &face, &bu, &bv);
         else
             t = intersect_shape(sc, i, ray, &face);
         if (t < best) { best = t; best_shape = i; best_face = face; best_u = bu; best_v = bv; }

@@ -1,6 +1,6 @@
 """Throughput of the one-thread-one-path coverage kernels on the fork's own render-test scenes: each of the ten
 covered participating-media scenes rendered with volpath and with volpathmis at 48 x 48 x `spp` samples through mi.render (device
-film, one D2H of the 48 x 48 image), second call timed.  Prints one JSON line per (scene, integrator).  Not a bench line of
+film, one D2H of the 48 x 48 image), second call timed (`ms`: wall clock of the call; `kernel_ms`: CUDA-event time of the kernel, the throughput's denominator).  Prints one JSON line per (scene, integrator).  Not a bench line of
 bench.py: these kernels exist for coverage of the reference's plugin set, the headline workloads run on the pool kernels.
 
     python profiles/coverage_bench.py [spp]"""
@@ -34,8 +34,12 @@ def main():
             t = time.perf_counter()
             img = np.asarray(mi.render(scene, seed=1, spp=spp))
             dt = time.perf_counter() - t
-            print(json.dumps({"scene": stem, "integrator": integrator, "spp": spp, "samples": 48 * 48 * spp, "ms": round(dt * 1e3, 2),
-                              "msamples_per_s": round(48 * 48 * spp / dt / 1e6, 1), "mean": round(float(img.mean()), 5)}), flush=True)
+            c = scene.device.counters()
+            n = 48 * 48 * spp
+            print(json.dumps({"scene": stem, "integrator": integrator, "spp": spp, "samples": n, "ms": round(dt * 1e3, 2),
+                              "kernel_ms": round(c['kernel_ms'], 2), "msamples_per_s": round(n / (c['kernel_ms'] * 1e-3) / 1e6, 1),
+                              "per_sample": {k: round(c[k] / n, 2) for k in ('n_lookups', 'n_real', 'n_null', 'n_nee_steps', 'n_surface')},
+                              "mean": round(float(img.mean()), 5)}), flush=True)
 
 
 if __name__ == "__main__":

@@ -29,6 +29,9 @@ funcs.sort()
 sass=subprocess.run(['ncu','-i',rep,'--page','source','--csv','--print-source','sass'],capture_output=True,text=True).stdout
 rows=list(csv.reader(sass.splitlines()))
 hdr=rows[1]; data=[r for r in rows[2:] if len(r)==len(hdr)]
+# a report with several launches repeats the header: keep the rows of the last launch
+last=max([i for i,r in enumerate(data) if r[hdr.index('Address')]=='Address'], default=-1); data=data[last+1:]
+TI=hdr.index('Thread Instructions Executed') if 'Thread Instructions Executed' in hdr else None
 iE=hdr.index('Instructions Executed'); iA=hdr.index('Address'); iSm=hdr.index('# Samples')
 base=int(data[0][iA],16)
 import bisect
@@ -39,6 +42,6 @@ for r in data:
     off=int(r[iA],16)-base; e=int(r[iE]); sm=int(r[iSm])
     i=bisect.bisect_right(offs,off)-1
     name=short(funcs[i][1]) if i>=0 else '?'
-    a=agg.setdefault(name,[0,0,0,0]); a[0]+=1; a[1]+= (e>0); a[2]+=e; a[3]+=sm; tot+=e; totS+=sm
-print('%-28s %7s %7s %8s %8s'%('function','instr','hot','exec%','stall%'))
-for k,v in sorted(agg.items(),key=lambda kv:-kv[1][2]): print('%-28s %7d %7d %7.1f%% %7.1f%%'%(k,v[0],v[1],100*v[2]/tot,100*v[3]/max(totS,1)))
+    a=agg.setdefault(name,[0,0,0,0,0]); a[0]+=1; a[1]+= (e>0); a[2]+=e; a[3]+=sm; a[4]+=(int(r[TI]) if TI is not None else 0); tot+=e; totS+=sm
+print('%-28s %7s %7s %8s %8s %6s'%('function','instr','hot','exec%','stall%','lanes'))
+for k,v in sorted(agg.items(),key=lambda kv:-kv[1][2]): print('%-28s %7d %7d %7.1f%% %7.1f%% %6.1f'%(k,v[0],v[1],100*v[2]/tot,100*v[3]/max(totS,1),v[4]/max(v[2],1)))
