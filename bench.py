@@ -77,6 +77,21 @@ def measured_traffic(kernel_key, n_samples):
         return None
 
 
+def measured_issue(kernel_key):
+    """What bounds these kernels is instruction issue, not a memory or FP32 roof: issue-slot utilisation, active lanes per
+    instruction, L2 hit rate and resident warps per scheduler from the same `ncu --set full` capture of THIS build as
+    measured_traffic (None when the capture on file is of other kernel sources)."""
+    try:
+        rec = json.load(open(os.path.join(ROOT, 'profiles', 'r02_traffic.json')))
+        if rec.get('lib_sha16') != lib_sha16() or kernel_key not in rec['kernels']:
+            return None
+        out = dict(rec['kernels'][kernel_key].get('issue') or {})
+        out['source'] = "ncu --set full capture of this build (%s; summaries profiles/r02_ncu_d_*.txt, profiles/r02_traffic.json)" % rec['kernels'][kernel_key].get('report', '')
+        return out
+    except Exception:
+        return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
@@ -361,6 +376,7 @@ def run_ours(args):
         "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
                      "frac": achieved_tf / peak_tf,
                      "traffic": measured_traffic("c2_forward", c1['n_samples']),
+                     "issue": measured_issue("c2_forward"),
                      "traffic_note": "dram bytes of one launch from the ncu --set full capture of this very build (profiles/r02_traffic.json, "
                                      "keyed by the sha256 of the kernel sources), scaled to this launch's samples; null when no capture of this build is on file",
                      "peak_source": "measured in this run: independent FFMA chains on all SMs (mib_debug_fp32_peak), best of 5" if fp32_peak else
@@ -433,6 +449,7 @@ def grid_roofline(device, peaks):
         sectors = 256 * cnt['n_lookups']
         leg = {"bound": "hbm", "achieved": b / t / 1e9, "peak": hbm, "unit": "GB/s", "frac": b / t / 1e9 / hbm,
                "traffic": measured_traffic("c3_forward_" + variant.replace('llvm_ad_', ''), cnt['n_samples']),
+               "issue": measured_issue("c3_forward_" + variant.replace('llvm_ad_', '')),
                "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback",
                "l2_roof": {"achieved": sectors / t / 1e9, "peak": l2, "unit": "GB/s", "frac": (sectors / t / 1e9 / l2) if l2 else None,
                            "note": "8 taps x 32-byte sectors per look-up (the gathers are L2 hits, ncu lts__t_sector_hit_rate ~90 %) against the L2 "
@@ -557,6 +574,7 @@ def adjoint_bench(device, rank, world, peaks):
            "grad_abs_sum": float(np.abs(g.astype(np.float64)).sum()), "events_this_rank": c,
            "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
                         "traffic": measured_traffic("c4_adjoint", c['n_samples']),
+                        "issue": measured_issue("c4_adjoint"),
                         "note": "32 B per look-up of both passes + 64 B gradient read-modify-write per backward look-up"},
            "note": "one sample = primal replay + backward pass of one lane (both passes timed)"}
     # ---- end to end with host buffers, this rank's share ----

@@ -4,7 +4,8 @@ only reports `roofline.traffic` when the capture on file is of the kernels it is
 
     python profiles/ncu_traffic.py <lib_sha16 | auto> key=report.ncu-rep:n_samples [key=...]
 
-keys used by bench.py: c2_forward, c3_forward_mono, c3_forward_mono_polarized, c4_adjoint."""
+keys used by bench.py: c2_forward, c3_forward_mono, c3_forward_mono_polarized, c4_adjoint.  Also kept per kernel: the issue-slot
+utilisation, active lanes per instruction, L2 hit rate and warps per scheduler of the same capture (bench.py `roofline.issue`)."""
 import csv
 import json
 import os
@@ -23,7 +24,14 @@ def dram_bytes(rep):
     for k in ('dram__bytes_read.sum', 'dram__bytes_write.sum'):
         v, u = d[k]
         total += float(v.replace(',', '')) * {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}[u]
-    return total, d['Kernel Name'][0]
+    extra = {}
+    for k, name in (('smsp__issue_active.avg.pct_of_peak_sustained_active', 'issue_slots_busy_pct'),
+                    ('smsp__thread_inst_executed_per_inst_executed.ratio', 'active_lanes_per_instruction'),
+                    ('lts__t_sector_hit_rate.pct', 'l2_hit_rate_pct'),
+                    ('smsp__warps_active.avg.per_cycle_active', 'warps_per_scheduler')):
+        if k in d:
+            extra[name] = round(float(d[k][0].replace(',', '')), 2)
+    return total, d['Kernel Name'][0], extra
 
 
 def main():
@@ -36,8 +44,8 @@ def main():
     for arg in sys.argv[2:]:
         key, rest = arg.split('=', 1)
         rep, n = rest.rsplit(':', 1)
-        b, name = dram_bytes(rep)
-        out["kernels"][key] = {"dram_bytes": b, "n_samples": int(n), "kernel": name, "report": os.path.basename(rep)}
+        b, name, extra = dram_bytes(rep)
+        out["kernels"][key] = {"dram_bytes": b, "n_samples": int(n), "kernel": name, "report": os.path.basename(rep), "issue": extra}
     json.dump(out, open(os.path.join(HERE, 'r02_traffic.json'), 'w'), indent=1)
     print(json.dumps(out, indent=1))
 
