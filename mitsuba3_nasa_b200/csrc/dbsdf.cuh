@@ -149,7 +149,7 @@ MIB_D void rough_sample(const mib_bsdf &b, V3 wi, float s1, float s2x, float s2y
     if constexpr (POL) m4_zero(W);
     const float eta = b.eta, cos_theta_i = wi.z;
     bool active = cos_theta_i != 0.f;
-    const Microfacet distr(b.distribution, b.alpha_u, b.alpha_v);
+    const Microfacet distr(b.distribution, b.alpha_u, b.alpha_v, b.sample_visible != 0);
     const V3 wi_up = v3(mulsign_ad(wi.x, cos_theta_i), mulsign_ad(wi.y, cos_theta_i), mulsign_ad(wi.z, cos_theta_i));
     const V3 m = distr.sample(wi_up, s2x, s2y, bs.pdf);
     active = active && bs.pdf != 0.f;
@@ -189,7 +189,8 @@ MIB_D void rough_sample(const mib_bsdf &b, V3 wi, float s1, float s2x, float s2y
         if constexpr (POL) m4_scale(W, factor);
         dwh_dwo = div_(sqr_(bs.eta) * wo_m, sqr_(wi_m + bs.eta * wo_m));
     }
-    const float g1 = distr.smith_g1(bs.wo, m);
+    // roughdielectric.cpp:402-408: the visible-normal weight, or (the fork's G = 1 form of) the weight of sampling D cos(theta_m)
+    const float g1 = distr.sample_visible ? distr.smith_g1(bs.wo, m) : div_(wi_m, cos_theta_i * m.z);
     w *= g1;
     if constexpr (POL) m4_scale(W, g1);
     bs.pdf *= fabsf(dwh_dwo);
@@ -446,7 +447,7 @@ MIB_D float rough_pdf(const mib_bsdf &b, V3 wi, V3 wo) {
     const float wi_m = dot(wi, m), wo_m = dot(wo, m);
     active = active && wi_m * wi.z > 0.f && wo_m * wo.z > 0.f;
     const float dwh_dwo = reflect ? rcp_(4.f * wo_m) : div_(eta_s * eta_s * wo_m, sqr_(wi_m + eta_s * wo_m));
-    const Microfacet distr(b.distribution, b.alpha_u, b.alpha_v);
+    const Microfacet distr(b.distribution, b.alpha_u, b.alpha_v, b.sample_visible != 0);
     const V3 wi_up = v3(mulsign_ad(wi.x, cos_theta_i), mulsign_ad(wi.y, cos_theta_i), mulsign_ad(wi.z, cos_theta_i));
     float prob = distr.pdf(wi_up, m);
     const float F = fresnel_(wi_m, eta).x;

@@ -59,7 +59,8 @@ MIB_D float erfinv_(float x) {
 
 struct Microfacet {
     int type; float alpha_u, alpha_v;     // type 0 = Beckmann, 1 = GGX
-    MIB_D Microfacet(int t, float au, float av) : type(t), alpha_u(fmaxf(au, 1e-4f)), alpha_v(fmaxf(av, 1e-4f)) {}
+    bool sample_visible;                  // false: normals drawn from D * cos(theta_m) (microfacet.h:246-293, isotropic roughness)
+    MIB_D Microfacet(int t, float au, float av, bool sv = true) : type(t), alpha_u(fmaxf(au, 1e-4f)), alpha_v(fmaxf(av, 1e-4f)), sample_visible(sv) {}
 
     MIB_D float eval(V3 m) const {
         float alpha_uv = alpha_u * alpha_v, cos_theta = m.z, cos_theta_2 = sqr_(cos_theta), result;
@@ -83,7 +84,10 @@ struct Microfacet {
         return result;
     }
 
-    MIB_D float pdf(V3 wi, V3 m) const { return eval(m) * div_(smith_g1(wi, m) * fabsf(dot(wi, m)), wi.z); }
+    MIB_D float pdf(V3 wi, V3 m) const {
+        if (!sample_visible) return eval(m) * m.z;
+        return eval(m) * div_(smith_g1(wi, m) * fabsf(dot(wi, m)), wi.z);
+    }
 
     MIB_D void sample_visible_11(float cos_theta_i, float sx, float sy, float &slope_x, float &slope_y) const {
         if (type == 0) {
@@ -119,6 +123,26 @@ struct Microfacet {
 
     // visible-normal sampling (microfacet.h:301-326); returns the normal, pdf_out as the reference computes it
     MIB_D V3 sample(V3 wi, float sx, float sy, float &pdf_out) const {
+        if (!sample_visible) {
+            float sin_phi, cos_phi;
+            sincos_((2.f * kPi) * sy, sin_phi, cos_phi);
+            const float alpha_2 = alpha_u * alpha_u;
+            float cos_theta, cos_theta_2;
+            if (type == 0) {
+                cos_theta = rsqrt_(fnma_(alpha_2, log_(1.f - sx), 1.f));
+                cos_theta_2 = sqr_(cos_theta);
+                const float cos_theta_3 = fmaxf(cos_theta_2 * cos_theta, 1e-20f);
+                pdf_out = div_(1.f - sx, kPi * alpha_u * alpha_v * cos_theta_3);
+            } else {
+                const float tan_theta_m_2 = div_(alpha_2 * sx, 1.f - sx);
+                cos_theta = rsqrt_(1.f + tan_theta_m_2);
+                cos_theta_2 = sqr_(cos_theta);
+                const float temp = 1.f + div_(tan_theta_m_2, alpha_2), cos_theta_3 = fmaxf(cos_theta_2 * cos_theta, 1e-20f);
+                pdf_out = rcp_(kPi * alpha_u * alpha_v * cos_theta_3 * sqr_(temp));
+            }
+            const float sin_theta = sqrt_(1.f - cos_theta_2);
+            return v3(cos_phi * sin_theta, sin_phi * sin_theta, cos_theta);
+        }
         V3 wi_p = normalize(v3(alpha_u * wi.x, alpha_v * wi.y, wi.z));
         float sin_theta_2 = fma_(wi_p.x, wi_p.x, sqr_(wi_p.y)), inv_sin_theta = rsqrt_(sin_theta_2);
         float cos_phi = wi_p.x * inv_sin_theta, sin_phi = wi_p.y * inv_sin_theta;

@@ -536,8 +536,6 @@ class Scene:
                     raise PluginError("Specified an invalid distribution \"%s\", must be \"beckmann\" or \"ggx\"!" % distr)
                 out.distribution = A.MICROFACET_BECKMANN if distr == 'beckmann' else A.MICROFACET_GGX
                 out.sample_visible = int(bool(pr.get('sample_visible', True)))
-                if not out.sample_visible:
-                    raise PluginError("roughdielectric: sample_visible = false is not implemented")
                 if pr.has('alpha_sq'):
                     if pr.has('alpha'):
                         raise PluginError("Microfacet model: please specify either 'alpha' or 'alpha_sq'.")
@@ -550,6 +548,8 @@ class Scene:
                     au, av = float(pr.get('alpha_u')), float(pr.get('alpha_v'))
                 else:
                     au = av = float(pr.get('alpha', 0.1))
+                if not out.sample_visible and au != av:
+                    raise PluginError("roughdielectric: sample_visible = false with an anisotropic roughness is not implemented")
                 out.alpha_u, out.alpha_v = au, av
         elif b.type in ('plastic', 'roughplastic'):
             # src/bsdfs/plastic.cpp:151-200, src/bsdfs/roughplastic.cpp:169-253

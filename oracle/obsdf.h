@@ -47,7 +47,7 @@ template <int SPEC> struct BSDF {
         USpec r; for (int c = 0; c < Tr::NC; ++c) r.v[c] = src[Tr::NC == 3 ? c : 0]; return r;
     }
     static Spec pick(float w, const Mueller &W) { if constexpr (Tr::POL) return W; else { (void) W; return Spec(w); } }
-    static RoughDielectric rough(const mib_bsdf &b) { return RoughDielectric{ b.distribution, b.alpha_u, b.alpha_v, b.eta }; }
+    static RoughDielectric rough(const mib_bsdf &b) { return RoughDielectric{ b.distribution, b.alpha_u, b.alpha_v, b.eta, b.sample_visible != 0 }; }
 
     static USpec uspec3(const float *src) { USpec r; for (int c = 0; c < Tr::NC; ++c) r.v[c] = src[Tr::NC == 3 ? c : 0]; return r; }
     // roughplastic.cpp:392-402

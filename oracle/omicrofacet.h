@@ -4,7 +4,7 @@
 // include/mitsuba/render/microfacet.h:185-440 (eval, pdf, smith_g1, G, visible-normal sampling for Beckmann and GGX),
 // with the Dr.Jit polynomials it needs: exp2 (drjit/math.h:756-820), erf (:1473-1527), erfinv (:1531-1552).
 // Pinned bit for bit against the reference headers in tests/test_oracle_vs_ref.py (blocks "microfacet_*", "erf*").
-// Not restated: the non-visible sampling branch (microfacet.h:246-300; `sample_visible` defaults to true).
+// sample_visible = false (microfacet.h:246-300, :219-226): the normals are drawn from D * cos(theta_m), isotropic roughness only.
 #pragma once
 #include "omath.h"
 #include "oplugins.h"   // square_to_uniform_disk_concentric (warp.h:54-90)
@@ -57,9 +57,9 @@ static inline Vec3 md_normalize(Vec3 v) { return v * md_rsqrt(squared_norm(v)); 
 static inline float md_sqnorm2(float x, float y) { return g_fresnel_scalar_forms ? x * x + y * y : fmadd(y, y, sqr(x)); }   // Point2f: left-to-right in the scalar headers (measured)
 
 struct Microfacet {
-    int type; float alpha_u, alpha_v;
+    int type; float alpha_u, alpha_v; bool sample_visible;
     // microfacet.h:76-99 + configure() :425-428
-    Microfacet(int t, float au, float av) : type(t), alpha_u(maximum(au, 1e-4f)), alpha_v(maximum(av, 1e-4f)) {}
+    Microfacet(int t, float au, float av, bool sv = true) : type(t), alpha_u(maximum(au, 1e-4f)), alpha_v(maximum(av, 1e-4f)), sample_visible(sv) {}
 
     // microfacet.h:185-207
     float eval(Vec3 m) const {
@@ -86,8 +86,11 @@ struct Microfacet {
     }
     float G(Vec3 wi, Vec3 wo, Vec3 m) const { return smith_g1(wi, m) * smith_g1(wo, m); }
 
-    // microfacet.h:219-226 (sample_visible = true)
-    float pdf(Vec3 wi, Vec3 m) const { return eval(m) * (smith_g1(wi, m) * std::fabs(md_dot(wi, m)) / wi.z); }
+    // microfacet.h:219-226
+    float pdf(Vec3 wi, Vec3 m) const {
+        if (!sample_visible) return eval(m) * m.z;
+        return eval(m) * (smith_g1(wi, m) * std::fabs(md_dot(wi, m)) / wi.z);
+    }
 
     // microfacet.h:368-422
     void sample_visible_11(float cos_theta_i, float sx, float sy, float *slope_x, float *slope_y) const {
@@ -124,6 +127,28 @@ struct Microfacet {
 
     // microfacet.h:244-326, visible-normal branch.  Returns the microfacet normal; *pdf_out as the reference computes it.
     Vec3 sample(Vec3 wi, float sx, float sy, float *pdf_out) const {
+        if (!sample_visible) {
+            // :246-293 (isotropic branch; anisotropic roughness with sample_visible = false is refused by the host)
+            float sin_phi, cos_phi;
+            sincos((2.f * Pi) * sy, &sin_phi, &cos_phi);
+            const float alpha_2 = alpha_u * alpha_u;
+            float cos_theta, cos_theta_2, pdf;
+            if (type == MICROFACET_BECKMANN) {
+                cos_theta = rsqrt(fnmadd(alpha_2, log_(1.f - sx), 1.f));
+                cos_theta_2 = sqr(cos_theta);
+                float cos_theta_3 = maximum(cos_theta_2 * cos_theta, 1e-20f);
+                pdf = (1.f - sx) / (Pi * alpha_u * alpha_v * cos_theta_3);
+            } else {
+                float tan_theta_m_2 = alpha_2 * sx / (1.f - sx);
+                cos_theta = rsqrt(1.f + tan_theta_m_2);
+                cos_theta_2 = sqr(cos_theta);
+                float temp = 1.f + tan_theta_m_2 / alpha_2, cos_theta_3 = maximum(cos_theta_2 * cos_theta, 1e-20f);
+                pdf = rcp(Pi * alpha_u * alpha_v * cos_theta_3 * sqr(temp));
+            }
+            float sin_theta = std::sqrt(1.f - cos_theta_2);
+            *pdf_out = pdf;
+            return Vec3(cos_phi * sin_theta, sin_phi * sin_theta, cos_theta);
+        }
         Vec3 wi_p = md_normalize(Vec3(alpha_u * wi.x, alpha_v * wi.y, wi.z));
         // Frame::sincos_phi, include/mitsuba/core/frame.h:111-122
         float sin_theta_2 = fmadd(wi_p.x, wi_p.x, sqr(wi_p.y)), inv_sin_theta = md_rsqrt(sin_theta_2);

@@ -1,5 +1,5 @@
 // oroughdielectric.h -- TEST INFRASTRUCTURE (CPU oracle).  RoughDielectric of the fork, src/bsdfs/roughdielectric.cpp:
-// sample :248-411, eval :413-519, pdf :521-603, TransportMode::Radiance, sample_visible = true, specular_reflectance /
+// sample :248-411, eval :413-519, pdf :521-603, TransportMode::Radiance, both sample_visible settings, specular_reflectance /
 // specular_transmittance = 1.  JIT forms throughout (fma-chain dot, rsqrt = sqrt(1/x)).  Built on the pinned blocks of
 // ofresnel.h and omicrofacet.h.  Reference quirks kept on purpose:
 //   * eval() uses G = 1 (:457), while sample() weights with smith_g1(wo, m) (:399-400): eval / pdf is therefore
@@ -15,7 +15,7 @@ namespace orc {
 enum : uint32_t { BSDF_GlossyReflection = 0x8, BSDF_GlossyTransmission = 0x10 };
 
 struct RoughDielectric {
-    int type; float alpha_u, alpha_v, eta;
+    int type; float alpha_u, alpha_v, eta; bool sample_visible = true;
 
     static Mueller zero_nan(Mueller M) { zero_nans(M); return M; }
 
@@ -31,7 +31,7 @@ struct RoughDielectric {
         Sample bs;
         float cos_theta_i = wi.z;
         bool active = cos_theta_i != 0.f;
-        Microfacet distr(type, alpha_u, alpha_v);
+        Microfacet distr(type, alpha_u, alpha_v, sample_visible);
         Vec3 wi_up(mulsign_ad(wi.x, cos_theta_i), mulsign_ad(wi.y, cos_theta_i), mulsign_ad(wi.z, cos_theta_i));
         Vec3 m = distr.sample(wi_up, s2x, s2y, &bs.pdf);
         active = active && bs.pdf != 0.f;
@@ -68,7 +68,8 @@ struct RoughDielectric {
             w *= factor; W = W * factor;
             dwh_dwo = (sqr(bs.eta) * dot(bs.wo, m)) / sqr(dot(wi, m) + bs.eta * dot(bs.wo, m));
         }
-        float g1 = distr.smith_g1(bs.wo, m);
+        // :402-408: the visible-normal weight, or (the fork's G = 1 form of) the weight of sampling D cos(theta_m)
+        float g1 = sample_visible ? distr.smith_g1(bs.wo, m) : dot(wi, m) / (cos_theta_i * m.z);
         w *= g1; W = W * g1;
         bs.pdf *= std::fabs(dwh_dwo);
         if (!active) { w = 0.f; W = Mueller(); }
@@ -93,7 +94,7 @@ struct RoughDielectric {
         float eta_s = cos_theta_i > 0.f ? eta : inv_eta_c, inv_eta_s = cos_theta_i > 0.f ? inv_eta_c : eta;
         Vec3 m = half_vector(wi, wo, reflect, eta_s);
         active = active && dot(wi, m) * wi.z > 0.f && dot(wo, m) * wo.z > 0.f;
-        Microfacet distr(type, alpha_u, alpha_v);
+        Microfacet distr(type, alpha_u, alpha_v, sample_visible);
         float D = distr.eval(m), F = fresnel(dot(wi, m), eta).r, G = 1.f;
         bool eval_r = has_reflection && reflect && active, eval_t = has_transmission && !reflect && active;
         if (!eval_r && !eval_t) return;
@@ -123,7 +124,7 @@ struct RoughDielectric {
         Vec3 m = half_vector(wi, wo, reflect, eta_s);
         active = active && dot(wi, m) * wi.z > 0.f && dot(wo, m) * wo.z > 0.f;
         float dwh_dwo = reflect ? rcp(4.f * dot(wo, m)) : (eta_s * eta_s * dot(wo, m)) / sqr(dot(wi, m) + eta_s * dot(wo, m));
-        Microfacet distr(type, alpha_u, alpha_v);
+        Microfacet distr(type, alpha_u, alpha_v, sample_visible);
         Vec3 wi_up(mulsign_ad(wi.x, cos_theta_i), mulsign_ad(wi.y, cos_theta_i), mulsign_ad(wi.z, cos_theta_i));
         float prob = distr.pdf(wi_up, m);
         if (has_transmission && has_reflection) {

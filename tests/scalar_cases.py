@@ -220,6 +220,28 @@ def cases():
     c['plastic_ggx_tint_nonlinear_rgb'] = dict(variant='scalar_rgb', scene=plastic_scene(distribution='ggx', alpha=0.35, tint=True, nonlinear=True), spp=16, seed=1, kind='samples')
     c['plastic_mono_mis'] = dict(variant='scalar_mono', scene=plastic_scene(integrator='volpathmis', alpha=0.25), spp=16, seed=2, kind='samples')
     c['plastic_pol'] = dict(variant='scalar_mono_polarized', scene=plastic_scene(alpha=0.2), spp=16, seed=3, kind='samples')
+    # the four active rough-dielectric configurations of the reference's own adjoint test (test_ad_volpathaos.py:235-338: a
+    # directly visible rough dielectric plane, `sample_visible = false`, lit by an area light or by the sun), primal side:
+    # volpathaos in the polarized variant, radiancemeter, max_depth 3
+    def ad_config(directional, alpha=0.1, distribution='beckmann', sample_visible=False):
+        d = {'type': 'scene',
+             'integrator': {'type': 'volpathaos', 'max_depth': 3},
+             'plane': {'type': 'rectangle',
+                       'bsdf': {'type': 'roughdielectric', 'int_ior': 1.34, 'ext_ior': 1.0, 'distribution': distribution,
+                                'alpha': alpha, 'sample_visible': sample_visible}},
+             'sensor': {'type': 'radiancemeter', 'to_world': T.look_at(origin=[0, 0, 4], target=[0, 0, 0], up=[0, 1, 0]),
+                        'film': {'type': 'hdrfilm', 'rfilter': {'type': 'box'}, 'width': 1, 'height': 1, 'sample_border': False,
+                                 'pixel_format': 'luminance', 'component_format': 'float32'},
+                        'sampler': {'type': 'independent', 'sample_count': 512}}}
+        if directional:
+            d['emitter'] = {'type': 'directional', 'direction': [-0.5, 0, -0.866], 'irradiance': 1.0}
+        else:
+            d['light'] = {'type': 'rectangle', 'to_world': T.translate([1.25, 0.0, 1.0]) @ T.rotate([0, 1, 0], -90),
+                          'emitter': {'type': 'area', 'radiance': {'type': 'rgb', 'value': [3.0, 3.0, 3.0]}}}
+        return d
+    c['ad_rough_dielectric_area'] = dict(variant='scalar_mono_polarized', scene=ad_config(False), spp=512, seed=0, kind='samples')
+    c['ad_rough_dielectric_directional'] = dict(variant='scalar_mono_polarized', scene=ad_config(True), spp=512, seed=1, kind='samples')
+    c['ad_rough_dielectric_ggx_area_mono'] = dict(variant='scalar_mono', scene=ad_config(False, alpha=0.3, distribution='ggx'), spp=512, seed=2, kind='samples')
     # radiancemeter looking through the cube
     d = scenes.c1_homogeneous_cube(res=1, spp=64, max_depth=16)
     d['sensor'] = {'type': 'radiancemeter', 'origin': [0.2, 0.1, 4.0], 'direction': [-0.05, 0.0, -1.0],
