@@ -122,7 +122,7 @@ typedef struct mib_bsdf {
     float   alpha_u;         /* roughdielectric roughness (src/bsdfs/roughdielectric.cpp:196-218) */
     float   alpha_v;
     int32_t distribution;    /* MIB_MICROFACET_* (roughdielectric.cpp:182-193) */
-    int32_t sample_visible;  /* roughdielectric.cpp:195 (only 1, the plugin's default, is implemented) */
+    int32_t sample_visible;  /* roughdielectric.cpp:195; 0: normals drawn from D cos(theta_m) (microfacet.h:246-293), isotropic roughness only */
     /* diffuse reflectance as a checkerboard texture (src/textures/checkerboard.cpp:66-84; SURVEY 8f rank 3: the background
        plane of the fork's participating_media test scenes): color0 where the two uv cells agree, color1 elsewhere */
     int32_t texture;         /* MIB_TEXTURE_*; UNIFORM: `reflectance` */
@@ -354,7 +354,7 @@ int  mib_debug_math(int op /*0 sincos,1 exp,2 log,3 cbrt,4 asin*/, const float *
    (zero under total internal reflection). */
 int  mib_debug_fresnel(int op, const float *in_host, float eta, float *out_host, size_t n);
 /* Microfacet distribution of the rough ocean interface on the device (csrc/dmicrofacet.cuh; groundwork for `roughdielectric`,
-   SURVEY 8f rank 2): MicrofacetDistribution eval / smith_g1 / pdf / visible-normal sample (include/mitsuba/render/microfacet.h:
+   SURVEY 8f rank 2): MicrofacetDistribution eval / smith_g1 / pdf / sample, visible normals (include/mitsuba/render/microfacet.h:
    185-440) and Dr.Jit's erf / erfinv / exp2 (ext/drjit/include/drjit/math.h:756-820,1473-1552).  type 0 = beckmann, 1 = ggx.
    op 0: in = (wi, m) [n][6] -> (eval, smith_g1, pdf) [n][3];  1: in = (wi, sample2) [n][5] -> (m, pdf) [n][4];
    2 / 3 / 4: in = x [n] -> erf(x) / erfinv(x) / exp2(x) [n] (type and alphas ignored). */

@@ -257,6 +257,10 @@ class SceneParameters:
         if kind == 'emitter_radiance':
             e = acc['emitter']
             return np.array(e.radiance[:]) if f.spectrum == A.SPEC_RGB else float(e.radiance[0])
+        if kind == 'bsdf_eta':
+            return float(acc['bsdf'].eta)
+        if kind == 'bsdf_alpha':
+            return float(acc['bsdf'].alpha_u)
         raise KeyError(key)
 
     def __setitem__(self, key, value):
@@ -302,6 +306,12 @@ class SceneParameters:
             if kind == 'volume_const':
                 # (an attached RGB constant keeps three channels so that its gradient comes back per channel)
                 acc['vol'].channels = 3 if (f.spectrum == A.SPEC_RGB and (len(set(col.tolist())) > 1 or key in self._torch)) else 1
+        elif kind == 'bsdf_eta':
+            eta = np.float32(value)
+            acc['bsdf'].eta = float(eta)
+            acc['bsdf'].inv_eta = float(np.float32(1.0) / eta)                   # roughdielectric.cpp:245
+        elif kind == 'bsdf_alpha':
+            acc['bsdf'].alpha_u = acc['bsdf'].alpha_v = float(np.float32(value))
         elif kind == 'phase_g':
             acc['phase'].g = float(value)
         elif kind == 'medium_scale':

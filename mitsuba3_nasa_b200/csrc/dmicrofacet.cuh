@@ -121,7 +121,7 @@ struct Microfacet {
         }
     }
 
-    // visible-normal sampling (microfacet.h:301-326); returns the normal, pdf_out as the reference computes it
+    // microfacet.h:244-326 (both sample_visible settings); returns the normal, pdf_out as the reference computes it
     MIB_D V3 sample(V3 wi, float sx, float sy, float &pdf_out) const {
         if (!sample_visible) {
             float sin_phi, cos_phi;

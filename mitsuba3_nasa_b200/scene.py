@@ -551,6 +551,12 @@ class Scene:
                 if not out.sample_visible and au != av:
                     raise PluginError("roughdielectric: sample_visible = false with an anisotropic roughness is not implemented")
                 out.alpha_u, out.alpha_v = au, av
+                # roughdielectric.cpp:224-236 traverse(): `eta`, and `alpha` (a uniform texture: key `alpha.value`) when isotropic.  Not
+                # differentiable here (the adjoint of the interface is not built); params.update() re-commits the scene, which is what
+                # the finite-difference side of the reference's adjoint test does (test_ad_volpathaos.py:504-529)
+                self.params[key + '.eta'] = {'kind': 'bsdf_eta', 'bsdf': out}
+                if au == av:
+                    self.params[key + '.alpha.value'] = {'kind': 'bsdf_alpha', 'bsdf': out}
         elif b.type in ('plastic', 'roughplastic'):
             # src/bsdfs/plastic.cpp:151-200, src/bsdfs/roughplastic.cpp:169-253
             int_ior = _lookup_ior(pr.get('int_ior', 'polypropylene'))

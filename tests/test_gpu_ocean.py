@@ -128,3 +128,27 @@ def test_primal_of_the_reference_adjoint_test_configurations(name):
     bad = (np.abs(g - o) > 1e-4 * np.maximum(np.abs(o).max(axis=1, keepdims=True), 1e-9)).any(axis=1)
     print("%s: bit-equal %s, over tolerance %d, non-zero lanes %d" % (name, np.array_equal(g, o), bad.sum(), (o[:, 0] != 0).sum()))
     assert (o[:, 0] != 0).any() and bad.mean() <= 2e-3
+
+
+def test_eta_and_alpha_are_scene_parameters():
+    """mi.traverse exposes the keys the reference's adjoint test perturbs (test_ad_volpathaos.py:238,264: 'plane.bsdf.eta',
+    'plane.bsdf.alpha.value'; roughdielectric.cpp:224-236); params.update() re-commits the scene, so the finite-difference side of
+    that test runs on this backend.  They are not differentiable here (the adjoint of the interface is not built)."""
+    import copy
+    import mitsuba3_nasa_b200 as mi
+    mi.set_variant('llvm_ad_mono_polarized')
+    d = copy.deepcopy(scalar_cases.cases()['ad_rough_dielectric_directional']['scene'])
+    scene = mi.load_dict(d)
+    p = mi.traverse(scene)
+    assert {'plane.bsdf.eta', 'plane.bsdf.alpha.value'} <= set(p.keys())
+    assert abs(p['plane.bsdf.eta'] - 1.34) < 1e-6 and abs(p['plane.bsdf.alpha.value'] - 0.1) < 1e-7
+    before = np.asarray(mi.render_1(scene, seed=1, spp=4096)).copy()
+    p['plane.bsdf.eta'] = 1.5
+    p['plane.bsdf.alpha.value'] = 0.2
+    p.update()
+    after = np.asarray(mi.render_1(scene, seed=1, spp=4096))
+    d['plane']['bsdf'].update(int_ior=1.5, alpha=0.2)
+    fresh = np.asarray(mi.render_1(mi.load_dict(d), seed=1, spp=4096))
+    assert np.array_equal(after, fresh) and not np.array_equal(after, before)
+    with pytest.raises(RuntimeError, match="not differentiable"):
+        p.enable_grad('plane.bsdf.eta')

@@ -40,3 +40,24 @@ def test_lanes_equal_the_oracle(stem):
     bad = (np.abs(g - o) > 1e-4 * np.maximum(np.abs(o).max(axis=1, keepdims=True), 1e-6)).any(axis=1)
     print("%s: lanes %d, bit-equal %s, over tolerance %d" % (stem, n, np.array_equal(g, o), bad.sum()))
     assert bad.mean() <= 2e-3
+
+
+def test_the_reference_test_body_runs_as_written(tmp_path):
+    """test_renders.py:205-213 with `mi` = this package: load_file(scene, spp=, integrator=), integrator().render(scene, seed=0,
+    spp=, develop=True), sensors()[0].film().bitmap(raw=False) -- then its Z-test; and film().write() gives an EXR that reads back."""
+    from mitsuba3_nasa_b200 import exr
+    mi.set_variant('llvm_ad_rgb')
+    stem = 'test_homo_null_envmap'
+    spp = int(2e6) // (48 * 48)
+    scene = mi.load_file(os.path.join(PM, stem + '_volpath.xml'), spp=spp, integrator='volpath')
+    scene.integrator().render(scene, seed=0, spp=spp, develop=True)
+    film = scene.sensors()[0].film()
+    img = np.asarray(film.bitmap(raw=False))
+    assert tuple(film.size()) == (48, 48) and img.shape[:2] == (48, 48)
+    ok, pmin, alpha = z_test_against_reference(img, spp, stem)
+    assert ok, (pmin, alpha)
+    out = os.path.join(str(tmp_path), "render.exr")
+    film.write(out)
+    back, names = exr.read_exr(out)
+    rgb = back[..., [names.index(c) for c in 'RGB']]
+    assert np.allclose(rgb, img[..., :3], rtol=1e-6, atol=1e-7)
