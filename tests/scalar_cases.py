@@ -107,6 +107,17 @@ def xml_cases():
     }
 
 
+def fd_scene(albedo, integrator='volpathaos', spp=64):
+    d = scenes.c1_homogeneous_cube(res=1, spp=spp, max_depth=12)
+    d['integrator'] = {'type': integrator, 'max_depth': 12, 'rr_depth': 1000}
+    d['medium1']['sigma_t'] = 0.6
+    d['medium1']['albedo'] = albedo
+    d['medium1']['phase'] = {'type': 'rayleigh'}
+    d['emitter'] = {'type': 'directional', 'direction': [0.3, -0.2, -1.0], 'irradiance': 1.0}
+    d['sensor']['film']['pixel_format'] = 'luminance'
+    return d
+
+
 def cases():
     c = {}
     # C1 (BASELINE configs[0]) at 32 x 32 x 16: homogeneous HG cube, volpath, rgb
@@ -242,6 +253,13 @@ def cases():
     c['ad_rough_dielectric_area'] = dict(variant='scalar_mono_polarized', scene=ad_config(False), spp=512, seed=0, kind='samples')
     c['ad_rough_dielectric_directional'] = dict(variant='scalar_mono_polarized', scene=ad_config(True), spp=512, seed=1, kind='samples')
     c['ad_rough_dielectric_ggx_area_mono'] = dict(variant='scalar_mono', scene=ad_config(False, alpha=0.3, distribution='ggx'), spp=512, seed=2, kind='samples')
+    # finite differences of the REFERENCE for the adjoint tests (the methodology of test_ad_volpathaos.py:504-529, with the medium
+    # configuration that file defines but leaves switched off, :340-437): render_1 of the unmodified volpathaos at albedo 0.8 -/+
+    # 0.01, one random stream (common random numbers), sun-lit homogeneous Rayleigh cube, polarized.  (volpath itself renders a
+    # directional light black in this fork: its shadow ray is spawned toward a point at infinity, volpath.cpp:352 with
+    # directional.cpp's ds.dist = inf -- reproduced by the oracle, and the reason the fork has volpathaos.)
+    for tag, albedo in (('minus', 0.79), ('plus', 0.81)):
+        c['fd_ref_albedo_' + tag] = dict(variant='scalar_mono_polarized', scene=fd_scene(albedo), spp=200000, seed=1, kind='render1')
     # radiancemeter looking through the cube
     d = scenes.c1_homogeneous_cube(res=1, spp=64, max_depth=16)
     d['sensor'] = {'type': 'radiancemeter', 'origin': [0.2, 0.1, 4.0], 'direction': [-0.05, 0.0, -1.0],

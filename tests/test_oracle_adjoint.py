@@ -146,3 +146,36 @@ def test_three_channel_albedo_grid_in_a_mono_variant():
     vals = [OracleScene(mk(alb + s * h * v, spp)).render_1(3, spp, nthreads=8)[0] for s in (1, -1)]
     fd = (vals[0] - vals[1]) / (2 * h)
     assert abs(float((g * v).sum()) / fd - 1) < 2e-3, (float((g * v).sum()), fd)
+
+
+def test_prb_volpathaos_albedo_gradient_against_finite_differences_of_the_reference():
+    """The reference's own methodology (test_ad_volpathaos.py:504-529, :599-618) with the reference's own numbers: central differences of
+    render_1 of the UNMODIFIED volpathaos (scalar_mono_polarized build, 2e5 samples, one random stream at albedo 0.79 and 0.81;
+    tests/golden/scalar_ref.npz fd_ref_albedo_*, generated by tests/golden/make_scalar_golden.py) against the adjoint oracle's gradient
+    of Stokes I w.r.t. the albedo.  prb_volpathaos' literal gradient is albedo x the true derivative (previous tests),
+    so the quotient must be 0.8; with the test-only unbiased switch it is 1.  Tolerance: the reference's 5 %."""
+    import scalar_cases
+    gold = np.load(os.path.join(ROOT, "tests", "golden", "scalar_ref.npz"))
+    lo, hi = (gold['fd_ref_albedo_' + t].reshape(4, 4)[:, 0].astype(np.float64) for t in ('minus', 'plus'))
+    fd = (hi - lo) / 0.02
+    spp = 1 << 17
+    o = OracleScene(S.load_dict(scalar_cases.fd_scene(0.8, integrator='prb_volpathaos', spp=64), 'llvm_ad_mono_polarized'))
+    o.render_1_backward(3, spp, [1.0, 0, 0, 0], nthreads=8)
+    g = o.grad_get_scalar(0)[0]
+    print("adjoint %.6g, reference FD %.6g, quotient %.4f" % (g, fd[0], g / fd[0]))
+    assert abs(g / fd[0] - 0.8) < 0.05 * 0.8
+    code = r'''
+import sys
+sys.path.insert(0, %r); sys.path.insert(0, %r)
+import scalar_cases
+from mitsuba3_nasa_b200 import scene as S
+from orc import OracleScene
+o = OracleScene(S.load_dict(scalar_cases.fd_scene(0.8, integrator='prb_volpathaos', spp=64), 'llvm_ad_mono_polarized'))
+o.render_1_backward(3, 1 << 17, [1.0, 0, 0, 0], nthreads=8)
+print("GRAD", o.grad_get_scalar(0)[0])
+''' % (ROOT, os.path.join(ROOT, "tests"))
+    out = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, ORC_PRB_AOS_UNBIASED="1"), capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr
+    g1 = float(out.stdout.split("GRAD")[1])
+    print("unbiased switch: adjoint %.6g, quotient %.4f" % (g1, g1 / fd[0]))
+    assert abs(g1 / fd[0] - 1.0) < 0.05
