@@ -204,3 +204,21 @@ def test_render_backward_through_reconstruction_filter(rfilter, spp):
     g, o = dev.grad_get_scalar(0), orc.grad_get_scalar(0)
     print("scalar grads gpu", g, "oracle", o)
     assert np.allclose(g, o, rtol=GRAD_TOL, atol=GRAD_TOL * np.abs(o).max())
+
+
+def test_kernel_gradient_against_finite_differences_of_the_reference():
+    """The CUDA adjoint kernel against the reference's own finite differences (render_1 of the unmodified volpathaos at albedo
+    0.79 / 0.81; tests/golden/scalar_ref.npz fd_ref_albedo_*, tests/test_oracle_adjoint.py): prb_volpathaos' literal gradient of
+    Stokes I w.r.t. the albedo is 0.8 x the true derivative, 4e6 lanes, within the reference's 5 %."""
+    import os
+    import scalar_cases
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "scalar_ref.npz"))
+    lo, hi = (gold['fd_ref_albedo_' + t].reshape(4, 4)[:, 0].astype(np.float64) for t in ('minus', 'plus'))
+    fd = (hi - lo) / 0.02
+    sc = S.load_dict(scalar_cases.fd_scene(0.8, integrator='prb_volpathaos', spp=64), 'llvm_ad_mono_polarized')
+    dev = _lib.DeviceScene(sc, 0)
+    dev.grad_zero()
+    dev.render_1_backward(3, 1 << 22, [1.0, 0, 0, 0])
+    g = dev.grad_get_scalar(0)[0]
+    print("kernel gradient %.6g, reference FD %.6g, quotient %.4f" % (g, fd[0], g / fd[0]))
+    assert abs(g / fd[0] - 0.8) < 0.05 * 0.8
