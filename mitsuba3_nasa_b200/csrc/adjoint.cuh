@@ -22,6 +22,7 @@ struct AdjParams {
     const float *grad_image;   // [H*W*Cd] image gradient (render_backward) or nullptr
     float grad1[4];            // d loss / d (I,Q,U,V)  (render_1_backward)
     int render_1;
+    int primal_only;           // pool kernel: stop after the primal pass and accumulate L as the forward kernels do (LaunchParams::mode)
 };
 
 // Per-thread gradient sink.  Grid gradients go straight to global memory; scalar

@@ -41,7 +41,8 @@ template <int SPEC> __host__ __device__ constexpr size_t apool_smem_bytes() {
     return pool_state_offset(APoolL<SPEC>::P) + (size_t) APoolL<SPEC>::F_COUNT * APoolL<SPEC>::P * sizeof(uint32_t) + kPoolDebugBytes;
 }
 
-template <int SPEC, int V>
+// PRIMAL: the primal-only instantiation (AdjParams::primal_only) -- its own kernel, so that the backward kernel carries none of its code
+template <int SPEC, int V, bool PRIMAL>
 __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_constant__ LaunchParams lp, const __grid_constant__ AdjParams ap) {
     using L = APoolL<SPEC>;
     constexpr int NR = ST<SPEC>::NR, NC = ST<SPEC>::NC, NT = ST<SPEC>::NT, Cd = SPEC == MIB_SPEC_MONO ? 1 : (SPEC == MIB_SPEC_RGB ? 3 : 4);
@@ -114,6 +115,62 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
                 j = pm.u(L::F_LANE, slot);
                 replay = j != kNoLane && !(pm.u(L::F_FLAGS, slot) & FL_BACKWARD);
             }
+            if constexpr (PRIMAL) {
+                // primal rendering with the prb integrators (mi.render / render_1 before backward()): a finished primal pass is a
+                // finished sample -- L goes to the film / the render_1 sums / the per-sample dump like in the forward kernels
+                // (kernels.cuh finish), and the slot takes the next lane
+                constexpr int C = RawChannels<SPEC>::C;
+                float aov[C];
+#pragma unroll
+                for (int c = 0; c < C; ++c) aov[c] = 0.f;
+                bool inside = false;
+                if (replay) {
+                    const uint64_t lane = stripe_map(lp, lp.lane_begin + q.lane_of(j));
+                    Pcg32 rng;
+                    rng.seed_lane(lp.seed_value, (uint32_t) lane);
+                    const uint32_t idx = (uint32_t) (lane / lp.spp);
+                    const uint32_t py = idx / (uint32_t) sn.crop_width, px = idx - (uint32_t) sn.crop_width * py;
+                    const float sx = (float) ((int) px + sn.crop_offset_x) + rng.next(), sy = (float) ((int) py + sn.crop_offset_y) + rng.next();
+                    float R[NR];
+#pragma unroll
+                    for (int r = 0; r < NR; ++r) R[r] = pm.f(L::F_L + r, slot);
+                    if constexpr (SPEC == MIB_SPEC_RGB) { aov[0] = R[0]; aov[1] = R[1]; aov[2] = R[2]; aov[3] = 1.f; }
+                    else if constexpr (SPEC == MIB_SPEC_MONO) { aov[0] = R[0]; aov[1] = 1.f; }
+                    else {
+                        const float ax = fma_(sx, scale_x, offset_x), ay = fma_(sy, scale_y, offset_y);
+                        float apx = .5f, apy = .5f;
+                        if (sn.needs_aperture_sample) { apx = rng.next(); apy = rng.next(); }
+                        const Ray ray0 = sensor_ray(ax, ay, apx, apy);
+                        to_sensor_stokes(ray0, R);
+                        aov[0] = R[0]; aov[1] = R[1]; aov[2] = R[2]; aov[3] = R[3];
+                    }
+                    const int ix = (int) floorf(sx) - sn.crop_offset_x, iy = (int) floorf(sy) - sn.crop_offset_y;
+                    inside = (uint32_t) ix < (uint32_t) sn.crop_width && (uint32_t) iy < (uint32_t) sn.crop_height;
+                    if (lp.mode == 2) {
+#pragma unroll
+                        for (int c = 0; c < C; ++c) lp.per_sample[(lane - lp.lane_begin) * C + c] = aov[c];
+                    } else if (lp.mode == 0 && (MIB_FT(FT_FILTER) && sn.rfilter != MIB_RFILTER_BOX)) {
+                        filter_footprint(lp.spp, sx, sy, [&](size_t pixel, float w) {
+#pragma unroll
+                            for (int c = 0; c < C; ++c) atomicAdd(lp.film + pixel * C + c, aov[c] * w);
+                        });
+                    } else if (lp.mode == 0 && inside) {
+                        const size_t pixel = (size_t) iy * sn.crop_width + ix;
+#pragma unroll
+                        for (int c = 0; c < C; ++c) atomicAdd(lp.film + pixel * C + c, aov[c]);
+                    }
+                }
+                if (lp.mode == 1) {
+                    // render_1: one double atomic per batch and channel (the batch is summed over the warp first)
+#pragma unroll
+                    for (int c = 0; c < C; ++c) {
+                        double v = (replay && inside) ? (double) aov[c] : 0.0;
+                        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+                        if (lane_id == 0 && v != 0.0) atomicAdd(lp.sums + c, v);
+                    }
+                }
+                replay = false;
+            }
             const bool need = has && !replay;
             const uint32_t jn = q.take_lanes(need);
             bool fresh = false;
@@ -140,7 +197,9 @@ __global__ void __launch_bounds__(MIB_POOL_NT, 1) k_adjoint_pool(const __grid_co
                 for (int r = 0; r < NR; ++r) Lin[r] = 0.f;
                 if (fresh) {
                     n_samples++;
-                    if (ap.render_1) {
+                    if (PRIMAL) {
+                        // no adjoint radiance: the replay never runs
+                    } else if (ap.render_1) {
 #pragma unroll
                         for (int c = 0; c < Cd; ++c) dl[c] = ap.grad1[c] * nf;
                     } else {

@@ -28,9 +28,14 @@ template <> int pool_slots<INST_SPEC, INST_MODE>() { return PoolL<INST_SPEC>::P;
 #define INST_VARIANT 0
 #endif
 template <> void launch_k_adjoint_pool<INST_SPEC, INST_VARIANT>(const DScene &scene, const LaunchParams &lp, const AdjParams &ap, unsigned blocks, unsigned threads, cudaStream_t st) {
-    cudaFuncSetAttribute(k_adjoint_pool<INST_SPEC, INST_VARIANT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
     cudaMemcpyToSymbolAsync(sc, &scene, sizeof(DScene), 0, cudaMemcpyHostToDevice, st);
-    k_adjoint_pool<INST_SPEC, INST_VARIANT><<<blocks, threads, apool_smem_bytes<INST_SPEC>(), st>>>(lp, ap);
+    if (ap.primal_only) {
+        cudaFuncSetAttribute(k_adjoint_pool<INST_SPEC, INST_VARIANT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+        k_adjoint_pool<INST_SPEC, INST_VARIANT, true><<<blocks, threads, apool_smem_bytes<INST_SPEC>(), st>>>(lp, ap);
+    } else {
+        cudaFuncSetAttribute(k_adjoint_pool<INST_SPEC, INST_VARIANT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+        k_adjoint_pool<INST_SPEC, INST_VARIANT, false><<<blocks, threads, apool_smem_bytes<INST_SPEC>(), st>>>(lp, ap);
+    }
 }
 #if INST_VARIANT == 0
 template <> int adjoint_pool_slots<INST_SPEC>() { return APoolL<INST_SPEC>::P; }

@@ -426,10 +426,31 @@ static bool forward_uses_pool(const mib_scene *s) {
     return pool;
 }
 
+template <int SPEC> static void launch_adjoint(mib_scene *s, const LaunchParams &lp, const AdjParams &ap);   // mib_api_adjoint.inc
+
+// Primal rendering with a prb integrator (mi.render / render_1 before backward(), the per-lane dump of the parity tests): the
+// adjoint pool kernel in its primal-only mode (apool.cuh) -- the same stages the backward launch replays, about twice as fast as
+// the one-thread-one-path walk.  MIB_PRB_PRIMAL_KERNEL=thread (or MIB_ADJOINT_KERNEL=thread) keeps the per-thread kernel.
+static bool prb_primal_uses_pool() {
+    const char *k = getenv("MIB_PRB_PRIMAL_KERNEL"), *a = getenv("MIB_ADJOINT_KERNEL");
+    return !(k && strcmp(k, "thread") == 0) && !(a && strcmp(a, "thread") == 0);
+}
+
 template <int SPEC, int MODE>
 static void launch_forward(mib_scene *s, const LaunchParams &lp) {
     if constexpr (MODE <= 1) {
         if (forward_uses_pool(s)) { launch_forward_pool<SPEC, MODE>(s, lp); return; }
+    }
+    if constexpr (MODE == 2 || MODE == 3) {
+        if (prb_primal_uses_pool()) {
+            AdjParams ap;
+            ap.grad_image = nullptr;
+            ap.render_1 = 0;
+            ap.primal_only = 1;
+            for (int i = 0; i < 4; ++i) ap.grad1[i] = 0.f;
+            launch_adjoint<SPEC>(s, lp, ap);
+            return;
+        }
     }
     uint64_t lanes = lp.lane_end - lp.lane_begin;
     uint64_t threads = (lanes + lp.spt - 1) / lp.spt;
