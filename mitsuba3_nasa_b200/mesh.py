@@ -16,7 +16,7 @@ import os
 
 import numpy as np
 
-LEAF = 4
+LEAF = int(os.environ.get('MIB_BVH_LEAF', '4'))       # triangles per leaf (MIB_BVH_LEAF: A/B runs, profiles/coverage_bench.py)
 INNER = 0x80000000
 
 
