@@ -107,10 +107,10 @@ def xml_cases():
     }
 
 
-def fd_scene(albedo, integrator='volpathaos', spp=64):
+def fd_scene(albedo, integrator='volpathaos', spp=64, sigma_t=0.6):
     d = scenes.c1_homogeneous_cube(res=1, spp=spp, max_depth=12)
     d['integrator'] = {'type': integrator, 'max_depth': 12, 'rr_depth': 1000}
-    d['medium1']['sigma_t'] = 0.6
+    d['medium1']['sigma_t'] = sigma_t
     d['medium1']['albedo'] = albedo
     d['medium1']['phase'] = {'type': 'rayleigh'}
     d['emitter'] = {'type': 'directional', 'direction': [0.3, -0.2, -1.0], 'irradiance': 1.0}
@@ -260,6 +260,8 @@ def cases():
     # directional.cpp's ds.dist = inf -- reproduced by the oracle, and the reason the fork has volpathaos.)
     for tag, albedo in (('minus', 0.79), ('plus', 0.81)):
         c['fd_ref_albedo_' + tag] = dict(variant='scalar_mono_polarized', scene=fd_scene(albedo), spp=200000, seed=1, kind='render1')
+    for tag, sigma_t in (('minus', 0.57), ('plus', 0.63)):
+        c['fd_ref_sigma_t_' + tag] = dict(variant='scalar_mono_polarized', scene=fd_scene(0.8, sigma_t=sigma_t), spp=200000, seed=1, kind='render1')
     # radiancemeter looking through the cube
     d = scenes.c1_homogeneous_cube(res=1, spp=64, max_depth=16)
     d['sensor'] = {'type': 'radiancemeter', 'origin': [0.2, 0.1, 4.0], 'direction': [-0.05, 0.0, -1.0],

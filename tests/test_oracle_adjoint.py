@@ -161,9 +161,16 @@ def test_prb_volpathaos_albedo_gradient_against_finite_differences_of_the_refere
     spp = 1 << 17
     o = OracleScene(S.load_dict(scalar_cases.fd_scene(0.8, integrator='prb_volpathaos', spp=64), 'llvm_ad_mono_polarized'))
     o.render_1_backward(3, spp, [1.0, 0, 0, 0], nthreads=8)
-    g = o.grad_get_scalar(0)[0]
+    gs = o.grad_get_scalar(0)
+    g = gs[0]
     print("adjoint %.6g, reference FD %.6g, quotient %.4f" % (g, fd[0], g / fd[0]))
     assert abs(g / fd[0] - 0.8) < 0.05 * 0.8
+    # the same for sigma_t (reference render_1 at sigma_t 0.57 / 0.63): the literal gradient mixes unbiased transmittance terms with
+    # scattering terms that carry the albedo factor (measured quotient 0.919); the unbiased switch must give 1
+    lo_s, hi_s = (gold['fd_ref_sigma_t_' + t].reshape(4, 4)[:, 0].astype(np.float64) for t in ('minus', 'plus'))
+    fd_s = (hi_s - lo_s) / 0.06
+    print("sigma_t: adjoint %.6g, reference FD %.6g, quotient %.4f" % (gs[3], fd_s[0], gs[3] / fd_s[0]))
+    assert 0.8 < gs[3] / fd_s[0] < 1.0
     code = r'''
 import sys
 sys.path.insert(0, %r); sys.path.insert(0, %r)
@@ -172,10 +179,11 @@ from mitsuba3_nasa_b200 import scene as S
 from orc import OracleScene
 o = OracleScene(S.load_dict(scalar_cases.fd_scene(0.8, integrator='prb_volpathaos', spp=64), 'llvm_ad_mono_polarized'))
 o.render_1_backward(3, 1 << 17, [1.0, 0, 0, 0], nthreads=8)
-print("GRAD", o.grad_get_scalar(0)[0])
+g = o.grad_get_scalar(0)
+print("GRAD", g[0], g[3])
 ''' % (ROOT, os.path.join(ROOT, "tests"))
     out = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, ORC_PRB_AOS_UNBIASED="1"), capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stderr
-    g1 = float(out.stdout.split("GRAD")[1])
-    print("unbiased switch: adjoint %.6g, quotient %.4f" % (g1, g1 / fd[0]))
-    assert abs(g1 / fd[0] - 1.0) < 0.05
+    g1, g3 = (float(x) for x in out.stdout.split("GRAD")[1].split())
+    print("unbiased switch: albedo quotient %.4f, sigma_t quotient %.4f" % (g1 / fd[0], g3 / fd_s[0]))
+    assert abs(g1 / fd[0] - 1.0) < 0.05 and abs(g3 / fd_s[0] - 1.0) < 0.05
