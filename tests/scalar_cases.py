@@ -118,6 +118,26 @@ def fd_scene(albedo, integrator='volpathaos', spp=64, sigma_t=0.6):
     return d
 
 
+def fd_grid(sign=0, h=0.05):
+    """5^3 density grid, its perturbation direction v, and grid + sign * h * v; voxel (0, 0, 0) pins the majorant."""
+    rng = np.random.default_rng(3)
+    grid = rng.uniform(0.2, 0.8, size=(5, 5, 5, 1)).astype(np.float32)
+    grid[0, 0, 0, 0] = 1.0
+    v = rng.uniform(0.0, 1.0, size=grid.shape).astype(np.float32)
+    v[0, 0, 0, 0] = 0
+    return (grid + np.float32(sign * h) * v).astype(np.float32), v
+
+
+def fd_grid_scene(sign=0, integrator='volpathaos', spp=64):
+    g, _ = fd_grid(sign)
+    d = scenes.c3_cloud(res=1, spp=spp, max_depth=12, integrator=integrator, grid=g, optical_depth=4.0, albedo=0.9, phase={'type': 'rayleigh'})
+    d['integrator']['rr_depth'] = 1000
+    d['object']['interior']['scale'] = 2.0
+    d['sensor']['film']['pixel_format'] = 'luminance'
+    d['emitter'] = {'type': 'directional', 'direction': [0.3, -0.2, -1.0], 'irradiance': 1.0}
+    return d
+
+
 def cases():
     c = {}
     # C1 (BASELINE configs[0]) at 32 x 32 x 16: homogeneous HG cube, volpath, rgb
@@ -260,6 +280,8 @@ def cases():
     # directional.cpp's ds.dist = inf -- reproduced by the oracle, and the reason the fork has volpathaos.)
     for tag, albedo in (('minus', 0.79), ('plus', 0.81)):
         c['fd_ref_albedo_' + tag] = dict(variant='scalar_mono_polarized', scene=fd_scene(albedo), spp=200000, seed=1, kind='render1')
+    for tag, sign in (('minus', -1), ('plus', +1)):
+        c['fd_ref_grid_' + tag] = dict(variant='scalar_mono_polarized', scene=fd_grid_scene(sign), spp=400000, seed=1, kind='render1')
     for tag, sigma_t in (('minus', 0.57), ('plus', 0.63)):
         c['fd_ref_sigma_t_' + tag] = dict(variant='scalar_mono_polarized', scene=fd_scene(0.8, sigma_t=sigma_t), spp=200000, seed=1, kind='render1')
     # radiancemeter looking through the cube
