@@ -222,3 +222,23 @@ def test_kernel_gradient_against_finite_differences_of_the_reference():
     g = dev.grad_get_scalar(0)[0]
     print("kernel gradient %.6g, reference FD %.6g, quotient %.4f" % (g, fd[0], g / fd[0]))
     assert abs(g / fd[0] - 0.8) < 0.05 * 0.8
+
+
+def test_kernel_grid_gradient_against_finite_differences_of_the_reference():
+    """The C4 kind of gradient on the CUDA adjoint kernel against the reference's own finite differences (render_1 of the unmodified
+    volpathaos on a 5^3 grid +/- 0.05 v; tests/golden/scalar_ref.npz fd_ref_grid_*, tests/test_oracle_adjoint.py): the literal
+    prb_volpathaos sits 13 % above the true derivative (the oracle's unbiased switch gives 1.013), and the kernel must sit where the
+    oracle's literal restatement sits."""
+    import os
+    import scalar_cases
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "scalar_ref.npz"))
+    lo, hi = (gold['fd_ref_grid_' + t].reshape(4, 4)[:, 0].astype(np.float64) for t in ('minus', 'plus'))
+    fd = (hi[0] - lo[0]) / 0.1
+    sc = S.load_dict(scalar_cases.fd_grid_scene(0, integrator='prb_volpathaos'), 'llvm_ad_mono_polarized')
+    dev = _lib.DeviceScene(sc, 0)
+    dev.grad_zero()
+    dev.render_1_backward(3, 1 << 22, [1.0, 0, 0, 0])
+    g = np.asarray(dev.grad_get(sc.desc.media[0].sigma_t.buffer, 125), np.float64)
+    q = float(g @ scalar_cases.fd_grid()[1].reshape(-1).astype(np.float64)) / fd
+    print("kernel <gradient, v> / reference FD = %.4f" % q)
+    assert abs(q - 1.13) < 0.05
