@@ -232,6 +232,10 @@ typedef struct mib_integrator {
                               * M > 0: "fast" mode, M^3 supergrid of local majorants + DDA free-flight sampling:
                               * unbiased, but no longer the reference's random sequence -- agreement is statistical only */
     int32_t spectral_mis;    /* volpathmis: `use_spectral_mis` (volpathmis.cpp:93, default 1): n x n weight matrices; 0: one spectrum */
+    int32_t unbiased_adjoint; /* prb_volpathaos, extension (property `unbiased`, default 0 = the reference): divide the replayed radiance by
+                               * the step's weight as prbvolpath does (prbvolpath.py:192-194) instead of prb_volpathaos.py:214-217's
+                               * `I = replace_grad(1, weight)`; the gradient then agrees with finite differences of the reference's
+                               * own volpathaos (tests/test_oracle_adjoint.py), which the reference's adjoint does not */
 } mib_integrator;
 
 typedef struct mib_scene_desc {

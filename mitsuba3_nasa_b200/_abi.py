@@ -83,7 +83,7 @@ class Sensor(C.Structure):
 
 class Integrator(C.Structure):
     _fields_ = [("type", i32), ("max_depth", i32), ("rr_depth", i32), ("hide_emitters", i32),
-                ("rng_arg_order", i32), ("double_phase_quirk", i32), ("majorant_res", i32), ("spectral_mis", i32)]
+                ("rng_arg_order", i32), ("double_phase_quirk", i32), ("majorant_res", i32), ("spectral_mis", i32), ("unbiased_adjoint", i32)]
 
 
 class SceneDesc(C.Structure):

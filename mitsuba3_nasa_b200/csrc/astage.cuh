@@ -138,11 +138,12 @@ MIB_D void prb_nee_step(Pcg32 &rng, Counters &cnt, Sink &sink, uint32_t channel,
             if (trm[0] > 0.f) {
                 if (homog) {
                     float sB = ((cs0 * dl[0] + cs1 * dl[1]) + cs2 * dl[2]) + cs3 * dl[3];
-                    cf[0] = ((sB * adj[0]) * (-t_h * md_scale)) * tr_h;
+                    cf[0] = ((sB * adj[0]) * (-t_h * md_scale)) * (sc.d.integrator.unbiased_adjoint ? 1.f : tr_h);
                     any = true;
                 } else if (active_medium && het_step) {
                     float s = ((dl[0] + dl[1]) + dl[2]) + dl[3];
                     cf[0] = div_((s * adj[0]) * (-md_scale), mei.maj[0]);
+                    if (sc.d.integrator.unbiased_adjoint) cf[0] = div_(cf[0], div_(mei.sigma_n[0], mei.maj[0]));   // the step's multiplier
                     any = true;
                 }
             }
@@ -309,7 +310,10 @@ MIB_D int prb_main(Pcg32 &rng, Counters &cnt, Sink &sink, PrbState<SPEC> &st) {
     if (backward && was_medium) {
         const mib_medium &md = sc.d.media[medium];
         float base[NC];
-        if (AOS) base[0] = dl_sum * L[0];                               // sum_all(dL @ L), no division (file header)
+        if (AOS) {
+            base[0] = dl_sum * L[0];                                    // sum_all(dL @ L), no division (file header)
+            if (sc.d.integrator.unbiased_adjoint) base[0] = div_(base[0], fmaxf(1e-8f, weight[0]));   // extension: prbvolpath's form
+        }
         else {
 #pragma unroll
             for (int c = 0; c < NC; ++c) base[c] = dl[c] * div_(L[c], fmaxf(1e-8f, weight[c]));

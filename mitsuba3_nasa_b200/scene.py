@@ -933,6 +933,9 @@ class Scene:
         out.double_phase_quirk = 1 if it.type == 'volpath' else 0
         # backend extension (not in the fork): M^3 supergrid of local majorants, 0 = the reference's global majorant
         out.majorant_res = int(pr.get('majorant_resolution', 0))
+        if it.type == 'prb_volpathaos':
+            # extension, off by default: the gradient that agrees with finite differences of volpathaos (mi_b200.h unbiased_adjoint)
+            out.unbiased_adjoint = int(bool(pr.get('unbiased', False)))
         if out.majorant_res < 0 or out.majorant_res > 128:
             raise PluginError("\"majorant_resolution\" must be in [0, 128]")
         if it.type == 'prb_volpathaos' and self.spectrum != A.SPEC_MONO_POLARIZED:

@@ -52,7 +52,9 @@ template <int SPEC> struct Adjoint {
     Counters &cnt;
     GradSink *sink = nullptr;
     bool handle_null_scattering = false, nee_handle_homogeneous = false;
-    bool unbiased_check = std::getenv("ORC_PRB_AOS_UNBIASED") != nullptr;   // tests only: see tests/test_oracle_adjoint.py
+    // prb_volpathaos with the division by the step's weight (mib_integrator.unbiased_adjoint, an extension; ORC_PRB_AOS_UNBIASED in the
+    // environment forces it): see tests/test_oracle_adjoint.py
+    bool unbiased_check = std::getenv("ORC_PRB_AOS_UNBIASED") != nullptr || sc.d.integrator.unbiased_adjoint != 0;
 
     Adjoint(const Scene &s, Sampler &sm, Counters &c) : sc(s), sampler(sm), cnt(c) {
         // prepare_scene (prbvolpath.py:76-89)

@@ -242,3 +242,49 @@ def test_kernel_grid_gradient_against_finite_differences_of_the_reference():
     q = float(g @ scalar_cases.fd_grid()[1].reshape(-1).astype(np.float64)) / fd
     print("kernel <gradient, v> / reference FD = %.4f" % q)
     assert abs(q - 1.13) < 0.05
+
+
+def test_unbiased_extension_equals_the_oracle_and_the_reference_finite_differences():
+    """prb_volpathaos with the integrator property `unbiased = true` (an extension, mi_b200.h unbiased_adjoint: the replayed radiance is
+    divided by the step's weight as prbvolpath does): kernel equals the oracle with the same flag, and both agree with finite
+    differences of the reference's own volpathaos -- albedo and the cells of a density grid -- within the reference's 5 %."""
+    import os
+    import scalar_cases
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "scalar_ref.npz"))
+
+    def stokes_i(name):
+        return gold[name].reshape(4, 4)[0, 0].astype(np.float64)
+    # parity with the oracle, homogeneous scalars and a grid
+    d = scalar_cases.fd_scene(0.8, integrator='prb_volpathaos')
+    d['integrator']['unbiased'] = True
+    sc = S.load_dict(d, 'llvm_ad_mono_polarized')
+    assert sc.desc.integrator.unbiased_adjoint == 1
+    dev, orc = _lib.DeviceScene(sc, 0), OracleScene(sc)
+    dev.grad_zero()
+    dev.render_1_backward(3, 4096, [0.3, -1.0, 0.5, 0.45])
+    orc.render_1_backward(3, 4096, [0.3, -1.0, 0.5, 0.45])
+    g, o = dev.grad_get_scalar(0), orc.grad_get_scalar(0)
+    print("scalar grads gpu", g, "oracle", o)
+    assert np.allclose(g, o, rtol=GRAD_TOL, atol=GRAD_TOL * np.abs(o).max())
+    # against the reference's finite differences
+    dev.grad_zero()
+    dev.render_1_backward(3, 1 << 22, [1.0, 0, 0, 0])
+    g = dev.grad_get_scalar(0)
+    q_albedo = g[0] / ((stokes_i('fd_ref_albedo_plus') - stokes_i('fd_ref_albedo_minus')) / 0.02)
+    q_sigma_t = g[3] / ((stokes_i('fd_ref_sigma_t_plus') - stokes_i('fd_ref_sigma_t_minus')) / 0.06)
+    d = scalar_cases.fd_grid_scene(0, integrator='prb_volpathaos')
+    d['integrator']['unbiased'] = True
+    sc = S.load_dict(d, 'llvm_ad_mono_polarized')
+    dev, orc = _lib.DeviceScene(sc, 0), OracleScene(sc)
+    slot = sc.desc.media[0].sigma_t.buffer
+    dev.grad_zero()
+    dev.render_1_backward(5, 4096, [1.0, 0, 0, 0])
+    orc.render_1_backward(5, 4096, [1.0, 0, 0, 0])
+    gg, og = dev.grad_get(slot, 125), orc.grad_get(slot, 125)
+    assert np.allclose(gg, og, rtol=GRAD_TOL, atol=GRAD_TOL * np.abs(og).max())
+    dev.grad_zero()
+    dev.render_1_backward(3, 1 << 22, [1.0, 0, 0, 0])
+    gg = np.asarray(dev.grad_get(slot, 125), np.float64)
+    q_grid = float(gg @ scalar_cases.fd_grid()[1].reshape(-1).astype(np.float64)) / ((stokes_i('fd_ref_grid_plus') - stokes_i('fd_ref_grid_minus')) / 0.1)
+    print("kernel, unbiased, over the reference's FD: albedo %.4f, sigma_t %.4f, grid %.4f" % (q_albedo, q_sigma_t, q_grid))
+    assert abs(q_albedo - 1) < 0.05 and abs(q_sigma_t - 1) < 0.05 and abs(q_grid - 1) < 0.05
